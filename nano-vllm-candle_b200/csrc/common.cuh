@@ -1,0 +1,104 @@
+// Shared declarations for the nvc_b200 CUDA library (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <cuda.h>
+#include <stdint.h>
+#include <string>
+
+#include "../../include/nvc_b200.h"
+#include "../../include/nvc_b200_engine.h"
+
+#define NVC_CUDA_CHECK(ctx, expr)                                               \
+  do {                                                                          \
+    cudaError_t _e = (expr);                                                    \
+    if (_e != cudaSuccess) {                                                    \
+      nvc_set_error((ctx), std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+      return NVC_CUDA_ERROR_BASE + (int)_e;                                     \
+    }                                                                           \
+  } while (0)
+
+#define NVC_REQUIRE(ctx, cond, code, msg)                                       \
+  do {                                                                          \
+    if (!(cond)) {                                                              \
+      nvc_set_error((ctx), std::string(__func__) + ": " + (msg));               \
+      return (code);                                                            \
+    }                                                                           \
+  } while (0)
+
+typedef CUresult (*nvc_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                        const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                        const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                        CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+struct nvc_nccl_api;  // collectives.cu
+
+struct nvc_ctx {
+  int device = 0;
+  int tp_rank = 0;
+  int tp_size = 1;
+  int num_sms = 148;
+  std::string last_error;
+  nvc_encode_tiled_fn encode_tiled = nullptr;
+  // split-K scratch for the tcgen05 GEMM (fp32 partial tiles + per-tile arrival counters)
+  float* gemm_ws = nullptr;
+  size_t gemm_ws_bytes = 0;
+  int* gemm_counters = nullptr;
+  int gemm_num_counters = 0;
+  // tensor-parallel communicator (NULL when tp_size == 1)
+  nvc_nccl_api* nccl = nullptr;
+  void* nccl_comm = nullptr;
+};
+
+void nvc_set_error(nvc_ctx* ctx, const std::string& msg);
+
+static inline cudaStream_t nvc_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+// ---------------------------------------------------------------------------------------
+// device helpers
+// ---------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);   // .x = lo (low 16 bits), .y = hi
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+__device__ __forceinline__ void unpack8(const uint4& u, float* f) {
+  f[0] = bf16_lo(u.x); f[1] = bf16_hi(u.x); f[2] = bf16_lo(u.y); f[3] = bf16_hi(u.y);
+  f[4] = bf16_lo(u.z); f[5] = bf16_hi(u.z); f[6] = bf16_lo(u.w); f[7] = bf16_hi(u.w);
+}
+
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  uint4 u;
+  u.x = pack_bf16(f[0], f[1]); u.y = pack_bf16(f[2], f[3]);
+  u.z = pack_bf16(f[4], f[5]); u.w = pack_bf16(f[6], f[7]);
+  return u;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ uint4 ldg_nc_u4(const void* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+  return r;
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+#endif  // __CUDACC__

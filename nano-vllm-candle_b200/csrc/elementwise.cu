@@ -1,0 +1,443 @@
+// HBM-bound kernels of the Qwen3 forward path: embedding gather, fused add+RMSNorm,
+// q/k-norm + RoPE + KV-cache scatter, stand-alone slot-mapping scatter, SiLU*mul,
+// last-token row gather, argmax.  All use 16-byte vector accesses, one pass over the
+// data, fp32 math, warp-shuffle reductions.  Each entry point cites the reference code it
+// replaces in include/nvc_b200.h.
+#include "common.cuh"
+
+#include <cmath>
+#include <vector>
+
+// ------------------------------------------------------------------------------------
+// K0 embed gather: out[n,:] = table[ids[n],:]        (src/models/qwen3.rs:465-468)
+// one warp per 512-byte slice of a row; 16 B per lane.
+// ------------------------------------------------------------------------------------
+__global__ void embed_gather_kernel(const int32_t* __restrict__ ids, const uint4* __restrict__ table,
+                                    uint4* __restrict__ out, int N, int vec_per_row) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t total = (int64_t)N * vec_per_row;
+  if (i >= total) return;
+  int n = (int)(i / vec_per_row);
+  int c = (int)(i - (int64_t)n * vec_per_row);
+  int id = __ldg(ids + n);
+  out[i] = __ldg(table + (int64_t)id * vec_per_row + c);
+}
+
+extern "C" int nvc_embed_gather(nvc_ctx* ctx, const int32_t* ids, const nvc_bf16* table, nvc_bf16* out,
+                                int N, int H, int V, void* stream) {
+  NVC_REQUIRE(ctx, ctx && ids && table && out, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, N >= 0 && H > 0 && V > 0, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, H % 8 == 0, NVC_ESHAPE, "H must be a multiple of 8");
+  if (N == 0) return NVC_OK;
+  int vpr = H / 8;
+  int64_t total = (int64_t)N * vpr;
+  int threads = 256;
+  int64_t blocks = (total + threads - 1) / threads;
+  embed_gather_kernel<<<(unsigned)blocks, threads, 0, nvc_stream(stream)>>>(
+      ids, reinterpret_cast<const uint4*>(table), reinterpret_cast<uint4*>(out), N, vpr);
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  return NVC_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// K1 fused add + RMSNorm                              (src/layers/layernorm.rs:44-60)
+// one CTA per row, one 8-element vector per thread (H <= 8192) kept in registers, or a
+// strided loop for wider rows (second pass re-reads residual_out from L2).
+// Algorithmic bytes per row: H * (2 [x] + 4 [res in] + 4 [res out] + 2 [out]).
+// ------------------------------------------------------------------------------------
+template <bool kLoop>
+__global__ void __launch_bounds__(1024)
+fused_add_rmsnorm_kernel(const uint4* __restrict__ x, const float4* __restrict__ res_in,
+                         float4* __restrict__ res_out, const uint4* __restrict__ w, float eps,
+                         uint4* __restrict__ out, int H) {
+  __shared__ float red[32];
+  const int row = blockIdx.x;
+  const int nvec = H >> 3;
+  const int64_t vbase = (int64_t)row * nvec;
+  float s[8];
+  float ss = 0.f;
+  if (!kLoop) {
+    const int v = threadIdx.x;
+    if (v < nvec) {
+      unpack8(ldg_nc_u4(x + vbase + v), s);
+      if (res_in) {
+        float4 a = res_in[(vbase + v) * 2], b = res_in[(vbase + v) * 2 + 1];
+        s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
+        s[4] += b.x; s[5] += b.y; s[6] += b.z; s[7] += b.w;
+      }
+      if (res_out) {
+        res_out[(vbase + v) * 2] = make_float4(s[0], s[1], s[2], s[3]);
+        res_out[(vbase + v) * 2 + 1] = make_float4(s[4], s[5], s[6], s[7]);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ss += s[i] * s[i];
+    }
+  } else {
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
+      unpack8(ldg_nc_u4(x + vbase + v), s);
+      if (res_in) {
+        float4 a = res_in[(vbase + v) * 2], b = res_in[(vbase + v) * 2 + 1];
+        s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
+        s[4] += b.x; s[5] += b.y; s[6] += b.z; s[7] += b.w;
+      }
+      if (res_out) {
+        res_out[(vbase + v) * 2] = make_float4(s[0], s[1], s[2], s[3]);
+        res_out[(vbase + v) * 2 + 1] = make_float4(s[4], s[5], s[6], s[7]);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) ss += s[i] * s[i];
+    }
+  }
+  ss = warp_sum(ss);
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) red[wid] = ss;
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  float tot = (lane < nw) ? red[lane] : 0.f;
+  tot = warp_sum(tot);
+  // reference: x * (1 / sqrt(mean + eps))
+  const float rstd = 1.0f / sqrtf(tot / (float)H + eps);
+  if (!kLoop) {
+    const int v = threadIdx.x;
+    if (v < nvec) {
+      float wf[8];
+      unpack8(__ldg(w + v), wf);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s[i] = s[i] * rstd * wf[i];
+      out[vbase + v] = pack8(s);
+    }
+  } else {
+    for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
+      if (res_out) {   // re-read the sum we just wrote (same thread wrote it)
+        float4 a = res_out[(vbase + v) * 2], b = res_out[(vbase + v) * 2 + 1];
+        s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+      } else {
+        unpack8(ldg_nc_u4(x + vbase + v), s);
+        if (res_in) {
+          float4 a = res_in[(vbase + v) * 2], b = res_in[(vbase + v) * 2 + 1];
+          s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
+          s[4] += b.x; s[5] += b.y; s[6] += b.z; s[7] += b.w;
+        }
+      }
+      float wf[8];
+      unpack8(__ldg(w + v), wf);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) s[i] = s[i] * rstd * wf[i];
+      out[vbase + v] = pack8(s);
+    }
+  }
+}
+
+extern "C" int nvc_fused_add_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x, const float* residual_in,
+                                     float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out,
+                                     int N, int H, void* stream) {
+  NVC_REQUIRE(ctx, ctx && x && w && out, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, N >= 0 && H > 0, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, H % 8 == 0 && H <= 65536, NVC_ESHAPE, "H must be a multiple of 8 and <= 65536");
+  if (N == 0) return NVC_OK;
+  const int nvec = H / 8;
+  auto xs = reinterpret_cast<const uint4*>(x);
+  auto ri = reinterpret_cast<const float4*>(residual_in);
+  auto ro = reinterpret_cast<float4*>(residual_out);
+  auto ws = reinterpret_cast<const uint4*>(w);
+  auto os = reinterpret_cast<uint4*>(out);
+  if (nvec <= 1024) {
+    int threads = ((nvec + 31) / 32) * 32;
+    fused_add_rmsnorm_kernel<false><<<N, threads, 0, nvc_stream(stream)>>>(xs, ri, ro, ws, eps, os, H);
+  } else {
+    fused_add_rmsnorm_kernel<true><<<N, 1024, 0, nvc_stream(stream)>>>(xs, ri, ro, ws, eps, os, H);
+  }
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  return NVC_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// rope table (host math = the reference's f32 powf/cos/sin)   (rotary_embedding.rs:56-80)
+// ------------------------------------------------------------------------------------
+extern "C" int nvc_rope_table_init_sync(nvc_ctx* ctx, float theta, int head_dim, int max_pos, float* out) {
+  NVC_REQUIRE(ctx, ctx && out, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, head_dim > 0 && head_dim % 2 == 0 && max_pos > 0, NVC_EINVAL, "bad sizes");
+  const int half = head_dim / 2;
+  std::vector<float> inv_freq(half);
+  for (int j = 0; j < half; ++j) {
+    float exponent = (2.0f * (float)j) / (float)head_dim;
+    inv_freq[j] = 1.0f / powf(theta, exponent);
+  }
+  std::vector<float> tab((size_t)max_pos * head_dim);
+  for (int p = 0; p < max_pos; ++p) {
+    float* row = tab.data() + (size_t)p * head_dim;
+    for (int j = 0; j < half; ++j) {
+      float ang = (float)p * inv_freq[j];
+      row[j] = cosf(ang);
+      row[half + j] = sinf(ang);
+    }
+  }
+  NVC_CUDA_CHECK(ctx, cudaMemcpy(out, tab.data(), tab.size() * sizeof(float), cudaMemcpyHostToDevice));
+  return NVC_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// K2 q/k RMSNorm + RoPE + KV-cache scatter, one pass over the fused qkv buffer.
+// (src/models/qwen3.rs:206-234, src/layers/rotary_embedding.rs:82-107, N3)
+// 8 lanes per (token, head) unit: lane l owns elements [8l, 8l+8) and [64+8l, 64+8l+8).
+// Algorithmic bytes per token: (nh+2kv)*256 read + (nh+kv)*256 written in place
+//                              + 2*kv*256 written to the cache.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+qk_norm_rope_store_kernel(uint4* __restrict__ qkv, const uint4* __restrict__ qw, const uint4* __restrict__ kw,
+                          float eps, const float4* __restrict__ cos_sin, const int32_t* __restrict__ positions,
+                          const int32_t* __restrict__ slot_mapping, uint4* __restrict__ k_cache,
+                          uint4* __restrict__ v_cache, int N, int nh, int kv) {
+  const int units_per_tok = nh + 2 * kv;
+  const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
+  const int l = threadIdx.x & 7;
+  const bool active = unit < (int64_t)N * units_per_tok;
+  // all 8 lanes of a unit share `active`; inactive units still take part in shuffles below
+  const int n = active ? (int)(unit / units_per_tok) : 0;
+  const int u = active ? (int)(unit - (int64_t)n * units_per_tok) : 0;
+  uint4* row = qkv + ((int64_t)n * units_per_tok + u) * 16;   // 16 uint4 per 128-element head
+  const int slot = (slot_mapping != nullptr && active) ? __ldg(slot_mapping + n) : -1;
+
+  if (u >= nh + kv) {   // V head: copy to the cache (bit-exact)
+    if (active && slot >= 0) {
+      const int h = u - nh - kv;
+      uint4* dst = v_cache + ((int64_t)slot * kv + h) * 16;
+      dst[l] = row[l];
+      dst[l + 8] = row[l + 8];
+    }
+    return;
+  }
+  // NOTE: a warp never mixes the early-returned V units with q/k units only if the unit
+  // kinds align to warp boundaries, which they do not in general; the shuffles below use
+  // an 8-lane mask so they only involve the lanes of this unit.
+  const unsigned mask = 0xffu << ((threadIdx.x & 31) & ~7);
+  float a[8], b[8];
+  if (active) {
+    unpack8(row[l], a);
+    unpack8(row[l + 8], b);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) a[i] = b[i] = 0.f;
+  }
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) ss += a[i] * a[i] + b[i] * b[i];
+  ss += __shfl_xor_sync(mask, ss, 1);
+  ss += __shfl_xor_sync(mask, ss, 2);
+  ss += __shfl_xor_sync(mask, ss, 4);
+  if (!active) return;
+  const float rstd = 1.0f / sqrtf(ss * (1.0f / 128.0f) + eps);
+  const bool is_q = u < nh;
+  float wa[8], wb[8];
+  const uint4* wp = is_q ? qw : kw;
+  unpack8(__ldg(wp + l), wa);
+  unpack8(__ldg(wp + l + 8), wb);
+  const int pos = __ldg(positions + n);
+  const float4* cs = cos_sin + (int64_t)pos * 32;   // 128 floats per position: cos[64], sin[64]
+  float4 c0 = __ldg(cs + 2 * l), c1 = __ldg(cs + 2 * l + 1);
+  float4 s0 = __ldg(cs + 16 + 2 * l), s1 = __ldg(cs + 16 + 2 * l + 1);
+  const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+  const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+  float y1[8], y2[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float x1 = a[i] * rstd * wa[i];
+    const float x2 = b[i] * rstd * wb[i];
+    y1[i] = x1 * c[i] - x2 * s[i];
+    y2[i] = x2 * c[i] + x1 * s[i];
+  }
+  const uint4 o1 = pack8(y1), o2 = pack8(y2);
+  row[l] = o1;
+  row[l + 8] = o2;
+  if (!is_q && slot >= 0) {
+    const int h = u - nh;
+    uint4* dst = k_cache + ((int64_t)slot * kv + h) * 16;
+    dst[l] = o1;
+    dst[l + 8] = o2;
+  }
+}
+
+extern "C" int nvc_qk_norm_rope_store(nvc_ctx* ctx, nvc_bf16* qkv, const nvc_bf16* qw, const nvc_bf16* kw,
+                                      float eps, const float* cos_sin, const int32_t* positions,
+                                      const int32_t* slot_mapping, nvc_bf16* k_cache, nvc_bf16* v_cache,
+                                      int N, int nh, int kv, int hd, void* stream) {
+  NVC_REQUIRE(ctx, ctx && qkv && qw && kw && cos_sin && positions, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, slot_mapping == nullptr || (k_cache && v_cache), NVC_EINVAL, "slot_mapping without caches");
+  NVC_REQUIRE(ctx, N >= 0 && nh > 0 && kv > 0, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, hd == 128, NVC_ESHAPE, "head_dim must be 128");
+  if (N == 0) return NVC_OK;
+  const int64_t units = (int64_t)N * (nh + 2 * kv);
+  const int threads = 256;
+  const int64_t blocks = (units * 8 + threads - 1) / threads;
+  qk_norm_rope_store_kernel<<<(unsigned)blocks, threads, 0, nvc_stream(stream)>>>(
+      reinterpret_cast<uint4*>(qkv), reinterpret_cast<const uint4*>(qw), reinterpret_cast<const uint4*>(kw),
+      eps, reinterpret_cast<const float4*>(cos_sin), positions, slot_mapping,
+      reinterpret_cast<uint4*>(k_cache), reinterpret_cast<uint4*>(v_cache), N, nh, kv);
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  return NVC_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// K2' stand-alone slot-mapping scatter (N3).  16 B per thread; bit-exact copy.
+// Algorithmic bytes per token: 2 * kv * hd * 2 read + the same written.
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+store_kvcache_kernel(const uint4* __restrict__ k, const uint4* __restrict__ v, int ld_vec,
+                     uint4* __restrict__ k_cache, uint4* __restrict__ v_cache,
+                     const int32_t* __restrict__ slot_mapping, int N, int row_vec) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)N * row_vec) return;
+  const int n = (int)(i / row_vec);
+  const int c = (int)(i - (int64_t)n * row_vec);
+  const int slot = __ldg(slot_mapping + n);
+  if (slot < 0) return;
+  k_cache[(int64_t)slot * row_vec + c] = ldg_nc_u4(k + (int64_t)n * ld_vec + c);
+  v_cache[(int64_t)slot * row_vec + c] = ldg_nc_u4(v + (int64_t)n * ld_vec + c);
+}
+
+extern "C" int nvc_store_kvcache(nvc_ctx* ctx, const nvc_bf16* k, const nvc_bf16* v, int ld,
+                                 nvc_bf16* k_cache, nvc_bf16* v_cache, const int32_t* slot_mapping,
+                                 int N, int kv, int hd, void* stream) {
+  NVC_REQUIRE(ctx, ctx && k && v && k_cache && v_cache && slot_mapping, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, N >= 0 && kv > 0 && hd > 0, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, (kv * hd) % 8 == 0 && ld % 8 == 0 && ld >= kv * hd, NVC_ESHAPE, "row must be 16-byte granular");
+  if (N == 0) return NVC_OK;
+  const int row_vec = kv * hd / 8;
+  const int64_t total = (int64_t)N * row_vec;
+  const int threads = 256;
+  store_kvcache_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, nvc_stream(stream)>>>(
+      reinterpret_cast<const uint4*>(k), reinterpret_cast<const uint4*>(v), ld / 8,
+      reinterpret_cast<uint4*>(k_cache), reinterpret_cast<uint4*>(v_cache), slot_mapping, N, row_vec);
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  return NVC_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// K6 SiLU(x[:, :I]) * x[:, I:]                          (src/layers/activation.rs:13-18)
+// Algorithmic bytes per token: I * (4 read + 2 written).
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+silu_and_mul_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int N, int ivec) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)N * ivec) return;
+  const int n = (int)(i / ivec);
+  const int c = (int)(i - (int64_t)n * ivec);
+  float g[8], u[8];
+  unpack8(ldg_nc_u4(x + (int64_t)n * 2 * ivec + c), g);
+  unpack8(ldg_nc_u4(x + (int64_t)n * 2 * ivec + ivec + c), u);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) g[j] = (g[j] / (1.0f + __expf(-g[j]))) * u[j];
+  out[i] = pack8(g);
+}
+
+extern "C" int nvc_silu_and_mul(nvc_ctx* ctx, const nvc_bf16* x, nvc_bf16* out, int N, int I, void* stream) {
+  NVC_REQUIRE(ctx, ctx && x && out, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, N >= 0 && I > 0, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, I % 8 == 0, NVC_ESHAPE, "I must be a multiple of 8");
+  if (N == 0) return NVC_OK;
+  const int ivec = I / 8;
+  const int64_t total = (int64_t)N * ivec;
+  const int threads = 256;
+  silu_and_mul_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, nvc_stream(stream)>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(out), N, ivec);
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  return NVC_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// K7 last-token row gather (hidden bf16 + residual f32)
+// ------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const uint4* __restrict__ x, const float4* __restrict__ res, const int32_t* __restrict__ rows,
+                   uint4* __restrict__ x_out, float4* __restrict__ res_out, int B, int hvec) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)B * hvec) return;
+  const int b = (int)(i / hvec);
+  const int c = (int)(i - (int64_t)b * hvec);
+  const int64_t r = __ldg(rows + b);
+  x_out[i] = x[r * hvec + c];
+  if (res != nullptr) {
+    res_out[i * 2] = res[(r * hvec + c) * 2];
+    res_out[i * 2 + 1] = res[(r * hvec + c) * 2 + 1];
+  }
+}
+
+extern "C" int nvc_gather_rows(nvc_ctx* ctx, const nvc_bf16* x, const float* residual, const int32_t* rows,
+                               nvc_bf16* x_out, float* residual_out, int B, int H, void* stream) {
+  NVC_REQUIRE(ctx, ctx && x && rows && x_out, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, (residual == nullptr) == (residual_out == nullptr), NVC_EINVAL, "residual in/out mismatch");
+  NVC_REQUIRE(ctx, B >= 0 && H > 0 && H % 8 == 0, NVC_ESHAPE, "H must be a multiple of 8");
+  if (B == 0) return NVC_OK;
+  const int hvec = H / 8;
+  const int64_t total = (int64_t)B * hvec;
+  const int threads = 256;
+  gather_rows_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, nvc_stream(stream)>>>(
+      reinterpret_cast<const uint4*>(x), reinterpret_cast<const float4*>(residual), rows,
+      reinterpret_cast<uint4*>(x_out), reinterpret_cast<float4*>(residual_out), B, hvec);
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  return NVC_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// K8 argmax with the reference's tie rule (LAST maximal index)  (llm_engine.rs:135-142)
+// one CTA per row; float4 loads; (value, index) reduced with "greater, or equal and later".
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ void argmax_combine(float& v, int& i, float ov, int oi) {
+  if (ov > v || (ov == v && oi > i)) { v = ov; i = oi; }
+}
+
+__global__ void __launch_bounds__(1024)
+argmax_last_kernel(const float* __restrict__ logits, int ld, int32_t* __restrict__ idx, float* __restrict__ val,
+                   int V, int index_offset) {
+  __shared__ float sv[32];
+  __shared__ int si[32];
+  const float* row = logits + (int64_t)blockIdx.x * ld;
+  float bv = -INFINITY;
+  int bi = -1;
+  const int v4 = V >> 2;
+  const float4* row4 = reinterpret_cast<const float4*>(row);
+  for (int j = threadIdx.x; j < v4; j += blockDim.x) {
+    const float4 f = __ldg(row4 + j);
+    const int base = j << 2;
+    argmax_combine(bv, bi, f.x, base);
+    argmax_combine(bv, bi, f.y, base + 1);
+    argmax_combine(bv, bi, f.z, base + 2);
+    argmax_combine(bv, bi, f.w, base + 3);
+  }
+  for (int j = (v4 << 2) + threadIdx.x; j < V; j += blockDim.x) argmax_combine(bv, bi, __ldg(row + j), j);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    argmax_combine(bv, bi, ov, oi);
+  }
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { sv[wid] = bv; si[wid] = bi; }
+  __syncthreads();
+  if (wid == 0) {
+    const int nw = (blockDim.x + 31) >> 5;
+    bv = lane < nw ? sv[lane] : -INFINITY;
+    bi = lane < nw ? si[lane] : -1;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      argmax_combine(bv, bi, ov, oi);
+    }
+    if (lane == 0) {
+      idx[blockIdx.x] = bi + index_offset;
+      if (val) val[blockIdx.x] = bv;
+    }
+  }
+}
+
+extern "C" int nvc_argmax_last(nvc_ctx* ctx, const float* logits, int ld, int32_t* idx, float* val,
+                               int B, int V, int index_offset, void* stream) {
+  NVC_REQUIRE(ctx, ctx && logits && idx, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, B >= 0 && V > 0 && ld >= V, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, ld % 4 == 0, NVC_ESHAPE, "ld must be a multiple of 4");
+  if (B == 0) return NVC_OK;
+  argmax_last_kernel<<<B, 1024, 0, nvc_stream(stream)>>>(logits, ld, idx, val, V, index_offset);
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  return NVC_OK;
+}

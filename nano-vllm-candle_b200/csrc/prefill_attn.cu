@@ -1,0 +1,292 @@
+// K4: varlen causal flash attention for prefill on tcgen05 / TMEM.
+// Replaces the dense attention of Qwen3Attention::forward (src/models/qwen3.rs:236-277):
+// GQA expand (:240-256), QK^T*scale (:258-259), host-built -1e9 mask + H2D (:260-270),
+// f32 softmax (:271-273), P*V and head merge (:275-277).  No mask tensor, no materialised
+// K/V copies, no [B,nh,T,T] scores.
+//
+// CTA = (128-row q tile, q head, sequence).  Roles:
+//   warp 0   : TMA producer (Q once; K and V tiles of 128 tokens, 2-stage ring), 3-D tensor
+//              maps {head_dim, head, token} so q/k/v are read in place from the fused qkv rows
+//   warp 1   : TMEM allocator + single-thread tcgen05.mma issuer
+//              S = Q K^T  (A, B K-major, 128B swizzle) and O_j = P V_j (B = V is MN-major)
+//   warps 2-5: one thread per q row: tcgen05.ld S, online softmax (log2 domain, fp32),
+//              P -> bf16 -> swizzled smem (A operand of the second MMA), then
+//              acc = acc * alpha + O_j with the output accumulator in registers
+// FLOPs per (sequence, head): 4 * 128 * T^2 / 2 (causal).
+#include "common.cuh"
+#include "ptx.cuh"
+
+int g_nvc_debug[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+extern "C" int nvc_debug_set(int key, int value) {
+  if (key < 0 || key >= 8) return NVC_EINVAL;
+  g_nvc_debug[key] = value;
+  return NVC_OK;
+}
+
+namespace {
+
+constexpr int kThreads = 192;
+constexpr int kQBytes = 128 * 128 * 2;        // 32 KB: two [128][64] swizzled halves
+constexpr int kKVStageBytes = 2 * kQBytes;    // K tile + V tile
+constexpr int kOffQ = 0;
+constexpr int kOffKV = kQBytes;
+constexpr int kOffP = kOffKV + 2 * kKVStageBytes;
+constexpr int kOffBar = kOffP + kQBytes;
+constexpr int kNumBars = 9;                   // q_full, kv_full[2], kv_empty[2], s_full, p_full, o_full, o_empty
+constexpr int kSmemBytes = kOffBar + kNumBars * 8 + 16 + 1024;
+constexpr int kTmemCols = 256;                // S: cols [0,128), O: cols [128,256)
+
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
+                    const __grid_constant__ CUtensorMap tma_v, const int32_t* __restrict__ cu_seqlens,
+                    int nh, int group, float scale_log2e, nvc_bf16* __restrict__ out, int v_lbo, int v_sbo) {
+  const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  const int seq_start = __ldg(cu_seqlens + b);
+  const int seq_len = __ldg(cu_seqlens + b + 1) - seq_start;
+  if (qt * 128 >= seq_len) return;            // whole CTA exits before any allocation
+  const int kvh = h / group;
+  const int n_tiles = qt + 1;                 // causal: kv tiles 0..qt
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* gen = smem_raw + (base - smem_u32(smem_raw));
+  const uint32_t bar0 = base + kOffBar;
+  const uint32_t q_full = bar0;
+  auto kv_full = [&](int s) { return bar0 + 8u * (1 + s); };
+  auto kv_empty = [&](int s) { return bar0 + 8u * (3 + s); };
+  const uint32_t s_full = bar0 + 8u * 5, p_full = bar0 + 8u * 6, o_full = bar0 + 8u * 7, o_empty = bar0 + 8u * 8;
+  const uint32_t tmem_slot = bar0 + 8u * kNumBars;
+  volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen + kOffBar + kNumBars * 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    ptx::tma_prefetch_desc(&tma_q);
+    ptx::tma_prefetch_desc(&tma_k);
+    ptx::tma_prefetch_desc(&tma_v);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      ptx::mbar_init(q_full, 1);
+      for (int s = 0; s < 2; ++s) { ptx::mbar_init(kv_full(s), 1); ptx::mbar_init(kv_empty(s), 1); }
+      ptx::mbar_init(s_full, 1);
+      ptx::mbar_init(p_full, 128);
+      ptx::mbar_init(o_full, 1);
+      ptx::mbar_init(o_empty, 128);
+      ptx::fence_barrier_init();
+    }
+    __syncwarp();
+    ptx::tmem_alloc(tmem_slot, kTmemCols);
+    ptx::tmem_relinquish();
+  }
+  ptx::tcgen05_fence_before();
+  __syncthreads();
+  ptx::tcgen05_fence_after();
+  const uint32_t tmem = *tmem_slot_gen;
+  const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      ptx::mbar_arrive_expect_tx(q_full, kQBytes);
+      ptx::tma_load_3d(base + kOffQ, &tma_q, q_full, 0, h, seq_start + qt * 128);
+      ptx::tma_load_3d(base + kOffQ + 16384, &tma_q, q_full, 64, h, seq_start + qt * 128);
+      for (int j = 0; j < n_tiles; ++j) {
+        const int s = j & 1;
+        ptx::mbar_wait(kv_empty(s), ((j >> 1) & 1) ^ 1u);
+        ptx::mbar_arrive_expect_tx(kv_full(s), kKVStageBytes);
+        const uint32_t kdst = base + kOffKV + s * kKVStageBytes, vdst = kdst + kQBytes;
+        const int row = seq_start + j * 128;
+        ptx::tma_load_3d(kdst, &tma_k, kv_full(s), 0, kvh, row);
+        ptx::tma_load_3d(kdst + 16384, &tma_k, kv_full(s), 64, kvh, row);
+        ptx::tma_load_3d(vdst, &tma_v, kv_full(s), 0, kvh, row);
+        ptx::tma_load_3d(vdst + 16384, &tma_v, kv_full(s), 64, kvh, row);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_qk = ptx::umma_idesc_bf16(128, 128, 0, 0);
+      constexpr uint32_t idesc_pv = ptx::umma_idesc_bf16(128, 128, 0, 1);   // B = V is MN-major
+      auto issue_s = [&](int j) {
+        const int s = j & 1;
+        ptx::mbar_wait(kv_full(s), (j >> 1) & 1);
+        ptx::tcgen05_fence_after();
+        const uint32_t qa = base + kOffQ, ka = base + kOffKV + s * kKVStageBytes;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const uint32_t off = (ks >> 2) * 16384 + (ks & 3) * 32;
+          ptx::umma_bf16_ss(tmem_s, ptx::umma_desc_sw128(qa + off, 16, 1024),
+                            ptx::umma_desc_sw128(ka + off, 16, 1024), idesc_qk, ks != 0);
+        }
+        ptx::umma_commit(s_full);
+      };
+      ptx::mbar_wait(q_full, 0);
+      issue_s(0);
+      for (int j = 0; j < n_tiles; ++j) {
+        ptx::mbar_wait(p_full, j & 1);           // P(j) is in smem and S(j) has been consumed
+        ptx::tcgen05_fence_after();
+        if (j + 1 < n_tiles) issue_s(j + 1);
+        if (j > 0) {
+          ptx::mbar_wait(o_empty, (j - 1) & 1);  // softmax threads are done with O(j-1)
+          ptx::tcgen05_fence_after();
+        }
+        const uint32_t pa = base + kOffP, va = base + kOffKV + (j & 1) * kKVStageBytes + kQBytes;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          // A = P: K-major, 16 kv tokens per step; B = V: MN-major, 16 token rows = 2048 bytes per step
+          const uint32_t poff = (ks >> 2) * 16384 + (ks & 3) * 32;
+          ptx::umma_bf16_ss(tmem_o, ptx::umma_desc_sw128(pa + poff, 16, 1024),
+                            ptx::umma_desc_sw128(va + ks * 2048, v_lbo, v_sbo), idesc_pv, ks != 0);
+        }
+        ptx::umma_commit(o_full);
+        ptx::umma_commit(kv_empty(j & 1));
+      }
+    }
+  } else {
+    // ------------------------------------------------------------ softmax / output warps
+    const int quad = warp & 3;
+    const int r = quad * 32 + lane;                 // row in the q tile
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    float acc[128];
+#pragma unroll
+    for (int i = 0; i < 128; ++i) acc[i] = 0.f;
+    float m = -INFINITY, l = 0.f;
+    uint8_t* p_row = gen + kOffP + r * 128;
+    for (int j = 0; j < n_tiles; ++j) {
+      ptx::mbar_wait(s_full, j & 1);
+      ptx::tcgen05_fence_after();
+      const bool diag = (j == qt);
+      // pass 1: row max
+      float mx = -INFINITY;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32b_x32(tmem_s + lane_addr + c * 32, v);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float x = __uint_as_float(v[i]);
+          if (!diag || (c * 32 + i) <= r) mx = fmaxf(mx, x);
+        }
+      }
+      const float m_new = fmaxf(m, mx * scale_log2e);
+      const float alpha = fast_exp2(m - m_new);
+      float psum = 0.f;
+      // pass 2: p = exp2(s*scale - m), bf16, swizzled store (chunk ^= row % 8)
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32b_x32(tmem_s + lane_addr + c * 32, v);
+        ptx::tmem_ld_wait();
+        float p[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const float x = __uint_as_float(v[i]) * scale_log2e - m_new;
+          p[i] = (!diag || (c * 32 + i) <= r) ? fast_exp2(x) : 0.f;
+          psum += p[i];
+        }
+        // columns [c*32, c*32+32) = half (c>>1), 16-byte chunks ((c&1)*4 .. +4) of this row
+        uint8_t* half_base = p_row + (c >> 1) * 16384;
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const int chunk = (c & 1) * 4 + k4;
+          *reinterpret_cast<uint4*>(half_base + ((chunk ^ (r & 7)) << 4)) = pack8(p + 8 * k4);
+        }
+      }
+      l = l * alpha + psum;
+      m = m_new;
+      ptx::fence_proxy_async_smem();
+      ptx::tcgen05_fence_before();
+      ptx::mbar_arrive(p_full);
+      // O_j = P V_j
+      ptx::mbar_wait(o_full, j & 1);
+      ptx::tcgen05_fence_after();
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32b_x32(tmem_o + lane_addr + c * 32, v);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) acc[c * 32 + i] = acc[c * 32 + i] * alpha + __uint_as_float(v[i]);
+      }
+      ptx::tcgen05_fence_before();
+      ptx::mbar_arrive(o_empty);
+    }
+    const int row_in_seq = qt * 128 + r;
+    if (row_in_seq < seq_len) {
+      const float inv = 1.0f / l;
+      uint4* dst = reinterpret_cast<uint4*>(out + ((int64_t)(seq_start + row_in_seq) * nh + h) * 128);
+#pragma unroll
+      for (int c = 0; c < 16; ++c) {
+        float o[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) o[i] = acc[c * 8 + i] * inv;
+        dst[c] = pack8(o);
+      }
+    }
+    ptx::tcgen05_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tcgen05_fence_after();
+    ptx::tmem_dealloc(tmem, kTmemCols);
+  }
+}
+
+int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, int64_t tokens, int ld) {
+  cuuint64_t gdim[3] = {128, (cuuint64_t)heads, (cuuint64_t)tokens};
+  cuuint64_t gstr[2] = {128 * 2, (cuuint64_t)ld * 2};
+  cuuint32_t box[3] = {64, 1, 128};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = ctx->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstr, box,
+                                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    nvc_set_error(ctx, "cuTensorMapEncodeTiled (attention) failed with CUresult " + std::to_string((int)r));
+    return NVC_EINVAL;
+  }
+  return NVC_OK;
+}
+
+}  // namespace
+
+extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k, int ldk,
+                                       const nvc_bf16* v, int ldv, const int32_t* cu_seqlens, int B,
+                                       int total_tokens, int max_seqlen, int nh, int kv, int hd, float scale,
+                                       nvc_bf16* out, void* stream) {
+  NVC_REQUIRE(ctx, ctx && q && k && v && cu_seqlens && out, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, B >= 0 && total_tokens >= 0 && max_seqlen >= 0 && nh > 0 && kv > 0, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, hd == 128, NVC_ESHAPE, "head_dim must be 128");
+  NVC_REQUIRE(ctx, nh % kv == 0, NVC_ESHAPE, "nh must be a multiple of kv");
+  NVC_REQUIRE(ctx, ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldq >= nh * hd && ldk >= kv * hd && ldv >= kv * hd,
+              NVC_ESHAPE, "row strides must cover the heads and be multiples of 8");
+  NVC_REQUIRE(ctx, ((uintptr_t)q % 16) == 0 && ((uintptr_t)k % 16) == 0 && ((uintptr_t)v % 16) == 0, NVC_EINVAL,
+              "pointers must be 16-byte aligned");
+  NVC_REQUIRE(ctx, ctx->encode_tiled != nullptr, NVC_EDEVICE, "cuTensorMapEncodeTiled unavailable");
+  if (B == 0 || total_tokens == 0 || max_seqlen == 0) return NVC_OK;
+  CUtensorMap tq, tk, tv;
+  int rc = make_tma_heads(ctx, &tq, q, nh, total_tokens, ldq);
+  if (rc) return rc;
+  rc = make_tma_heads(ctx, &tk, k, kv, total_tokens, ldk);
+  if (rc) return rc;
+  rc = make_tma_heads(ctx, &tv, v, kv, total_tokens, ldv);
+  if (rc) return rc;
+  static bool attr_set = false;
+  if (!attr_set) {
+    NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    attr_set = true;
+  }
+  // V (B operand, MN-major, 128B swizzle): LBO = stride between the two 64-wide head-dim
+  // halves (16 KB), SBO = stride between groups of 8 token rows (1 KB).
+  int v_lbo = 16384, v_sbo = 1024;
+  if (g_nvc_debug[0] == 1) { v_lbo = 1024; v_sbo = 16384; }
+  dim3 grid((max_seqlen + 127) / 128, nh, B);
+  prefill_attn_kernel<<<grid, kThreads, kSmemBytes, nvc_stream(stream)>>>(
+      tq, tk, tv, cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out, v_lbo, v_sbo);
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  return NVC_OK;
+}

@@ -68,6 +68,8 @@ int nvc_ctx_device(const nvc_ctx* ctx);
 int nvc_ctx_tp_rank(const nvc_ctx* ctx);
 int nvc_ctx_tp_size(const nvc_ctx* ctx);
 int nvc_ctx_num_sms(const nvc_ctx* ctx);
+/* Kernels launched through this context so far (bench.py reports the per-step difference). */
+uint64_t nvc_ctx_launch_count(const nvc_ctx* ctx);
 
 /* Tensor-parallel communicator (absent in the reference: src/tp.rs has no collectives,
  * src/layers/linear.rs:184-198 does no all-reduce).  `unique_id` is the 128-byte
@@ -122,6 +124,7 @@ int nvc_rope_table_init_sync(nvc_ctx* ctx, float theta, int head_dim, int max_po
  *   if slot_mapping != NULL and slot_mapping[n] >= 0:
  *       k_cache[slot, h, :] = k_h;  v_cache[slot, h, :] = v_h      (bit-exact copies)
  * k_cache / v_cache: bf16 [num_slots, kv, hd] = [num_blocks, block_size, kv, hd].
+ * qw == kw == NULL skips the norm (rope only = RotaryEmbedding::apply by itself).
  * hd must be 128. */
 int nvc_qk_norm_rope_store(nvc_ctx* ctx, nvc_bf16* qkv, const nvc_bf16* qw, const nvc_bf16* kw,
                            float eps, const float* cos_sin, const int32_t* positions,

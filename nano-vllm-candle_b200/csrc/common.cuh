@@ -39,6 +39,7 @@ struct nvc_ctx {
   int tp_size = 1;
   int num_sms = 148;
   std::string last_error;
+  uint64_t launches = 0;   // kernels launched through this context (bench.py gpu_launches)
   nvc_encode_tiled_fn encode_tiled = nullptr;
   // split-K scratch for the tcgen05 GEMM (fp32 partial tiles + per-tile arrival counters)
   float* gemm_ws = nullptr;

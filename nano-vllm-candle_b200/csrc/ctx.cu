@@ -1,5 +1,6 @@
 // Context lifetime, status strings, driver entry points.
 #include "common.cuh"
+#include "internal.h"
 
 #include <cstring>
 
@@ -86,9 +87,20 @@ extern "C" int nvc_ctx_create(int device, int tp_rank, int tp_size, nvc_ctx** ou
     delete ctx;
     return NVC_CUDA_ERROR_BASE + (int)e;
   }
+  int rc = nvc_gemm_init(ctx);
+  if (rc == NVC_OK) rc = nvc_prefill_attn_init(ctx);
+  if (rc != NVC_OK) {
+    nvc_set_error(nullptr, "nvc_ctx_create: kernel attribute setup failed: " + ctx->last_error);
+    cudaFree(ctx->gemm_ws);
+    cudaFree(ctx->gemm_counters);
+    delete ctx;
+    return rc;
+  }
   *out = ctx;
   return NVC_OK;
 }
+
+extern "C" uint64_t nvc_ctx_launch_count(const nvc_ctx* ctx) { return ctx ? ctx->launches : 0; }
 
 extern "C" int nvc_ctx_destroy(nvc_ctx* ctx) {
   if (!ctx) return NVC_EINVAL;

@@ -4,6 +4,7 @@
 // data, fp32 math, warp-shuffle reductions.  Each entry point cites the reference code it
 // replaces in include/nvc_b200.h.
 #include "common.cuh"
+#include "internal.h"
 
 #include <cmath>
 #include <vector>
@@ -36,6 +37,7 @@ extern "C" int nvc_embed_gather(nvc_ctx* ctx, const int32_t* ids, const nvc_bf16
   embed_gather_kernel<<<(unsigned)blocks, threads, 0, nvc_stream(stream)>>>(
       ids, reinterpret_cast<const uint4*>(table), reinterpret_cast<uint4*>(out), N, vpr);
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   return NVC_OK;
 }
 
@@ -148,6 +150,7 @@ extern "C" int nvc_fused_add_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x, const floa
     fused_add_rmsnorm_kernel<true><<<N, 1024, 0, nvc_stream(stream)>>>(xs, ri, ro, ws, eps, os, H);
   }
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   return NVC_OK;
 }
 
@@ -226,12 +229,18 @@ qk_norm_rope_store_kernel(uint4* __restrict__ qkv, const uint4* __restrict__ qw,
   ss += __shfl_xor_sync(mask, ss, 2);
   ss += __shfl_xor_sync(mask, ss, 4);
   if (!active) return;
-  const float rstd = 1.0f / sqrtf(ss * (1.0f / 128.0f) + eps);
   const bool is_q = u < nh;
-  float wa[8], wb[8];
   const uint4* wp = is_q ? qw : kw;
-  unpack8(__ldg(wp + l), wa);
-  unpack8(__ldg(wp + l + 8), wb);
+  float rstd = 1.0f;
+  float wa[8], wb[8];
+  if (wp != nullptr) {   // NULL weight: rope only (RotaryEmbedding::apply on its own)
+    rstd = 1.0f / sqrtf(ss * (1.0f / 128.0f) + eps);
+    unpack8(__ldg(wp + l), wa);
+    unpack8(__ldg(wp + l + 8), wb);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) wa[i] = wb[i] = 1.0f;
+  }
   const int pos = __ldg(positions + n);
   const float4* cs = cos_sin + (int64_t)pos * 32;   // 128 floats per position: cos[64], sin[64]
   float4 c0 = __ldg(cs + 2 * l), c1 = __ldg(cs + 2 * l + 1);
@@ -261,7 +270,8 @@ extern "C" int nvc_qk_norm_rope_store(nvc_ctx* ctx, nvc_bf16* qkv, const nvc_bf1
                                       float eps, const float* cos_sin, const int32_t* positions,
                                       const int32_t* slot_mapping, nvc_bf16* k_cache, nvc_bf16* v_cache,
                                       int N, int nh, int kv, int hd, void* stream) {
-  NVC_REQUIRE(ctx, ctx && qkv && qw && kw && cos_sin && positions, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, ctx && qkv && cos_sin && positions, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, (qw == nullptr) == (kw == nullptr), NVC_EINVAL, "q/k norm weights must both be given or both be NULL");
   NVC_REQUIRE(ctx, slot_mapping == nullptr || (k_cache && v_cache), NVC_EINVAL, "slot_mapping without caches");
   NVC_REQUIRE(ctx, N >= 0 && nh > 0 && kv > 0, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, hd == 128, NVC_ESHAPE, "head_dim must be 128");
@@ -274,6 +284,7 @@ extern "C" int nvc_qk_norm_rope_store(nvc_ctx* ctx, nvc_bf16* qkv, const nvc_bf1
       eps, reinterpret_cast<const float4*>(cos_sin), positions, slot_mapping,
       reinterpret_cast<uint4*>(k_cache), reinterpret_cast<uint4*>(v_cache), N, nh, kv);
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   return NVC_OK;
 }
 
@@ -309,6 +320,7 @@ extern "C" int nvc_store_kvcache(nvc_ctx* ctx, const nvc_bf16* k, const nvc_bf16
       reinterpret_cast<const uint4*>(k), reinterpret_cast<const uint4*>(v), ld / 8,
       reinterpret_cast<uint4*>(k_cache), reinterpret_cast<uint4*>(v_cache), slot_mapping, N, row_vec);
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   return NVC_OK;
 }
 
@@ -341,6 +353,7 @@ extern "C" int nvc_silu_and_mul(nvc_ctx* ctx, const nvc_bf16* x, nvc_bf16* out, 
   silu_and_mul_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, nvc_stream(stream)>>>(
       reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(out), N, ivec);
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   return NVC_OK;
 }
 
@@ -375,6 +388,7 @@ extern "C" int nvc_gather_rows(nvc_ctx* ctx, const nvc_bf16* x, const float* res
       reinterpret_cast<const uint4*>(x), reinterpret_cast<const float4*>(residual), rows,
       reinterpret_cast<uint4*>(x_out), reinterpret_cast<float4*>(residual_out), B, hvec);
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   return NVC_OK;
 }
 
@@ -439,5 +453,23 @@ extern "C" int nvc_argmax_last(nvc_ctx* ctx, const float* logits, int ld, int32_
   if (B == 0) return NVC_OK;
   argmax_last_kernel<<<B, 1024, 0, nvc_stream(stream)>>>(logits, ld, idx, val, V, index_offset);
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
+  return NVC_OK;
+}
+
+// (max, idx) of a vocab shard as one 8-byte record per sequence (TP argmax exchange)
+__global__ void pack_argmax_pairs_kernel(const float* __restrict__ val, const int32_t* __restrict__ idx,
+                                         float2* __restrict__ pairs, int B) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b < B) pairs[b] = make_float2(val[b], __int_as_float(idx[b]));
+}
+
+extern "C" int nvc_pack_argmax_pairs(nvc_ctx* ctx, const float* val, const int32_t* idx, float* pairs, int B,
+                                     void* stream) {
+  NVC_REQUIRE(ctx, ctx && val && idx && pairs && B >= 0, NVC_EINVAL, "bad arguments");
+  if (B == 0) return NVC_OK;
+  pack_argmax_pairs_kernel<<<(B + 127) / 128, 128, 0, nvc_stream(stream)>>>(val, idx, reinterpret_cast<float2*>(pairs), B);
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   return NVC_OK;
 }

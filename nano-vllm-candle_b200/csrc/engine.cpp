@@ -1,0 +1,449 @@
+// Host-side engine book-keeping behind the C ABI of include/nvc_b200_engine.h:
+// Sequence / BlockManager / Scheduler / LLMEngine of the reference, in C++ because the
+// reference's own host language (Rust) has no toolchain here.
+//
+//   Sequence      src/engine/sequence.rs:16-97
+//   BlockManager  src/engine/block_manager.rs:31-99  (the reference's is a stub with identity
+//                 block tables and always-true capacity; this one keeps the same methods and
+//                 makes them real: FIFO free list, disjoint block ids, truthful can_allocate /
+//                 can_append, may_append grows the table when len % block_size == 1)
+//   Scheduler     src/engine/scheduler.rs:58-250     (same control flow, statement by statement)
+//   LLMEngine     src/engine/llm_engine.rs:209-326
+// plus the integer contract the north_star adds (N1 slot_mapping, N2 block_tables), written
+// only in terms of the Sequence helpers the reference exposes (sequence.rs:73-91).
+#include <algorithm>
+#include <cstdint>
+#include <deque>
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/nvc_b200_engine.h"
+
+namespace {
+
+enum class Status { Waiting, Running, Finished };
+
+struct Sequence {
+  int64_t seq_id;
+  int block_size;
+  std::vector<int32_t> block_table;
+  Status status = Status::Waiting;
+  std::vector<int32_t> token_ids;
+  int32_t last_token = 0;
+  size_t num_tokens = 0;
+  size_t num_prompt_tokens = 0;
+  size_t num_cached_tokens = 0;
+  double temperature = 1.0;
+  size_t max_tokens = 64;
+  bool ignore_eos = false;
+
+  size_t len() const { return num_tokens; }
+  bool is_finished() const { return status == Status::Finished; }
+  size_t num_completion_tokens() const { return num_tokens - num_prompt_tokens; }
+  size_t num_cached_blocks() const { return num_cached_tokens / block_size; }
+  size_t num_blocks() const { return (num_tokens + block_size - 1) / block_size; }
+  size_t last_block_num_tokens() const { return num_tokens - (num_blocks() - 1) * block_size; }
+  void append_token(int32_t t) {
+    token_ids.push_back(t);
+    last_token = t;
+    num_tokens += 1;
+  }
+};
+using SeqPtr = std::shared_ptr<Sequence>;
+
+struct BlockManager {
+  int num_blocks_;
+  int block_size_;
+  std::deque<int32_t> free_;
+
+  BlockManager(int num_blocks, int block_size) : num_blocks_(num_blocks), block_size_(block_size) {
+    for (int i = 0; i < num_blocks; ++i) free_.push_back(i);
+  }
+  int block_size() const { return block_size_; }
+  int num_blocks() const { return num_blocks_; }
+  bool can_allocate(const Sequence& s) const { return free_.size() >= s.num_blocks(); }
+  void allocate(Sequence& s) {
+    s.block_table.clear();
+    for (size_t i = 0; i < s.num_blocks(); ++i) {
+      s.block_table.push_back(free_.front());
+      free_.pop_front();
+    }
+    s.num_cached_tokens = 0;   // no prefix cache: nothing of this sequence is cached yet
+  }
+  void deallocate(Sequence& s) {
+    for (auto it = s.block_table.rbegin(); it != s.block_table.rend(); ++it) free_.push_back(*it);
+    s.block_table.clear();
+    s.num_cached_tokens = 0;
+  }
+  bool can_append(const Sequence& s) const {
+    return free_.size() >= (size_t)((s.len() % block_size_ == 1) ? 1 : 0);
+  }
+  void may_append(Sequence& s) {
+    if (s.len() % block_size_ == 1 && s.block_table.size() < s.num_blocks()) {
+      s.block_table.push_back(free_.front());
+      free_.pop_front();
+    }
+  }
+};
+
+struct Scheduler {
+  size_t max_num_seqs;
+  size_t max_num_batched_tokens;
+  BlockManager block_manager;
+  std::deque<SeqPtr> waiting, running;
+  int32_t eos;
+
+  explicit Scheduler(const nvc_scheduler_config& c)
+      : max_num_seqs(c.max_num_seqs), max_num_batched_tokens(c.max_num_batched_tokens),
+        block_manager(c.num_kvcache_blocks, c.kvcache_block_size), eos(c.eos) {}
+
+  bool is_finished() const { return waiting.empty() && running.empty(); }
+  void add(const SeqPtr& s) { waiting.push_back(s); }
+
+  // scheduler.rs:113-157
+  bool try_schedule_prefill(std::vector<SeqPtr>& out) {
+    size_t num_seqs = 0, num_batched = 0;
+    while (!waiting.empty() && num_seqs < max_num_seqs) {
+      SeqPtr seq = waiting.front();
+      const bool ok = num_batched + seq->len() <= max_num_batched_tokens && block_manager.can_allocate(*seq);
+      if (!ok) break;
+      num_seqs += 1;
+      block_manager.allocate(*seq);
+      num_batched += seq->len() - seq->num_cached_tokens;
+      seq->status = Status::Running;
+      waiting.pop_front();
+      running.push_back(seq);
+      out.push_back(seq);
+    }
+    return !out.empty();
+  }
+
+  // scheduler.rs:188-198
+  bool ensure_can_append(const SeqPtr& seq) {
+    while (!block_manager.can_append(*seq)) {
+      if (!running.empty()) {
+        SeqPtr victim = running.back();
+        running.pop_back();
+        preempt(victim);
+      } else {
+        preempt(seq);
+        return false;
+      }
+    }
+    return true;
+  }
+
+  // scheduler.rs:159-186.  Returns false where the reference would hit its assert.
+  bool schedule_decode(std::vector<SeqPtr>& out) {
+    size_t num_seqs = 0;
+    while (!running.empty() && num_seqs < max_num_seqs) {
+      SeqPtr seq = running.front();
+      running.pop_front();
+      if (ensure_can_append(seq)) {
+        num_seqs += 1;
+        block_manager.may_append(*seq);
+        out.push_back(seq);
+      }
+    }
+    if (out.empty()) return false;
+    for (auto it = out.rbegin(); it != out.rend(); ++it) running.push_front(*it);
+    return true;
+  }
+
+  // scheduler.rs:200-211
+  void preempt(const SeqPtr& seq) {
+    seq->status = Status::Waiting;
+    block_manager.deallocate(*seq);
+    waiting.push_front(seq);
+  }
+
+  // scheduler.rs:219-249; returns true when the sequence finished
+  bool process_single(const SeqPtr& seq, int32_t tok) {
+    seq->append_token(tok);
+    const bool is_eos = tok == eos;
+    const bool reached_max = seq->num_completion_tokens() >= seq->max_tokens;
+    const bool finished = (!seq->ignore_eos && is_eos) || reached_max;
+    if (finished) {
+      seq->status = Status::Finished;
+      block_manager.deallocate(*seq);
+      const int64_t id = seq->seq_id;
+      running.erase(std::remove_if(running.begin(), running.end(),
+                                   [id](const SeqPtr& s) { return s->seq_id == id; }),
+                    running.end());
+    }
+    return finished;
+  }
+};
+
+}  // namespace
+
+struct nvc_engine {
+  Scheduler scheduler;
+  nvc_runner* runner;
+  int block_size;
+  int64_t next_seq_id = 0;                     // sequence.rs:5 SEQ_COUNTER (per engine here)
+  std::map<int64_t, SeqPtr> all;               // every sequence ever added (outputs / introspection)
+  int num_finished = 0;
+  std::string err;
+  // last scheduled batch and its step inputs
+  std::vector<SeqPtr> batch;
+  bool batch_is_prefill = false;
+  bool batch_valid = false;
+  std::vector<int32_t> ids, positions, cu_seqlens, slot_mapping, block_tables, context_lens, out_tokens;
+  std::vector<int64_t> seq_ids;
+  int max_blocks = 0, max_seqlen = 0;
+
+  nvc_engine(const nvc_scheduler_config& c, nvc_runner* r) : scheduler(c), runner(r), block_size(c.kvcache_block_size) {}
+};
+
+namespace {
+
+// N1 (prefill): block i in num_cached_blocks..num_blocks -> slots block_table[i]*BS + [0, BS)
+// (last block: [0, last_block_num_tokens)).
+void prefill_slots(const Sequence& s, std::vector<int32_t>& out) {
+  const int bs = s.block_size;
+  for (size_t i = s.num_cached_blocks(); i < s.num_blocks(); ++i) {
+    const int32_t start = s.block_table[i] * bs;
+    const size_t n = (i != s.num_blocks() - 1) ? (size_t)bs : s.last_block_num_tokens();
+    for (size_t j = 0; j < n; ++j) out.push_back(start + (int32_t)j);
+  }
+}
+
+void build_inputs(nvc_engine* e) {
+  e->ids.clear(); e->positions.clear(); e->cu_seqlens.clear(); e->slot_mapping.clear();
+  e->block_tables.clear(); e->context_lens.clear(); e->seq_ids.clear();
+  e->max_blocks = 0; e->max_seqlen = 0;
+  for (auto& s : e->batch) e->seq_ids.push_back(s->seq_id);
+  if (e->batch_is_prefill) {
+    e->cu_seqlens.push_back(0);
+    for (auto& sp : e->batch) {
+      const Sequence& s = *sp;
+      const size_t start = s.num_cached_tokens;
+      for (size_t t = start; t < s.len(); ++t) {
+        e->ids.push_back(s.token_ids[t]);
+        e->positions.push_back((int32_t)t);
+      }
+      e->cu_seqlens.push_back(e->cu_seqlens.back() + (int32_t)(s.len() - start));
+      e->max_seqlen = std::max(e->max_seqlen, (int)(s.len() - start));
+      prefill_slots(s, e->slot_mapping);
+      e->context_lens.push_back((int32_t)s.len());
+    }
+  } else {
+    for (auto& sp : e->batch) {
+      const Sequence& s = *sp;
+      e->ids.push_back(s.last_token);
+      e->positions.push_back((int32_t)s.len() - 1);
+      // N1 (decode): block_table[last]*BS + last_block_num_tokens - 1
+      e->slot_mapping.push_back(s.block_table.back() * s.block_size + (int32_t)s.last_block_num_tokens() - 1);
+      e->context_lens.push_back((int32_t)s.len());
+    }
+    e->max_seqlen = 1;
+  }
+  // N2: [B, max_blocks] padded with -1
+  for (auto& sp : e->batch) e->max_blocks = std::max(e->max_blocks, (int)sp->block_table.size());
+  e->block_tables.assign((size_t)e->batch.size() * e->max_blocks, -1);
+  for (size_t b = 0; b < e->batch.size(); ++b)
+    std::copy(e->batch[b]->block_table.begin(), e->batch[b]->block_table.end(),
+              e->block_tables.begin() + b * e->max_blocks);
+}
+
+int do_schedule(nvc_engine* e) {
+  e->batch.clear();
+  e->batch_valid = false;
+  if (e->scheduler.is_finished()) {
+    e->err = "schedule: no waiting or running sequences";
+    return NVC_ESTATE;
+  }
+  if (e->scheduler.try_schedule_prefill(e->batch)) {
+    e->batch_is_prefill = true;
+  } else {
+    e->batch.clear();
+    if (!e->scheduler.schedule_decode(e->batch)) {
+      e->err = "decode stage should schedule at least one sequence (KV pool exhausted)";   // scheduler.rs:175-178
+      return NVC_ENOMEM;
+    }
+    e->batch_is_prefill = false;
+  }
+  build_inputs(e);
+  e->batch_valid = true;
+  return NVC_OK;
+}
+
+int do_post_process(nvc_engine* e, const int32_t* toks, int n, int* finished_out) {
+  if (!e->batch_valid || n != (int)e->batch.size()) {
+    e->err = "post_process: no scheduled batch of that size";
+    return NVC_ESTATE;
+  }
+  int fin = 0;
+  for (int i = 0; i < n; ++i) fin += e->scheduler.process_single(e->batch[i], toks[i]) ? 1 : 0;
+  e->num_finished += fin;
+  e->batch_valid = false;
+  if (finished_out) *finished_out = fin;
+  return NVC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nvc_engine_create(const nvc_scheduler_config* cfg, nvc_runner* runner, nvc_engine** out) {
+  if (!cfg || !out) return NVC_EINVAL;
+  if (cfg->max_num_seqs <= 0 || cfg->max_num_batched_tokens <= 0 || cfg->kvcache_block_size <= 0 ||
+      cfg->num_kvcache_blocks < 0)
+    return NVC_EINVAL;
+  *out = new nvc_engine(*cfg, runner);
+  return NVC_OK;
+}
+
+int nvc_engine_destroy(nvc_engine* e) {
+  if (!e) return NVC_EINVAL;
+  delete e;
+  return NVC_OK;
+}
+
+const char* nvc_engine_last_error(const nvc_engine* e) { return e ? e->err.c_str() : ""; }
+
+int64_t nvc_engine_add_request(nvc_engine* e, const int32_t* token_ids, int n, double temperature, int max_tokens,
+                               int ignore_eos) {
+  if (!e || (n > 0 && !token_ids) || n < 0) return NVC_EINVAL;
+  if (!(temperature > 1e-10)) {   // sampling_params.rs:20,30
+    e->err = "greedy sampling is not permitted (temperature must be > 1e-10)";
+    return NVC_EINVAL;
+  }
+  auto s = std::make_shared<Sequence>();
+  s->seq_id = e->next_seq_id++;
+  s->block_size = e->block_size;
+  s->token_ids.assign(token_ids, token_ids + n);
+  s->last_token = n ? token_ids[n - 1] : 0;
+  s->num_tokens = s->num_prompt_tokens = (size_t)n;
+  s->temperature = temperature;
+  s->max_tokens = (size_t)max_tokens;
+  s->ignore_eos = ignore_eos != 0;
+  e->all[s->seq_id] = s;
+  e->scheduler.add(s);
+  return s->seq_id;
+}
+
+int nvc_engine_schedule(nvc_engine* e, nvc_schedule_info* info) {
+  if (!e || !info) return NVC_EINVAL;
+  int rc = do_schedule(e);
+  if (rc) return rc;
+  info->is_prefill = e->batch_is_prefill;
+  info->num_seqs = (int)e->batch.size();
+  info->num_tokens = (int)e->ids.size();
+  info->max_blocks = e->max_blocks;
+  info->max_seqlen = e->max_seqlen;
+  return NVC_OK;
+}
+
+int nvc_engine_step_inputs(const nvc_engine* e, const int32_t** ids, const int32_t** positions,
+                           const int32_t** cu_seqlens, const int32_t** slot_mapping, const int32_t** block_tables,
+                           const int32_t** context_lens, const int64_t** seq_ids) {
+  if (!e) return NVC_EINVAL;
+  if (!e->batch_valid) return NVC_ESTATE;
+  if (ids) *ids = e->ids.data();
+  if (positions) *positions = e->positions.data();
+  if (cu_seqlens) *cu_seqlens = e->cu_seqlens.data();
+  if (slot_mapping) *slot_mapping = e->slot_mapping.data();
+  if (block_tables) *block_tables = e->block_tables.data();
+  if (context_lens) *context_lens = e->context_lens.data();
+  if (seq_ids) *seq_ids = e->seq_ids.data();
+  return NVC_OK;
+}
+
+int nvc_engine_post_process(nvc_engine* e, const int32_t* token_ids, int n) {
+  if (!e || !token_ids) return NVC_EINVAL;
+  return do_post_process(e, token_ids, n, nullptr);
+}
+
+int nvc_engine_step(nvc_engine* e, nvc_step_output* out) {
+  if (!e || !out) return NVC_EINVAL;
+  int rc = do_schedule(e);
+  if (rc) return rc;
+  const int B = (int)e->batch.size();
+  e->out_tokens.assign(B, 0);
+  if (e->runner == nullptr) {
+    for (int i = 0; i < B; ++i) e->out_tokens[i] = e->batch[i]->last_token + 1;   // DummyModelRunner
+  } else if (e->batch_is_prefill) {
+    rc = nvc_runner_prefill(e->runner, e->ids.data(), e->positions.data(), e->cu_seqlens.data(),
+                            e->slot_mapping.data(), B, (int)e->ids.size(), e->max_seqlen, e->out_tokens.data());
+  } else {
+    rc = nvc_runner_decode(e->runner, e->ids.data(), e->positions.data(), e->slot_mapping.data(),
+                           e->block_tables.data(), e->max_blocks, e->context_lens.data(), B, e->out_tokens.data());
+  }
+  if (rc) {
+    e->err = "runner step failed";
+    return rc;   // errors propagate; the reference would emit eos for every sequence (llm_engine.rs:153-175)
+  }
+  const bool is_prefill = e->batch_is_prefill;
+  std::vector<SeqPtr> seqs = e->batch;
+  int fin = 0;
+  rc = do_post_process(e, e->out_tokens.data(), B, &fin);
+  if (rc) return rc;
+  out->is_prefill = is_prefill;
+  out->num_seqs = B;
+  out->num_finished = fin;
+  if (is_prefill) {
+    int tot = 0;
+    for (auto& s : seqs) tot += (int)s->len();   // llm_engine.rs:253-254 (counted after the append)
+    out->num_tokens = tot;
+  } else {
+    out->num_tokens = -B;
+  }
+  return NVC_OK;
+}
+
+int nvc_engine_is_finished(const nvc_engine* e) { return e ? (e->scheduler.is_finished() ? 1 : 0) : 1; }
+
+int nvc_engine_preempt(nvc_engine* e, int64_t seq_id) {
+  if (!e) return NVC_EINVAL;
+  auto& run = e->scheduler.running;
+  for (auto it = run.begin(); it != run.end(); ++it) {
+    if ((*it)->seq_id == seq_id) {
+      SeqPtr s = *it;
+      run.erase(it);
+      e->scheduler.preempt(s);
+      e->batch_valid = false;
+      return NVC_OK;
+    }
+  }
+  e->err = "preempt: sequence is not running";
+  return NVC_ESTATE;
+}
+
+int nvc_engine_num_finished(const nvc_engine* e) { return e ? e->num_finished : 0; }
+
+int nvc_engine_get_output(const nvc_engine* e, int64_t seq_id, int32_t* tokens, int capacity, int* n_tokens) {
+  if (!e || !n_tokens) return NVC_EINVAL;
+  auto it = e->all.find(seq_id);
+  if (it == e->all.end()) return NVC_EINVAL;
+  const Sequence& s = *it->second;
+  const int n = (int)s.num_completion_tokens();
+  *n_tokens = n;
+  if (tokens) {
+    if (capacity < n) return NVC_ENOMEM;
+    std::copy(s.token_ids.begin() + s.num_prompt_tokens, s.token_ids.end(), tokens);
+  }
+  return s.is_finished() ? NVC_OK : NVC_ESTATE;
+}
+
+int nvc_engine_seq_block_table(const nvc_engine* e, int64_t seq_id, int32_t* blocks, int capacity, int* n_blocks) {
+  if (!e || !n_blocks) return NVC_EINVAL;
+  auto it = e->all.find(seq_id);
+  if (it == e->all.end()) return NVC_EINVAL;
+  const auto& bt = it->second->block_table;
+  *n_blocks = (int)bt.size();
+  if (blocks) {
+    if (capacity < (int)bt.size()) return NVC_ENOMEM;
+    std::copy(bt.begin(), bt.end(), blocks);
+  }
+  return NVC_OK;
+}
+
+int nvc_engine_num_free_blocks(const nvc_engine* e) { return e ? (int)e->scheduler.block_manager.free_.size() : 0; }
+int nvc_engine_num_waiting(const nvc_engine* e) { return e ? (int)e->scheduler.waiting.size() : 0; }
+int nvc_engine_num_running(const nvc_engine* e) { return e ? (int)e->scheduler.running.size() : 0; }
+
+}  // extern "C"

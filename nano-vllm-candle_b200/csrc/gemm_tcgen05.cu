@@ -14,6 +14,7 @@
 // Rows >= M and columns >= N of edge tiles are zero-filled by TMA and masked at the store.
 #include "common.cuh"
 #include "ptx.cuh"
+#include "internal.h"
 
 namespace {
 
@@ -246,12 +247,6 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
   if (rc) return rc;
   rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, BN);
   if (rc) return rc;
-  static bool attr_set = false;   // per template instantiation
-  if (!attr_set) {
-    NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, cfg::kSmemBytes));
-    attr_set = true;
-  }
   const int kb_total = K / BK;
   const int kb_per = (kb_total + splits - 1) / splits;
   const int eff_splits = (kb_total + kb_per - 1) / kb_per;   // no empty splits
@@ -259,6 +254,7 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
   gemm_bf16_tcgen05_kernel<BN><<<grid, kThreads, cfg::kSmemBytes, stream>>>(
       ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, ctx->gemm_ws, ctx->gemm_counters);
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   return NVC_OK;
 }
 
@@ -298,6 +294,14 @@ void choose_config(const nvc_ctx* ctx, int M, int N, int K, int* bn_out, int* sp
 }
 
 }  // namespace
+
+extern "C" int nvc_gemm_init(nvc_ctx* ctx) {
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<256>::kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<128>::kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<64>::kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<32>::kSmemBytes));
+  return NVC_OK;
+}
 
 extern "C" int nvc_gemm_bf16_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
                                 int out_dtype, int M, int Nout, int K, int force_bn, int force_splits,

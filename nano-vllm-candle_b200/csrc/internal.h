@@ -1,0 +1,20 @@
+// Library-internal entry points (not part of the public C ABI).
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+#include "../../include/nvc_b200.h"
+
+extern "C" {
+// paged decode with separate block-table row stride and a max-blocks hint for the split choice
+int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
+                             const nvc_bf16* v_cache, const int32_t* block_tables, int bt_stride, int max_blocks_hint,
+                             const int32_t* context_lens, int B, int nh, int kv, int hd, int block_size, float scale,
+                             nvc_bf16* out, void* workspace, size_t workspace_bytes, void* stream);
+// pairs[b] = {val[b], idx[b]} as 8-byte records
+int nvc_pack_argmax_pairs(nvc_ctx* ctx, const float* val, const int32_t* idx, float* pairs, int B, void* stream);
+int nvc_gemm_bf16_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_dtype,
+                     int M, int Nout, int K, int force_bn, int force_splits, void* stream);
+// set max-dynamic-smem attributes of every kernel instantiation (called once per context)
+int nvc_gemm_init(nvc_ctx* ctx);
+int nvc_prefill_attn_init(nvc_ctx* ctx);
+}

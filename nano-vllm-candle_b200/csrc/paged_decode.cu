@@ -14,6 +14,7 @@
 // the 8 (warp, half) partial states are merged through shared memory.  With KV splits > 1
 // the partials go to a workspace and a second kernel combines them.
 #include "common.cuh"
+#include "internal.h"
 
 namespace {
 
@@ -212,13 +213,13 @@ extern "C" size_t nvc_paged_decode_workspace_bytes(int B, int nh, int hd, int nu
   return (size_t)B * nh * S * (hd + 2) * sizeof(float);
 }
 
-extern "C" int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
-                                     const nvc_bf16* v_cache, const int32_t* block_tables, int max_blocks,
-                                     const int32_t* context_lens, int B, int nh, int kv, int hd, int block_size,
-                                     float scale, nvc_bf16* out, void* workspace, size_t workspace_bytes,
-                                     void* stream) {
+extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
+                                        const nvc_bf16* v_cache, const int32_t* block_tables, int max_blocks,
+                                        int max_blocks_hint, const int32_t* context_lens, int B, int nh, int kv,
+                                        int hd, int block_size, float scale, nvc_bf16* out, void* workspace,
+                                        size_t workspace_bytes, void* stream) {
   NVC_REQUIRE(ctx, ctx && q && k_cache && v_cache && block_tables && context_lens && out, NVC_EINVAL, "null pointer");
-  NVC_REQUIRE(ctx, B >= 0 && nh > 0 && kv > 0 && max_blocks > 0, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, B >= 0 && nh > 0 && kv > 0 && max_blocks > 0 && max_blocks_hint > 0, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, hd == 128, NVC_ESHAPE, "head_dim must be 128");
   NVC_REQUIRE(ctx, nh % kv == 0, NVC_ESHAPE, "nh must be a multiple of kv");
   NVC_REQUIRE(ctx, block_size > 0 && block_size % 16 == 0, NVC_ESHAPE, "block_size must be a multiple of 16");
@@ -231,7 +232,7 @@ extern "C" int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, c
   else if (group % 2 == 0) G = 2;
   else G = 1;
   const int chunks = group / G;
-  const int max_tiles = (int)(((int64_t)max_blocks * block_size + kTile - 1) / kTile);
+  const int max_tiles = (int)(((int64_t)max_blocks_hint * block_size + kTile - 1) / kTile);
   int splits = (2 * ctx->num_sms + B * kv * chunks - 1) / (B * kv * chunks);
   const int cap = max_splits_for_batch(B, ctx->num_sms);
   if (splits > cap) splits = cap;
@@ -262,9 +263,20 @@ extern "C" int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, c
   }
 #undef NVC_LAUNCH_PD
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   if (splits > 1) {
     paged_decode_combine_kernel<<<dim3(nh, B), 128, 0, st>>>(part_o, part_ml, out, nh, splits);
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   }
   return NVC_OK;
+}
+
+extern "C" int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
+                                     const nvc_bf16* v_cache, const int32_t* block_tables, int max_blocks,
+                                     const int32_t* context_lens, int B, int nh, int kv, int hd, int block_size,
+                                     float scale, nvc_bf16* out, void* workspace, size_t workspace_bytes,
+                                     void* stream) {
+  return nvc_paged_decode_attn_ex(ctx, q, ldq, k_cache, v_cache, block_tables, max_blocks, max_blocks, context_lens, B,
+                                  nh, kv, hd, block_size, scale, out, workspace, workspace_bytes, stream);
 }

@@ -15,6 +15,7 @@
 // FLOPs per (sequence, head): 4 * 128 * T^2 / 2 (causal).
 #include "common.cuh"
 #include "ptx.cuh"
+#include "internal.h"
 
 int g_nvc_debug[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 extern "C" int nvc_debug_set(int key, int value) {
@@ -254,6 +255,11 @@ int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, 
 
 }  // namespace
 
+extern "C" int nvc_prefill_attn_init(nvc_ctx* ctx) {
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  return NVC_OK;
+}
+
 extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k, int ldk,
                                        const nvc_bf16* v, int ldv, const int32_t* cu_seqlens, int B,
                                        int total_tokens, int max_seqlen, int nh, int kv, int hd, float scale,
@@ -275,11 +281,6 @@ extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq,
   if (rc) return rc;
   rc = make_tma_heads(ctx, &tv, v, kv, total_tokens, ldv);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
-    NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr_set = true;
-  }
   // V (B operand, MN-major, 128B swizzle): LBO = stride between the two 64-wide head-dim
   // halves (16 KB), SBO = stride between groups of 8 token rows (1 KB).
   int v_lbo = 16384, v_sbo = 1024;
@@ -288,5 +289,6 @@ extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq,
   prefill_attn_kernel<<<grid, kThreads, kSmemBytes, nvc_stream(stream)>>>(
       tq, tk, tv, cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out, v_lbo, v_sbo);
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
   return NVC_OK;
 }

@@ -5,6 +5,7 @@
 #pragma once
 #include <cuda.h>
 #include <stdint.h>
+#include <stdio.h>
 
 namespace ptx {
 
@@ -30,8 +31,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
   return ok != 0;
 }
+// Spin on try_wait (which itself sleeps in hardware up to a time limit).  A bounded spin
+// turns a lost arrival into a trap ("unspecified launch failure") instead of a hung GPU.
+#ifndef NVC_MBAR_SPIN_LIMIT
+#define NVC_MBAR_SPIN_LIMIT (1u << 23)
+#endif
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {}
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > NVC_MBAR_SPIN_LIMIT) {
+      printf("nvc: mbarrier wait timed out (block %d,%d,%d thread %d bar 0x%x parity %u)\n", blockIdx.x,
+             blockIdx.y, blockIdx.z, threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
 }
 
 // ------------------------------------------------------------------ fences

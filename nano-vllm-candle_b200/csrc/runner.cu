@@ -1,0 +1,651 @@
+// Qwen3 step executor: owns this rank's weight shard, the per-rank paged KV pool, the
+// activation buffers and the decode CUDA graphs, and runs one engine step from flat step
+// inputs.  Replaces Qwen3ModelRunner::run (src/engine/llm_engine.rs:146-189) and the model
+// forward it drives (src/models/qwen3.rs:202-281,323-327,374-399,458-499,542-550).
+//
+// Per layer (prefill and decode differ only in the attention kernel):
+//   fused_add_rmsnorm -> qkv GEMM -> qk_norm_rope_store -> attention -> o_proj GEMM [-> all-reduce]
+//   -> fused_add_rmsnorm -> gate_up GEMM -> silu_and_mul -> down GEMM [-> all-reduce]
+// then: gather last rows -> final fused_add_rmsnorm -> lm_head GEMM (fp32) -> argmax.
+#include "common.cuh"
+#include "internal.h"
+
+#include <algorithm>
+#include <cstring>
+#include <map>
+#include <set>
+#include <vector>
+
+namespace {
+
+struct Layer {
+  nvc_bf16 *w_qkv = nullptr, *w_o = nullptr, *q_norm = nullptr, *k_norm = nullptr;
+  nvc_bf16 *w_gu = nullptr, *w_down = nullptr, *ln1 = nullptr, *ln2 = nullptr;
+  nvc_bf16 *k_cache = nullptr, *v_cache = nullptr;
+};
+
+struct ArgPair { float val; int32_t idx; };
+
+}  // namespace
+
+struct nvc_runner {
+  nvc_ctx* ctx = nullptr;
+  nvc_qwen3_config cfg{};
+  nvc_runner_options opt{};
+  int tp = 1, rank = 0;
+  int nh_l = 0, kv_l = 0, I_l = 0, V_l = 0, qkv_l = 0, max_blocks_cap = 0;
+  bool finalized = false;
+  cudaStream_t stream = nullptr;
+  std::vector<Layer> layers;
+  nvc_bf16 *embed = nullptr, *final_norm = nullptr, *lm_head = nullptr;
+  float* rope = nullptr;
+  std::set<std::string> loaded;
+  int64_t weight_bytes = 0;
+  std::vector<void*> allocs;
+  // activations
+  nvc_bf16 *x = nullptr, *xn = nullptr, *qkv = nullptr, *attn = nullptr, *gu = nullptr, *act = nullptr;
+  float* residual = nullptr;
+  nvc_bf16 *x_last = nullptr, *xn_last = nullptr;
+  float *res_last = nullptr, *logits = nullptr;
+  void* decode_ws = nullptr;
+  size_t decode_ws_bytes = 0;
+  // step inputs on device + pinned staging
+  int32_t *d_ids = nullptr, *d_pos = nullptr, *d_cu = nullptr, *d_slots = nullptr, *d_bt = nullptr, *d_ctx = nullptr,
+          *d_last_rows = nullptr, *d_tok = nullptr;
+  float* d_tok_val = nullptr;
+  ArgPair* d_pairs = nullptr;
+  int32_t* h_stage = nullptr;   // pinned
+  size_t h_stage_ints = 0;
+  ArgPair* h_pairs = nullptr;   // pinned
+  int32_t* h_tok = nullptr;     // pinned
+  int last_B = 0;
+  // decode graphs keyed by (B, blocks hint)
+  std::map<std::pair<int, int>, cudaGraphExec_t> graphs;
+  int launches_per_decode = 0;
+  int last_decode_hint = 0;
+};
+
+namespace {
+
+#define R_CUDA(expr) NVC_CUDA_CHECK(r->ctx, expr)
+
+template <typename T>
+int dev_alloc(nvc_runner* r, T** p, size_t count) {
+  void* q = nullptr;
+  R_CUDA(cudaMalloc(&q, std::max<size_t>(count, 1) * sizeof(T)));
+  r->allocs.push_back(q);
+  *p = reinterpret_cast<T*>(q);
+  return NVC_OK;
+}
+
+int launch_count_layer(const nvc_runner* r) { return r->tp > 1 ? 11 : 9; }
+
+// The transformer body over N tokens already embedded in r->x.  decode: attention over the
+// paged cache; prefill: varlen causal flash over the tokens of this step.
+int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blocks_hint) {
+  const nvc_qwen3_config& c = r->cfg;
+  nvc_ctx* ctx = r->ctx;
+  void* st = r->stream;
+  const int H = c.hidden_size, hd = c.head_dim;
+  const float scale = 1.0f / sqrtf((float)hd);   // (head_dim as f32).powf(-0.5), qwen3.rs:132
+  int rc;
+  for (int li = 0; li < c.num_hidden_layers; ++li) {
+    Layer& L = r->layers[li];
+    // input_layernorm with fused residual add; layer 0 seeds the residual stream (qwen3.rs:376-387)
+    rc = nvc_fused_add_rmsnorm(ctx, r->x, li == 0 ? nullptr : r->residual, r->residual, L.ln1, c.rms_norm_eps, r->xn, N, H, st);
+    if (rc) return rc;
+    rc = nvc_gemm_bf16(ctx, r->xn, H, L.w_qkv, r->qkv, r->qkv_l, NVC_DT_BF16, N, r->qkv_l, H, st);
+    if (rc) return rc;
+    rc = nvc_qk_norm_rope_store(ctx, r->qkv, L.q_norm, L.k_norm, c.rms_norm_eps, r->rope, r->d_pos, r->d_slots,
+                                L.k_cache, L.v_cache, N, r->nh_l, r->kv_l, hd, st);
+    if (rc) return rc;
+    if (decode) {
+      rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, L.k_cache, L.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
+                                    r->d_ctx, B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
+                                    r->decode_ws, r->decode_ws_bytes, st);
+    } else {
+      rc = nvc_prefill_attn_varlen(ctx, r->qkv, r->qkv_l, r->qkv + (size_t)r->nh_l * hd, r->qkv_l,
+                                   r->qkv + (size_t)(r->nh_l + r->kv_l) * hd, r->qkv_l, r->d_cu, B, N, max_seqlen,
+                                   r->nh_l, r->kv_l, hd, scale, r->attn, st);
+    }
+    if (rc) return rc;
+    rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, L.w_o, r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
+    if (rc) return rc;
+    if (r->tp > 1) { rc = nvc_allreduce_bf16(ctx, r->x, (size_t)N * H, st); if (rc) return rc; }   // N4
+    rc = nvc_fused_add_rmsnorm(ctx, r->x, r->residual, r->residual, L.ln2, c.rms_norm_eps, r->xn, N, H, st);
+    if (rc) return rc;
+    rc = nvc_gemm_bf16(ctx, r->xn, H, L.w_gu, r->gu, 2 * r->I_l, NVC_DT_BF16, N, 2 * r->I_l, H, st);
+    if (rc) return rc;
+    rc = nvc_silu_and_mul(ctx, r->gu, r->act, N, r->I_l, st);
+    if (rc) return rc;
+    rc = nvc_gemm_bf16(ctx, r->act, r->I_l, L.w_down, r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
+    if (rc) return rc;
+    if (r->tp > 1) { rc = nvc_allreduce_bf16(ctx, r->x, (size_t)N * H, st); if (rc) return rc; }   // N4
+  }
+  return NVC_OK;
+}
+
+// last-token rows -> final norm -> lm_head (fp32 logits) -> argmax (vocab shard offset)
+int run_head(nvc_runner* r, int B, bool decode) {
+  const nvc_qwen3_config& c = r->cfg;
+  nvc_ctx* ctx = r->ctx;
+  void* st = r->stream;
+  const int H = c.hidden_size;
+  int rc;
+  const nvc_bf16* xs = r->x;
+  const float* rs = r->residual;
+  if (!decode) {
+    rc = nvc_gather_rows(ctx, r->x, r->residual, r->d_last_rows, r->x_last, r->res_last, B, H, st);
+    if (rc) return rc;
+    xs = r->x_last;
+    rs = r->res_last;
+  }
+  rc = nvc_fused_add_rmsnorm(ctx, xs, rs, nullptr, r->final_norm, c.rms_norm_eps, r->xn_last, B, H, st);   // qwen3.rs:497
+  if (rc) return rc;
+  rc = nvc_gemm_bf16(ctx, r->xn_last, H, r->lm_head, r->logits, r->V_l, NVC_DT_F32, B, r->V_l, H, st);     // qwen3.rs:548
+  if (rc) return rc;
+  rc = nvc_argmax_last(ctx, r->logits, r->V_l, r->d_tok, r->d_tok_val, B, r->V_l, r->rank * r->V_l, st);    // llm_engine.rs:135-142
+  if (rc || r->tp == 1) return rc;
+  // TP: every rank holds (max, idx) of its vocab shard; gather the 8-byte pairs
+  rc = nvc_pack_argmax_pairs(ctx, r->d_tok_val, r->d_tok, reinterpret_cast<float*>(r->d_pairs + (size_t)r->rank * B), B, st);
+  if (rc) return rc;
+  return nvc_allgather_bytes(ctx, r->d_pairs, (size_t)B * sizeof(ArgPair), st);
+}
+
+int finish_tokens(nvc_runner* r, int B, int32_t* out_tokens) {
+  if (r->tp == 1) {
+    R_CUDA(cudaMemcpyAsync(r->h_tok, r->d_tok, B * sizeof(int32_t), cudaMemcpyDeviceToHost, r->stream));
+    R_CUDA(cudaStreamSynchronize(r->stream));
+    memcpy(out_tokens, r->h_tok, B * sizeof(int32_t));
+    return NVC_OK;
+  }
+  // TP: pick the largest value over the gathered shard maxima, ties -> the larger index
+  // (= the reference's "last maximum" over the full row).
+  R_CUDA(cudaMemcpyAsync(r->h_pairs, r->d_pairs, (size_t)r->tp * B * sizeof(ArgPair), cudaMemcpyDeviceToHost, r->stream));
+  R_CUDA(cudaStreamSynchronize(r->stream));
+  for (int b = 0; b < B; ++b) {
+    ArgPair best = r->h_pairs[b];
+    for (int k = 1; k < r->tp; ++k) {
+      const ArgPair p = r->h_pairs[(size_t)k * B + b];
+      if (p.val > best.val || (p.val == best.val && p.idx > best.idx)) best = p;
+    }
+    out_tokens[b] = best.idx;
+  }
+  return NVC_OK;
+}
+
+int decode_body(nvc_runner* r, int B, int blocks_hint) {
+  int rc = nvc_embed_gather(r->ctx, r->d_ids, r->embed, r->x, B, r->cfg.hidden_size, r->cfg.vocab_size, r->stream);
+  if (rc) return rc;
+  rc = run_layers(r, B, true, B, 1, blocks_hint);
+  if (rc) return rc;
+  return run_head(r, B, true);
+}
+
+int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+}  // namespace
+
+extern "C" {
+
+int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runner_options* opt, nvc_runner** out) {
+  NVC_REQUIRE(ctx, ctx && cfg && opt && out, NVC_EINVAL, "null pointer");
+  *out = nullptr;
+  const int tp = ctx->tp_size;
+  NVC_REQUIRE(ctx, cfg->head_dim == 128, NVC_ESHAPE, "head_dim must be 128");
+  NVC_REQUIRE(ctx, cfg->num_attention_heads % cfg->num_key_value_heads == 0, NVC_ESHAPE, "nh % kv != 0");
+  NVC_REQUIRE(ctx, cfg->num_key_value_heads % tp == 0 && cfg->num_attention_heads % tp == 0, NVC_ESHAPE,
+              "heads must divide by tp_size");
+  NVC_REQUIRE(ctx, cfg->intermediate_size % (tp * 64) == 0, NVC_ESHAPE, "intermediate_size must divide by tp_size*64");
+  NVC_REQUIRE(ctx, cfg->vocab_size % (tp * 16) == 0, NVC_ESHAPE, "vocab_size must divide by tp_size*16");
+  NVC_REQUIRE(ctx, cfg->hidden_size % 64 == 0, NVC_ESHAPE, "hidden_size must be a multiple of 64");
+  NVC_REQUIRE(ctx, opt->kvcache_block_size > 0 && opt->kvcache_block_size % 16 == 0, NVC_ESHAPE, "block size % 16");
+  NVC_REQUIRE(ctx, opt->allreduce_f32 == 0, NVC_ENOTIMPL, "allreduce_f32 is not implemented");
+  NVC_REQUIRE(ctx, opt->num_kvcache_blocks > 0 && opt->max_num_seqs > 0 && opt->max_num_batched_tokens > 0 &&
+                       opt->max_model_len > 0, NVC_EINVAL, "bad runner options");
+  NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+  nvc_runner* r = new nvc_runner();
+  r->ctx = ctx;
+  r->cfg = *cfg;
+  r->opt = *opt;
+  r->tp = tp;
+  r->rank = ctx->tp_rank;
+  r->nh_l = cfg->num_attention_heads / tp;
+  r->kv_l = cfg->num_key_value_heads / tp;
+  r->I_l = cfg->intermediate_size / tp;
+  r->V_l = cfg->vocab_size / tp;
+  r->qkv_l = (r->nh_l + 2 * r->kv_l) * cfg->head_dim;
+  r->max_blocks_cap = (opt->max_model_len + opt->kvcache_block_size - 1) / opt->kvcache_block_size;
+  *out = r;   // from here on the caller destroys it, also on failure
+  int rc;
+  R_CUDA(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
+  const int H = cfg->hidden_size, hd = cfg->head_dim;
+  const size_t T = (size_t)std::max(opt->max_num_batched_tokens, opt->max_num_seqs);
+  const size_t Bm = (size_t)opt->max_num_seqs;
+  r->layers.resize(cfg->num_hidden_layers);
+  const size_t cache_elems = (size_t)opt->num_kvcache_blocks * opt->kvcache_block_size * r->kv_l * hd;
+  for (auto& L : r->layers) {
+    if ((rc = dev_alloc(r, &L.w_qkv, (size_t)r->qkv_l * H))) return rc;
+    if ((rc = dev_alloc(r, &L.w_o, (size_t)H * r->nh_l * hd))) return rc;
+    if ((rc = dev_alloc(r, &L.q_norm, hd))) return rc;
+    if ((rc = dev_alloc(r, &L.k_norm, hd))) return rc;
+    if ((rc = dev_alloc(r, &L.w_gu, (size_t)2 * r->I_l * H))) return rc;
+    if ((rc = dev_alloc(r, &L.w_down, (size_t)H * r->I_l))) return rc;
+    if ((rc = dev_alloc(r, &L.ln1, H))) return rc;
+    if ((rc = dev_alloc(r, &L.ln2, H))) return rc;
+    if ((rc = dev_alloc(r, &L.k_cache, cache_elems))) return rc;
+    if ((rc = dev_alloc(r, &L.v_cache, cache_elems))) return rc;
+    r->weight_bytes += 2 * ((int64_t)r->qkv_l * H + (int64_t)H * r->nh_l * hd + 2 * hd + 3 * (int64_t)r->I_l * H + 2 * H);
+  }
+  if ((rc = dev_alloc(r, &r->embed, (size_t)cfg->vocab_size * H))) return rc;
+  if ((rc = dev_alloc(r, &r->final_norm, H))) return rc;
+  if ((rc = dev_alloc(r, &r->lm_head, (size_t)r->V_l * H))) return rc;
+  r->weight_bytes += 2 * ((int64_t)cfg->vocab_size * H + H + (int64_t)r->V_l * H);
+  if ((rc = dev_alloc(r, &r->rope, (size_t)opt->max_model_len * hd))) return rc;
+  if ((rc = dev_alloc(r, &r->x, T * H))) return rc;
+  if ((rc = dev_alloc(r, &r->xn, T * H))) return rc;
+  if ((rc = dev_alloc(r, &r->residual, T * H))) return rc;
+  if ((rc = dev_alloc(r, &r->qkv, T * r->qkv_l))) return rc;
+  if ((rc = dev_alloc(r, &r->attn, T * r->nh_l * hd))) return rc;
+  if ((rc = dev_alloc(r, &r->gu, T * 2 * r->I_l))) return rc;
+  if ((rc = dev_alloc(r, &r->act, T * r->I_l))) return rc;
+  if ((rc = dev_alloc(r, &r->x_last, Bm * H))) return rc;
+  if ((rc = dev_alloc(r, &r->xn_last, Bm * H))) return rc;
+  if ((rc = dev_alloc(r, &r->res_last, Bm * H))) return rc;
+  if ((rc = dev_alloc(r, &r->logits, Bm * r->V_l))) return rc;
+  r->decode_ws_bytes = 0;
+  for (int b = 1; b <= opt->max_num_seqs; ++b)
+    r->decode_ws_bytes = std::max(r->decode_ws_bytes, nvc_paged_decode_workspace_bytes(b, r->nh_l, hd, ctx->num_sms));
+  if ((rc = dev_alloc(r, reinterpret_cast<uint8_t**>(&r->decode_ws), r->decode_ws_bytes))) return rc;
+  if ((rc = dev_alloc(r, &r->d_ids, T))) return rc;
+  if ((rc = dev_alloc(r, &r->d_pos, T))) return rc;
+  if ((rc = dev_alloc(r, &r->d_slots, T))) return rc;
+  if ((rc = dev_alloc(r, &r->d_cu, Bm + 1))) return rc;
+  if ((rc = dev_alloc(r, &r->d_bt, Bm * r->max_blocks_cap))) return rc;
+  if ((rc = dev_alloc(r, &r->d_ctx, Bm))) return rc;
+  if ((rc = dev_alloc(r, &r->d_last_rows, Bm))) return rc;
+  if ((rc = dev_alloc(r, &r->d_tok, Bm))) return rc;
+  if ((rc = dev_alloc(r, &r->d_tok_val, Bm))) return rc;
+  if ((rc = dev_alloc(r, &r->d_pairs, Bm * tp))) return rc;
+  r->h_stage_ints = 3 * T + (Bm + 1) + Bm * r->max_blocks_cap + 2 * Bm;
+  R_CUDA(cudaMallocHost(&r->h_stage, r->h_stage_ints * sizeof(int32_t)));
+  R_CUDA(cudaMallocHost(&r->h_pairs, Bm * tp * sizeof(ArgPair)));
+  R_CUDA(cudaMallocHost(&r->h_tok, Bm * sizeof(int32_t)));
+  return NVC_OK;
+}
+
+int nvc_runner_destroy(nvc_runner* r) {
+  if (!r) return NVC_EINVAL;
+  cudaSetDevice(r->ctx->device);
+  if (r->stream) cudaStreamSynchronize(r->stream);
+  for (auto& g : r->graphs) cudaGraphExecDestroy(g.second);
+  for (void* p : r->allocs) cudaFree(p);
+  if (r->h_stage) cudaFreeHost(r->h_stage);
+  if (r->h_pairs) cudaFreeHost(r->h_pairs);
+  if (r->h_tok) cudaFreeHost(r->h_tok);
+  if (r->stream) cudaStreamDestroy(r->stream);
+  delete r;
+  return NVC_OK;
+}
+
+int64_t nvc_runner_weight_bytes(const nvc_runner* r) { return r ? r->weight_bytes : 0; }
+int64_t nvc_runner_kv_bytes_per_token(const nvc_runner* r) {
+  return r ? (int64_t)2 * r->cfg.num_hidden_layers * r->kv_l * r->cfg.head_dim * 2 : 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// weights
+// ------------------------------------------------------------------------------------------
+namespace {
+
+int copy_rows(nvc_runner* r, nvc_bf16* dst, const nvc_bf16* src, int64_t row0, int64_t nrows, int64_t cols) {
+  R_CUDA(cudaMemcpy(dst, src + row0 * cols, (size_t)nrows * cols * 2, cudaMemcpyHostToDevice));
+  return NVC_OK;
+}
+// dst[rows, ncols] = src[rows, col0 : col0+ncols] of a [rows, cols] matrix
+int copy_cols(nvc_runner* r, nvc_bf16* dst, const nvc_bf16* src, int64_t rows, int64_t cols, int64_t col0, int64_t ncols) {
+  R_CUDA(cudaMemcpy2D(dst, (size_t)ncols * 2, src + col0, (size_t)cols * 2, (size_t)ncols * 2, (size_t)rows,
+                      cudaMemcpyHostToDevice));
+  return NVC_OK;
+}
+
+}  // namespace
+
+extern "C" int nvc_runner_load_weight(nvc_runner* r, const char* hf_name, const nvc_bf16* data, int64_t rows,
+                                      int64_t cols) {
+  if (!r) return NVC_EINVAL;
+  nvc_ctx* ctx = r->ctx;
+  NVC_REQUIRE(ctx, hf_name && data, NVC_EINVAL, "null pointer");
+  NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+  const nvc_qwen3_config& c = r->cfg;
+  const int64_t H = c.hidden_size, hd = c.head_dim, V = c.vocab_size, I = c.intermediate_size;
+  const int64_t nh = c.num_attention_heads, kv = c.num_key_value_heads;
+  const std::string name(hf_name);
+  auto shape_is = [&](int64_t rr, int64_t cc) { return rows == rr && cols == cc; };
+  auto bad_shape = [&]() {
+    nvc_set_error(ctx, "nvc_runner_load_weight: unexpected shape [" + std::to_string(rows) + "," +
+                           std::to_string(cols) + "] for " + name);
+    return NVC_ESHAPE;
+  };
+  int rc = NVC_OK;
+  if (name == "model.embed_tokens.weight") {
+    if (!shape_is(V, H)) return bad_shape();
+    rc = copy_rows(r, r->embed, data, 0, V, H);
+  } else if (name == "model.norm.weight") {
+    if (!shape_is(H, 1)) return bad_shape();
+    rc = copy_rows(r, r->final_norm, data, 0, H, 1);
+  } else if (name == "lm_head.weight") {
+    if (!shape_is(V, H)) return bad_shape();
+    rc = copy_rows(r, r->lm_head, data, (int64_t)r->rank * r->V_l, r->V_l, H);   // vocab (column-parallel) shard
+  } else if (name.rfind("model.layers.", 0) == 0) {
+    const size_t p0 = strlen("model.layers.");
+    const size_t p1 = name.find('.', p0);
+    NVC_REQUIRE(ctx, p1 != std::string::npos, NVC_EINVAL, "malformed tensor name " + name);
+    const int li = atoi(name.substr(p0, p1 - p0).c_str());
+    NVC_REQUIRE(ctx, li >= 0 && li < c.num_hidden_layers, NVC_EINVAL, "layer index out of range in " + name);
+    Layer& L = r->layers[li];
+    const std::string sub = name.substr(p1 + 1);
+    const int64_t qrows = (int64_t)r->nh_l * hd, kvrows = (int64_t)r->kv_l * hd;
+    if (sub == "self_attn.q_proj.weight") {            // fused rows [q; k; v], qwen3.rs:171
+      if (!shape_is(nh * hd, H)) return bad_shape();
+      rc = copy_rows(r, L.w_qkv, data, r->rank * qrows, qrows, H);
+    } else if (sub == "self_attn.k_proj.weight") {
+      if (!shape_is(kv * hd, H)) return bad_shape();
+      rc = copy_rows(r, L.w_qkv + qrows * H, data, r->rank * kvrows, kvrows, H);
+    } else if (sub == "self_attn.v_proj.weight") {
+      if (!shape_is(kv * hd, H)) return bad_shape();
+      rc = copy_rows(r, L.w_qkv + (qrows + kvrows) * H, data, r->rank * kvrows, kvrows, H);
+    } else if (sub == "self_attn.o_proj.weight") {     // row-parallel: shard the INPUT dim
+      if (!shape_is(H, nh * hd)) return bad_shape();
+      rc = copy_cols(r, L.w_o, data, H, nh * hd, r->rank * qrows, qrows);
+    } else if (sub == "self_attn.q_norm.weight") {
+      if (!shape_is(hd, 1)) return bad_shape();
+      rc = copy_rows(r, L.q_norm, data, 0, hd, 1);
+    } else if (sub == "self_attn.k_norm.weight") {
+      if (!shape_is(hd, 1)) return bad_shape();
+      rc = copy_rows(r, L.k_norm, data, 0, hd, 1);
+    } else if (sub == "mlp.gate_proj.weight") {        // fused rows [gate; up], qwen3.rs:310
+      if (!shape_is(I, H)) return bad_shape();
+      rc = copy_rows(r, L.w_gu, data, (int64_t)r->rank * r->I_l, r->I_l, H);
+    } else if (sub == "mlp.up_proj.weight") {
+      if (!shape_is(I, H)) return bad_shape();
+      rc = copy_rows(r, L.w_gu + (int64_t)r->I_l * H, data, (int64_t)r->rank * r->I_l, r->I_l, H);
+    } else if (sub == "mlp.down_proj.weight") {
+      if (!shape_is(H, I)) return bad_shape();
+      rc = copy_cols(r, L.w_down, data, H, I, (int64_t)r->rank * r->I_l, r->I_l);
+    } else if (sub == "input_layernorm.weight") {
+      if (!shape_is(H, 1)) return bad_shape();
+      rc = copy_rows(r, L.ln1, data, 0, H, 1);
+    } else if (sub == "post_attention_layernorm.weight") {
+      if (!shape_is(H, 1)) return bad_shape();
+      rc = copy_rows(r, L.ln2, data, 0, H, 1);
+    } else {
+      NVC_REQUIRE(ctx, false, NVC_EINVAL, "unknown tensor " + name);
+    }
+  } else {
+    NVC_REQUIRE(ctx, false, NVC_EINVAL, "unknown tensor " + name);
+  }
+  if (rc == NVC_OK) r->loaded.insert(name);
+  return rc;
+}
+
+extern "C" int nvc_runner_finalize(nvc_runner* r) {
+  if (!r) return NVC_EINVAL;
+  nvc_ctx* ctx = r->ctx;
+  const size_t want = 3 + 11 * (size_t)r->cfg.num_hidden_layers;
+  NVC_REQUIRE(ctx, r->loaded.size() == want, NVC_ESTATE,
+              "missing weights: " + std::to_string(r->loaded.size()) + " of " + std::to_string(want) +
+                  " tensors loaded (lm_head.weight has no tied-embedding fallback, qwen3.rs:525-528)");
+  int rc = nvc_rope_table_init_sync(ctx, r->cfg.rope_theta, r->cfg.head_dim, r->opt.max_model_len, r->rope);
+  if (rc) return rc;
+  r->finalized = true;
+  return NVC_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// steps
+// ------------------------------------------------------------------------------------------
+extern "C" int nvc_runner_prefill(nvc_runner* r, const int32_t* ids, const int32_t* positions,
+                                  const int32_t* cu_seqlens, const int32_t* slot_mapping, int B, int N, int max_seqlen,
+                                  int32_t* out_tokens) {
+  if (!r) return NVC_EINVAL;
+  nvc_ctx* ctx = r->ctx;
+  NVC_REQUIRE(ctx, r->finalized, NVC_ESTATE, "nvc_runner_finalize not called");
+  NVC_REQUIRE(ctx, ids && positions && cu_seqlens && slot_mapping && out_tokens, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, B > 0 && N > 0 && B <= r->opt.max_num_seqs && N <= r->opt.max_num_batched_tokens, NVC_ENOMEM,
+              "prefill step exceeds max_num_seqs / max_num_batched_tokens");
+  NVC_REQUIRE(ctx, cu_seqlens[0] == 0 && cu_seqlens[B] == N, NVC_EINVAL, "cu_seqlens does not cover N tokens");
+  const int64_t nslots = (int64_t)r->opt.num_kvcache_blocks * r->opt.kvcache_block_size;
+  for (int i = 0; i < N; ++i) {
+    NVC_REQUIRE(ctx, ids[i] >= 0 && ids[i] < r->cfg.vocab_size, NVC_EINVAL, "token id out of range");
+    NVC_REQUIRE(ctx, positions[i] >= 0 && positions[i] < r->opt.max_model_len, NVC_EINVAL, "position out of range");
+    NVC_REQUIRE(ctx, slot_mapping[i] >= -1 && slot_mapping[i] < nslots, NVC_EINVAL, "slot out of range");
+  }
+  NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+  int32_t* h = r->h_stage;
+  memcpy(h, ids, N * 4);
+  memcpy(h + N, positions, N * 4);
+  memcpy(h + 2 * N, slot_mapping, N * 4);
+  memcpy(h + 3 * N, cu_seqlens, (B + 1) * 4);
+  int32_t* last = h + 3 * N + B + 1;
+  for (int b = 0; b < B; ++b) {
+    NVC_REQUIRE(ctx, cu_seqlens[b + 1] > cu_seqlens[b] && cu_seqlens[b + 1] - cu_seqlens[b] <= max_seqlen, NVC_EINVAL,
+                "bad cu_seqlens / max_seqlen");
+    last[b] = cu_seqlens[b + 1] - 1;
+  }
+  cudaStream_t st = r->stream;
+  R_CUDA(cudaMemcpyAsync(r->d_ids, h, N * 4, cudaMemcpyHostToDevice, st));
+  R_CUDA(cudaMemcpyAsync(r->d_pos, h + N, N * 4, cudaMemcpyHostToDevice, st));
+  R_CUDA(cudaMemcpyAsync(r->d_slots, h + 2 * N, N * 4, cudaMemcpyHostToDevice, st));
+  R_CUDA(cudaMemcpyAsync(r->d_cu, h + 3 * N, (B + 1) * 4, cudaMemcpyHostToDevice, st));
+  R_CUDA(cudaMemcpyAsync(r->d_last_rows, last, B * 4, cudaMemcpyHostToDevice, st));
+  int rc = nvc_embed_gather(ctx, r->d_ids, r->embed, r->x, N, r->cfg.hidden_size, r->cfg.vocab_size, st);
+  if (rc) return rc;
+  rc = run_layers(r, N, false, B, max_seqlen, 0);
+  if (rc) return rc;
+  rc = run_head(r, B, false);
+  if (rc) return rc;
+  r->last_B = B;
+  return finish_tokens(r, B, out_tokens);
+}
+
+extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_t* positions,
+                                 const int32_t* slot_mapping, const int32_t* block_tables, int max_blocks,
+                                 const int32_t* context_lens, int B, int32_t* out_tokens) {
+  if (!r) return NVC_EINVAL;
+  nvc_ctx* ctx = r->ctx;
+  NVC_REQUIRE(ctx, r->finalized, NVC_ESTATE, "nvc_runner_finalize not called");
+  NVC_REQUIRE(ctx, ids && positions && slot_mapping && block_tables && context_lens && out_tokens, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, B > 0 && B <= r->opt.max_num_seqs, NVC_ENOMEM, "decode batch exceeds max_num_seqs");
+  NVC_REQUIRE(ctx, max_blocks > 0 && max_blocks <= r->max_blocks_cap, NVC_ENOMEM, "block table wider than max_model_len allows");
+  const int bs = r->opt.kvcache_block_size;
+  const int64_t nslots = (int64_t)r->opt.num_kvcache_blocks * bs;
+  for (int b = 0; b < B; ++b) {
+    NVC_REQUIRE(ctx, ids[b] >= 0 && ids[b] < r->cfg.vocab_size, NVC_EINVAL, "token id out of range");
+    NVC_REQUIRE(ctx, positions[b] >= 0 && positions[b] < r->opt.max_model_len, NVC_EINVAL, "position out of range");
+    NVC_REQUIRE(ctx, slot_mapping[b] >= 0 && slot_mapping[b] < nslots, NVC_EINVAL, "slot out of range");
+    NVC_REQUIRE(ctx, context_lens[b] > 0 && (context_lens[b] + bs - 1) / bs <= max_blocks, NVC_EINVAL, "context_len vs block table");
+    for (int j = 0; j < (context_lens[b] + bs - 1) / bs; ++j)
+      NVC_REQUIRE(ctx, block_tables[(size_t)b * max_blocks + j] >= 0 &&
+                           block_tables[(size_t)b * max_blocks + j] < r->opt.num_kvcache_blocks, NVC_EINVAL, "block id out of range");
+  }
+  NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+  int32_t* h = r->h_stage;
+  memcpy(h, ids, B * 4);
+  memcpy(h + B, positions, B * 4);
+  memcpy(h + 2 * B, slot_mapping, B * 4);
+  memcpy(h + 3 * B, context_lens, B * 4);
+  int32_t* hbt = h + 4 * B;
+  const int cap = r->max_blocks_cap;
+  for (int b = 0; b < B; ++b) {
+    memcpy(hbt + (size_t)b * cap, block_tables + (size_t)b * max_blocks, max_blocks * 4);
+    for (int j = max_blocks; j < cap; ++j) hbt[(size_t)b * cap + j] = -1;
+  }
+  cudaStream_t st = r->stream;
+  R_CUDA(cudaMemcpyAsync(r->d_ids, h, B * 4, cudaMemcpyHostToDevice, st));
+  R_CUDA(cudaMemcpyAsync(r->d_pos, h + B, B * 4, cudaMemcpyHostToDevice, st));
+  R_CUDA(cudaMemcpyAsync(r->d_slots, h + 2 * B, B * 4, cudaMemcpyHostToDevice, st));
+  R_CUDA(cudaMemcpyAsync(r->d_ctx, h + 3 * B, B * 4, cudaMemcpyHostToDevice, st));
+  R_CUDA(cudaMemcpyAsync(r->d_bt, hbt, (size_t)B * cap * 4, cudaMemcpyHostToDevice, st));
+  const int hint = std::min(next_pow2(max_blocks), cap);
+  int rc;
+  if (r->opt.use_cuda_graph) {
+    const auto key = std::make_pair(B, hint);
+    auto it = r->graphs.find(key);
+    if (it == r->graphs.end()) {
+      // capture this (batch size, context bucket) once; pointers and shapes are fixed inside
+      const uint64_t l0 = ctx->launches;
+      R_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+      rc = decode_body(r, B, hint);
+      cudaGraph_t graph = nullptr;
+      cudaError_t ce = cudaStreamEndCapture(st, &graph);
+      if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+      R_CUDA(ce);
+      cudaGraphExec_t exec = nullptr;
+      ce = cudaGraphInstantiate(&exec, graph, 0);
+      cudaGraphDestroy(graph);
+      R_CUDA(ce);
+      r->launches_per_decode = (int)(ctx->launches - l0);
+      it = r->graphs.emplace(key, exec).first;
+    }
+    R_CUDA(cudaGraphLaunch(it->second, st));
+  } else {
+    const uint64_t l0 = ctx->launches;
+    rc = decode_body(r, B, hint);
+    if (rc) return rc;
+    r->launches_per_decode = (int)(ctx->launches - l0);
+  }
+  r->last_B = B;
+  r->last_decode_hint = hint;
+  return finish_tokens(r, B, out_tokens);
+}
+
+extern "C" int nvc_runner_last_logits(nvc_runner* r, float* out, int B) {
+  if (!r) return NVC_EINVAL;
+  nvc_ctx* ctx = r->ctx;
+  NVC_REQUIRE(ctx, out && B > 0 && B <= r->last_B, NVC_EINVAL, "no logits for that batch");
+  NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+  R_CUDA(cudaMemcpyAsync(out, r->logits, (size_t)B * r->V_l * sizeof(float), cudaMemcpyDeviceToHost, r->stream));
+  R_CUDA(cudaStreamSynchronize(r->stream));
+  return NVC_OK;
+}
+
+extern "C" int nvc_runner_time_decode(nvc_runner* r, int iters, float* ms_per_step, int* launches_per_step) {
+  if (!r) return NVC_EINVAL;
+  nvc_ctx* ctx = r->ctx;
+  NVC_REQUIRE(ctx, ms_per_step && iters > 0, NVC_EINVAL, "bad arguments");
+  NVC_REQUIRE(ctx, r->last_B > 0 && r->last_decode_hint > 0, NVC_ESTATE, "no decode step has run yet");
+  NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+  cudaEvent_t e0, e1;
+  R_CUDA(cudaEventCreate(&e0));
+  R_CUDA(cudaEventCreate(&e1));
+  cudaStream_t st = r->stream;
+  auto it = r->graphs.find(std::make_pair(r->last_B, r->last_decode_hint));
+  R_CUDA(cudaStreamSynchronize(st));
+  R_CUDA(cudaEventRecord(e0, st));
+  int rc = NVC_OK;
+  for (int i = 0; i < iters && rc == NVC_OK; ++i) {
+    if (it != r->graphs.end()) {
+      cudaError_t ce = cudaGraphLaunch(it->second, st);
+      if (ce != cudaSuccess) rc = NVC_CUDA_ERROR_BASE + (int)ce;
+    } else {
+      rc = decode_body(r, r->last_B, r->last_decode_hint);
+    }
+  }
+  cudaEventRecord(e1, st);
+  cudaError_t ce = cudaEventSynchronize(e1);
+  float ms = 0.f;
+  if (ce == cudaSuccess) ce = cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (rc) return rc;
+  R_CUDA(ce);
+  *ms_per_step = ms / iters;
+  if (launches_per_step) *launches_per_step = r->launches_per_decode;
+  return NVC_OK;
+}
+
+// ------------------------------------------------------------------------------------------
+// Per-kernel timing for bench.py's roofline line: runs ONE kernel family over every layer's
+// own weights / KV pool (so the working set is the real one, far larger than L2) with the
+// inputs of the last decode step, `iters` times, between CUDA events on the runner's stream.
+// ------------------------------------------------------------------------------------------
+extern "C" int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_per_launch, int* launches) {
+  if (!r) return NVC_EINVAL;
+  nvc_ctx* ctx = r->ctx;
+  NVC_REQUIRE(ctx, ms_per_launch && iters > 0, NVC_EINVAL, "bad arguments");
+  NVC_REQUIRE(ctx, r->last_B > 0 && r->last_decode_hint > 0, NVC_ESTATE, "no decode step has run yet");
+  NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+  const nvc_qwen3_config& c = r->cfg;
+  const int B = r->last_B, H = c.hidden_size, hd = c.head_dim;
+  const float scale = 1.0f / sqrtf((float)hd);
+  void* st = r->stream;
+  cudaEvent_t e0, e1;
+  R_CUDA(cudaEventCreate(&e0));
+  R_CUDA(cudaEventCreate(&e1));
+  R_CUDA(cudaStreamSynchronize(r->stream));
+  int rc = NVC_OK, n = 0;
+  const uint64_t l0 = ctx->launches;
+  R_CUDA(cudaEventRecord(e0, r->stream));
+  for (int it = 0; it < iters && rc == NVC_OK; ++it) {
+    if (op == NVC_OP_LM_HEAD) {
+      rc = nvc_gemm_bf16(ctx, r->xn_last, H, r->lm_head, r->logits, r->V_l, NVC_DT_F32, B, r->V_l, H, st);
+      ++n;
+      continue;
+    }
+    if (op == NVC_OP_ARGMAX) {
+      rc = nvc_argmax_last(ctx, r->logits, r->V_l, r->d_tok, r->d_tok_val, B, r->V_l, r->rank * r->V_l, st);
+      ++n;
+      continue;
+    }
+    for (int li = 0; li < c.num_hidden_layers && rc == NVC_OK; ++li, ++n) {
+      Layer& L = r->layers[li];
+      switch (op) {
+        case NVC_OP_PAGED_DECODE:
+          rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, L.k_cache, L.v_cache, r->d_bt, r->max_blocks_cap,
+                                        r->last_decode_hint, r->d_ctx, B, r->nh_l, r->kv_l, hd,
+                                        r->opt.kvcache_block_size, scale, r->attn, r->decode_ws, r->decode_ws_bytes, st);
+          break;
+        case NVC_OP_GEMM_QKV:
+          rc = nvc_gemm_bf16(ctx, r->xn, H, L.w_qkv, r->qkv, r->qkv_l, NVC_DT_BF16, B, r->qkv_l, H, st);
+          break;
+        case NVC_OP_GEMM_O:
+          rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, L.w_o, r->x, H, NVC_DT_BF16, B, H, r->nh_l * hd, st);
+          break;
+        case NVC_OP_GEMM_GATE_UP:
+          rc = nvc_gemm_bf16(ctx, r->xn, H, L.w_gu, r->gu, 2 * r->I_l, NVC_DT_BF16, B, 2 * r->I_l, H, st);
+          break;
+        case NVC_OP_GEMM_DOWN:
+          rc = nvc_gemm_bf16(ctx, r->act, r->I_l, L.w_down, r->x, H, NVC_DT_BF16, B, H, r->I_l, st);
+          break;
+        case NVC_OP_RMSNORM:
+          rc = nvc_fused_add_rmsnorm(ctx, r->x, r->residual, r->residual, L.ln2, c.rms_norm_eps, r->xn, B, H, st);
+          break;
+        case NVC_OP_QK_NORM_ROPE:
+          // slot_mapping = NULL: do not scatter (the qkv buffer no longer holds this step's k/v)
+          rc = nvc_qk_norm_rope_store(ctx, r->qkv, L.q_norm, L.k_norm, c.rms_norm_eps, r->rope, r->d_pos, nullptr,
+                                      nullptr, nullptr, B, r->nh_l, r->kv_l, hd, st);
+          break;
+        case NVC_OP_SILU_MUL:
+          rc = nvc_silu_and_mul(ctx, r->gu, r->act, B, r->I_l, st);
+          break;
+        default:
+          rc = NVC_EINVAL;
+      }
+    }
+  }
+  cudaEventRecord(e1, r->stream);
+  cudaError_t ce = cudaEventSynchronize(e1);
+  float ms = 0.f;
+  if (ce == cudaSuccess) ce = cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  if (rc) return rc;
+  R_CUDA(ce);
+  const int kernels = (int)(ctx->launches - l0);
+  *ms_per_launch = n ? ms / n : 0.f;
+  if (launches) *launches = kernels;
+  return NVC_OK;
+}

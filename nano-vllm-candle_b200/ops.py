@@ -1,0 +1,179 @@
+"""Kernel-level Python entry points: torch tensors are used ONLY as device-memory handles
+(data_ptr) and for the current CUDA stream; all compute is in libnvc_b200.so through the C ABI
+(include/nvc_b200.h).  There is no torch / CPU fallback: a missing library or a non-zero status
+raises."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import check
+
+BF16 = torch.bfloat16
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _req(t: torch.Tensor, dtype, name: str):
+    if not t.is_cuda:
+        raise ValueError(f"{name} must be a CUDA tensor (no CPU fallback on this path)")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+
+
+class Context:
+    """nvc_ctx: one per (process, device).  Mirrors TPConfig{size, rank} (src/tp.rs:3-70)."""
+
+    def __init__(self, device: int = 0, tp_rank: int = 0, tp_size: int = 1):
+        self.l = _lib.lib()
+        h = C.c_void_p()
+        check(self.l.nvc_ctx_create(device, tp_rank, tp_size, C.byref(h)), "nvc_ctx_create")
+        self.h = h
+        self.device = device
+        self.tp_rank, self.tp_size = tp_rank, tp_size
+        self.num_sms = self.l.nvc_ctx_num_sms(self.h)
+        self._ws = None
+
+    def close(self):
+        if self.h:
+            self.l.nvc_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, st, where):
+        check(st, where, self.h)
+
+    # ---- collectives
+    @staticmethod
+    def nccl_unique_id() -> bytes:
+        buf = C.create_string_buffer(128)
+        check(_lib.lib().nvc_nccl_unique_id(buf), "nvc_nccl_unique_id")
+        return buf.raw
+
+    def init_nccl(self, unique_id: bytes):
+        assert len(unique_id) == 128
+        self._ck(self.l.nvc_ctx_init_nccl(self.h, C.c_char_p(unique_id)), "nvc_ctx_init_nccl")
+
+    def allreduce(self, buf: torch.Tensor):
+        if buf.dtype == BF16:
+            self._ck(self.l.nvc_allreduce_bf16(self.h, _ptr(buf), buf.numel(), _stream()), "nvc_allreduce_bf16")
+        elif buf.dtype == torch.float32:
+            self._ck(self.l.nvc_allreduce_f32(self.h, _ptr(buf), buf.numel(), _stream()), "nvc_allreduce_f32")
+        else:
+            raise TypeError("allreduce: bf16 or f32")
+        return buf
+
+    # ---- kernels
+    def embed_gather(self, ids: torch.Tensor, table: torch.Tensor, out: Optional[torch.Tensor] = None):
+        _req(ids, torch.int32, "ids"); _req(table, BF16, "table")
+        N, (V, H) = ids.numel(), table.shape
+        out = torch.empty((N, H), dtype=BF16, device=table.device) if out is None else out
+        self._ck(self.l.nvc_embed_gather(self.h, _ptr(ids), _ptr(table), _ptr(out), N, H, V, _stream()), "nvc_embed_gather")
+        return out
+
+    def fused_add_rmsnorm(self, x, w, eps, residual_in=None, residual_out=None, out=None):
+        _req(x, BF16, "x"); _req(w, BF16, "w")
+        N, H = x.shape
+        out = torch.empty_like(x) if out is None else out
+        self._ck(self.l.nvc_fused_add_rmsnorm(self.h, _ptr(x), _ptr(residual_in), _ptr(residual_out), _ptr(w),
+                                              float(eps), _ptr(out), N, H, _stream()), "nvc_fused_add_rmsnorm")
+        return out
+
+    def gemm(self, a: torch.Tensor, w: torch.Tensor, out_dtype=BF16, out=None, force_bn=0, force_splits=0):
+        """C = a @ w.T; a [M,K] (row stride allowed), w [N,K] contiguous."""
+        _req(a, BF16, "a"); _req(w, BF16, "w")
+        M, K = a.shape
+        N = w.shape[0]
+        assert w.shape[1] == K and w.is_contiguous() and a.stride(1) == 1
+        if out is None:
+            out = torch.empty((M, N), dtype=out_dtype, device=a.device)
+        dt = 0 if out.dtype == BF16 else 1
+        self._ck(self.l.nvc_gemm_bf16_ex(self.h, _ptr(a), a.stride(0), _ptr(w), _ptr(out), out.stride(0), dt,
+                                         M, N, K, force_bn, force_splits, _stream()), "nvc_gemm_bf16")
+        return out
+
+    def rope_table(self, theta: float, head_dim: int, max_pos: int, device=None):
+        dev = torch.device("cuda", self.device) if device is None else device
+        tab = torch.empty((max_pos, head_dim), dtype=torch.float32, device=dev)
+        self._ck(self.l.nvc_rope_table_init_sync(self.h, float(theta), head_dim, max_pos, _ptr(tab)), "nvc_rope_table_init_sync")
+        return tab
+
+    def qk_norm_rope_store(self, qkv, qw, kw, eps, cos_sin, positions, nh, kv, hd,
+                           slot_mapping=None, k_cache=None, v_cache=None):
+        _req(qkv, BF16, "qkv"); _req(positions, torch.int32, "positions")
+        N = qkv.shape[0]
+        assert qkv.is_contiguous() and qkv.shape[1] == (nh + 2 * kv) * hd
+        self._ck(self.l.nvc_qk_norm_rope_store(self.h, _ptr(qkv), _ptr(qw), _ptr(kw), float(eps), _ptr(cos_sin),
+                                               _ptr(positions), _ptr(slot_mapping), _ptr(k_cache), _ptr(v_cache),
+                                               N, nh, kv, hd, _stream()), "nvc_qk_norm_rope_store")
+        return qkv
+
+    def store_kvcache(self, k, v, k_cache, v_cache, slot_mapping, kv, hd):
+        _req(k, BF16, "k"); _req(slot_mapping, torch.int32, "slot_mapping")
+        N = k.shape[0]
+        assert k.stride(0) == v.stride(0)
+        self._ck(self.l.nvc_store_kvcache(self.h, _ptr(k), _ptr(v), k.stride(0), _ptr(k_cache), _ptr(v_cache),
+                                          _ptr(slot_mapping), N, kv, hd, _stream()), "nvc_store_kvcache")
+
+    def prefill_attn(self, q, k, v, cu_seqlens, max_seqlen, nh, kv, hd, scale, out=None):
+        """q [N, nh*hd], k/v [N, kv*hd] views (row stride allowed)."""
+        _req(q, BF16, "q"); _req(cu_seqlens, torch.int32, "cu_seqlens")
+        N = q.shape[0]
+        B = cu_seqlens.numel() - 1
+        out = torch.empty((N, nh * hd), dtype=BF16, device=q.device) if out is None else out
+        self._ck(self.l.nvc_prefill_attn_varlen(self.h, _ptr(q), q.stride(0), _ptr(k), k.stride(0), _ptr(v), v.stride(0),
+                                                _ptr(cu_seqlens), B, N, max_seqlen, nh, kv, hd, float(scale),
+                                                _ptr(out), _stream()), "nvc_prefill_attn_varlen")
+        return out
+
+    def paged_decode_attn(self, q, k_cache, v_cache, block_tables, context_lens, nh, kv, hd, block_size, scale, out=None):
+        _req(q, BF16, "q"); _req(block_tables, torch.int32, "block_tables"); _req(context_lens, torch.int32, "context_lens")
+        B = q.shape[0]
+        out = torch.empty((B, nh * hd), dtype=BF16, device=q.device) if out is None else out
+        need = self.l.nvc_paged_decode_workspace_bytes(B, nh, hd, self.num_sms)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(max(need, 1), dtype=torch.uint8, device=q.device)
+        self._ck(self.l.nvc_paged_decode_attn(self.h, _ptr(q), q.stride(0), _ptr(k_cache), _ptr(v_cache),
+                                              _ptr(block_tables), block_tables.shape[1], _ptr(context_lens), B, nh, kv,
+                                              hd, block_size, float(scale), _ptr(out), _ptr(self._ws),
+                                              self._ws.numel(), _stream()), "nvc_paged_decode_attn")
+        return out
+
+    def silu_and_mul(self, x, out=None):
+        _req(x, BF16, "x")
+        N, I2 = x.shape
+        out = torch.empty((N, I2 // 2), dtype=BF16, device=x.device) if out is None else out
+        self._ck(self.l.nvc_silu_and_mul(self.h, _ptr(x), _ptr(out), N, I2 // 2, _stream()), "nvc_silu_and_mul")
+        return out
+
+    def gather_rows(self, x, residual, rows):
+        _req(x, BF16, "x"); _req(rows, torch.int32, "rows")
+        B, H = rows.numel(), x.shape[1]
+        xo = torch.empty((B, H), dtype=BF16, device=x.device)
+        ro = None if residual is None else torch.empty((B, H), dtype=torch.float32, device=x.device)
+        self._ck(self.l.nvc_gather_rows(self.h, _ptr(x), _ptr(residual), _ptr(rows), _ptr(xo), _ptr(ro), B, H, _stream()),
+                 "nvc_gather_rows")
+        return xo, ro
+
+    def argmax_last(self, logits, index_offset=0):
+        _req(logits, torch.float32, "logits")
+        B, V = logits.shape
+        idx = torch.empty((B,), dtype=torch.int32, device=logits.device)
+        val = torch.empty((B,), dtype=torch.float32, device=logits.device)
+        self._ck(self.l.nvc_argmax_last(self.h, _ptr(logits), logits.stride(0), _ptr(idx), _ptr(val), B, V,
+                                        index_offset, _stream()), "nvc_argmax_last")
+        return idx, val

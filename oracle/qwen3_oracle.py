@@ -130,14 +130,23 @@ def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float,
 
 def build_cos_sin(t: int, head_size: int, base: float) -> Tuple[torch.Tensor, torch.Tensor]:
     """src/layers/rotary_embedding.rs:56-80.  All arithmetic in f32:
-    inv_freq_j = 1 / base.powf(2j/dim); ang = (pos as f32) * inv_freq_j."""
+    inv_freq_j = 1 / base.powf(2j/dim); ang = (pos as f32) * inv_freq_j; cos/sin in f32.
+
+    Rust's f32::powf / cos / sin lower to the platform libm (glibc powf/cosf/sinf), which are
+    correctly rounded (computed in double, rounded once).  numpy's float32 ufuncs use SIMD
+    approximations that can be 1 ulp off, and a 1-ulp inv_freq error grows to ~2e-4 rad at
+    position 4096; so each libm call is restated as "evaluate in float64 on the f32 inputs,
+    round once to f32"."""
     half = head_size // 2
     j = np.arange(half, dtype=np.float32)
-    exponent = (np.float32(2.0) * j) / np.float32(head_size)
-    inv_freq = (np.float32(1.0) / np.power(np.float32(base), exponent, dtype=np.float32)).astype(np.float32)
+    exponent = ((np.float32(2.0) * j) / np.float32(head_size)).astype(np.float32)
+    powed = np.power(np.float64(np.float32(base)), exponent.astype(np.float64)).astype(np.float32)
+    inv_freq = (np.float32(1.0) / powed).astype(np.float32)
     pos = np.arange(t, dtype=np.float32)
     ang = (pos[:, None] * inv_freq[None, :]).astype(np.float32)
-    return torch.from_numpy(np.cos(ang).astype(np.float32)), torch.from_numpy(np.sin(ang).astype(np.float32))
+    cos = np.cos(ang.astype(np.float64)).astype(np.float32)
+    sin = np.sin(ang.astype(np.float64)).astype(np.float32)
+    return torch.from_numpy(cos), torch.from_numpy(sin)
 
 
 def apply_rotary(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:

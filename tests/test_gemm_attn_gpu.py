@@ -1,0 +1,175 @@
+"""GPU parity tests for the tensor-core kernels (tcgen05 GEMM, tcgen05 prefill attention) and
+the paged decode attention, against the fp32 oracle."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import qwen3_oracle as O
+from conftest import diag
+from test_kernels_gpu import _close
+
+pytestmark = pytest.mark.gpu
+BF16 = torch.bfloat16
+
+
+# ----------------------------------------------------------------------------- K3 GEMM
+GEMM_SHAPES = [
+    # (M, N, K, force_bn, force_splits)
+    (128, 128, 64, 128, 1),        # one tile, one k-block
+    (128, 128, 512, 128, 1),       # pipeline wraps (8 k-blocks > 6 stages)
+    (128, 256, 256, 256, 1),
+    (128, 64, 256, 64, 1),
+    (128, 32, 256, 32, 1),
+    (256, 512, 1024, 128, 1),      # several tiles
+    (64, 1024, 2048, 0, 0),        # decode shapes, auto config (0.6B o_proj)
+    (64, 4096, 1024, 0, 0),        # 0.6B qkv
+    (64, 6144, 1024, 0, 0),        # 0.6B gate_up
+    (64, 1024, 3072, 0, 0),        # 0.6B down
+    (1, 1024, 1024, 0, 0),         # M = 1
+    (200, 4096, 1024, 0, 0),       # ragged M
+    (333, 1040, 192, 128, 1),      # ragged M and N (N % 16 == 0 only)
+    (64, 1024, 2048, 64, 4),       # forced split-K
+    (130, 256, 1024, 128, 8),      # split-K with 2 m-tiles
+    (64, 2000, 512, 32, 2),        # split-K, ragged N, BN=32
+    (256, 6144, 4096, 0, 0),       # 8B qkv at batch 256
+    (2048, 1024, 1024, 0, 0),      # prefill-sized
+]
+
+
+@pytest.mark.parametrize("M,N,K,bn,splits", GEMM_SHAPES)
+@pytest.mark.parametrize("out_dtype", [BF16, torch.float32])
+def test_gemm_bf16(ctx, M, N, K, bn, splits, out_dtype):
+    g = torch.Generator().manual_seed(M * 31 + N * 7 + K)
+    a = torch.randn(M, K, generator=g).to(BF16)
+    w = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(BF16)
+    ref = O.linear(a.float(), w.float())
+    out = ctx.gemm(a.cuda(), w.cuda(), out_dtype=out_dtype, force_bn=bn, force_splits=splits)
+    torch.cuda.synchronize()
+    # fp32 accumulation of exact bf16 products: only summation order differs (1e-3 abs on O(1)
+    # values); bf16 output adds one rounding (2^-8 relative)
+    rtol = 2 ** -8 if out_dtype == BF16 else 1e-5
+    _close(out, ref, 2e-3, rtol, f"gemm M={M} N={N} K={K} bn={bn} s={splits} {out_dtype}")
+
+
+def test_gemm_reference_goldens(ctx):
+    """src/layers/linear.rs:231-267 (replicated, exact small integers; bias added on the host
+    here since the Qwen3 path has no biases) and :274-319 (two hand-sharded column ranks),
+    zero-padded to the kernel's K % 64 / N % 16 granularity."""
+    x = torch.tensor([[1., 2., 3., 4.], [-1., 0., 1., 2.]])
+    w = torch.tensor([[1., 0., -1., 2.], [0., 1., 2., -1.], [2., -1., 0., 1.],
+                      [-2., 1., 1., 0.], [1., 1., 1., 1.], [3., 0., -2., 1.]])
+    bias = torch.tensor([1., -2., 0., 3., -1., 2.])
+    want = torch.tensor([[7., 2., 4., 6., 9., 3.], [3., -2., 0., 6., 1., -1.]])
+    xp = torch.zeros(2, 64); xp[:, :4] = x
+    wp = torch.zeros(16, 64); wp[:6, :4] = w
+    out = ctx.gemm(xp.to(BF16).cuda(), wp.to(BF16).cuda(), out_dtype=torch.float32).cpu()
+    assert torch.equal(out[:, :6] + bias, want)
+    # column-parallel: rank r owns rows [3r, 3r+3) of W; concat of the shards == unsharded
+    for r in range(2):
+        ws = torch.zeros(16, 64); ws[:3, :4] = w[3 * r:3 * r + 3]
+        o = ctx.gemm(xp.to(BF16).cuda(), ws.to(BF16).cuda(), out_dtype=torch.float32).cpu()
+        assert torch.equal(o[:, :3] + bias[3 * r:3 * r + 3], want[:, 3 * r:3 * r + 3])
+
+
+def test_gemm_strided_input_and_determinism(ctx):
+    g = torch.Generator().manual_seed(5)
+    big = torch.randn(96, 3 * 512, generator=g).to(BF16).cuda()
+    a = big[:, 512:1024]                                    # row stride 1536
+    w = (torch.randn(1024, 512, generator=g) / 22).to(BF16).cuda()
+    ref = O.linear(a.float().cpu(), w.float().cpu())
+    o1 = ctx.gemm(a, w, force_bn=64, force_splits=4)
+    o2 = ctx.gemm(a, w, force_bn=64, force_splits=4)
+    _close(o1, ref, 2e-3, 2 ** -8, "gemm strided split-K")
+    assert torch.equal(o1, o2), "split-K must be deterministic (fixed reduction order)"
+
+
+# ----------------------------------------------------------------------------- K4 prefill
+def _dense_causal_ref(q, k, v, nh, kv, scale):
+    """oracle attention core, src/models/qwen3.rs:236-277, one sequence: q [T,nh,hd], k/v [T,kv,hd]."""
+    T = q.shape[0]
+    qh = q.permute(1, 0, 2)[None].float()
+    kh = O.gqa_expand(k.permute(1, 0, 2)[None].float(), nh // kv)
+    vh = O.gqa_expand(v.permute(1, 0, 2)[None].float(), nh // kv)
+    s = (qh @ kh.transpose(2, 3)) * scale
+    idx = torch.arange(T)
+    s = s + torch.where(idx[None, :] > idx[:, None], torch.tensor(-1e9), torch.tensor(0.0))
+    p = torch.softmax(s, dim=-1)
+    return (p @ vh)[0].permute(1, 0, 2).reshape(T, -1)
+
+
+@pytest.mark.parametrize("lens,nh,kv", [
+    ([128], 2, 1),
+    ([1], 2, 2),
+    ([17, 128, 129, 300, 1, 512], 4, 2),
+    ([640, 33], 16, 8),
+    ([1000], 8, 1),
+])
+def test_prefill_attn_varlen(ctx, nvc, lens, nh, kv):
+    hd = 128
+    N = sum(lens)
+    g = torch.Generator().manual_seed(N + nh)
+    qkv = torch.randn(N, (nh + 2 * kv) * hd, generator=g).to(BF16)
+    cu = torch.tensor([0] + list(np.cumsum(lens)), dtype=torch.int32)
+    scale = hd ** -0.5
+    ref = torch.cat([_dense_causal_ref(
+        qkv[s:e, :nh * hd].reshape(-1, nh, hd), qkv[s:e, nh * hd:(nh + kv) * hd].reshape(-1, kv, hd),
+        qkv[s:e, (nh + kv) * hd:].reshape(-1, kv, hd), nh, kv, scale) for s, e in zip(cu[:-1], cu[1:])])
+    d = qkv.cuda()
+    results = {}
+    for variant in (0, 1):
+        nvc.lib().nvc_debug_set(0, variant)
+        out = ctx.prefill_attn(d[:, :nh * hd], d[:, nh * hd:(nh + kv) * hd], d[:, (nh + kv) * hd:],
+                               cu.cuda(), max(lens), nh, kv, hd, scale)
+        torch.cuda.synchronize()
+        results[variant] = (out.float().cpu() - ref).abs().max().item()
+    nvc.lib().nvc_debug_set(0, 0)
+    diag(f"[prefill lens={lens} nh={nh} kv={kv}] max_err variant0={results[0]:.4e} variant1={results[1]:.4e}")
+    out = ctx.prefill_attn(d[:, :nh * hd], d[:, nh * hd:(nh + kv) * hd], d[:, (nh + kv) * hd:],
+                           cu.cuda(), max(lens), nh, kv, hd, scale)
+    # P is rounded to bf16 before P*V and the output is bf16: 2e-2 abs on O(1) values
+    _close(out, ref, 2e-2, 2 ** -6, f"prefill lens={lens} nh={nh} kv={kv}")
+
+
+# ----------------------------------------------------------------------------- K5 decode
+@pytest.mark.parametrize("nh,kv,block_size,ctx_lens", [
+    (16, 8, 256, [1, 16, 17, 255, 256, 257, 1000, 64]),
+    (32, 8, 256, [700, 3, 1025]),
+    (4, 4, 16, [5, 40]),
+    (40, 8, 256, [300, 1]),          # group 5 (Qwen3-14B)
+    (64, 8, 256, [513]),             # group 8 (Qwen3-32B): two chunks of 4
+    (16, 8, 256, [2048]),            # single sequence -> split-KV + combine
+])
+def test_paged_decode_attn(ctx, nh, kv, block_size, ctx_lens):
+    hd = 128
+    B = len(ctx_lens)
+    g = torch.Generator().manual_seed(nh * 100 + B)
+    nblk_per = [(c + block_size - 1) // block_size for c in ctx_lens]
+    total_blk = sum(nblk_per) + 3
+    perm = torch.randperm(total_blk, generator=g).tolist()
+    bt = torch.full((B, max(nblk_per)), -1, dtype=torch.int32)
+    kc = torch.full((total_blk * block_size, kv, hd), float("nan")).to(BF16)    # unwritten slots are poison
+    vc = torch.full((total_blk * block_size, kv, hd), float("nan")).to(BF16)
+    q = torch.randn(B, nh, hd, generator=g).to(BF16)
+    ref = torch.empty(B, nh * hd)
+    scale = hd ** -0.5
+    p = 0
+    for b, c in enumerate(ctx_lens):
+        blocks = perm[p:p + nblk_per[b]]; p += nblk_per[b]
+        bt[b, :len(blocks)] = torch.tensor(blocks, dtype=torch.int32)
+        k = torch.randn(c, kv, hd, generator=g).to(BF16)
+        v = torch.randn(c, kv, hd, generator=g).to(BF16)
+        for t in range(c):
+            slot = blocks[t // block_size] * block_size + t % block_size
+            kc[slot], vc[slot] = k[t], v[t]
+        # oracle: last row of dense causal attention == attention of q over all c cached tokens
+        kh = O.gqa_expand(k.permute(1, 0, 2)[None].float(), nh // kv)[0]
+        vh = O.gqa_expand(v.permute(1, 0, 2)[None].float(), nh // kv)[0]
+        s = torch.einsum("hd,htd->ht", q[b].float(), kh) * scale
+        ref[b] = torch.einsum("ht,htd->hd", torch.softmax(s, dim=-1), vh).reshape(-1)
+    out = ctx.paged_decode_attn(q.reshape(B, nh * hd).cuda(), kc.cuda(), vc.cuda(), bt.cuda(),
+                                torch.tensor(ctx_lens, dtype=torch.int32).cuda(), nh, kv, hd, block_size, scale)
+    torch.cuda.synchronize()
+    assert not torch.isnan(out.float()).any(), "poisoned (unwritten) cache slots leaked into the output"
+    _close(out, ref, 1e-2, 2 ** -7, f"paged decode nh={nh} kv={kv} bs={block_size} ctx={ctx_lens}")

@@ -121,6 +121,22 @@ class Qwen3Config:
                             self.bos_token_id, self.eos_token_id)
 
 
+def _cfg(H, L, nh, kv, I, V=151936, maxpos=40960, bos=151643, eos=151645) -> Qwen3Config:
+    return Qwen3Config(vocab_size=V, hidden_size=H, head_dim=128, num_hidden_layers=L, num_attention_heads=nh,
+                       num_key_value_heads=kv, intermediate_size=I, max_position_embeddings=maxpos,
+                       bos_token_id=bos, eos_token_id=eos)
+
+
+# Published Qwen3 dense shapes + a toy shape for fast tests.
+MODEL_CONFIGS: Dict[str, Qwen3Config] = {
+    "qwen3-0.6b": _cfg(1024, 28, 16, 8, 3072),
+    "qwen3-8b": _cfg(4096, 36, 32, 8, 12288),
+    "qwen3-14b": _cfg(5120, 40, 40, 8, 17408),
+    "qwen3-32b": _cfg(5120, 64, 64, 8, 25600),
+    "qwen3-tiny": _cfg(256, 3, 4, 2, 512, V=2048, maxpos=4096, bos=1, eos=2),
+}
+
+
 # ----------------------------------------------------------------------------- runners
 class DummyModelRunner:
     """next token = last_token + 1 (implemented inside the C++ engine when no runner is given)."""

@@ -40,6 +40,7 @@ struct nvc_ctx {
   int num_sms = 148;
   std::string last_error;
   uint64_t launches = 0;   // kernels launched through this context (bench.py gpu_launches)
+  int use_pdl = 1;         // programmatic dependent launch between the kernels of a step (NVC_PDL=0 disables)
   nvc_encode_tiled_fn encode_tiled = nullptr;
   // split-K scratch for the tcgen05 GEMM (fp32 partial tiles + per-tile arrival counters)
   float* gemm_ws = nullptr;
@@ -55,10 +56,36 @@ void nvc_set_error(nvc_ctx* ctx, const std::string& msg);
 
 static inline cudaStream_t nvc_stream(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
+#ifdef __CUDACC__
+// Launch with programmatic stream serialization: the kernel may start (run its prologue up to
+// pdl_wait()) while its predecessor in the stream is still draining.  Every kernel of this
+// library calls pdl_wait() before it touches global memory and pdl_trigger() at its top.
+template <typename... KArgs, typename... Args>
+static inline cudaError_t nvc_launch(const nvc_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                     cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = (ctx && ctx->use_pdl) ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
+
 // ---------------------------------------------------------------------------------------
 // device helpers
 // ---------------------------------------------------------------------------------------
 #ifdef __CUDACC__
+
+// Programmatic dependent launch (griddepcontrol): wait = all prerequisite grids have completed
+// and their memory is visible; trigger = the next grid in the stream may be scheduled.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 __device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }

@@ -2,6 +2,7 @@
 #include "common.cuh"
 #include "internal.h"
 
+#include <cstdlib>
 #include <cstring>
 
 void nvc_collectives_destroy(nvc_ctx* ctx);   // collectives.cu
@@ -65,6 +66,7 @@ extern "C" int nvc_ctx_create(int device, int tp_rank, int tp_size, nvc_ctx** ou
   ctx->tp_rank = tp_rank;
   ctx->tp_size = tp_size;
   ctx->num_sms = prop.multiProcessorCount;
+  if (const char* e = getenv("NVC_PDL")) ctx->use_pdl = atoi(e) != 0;
 
   void* fn = nullptr;
   cudaDriverEntryPointQueryResult qres;

@@ -15,6 +15,8 @@
 // ------------------------------------------------------------------------------------
 __global__ void embed_gather_kernel(const int32_t* __restrict__ ids, const uint4* __restrict__ table,
                                     uint4* __restrict__ out, int N, int vec_per_row) {
+  pdl_trigger();
+  pdl_wait();
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int64_t total = (int64_t)N * vec_per_row;
   if (i >= total) return;
@@ -34,8 +36,8 @@ extern "C" int nvc_embed_gather(nvc_ctx* ctx, const int32_t* ids, const nvc_bf16
   int64_t total = (int64_t)N * vpr;
   int threads = 256;
   int64_t blocks = (total + threads - 1) / threads;
-  embed_gather_kernel<<<(unsigned)blocks, threads, 0, nvc_stream(stream)>>>(
-      ids, reinterpret_cast<const uint4*>(table), reinterpret_cast<uint4*>(out), N, vpr);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, embed_gather_kernel, dim3((unsigned)blocks), dim3(threads), 0, nvc_stream(stream),
+                                 ids, reinterpret_cast<const uint4*>(table), reinterpret_cast<uint4*>(out), N, vpr));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -53,6 +55,8 @@ fused_add_rmsnorm_kernel(const uint4* __restrict__ x, const float4* __restrict__
                          float4* __restrict__ res_out, const uint4* __restrict__ w, float eps,
                          uint4* __restrict__ out, int H) {
   __shared__ float red[32];
+  pdl_trigger();
+  pdl_wait();
   const int row = blockIdx.x;
   const int nvec = H >> 3;
   const int64_t vbase = (int64_t)row * nvec;
@@ -145,9 +149,11 @@ extern "C" int nvc_fused_add_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x, const floa
   auto os = reinterpret_cast<uint4*>(out);
   if (nvec <= 1024) {
     int threads = ((nvec + 31) / 32) * 32;
-    fused_add_rmsnorm_kernel<false><<<N, threads, 0, nvc_stream(stream)>>>(xs, ri, ro, ws, eps, os, H);
+    NVC_CUDA_CHECK(ctx, nvc_launch(ctx, fused_add_rmsnorm_kernel<false>, dim3(N), dim3(threads), 0, nvc_stream(stream),
+                                   xs, ri, ro, ws, eps, os, H));
   } else {
-    fused_add_rmsnorm_kernel<true><<<N, 1024, 0, nvc_stream(stream)>>>(xs, ri, ro, ws, eps, os, H);
+    NVC_CUDA_CHECK(ctx, nvc_launch(ctx, fused_add_rmsnorm_kernel<true>, dim3(N), dim3(1024), 0, nvc_stream(stream),
+                                   xs, ri, ro, ws, eps, os, H));
   }
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
@@ -191,6 +197,8 @@ qk_norm_rope_store_kernel(uint4* __restrict__ qkv, const uint4* __restrict__ qw,
                           float eps, const float4* __restrict__ cos_sin, const int32_t* __restrict__ positions,
                           const int32_t* __restrict__ slot_mapping, uint4* __restrict__ k_cache,
                           uint4* __restrict__ v_cache, int N, int nh, int kv) {
+  pdl_trigger();
+  pdl_wait();
   const int units_per_tok = nh + 2 * kv;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
   const int l = threadIdx.x & 7;
@@ -279,10 +287,11 @@ extern "C" int nvc_qk_norm_rope_store(nvc_ctx* ctx, nvc_bf16* qkv, const nvc_bf1
   const int64_t units = (int64_t)N * (nh + 2 * kv);
   const int threads = 256;
   const int64_t blocks = (units * 8 + threads - 1) / threads;
-  qk_norm_rope_store_kernel<<<(unsigned)blocks, threads, 0, nvc_stream(stream)>>>(
-      reinterpret_cast<uint4*>(qkv), reinterpret_cast<const uint4*>(qw), reinterpret_cast<const uint4*>(kw),
-      eps, reinterpret_cast<const float4*>(cos_sin), positions, slot_mapping,
-      reinterpret_cast<uint4*>(k_cache), reinterpret_cast<uint4*>(v_cache), N, nh, kv);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, qk_norm_rope_store_kernel, dim3((unsigned)blocks), dim3(threads), 0,
+                                 nvc_stream(stream), reinterpret_cast<uint4*>(qkv), reinterpret_cast<const uint4*>(qw),
+                                 reinterpret_cast<const uint4*>(kw), eps, reinterpret_cast<const float4*>(cos_sin),
+                                 positions, slot_mapping, reinterpret_cast<uint4*>(k_cache),
+                                 reinterpret_cast<uint4*>(v_cache), N, nh, kv));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -296,6 +305,8 @@ __global__ void __launch_bounds__(256)
 store_kvcache_kernel(const uint4* __restrict__ k, const uint4* __restrict__ v, int ld_vec,
                      uint4* __restrict__ k_cache, uint4* __restrict__ v_cache,
                      const int32_t* __restrict__ slot_mapping, int N, int row_vec) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (int64_t)N * row_vec) return;
   const int n = (int)(i / row_vec);
@@ -316,9 +327,10 @@ extern "C" int nvc_store_kvcache(nvc_ctx* ctx, const nvc_bf16* k, const nvc_bf16
   const int row_vec = kv * hd / 8;
   const int64_t total = (int64_t)N * row_vec;
   const int threads = 256;
-  store_kvcache_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, nvc_stream(stream)>>>(
-      reinterpret_cast<const uint4*>(k), reinterpret_cast<const uint4*>(v), ld / 8,
-      reinterpret_cast<uint4*>(k_cache), reinterpret_cast<uint4*>(v_cache), slot_mapping, N, row_vec);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, store_kvcache_kernel, dim3((unsigned)((total + threads - 1) / threads)),
+                                 dim3(threads), 0, nvc_stream(stream), reinterpret_cast<const uint4*>(k),
+                                 reinterpret_cast<const uint4*>(v), ld / 8, reinterpret_cast<uint4*>(k_cache),
+                                 reinterpret_cast<uint4*>(v_cache), slot_mapping, N, row_vec));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -330,6 +342,8 @@ extern "C" int nvc_store_kvcache(nvc_ctx* ctx, const nvc_bf16* k, const nvc_bf16
 // ------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 silu_and_mul_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int N, int ivec) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (int64_t)N * ivec) return;
   const int n = (int)(i / ivec);
@@ -350,8 +364,9 @@ extern "C" int nvc_silu_and_mul(nvc_ctx* ctx, const nvc_bf16* x, nvc_bf16* out, 
   const int ivec = I / 8;
   const int64_t total = (int64_t)N * ivec;
   const int threads = 256;
-  silu_and_mul_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, nvc_stream(stream)>>>(
-      reinterpret_cast<const uint4*>(x), reinterpret_cast<uint4*>(out), N, ivec);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, silu_and_mul_kernel, dim3((unsigned)((total + threads - 1) / threads)),
+                                 dim3(threads), 0, nvc_stream(stream), reinterpret_cast<const uint4*>(x),
+                                 reinterpret_cast<uint4*>(out), N, ivec));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -363,6 +378,8 @@ extern "C" int nvc_silu_and_mul(nvc_ctx* ctx, const nvc_bf16* x, nvc_bf16* out, 
 __global__ void __launch_bounds__(256)
 gather_rows_kernel(const uint4* __restrict__ x, const float4* __restrict__ res, const int32_t* __restrict__ rows,
                    uint4* __restrict__ x_out, float4* __restrict__ res_out, int B, int hvec) {
+  pdl_trigger();
+  pdl_wait();
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (int64_t)B * hvec) return;
   const int b = (int)(i / hvec);
@@ -384,9 +401,10 @@ extern "C" int nvc_gather_rows(nvc_ctx* ctx, const nvc_bf16* x, const float* res
   const int hvec = H / 8;
   const int64_t total = (int64_t)B * hvec;
   const int threads = 256;
-  gather_rows_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, nvc_stream(stream)>>>(
-      reinterpret_cast<const uint4*>(x), reinterpret_cast<const float4*>(residual), rows,
-      reinterpret_cast<uint4*>(x_out), reinterpret_cast<float4*>(residual_out), B, hvec);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, gather_rows_kernel, dim3((unsigned)((total + threads - 1) / threads)),
+                                 dim3(threads), 0, nvc_stream(stream), reinterpret_cast<const uint4*>(x),
+                                 reinterpret_cast<const float4*>(residual), rows, reinterpret_cast<uint4*>(x_out),
+                                 reinterpret_cast<float4*>(residual_out), B, hvec));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -403,6 +421,8 @@ __device__ __forceinline__ void argmax_combine(float& v, int& i, float ov, int o
 __global__ void __launch_bounds__(1024)
 argmax_last_kernel(const float* __restrict__ logits, int ld, int32_t* __restrict__ idx, float* __restrict__ val,
                    int V, int index_offset) {
+  pdl_trigger();
+  pdl_wait();
   __shared__ float sv[32];
   __shared__ int si[32];
   const float* row = logits + (int64_t)blockIdx.x * ld;
@@ -451,7 +471,8 @@ extern "C" int nvc_argmax_last(nvc_ctx* ctx, const float* logits, int ld, int32_
   NVC_REQUIRE(ctx, B >= 0 && V > 0 && ld >= V, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, ld % 4 == 0, NVC_ESHAPE, "ld must be a multiple of 4");
   if (B == 0) return NVC_OK;
-  argmax_last_kernel<<<B, 1024, 0, nvc_stream(stream)>>>(logits, ld, idx, val, V, index_offset);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, argmax_last_kernel, dim3(B), dim3(1024), 0, nvc_stream(stream), logits, ld, idx,
+                                 val, V, index_offset));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -460,6 +481,8 @@ extern "C" int nvc_argmax_last(nvc_ctx* ctx, const float* logits, int ld, int32_
 // (max, idx) of a vocab shard as one 8-byte record per sequence (TP argmax exchange)
 __global__ void pack_argmax_pairs_kernel(const float* __restrict__ val, const int32_t* __restrict__ idx,
                                          float2* __restrict__ pairs, int B) {
+  pdl_trigger();
+  pdl_wait();
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b < B) pairs[b] = make_float2(val[b], __int_as_float(idx[b]));
 }
@@ -468,7 +491,8 @@ extern "C" int nvc_pack_argmax_pairs(nvc_ctx* ctx, const float* val, const int32
                                      void* stream) {
   NVC_REQUIRE(ctx, ctx && val && idx && pairs && B >= 0, NVC_EINVAL, "bad arguments");
   if (B == 0) return NVC_OK;
-  pack_argmax_pairs_kernel<<<(B + 127) / 128, 128, 0, nvc_stream(stream)>>>(val, idx, reinterpret_cast<float2*>(pairs), B);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, pack_argmax_pairs_kernel, dim3((B + 127) / 128), dim3(128), 0, nvc_stream(stream),
+                                 val, idx, reinterpret_cast<float2*>(pairs), B));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;

@@ -3,14 +3,18 @@
 // (src/layers/linear.rs:33-38,72-77,99-104,171-175,184-198) and compute_logits
 // (src/models/qwen3.rs:542-550).
 //
-// Structure (one 128 x BN output tile per CTA, optional split-K over gridDim.z):
-//   warp 0   : TMA producer  - cp.async.bulk.tensor 2D, 128B-swizzled [128 x 64] A tile and
-//              [BN x 64] W tile per stage, mbarrier expect_tx ring of kStages stages
-//   warp 1   : allocates TMEM, one elected lane issues tcgen05.mma (M=128, N=BN, K=16) x4 per
-//              stage, tcgen05.commit frees the stage / publishes the accumulator
+// One 128 x BN output tile per CTA, optional split-K over gridDim.z.  A pipeline stage holds
+// KPS k-blocks of 64 (KPS x [128 x 64] A sub-tiles + KPS x [BN x 64] W sub-tiles, each a
+// 128B-swizzled TMA box), so one mbarrier round trip (~130 cycles) is amortised over 4*KPS MMAs.
+//   warp 0   : TMA producer for the activation sub-tiles (only the rows that exist when M < 128)
+//   warp 2   : TMA producer for the weight sub-tiles, then joins the epilogue
+//   warp 1   : allocates TMEM; one elected lane issues tcgen05.mma (M=128, N=BN, K=16);
+//              tcgen05.commit frees the stage / publishes the accumulator
 //   warps 2-5: epilogue - tcgen05.ld 32 lanes x 16 columns, convert, 16-byte stores
+// All role loops are executed by the whole warp with one elected lane issuing, which keeps the
+// TMA / UMMA operands in uniform registers (back-to-back UTMALDG / UTCHMMA in SASS).
 // Split-K: each split writes its fp32 partial tile to a workspace; the CTA that takes the last
-// ticket of a tile sums the partials in split order (deterministic) and writes the output.
+// ticket (acq_rel atomic) sums the partials in split order (deterministic, coalesced).
 // Rows >= M and columns >= N of edge tiles are zero-filled by TMA and masked at the store.
 #include "common.cuh"
 #include "ptx.cuh"
@@ -22,24 +26,37 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kThreads = 192;
 constexpr int kEpilogueThreads = 128;
+constexpr int kSmemBudget = 200 * 1024;
 
-template <int BN>
+template <int BN, int KPS>
 struct Cfg {
-  static constexpr int kBytesA = BM * BK * 2;
-  static constexpr int kBytesB = BN * BK * 2;
-  static constexpr int kStageBytes = kBytesA + kBytesB;
-  static constexpr int kStages = (BN >= 256) ? 4 : (BN >= 128) ? 6 : 8;
-  static constexpr int kTmemCols = BN < 32 ? 32 : BN;   // BN in {32,64,128,256}: already a power of two
+  static constexpr int kBytesA = BM * BK * 2;                 // one A sub-tile
+  static constexpr int kBytesB = BN * BK * 2;                 // one W sub-tile
+  static constexpr int kStageBytes = KPS * (kBytesA + kBytesB);
+  static constexpr int kStages = kSmemBudget / kStageBytes < 8 ? kSmemBudget / kStageBytes : 8;
+  static constexpr int kTmemCols = BN < 32 ? 32 : BN;         // BN in {32,64,128,256}: a power of two
   // tiles + (2*stages + 1) mbarriers + tmem slot + ticket, plus 1024 for manual alignment
   static constexpr int kSmemBytes = kStages * kStageBytes + (2 * kStages + 1) * 8 + 16 + 1024;
+  static_assert(kStages >= 2, "need at least a double buffer");
 };
 
-template <int BN>
+__device__ __forceinline__ int atomic_add_acq_rel_gpu(int* p, int v) {
+  int old;
+  asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+
+template <int BN, int KPS>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total,
-                         int k_blocks_per_split, float* __restrict__ ws, int* __restrict__ counters) {
-  using cfg = Cfg<BN>;
+                         int k_blocks_per_split, int a_box_rows, float* __restrict__ ws,
+                         int* __restrict__ counters, long long* __restrict__ trace) {
+  using cfg = Cfg<BN, KPS>;
+  // optional phase timestamps of CTA (0,0,0) (tools/gemm_microbench.py); NULL in production
+  const bool tr = trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
+  pdl_trigger();   // the next kernel may start its own prologue
+  if (tr && threadIdx.x == 0) trace[0] = clock64();
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -59,6 +76,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   const int kb_begin = split * k_blocks_per_split;
   const int kb_end = min(k_blocks_total, kb_begin + k_blocks_per_split);
   const int num_kb = kb_end - kb_begin;
+  const int num_it = (num_kb + KPS - 1) / KPS;       // pipeline iterations (stages consumed)
 
   if (warp == 0 && lane == 0) {
     ptx::tma_prefetch_desc(&tma_a);
@@ -67,7 +85,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   if (warp == 1) {
     if (lane == 0) {
       for (int s = 0; s < cfg::kStages; ++s) {
-        ptx::mbar_init(full_bar(s), 1);
+        ptx::mbar_init(full_bar(s), 2);   // two producers: warp 0 (A sub-tiles) and warp 2 (W sub-tiles)
         ptx::mbar_init(empty_bar(s), 1);
       }
       ptx::mbar_init(tmem_full_bar, 1);
@@ -81,45 +99,69 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   __syncthreads();
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot_gen;
+  pdl_wait();      // everything above (barrier init, TMEM alloc, descriptor prefetch) overlapped the predecessor
+  if (tr && threadIdx.x == 0) trace[1] = clock64();
 
-  if (warp == 0) {
-    // ------------------------------------------------------------ TMA producer
-    if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % cfg::kStages;
-        const uint32_t ph = (kb / cfg::kStages) & 1;
-        ptx::mbar_wait(empty_bar(s), ph ^ 1u);
-        ptx::mbar_arrive_expect_tx(full_bar(s), cfg::kStageBytes);
-        const uint32_t sa = smem_base + s * cfg::kStageBytes;
-        const uint32_t sb = sa + cfg::kBytesA;
-        const int kcoord = (kb_begin + kb) * BK;
-        ptx::tma_load_2d(sa, &tma_a, full_bar(s), kcoord, m_tile * BM);
-        ptx::tma_load_2d(sb, &tma_b, full_bar(s), kcoord, n_tile * BN);
+  if (warp == 0 || warp == 2) {
+    // ------------------------------------------------------------ TMA producers
+    const bool is_a = warp == 0;
+    const uint32_t sub_bytes = is_a ? (uint32_t)a_box_rows * (BK * 2) : (uint32_t)cfg::kBytesB;   // bytes one box delivers
+    const uint32_t sub_stride = is_a ? (uint32_t)cfg::kBytesA : (uint32_t)cfg::kBytesB;
+    const CUtensorMap* map = is_a ? &tma_a : &tma_b;
+    const int row0 = is_a ? m_tile * BM : n_tile * BN;
+    const uint32_t off = is_a ? 0u : (uint32_t)(KPS * cfg::kBytesA);
+    for (int it = 0; it < num_it; ++it) {
+      const int s = it % cfg::kStages;
+      if (it >= cfg::kStages) ptx::mbar_wait(empty_bar(s), ((it / cfg::kStages) & 1) ^ 1u);   // first lap: slots are free
+      if (ptx::elect_one()) {
+        const int nsub = min(KPS, num_kb - it * KPS);
+        ptx::mbar_arrive_expect_tx(full_bar(s), sub_bytes * nsub);
+        const uint32_t dst = smem_base + s * cfg::kStageBytes + off;
+        const int k0 = (kb_begin + it * KPS) * BK;
+#pragma unroll
+        for (int j = 0; j < KPS; ++j)
+          if (j < nsub) ptx::tma_load_2d(dst + j * sub_stride, map, full_bar(s), k0 + j * BK, row0);
+        if (tr && is_a && it < 32) trace[2 + it] = clock64();
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, 0, 0);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % cfg::kStages;
-        const uint32_t ph = (kb / cfg::kStages) & 1;
-        ptx::mbar_wait(full_bar(s), ph);
-        ptx::tcgen05_fence_after();
-        const uint32_t sa = smem_base + s * cfg::kStageBytes;
-        const uint32_t sb = sa + cfg::kBytesA;
+    constexpr uint32_t idesc = ptx::umma_idesc_bf16(BM, BN, 0, 0);
+    constexpr uint32_t desc_hi = ptx::umma_desc_hi_sw128(1024);
+    const uint32_t a_lo0 = ptx::umma_desc_lo(smem_base, 16);
+    const uint32_t b_lo0 = ptx::umma_desc_lo(smem_base + KPS * cfg::kBytesA, 16);
+    for (int it = 0; it < num_it; ++it) {
+      const int s = it % cfg::kStages;
+      ptx::mbar_wait(full_bar(s), (it / cfg::kStages) & 1);
+      ptx::tcgen05_fence_after();
+      if (ptx::elect_one()) {
+        if (tr && it < 32) trace[40 + it] = clock64();
+        const int nsub = min(KPS, num_kb - it * KPS);
+        const uint32_t a_lo = a_lo0 + s * (cfg::kStageBytes >> 4);
+        const uint32_t b_lo = b_lo0 + s * (cfg::kStageBytes >> 4);
 #pragma unroll
-        for (int k = 0; k < BK / 16; ++k) {
-          // advance 16 bf16 = 32 bytes along K inside the 128-byte swizzle span
-          const uint64_t da = ptx::umma_desc_sw128(sa + k * 32, 16, 1024);
-          const uint64_t db = ptx::umma_desc_sw128(sb + k * 32, 16, 1024);
-          ptx::umma_bf16_ss(tmem_base, da, db, idesc, (kb | k) != 0 ? 1u : 0u);
+        for (int j = 0; j < KPS; ++j) {
+          if (j < nsub) {
+#pragma unroll
+            for (int k = 0; k < BK / 16; ++k) {
+              // 16 bf16 = 32 bytes along K inside the 128-byte swizzle span: +2 in the address field
+              ptx::umma_bf16_ss(tmem_base, ptx::umma_desc(a_lo + j * (cfg::kBytesA >> 4) + 2 * k, desc_hi),
+                                ptx::umma_desc(b_lo + j * (cfg::kBytesB >> 4) + 2 * k, desc_hi), idesc,
+                                (it | j | k) != 0 ? 1u : 0u);
+            }
+          }
         }
-        ptx::umma_commit(empty_bar(s));   // stage reusable once these MMAs have read it
+        ptx::umma_commit(empty_bar(s));       // stage reusable once these MMAs have read it
+        if (it == num_it - 1) {
+          ptx::umma_commit(tmem_full_bar);    // accumulator complete
+          if (tr) trace[80] = clock64();
+        }
       }
-      ptx::umma_commit(tmem_full_bar);    // accumulator complete
+      __syncwarp();
     }
-  } else {
+  }
+  if (warp >= 2) {
     // ------------------------------------------------------------ epilogue (warps 2..5)
     const int q = warp & 3;                 // TMEM lane quadrant this warp may access
     const int r = q * 32 + lane;            // row inside the tile
@@ -127,6 +169,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const bool row_ok = grow < M;
     ptx::mbar_wait(tmem_full_bar, 0);
     ptx::tcgen05_fence_after();
+    if (tr && threadIdx.x == 64) trace[81] = clock64();
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
     const int tile_id = m_tile * gridDim.x + n_tile;
 
@@ -176,43 +219,54 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
                                         __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3])));
         }
       }
-      __threadfence();
+      // CTA barrier orders every thread's stores before thread 64's release; the acquire half of the
+      // same atomic plus the second barrier orders the last CTA's loads after all other CTAs' stores.
       ptx::named_bar_sync(1, kEpilogueThreads);
-      if (threadIdx.x == 64) *ticket_gen = atomicAdd(counters + tile_id, 1);
+      if (threadIdx.x == 64) *ticket_gen = atomic_add_acq_rel_gpu(counters + tile_id, 1);
       ptx::named_bar_sync(1, kEpilogueThreads);
       if (*ticket_gen == num_splits - 1) {
-        __threadfence();
-        const float* base = ws + (int64_t)tile_id * num_splits * (BM * BN) + (int64_t)r * BN;
-        if (row_ok) {
-#pragma unroll 1
-          for (int c = 0; c < BN / 16; ++c) {
-            const int n0 = n_tile * BN + c * 16;
-            if (n0 >= N) break;
-            float acc[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) acc[j] = 0.f;
-            for (int z = 0; z < num_splits; ++z) {
-              const float4* src = reinterpret_cast<const float4*>(base + (int64_t)z * (BM * BN) + c * 16);
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                const float4 f = __ldcg(src + j);
-                acc[4 * j] += f.x; acc[4 * j + 1] += f.y; acc[4 * j + 2] += f.z; acc[4 * j + 3] += f.w;
-              }
-            }
-            if (out_f32) {
-              float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(C) + (int64_t)grow * ldc + n0);
-#pragma unroll
-              for (int j = 0; j < 4; ++j) dst[j] = make_float4(acc[4 * j], acc[4 * j + 1], acc[4 * j + 2], acc[4 * j + 3]);
-            } else {
-              uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<nvc_bf16*>(C) + (int64_t)grow * ldc + n0);
-              dst[0] = pack8(acc);
-              dst[1] = pack8(acc + 8);
-            }
+        // coalesced reduction over the valid rows of the tile: thread t takes float4 #(t + 128 i);
+        // the partials of all splits are summed in split order (deterministic)
+        const float* tile_ws = ws + (int64_t)tile_id * num_splits * (BM * BN);
+        const int rows_valid = min(BM, M - m_tile * BM);
+        const int cols_valid = min(BN, N - n_tile * BN);
+        constexpr int kVecPerRow = BN / 4;
+        const int et = threadIdx.x - 64;
+#pragma unroll 4
+        for (int v = et; v < rows_valid * kVecPerRow; v += kEpilogueThreads) {
+          const int rr = v / kVecPerRow, c4 = v - rr * kVecPerRow;
+          if (c4 * 4 >= cols_valid) continue;
+          const float4* src = reinterpret_cast<const float4*>(tile_ws + (int64_t)rr * BN) + c4;
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+          int z = 0;
+          for (; z + 4 <= num_splits; z += 4) {
+            const float4 f0 = __ldcg(src + (int64_t)(z + 0) * (BM * BN / 4));
+            const float4 f1 = __ldcg(src + (int64_t)(z + 1) * (BM * BN / 4));
+            const float4 f2 = __ldcg(src + (int64_t)(z + 2) * (BM * BN / 4));
+            const float4 f3 = __ldcg(src + (int64_t)(z + 3) * (BM * BN / 4));
+            acc.x = (((acc.x + f0.x) + f1.x) + f2.x) + f3.x;
+            acc.y = (((acc.y + f0.y) + f1.y) + f2.y) + f3.y;
+            acc.z = (((acc.z + f0.z) + f1.z) + f2.z) + f3.z;
+            acc.w = (((acc.w + f0.w) + f1.w) + f2.w) + f3.w;
+          }
+          for (; z < num_splits; ++z) {
+            const float4 f = __ldcg(src + (int64_t)z * (BM * BN / 4));
+            acc.x += f.x; acc.y += f.y; acc.z += f.z; acc.w += f.w;
+          }
+          const int64_t o = (int64_t)(m_tile * BM + rr) * ldc + n_tile * BN + c4 * 4;
+          if (out_f32) {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(C) + o) = acc;
+          } else {
+            uint2 pk;
+            pk.x = pack_bf16(acc.x, acc.y);
+            pk.y = pack_bf16(acc.z, acc.w);
+            *reinterpret_cast<uint2*>(reinterpret_cast<nvc_bf16*>(C) + o) = pk;
           }
         }
         if (threadIdx.x == 64) counters[tile_id] = 0;   // re-arm for the next launch
       }
     }
+    if (tr && threadIdx.x == 64) trace[82] = clock64();
     ptx::tcgen05_fence_before();
   }
   __syncthreads();
@@ -220,6 +274,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     ptx::tcgen05_fence_after();
     ptx::tmem_dealloc(tmem_base, cfg::kTmemCols);
   }
+  if (tr && threadIdx.x == 0) trace[83] = clock64();
 }
 
 int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner, uint64_t rows,
@@ -238,12 +293,14 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
   return NVC_OK;
 }
 
-template <int BN>
+template <int BN, int KPS>
 int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M,
-           int N, int K, int splits, cudaStream_t stream) {
-  using cfg = Cfg<BN>;
+           int N, int K, int splits, cudaStream_t stream, long long* trace) {
+  using cfg = Cfg<BN, KPS>;
   CUtensorMap ta, tb;
-  int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, BM);
+  // a single partial m-tile only needs the rows that exist (rounded to the 8-row swizzle atom)
+  const int a_rows = M >= BM ? BM : ((M + 7) / 8) * 8;
+  int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, a_rows);
   if (rc) return rc;
   rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, BN);
   if (rc) return rc;
@@ -251,61 +308,68 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
   const int kb_per = (kb_total + splits - 1) / splits;
   const int eff_splits = (kb_total + kb_per - 1) / kb_per;   // no empty splits
   dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, eff_splits);
-  gemm_bf16_tcgen05_kernel<BN><<<grid, kThreads, cfg::kSmemBytes, stream>>>(
-      ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, ctx->gemm_ws, ctx->gemm_counters);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, gemm_bf16_tcgen05_kernel<BN, KPS>, grid, dim3(kThreads), cfg::kSmemBytes, stream,
+                                 ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, a_rows, ctx->gemm_ws,
+                                 ctx->gemm_counters, trace));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
 }
 
-// Tile / split-K choice: minimise waves * per-CTA time under a crude cycle model
-// (MMA floor 2*BN cycles per 64-wide k-block, ~48 B/clk/SM of L2->SM bandwidth when the
-// chip is full, a fixed prologue/epilogue cost, and the split-K round trip through L2).
-void choose_config(const nvc_ctx* ctx, int M, int N, int K, int* bn_out, int* splits_out) {
+// (BN, KPS) instantiations.  KPS > 1 (several k-blocks per mbarrier round trip) is for short,
+// latency-bound CTAs (decode); KPS = 1 keeps the deepest ring for long compute-bound k-loops.
+#define NVC_GEMM_CONFIGS(X) X(256, 1) X(128, 1) X(128, 2) X(64, 2) X(64, 4) X(32, 4)
+
+// Tile choice, fitted to tools/gemm_microbench.py (CUDA-graph timing + CTA phase traces) on B200:
+//  * a CTA ingests ~60 B/clk through TMA when the operands stream from HBM, so a k-block costs
+//    max(2*BN [tcgen05 floor], (rows + BN) * 128 / 60 [TMA]) cycles, plus ~2500 cycles of
+//    prologue + first-load latency + epilogue per CTA;
+//  * decode (M <= 128): one wave, as many CTAs as the N dimension gives (up to ~all SMs), several
+//    k-blocks per pipeline stage; split-K through the L2 workspace costs >= 6 us (ticket atomic +
+//    reduction round trips) and never won in the sweep, so it is only used when forced.
+void choose_config(const nvc_ctx* ctx, int M, int N, int K, int* bn_out, int* kps_out, int* splits_out) {
+  *splits_out = 1;
+  if (M <= BM) {
+    int bn = 32;
+    const int cands[3] = {256, 128, 64};
+    for (int i = 0; i < 3; ++i)
+      if ((N + cands[i] - 1) / cands[i] >= 96) { bn = cands[i]; break; }
+    *bn_out = bn;
+    *kps_out = bn == 256 ? 1 : (bn == 128 ? 2 : 4);
+    return;
+  }
   const int kb = K / BK;
   const int m_tiles = (M + BM - 1) / BM;
-  const int rows_in_tile = M < BM ? M : BM;
-  const int bns[4] = {256, 128, 64, 32};
+  const int cands[3] = {256, 128, 64};
   double best = 1e30;
-  int best_bn = 128, best_s = 1;
-  for (int bi = 0; bi < 4; ++bi) {
-    const int bn = bns[bi];
-    if (bn > 32 && bn / 2 >= N) continue;            // tile mostly empty
-    const int tiles = m_tiles * ((N + bn - 1) / bn);
-    for (int s = 1; s <= 16 && s <= kb; ++s) {
-      const int kb_per = (kb + s - 1) / s;
-      const int eff_s = (kb + kb_per - 1) / kb_per;
-      if (eff_s != s) continue;
-      if (s > 1 && kb_per < 2) continue;
-      if (s > 1 && (size_t)tiles * s * BM * bn * 4 > ctx->gemm_ws_bytes) continue;
-      if (s > 1 && tiles > ctx->gemm_num_counters) continue;
-      const double ctas = (double)tiles * s;
-      const double waves = ceil(ctas / ctx->num_sms);
-      const double mma = 2.0 * bn;
-      const double load = (rows_in_tile * 128.0 + bn * 128.0) / 48.0;
-      double per = kb_per * (mma > load ? mma : load) + 2500.0 + bn * 6.0;
-      if (s > 1) per += 1500.0 + (double)rows_in_tile * bn * 4.0 * (1.0 + 1.0) / 48.0;
-      const double t = waves * per;
-      if (t < best) { best = t; best_bn = bn; best_s = s; }
-    }
+  int best_bn = 256;
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cands[i];
+    if (bn / 2 >= N) continue;                       // tile mostly empty
+    const double tiles = (double)m_tiles * ((N + bn - 1) / bn);
+    const double waves = ceil(tiles / ctx->num_sms);
+    const double per_kb = fmax(2.0 * bn, (BM + bn) * 128.0 / 60.0);
+    const double t = waves * (kb * per_kb + 2500.0 + bn * 18.0);
+    if (t < best * 0.999) { best = t; best_bn = bn; }
   }
   *bn_out = best_bn;
-  *splits_out = best_s;
+  *kps_out = best_bn == 64 ? 2 : 1;
 }
 
 }  // namespace
 
 extern "C" int nvc_gemm_init(nvc_ctx* ctx) {
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<256>::kSmemBytes));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<128>::kSmemBytes));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<64>::kSmemBytes));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<32>::kSmemBytes));
+#define X(BN, KPS)                                                                   \
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, KPS>,        \
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, KPS>::kSmemBytes));
+  NVC_GEMM_CONFIGS(X)
+#undef X
   return NVC_OK;
 }
 
-extern "C" int nvc_gemm_bf16_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
-                                int out_dtype, int M, int Nout, int K, int force_bn, int force_splits,
-                                void* stream) {
+static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
+                     int out_dtype, int M, int Nout, int K, int force_bn, int force_splits,
+                     void* stream, long long* trace) {
   NVC_REQUIRE(ctx, ctx && A && W && C, NVC_EINVAL, "null pointer");
   NVC_REQUIRE(ctx, M >= 0 && Nout > 0 && K > 0, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, K % 64 == 0, NVC_ESHAPE, "K must be a multiple of 64");
@@ -317,9 +381,13 @@ extern "C" int nvc_gemm_bf16_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const 
               "pointers must be 16-byte aligned");
   NVC_REQUIRE(ctx, ctx->encode_tiled != nullptr, NVC_EDEVICE, "cuTensorMapEncodeTiled unavailable");
   if (M == 0) return NVC_OK;
-  int bn, splits;
-  choose_config(ctx, M, Nout, K, &bn, &splits);
-  if (force_bn) bn = force_bn;
+  int bn, kps, splits;
+  choose_config(ctx, M, Nout, K, &bn, &kps, &splits);
+  if (force_bn) {          // force_bn = BN + 1000 * KPS (KPS 0: the first instantiation of that BN)
+    bn = force_bn % 1000;
+    kps = force_bn / 1000;
+    if (kps == 0) kps = bn >= 128 ? 1 : (bn == 64 ? 2 : 4);
+  }
   if (force_splits) splits = force_splits;
   if (splits > K / BK) splits = K / BK;
   const int tiles = ((M + BM - 1) / BM) * ((Nout + bn - 1) / bn);
@@ -329,14 +397,25 @@ extern "C" int nvc_gemm_bf16_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const 
   }
   cudaStream_t st = nvc_stream(stream);
   const int f32 = out_dtype == NVC_DT_F32;
-  switch (bn) {
-    case 256: return launch<256>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, st);
-    case 128: return launch<128>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, st);
-    case 64: return launch<64>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, st);
-    case 32: return launch<32>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, st);
-    default: NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported tile width");
-  }
+#define X(BN, KPS) \
+  if (bn == BN && kps == KPS) return launch<BN, KPS>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, st, trace);
+  NVC_GEMM_CONFIGS(X)
+#undef X
+  NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported tile configuration");
   return NVC_OK;
+}
+
+extern "C" int nvc_gemm_bf16_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
+                                int out_dtype, int M, int Nout, int K, int force_bn, int force_splits,
+                                void* stream) {
+  return gemm_impl(ctx, A, lda, W, C, ldc, out_dtype, M, Nout, K, force_bn, force_splits, stream, nullptr);
+}
+
+// Debug: same GEMM, CTA (0,0,0) writes clock64() phase stamps to trace_d[0..128) (device memory).
+extern "C" int nvc_gemm_bf16_trace(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
+                                   int out_dtype, int M, int Nout, int K, int force_bn, int force_splits,
+                                   void* stream, long long* trace_d) {
+  return gemm_impl(ctx, A, lda, W, C, ldc, out_dtype, M, Nout, K, force_bn, force_splits, stream, trace_d);
 }
 
 extern "C" int nvc_gemm_bf16(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,

@@ -38,6 +38,8 @@ paged_decode_kernel(const nvc_bf16* __restrict__ q, int ldq, const uint4* __rest
   __shared__ float sm_m[2 * kWarps][G];
   __shared__ float sm_l[2 * kWarps][G];
   __shared__ float sm_acc[2 * kWarps][G][128];
+  pdl_trigger();
+  pdl_wait();
 
   const int chunks = group / G;
   const int kvh = blockIdx.x / chunks;
@@ -184,6 +186,8 @@ paged_decode_kernel(const nvc_bf16* __restrict__ q, int ldq, const uint4* __rest
 __global__ void __launch_bounds__(128)
 paged_decode_combine_kernel(const float* __restrict__ part_o, const float* __restrict__ part_ml,
                             nvc_bf16* __restrict__ out, int nh, int num_splits) {
+  pdl_trigger();
+  pdl_wait();
   const int head = blockIdx.x, b = blockIdx.y, d = threadIdx.x;
   const int64_t p0 = ((int64_t)b * nh + head) * num_splits;
   float M = -INFINITY;
@@ -252,9 +256,9 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
   auto kc = reinterpret_cast<const uint4*>(k_cache);
   auto vc = reinterpret_cast<const uint4*>(v_cache);
 #define NVC_LAUNCH_PD(GV)                                                                                   \
-  paged_decode_kernel<GV><<<grid, kThreads, 0, st>>>(q, ldq, kc, vc, block_tables, max_blocks, context_lens, \
-                                                     nh, kv, group, block_size, scale_log2e, out, part_o,    \
-                                                     part_ml, splits)
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, paged_decode_kernel<GV>, grid, dim3(kThreads), 0, st, q, ldq, kc, vc,      \
+                                 block_tables, max_blocks, context_lens, nh, kv, group, block_size,            \
+                                 scale_log2e, out, part_o, part_ml, splits))
   switch (G) {
     case 4: NVC_LAUNCH_PD(4); break;
     case 5: NVC_LAUNCH_PD(5); break;
@@ -265,7 +269,8 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   if (splits > 1) {
-    paged_decode_combine_kernel<<<dim3(nh, B), 128, 0, st>>>(part_o, part_ml, out, nh, splits);
+    NVC_CUDA_CHECK(ctx, nvc_launch(ctx, paged_decode_combine_kernel, dim3(nh, B), dim3(128), 0, st, part_o, part_ml, out,
+                                   nh, splits));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   }

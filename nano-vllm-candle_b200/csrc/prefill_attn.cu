@@ -48,6 +48,8 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
                     const __grid_constant__ CUtensorMap tma_v, const int32_t* __restrict__ cu_seqlens,
                     int nh, int group, float scale_log2e, nvc_bf16* __restrict__ out, int v_lbo, int v_sbo) {
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+  pdl_trigger();
+  pdl_wait();      // cu_seqlens is read right away, so there is no prologue to overlap here
   const int seq_start = __ldg(cu_seqlens + b);
   const int seq_len = __ldg(cu_seqlens + b + 1) - seq_start;
   if (qt * 128 >= seq_len) return;            // whole CTA exits before any allocation
@@ -92,13 +94,17 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
   const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
 
   if (warp == 0) {
-    if (lane == 0) {
+    // ------------------------------------------------------------ TMA producer (whole warp loops, one lane issues)
+    if (ptx::elect_one()) {
       ptx::mbar_arrive_expect_tx(q_full, kQBytes);
       ptx::tma_load_3d(base + kOffQ, &tma_q, q_full, 0, h, seq_start + qt * 128);
       ptx::tma_load_3d(base + kOffQ + 16384, &tma_q, q_full, 64, h, seq_start + qt * 128);
-      for (int j = 0; j < n_tiles; ++j) {
-        const int s = j & 1;
-        ptx::mbar_wait(kv_empty(s), ((j >> 1) & 1) ^ 1u);
+    }
+    __syncwarp();
+    for (int j = 0; j < n_tiles; ++j) {
+      const int s = j & 1;
+      ptx::mbar_wait(kv_empty(s), ((j >> 1) & 1) ^ 1u);
+      if (ptx::elect_one()) {
         ptx::mbar_arrive_expect_tx(kv_full(s), kKVStageBytes);
         const uint32_t kdst = base + kOffKV + s * kKVStageBytes, vdst = kdst + kQBytes;
         const int row = seq_start + j * 128;
@@ -107,45 +113,54 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
         ptx::tma_load_3d(vdst, &tma_v, kv_full(s), 0, kvh, row);
         ptx::tma_load_3d(vdst + 16384, &tma_v, kv_full(s), 64, kvh, row);
       }
+      __syncwarp();
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      constexpr uint32_t idesc_qk = ptx::umma_idesc_bf16(128, 128, 0, 0);
-      constexpr uint32_t idesc_pv = ptx::umma_idesc_bf16(128, 128, 0, 1);   // B = V is MN-major
-      auto issue_s = [&](int j) {
-        const int s = j & 1;
-        ptx::mbar_wait(kv_full(s), (j >> 1) & 1);
-        ptx::tcgen05_fence_after();
-        const uint32_t qa = base + kOffQ, ka = base + kOffKV + s * kKVStageBytes;
+    // ------------------------------------------------------------ MMA issuer (whole warp loops, one lane issues)
+    constexpr uint32_t idesc_qk = ptx::umma_idesc_bf16(128, 128, 0, 0);
+    constexpr uint32_t idesc_pv = ptx::umma_idesc_bf16(128, 128, 0, 1);   // B = V is MN-major
+    constexpr uint32_t hi_k = ptx::umma_desc_hi_sw128(1024);
+    const uint32_t hi_v = ptx::umma_desc_hi_sw128((uint32_t)v_sbo);
+    const uint32_t q_lo = ptx::umma_desc_lo(base + kOffQ, 16);
+    const uint32_t p_lo = ptx::umma_desc_lo(base + kOffP, 16);
+    auto issue_s = [&](int j) {   // S = Q K_j^T : 8 k-steps of 16 over head_dim (two 64-wide swizzled halves)
+      const int s = j & 1;
+      ptx::mbar_wait(kv_full(s), (j >> 1) & 1);
+      ptx::tcgen05_fence_after();
+      if (ptx::elect_one()) {
+        const uint32_t k_lo = ptx::umma_desc_lo(base + kOffKV + s * kKVStageBytes, 16);
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
-          const uint32_t off = (ks >> 2) * 16384 + (ks & 3) * 32;
-          ptx::umma_bf16_ss(tmem_s, ptx::umma_desc_sw128(qa + off, 16, 1024),
-                            ptx::umma_desc_sw128(ka + off, 16, 1024), idesc_qk, ks != 0);
+          const uint32_t off = ((ks >> 2) * 16384 + (ks & 3) * 32) >> 4;
+          ptx::umma_bf16_ss(tmem_s, ptx::umma_desc(q_lo + off, hi_k), ptx::umma_desc(k_lo + off, hi_k), idesc_qk, ks != 0);
         }
         ptx::umma_commit(s_full);
-      };
-      ptx::mbar_wait(q_full, 0);
-      issue_s(0);
-      for (int j = 0; j < n_tiles; ++j) {
-        ptx::mbar_wait(p_full, j & 1);           // P(j) is in smem and S(j) has been consumed
+      }
+      __syncwarp();
+    };
+    ptx::mbar_wait(q_full, 0);
+    issue_s(0);
+    for (int j = 0; j < n_tiles; ++j) {
+      ptx::mbar_wait(p_full, j & 1);           // P(j) is in smem and S(j) has been consumed
+      ptx::tcgen05_fence_after();
+      if (j + 1 < n_tiles) issue_s(j + 1);
+      if (j > 0) {
+        ptx::mbar_wait(o_empty, (j - 1) & 1);  // softmax threads are done with O(j-1)
         ptx::tcgen05_fence_after();
-        if (j + 1 < n_tiles) issue_s(j + 1);
-        if (j > 0) {
-          ptx::mbar_wait(o_empty, (j - 1) & 1);  // softmax threads are done with O(j-1)
-          ptx::tcgen05_fence_after();
-        }
-        const uint32_t pa = base + kOffP, va = base + kOffKV + (j & 1) * kKVStageBytes + kQBytes;
+      }
+      if (ptx::elect_one()) {
+        // O_j = P V_j: A = P (K-major, 16 kv tokens per step); B = V (MN-major: 16 token rows = 2048 bytes per step)
+        const uint32_t v_lo = ptx::umma_desc_lo(base + kOffKV + (j & 1) * kKVStageBytes + kQBytes, (uint32_t)v_lbo);
 #pragma unroll
         for (int ks = 0; ks < 8; ++ks) {
-          // A = P: K-major, 16 kv tokens per step; B = V: MN-major, 16 token rows = 2048 bytes per step
-          const uint32_t poff = (ks >> 2) * 16384 + (ks & 3) * 32;
-          ptx::umma_bf16_ss(tmem_o, ptx::umma_desc_sw128(pa + poff, 16, 1024),
-                            ptx::umma_desc_sw128(va + ks * 2048, v_lbo, v_sbo), idesc_pv, ks != 0);
+          const uint32_t poff = ((ks >> 2) * 16384 + (ks & 3) * 32) >> 4;
+          ptx::umma_bf16_ss(tmem_o, ptx::umma_desc(p_lo + poff, hi_k), ptx::umma_desc(v_lo + ks * (2048 >> 4), hi_v),
+                            idesc_pv, ks != 0);
         }
         ptx::umma_commit(o_full);
         ptx::umma_commit(kv_empty(j & 1));
       }
+      __syncwarp();
     }
   } else {
     // ------------------------------------------------------------ softmax / output warps
@@ -286,8 +301,8 @@ extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq,
   int v_lbo = 16384, v_sbo = 1024;
   if (g_nvc_debug[0] == 1) { v_lbo = 1024; v_sbo = 16384; }
   dim3 grid((max_seqlen + 127) / 128, nh, B);
-  prefill_attn_kernel<<<grid, kThreads, kSmemBytes, nvc_stream(stream)>>>(
-      tq, tk, tv, cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out, v_lbo, v_sbo);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, prefill_attn_kernel, grid, dim3(kThreads), kSmemBytes, nvc_stream(stream), tq, tk, tv,
+                                 cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out, v_lbo, v_sbo));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;

@@ -47,6 +47,18 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// One lane of a fully converged warp (warp-uniform control flow around it lets the compiler keep
+// TMA / UMMA operands in uniform registers).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .b32 rx;\n\t.reg .pred px;\n\t"
+      "elect.sync rx|px, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, px;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ------------------------------------------------------------------ fences
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -127,6 +139,17 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr, uint32_t
   d |= 1ull << 46;
   d |= 2ull << 61;
   return d;
+}
+// Same descriptor split into a per-tile low word (start address and LBO; advance by adding
+// bytes >> 4) and a constant high word (SBO, version, swizzle mode).
+__device__ __forceinline__ uint32_t umma_desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return (smem_addr >> 4) | ((lbo_bytes >> 4) << 16);       // smem window < 256 KB: 14 bits suffice
+}
+__host__ __device__ constexpr uint32_t umma_desc_hi_sw128(uint32_t sbo_bytes) {
+  return (sbo_bytes >> 4) | (1u << 14) | (2u << 29);
+}
+__device__ __forceinline__ uint64_t umma_desc(uint32_t lo, uint32_t hi) {
+  return ((uint64_t)hi << 32) | lo;
 }
 // Instruction descriptor for kind::f16, bf16 x bf16 -> f32.
 //   [4,6) D format (1 = f32)  [7,10) A format (1 = bf16)  [10,13) B format (1 = bf16)

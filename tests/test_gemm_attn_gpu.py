@@ -33,6 +33,10 @@ GEMM_SHAPES = [
     (64, 1024, 2048, 64, 4),       # forced split-K
     (130, 256, 1024, 128, 8),      # split-K with 2 m-tiles
     (64, 2000, 512, 32, 2),        # split-K, ragged N, BN=32
+    (64, 1024, 3072, 2128, 4),     # two k-blocks per stage (KPS=2) + split-K, ragged last stage (12 k-blocks / 4 / 2)
+    (64, 1024, 1088, 4064, 1),     # KPS=4 with a partial last stage (17 k-blocks)
+    (64, 4096, 1024, 4032, 1),     # KPS=4, BN=32
+    (100, 512, 320, 1128, 1),      # KPS=1, 5 k-blocks
     (256, 6144, 4096, 0, 0),       # 8B qkv at batch 256
     (2048, 1024, 1024, 0, 0),      # prefill-sized
 ]

@@ -1,0 +1,95 @@
+"""GPU microbenchmark of the tcgen05 GEMM: time vs shape / tile / split-K with cold weights
+(rotating over enough weight copies to exceed L2), plus phase timestamps of one CTA."""
+import ctypes as C
+import importlib
+import sys
+import os
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+ops = importlib.import_module("nano-vllm-candle_b200.ops")
+ctx = ops.Context(0)
+BF16 = torch.bfloat16
+
+
+def bench(M, N, K, bn=0, splits=0, out_dtype=BF16, iters=20):
+    """GPU time per GEMM: `iters` launches over rotating (cold) weight copies captured in ONE CUDA
+    graph, so host launch cost (python + 2 tensor-map encodes, ~11 us) is not what is measured."""
+    ncopies = max(2, min(64, int(300e6 // (N * K * 2)) + 1))
+    a = torch.randn(M, K, device="cuda").to(BF16)
+    ws = [torch.randn(N, K, device="cuda").to(BF16) for _ in range(ncopies)]
+    out = torch.empty(M, N, device="cuda", dtype=out_dtype)
+    for w in ws[:2]:
+        ctx.gemm(a, w, out=out, force_bn=bn, force_splits=splits)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(iters):
+            ctx.gemm(a, ws[i % ncopies], out=out, force_bn=bn, force_splits=splits)
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / iters
+    gbs = (N * K * 2 + M * K * 2 + M * N * out.element_size()) / us / 1e3
+    tf = 2.0 * M * N * K / us / 1e6
+    return us, gbs, tf
+
+
+def trace(M, N, K, bn, splits):
+    a = torch.randn(M, K, device="cuda").to(BF16)
+    w = torch.randn(N, K, device="cuda").to(BF16)
+    out = torch.empty(M, N, device="cuda", dtype=BF16)
+    t = torch.zeros(128, dtype=torch.int64, device="cuda")
+    for _ in range(2):
+        st = ctx.l.nvc_gemm_bf16_trace(ctx.h, C.c_void_p(a.data_ptr()), K, C.c_void_p(w.data_ptr()), C.c_void_p(out.data_ptr()),
+                                       N, 0, M, N, K, bn, splits, C.c_void_p(torch.cuda.current_stream().cuda_stream),
+                                       C.c_void_p(t.data_ptr()))
+        assert st == 0
+    torch.cuda.synchronize()
+    t = t.cpu().tolist()
+    t0 = t[0]
+    kps = max(bn // 1000, 1)
+    kb = -(-(K // 64 // max(splits, 1)) // kps)
+    print(f"trace M={M} N={N} K={K} bn={bn} splits={splits} (cycles from kernel start)")
+    print("  setup done        ", t[1] - t0)
+    print("  tma issued  kb:   ", [t[2 + i] - t0 for i in range(min(kb, 32))])
+    print("  full waited kb:   ", [t[40 + i] - t0 for i in range(min(kb, 32))])
+    print("  mma all committed ", t[80] - t0)
+    print("  epilogue start    ", t[81] - t0)
+    print("  epilogue end      ", t[82] - t0)
+    print("  kernel end        ", t[83] - t0)
+
+
+if __name__ == "__main__":
+    print("M N K bn splits -> us, GB/s, TFLOP/s")
+    if "--trace-only" in sys.argv:
+        trace(64, 4096, 1024, 4032, 1)
+        trace(64, 4096, 1024, 2128, 4)
+        trace(4096, 4096, 4096, 1256, 1)
+        sys.exit(0)
+    small = [(0, 0), (4032, 1), (2064, 1), (4064, 1), (2128, 1), (1128, 1), (1256, 1), (2064, 2), (4064, 2),
+             (2128, 2), (2128, 4), (4064, 4), (2064, 4), (1256, 4), (2128, 8), (4064, 8)]
+    mid = [(0, 0), (2064, 1), (1128, 1), (2128, 1), (1256, 1), (1128, 2), (2128, 2), (1256, 2), (2128, 4)]
+    big = [(0, 0), (1128, 1), (1256, 1)]
+    for (M, N, K) in [(64, 4096, 1024), (64, 1024, 2048), (64, 6144, 1024), (64, 1024, 3072), (64, 151936, 1024),
+                      (1, 4096, 1024), (16, 1024, 3072),
+                      (256, 6144, 4096), (256, 4096, 4096), (256, 24576, 4096), (256, 4096, 12288),
+                      (4096, 4096, 4096), (8192, 8192, 8192), (32768, 4096, 1024), (32768, 1024, 3072)]:
+        combos = small if M <= 128 else (mid if M <= 256 else big)
+        for bn, sp in combos:
+            if N > 100000 and sp > 1:
+                continue
+            try:
+                us, gbs, tf = bench(M, N, K, bn, sp)
+                print(f"{M:6d} {N:6d} {K:6d} bn={bn % 1000:3d} kps={bn // 1000} s={sp} -> {us:9.2f} us {gbs:8.1f} GB/s {tf:8.1f} TF/s", flush=True)
+            except Exception as ex:
+                print(f"{M} {N} {K} bn={bn} s={sp} failed: {ex}")
+    trace(64, 4096, 1024, 4032, 1)
+    trace(64, 4096, 1024, 2128, 4)
+    trace(64, 1024, 2048, 4064, 4)
+    trace(4096, 4096, 4096, 1256, 1)

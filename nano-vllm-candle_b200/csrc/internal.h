@@ -19,4 +19,5 @@ int nvc_gemm_bf16_trace(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16
 // set max-dynamic-smem attributes of every kernel instantiation (called once per context)
 int nvc_gemm_init(nvc_ctx* ctx);
 int nvc_prefill_attn_init(nvc_ctx* ctx);
+int nvc_paged_decode_init(nvc_ctx* ctx);
 }

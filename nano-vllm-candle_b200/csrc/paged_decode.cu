@@ -15,6 +15,9 @@
 // the partials go to a workspace and a second kernel combines them.
 #include "common.cuh"
 #include "internal.h"
+#include "paged_decode_mma.cuh"
+
+#include <cstdlib>
 
 namespace {
 
@@ -211,6 +214,12 @@ int max_splits_for_batch(int B, int num_sms) {
 
 }  // namespace
 
+extern "C" int nvc_paged_decode_init(nvc_ctx* ctx) {
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(pdmma::paged_decode_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           pdmma::kSmemBytes));
+  return NVC_OK;
+}
+
 extern "C" size_t nvc_paged_decode_workspace_bytes(int B, int nh, int hd, int num_sms) {
   if (B <= 0 || nh <= 0 || hd <= 0) return 0;
   const size_t S = (size_t)max_splits_for_batch(B, num_sms > 0 ? num_sms : 148);
@@ -230,18 +239,26 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
   NVC_REQUIRE(ctx, ldq % 8 == 0 && ldq >= nh * hd, NVC_ESHAPE, "ldq must be >= nh*hd and a multiple of 8");
   if (B == 0) return NVC_OK;
   const int group = nh / kv;
+  // default: tensor-core kernel (whole group = the M dimension of mma.sync); NVC_PD_SIMT=1 selects the
+  // CUDA-core kernel (kept for A/B measurements, tools/decode_microbench.py)
+  static const bool use_simt = getenv("NVC_PD_SIMT") != nullptr && atoi(getenv("NVC_PD_SIMT")) != 0;
   int G;
-  if (group % 4 == 0) G = 4;
+  if (!use_simt) G = group < 16 ? group : 16;
+  else if (group % 4 == 0) G = 4;
   else if (group % 5 == 0) G = 5;
   else if (group % 2 == 0) G = 2;
   else G = 1;
-  const int chunks = group / G;
+  const int chunks = (group + G - 1) / G;
   const int max_tiles = (int)(((int64_t)max_blocks_hint * block_size + kTile - 1) / kTile);
   int splits = (2 * ctx->num_sms + B * kv * chunks - 1) / (B * kv * chunks);
   const int cap = max_splits_for_batch(B, ctx->num_sms);
   if (splits > cap) splits = cap;
   if (splits > max_tiles) splits = max_tiles;
   if (splits < 1) splits = 1;
+  if (const char* e = getenv("NVC_PD_SPLITS")) {   // tuning override (tools/decode_microbench.py)
+    const int f = atoi(e);
+    if (f > 0) splits = f < cap ? f : cap;
+  }
   float* part_o = nullptr;
   float* part_ml = nullptr;
   if (splits > 1) {
@@ -259,11 +276,17 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
   NVC_CUDA_CHECK(ctx, nvc_launch(ctx, paged_decode_kernel<GV>, grid, dim3(kThreads), 0, st, q, ldq, kc, vc,      \
                                  block_tables, max_blocks, context_lens, nh, kv, group, block_size,            \
                                  scale_log2e, out, part_o, part_ml, splits))
-  switch (G) {
-    case 4: NVC_LAUNCH_PD(4); break;
-    case 5: NVC_LAUNCH_PD(5); break;
-    case 2: NVC_LAUNCH_PD(2); break;
-    default: NVC_LAUNCH_PD(1); break;
+  if (!use_simt) {
+    NVC_CUDA_CHECK(ctx, nvc_launch(ctx, pdmma::paged_decode_mma_kernel, grid, dim3(pdmma::kThreads), pdmma::kSmemBytes, st,
+                                   q, ldq, k_cache, v_cache, block_tables, max_blocks, context_lens, nh, kv, group, G,
+                                   block_size, scale_log2e, out, part_o, part_ml, splits));
+  } else {
+    switch (G) {
+      case 4: NVC_LAUNCH_PD(4); break;
+      case 5: NVC_LAUNCH_PD(5); break;
+      case 2: NVC_LAUNCH_PD(2); break;
+      default: NVC_LAUNCH_PD(1); break;
+    }
   }
 #undef NVC_LAUNCH_PD
   NVC_CUDA_CHECK(ctx, cudaGetLastError());

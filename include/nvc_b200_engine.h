@@ -58,7 +58,7 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
 int nvc_runner_destroy(nvc_runner* r);
 
 /* One HF tensor (names / shapes of src/models/qwen3.rs:146-187,301-314,351-363,431-447,525-528),
- * FULL (unsharded) bf16 data in host memory, row-major [rows, cols] (cols = 1 for vectors).
+ * FULL (unsharded) bf16 data in host (or device) memory, row-major [rows, cols] (cols = 1 for vectors).
  * The runner fuses q/k/v (:171) and gate/up (:310) and slices its tensor-parallel shard:
  * q/k/v/gate/up rows and lm_head rows by head / column group, o_proj / down_proj input
  * columns (the reference's tp_dim 0 for RowParallelLinear, linear.rs:217, is wrong for this). */
@@ -87,7 +87,8 @@ int nvc_runner_time_decode(nvc_runner* r, int iters, float* ms_per_step, int* la
  * *ms_per_launch = average duration of one call; *launches = kernels launched in total. */
 enum {
   NVC_OP_PAGED_DECODE = 0, NVC_OP_GEMM_QKV = 1, NVC_OP_GEMM_O = 2, NVC_OP_GEMM_GATE_UP = 3, NVC_OP_GEMM_DOWN = 4,
-  NVC_OP_LM_HEAD = 5, NVC_OP_RMSNORM = 6, NVC_OP_QK_NORM_ROPE = 7, NVC_OP_SILU_MUL = 8, NVC_OP_ARGMAX = 9
+  NVC_OP_LM_HEAD = 5, NVC_OP_RMSNORM = 6, NVC_OP_QK_NORM_ROPE = 7, NVC_OP_SILU_MUL = 8, NVC_OP_ARGMAX = 9,
+  NVC_OP_NOOP = 10, NVC_OP_ALLREDUCE = 11
 };
 int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_per_launch, int* launches);
 int64_t nvc_runner_weight_bytes(const nvc_runner* r);

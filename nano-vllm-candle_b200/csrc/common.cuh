@@ -61,19 +61,35 @@ static inline cudaStream_t nvc_stream(void* s) { return reinterpret_cast<cudaStr
 // pdl_wait()) while its predecessor in the stream is still draining.  Every kernel of this
 // library calls pdl_wait() before it touches global memory and pdl_trigger() at its top.
 template <typename... KArgs, typename... Args>
-static inline cudaError_t nvc_launch(const nvc_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
-                                     cudaStream_t stream, Args&&... args) {
+static inline cudaError_t nvc_launch_cluster(const nvc_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block,
+                                             size_t smem, cudaStream_t stream, int cluster_x, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  if (ctx && ctx->use_pdl) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  if (cluster_x > 1) {
+    attr[n].id = cudaLaunchAttributeClusterDimension;
+    attr[n].val.clusterDim.x = cluster_x;
+    attr[n].val.clusterDim.y = 1;
+    attr[n].val.clusterDim.z = 1;
+    ++n;
+  }
   cfg.attrs = attr;
-  cfg.numAttrs = (ctx && ctx->use_pdl) ? 1 : 0;
+  cfg.numAttrs = n;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t nvc_launch(const nvc_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                                     cudaStream_t stream, Args&&... args) {
+  return nvc_launch_cluster(ctx, kernel, grid, block, smem, stream, 1, static_cast<Args&&>(args)...);
 }
 #endif
 

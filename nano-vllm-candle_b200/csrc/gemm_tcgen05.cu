@@ -20,6 +20,10 @@
 #include "ptx.cuh"
 #include "internal.h"
 
+#include <cstdlib>
+
+static int g_nvc_gemm_prefetch = getenv("NVC_GEMM_PREFETCH") ? atoi(getenv("NVC_GEMM_PREFETCH")) : 1;
+
 namespace {
 
 constexpr int BM = 128;
@@ -34,7 +38,7 @@ struct Cfg {
   static constexpr int kBytesB = BN * BK * 2;                 // one W sub-tile
   static constexpr int kStageBytes = KPS * (kBytesA + kBytesB);
   static constexpr int kStages = kSmemBudget / kStageBytes < 8 ? kSmemBudget / kStageBytes : 8;
-  static constexpr int kTmemCols = BN < 32 ? 32 : BN;         // BN in {32,64,128,256}: a power of two
+  static constexpr int kTmemCols = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));   // power of two >= 32
   // tiles + (2*stages + 1) mbarriers + tmem slot + ticket, plus 1024 for manual alignment
   static constexpr int kSmemBytes = kStages * kStageBytes + (2 * kStages + 1) * 8 + 16 + 1024;
   static_assert(kStages >= 2, "need at least a double buffer");
@@ -46,11 +50,11 @@ __device__ __forceinline__ int atomic_add_acq_rel_gpu(int* p, int v) {
   return old;
 }
 
-template <int BN, int KPS>
+template <int BN, int KPS, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total,
-                         int k_blocks_per_split, int a_box_rows, float* __restrict__ ws,
+                         int k_blocks_per_split, int a_box_rows, int prefetch_w, float* __restrict__ ws,
                          int* __restrict__ counters, long long* __restrict__ trace) {
   using cfg = Cfg<BN, KPS>;
   // optional phase timestamps of CTA (0,0,0) (tools/gemm_microbench.py); NULL in production
@@ -77,6 +81,10 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   const int kb_end = min(k_blocks_total, kb_begin + k_blocks_per_split);
   const int num_kb = kb_end - kb_begin;
   const int num_it = (num_kb + KPS - 1) / KPS;       // pipeline iterations (stages consumed)
+  // CL > 1: the CL CTAs of a cluster work on CL adjacent n-tiles of the same m-tile / k-range and share
+  // the activation tile: each loads 1/CL of its rows and multicasts them to all (a_box_rows = rows per CTA)
+  const uint32_t cta_rank = CL > 1 ? ptx::cluster_ctarank() : 0u;
+  constexpr uint16_t kMask = (uint16_t)((1u << CL) - 1u);
 
   if (warp == 0 && lane == 0) {
     ptx::tma_prefetch_desc(&tma_a);
@@ -86,7 +94,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     if (lane == 0) {
       for (int s = 0; s < cfg::kStages; ++s) {
         ptx::mbar_init(full_bar(s), 2);   // two producers: warp 0 (A sub-tiles) and warp 2 (W sub-tiles)
-        ptx::mbar_init(empty_bar(s), 1);
+        ptx::mbar_init(empty_bar(s), CL);   // released by the MMA warps of all CTAs that received the multicast
       }
       ptx::mbar_init(tmem_full_bar, 1);
       ptx::fence_barrier_init();
@@ -99,17 +107,31 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   __syncthreads();
   ptx::tcgen05_fence_after();
   const uint32_t tmem_base = *tmem_slot_gen;
+  if (CL > 1) ptx::cluster_sync_all();   // peers' barriers are initialised before anyone multicasts into them
+  // Weights are never written by a kernel, so their first kPrefetchKb k-blocks are pulled into L2
+  // BEFORE the dependency wait (overlapping the predecessor), and the producer keeps prefetching
+  // that far ahead of its shared-memory ring: a CTA's ring (~190 KB) covers only ~60 B/clk at HBM
+  // latency, the L2 prefetch decouples the bytes in flight from the ring size.
+  constexpr int kPrefetchKb = BN >= 256 ? 8 : (BN >= 128 ? 16 : 32);
+  if (warp == 2 && prefetch_w) {
+    if (ptx::elect_one()) {
+      const int n = min(num_kb, kPrefetchKb);
+      for (int kb = 0; kb < n; ++kb) ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, n_tile * BN);
+    }
+    __syncwarp();
+  }
   pdl_wait();      // everything above (barrier init, TMEM alloc, descriptor prefetch) overlapped the predecessor
   if (tr && threadIdx.x == 0) trace[1] = clock64();
 
   if (warp == 0 || warp == 2) {
     // ------------------------------------------------------------ TMA producers
     const bool is_a = warp == 0;
-    const uint32_t sub_bytes = is_a ? (uint32_t)a_box_rows * (BK * 2) : (uint32_t)cfg::kBytesB;   // bytes one box delivers
+    // bytes ONE box delivers into this CTA per k-block (A: all CL slices land here)
+    const uint32_t sub_bytes = is_a ? (uint32_t)a_box_rows * CL * (BK * 2) : (uint32_t)cfg::kBytesB;
     const uint32_t sub_stride = is_a ? (uint32_t)cfg::kBytesA : (uint32_t)cfg::kBytesB;
     const CUtensorMap* map = is_a ? &tma_a : &tma_b;
-    const int row0 = is_a ? m_tile * BM : n_tile * BN;
-    const uint32_t off = is_a ? 0u : (uint32_t)(KPS * cfg::kBytesA);
+    const int row0 = is_a ? m_tile * BM + (int)cta_rank * a_box_rows : n_tile * BN;
+    const uint32_t off = is_a ? cta_rank * (uint32_t)a_box_rows * (BK * 2) : (uint32_t)(KPS * cfg::kBytesA);
     for (int it = 0; it < num_it; ++it) {
       const int s = it % cfg::kStages;
       if (it >= cfg::kStages) ptx::mbar_wait(empty_bar(s), ((it / cfg::kStages) & 1) ^ 1u);   // first lap: slots are free
@@ -119,8 +141,19 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         const uint32_t dst = smem_base + s * cfg::kStageBytes + off;
         const int k0 = (kb_begin + it * KPS) * BK;
 #pragma unroll
-        for (int j = 0; j < KPS; ++j)
-          if (j < nsub) ptx::tma_load_2d(dst + j * sub_stride, map, full_bar(s), k0 + j * BK, row0);
+        for (int j = 0; j < KPS; ++j) {
+          if (j < nsub) {
+            if (CL > 1 && is_a) ptx::tma_load_2d_mcast(dst + j * sub_stride, map, full_bar(s), k0 + j * BK, row0, kMask);
+            else ptx::tma_load_2d(dst + j * sub_stride, map, full_bar(s), k0 + j * BK, row0);
+          }
+        }
+        if (!is_a && prefetch_w) {       // stay kPrefetchKb k-blocks ahead in L2
+#pragma unroll
+          for (int j = 0; j < KPS; ++j) {
+            const int kb = it * KPS + j + kPrefetchKb;
+            if (kb < num_kb) ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, row0);
+          }
+        }
         if (tr && is_a && it < 32) trace[2 + it] = clock64();
       }
       __syncwarp();
@@ -152,7 +185,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
             }
           }
         }
-        ptx::umma_commit(empty_bar(s));       // stage reusable once these MMAs have read it
+        if (CL > 1) ptx::umma_commit_mcast(empty_bar(s), kMask);   // every CTA of the cluster wrote into this stage
+        else ptx::umma_commit(empty_bar(s));       // stage reusable once these MMAs have read it
         if (it == num_it - 1) {
           ptx::umma_commit(tmem_full_bar);    // accumulator complete
           if (tr) trace[80] = clock64();
@@ -270,6 +304,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     ptx::tcgen05_fence_before();
   }
   __syncthreads();
+  if (CL > 1) ptx::cluster_sync_all();   // nobody exits while a peer may still arrive on its barriers
   if (warp == 1) {
     ptx::tcgen05_fence_after();
     ptx::tmem_dealloc(tmem_base, cfg::kTmemCols);
@@ -293,24 +328,28 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
   return NVC_OK;
 }
 
-template <int BN, int KPS>
+template <int BN, int KPS, int CL>
 int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M,
            int N, int K, int splits, cudaStream_t stream, long long* trace) {
   using cfg = Cfg<BN, KPS>;
   CUtensorMap ta, tb;
-  // a single partial m-tile only needs the rows that exist (rounded to the 8-row swizzle atom)
-  const int a_rows = M >= BM ? BM : ((M + 7) / 8) * 8;
-  int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, a_rows);
+  // a single partial m-tile only needs the rows that exist (rounded to the 8-row swizzle atom per
+  // cluster CTA); each CTA of a cluster loads a_rows / CL of them
+  const int a_rows = M >= BM ? BM : ((M + 8 * CL - 1) / (8 * CL)) * (8 * CL);
+  int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, a_rows / CL);
   if (rc) return rc;
   rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, BN);
   if (rc) return rc;
   const int kb_total = K / BK;
   const int kb_per = (kb_total + splits - 1) / splits;
   const int eff_splits = (kb_total + kb_per - 1) / kb_per;   // no empty splits
-  dim3 grid((N + BN - 1) / BN, (M + BM - 1) / BM, eff_splits);
-  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, gemm_bf16_tcgen05_kernel<BN, KPS>, grid, dim3(kThreads), cfg::kSmemBytes, stream,
-                                 ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, a_rows, ctx->gemm_ws,
-                                 ctx->gemm_counters, trace));
+  const int n_tiles = (N + BN - 1) / BN;
+  NVC_REQUIRE(ctx, n_tiles % CL == 0, NVC_ESHAPE, "n-tiles must divide by the cluster size");
+  dim3 grid(n_tiles, (M + BM - 1) / BM, eff_splits);
+  NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, gemm_bf16_tcgen05_kernel<BN, KPS, CL>, grid, dim3(kThreads), cfg::kSmemBytes,
+                                         stream, CL, ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, a_rows / CL,
+                                         (g_nvc_gemm_prefetch && M <= BM) ? 1 : 0,   // helps latency-bound decode, hurts M >= 256
+                                         ctx->gemm_ws, ctx->gemm_counters, trace));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -318,7 +357,10 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
 
 // (BN, KPS) instantiations.  KPS > 1 (several k-blocks per mbarrier round trip) is for short,
 // latency-bound CTAs (decode); KPS = 1 keeps the deepest ring for long compute-bound k-loops.
-#define NVC_GEMM_CONFIGS(X) X(256, 1) X(128, 1) X(128, 2) X(64, 2) X(64, 4) X(32, 4)
+// CL > 1: cluster of CL CTAs along N sharing the activation tile through TMA multicast (decode).
+#define NVC_GEMM_CONFIGS(X)                                                                          \
+  X(256, 1, 1) X(128, 1, 1) X(128, 2, 1) X(64, 2, 1) X(64, 4, 1) X(32, 4, 1)                       \
+  X(16, 4, 8) X(16, 4, 4) X(32, 4, 4) X(32, 4, 8) X(64, 4, 4) X(64, 2, 4) X(96, 2, 4) X(128, 2, 4) X(128, 1, 4) X(256, 1, 2)
 
 // Tile choice, fitted to tools/gemm_microbench.py (CUDA-graph timing + CTA phase traces) on B200:
 //  * a CTA ingests ~60 B/clk through TMA when the operands stream from HBM, so a k-block costs
@@ -327,8 +369,9 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
 //  * decode (M <= 128): one wave, as many CTAs as the N dimension gives (up to ~all SMs), several
 //    k-blocks per pipeline stage; split-K through the L2 workspace costs >= 6 us (ticket atomic +
 //    reduction round trips) and never won in the sweep, so it is only used when forced.
-void choose_config(const nvc_ctx* ctx, int M, int N, int K, int* bn_out, int* kps_out, int* splits_out) {
+void choose_config(const nvc_ctx* ctx, int M, int N, int K, int* bn_out, int* kps_out, int* splits_out, int* cl_out) {
   *splits_out = 1;
+  *cl_out = 1;
   if (M <= BM) {
     int bn = 32;
     const int cands[3] = {256, 128, 64};
@@ -359,8 +402,8 @@ void choose_config(const nvc_ctx* ctx, int M, int N, int K, int* bn_out, int* kp
 }  // namespace
 
 extern "C" int nvc_gemm_init(nvc_ctx* ctx) {
-#define X(BN, KPS)                                                                   \
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, KPS>,        \
+#define X(BN, KPS, CL)                                                               \
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, KPS, CL>,    \
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, KPS>::kSmemBytes));
   NVC_GEMM_CONFIGS(X)
 #undef X
@@ -381,11 +424,13 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
               "pointers must be 16-byte aligned");
   NVC_REQUIRE(ctx, ctx->encode_tiled != nullptr, NVC_EDEVICE, "cuTensorMapEncodeTiled unavailable");
   if (M == 0) return NVC_OK;
-  int bn, kps, splits;
-  choose_config(ctx, M, Nout, K, &bn, &kps, &splits);
-  if (force_bn) {          // force_bn = BN + 1000 * KPS (KPS 0: the first instantiation of that BN)
+  int bn, kps, splits, cl = 1;
+  choose_config(ctx, M, Nout, K, &bn, &kps, &splits, &cl);
+  if (force_bn) {          // force_bn = BN + 1000 * KPS + 10000 * CL (KPS 0: the first instantiation of that BN)
     bn = force_bn % 1000;
-    kps = force_bn / 1000;
+    kps = (force_bn / 1000) % 10;
+    cl = force_bn / 10000;
+    if (cl == 0) cl = 1;
     if (kps == 0) kps = bn >= 128 ? 1 : (bn == 64 ? 2 : 4);
   }
   if (force_splits) splits = force_splits;
@@ -397,8 +442,8 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   }
   cudaStream_t st = nvc_stream(stream);
   const int f32 = out_dtype == NVC_DT_F32;
-#define X(BN, KPS) \
-  if (bn == BN && kps == KPS) return launch<BN, KPS>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, st, trace);
+#define X(BN, KPS, CL) \
+  if (bn == BN && kps == KPS && cl == CL) return launch<BN, KPS, CL>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, st, trace);
   NVC_GEMM_CONFIGS(X)
 #undef X
   NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported tile configuration");

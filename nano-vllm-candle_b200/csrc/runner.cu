@@ -301,13 +301,13 @@ int64_t nvc_runner_kv_bytes_per_token(const nvc_runner* r) {
 namespace {
 
 int copy_rows(nvc_runner* r, nvc_bf16* dst, const nvc_bf16* src, int64_t row0, int64_t nrows, int64_t cols) {
-  R_CUDA(cudaMemcpy(dst, src + row0 * cols, (size_t)nrows * cols * 2, cudaMemcpyHostToDevice));
+  R_CUDA(cudaMemcpy(dst, src + row0 * cols, (size_t)nrows * cols * 2, cudaMemcpyDefault));   // host or device source
   return NVC_OK;
 }
 // dst[rows, ncols] = src[rows, col0 : col0+ncols] of a [rows, cols] matrix
 int copy_cols(nvc_runner* r, nvc_bf16* dst, const nvc_bf16* src, int64_t rows, int64_t cols, int64_t col0, int64_t ncols) {
   R_CUDA(cudaMemcpy2D(dst, (size_t)ncols * 2, src + col0, (size_t)cols * 2, (size_t)ncols * 2, (size_t)rows,
-                      cudaMemcpyHostToDevice));
+                      cudaMemcpyDefault));
   return NVC_OK;
 }
 
@@ -588,8 +588,10 @@ extern "C" int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_pe
   R_CUDA(cudaStreamSynchronize(r->stream));
   int rc = NVC_OK, n = 0;
   const uint64_t l0 = ctx->launches;
-  R_CUDA(cudaEventRecord(e0, r->stream));
-  for (int it = 0; it < iters && rc == NVC_OK; ++it) {
+  // one pass over the layers is captured into a CUDA graph and replayed `iters` times, so the
+  // number is GPU time (launch gaps as in the real step), not host launch cost
+  R_CUDA(cudaStreamBeginCapture(r->stream, cudaStreamCaptureModeThreadLocal));
+  for (int it = 0; it < 1 && rc == NVC_OK; ++it) {
     if (op == NVC_OP_LM_HEAD) {
       rc = nvc_gemm_bf16(ctx, r->xn_last, H, r->lm_head, r->logits, r->V_l, NVC_DT_F32, B, r->V_l, H, st);
       ++n;
@@ -631,20 +633,38 @@ extern "C" int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_pe
         case NVC_OP_SILU_MUL:
           rc = nvc_silu_and_mul(ctx, r->gu, r->act, B, r->I_l, st);
           break;
+        case NVC_OP_NOOP:   // smallest possible kernel: the per-launch floor inside a graph
+          rc = nvc_gather_rows(ctx, r->x, nullptr, r->d_last_rows, r->x_last, nullptr, 1, H, st);
+          break;
+        case NVC_OP_ALLREDUCE:
+          rc = nvc_allreduce_bf16(ctx, r->x, (size_t)B * H, st);
+          break;
         default:
           rc = NVC_EINVAL;
       }
     }
   }
-  cudaEventRecord(e1, r->stream);
-  cudaError_t ce = cudaEventSynchronize(e1);
+  cudaGraph_t graph = nullptr;
+  cudaError_t ce = cudaStreamEndCapture(r->stream, &graph);
+  cudaGraphExec_t exec = nullptr;
+  if (ce == cudaSuccess && rc == NVC_OK) ce = cudaGraphInstantiate(&exec, graph, 0);
+  if (graph) cudaGraphDestroy(graph);
   float ms = 0.f;
-  if (ce == cudaSuccess) ce = cudaEventElapsedTime(&ms, e0, e1);
+  if (ce == cudaSuccess && rc == NVC_OK) {
+    ce = cudaGraphLaunch(exec, r->stream);                      // warm-up replay
+    if (ce == cudaSuccess) ce = cudaEventRecord(e0, r->stream);
+    for (int it = 0; it < iters && ce == cudaSuccess; ++it) ce = cudaGraphLaunch(exec, r->stream);
+    if (ce == cudaSuccess) ce = cudaEventRecord(e1, r->stream);
+    if (ce == cudaSuccess) ce = cudaEventSynchronize(e1);
+    if (ce == cudaSuccess) ce = cudaEventElapsedTime(&ms, e0, e1);
+  }
+  if (exec) cudaGraphExecDestroy(exec);
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);
   if (rc) return rc;
   R_CUDA(ce);
-  const int kernels = (int)(ctx->launches - l0);
+  const int kernels = (int)(ctx->launches - l0) * iters;
+  n *= iters;
   *ms_per_launch = n ? ms / n : 0.f;
   if (launches) *launches = kernels;
   return NVC_OK;

@@ -208,7 +208,7 @@ class Qwen3ModelRunner:
 
     def load_weight(self, name: str, t) -> None:
         import torch
-        t = t.detach().to("cpu", torch.bfloat16).contiguous()
+        t = t.detach().to(torch.bfloat16).contiguous()          # host or device memory, both accepted
         rows = t.shape[0]
         cols = t.shape[1] if t.dim() == 2 else 1
         st = self.l.nvc_runner_load_weight(self.handle, name.encode(), C.c_void_p(t.data_ptr()), rows, cols)
@@ -261,7 +261,7 @@ class Qwen3ModelRunner:
         return ms.value, n.value
 
     OPS = {"paged_decode": 0, "gemm_qkv": 1, "gemm_o": 2, "gemm_gate_up": 3, "gemm_down": 4, "lm_head": 5,
-           "rmsnorm": 6, "qk_norm_rope": 7, "silu_mul": 8, "argmax": 9}
+           "rmsnorm": 6, "qk_norm_rope": 7, "silu_mul": 8, "argmax": 9, "noop": 10, "allreduce": 11}
 
     def time_op(self, op: str, iters: int) -> Tuple[float, int]:
         """(average ms per call, kernels launched) of one kernel family over all layers."""

@@ -105,3 +105,18 @@ def make_prompts(num: int, length, vocab: int, seed: int) -> List[List[int]]:
         n = length if isinstance(length, int) else int(rng.integers(length[0], length[1] + 1))
         out.append(rng.integers(0, vocab, size=n).astype(np.int64).tolist())
     return out
+
+
+def iter_weights_device(cfg, seed: int = 0, std: float = 0.02, device="cuda"):
+    """Same tensor set generated on the GPU with torch's Philox generator: NOT the numpy streams of
+    make_tensor (no oracle parity), only for throughput sweeps of the large models where host-side
+    generation of 8-32 B normals would dominate the run."""
+    g = torch.Generator(device=device)
+    for i, (name, shape, kind) in enumerate(tensor_specs(cfg)):
+        if kind == "norm":
+            yield name, torch.ones(shape, dtype=torch.bfloat16, device=device)
+        else:
+            g.manual_seed(seed * 1000003 + i)
+            t = torch.empty(shape, dtype=torch.bfloat16, device=device)
+            t.normal_(0.0, std, generator=g)
+            yield name, t

@@ -37,6 +37,14 @@ GEMM_SHAPES = [
     (64, 1024, 1088, 4064, 1),     # KPS=4 with a partial last stage (17 k-blocks)
     (64, 4096, 1024, 4032, 1),     # KPS=4, BN=32
     (100, 512, 320, 1128, 1),      # KPS=1, 5 k-blocks
+    (64, 1024, 2048, 84016, 1),    # cluster of 8 CTAs, activation tile multicast, BN=16
+    (64, 4096, 1024, 44032, 1),    # cluster of 4, BN=32
+    (64, 6144, 1024, 44064, 1),    # cluster of 4, BN=64
+    (1, 1024, 1024, 84016, 1),     # M=1 through the cluster path (rows zero-filled up to 8 per CTA)
+    (130, 1024, 512, 44032, 1),    # two m-tiles, second one ragged, clusters along N
+    (256, 6144, 4096, 42096, 1),   # BN=96 (UMMA N=96), cluster 4: 8B qkv at batch 256
+    (256, 4096, 4096, 42064, 1),   # 8B o_proj at batch 256
+    (256, 2048, 512, 21256, 1),    # BN=256 cluster of 2
     (256, 6144, 4096, 0, 0),       # 8B qkv at batch 256
     (2048, 1024, 1024, 0, 0),      # prefill-sized
 ]

@@ -173,9 +173,7 @@ def run_ours(args):
 
     ctx = ops.Context(local, rank, world)
     if world > 1:
-        box = [ops.Context.nccl_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)
-        ctx.init_nccl(box[0])
+        ctx.init_tp(dist)                  # NCCL communicator + NVLink peer buffers
     cfg = eng.MODEL_CONFIGS[MODEL]
     K, W = args.steps, args.warmup
     total_len = PROMPT_LEN + W + K + 16

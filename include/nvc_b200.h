@@ -83,6 +83,24 @@ int nvc_allreduce_f32(nvc_ctx* ctx, float* buf, size_t count, void* stream);
 /* In-place all-gather: every rank contributes `count_per_rank` bytes at offset rank*count. */
 int nvc_allgather_bytes(nvc_ctx* ctx, void* buf, size_t bytes_per_rank, void* stream);
 
+/* Peer-memory all-reduce over NVLink / NVSwitch (one-shot, for decode-sized messages), fused with
+ * the residual add + RMSNorm that follow every row-parallel linear.  Setup: every rank calls
+ * nvc_ctx_p2p_export (allocates [flags | slot 0 | slot 1] and returns a 64-byte CUDA IPC handle),
+ * the caller all-gathers the handles, every rank calls nvc_ctx_p2p_import with the tp_size x 64
+ * bytes.  The row-parallel GEMM writes its partial [N, H] bf16 result into nvc_ctx_p2p_slot(s)
+ * (alternate s between consecutive all-reduces), then
+ *   nvc_p2p_allreduce_rmsnorm: sum = sum over ranks (fp32, rank order) of slot s;
+ *     w != NULL: s = sum + residual_in; residual_out = s; out = bf16(rmsnorm(s) * w)  (K9 + K1)
+ *     w == NULL: out = bf16(sum).
+ * tp_size in {2, 4, 8}; N * H * 2 <= slot_bytes. */
+int nvc_ctx_p2p_export(nvc_ctx* ctx, size_t slot_bytes, void* handle_64B);
+int nvc_ctx_p2p_import(nvc_ctx* ctx, const void* handles_tp_x_64B);
+int nvc_ctx_p2p_ready(const nvc_ctx* ctx);
+size_t nvc_ctx_p2p_slot_bytes(const nvc_ctx* ctx);
+void* nvc_ctx_p2p_slot(nvc_ctx* ctx, int slot);
+int nvc_p2p_allreduce_rmsnorm(nvc_ctx* ctx, int slot, const float* residual_in, float* residual_out,
+                              const nvc_bf16* w, float eps, nvc_bf16* out, int N, int H, void* stream);
+
 /* ------------------------------------------------------------------ kernels */
 
 /* K0. Replaces Tensor::embedding in Qwen3Model::forward (src/models/qwen3.rs:465-468).

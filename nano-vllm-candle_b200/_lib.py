@@ -64,6 +64,10 @@ def _declare(l: C.CDLL) -> None:
         "nvc_allreduce_bf16": [_vp, _vp, _sz, _vp],
         "nvc_allreduce_f32": [_vp, _vp, _sz, _vp],
         "nvc_allgather_bytes": [_vp, _vp, _sz, _vp],
+        "nvc_ctx_p2p_export": [_vp, _sz, _vp],
+        "nvc_ctx_p2p_import": [_vp, _vp],
+        "nvc_ctx_p2p_ready": [_vp],
+        "nvc_p2p_allreduce_rmsnorm": [_vp, _i, _vp, _vp, _vp, _f, _vp, _i, _i, _vp],
         "nvc_embed_gather": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp],
         "nvc_fused_add_rmsnorm": [_vp, _vp, _vp, _vp, _vp, _f, _vp, _i, _i, _vp],
         "nvc_gemm_bf16": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp],
@@ -83,6 +87,10 @@ def _declare(l: C.CDLL) -> None:
         fn = getattr(l, name)
         fn.argtypes = args
         fn.restype = _i
+    l.nvc_ctx_p2p_slot.restype = _vp
+    l.nvc_ctx_p2p_slot.argtypes = [_vp, _i]
+    l.nvc_ctx_p2p_slot_bytes.restype = _sz
+    l.nvc_ctx_p2p_slot_bytes.argtypes = [_vp]
     l.nvc_paged_decode_workspace_bytes.restype = _sz
     l.nvc_paged_decode_workspace_bytes.argtypes = [_i, _i, _i, _i]
     from . import _engine_sigs

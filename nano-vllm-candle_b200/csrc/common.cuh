@@ -50,6 +50,14 @@ struct nvc_ctx {
   // tensor-parallel communicator (NULL when tp_size == 1)
   nvc_nccl_api* nccl = nullptr;
   void* nccl_comm = nullptr;
+  // peer-memory all-reduce over NVLink (p2p_allreduce.cu): one cudaMalloc'ed buffer per rank,
+  // mapped into every peer with CUDA IPC.  Layout: [flags 4 KB][slot 0][slot 1]
+  uint8_t* p2p_local = nullptr;          // this rank's buffer
+  uint8_t* p2p_peer[8] = {nullptr};      // every rank's buffer as seen from this rank (own included)
+  uint8_t** p2p_peer_d = nullptr;        // the same table in device memory
+  uint32_t* p2p_state = nullptr;         // device: [0] epoch, [1] CTAs done
+  size_t p2p_slot_bytes = 0;
+  bool p2p_ready = false;
 };
 
 void nvc_set_error(nvc_ctx* ctx, const std::string& msg);

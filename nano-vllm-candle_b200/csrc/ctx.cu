@@ -6,6 +6,7 @@
 #include <cstring>
 
 void nvc_collectives_destroy(nvc_ctx* ctx);   // collectives.cu
+void nvc_p2p_destroy(nvc_ctx* ctx);           // p2p_allreduce.cu
 
 static thread_local std::string g_null_ctx_error;
 
@@ -108,6 +109,7 @@ extern "C" uint64_t nvc_ctx_launch_count(const nvc_ctx* ctx) { return ctx ? ctx-
 extern "C" int nvc_ctx_destroy(nvc_ctx* ctx) {
   if (!ctx) return NVC_EINVAL;
   cudaSetDevice(ctx->device);
+  nvc_p2p_destroy(ctx);
   nvc_collectives_destroy(ctx);
   if (ctx->gemm_ws) cudaFree(ctx->gemm_ws);
   if (ctx->gemm_counters) cudaFree(ctx->gemm_counters);

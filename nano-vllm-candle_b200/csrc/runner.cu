@@ -11,6 +11,7 @@
 #include "internal.h"
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <set>
@@ -82,25 +83,40 @@ int launch_count_layer(const nvc_runner* r) { return r->tp > 1 ? 11 : 9; }
 
 // The transformer body over N tokens already embedded in r->x.  decode: attention over the
 // paged cache; prefill: varlen causal flash over the tokens of this step.
-int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blocks_hint) {
+// Under TP the partial sums of o_proj / down_proj are reduced either by NCCL (in place, then the
+// fused add + RMSNorm kernel) or, for decode-sized messages when the NVLink peer buffers are set
+// up, by ONE kernel that reads the peers' partials and applies residual add + RMSNorm
+// (p2p_allreduce.cu).  In that mode the norm that opens layer l+1 is produced at the end of layer
+// l, and the final norm by the last layer (*final_norm_done).
+int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blocks_hint, bool* final_norm_done) {
   const nvc_qwen3_config& c = r->cfg;
   nvc_ctx* ctx = r->ctx;
   void* st = r->stream;
-  const int H = c.hidden_size, hd = c.head_dim;
+  const int H = c.hidden_size, hd = c.head_dim, L = c.num_hidden_layers;
   const float scale = 1.0f / sqrtf((float)hd);   // (head_dim as f32).powf(-0.5), qwen3.rs:132
+  static const bool p2p_env = !(getenv("NVC_P2P_AR") && atoi(getenv("NVC_P2P_AR")) == 0);
+  const bool p2p = r->tp > 1 && decode && p2p_env && nvc_ctx_p2p_ready(ctx) &&
+                   (size_t)N * H * 2 <= nvc_ctx_p2p_slot_bytes(ctx);
+  nvc_bf16* slot0 = p2p ? reinterpret_cast<nvc_bf16*>(nvc_ctx_p2p_slot(ctx, 0)) : nullptr;
+  nvc_bf16* slot1 = p2p ? reinterpret_cast<nvc_bf16*>(nvc_ctx_p2p_slot(ctx, 1)) : nullptr;
+  *final_norm_done = false;
+  bool xn_ready = false;
   int rc;
-  for (int li = 0; li < c.num_hidden_layers; ++li) {
-    Layer& L = r->layers[li];
-    // input_layernorm with fused residual add; layer 0 seeds the residual stream (qwen3.rs:376-387)
-    rc = nvc_fused_add_rmsnorm(ctx, r->x, li == 0 ? nullptr : r->residual, r->residual, L.ln1, c.rms_norm_eps, r->xn, N, H, st);
+  for (int li = 0; li < L; ++li) {
+    Layer& Ly = r->layers[li];
+    if (!xn_ready) {
+      // input_layernorm with fused residual add; layer 0 seeds the residual stream (qwen3.rs:376-387)
+      rc = nvc_fused_add_rmsnorm(ctx, r->x, li == 0 ? nullptr : r->residual, r->residual, Ly.ln1, c.rms_norm_eps, r->xn, N, H, st);
+      if (rc) return rc;
+    }
+    xn_ready = false;
+    rc = nvc_gemm_bf16(ctx, r->xn, H, Ly.w_qkv, r->qkv, r->qkv_l, NVC_DT_BF16, N, r->qkv_l, H, st);
     if (rc) return rc;
-    rc = nvc_gemm_bf16(ctx, r->xn, H, L.w_qkv, r->qkv, r->qkv_l, NVC_DT_BF16, N, r->qkv_l, H, st);
-    if (rc) return rc;
-    rc = nvc_qk_norm_rope_store(ctx, r->qkv, L.q_norm, L.k_norm, c.rms_norm_eps, r->rope, r->d_pos, r->d_slots,
-                                L.k_cache, L.v_cache, N, r->nh_l, r->kv_l, hd, st);
+    rc = nvc_qk_norm_rope_store(ctx, r->qkv, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos, r->d_slots,
+                                Ly.k_cache, Ly.v_cache, N, r->nh_l, r->kv_l, hd, st);
     if (rc) return rc;
     if (decode) {
-      rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, L.k_cache, L.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
+      rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
                                     r->d_ctx, B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
                                     r->decode_ws, r->decode_ws_bytes, st);
     } else {
@@ -109,24 +125,40 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
                                    r->nh_l, r->kv_l, hd, scale, r->attn, st);
     }
     if (rc) return rc;
-    rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, L.w_o, r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
+    // o_proj (row-parallel) -> [all-reduce, N4] -> post_attention_layernorm with residual add
+    rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, Ly.w_o, p2p ? slot0 : r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
     if (rc) return rc;
-    if (r->tp > 1) { rc = nvc_allreduce_bf16(ctx, r->x, (size_t)N * H, st); if (rc) return rc; }   // N4
-    rc = nvc_fused_add_rmsnorm(ctx, r->x, r->residual, r->residual, L.ln2, c.rms_norm_eps, r->xn, N, H, st);
+    if (p2p) {
+      rc = nvc_p2p_allreduce_rmsnorm(ctx, 0, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
+    } else {
+      if (r->tp > 1) { rc = nvc_allreduce_bf16(ctx, r->x, (size_t)N * H, st); if (rc) return rc; }
+      rc = nvc_fused_add_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
+    }
     if (rc) return rc;
-    rc = nvc_gemm_bf16(ctx, r->xn, H, L.w_gu, r->gu, 2 * r->I_l, NVC_DT_BF16, N, 2 * r->I_l, H, st);
+    rc = nvc_gemm_bf16(ctx, r->xn, H, Ly.w_gu, r->gu, 2 * r->I_l, NVC_DT_BF16, N, 2 * r->I_l, H, st);
     if (rc) return rc;
     rc = nvc_silu_and_mul(ctx, r->gu, r->act, N, r->I_l, st);
     if (rc) return rc;
-    rc = nvc_gemm_bf16(ctx, r->act, r->I_l, L.w_down, r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
+    // down_proj (row-parallel) -> [all-reduce, N4]
+    rc = nvc_gemm_bf16(ctx, r->act, r->I_l, Ly.w_down, p2p ? slot1 : r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
     if (rc) return rc;
-    if (r->tp > 1) { rc = nvc_allreduce_bf16(ctx, r->x, (size_t)N * H, st); if (rc) return rc; }   // N4
+    if (p2p) {
+      const bool last = li + 1 == L;
+      rc = nvc_p2p_allreduce_rmsnorm(ctx, 1, r->residual, r->residual, last ? r->final_norm : r->layers[li + 1].ln1,
+                                     c.rms_norm_eps, last ? r->xn_last : r->xn, N, H, st);
+      if (rc) return rc;
+      xn_ready = !last;
+      *final_norm_done = last;
+    } else if (r->tp > 1) {
+      rc = nvc_allreduce_bf16(ctx, r->x, (size_t)N * H, st);
+      if (rc) return rc;
+    }
   }
   return NVC_OK;
 }
 
 // last-token rows -> final norm -> lm_head (fp32 logits) -> argmax (vocab shard offset)
-int run_head(nvc_runner* r, int B, bool decode) {
+int run_head(nvc_runner* r, int B, bool decode, bool final_norm_done) {
   const nvc_qwen3_config& c = r->cfg;
   nvc_ctx* ctx = r->ctx;
   void* st = r->stream;
@@ -140,8 +172,10 @@ int run_head(nvc_runner* r, int B, bool decode) {
     xs = r->x_last;
     rs = r->res_last;
   }
-  rc = nvc_fused_add_rmsnorm(ctx, xs, rs, nullptr, r->final_norm, c.rms_norm_eps, r->xn_last, B, H, st);   // qwen3.rs:497
-  if (rc) return rc;
+  if (!final_norm_done) {
+    rc = nvc_fused_add_rmsnorm(ctx, xs, rs, nullptr, r->final_norm, c.rms_norm_eps, r->xn_last, B, H, st);   // qwen3.rs:497
+    if (rc) return rc;
+  }
   rc = nvc_gemm_bf16(ctx, r->xn_last, H, r->lm_head, r->logits, r->V_l, NVC_DT_F32, B, r->V_l, H, st);     // qwen3.rs:548
   if (rc) return rc;
   rc = nvc_argmax_last(ctx, r->logits, r->V_l, r->d_tok, r->d_tok_val, B, r->V_l, r->rank * r->V_l, st);    // llm_engine.rs:135-142
@@ -177,9 +211,10 @@ int finish_tokens(nvc_runner* r, int B, int32_t* out_tokens) {
 int decode_body(nvc_runner* r, int B, int blocks_hint) {
   int rc = nvc_embed_gather(r->ctx, r->d_ids, r->embed, r->x, B, r->cfg.hidden_size, r->cfg.vocab_size, r->stream);
   if (rc) return rc;
-  rc = run_layers(r, B, true, B, 1, blocks_hint);
+  bool fnd = false;
+  rc = run_layers(r, B, true, B, 1, blocks_hint, &fnd);
   if (rc) return rc;
-  return run_head(r, B, true);
+  return run_head(r, B, true, fnd);
 }
 
 int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
@@ -443,9 +478,10 @@ extern "C" int nvc_runner_prefill(nvc_runner* r, const int32_t* ids, const int32
   R_CUDA(cudaMemcpyAsync(r->d_last_rows, last, B * 4, cudaMemcpyHostToDevice, st));
   int rc = nvc_embed_gather(ctx, r->d_ids, r->embed, r->x, N, r->cfg.hidden_size, r->cfg.vocab_size, st);
   if (rc) return rc;
-  rc = run_layers(r, N, false, B, max_seqlen, 0);
+  bool fnd = false;
+  rc = run_layers(r, N, false, B, max_seqlen, 0, &fnd);
   if (rc) return rc;
-  rc = run_head(r, B, false);
+  rc = run_head(r, B, false, fnd);
   if (rc) return rc;
   r->last_B = B;
   return finish_tokens(r, B, out_tokens);
@@ -636,8 +672,12 @@ extern "C" int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_pe
         case NVC_OP_NOOP:   // smallest possible kernel: the per-launch floor inside a graph
           rc = nvc_gather_rows(ctx, r->x, nullptr, r->d_last_rows, r->x_last, nullptr, 1, H, st);
           break;
-        case NVC_OP_ALLREDUCE:
-          rc = nvc_allreduce_bf16(ctx, r->x, (size_t)B * H, st);
+        case NVC_OP_ALLREDUCE:     // what the decode step uses: fused peer all-reduce + norm, or NCCL
+          if (nvc_ctx_p2p_ready(ctx) && (size_t)B * H * 2 <= nvc_ctx_p2p_slot_bytes(ctx) &&
+              !(getenv("NVC_P2P_AR") && atoi(getenv("NVC_P2P_AR")) == 0))
+            rc = nvc_p2p_allreduce_rmsnorm(ctx, li & 1, r->residual, r->residual, L.ln2, c.rms_norm_eps, r->xn, B, H, st);
+          else
+            rc = nvc_allreduce_bf16(ctx, r->x, (size_t)B * H, st);
           break;
         default:
           rc = NVC_EINVAL;

@@ -68,6 +68,28 @@ class Context:
         assert len(unique_id) == 128
         self._ck(self.l.nvc_ctx_init_nccl(self.h, C.c_char_p(unique_id)), "nvc_ctx_init_nccl")
 
+    def p2p_export(self, slot_bytes: int) -> bytes:
+        """Allocates this rank's peer buffer; returns the 64-byte CUDA IPC handle to all-gather."""
+        buf = C.create_string_buffer(64)
+        self._ck(self.l.nvc_ctx_p2p_export(self.h, slot_bytes, buf), "nvc_ctx_p2p_export")
+        return buf.raw
+
+    def p2p_import(self, handles) -> None:
+        """handles: the tp_size 64-byte handles in rank order."""
+        blob = b"".join(handles)
+        assert len(blob) == 64 * self.tp_size
+        self._ck(self.l.nvc_ctx_p2p_import(self.h, C.c_char_p(blob)), "nvc_ctx_p2p_import")
+
+    def init_tp(self, dist, slot_bytes: int = 4 << 20) -> None:
+        """NCCL communicator + NVLink peer buffers, rendezvous through torch.distributed."""
+        box = [Context.nccl_unique_id() if self.tp_rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        self.init_nccl(box[0])
+        mine = self.p2p_export(slot_bytes)
+        allh = [None] * self.tp_size
+        dist.all_gather_object(allh, mine)
+        self.p2p_import(allh)
+
     def allreduce(self, buf: torch.Tensor):
         if buf.dtype == BF16:
             self._ck(self.l.nvc_allreduce_bf16(self.h, _ptr(buf), buf.numel(), _stream()), "nvc_allreduce_bf16")

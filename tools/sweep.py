@@ -36,9 +36,7 @@ def main():
     synth = importlib.import_module("nano-vllm-candle_b200.synth")
     ctx = ops.Context(local, rank, world)
     if world > 1:
-        box = [ops.Context.nccl_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)
-        ctx.init_nccl(box[0])
+        ctx.init_tp(dist)                  # NCCL communicator + NVLink peer buffers
     cfg = eng.MODEL_CONFIGS[a.model]
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else \
         {"hbm_gbs": 6650.0, "bf16_tflops_sustained": 1400.0, "bf16_tflops": 1590.0}

@@ -35,9 +35,7 @@ def main():
     eng = importlib.import_module("nano-vllm-candle_b200.engine")
     synth = importlib.import_module("nano-vllm-candle_b200.synth")
     ctx = ops.Context(local, rank, world)
-    box = [ops.Context.nccl_unique_id() if rank == 0 else None]
-    dist.broadcast_object_list(box, src=0)
-    ctx.init_nccl(box[0])
+    ctx.init_tp(dist)                      # NCCL communicator + NVLink peer buffers
     cfg = eng.MODEL_CONFIGS[a.model]
     tiny = a.model == "qwen3-tiny"
     bs = 16 if tiny else 256

@@ -47,6 +47,7 @@ struct nvc_ctx {
   size_t gemm_ws_bytes = 0;
   int* gemm_counters = nullptr;
   int gemm_num_counters = 0;
+  int pair_clusters[5] = {0, 0, 0, 0, 0};   // co-resident clusters of 2S CTAs of the pair GEMM, S = 1..4
   // tensor-parallel communicator (NULL when tp_size == 1)
   nvc_nccl_api* nccl = nullptr;
   void* nccl_comm = nullptr;
@@ -69,8 +70,8 @@ static inline cudaStream_t nvc_stream(void* s) { return reinterpret_cast<cudaStr
 // pdl_wait()) while its predecessor in the stream is still draining.  Every kernel of this
 // library calls pdl_wait() before it touches global memory and pdl_trigger() at its top.
 template <typename... KArgs, typename... Args>
-static inline cudaError_t nvc_launch_cluster(const nvc_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block,
-                                             size_t smem, cudaStream_t stream, int cluster_x, Args&&... args) {
+static inline cudaError_t nvc_launch_cluster3(const nvc_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block,
+                                              size_t smem, cudaStream_t stream, dim3 cluster, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -83,16 +84,22 @@ static inline cudaError_t nvc_launch_cluster(const nvc_ctx* ctx, void (*kernel)(
     attr[n].val.programmaticStreamSerializationAllowed = 1;
     ++n;
   }
-  if (cluster_x > 1) {
+  if (cluster.x * cluster.y * cluster.z > 1) {
     attr[n].id = cudaLaunchAttributeClusterDimension;
-    attr[n].val.clusterDim.x = cluster_x;
-    attr[n].val.clusterDim.y = 1;
-    attr[n].val.clusterDim.z = 1;
+    attr[n].val.clusterDim.x = cluster.x;
+    attr[n].val.clusterDim.y = cluster.y;
+    attr[n].val.clusterDim.z = cluster.z;
     ++n;
   }
   cfg.attrs = attr;
   cfg.numAttrs = n;
   return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+template <typename... KArgs, typename... Args>
+static inline cudaError_t nvc_launch_cluster(const nvc_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block,
+                                             size_t smem, cudaStream_t stream, int cluster_x, Args&&... args) {
+  return nvc_launch_cluster3(ctx, kernel, grid, block, smem, stream, dim3(cluster_x > 1 ? cluster_x : 1, 1, 1),
+                             static_cast<Args&&>(args)...);
 }
 template <typename... KArgs, typename... Args>
 static inline cudaError_t nvc_launch(const nvc_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,

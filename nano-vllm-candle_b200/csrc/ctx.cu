@@ -91,6 +91,7 @@ extern "C" int nvc_ctx_create(int device, int tp_rank, int tp_size, nvc_ctx** ou
     return NVC_CUDA_ERROR_BASE + (int)e;
   }
   int rc = nvc_gemm_init(ctx);
+  if (rc == NVC_OK) rc = nvc_gemm_pair_init(ctx);
   if (rc == NVC_OK) rc = nvc_prefill_attn_init(ctx);
   if (rc == NVC_OK) rc = nvc_paged_decode_init(ctx);
   if (rc != NVC_OK) {

@@ -1,0 +1,433 @@
+// K3 (M > 128): C[M,N] = A[M,K] * W[N,K]^T on CTA PAIRS (tcgen05.mma.cta_group::2).
+// Replaces the same reference calls as gemm_tcgen05.cu (src/layers/linear.rs:33-38,72-77,
+// 99-104,171-175,184-198; src/models/qwen3.rs:542-550) for prefill and for decode batches > 128.
+//
+// Output tile = 256 x 256 per CTA pair (two SMs of one TPC).  CTA h of the pair (h = cluster
+// rank & 1) loads rows [128h, 128h+128) of the A tile AND rows [128h, 128h+128) of the W tile
+// (its half of the N dimension); one tcgen05.mma.cta_group::2 (M=256, N=256, K=16) issued by the
+// leader (h = 0) reads both halves of W and writes 128 accumulator rows x 256 columns into each
+// CTA's tensor memory.  Per SM and k-block that is 32 KB of shared-memory ingest for 512 tensor
+// cycles (64 B/clk) against 48 KB (96 B/clk) for the 1-CTA 128 x 256 tile.
+//
+// Two schedules share the kernel:
+//  * S = 1, persistent: min(tiles, #pairs) clusters of 2 walk the tiles (n fastest); two
+//    256-column accumulators in tensor memory (all 512 columns) so the epilogue of tile i
+//    overlaps the main loop of tile i+1.
+//  * S > 1, split-K inside a cluster of 2S CTAs (decode, M <= 256: too few tiles to fill 148
+//    SMs): pair p of the cluster takes k-blocks [p*kb_per, ...) of ONE tile; partial accumulators
+//    are exchanged through distributed shared memory (every CTA parks the 16-column chunks it
+//    does not own in its own, now idle, operand ring; CTA (p, h) sums chunk c, c % S == p, in
+//    split order 0..S-1: deterministic) - no global workspace, no atomics.
+// Roles per CTA (192 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer (leader
+// only), warps 2-5 epilogue (tcgen05.ld -> bf16/f32 -> 16-byte stores).
+#include "common.cuh"
+#include "ptx.cuh"
+#include "internal.h"
+
+#include <cmath>
+#include <cstdlib>
+
+namespace {
+
+constexpr int kTileM = 256, kTileN = 256, kHalf = 128, BK = 64;
+constexpr int kThreads = 192;
+constexpr int kStages = 6;
+constexpr int kBytesA = kHalf * BK * 2;            // 16 KB: this CTA's 128 rows of the activation tile
+constexpr int kBytesB = kHalf * BK * 2;            // 16 KB: this CTA's 128 rows (N half) of the weight tile
+constexpr int kStageBytes = kBytesA + kBytesB;
+constexpr int kNumBars = 2 * kStages + 4;          // full[6], empty[6], tmem_full[2], tmem_empty[2]
+constexpr int kSmemBytes = kStages * kStageBytes + kNumBars * 8 + 16 + 1024;
+constexpr int kTmemCols = 512;
+constexpr int kDumpBytes = 16 * 4 * kHalf * 16;    // 128 KB: [chunk 16][float4 4][row 128] fp32 partials
+static_assert(kDumpBytes <= kStages * kStageBytes, "the partial-accumulator dump reuses the operand ring");
+
+// ---- PTX used only by the pair kernel (cta_group::2 / cluster forms)
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+}
+// this CTA's box -> its own shared memory; bytes complete on the LEADER's mbarrier (cluster address)
+__device__ __forceinline__ void tma_load_2d_pair(uint32_t smem_dst, const CUtensorMap* m, uint32_t leader_bar,
+                                                 int32_t c0, int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_dst, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish_pair() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc_pair(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_bf16_ss_pair(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                                  uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate) : "memory");
+}
+// arrive (once all tcgen05 ops issued so far by this thread have retired) on the mbarrier at this
+// CTA-relative offset in every CTA of `cta_mask`
+__device__ __forceinline__ void umma_commit_pair_mcast(uint32_t bar, uint16_t cta_mask) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(bar), "h"(cta_mask) : "memory");
+}
+// 16 accumulator columns of one row -> C (bf16 or f32), 16-byte stores
+__device__ __forceinline__ void store16(void* C, int out_f32, int64_t off, const float* f) {
+  if (out_f32) {
+    float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(C) + off);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+  } else {
+    uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<nvc_bf16*>(C) + off);
+    dst[0] = pack8(f);
+    dst[1] = pack8(f + 8);
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
+                 void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total, int kb_per_split,
+                 int num_tiles, int n_tiles, int prefetch_w, long long* __restrict__ trace) {
+  // optional phase timestamps of CTA 0 (tools/gemm_microbench.py); NULL in production
+  const bool tr = trace != nullptr && blockIdx.x == 0;
+  pdl_trigger();
+  if (tr && threadIdx.x == 0) trace[0] = clock64();
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t bar_base = smem_base + kStages * kStageBytes;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
+  auto tmem_full_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
+  auto tmem_empty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
+  const uint32_t tmem_slot = bar_base + 8u * kNumBars;
+  volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * kStageBytes + kNumBars * 8);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t crank = ptx::cluster_ctarank();
+  uint32_t csize;
+  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(csize));
+  const int S = (int)(csize >> 1);              // k-splits sharing one output tile
+  const int p = (int)(crank >> 1);              // this pair's split
+  const int h = (int)(crank & 1u);              // half of the tile rows (A) / of the tile columns (W)
+  const uint32_t leader_rank = crank & ~1u;
+  const uint16_t pair_mask = (uint16_t)(3u << leader_rank);
+  const int cluster_id = blockIdx.x / csize;
+  const int num_clusters = gridDim.x / csize;
+  const int kb_begin = p * kb_per_split;
+  const int num_kb = min(kb_per_split, k_blocks_total - kb_begin);
+
+  if (warp == 0 && lane == 0) {
+    ptx::tma_prefetch_desc(&tma_a);
+    ptx::tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int s = 0; s < kStages; ++s) {
+        ptx::mbar_init(full_bar(s), 1);     // the leader's arrive.expect_tx; bytes of BOTH CTAs complete on the leader's barrier
+        ptx::mbar_init(empty_bar(s), 1);    // the leader's tcgen05.commit, multicast to both CTAs
+      }
+      for (int a = 0; a < 2; ++a) {
+        ptx::mbar_init(tmem_full_bar(a), 1);    // leader's commit after the last k-block of a tile (multicast)
+        ptx::mbar_init(tmem_empty_bar(a), 8);   // 4 epilogue warps x 2 CTAs, on the leader's barrier
+      }
+      ptx::fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc_pair(tmem_slot, kTmemCols);
+    tmem_relinquish_pair();
+  }
+  ptx::tcgen05_fence_before();
+  __syncthreads();
+  ptx::tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot_gen;
+  ptx::cluster_sync_all();       // every CTA's barriers exist before a peer's TMA / commit / arrive targets them
+  if (tr && threadIdx.x == 0) trace[1] = clock64();
+
+  // weights are never written by a kernel: pull this CTA's first k-blocks of W into L2 while the
+  // predecessor is still running (decode only; the persistent schedule streams anyway)
+  constexpr int kPrefetchKb = 16;
+  if (warp == 0 && prefetch_w && cluster_id < num_tiles) {
+    if (ptx::elect_one()) {
+      const int n_tile = cluster_id % n_tiles;
+      const int n = min(num_kb, kPrefetchKb);
+      for (int kb = 0; kb < n; ++kb) ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, n_tile * kTileN + h * kHalf);
+    }
+    __syncwarp();
+  }
+  pdl_wait();
+  if (tr && threadIdx.x == 0) trace[2] = clock64();
+
+  if (warp == 0) {
+    // ------------------------------------------------------------ TMA producer (both CTAs)
+    const uint32_t leader_full0 = ptx::mapa_u32(full_bar(0), leader_rank);
+    uint32_t it = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      const int m_tile = tile / n_tiles, n_tile = tile - m_tile * n_tiles;
+      const int a_row = m_tile * kTileM + h * kHalf;
+      const int b_row = n_tile * kTileN + h * kHalf;
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int s = it % kStages;
+        if (it >= kStages) ptx::mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1u);   // first lap: slots are free
+        if (ptx::elect_one()) {
+          if (h == 0) ptx::mbar_arrive_expect_tx(full_bar(s), 2 * kStageBytes);
+          const uint32_t dst = smem_base + s * kStageBytes;
+          const int k0 = (kb_begin + kb) * BK;
+          tma_load_2d_pair(dst, &tma_a, leader_full0 + 8u * s, k0, a_row);
+          tma_load_2d_pair(dst + kBytesA, &tma_b, leader_full0 + 8u * s, k0, b_row);
+          if (prefetch_w && kb + kPrefetchKb < num_kb)
+            ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb + kPrefetchKb) * BK, b_row);
+          if (tr && it < 32) trace[3 + it] = clock64();
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1 && h == 0) {
+    // ------------------------------------------------------------ MMA issuer (leader CTA of the pair)
+    constexpr uint32_t idesc = ptx::umma_idesc_bf16(kTileM, kTileN, 0, 0);
+    constexpr uint32_t desc_hi = ptx::umma_desc_hi_sw128(1024);
+    const uint32_t a_lo0 = ptx::umma_desc_lo(smem_base, 16);
+    uint32_t it = 0;
+    int ti = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
+      const int acc = ti & 1, use = ti >> 1;
+      ptx::mbar_wait(tmem_empty_bar(acc), (use & 1) ^ 1u);    // both CTAs' epilogues drained this accumulator
+      ptx::tcgen05_fence_after();
+      const uint32_t d = tmem_base + (uint32_t)(acc * kTileN);
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int s = it % kStages;
+        ptx::mbar_wait(full_bar(s), (it / kStages) & 1);
+        ptx::tcgen05_fence_after();
+        if (ptx::elect_one()) {
+          if (tr && it < 32) trace[40 + it] = clock64();
+          const uint32_t a_lo = a_lo0 + s * (kStageBytes >> 4);
+          const uint32_t b_lo = a_lo + (kBytesA >> 4);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k)
+            umma_bf16_ss_pair(d, ptx::umma_desc(a_lo + 2 * k, desc_hi), ptx::umma_desc(b_lo + 2 * k, desc_hi), idesc,
+                              (kb | k) != 0 ? 1u : 0u);
+          umma_commit_pair_mcast(empty_bar(s), pair_mask);                             // stage reusable in both CTAs
+          if (kb == num_kb - 1) umma_commit_pair_mcast(tmem_full_bar(acc), pair_mask);  // accumulator complete
+          if (tr && kb == num_kb - 1 && ti == 0) trace[80] = clock64();
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 2 && S == 1) {
+    // ------------------------------------------------------------ epilogue, persistent schedule
+    const int q = warp & 3;                 // TMEM lane quadrant this warp may access
+    const int r = q * 32 + lane;
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t leader_tmem_empty0 = ptx::mapa_u32(tmem_empty_bar(0), leader_rank);
+    int ti = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
+      const int m_tile = tile / n_tiles, n_tile = tile - m_tile * n_tiles;
+      const int acc = ti & 1, use = ti >> 1;
+      const int grow = m_tile * kTileM + h * kHalf + r;
+      const bool row_ok = grow < M;
+      ptx::mbar_wait(tmem_full_bar(acc), use & 1);
+      ptx::tcgen05_fence_after();
+      if (tr && threadIdx.x == 64 && ti == 0) trace[81] = clock64();
+#pragma unroll 1
+      for (int c = 0; c < kTileN / 32; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)(acc * kTileN + c * 32), v);
+        ptx::tmem_ld_wait();
+        const int n0 = n_tile * kTileN + c * 32;
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+        if (row_ok && n0 < N) store16(C, out_f32, (int64_t)grow * ldc + n0, f);
+        if (row_ok && n0 + 16 < N) store16(C, out_f32, (int64_t)grow * ldc + n0 + 16, f + 16);
+      }
+      ptx::tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cluster(leader_tmem_empty0 + 8u * acc);
+      if (tr && threadIdx.x == 64 && ti == 0) trace[83] = clock64();
+    }
+  }
+
+  if (S > 1) {
+    // ------------------------------------------------------------ split-K exchange over DSMEM (one tile per cluster)
+    const int tile = cluster_id;
+    const int m_tile = tile / n_tiles, n_tile = tile - m_tile * n_tiles;
+    const int q = warp & 3;
+    const int r = q * 32 + lane;
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t dump = smem_base;        // the operand ring is idle once the accumulator is complete
+    if (warp >= 2) {
+      ptx::mbar_wait(tmem_full_bar(0), 0);  // all MMAs of this pair have retired: nothing reads the ring any more
+      ptx::tcgen05_fence_after();
+      if (tr && threadIdx.x == 64) trace[81] = clock64();
+      ptx::fence_proxy_async_smem();
+#pragma unroll 1
+      for (int c = 0; c < kTileN / 16; ++c) {
+        if (c % S == p) continue;           // my chunks stay in tensor memory
+        uint32_t v[16];
+        ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(c * 16), v);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          ptx::st_shared_f4(dump + (uint32_t)(((c * 4 + j) * kHalf + r) * 16), __uint_as_float(v[4 * j]),
+                       __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+      }
+    }
+    if (tr && threadIdx.x == 64) trace[82] = clock64();
+    ptx::cluster_sync_all();                // every partial is parked (release / acquire at cluster scope)
+    if (tr && threadIdx.x == 64) trace[85] = clock64();
+    if (warp >= 2) {
+      const int grow = m_tile * kTileM + h * kHalf + r;
+      const bool row_ok = grow < M;
+#pragma unroll 1
+      for (int c = p; c < kTileN / 16; c += S) {
+        uint32_t v[16];
+        ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(c * 16), v);
+        ptx::tmem_ld_wait();
+        // all peers' copies of this chunk are requested before the first add (one DSMEM round trip per chunk)
+        float4 t[3][4];
+        const uint32_t off = dump + (uint32_t)((c * 4 * kHalf + r) * 16);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+          const int z = i + (i >= p ? 1 : 0);         // the i-th split that is not mine
+          if (i < S - 1) {
+            const uint32_t peer = ptx::mapa_u32(off, (uint32_t)(2 * z + h));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) t[i][j] = ptx::ld_cluster_f4(peer + (uint32_t)(j * kHalf * 16));
+          }
+        }
+        float f[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) f[j] = 0.f;
+#pragma unroll
+        for (int z = 0; z < 4; ++z) {       // split order 0..S-1 whoever reduces: deterministic
+          if (z < S) {
+            if (z == p) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) f[j] += __uint_as_float(v[j]);
+            } else {
+              const int i = z - (z > p ? 1 : 0);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                // i is not a compile-time constant: select among the (at most 3) register batches
+                const float4 q4 = i == 0 ? t[0][j] : (i == 1 ? t[1][j] : t[2][j]);
+                f[4 * j] += q4.x; f[4 * j + 1] += q4.y; f[4 * j + 2] += q4.z; f[4 * j + 3] += q4.w;
+              }
+            }
+          }
+        }
+        const int n0 = n_tile * kTileN + c * 16;
+        if (row_ok && n0 < N) store16(C, out_f32, (int64_t)grow * ldc + n0, f);
+      }
+      if (tr && threadIdx.x == 64) trace[83] = clock64();
+    }
+  }
+  ptx::tcgen05_fence_before();
+  ptx::cluster_sync_all();       // nobody exits (or frees tensor memory) while a peer may still read its smem / signal its barriers
+  if (warp == 1) {
+    ptx::tcgen05_fence_after();
+    tmem_dealloc_pair(tmem_base, kTmemCols);
+  }
+  if (tr && threadIdx.x == 0) trace[84] = clock64();
+}
+
+int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner, uint64_t rows,
+                uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_rows) {
+  cuuint64_t gdim[2] = {inner, rows};
+  cuuint64_t gstr[1] = {row_stride_bytes};
+  cuuint32_t box[2] = {box_inner, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = ctx->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstr, box,
+                                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    nvc_set_error(ctx, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+    return NVC_EINVAL;
+  }
+  return NVC_OK;
+}
+
+}  // namespace
+
+// Co-resident clusters of 2S CTAs (S = 1..4), measured once per context: the schedule model needs
+// them (cluster placement is per GPC, so 148 SMs do not hold 148 / (2S) clusters for every S).
+extern "C" int nvc_gemm_pair_init(nvc_ctx* ctx) {
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  for (int S = 1; S <= 4; ++S) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(2 * S * 64);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = kSmemBytes;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2 * S;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    int n = 0;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel, &cfg);
+    if (e != cudaSuccess || n <= 0) {
+      (void)cudaGetLastError();
+      n = ctx->num_sms / (2 * S);
+    }
+    ctx->pair_clusters[S] = n;
+  }
+  if (getenv("NVC_DEBUG"))
+    fprintf(stderr, "nvc: pair GEMM co-resident clusters of 2/4/6/8 CTAs: %d %d %d %d\n", ctx->pair_clusters[1],
+            ctx->pair_clusters[2], ctx->pair_clusters[3], ctx->pair_clusters[4]);
+  return NVC_OK;
+}
+
+// Schedule choice: persistent (S = 1) when the tiles fill the pairs; otherwise split K inside a
+// cluster so that ~all SMs stream weights.  Cycle model: a k-block costs 512 tensor cycles per
+// pair; a CTA pays ~3000 cycles of prologue / first-load latency / epilogue, the DSMEM exchange
+// ~2500 more.
+static int choose_splits(const nvc_ctx* ctx, int tiles, int kb) {
+  double best = 1e30;
+  int best_s = 1;
+  for (int S = 1; S <= 4; ++S) {
+    if (S > kb) break;
+    const int avail = ctx->pair_clusters[S] > 0 ? ctx->pair_clusters[S] : ctx->num_sms / (2 * S);
+    const double waves = ceil((double)tiles / avail);
+    const double kbs = ceil((double)kb / S);
+    const double t = S == 1 ? waves * kbs * 512.0 + 3500.0 : waves * (kbs * 512.0 + 5500.0);
+    if (t < best * 0.97) { best = t; best_s = S; }
+  }
+  return best_s;
+}
+
+extern "C" int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32,
+                             int M, int N, int K, int force_splits, void* stream, long long* trace) {
+  CUtensorMap ta, tb;
+  int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, kHalf);
+  if (rc) return rc;
+  rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, kHalf);
+  if (rc) return rc;
+  const int kb_total = K / BK;
+  const int m_tiles = (M + kTileM - 1) / kTileM, n_tiles = (N + kTileN - 1) / kTileN;
+  const int tiles = m_tiles * n_tiles;
+  int S = force_splits > 0 ? force_splits : choose_splits(ctx, tiles, kb_total);
+  if (S > 4) S = 4;
+  if (S > kb_total) S = kb_total;
+  int kb_per = (kb_total + S - 1) / S;
+  S = (kb_total + kb_per - 1) / kb_per;      // no empty splits
+  int clusters = tiles;
+  if (S == 1) {
+    const int avail = ctx->pair_clusters[1] > 0 ? ctx->pair_clusters[1] : ctx->num_sms / 2;
+    // equal tiles per cluster where possible: ceil(tiles / waves) clusters, not a ragged last wave
+    const int waves = (tiles + avail - 1) / avail;
+    clusters = (tiles + waves - 1) / waves;
+  }
+  dim3 grid(clusters * 2 * S);
+  NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, gemm_pair_kernel, grid, dim3(kThreads), kSmemBytes, nvc_stream(stream),
+                                         2 * S, ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, tiles, n_tiles,
+                                         (M <= kTileM) ? 1 : 0, trace));
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
+  return NVC_OK;
+}

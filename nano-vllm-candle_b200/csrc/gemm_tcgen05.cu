@@ -24,6 +24,9 @@
 
 static int g_nvc_gemm_prefetch = getenv("NVC_GEMM_PREFETCH") ? atoi(getenv("NVC_GEMM_PREFETCH")) : 1;
 
+static int g_nvc_gemm_ks = getenv("NVC_GEMM_KS") ? atoi(getenv("NVC_GEMM_KS")) : 1;
+static int g_nvc_gemm_pair = getenv("NVC_GEMM_PAIR") ? atoi(getenv("NVC_GEMM_PAIR")) : 1;
+
 namespace {
 
 constexpr int BM = 128;
@@ -54,7 +57,7 @@ template <int BN, int KPS, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total,
-                         int k_blocks_per_split, int a_box_rows, int prefetch_w, float* __restrict__ ws,
+                         int k_blocks_per_split, int a_box_rows, int prefetch_w, int ks_cluster, float* __restrict__ ws,
                          int* __restrict__ counters, long long* __restrict__ trace) {
   using cfg = Cfg<BN, KPS>;
   // optional phase timestamps of CTA (0,0,0) (tools/gemm_microbench.py); NULL in production
@@ -237,6 +240,20 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           }
         }
       }
+    } else if (ks_cluster) {
+      // ---- split-K inside a cluster (1,1,S): park this CTA's fp32 partial tile in its own, now idle,
+      // operand ring as [float4 column group][row] (conflict-free); summed after the cluster barrier below
+      ptx::fence_proxy_async_smem();
+#pragma unroll 1
+      for (int c = 0; c < BN / 16; ++c) {
+        uint32_t v[16];
+        ptx::tmem_ld_32x32b_x16(taddr + c * 16, v);
+        ptx::tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          ptx::st_shared_f4(smem_base + (uint32_t)(((c * 4 + j) * BM + r) * 16), __uint_as_float(v[4 * j]),
+                            __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+      }
     } else {
       // ---- split-K: publish the partial, last arriver reduces in split order
       float* my = ws + ((int64_t)tile_id * num_splits + split) * (BM * BN) + (int64_t)r * BN;
@@ -300,11 +317,47 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         if (threadIdx.x == 64) counters[tile_id] = 0;   // re-arm for the next launch
       }
     }
-    if (tr && threadIdx.x == 64) trace[82] = clock64();
+    if (tr && threadIdx.x == 64 && !ks_cluster) trace[82] = clock64();
     ptx::tcgen05_fence_before();
   }
+  if (ks_cluster) {
+    // Distributed-shared-memory reduction: CTA `split` of the cluster owns the float4 column groups
+    // g with g % S == split and sums them over the S partial tiles in split order (deterministic);
+    // no global workspace, no atomics.
+    ptx::cluster_sync_all();             // all partials parked (release / acquire at cluster scope)
+    if (warp >= 2) {
+      const int r = (warp & 3) * 32 + lane;
+      const int grow = m_tile * BM + r;
+      if (grow < M) {
+        for (int g = split; g < BN / 4; g += num_splits) {
+          const int n0 = n_tile * BN + g * 4;
+          if (n0 >= N) break;
+          const uint32_t mine = smem_base + (uint32_t)((g * BM + r) * 16);
+          // request every split's copy before the first add: one DSMEM round trip per column group
+          float4 t[8];
+#pragma unroll
+          for (int z = 0; z < 8; ++z)
+            if (z < num_splits) t[z] = ptx::ld_cluster_f4(ptx::mapa_u32(mine, (uint32_t)z));
+          float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int z = 0; z < 8; ++z)
+            if (z < num_splits) { acc.x += t[z].x; acc.y += t[z].y; acc.z += t[z].z; acc.w += t[z].w; }
+          const int64_t o = (int64_t)grow * ldc + n0;
+          if (out_f32) {
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(C) + o) = acc;
+          } else {
+            uint2 pk;
+            pk.x = pack_bf16(acc.x, acc.y);
+            pk.y = pack_bf16(acc.z, acc.w);
+            *reinterpret_cast<uint2*>(reinterpret_cast<nvc_bf16*>(C) + o) = pk;
+          }
+        }
+      }
+      if (tr && threadIdx.x == 64) trace[82] = clock64();
+    }
+  }
   __syncthreads();
-  if (CL > 1) ptx::cluster_sync_all();   // nobody exits while a peer may still arrive on its barriers
+  if (CL > 1 || ks_cluster) ptx::cluster_sync_all();   // nobody exits while a peer may still arrive on its barriers / read its smem
   if (warp == 1) {
     ptx::tcgen05_fence_after();
     ptx::tmem_dealloc(tmem_base, cfg::kTmemCols);
@@ -330,7 +383,7 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
 
 template <int BN, int KPS, int CL>
 int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M,
-           int N, int K, int splits, cudaStream_t stream, long long* trace) {
+           int N, int K, int splits, int ks_cluster, cudaStream_t stream, long long* trace) {
   using cfg = Cfg<BN, KPS>;
   CUtensorMap ta, tb;
   // a single partial m-tile only needs the rows that exist (rounded to the 8-row swizzle atom per
@@ -346,10 +399,14 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
   const int n_tiles = (N + BN - 1) / BN;
   NVC_REQUIRE(ctx, n_tiles % CL == 0, NVC_ESHAPE, "n-tiles must divide by the cluster size");
   dim3 grid(n_tiles, (M + BM - 1) / BM, eff_splits);
-  NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, gemm_bf16_tcgen05_kernel<BN, KPS, CL>, grid, dim3(kThreads), cfg::kSmemBytes,
-                                         stream, CL, ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, a_rows / CL,
-                                         (g_nvc_gemm_prefetch && M <= BM) ? 1 : 0,   // helps latency-bound decode, hurts M >= 256
-                                         ctx->gemm_ws, ctx->gemm_counters, trace));
+  // ks_cluster: the eff_splits CTAs of one output tile form a cluster (1,1,S) and reduce over DSMEM
+  const int ks = (ks_cluster && CL == 1 && eff_splits > 1 && eff_splits <= 8) ? 1 : 0;
+  NVC_REQUIRE(ctx, !ks || (size_t)BN * BM * 4 <= (size_t)cfg::kStages * cfg::kStageBytes, NVC_EINVAL, "ring too small for the partial tile");
+  NVC_CUDA_CHECK(ctx, nvc_launch_cluster3(ctx, gemm_bf16_tcgen05_kernel<BN, KPS, CL>, grid, dim3(kThreads), cfg::kSmemBytes,
+                                          stream, dim3(CL, 1, ks ? eff_splits : 1), ta, tb, C, ldc, out_f32, M, N, kb_total,
+                                          kb_per, a_rows / CL,
+                                          (g_nvc_gemm_prefetch && M <= BM) ? 1 : 0,   // helps latency-bound decode, hurts M >= 256
+                                          ks, ctx->gemm_ws, ctx->gemm_counters, trace));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -369,9 +426,25 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
 //  * decode (M <= 128): one wave, as many CTAs as the N dimension gives (up to ~all SMs), several
 //    k-blocks per pipeline stage; split-K through the L2 workspace costs >= 6 us (ticket atomic +
 //    reduction round trips) and never won in the sweep, so it is only used when forced.
-void choose_config(const nvc_ctx* ctx, int M, int N, int K, int* bn_out, int* kps_out, int* splits_out, int* cl_out) {
+void choose_config(const nvc_ctx* ctx, int M, int N, int K, int* bn_out, int* kps_out, int* splits_out, int* cl_out,
+                   int* ks_out) {
   *splits_out = 1;
   *cl_out = 1;
+  *ks_out = 0;
+  if (M <= BM && g_nvc_gemm_ks && (N + 31) / 32 <= 48 && K >= 1024) {
+    // narrow, deep decode GEMM (o_proj / down_proj of the small models): too few n-tiles to stream the
+    // weights from more than ~32 SMs -> split K inside clusters (1,1,S), partials reduced over DSMEM
+    const int tiles = (N + 31) / 32;
+    int s = 8;
+    while (s > 1 && (tiles * s > 160 || K / BK / s < 4)) s >>= 1;
+    if (s > 1) {
+      *bn_out = 32;
+      *kps_out = 4;
+      *splits_out = s;
+      *ks_out = 1;
+      return;
+    }
+  }
   if (M <= BM) {
     int bn = 32;
     const int cands[3] = {256, 128, 64};
@@ -424,26 +497,34 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
               "pointers must be 16-byte aligned");
   NVC_REQUIRE(ctx, ctx->encode_tiled != nullptr, NVC_EDEVICE, "cuTensorMapEncodeTiled unavailable");
   if (M == 0) return NVC_OK;
-  int bn, kps, splits, cl = 1;
-  choose_config(ctx, M, Nout, K, &bn, &kps, &splits, &cl);
+  // M > 128: CTA-pair kernel (gemm_pair.cu); force_bn = 512 selects it explicitly, any other force_bn the 1-CTA tiles
+  if (force_bn == 512 || (force_bn == 0 && M > BM && g_nvc_gemm_pair))
+    return nvc_gemm_pair(ctx, A, lda, W, C, ldc, out_dtype == NVC_DT_F32, M, Nout, K, force_splits, stream, trace);
+  int bn, kps, splits, cl = 1, ks = 0;
+  choose_config(ctx, M, Nout, K, &bn, &kps, &splits, &cl, &ks);
   if (force_bn) {          // force_bn = BN + 1000 * KPS + 10000 * CL (KPS 0: the first instantiation of that BN)
     bn = force_bn % 1000;
     kps = (force_bn / 1000) % 10;
     cl = force_bn / 10000;
     if (cl == 0) cl = 1;
     if (kps == 0) kps = bn >= 128 ? 1 : (bn == 64 ? 2 : 4);
+    ks = 0;
+    splits = 1;
   }
-  if (force_splits) splits = force_splits;
+  // force_splits: 1..99 = split-K through the global workspace; 100 + S = split-K inside a cluster (1,1,S), S <= 8
+  if (force_splits >= 100) { splits = force_splits - 100; ks = 1; cl = 1; }
+  else if (force_splits) { splits = force_splits; ks = 0; }
+  NVC_REQUIRE(ctx, !ks || splits <= 8, NVC_EINVAL, "cluster split-K supports at most 8 splits");
   if (splits > K / BK) splits = K / BK;
   const int tiles = ((M + BM - 1) / BM) * ((Nout + bn - 1) / bn);
-  if (splits > 1) {
+  if (splits > 1 && !ks) {
     NVC_REQUIRE(ctx, (size_t)tiles * splits * BM * bn * 4 <= ctx->gemm_ws_bytes && tiles <= ctx->gemm_num_counters,
                 NVC_ENOMEM, "split-K workspace too small");
   }
   cudaStream_t st = nvc_stream(stream);
   const int f32 = out_dtype == NVC_DT_F32;
 #define X(BN, KPS, CL) \
-  if (bn == BN && kps == KPS && cl == CL) return launch<BN, KPS, CL>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, st, trace);
+  if (bn == BN && kps == KPS && cl == CL) return launch<BN, KPS, CL>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, ks, st, trace);
   NVC_GEMM_CONFIGS(X)
 #undef X
   NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported tile configuration");

@@ -47,6 +47,30 @@ GEMM_SHAPES = [
     (256, 2048, 512, 21256, 1),    # BN=256 cluster of 2
     (256, 6144, 4096, 0, 0),       # 8B qkv at batch 256
     (2048, 1024, 1024, 0, 0),      # prefill-sized
+    # split-K inside a cluster (1,1,S), partial tiles reduced over distributed shared memory: force_splits = 100 + S
+    (64, 1024, 2048, 4032, 104),   # 0.6B o_proj: BN=32, 4 splits of 8 k-blocks
+    (64, 1024, 3072, 4032, 104),   # 0.6B down_proj
+    (64, 1024, 2048, 2064, 108),   # BN=64, cluster of 8
+    (1, 1024, 1024, 4032, 104),    # M = 1
+    (100, 2000, 1088, 4032, 104),  # ragged N, 17 k-blocks (5+5+5+2)
+    (128, 512, 4096, 2128, 102),   # BN=128, 2 splits
+    (64, 1024, 2048, 1256, 103),   # BN=256 (128 KB partial tile in the ring), 3 splits
+    # CTA-pair kernel (gemm_pair.cu): force_bn = 512, force_splits = in-cluster split-K factor (0 = auto)
+    (256, 256, 64, 512, 1),        # one pair tile, one k-block
+    (129, 256, 64, 512, 1),        # second CTA of the pair holds a single valid row
+    (128, 256, 128, 512, 1),       # second CTA's activation box entirely out of bounds (zero-filled)
+    (256, 512, 1024, 512, 1),      # ring wraps (16 k-blocks > 6 stages)
+    (300, 1040, 192, 512, 1),      # ragged M and N (N % 16 == 0 only)
+    (4096, 2048, 512, 512, 1),     # 128 tiles: persistent, two tiles per cluster (both accumulators)
+    (8192, 4096, 256, 512, 1),     # 512 tiles: ~7 per cluster, accumulator + ring phases wrap
+    (256, 4096, 4096, 512, 4),     # 8B o_proj at batch 256: split-K 4 in clusters of 8, DSMEM exchange
+    (256, 6144, 4096, 512, 3),     # 8B qkv: split 3 (uneven k ranges 22/22/20), clusters of 6
+    (256, 4096, 12288, 512, 4),    # 8B down_proj
+    (256, 24576, 4096, 512, 2),    # 8B gate_up: 96 tiles x 2 splits, several waves of clusters
+    (200, 784, 448, 512, 2),       # split 2, ragged M and N, 7 k-blocks (4 + 3)
+    (256, 512, 64, 512, 4),        # more splits than k-blocks: clamps to 1
+    (256, 4096, 4096, 512, 0),     # auto split choice
+    (512, 151936 // 8, 1024, 512, 0),   # lm_head shard, ragged last n-tile
 ]
 
 
@@ -83,6 +107,20 @@ def test_gemm_reference_goldens(ctx):
         ws = torch.zeros(16, 64); ws[:3, :4] = w[3 * r:3 * r + 3]
         o = ctx.gemm(xp.to(BF16).cuda(), ws.to(BF16).cuda(), out_dtype=torch.float32).cpu()
         assert torch.equal(o[:, :3] + bias[3 * r:3 * r + 3], want[:, 3 * r:3 * r + 3])
+
+
+def test_gemm_pair_split_determinism(ctx):
+    """in-cluster split-K sums the partials in split order whichever CTA reduces: bit-identical reruns"""
+    g = torch.Generator().manual_seed(11)
+    a = torch.randn(256, 4096, generator=g).to(BF16).cuda()
+    w = (torch.randn(4096, 4096, generator=g) / 64).to(BF16).cuda()
+    outs = [ctx.gemm(a, w, out_dtype=torch.float32, force_bn=512, force_splits=4) for _ in range(3)]
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
+    big = torch.randn(256, 3 * 1024, generator=g).to(BF16).cuda()
+    av = big[:, 1024:2048]                                   # row stride 3072
+    w2 = (torch.randn(512, 1024, generator=g) / 32).to(BF16).cuda()
+    ref = O.linear(av.float().cpu(), w2.float().cpu())
+    _close(ctx.gemm(av, w2, force_bn=512, force_splits=2), ref, 2e-3, 2 ** -8, "pair gemm strided split-K")
 
 
 def test_gemm_strided_input_and_determinism(ctx):

@@ -40,6 +40,30 @@ def bench(M, N, K, bn=0, splits=0, out_dtype=BF16, iters=20):
     return us, gbs, tf
 
 
+def bench_cublas(M, N, K, iters=20):
+    """torch.matmul (cuBLAS) on the same shapes with the same cold-weight rotation, for reference."""
+    ncopies = max(2, min(64, int(300e6 // (N * K * 2)) + 1))
+    a = torch.randn(M, K, device="cuda").to(BF16)
+    ws = [torch.randn(N, K, device="cuda").to(BF16) for _ in range(ncopies)]
+    out = torch.empty(M, N, device="cuda", dtype=BF16)
+    for w in ws[:2]:
+        torch.matmul(a, w.t(), out=out)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(iters):
+            torch.matmul(a, ws[i % ncopies].t(), out=out)
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    g.replay()
+    e1.record()
+    torch.cuda.synchronize()
+    us = e0.elapsed_time(e1) * 1e3 / iters
+    return us, 2.0 * M * N * K / us / 1e6
+
+
 def trace(M, N, K, bn, splits):
     a = torch.randn(M, K, device="cuda").to(BF16)
     w = torch.randn(N, K, device="cuda").to(BF16)
@@ -65,6 +89,32 @@ def trace(M, N, K, bn, splits):
     print("  kernel end        ", t[83] - t0)
 
 
+def trace_pair(M, N, K, splits):
+    a = torch.randn(M, K, device="cuda").to(BF16)
+    ws = [torch.randn(N, K, device="cuda").to(BF16) for _ in range(max(2, int(300e6 // (N * K * 2)) + 1))]
+    out = torch.empty(M, N, device="cuda", dtype=BF16)
+    t = torch.zeros(128, dtype=torch.int64, device="cuda")
+    for w in ws:       # the last launch reads cold weights
+        st = ctx.l.nvc_gemm_bf16_trace(ctx.h, C.c_void_p(a.data_ptr()), K, C.c_void_p(w.data_ptr()), C.c_void_p(out.data_ptr()),
+                                       N, 0, M, N, K, 512, splits, C.c_void_p(torch.cuda.current_stream().cuda_stream),
+                                       C.c_void_p(t.data_ptr()))
+        assert st == 0
+    torch.cuda.synchronize()
+    t = t.cpu().tolist()
+    t0 = t[0]
+    kb = min(32, K // 64 // max(splits, 1))
+    print(f"pair trace M={M} N={N} K={K} splits={splits} (cycles from kernel start, CTA 0)")
+    print("  cluster set up    ", t[1] - t0, " pdl wait done", t[2] - t0)
+    print("  tma issued  kb:   ", [t[3 + i] - t0 for i in range(kb)])
+    print("  full waited kb:   ", [t[40 + i] - t0 for i in range(kb)])
+    print("  mma all committed ", t[80] - t0)
+    print("  epilogue start    ", t[81] - t0)
+    if splits > 1:
+        print("  partials parked   ", t[82] - t0, " cluster barrier passed", t[85] - t0)
+    print("  epilogue end      ", t[83] - t0)
+    print("  kernel end        ", t[84] - t0)
+
+
 if __name__ == "__main__":
     print("M N K bn splits -> us, GB/s, TFLOP/s")
     if "--single" in sys.argv:      # one shape, a few plain launches (for ncu)
@@ -77,6 +127,40 @@ if __name__ == "__main__":
             ctx.gemm(a, w, out=out, force_bn=bn, force_splits=1)
         torch.cuda.synchronize()
         print("single ok")
+        sys.exit(0)
+    if "--pair" in sys.argv:        # CTA-pair kernel vs the best 1-CTA tiles vs cuBLAS, M > 128
+        shapes = [(256, 6144, 4096), (256, 4096, 4096), (256, 24576, 4096), (256, 4096, 12288), (256, 151936, 4096),
+                  (256, 4096, 1024), (256, 1024, 2048), (256, 6144, 1024), (256, 1024, 3072),
+                  (192, 4096, 4096), (512, 4096, 4096),
+                  (4096, 4096, 4096), (8192, 8192, 8192), (32768, 4096, 1024), (32768, 1024, 2048), (32768, 6144, 1024),
+                  (32768, 1024, 3072), (16384, 6144, 4096), (16384, 4096, 12288)]
+        for (M, N, K) in shapes:
+            us, tf = bench_cublas(M, N, K)
+            print(f"{M:6d} {N:6d} {K:6d} cuBLAS                 -> {us:9.2f} us {tf:8.1f} TF/s", flush=True)
+            for bn, sp in [(2064, 1), (2128, 1), (1256, 1), (512, 0), (512, 1), (512, 2), (512, 3), (512, 4)]:
+                if M > 512 and (bn == 2064 or sp > 1):
+                    continue
+                try:
+                    us, gbs, tf = bench(M, N, K, bn, sp)
+                    print(f"{M:6d} {N:6d} {K:6d} bn={bn % 1000:3d} kps={(bn // 1000) % 10} s={sp}        -> {us:9.2f} us {tf:8.1f} TF/s {gbs:8.1f} GB/s", flush=True)
+                except Exception as ex:
+                    print(f"{M} {N} {K} bn={bn} s={sp} failed: {ex}")
+        for sp in (1, 2, 3):
+            trace_pair(256, 4096, 4096, sp)
+        trace_pair(256, 24576, 4096, 1)
+        sys.exit(0)
+    if "--ks" in sys.argv:          # cluster split-K (DSMEM) for the narrow decode GEMMs vs the plain tiles vs cuBLAS
+        for (M, N, K) in [(64, 1024, 2048), (64, 1024, 3072), (64, 4096, 1024), (64, 6144, 1024), (1, 1024, 2048),
+                          (64, 4096, 4096), (64, 4096, 12288), (64, 6144, 4096), (64, 5120, 5120), (128, 1024, 3072)]:
+            us, tf = bench_cublas(M, N, K)
+            print(f"{M:6d} {N:6d} {K:6d} cuBLAS                 -> {us:9.2f} us {tf:8.1f} TF/s", flush=True)
+            for bn, sp in [(0, 0), (4032, 1), (4032, 102), (4032, 104), (4032, 108), (2064, 102), (2064, 104), (2064, 108),
+                           (2128, 102), (2128, 104), (2128, 108)]:
+                try:
+                    us, gbs, tf = bench(M, N, K, bn, sp)
+                    print(f"{M:6d} {N:6d} {K:6d} bn={bn % 1000:3d} kps={(bn // 1000) % 10} s={sp:3d}      -> {us:9.2f} us {tf:8.1f} TF/s {gbs:8.1f} GB/s", flush=True)
+                except Exception as ex:
+                    print(f"{M} {N} {K} bn={bn} s={sp} failed: {ex}")
         sys.exit(0)
     if "--trace-only" in sys.argv:
         trace(64, 4096, 1024, 4032, 1)

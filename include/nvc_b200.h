@@ -128,6 +128,15 @@ enum { NVC_DT_BF16 = 0, NVC_DT_F32 = 1 };
 int nvc_gemm_bf16(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
                   int out_dtype, int M, int Nout, int K, void* stream);
 
+/* K3 + K6 fused.  Replaces Qwen3MLP::forward's gate_up projection and SiluAndMul
+ * (src/models/qwen3.rs:323-327, src/layers/activation.rs:13-18) in one kernel:
+ *   act[M, I] = silu(A Wgate^T) * (A Wup^T),  silu(x) = x / (1 + exp(-x)) on the fp32 accumulators.
+ * W_gu16: bf16 [2I, K], the reference's fused [gate; up] rows (qwen3.rs:310) re-ordered in groups of
+ * 16 so that both halves of a feature meet in one epilogue thread: rows [32g, 32g+16) = gate rows
+ * [16g, 16g+16), rows [32g+16, 32g+32) = up rows [16g, 16g+16).  I % 16 == 0, K % 64 == 0. */
+int nvc_gemm_bf16_silu_mul(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W_gu16, nvc_bf16* act,
+                           int ldc, int M, int I, int K, void* stream);
+
 /* Host-side rope table: replaces RotaryEmbedding::build_cos_sin
  * (src/layers/rotary_embedding.rs:56-80), which the reference recomputes per call.
  * out: f32 [max_pos, head_dim]; row p = [cos(p*f_0..f_{hd/2-1}), sin(p*f_0..)], with

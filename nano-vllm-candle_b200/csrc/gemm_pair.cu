@@ -15,31 +15,53 @@
 //    overlaps the main loop of tile i+1.
 //  * S > 1, split-K inside a cluster of 2S CTAs (decode, M <= 256: too few tiles to fill 148
 //    SMs): pair p of the cluster takes k-blocks [p*kb_per, ...) of ONE tile; partial accumulators
-//    are exchanged through distributed shared memory (every CTA parks the 16-column chunks it
-//    does not own in its own, now idle, operand ring; CTA (p, h) sums chunk c, c % S == p, in
-//    split order 0..S-1: deterministic) - no global workspace, no atomics.
+//    are exchanged through an L2-resident workspace between two cluster barriers (every CTA
+//    publishes the 16-column chunks it does not own; CTA (p, h) sums chunk c, c % S == p, in
+//    split order 0..S-1: deterministic, no atomics).  Distributed shared memory was measured
+//    first and is too slow for 128 KB partial tiles (~17 B/clk per SM).
 // Roles per CTA (192 threads): warp 0 TMA producer, warp 1 TMEM allocator + MMA issuer (leader
 // only), warps 2-5 epilogue (tcgen05.ld -> bf16/f32 -> 16-byte stores).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "internal.h"
+#include "gemm_epilogue.cuh"
 
 #include <cmath>
 #include <cstdlib>
 
 namespace {
 
-constexpr int kTileM = 256, kTileN = 256, kHalf = 128, BK = 64;
+constexpr int kTileM = 256, kHalf = 128, BK = 64;
 constexpr int kThreads = 192;
-constexpr int kStages = 6;
 constexpr int kBytesA = kHalf * BK * 2;            // 16 KB: this CTA's 128 rows of the activation tile
-constexpr int kBytesB = kHalf * BK * 2;            // 16 KB: this CTA's 128 rows (N half) of the weight tile
-constexpr int kStageBytes = kBytesA + kBytesB;
-constexpr int kNumBars = 2 * kStages + 4;          // full[6], empty[6], tmem_full[2], tmem_empty[2]
-constexpr int kSmemBytes = kStages * kStageBytes + kNumBars * 8 + 16 + 1024;
 constexpr int kTmemCols = 512;
-constexpr int kDumpBytes = 16 * 4 * kHalf * 16;    // 128 KB: [chunk 16][float4 4][row 128] fp32 partials
-static_assert(kDumpBytes <= kStages * kStageBytes, "the partial-accumulator dump reuses the operand ring");
+constexpr int kRingBudget = 200 * 1024;
+
+// Tile width NT.  NT = 256: one MMA (N = 256) per k-step, two accumulator stages (persistent
+// schedule overlaps the epilogue).  NT in (256, 512]: two MMAs of N = NT/2 per k-step into
+// tensor-memory columns [0, NT/2) and [256, 256 + NT/2), one accumulator stage - used when a
+// decode GEMM has between #pairs and 2 x #pairs 256-wide tiles, so that wider tiles finish in ONE
+// wave (Qwen3-8B gate_up at batch 256: 96 tiles of 256 -> 70 tiles of 352 on 74 pairs).
+template <int NT>
+struct PairCfg {
+  static_assert(NT == 256 || (NT > 256 && NT <= 512 && NT % 32 == 0), "tile width");
+  static constexpr bool kTwo = NT > 256;
+  static constexpr int NH = kTwo ? NT / 2 : NT;          // N of one tcgen05.mma
+  static constexpr int kBoxRowsB = NH / 2;               // rows of W one CTA supplies per MMA (multiple of 8)
+  static constexpr int kBytesB = (NT / 2) * BK * 2;      // this CTA's rows of the weight tile per k-block
+  static constexpr int kStageBytes = kBytesA + kBytesB;
+  static constexpr int kStages = kRingBudget / kStageBytes < 6 ? kRingBudget / kStageBytes : 6;
+  static constexpr int kAccStages = kTwo ? 1 : 2;
+  static constexpr int kNumBars = 2 * kStages + 4;       // full[], empty[], tmem_full[2], tmem_empty[2]
+  static constexpr int kSmemBytes = kStages * kStageBytes + kNumBars * 8 + 16 + 1024;
+  static constexpr int kChunks = NT / 16;                // 16-column accumulator chunks of a tile
+  static constexpr int kPartF4 = kChunks * 4 * kHalf;    // float4s of one CTA's partial tile in the split-K workspace
+  static_assert(kStageBytes % 1024 == 0 && (kBoxRowsB % 8) == 0, "swizzle atoms");
+  // tensor-memory column of accumulator chunk c (accumulator stage 0)
+  __device__ static constexpr uint32_t chunk_col(int c) {
+    return kTwo && c * 16 >= NH ? (uint32_t)(256 + c * 16 - NH) : (uint32_t)(c * 16);
+  }
+};
 
 // ---- PTX used only by the pair kernel (cta_group::2 / cluster forms)
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
@@ -75,23 +97,93 @@ __device__ __forceinline__ void umma_commit_pair_mcast(uint32_t bar, uint16_t ct
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
                ::"r"(bar), "h"(cta_mask) : "memory");
 }
-// 16 accumulator columns of one row -> C (bf16 or f32), 16-byte stores
-__device__ __forceinline__ void store16(void* C, int out_f32, int64_t off, const float* f) {
-  if (out_f32) {
-    float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(C) + off);
+// Split-K exchange, executed by the 4 epilogue warps of every CTA of a cluster of 2S CTAs between
+// two cluster barriers.  Partial accumulators go through an L2-resident workspace, not distributed
+// shared memory (DSMEM moves ~17 B/clk per SM: measured 7.4k cycles for a 128 x 256 fp32 tile).
+// Workspace layout per CTA: [chunk][float4 4][row 128], so a warp's 32 rows are 512 contiguous bytes.
+// Ownership is per 32-column unit (two chunks: what the fused SiLU-mul epilogue needs in one thread):
+// CTA (p, h) owns the units u with u % S == p and sums them in split order 0..S-1 (deterministic).
+template <int NT, int S>
+__device__ __forceinline__ void pair_publish(float4* __restrict__ my_ws, uint32_t taddr, int p, int r) {
+  using cfg = PairCfg<NT>;
+#pragma unroll 1
+  for (int u = 0; u < cfg::kChunks / 2; ++u) {
+    if (u % S == p) continue;           // my units stay in tensor memory
+    uint32_t v[32];
+    ptx::tmem_ld_32x32b_x16(taddr + cfg::chunk_col(2 * u), v);
+    ptx::tmem_ld_32x32b_x16(taddr + cfg::chunk_col(2 * u + 1), v + 16);
+    ptx::tmem_ld_wait();
 #pragma unroll
-    for (int j = 0; j < 4; ++j) dst[j] = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-  } else {
-    uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<nvc_bf16*>(C) + off);
-    dst[0] = pack8(f);
-    dst[1] = pack8(f + 8);
+    for (int j = 0; j < 8; ++j)
+      __stcg(my_ws + (u * 8 + j) * kHalf + r, make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
+                                                         __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3])));
   }
 }
 
+template <int NT, int S>
+__device__ __forceinline__ void pair_reduce(const float4* __restrict__ ws_cluster, uint32_t taddr, int p, int h, int r,
+                                            void* __restrict__ C, int out_f32, int epi, int64_t row_off, bool row_ok,
+                                            int n_base, int N) {
+  using cfg = PairCfg<NT>;
+  constexpr int kUnits = cfg::kChunks / 2;
+  // G units per batch: 16-24 independent 16-byte L2 loads in flight per thread (one round trip per batch)
+  constexpr int G = S == 2 ? 3 : 1;
+  constexpr int kOwnedMax = (kUnits + S - 1) / S;
+#pragma unroll 1
+  for (int k0 = 0; k0 < kOwnedMax; k0 += G) {
+    float4 t[G][S - 1][8];
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const int u = min(p + (k0 + g) * S, kUnits - 1);       // clamped: a redundant load instead of a branch
+#pragma unroll
+      for (int i = 0; i < S - 1; ++i) {
+        const int z = i + (i >= p ? 1 : 0);                  // the i-th split that is not mine
+        const float4* peer = ws_cluster + (size_t)(2 * z + h) * cfg::kPartF4 + u * 8 * kHalf + r;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[g][i][j] = __ldcg(peer + j * kHalf);
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < G; ++g) {
+      const int u = p + (k0 + g) * S;
+      if (u < kUnits) {                   // uniform over the CTA
+        uint32_t v[32];
+        ptx::tmem_ld_32x32b_x16(taddr + cfg::chunk_col(2 * u), v);
+        ptx::tmem_ld_32x32b_x16(taddr + cfg::chunk_col(2 * u + 1), v + 16);
+        ptx::tmem_ld_wait();
+        float f[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) f[j] = 0.f;
+        // split order 0..S-1 whoever reduces: peers i < p are splits 0..p-1, then mine, then splits p+1..
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+          if (i == p) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) f[j] += __uint_as_float(v[j]);
+          }
+          if (i < S - 1) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              f[4 * j] += t[g][i][j].x; f[4 * j + 1] += t[g][i][j].y;
+              f[4 * j + 2] += t[g][i][j].z; f[4 * j + 3] += t[g][i][j].w;
+            }
+          }
+        }
+        if (row_ok) emit32(C, out_f32, epi, row_off, n_base + u * 32, N, f);
+      }
+    }
+  }
+}
+
+template <int NT>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total, int kb_per_split,
-                 int num_tiles, int n_tiles, int prefetch_w, long long* __restrict__ trace) {
+                 int num_tiles, int n_tiles, int prefetch_w, int epi, float4* __restrict__ ws,
+                 long long* __restrict__ trace) {
+  using cfg = PairCfg<NT>;
+  constexpr int kStages = cfg::kStages;
+  constexpr int kStageBytes = cfg::kStageBytes;
   // optional phase timestamps of CTA 0 (tools/gemm_microbench.py); NULL in production
   const bool tr = trace != nullptr && blockIdx.x == 0;
   pdl_trigger();
@@ -104,17 +196,17 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   auto empty_bar = [&](int s) { return bar_base + 8u * (kStages + s); };
   auto tmem_full_bar = [&](int a) { return bar_base + 8u * (2 * kStages + a); };
   auto tmem_empty_bar = [&](int a) { return bar_base + 8u * (2 * kStages + 2 + a); };
-  const uint32_t tmem_slot = bar_base + 8u * kNumBars;
-  volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * kStageBytes + kNumBars * 8);
+  const uint32_t tmem_slot = bar_base + 8u * cfg::kNumBars;
+  volatile uint32_t* tmem_slot_gen =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + kStages * kStageBytes + cfg::kNumBars * 8);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const uint32_t crank = ptx::cluster_ctarank();
-  uint32_t csize;
-  asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(csize));
+  const uint32_t csize = ptx::cluster_nctarank();
   const int S = (int)(csize >> 1);              // k-splits sharing one output tile
   const int p = (int)(crank >> 1);              // this pair's split
-  const int h = (int)(crank & 1u);              // half of the tile rows (A) / of the tile columns (W)
+  const int h = (int)(crank & 1u);              // half of the tile rows (A) / of each MMA's columns (W)
   const uint32_t leader_rank = crank & ~1u;
   const uint16_t pair_mask = (uint16_t)(3u << leader_rank);
   const int cluster_id = blockIdx.x / csize;
@@ -156,7 +248,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     if (ptx::elect_one()) {
       const int n_tile = cluster_id % n_tiles;
       const int n = min(num_kb, kPrefetchKb);
-      for (int kb = 0; kb < n; ++kb) ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, n_tile * kTileN + h * kHalf);
+      for (int kb = 0; kb < n; ++kb) {
+#pragma unroll
+        for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i)
+          ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, n_tile * NT + i * cfg::NH + h * cfg::kBoxRowsB);
+      }
     }
     __syncwarp();
   }
@@ -170,7 +266,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       const int m_tile = tile / n_tiles, n_tile = tile - m_tile * n_tiles;
       const int a_row = m_tile * kTileM + h * kHalf;
-      const int b_row = n_tile * kTileN + h * kHalf;
+      const int b_row = n_tile * NT + h * cfg::kBoxRowsB;
       for (int kb = 0; kb < num_kb; ++kb, ++it) {
         const int s = it % kStages;
         if (it >= kStages) ptx::mbar_wait(empty_bar(s), ((it / kStages) & 1) ^ 1u);   // first lap: slots are free
@@ -179,9 +275,15 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           const uint32_t dst = smem_base + s * kStageBytes;
           const int k0 = (kb_begin + kb) * BK;
           tma_load_2d_pair(dst, &tma_a, leader_full0 + 8u * s, k0, a_row);
-          tma_load_2d_pair(dst + kBytesA, &tma_b, leader_full0 + 8u * s, k0, b_row);
-          if (prefetch_w && kb + kPrefetchKb < num_kb)
-            ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb + kPrefetchKb) * BK, b_row);
+#pragma unroll
+          for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i)     // this CTA's rows of each MMA's weight tile
+            tma_load_2d_pair(dst + kBytesA + i * (cfg::kBoxRowsB * BK * 2), &tma_b, leader_full0 + 8u * s, k0,
+                             b_row + i * cfg::NH);
+          if (prefetch_w && kb + kPrefetchKb < num_kb) {
+#pragma unroll
+            for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i)
+              ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb + kPrefetchKb) * BK, b_row + i * cfg::NH);
+          }
           if (tr && it < 32) trace[3 + it] = clock64();
         }
         __syncwarp();
@@ -189,16 +291,16 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     }
   } else if (warp == 1 && h == 0) {
     // ------------------------------------------------------------ MMA issuer (leader CTA of the pair)
-    constexpr uint32_t idesc = ptx::umma_idesc_bf16(kTileM, kTileN, 0, 0);
+    constexpr uint32_t idesc = ptx::umma_idesc_bf16(kTileM, cfg::NH, 0, 0);
     constexpr uint32_t desc_hi = ptx::umma_desc_hi_sw128(1024);
     const uint32_t a_lo0 = ptx::umma_desc_lo(smem_base, 16);
     uint32_t it = 0;
     int ti = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
-      const int acc = ti & 1, use = ti >> 1;
+      const int acc = cfg::kTwo ? 0 : (ti & 1), use = cfg::kTwo ? ti : (ti >> 1);
       ptx::mbar_wait(tmem_empty_bar(acc), (use & 1) ^ 1u);    // both CTAs' epilogues drained this accumulator
       ptx::tcgen05_fence_after();
-      const uint32_t d = tmem_base + (uint32_t)(acc * kTileN);
+      const uint32_t d = tmem_base + (uint32_t)(acc * 256);
       for (int kb = 0; kb < num_kb; ++kb, ++it) {
         const int s = it % kStages;
         ptx::mbar_wait(full_bar(s), (it / kStages) & 1);
@@ -208,9 +310,13 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           const uint32_t a_lo = a_lo0 + s * (kStageBytes >> 4);
           const uint32_t b_lo = a_lo + (kBytesA >> 4);
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k)
-            umma_bf16_ss_pair(d, ptx::umma_desc(a_lo + 2 * k, desc_hi), ptx::umma_desc(b_lo + 2 * k, desc_hi), idesc,
-                              (kb | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < BK / 16; ++k) {
+#pragma unroll
+            for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i)
+              umma_bf16_ss_pair(d + (uint32_t)(i * 256), ptx::umma_desc(a_lo + 2 * k, desc_hi),
+                                ptx::umma_desc(b_lo + i * ((cfg::kBoxRowsB * BK * 2) >> 4) + 2 * k, desc_hi), idesc,
+                                (kb | k) != 0 ? 1u : 0u);
+          }
           umma_commit_pair_mcast(empty_bar(s), pair_mask);                             // stage reusable in both CTAs
           if (kb == num_kb - 1) umma_commit_pair_mcast(tmem_full_bar(acc), pair_mask);  // accumulator complete
           if (tr && kb == num_kb - 1 && ti == 0) trace[80] = clock64();
@@ -227,23 +333,23 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     int ti = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
       const int m_tile = tile / n_tiles, n_tile = tile - m_tile * n_tiles;
-      const int acc = ti & 1, use = ti >> 1;
+      const int acc = cfg::kTwo ? 0 : (ti & 1), use = cfg::kTwo ? ti : (ti >> 1);
       const int grow = m_tile * kTileM + h * kHalf + r;
       const bool row_ok = grow < M;
       ptx::mbar_wait(tmem_full_bar(acc), use & 1);
       ptx::tcgen05_fence_after();
       if (tr && threadIdx.x == 64 && ti == 0) trace[81] = clock64();
 #pragma unroll 1
-      for (int c = 0; c < kTileN / 32; ++c) {
+      for (int c = 0; c < cfg::kChunks; c += 2) {       // two 16-column chunks per tensor-memory round trip
         uint32_t v[32];
-        ptx::tmem_ld_32x32b_x32(taddr + (uint32_t)(acc * kTileN + c * 32), v);
+        ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(acc * 256) + cfg::chunk_col(c), v);
+        ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(acc * 256) + cfg::chunk_col(c + 1), v + 16);
         ptx::tmem_ld_wait();
-        const int n0 = n_tile * kTileN + c * 32;
+        const int n0 = n_tile * NT + c * 16;
         float f[32];
 #pragma unroll
         for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-        if (row_ok && n0 < N) store16(C, out_f32, (int64_t)grow * ldc + n0, f);
-        if (row_ok && n0 + 16 < N) store16(C, out_f32, (int64_t)grow * ldc + n0 + 16, f + 16);
+        if (row_ok) emit32(C, out_f32, epi, (int64_t)grow * ldc, n0, N, f);
       }
       ptx::tcgen05_fence_before();
       __syncwarp();
@@ -253,81 +359,37 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
   }
 
   if (S > 1) {
-    // ------------------------------------------------------------ split-K exchange over DSMEM (one tile per cluster)
+    // ------------------------------------------------------------ split-K exchange (one tile per cluster)
     const int tile = cluster_id;
     const int m_tile = tile / n_tiles, n_tile = tile - m_tile * n_tiles;
     const int q = warp & 3;
     const int r = q * 32 + lane;
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
-    const uint32_t dump = smem_base;        // the operand ring is idle once the accumulator is complete
+    float4* ws_cluster = ws + (size_t)cluster_id * csize * cfg::kPartF4;
     if (warp >= 2) {
-      ptx::mbar_wait(tmem_full_bar(0), 0);  // all MMAs of this pair have retired: nothing reads the ring any more
+      ptx::mbar_wait(tmem_full_bar(0), 0);  // all MMAs of this pair have retired
       ptx::tcgen05_fence_after();
       if (tr && threadIdx.x == 64) trace[81] = clock64();
-      ptx::fence_proxy_async_smem();
-#pragma unroll 1
-      for (int c = 0; c < kTileN / 16; ++c) {
-        if (c % S == p) continue;           // my chunks stay in tensor memory
-        uint32_t v[16];
-        ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(c * 16), v);
-        ptx::tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-          ptx::st_shared_f4(dump + (uint32_t)(((c * 4 + j) * kHalf + r) * 16), __uint_as_float(v[4 * j]),
-                       __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-      }
+      float4* my_ws = ws_cluster + (size_t)crank * cfg::kPartF4;
+      if (S == 2) pair_publish<NT, 2>(my_ws, taddr, p, r);
+      else if (S == 3) pair_publish<NT, 3>(my_ws, taddr, p, r);
+      else pair_publish<NT, 4>(my_ws, taddr, p, r);
     }
     if (tr && threadIdx.x == 64) trace[82] = clock64();
-    ptx::cluster_sync_all();                // every partial is parked (release / acquire at cluster scope)
+    ptx::cluster_sync_all();                // every partial is published (release / acquire at cluster scope)
     if (tr && threadIdx.x == 64) trace[85] = clock64();
     if (warp >= 2) {
       const int grow = m_tile * kTileM + h * kHalf + r;
       const bool row_ok = grow < M;
-#pragma unroll 1
-      for (int c = p; c < kTileN / 16; c += S) {
-        uint32_t v[16];
-        ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(c * 16), v);
-        ptx::tmem_ld_wait();
-        // all peers' copies of this chunk are requested before the first add (one DSMEM round trip per chunk)
-        float4 t[3][4];
-        const uint32_t off = dump + (uint32_t)((c * 4 * kHalf + r) * 16);
-#pragma unroll
-        for (int i = 0; i < 3; ++i) {
-          const int z = i + (i >= p ? 1 : 0);         // the i-th split that is not mine
-          if (i < S - 1) {
-            const uint32_t peer = ptx::mapa_u32(off, (uint32_t)(2 * z + h));
-#pragma unroll
-            for (int j = 0; j < 4; ++j) t[i][j] = ptx::ld_cluster_f4(peer + (uint32_t)(j * kHalf * 16));
-          }
-        }
-        float f[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) f[j] = 0.f;
-#pragma unroll
-        for (int z = 0; z < 4; ++z) {       // split order 0..S-1 whoever reduces: deterministic
-          if (z < S) {
-            if (z == p) {
-#pragma unroll
-              for (int j = 0; j < 16; ++j) f[j] += __uint_as_float(v[j]);
-            } else {
-              const int i = z - (z > p ? 1 : 0);
-#pragma unroll
-              for (int j = 0; j < 4; ++j) {
-                // i is not a compile-time constant: select among the (at most 3) register batches
-                const float4 q4 = i == 0 ? t[0][j] : (i == 1 ? t[1][j] : t[2][j]);
-                f[4 * j] += q4.x; f[4 * j + 1] += q4.y; f[4 * j + 2] += q4.z; f[4 * j + 3] += q4.w;
-              }
-            }
-          }
-        }
-        const int n0 = n_tile * kTileN + c * 16;
-        if (row_ok && n0 < N) store16(C, out_f32, (int64_t)grow * ldc + n0, f);
-      }
+      const int64_t row_off = (int64_t)grow * ldc;
+      if (S == 2) pair_reduce<NT, 2>(ws_cluster, taddr, p, h, r, C, out_f32, epi, row_off, row_ok, n_tile * NT, N);
+      else if (S == 3) pair_reduce<NT, 3>(ws_cluster, taddr, p, h, r, C, out_f32, epi, row_off, row_ok, n_tile * NT, N);
+      else pair_reduce<NT, 4>(ws_cluster, taddr, p, h, r, C, out_f32, epi, row_off, row_ok, n_tile * NT, N);
       if (tr && threadIdx.x == 64) trace[83] = clock64();
     }
   }
   ptx::tcgen05_fence_before();
-  ptx::cluster_sync_all();       // nobody exits (or frees tensor memory) while a peer may still read its smem / signal its barriers
+  ptx::cluster_sync_all();       // nobody exits (or frees tensor memory) while a peer may still signal its barriers
   if (warp == 1) {
     ptx::tcgen05_fence_after();
     tmem_dealloc_pair(tmem_base, kTmemCols);
@@ -351,17 +413,53 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
   return NVC_OK;
 }
 
+#define NVC_PAIR_WIDTHS(X) X(256) X(320) X(352) X(384) X(448) X(512)
+
+template <int NT>
+int launch_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M, int N,
+                int K, int S, int epi, cudaStream_t stream, long long* trace) {
+  using cfg = PairCfg<NT>;
+  CUtensorMap ta, tb;
+  int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, kHalf);
+  if (rc) return rc;
+  rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, cfg::kBoxRowsB);
+  if (rc) return rc;
+  const int kb_total = K / BK;
+  const int m_tiles = (M + kTileM - 1) / kTileM, n_tiles = (N + NT - 1) / NT;
+  const int tiles = m_tiles * n_tiles;
+  if (S > 1 && (size_t)tiles * 2 * S * cfg::kPartF4 * sizeof(float4) > ctx->gemm_ws_bytes) S = 1;   // workspace too small
+  int kb_per = (kb_total + S - 1) / S;
+  S = (kb_total + kb_per - 1) / kb_per;      // no empty splits
+  int clusters = tiles;
+  if (S == 1) {
+    const int avail = ctx->pair_clusters[1] > 0 ? ctx->pair_clusters[1] : ctx->num_sms / 2;
+    // equal tiles per cluster where possible: ceil(tiles / waves) clusters, not a ragged last wave
+    const int waves = (tiles + avail - 1) / avail;
+    clusters = (tiles + waves - 1) / waves;
+  }
+  dim3 grid(clusters * 2 * S);
+  NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, gemm_pair_kernel<NT>, grid, dim3(kThreads), cfg::kSmemBytes, stream, 2 * S,
+                                         ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, tiles, n_tiles,
+                                         (M <= kTileM) ? 1 : 0, epi, reinterpret_cast<float4*>(ctx->gemm_ws), trace));
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
+  return NVC_OK;
+}
+
 }  // namespace
 
 // Co-resident clusters of 2S CTAs (S = 1..4), measured once per context: the schedule model needs
-// them (cluster placement is per GPC, so 148 SMs do not hold 148 / (2S) clusters for every S).
+// them (cluster placement is per GPC: B200 holds 74 / 33 / 22 / 15 clusters of 2 / 4 / 6 / 8 CTAs).
 extern "C" int nvc_gemm_pair_init(nvc_ctx* ctx) {
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+#define X(NT) \
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_pair_kernel<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, PairCfg<NT>::kSmemBytes));
+  NVC_PAIR_WIDTHS(X)
+#undef X
   for (int S = 1; S <= 4; ++S) {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(2 * S * 64);
     cfg.blockDim = dim3(kThreads);
-    cfg.dynamicSmemBytes = kSmemBytes;
+    cfg.dynamicSmemBytes = PairCfg<256>::kSmemBytes;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2 * S;
@@ -370,7 +468,7 @@ extern "C" int nvc_gemm_pair_init(nvc_ctx* ctx) {
     cfg.attrs = attr;
     cfg.numAttrs = 1;
     int n = 0;
-    cudaError_t e = cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel, &cfg);
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&n, gemm_pair_kernel<256>, &cfg);
     if (e != cudaSuccess || n <= 0) {
       (void)cudaGetLastError();
       n = ctx->num_sms / (2 * S);
@@ -383,51 +481,43 @@ extern "C" int nvc_gemm_pair_init(nvc_ctx* ctx) {
   return NVC_OK;
 }
 
-// Schedule choice: persistent (S = 1) when the tiles fill the pairs; otherwise split K inside a
-// cluster so that ~all SMs stream weights.  Cycle model: a k-block costs 512 tensor cycles per
-// pair; a CTA pays ~3000 cycles of prologue / first-load latency / epilogue, the DSMEM exchange
-// ~2500 more.
-static int choose_splits(const nvc_ctx* ctx, int tiles, int kb) {
+// Schedule choice (cycle model fitted to tools/gemm_microbench.py --pair on B200):
+//  * a k-block costs ~2 * NT tensor cycles per pair (~600 for NT = 256 once the weights stream from HBM);
+//  * the persistent schedule (S = 1) pays ~10k cycles once (prologue, first loads, last epilogue);
+//    a split-K cluster pays ~12k (prologue, drain, publish, cluster barrier, reduce);
+//  * waves = ceil(tiles / co-resident clusters of that size).
+// Between one and two waves of 256-wide tiles, the narrowest wider tile that fits ONE wave wins.
+static void choose_schedule(const nvc_ctx* ctx, int M, int N, int kb, int* nt_out, int* s_out) {
+  const int m_tiles = (M + kTileM - 1) / kTileM;
   double best = 1e30;
-  int best_s = 1;
-  for (int S = 1; S <= 4; ++S) {
-    if (S > kb) break;
-    const int avail = ctx->pair_clusters[S] > 0 ? ctx->pair_clusters[S] : ctx->num_sms / (2 * S);
-    const double waves = ceil((double)tiles / avail);
+  int best_s = 1, best_nt = 256;
+  auto avail = [&](int S) { return ctx->pair_clusters[S] > 0 ? ctx->pair_clusters[S] : ctx->num_sms / (2 * S); };
+  for (int S = 1; S <= 4 && S <= kb; ++S) {
+    const int tiles = m_tiles * ((N + 255) / 256);
+    const double waves = ceil((double)tiles / avail(S));
     const double kbs = ceil((double)kb / S);
-    const double t = S == 1 ? waves * kbs * 512.0 + 3500.0 : waves * (kbs * 512.0 + 5500.0);
-    if (t < best * 0.97) { best = t; best_s = S; }
+    const double t = S == 1 ? waves * kbs * 560.0 + 10000.0 : waves * (kbs * 600.0 + 12000.0);
+    if (t < best * 0.98) { best = t; best_s = S; best_nt = 256; }
   }
-  return best_s;
+  // Wide tiles (NT > 256, one wave instead of two for 75..148 tiles) are NOT chosen automatically: measured on
+  // Qwen3-8B gate_up at batch 256 (N 24576: 70 tiles of 352) 53.1 us vs 53.6 us for two waves of 256-wide tiles -
+  // at M = 256 the GEMM sits on the HBM / L2-fabric ridge (k-block pace 808 cycles vs 704 of MMA), and the single
+  // accumulator stage exposes the 11k-cycle epilogue.  They stay selectable (force_splits = 1000 + NT) and tested.
+  *nt_out = best_nt;
+  *s_out = best_s;
 }
 
+// force_splits: 0 = choose; 1..4 = in-cluster split-K factor with 256-wide tiles; 1000 + NT = one-wave wide tiles
 extern "C" int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32,
-                             int M, int N, int K, int force_splits, void* stream, long long* trace) {
-  CUtensorMap ta, tb;
-  int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, kHalf);
-  if (rc) return rc;
-  rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, kHalf);
-  if (rc) return rc;
-  const int kb_total = K / BK;
-  const int m_tiles = (M + kTileM - 1) / kTileM, n_tiles = (N + kTileN - 1) / kTileN;
-  const int tiles = m_tiles * n_tiles;
-  int S = force_splits > 0 ? force_splits : choose_splits(ctx, tiles, kb_total);
-  if (S > 4) S = 4;
-  if (S > kb_total) S = kb_total;
-  int kb_per = (kb_total + S - 1) / S;
-  S = (kb_total + kb_per - 1) / kb_per;      // no empty splits
-  int clusters = tiles;
-  if (S == 1) {
-    const int avail = ctx->pair_clusters[1] > 0 ? ctx->pair_clusters[1] : ctx->num_sms / 2;
-    // equal tiles per cluster where possible: ceil(tiles / waves) clusters, not a ragged last wave
-    const int waves = (tiles + avail - 1) / avail;
-    clusters = (tiles + waves - 1) / waves;
-  }
-  dim3 grid(clusters * 2 * S);
-  NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, gemm_pair_kernel, grid, dim3(kThreads), kSmemBytes, nvc_stream(stream),
-                                         2 * S, ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, tiles, n_tiles,
-                                         (M <= kTileM) ? 1 : 0, trace));
-  NVC_CUDA_CHECK(ctx, cudaGetLastError());
-  ctx->launches++;
+                             int M, int N, int K, int force_splits, int epi, void* stream, long long* trace) {
+  int nt = 256, S = 1;
+  if (force_splits >= 1000) { nt = force_splits - 1000; S = 1; }
+  else if (force_splits > 0) { S = force_splits > 4 ? 4 : force_splits; }
+  else choose_schedule(ctx, M, N, K / BK, &nt, &S);
+#define X(NT) \
+  if (nt == NT) return launch_pair<NT>(ctx, A, lda, W, C, ldc, out_f32, M, N, K, S, epi, nvc_stream(stream), trace);
+  NVC_PAIR_WIDTHS(X)
+#undef X
+  NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported pair tile width");
   return NVC_OK;
 }

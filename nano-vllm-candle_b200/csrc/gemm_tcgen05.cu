@@ -19,6 +19,7 @@
 #include "common.cuh"
 #include "ptx.cuh"
 #include "internal.h"
+#include "gemm_epilogue.cuh"
 
 #include <cstdlib>
 
@@ -57,7 +58,7 @@ template <int BN, int KPS, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total,
-                         int k_blocks_per_split, int a_box_rows, int prefetch_w, int ks_cluster, float* __restrict__ ws,
+                         int k_blocks_per_split, int a_box_rows, int prefetch_w, int ks_cluster, int epi, float* __restrict__ ws,
                          int* __restrict__ counters, long long* __restrict__ trace) {
   using cfg = Cfg<BN, KPS>;
   // optional phase timestamps of CTA (0,0,0) (tools/gemm_microbench.py); NULL in production
@@ -211,34 +212,26 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const int tile_id = m_tile * gridDim.x + n_tile;
 
     if (num_splits == 1) {
+      if constexpr (BN >= 32) {
 #pragma unroll 1
-      for (int c = 0; c < BN / 16; ++c) {
-        uint32_t v[16];
-        ptx::tmem_ld_32x32b_x16(taddr + c * 16, v);
-        ptx::tmem_ld_wait();
-        const int n0 = n_tile * BN + c * 16;
-        if (row_ok && n0 < N) {
-          if (out_f32) {
-            float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(C) + (int64_t)grow * ldc + n0);
+        for (int c = 0; c < BN / 16; c += 2) {          // two 16-column chunks per tensor-memory round trip
+          uint32_t v[32];
+          ptx::tmem_ld_32x32b_x16(taddr + c * 16, v);
+          ptx::tmem_ld_32x32b_x16(taddr + c * 16 + 16, v + 16);
+          ptx::tmem_ld_wait();
+          float f[32];
 #pragma unroll
-            for (int j = 0; j < 4; ++j)
-              dst[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]),
-                                   __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-          } else {
-            uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<nvc_bf16*>(C) + (int64_t)grow * ldc + n0);
-            uint4 o0, o1;
-            o0.x = pack_bf16(__uint_as_float(v[0]), __uint_as_float(v[1]));
-            o0.y = pack_bf16(__uint_as_float(v[2]), __uint_as_float(v[3]));
-            o0.z = pack_bf16(__uint_as_float(v[4]), __uint_as_float(v[5]));
-            o0.w = pack_bf16(__uint_as_float(v[6]), __uint_as_float(v[7]));
-            o1.x = pack_bf16(__uint_as_float(v[8]), __uint_as_float(v[9]));
-            o1.y = pack_bf16(__uint_as_float(v[10]), __uint_as_float(v[11]));
-            o1.z = pack_bf16(__uint_as_float(v[12]), __uint_as_float(v[13]));
-            o1.w = pack_bf16(__uint_as_float(v[14]), __uint_as_float(v[15]));
-            dst[0] = o0;
-            dst[1] = o1;
-          }
+          for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+          if (row_ok) emit32(C, out_f32, epi, (int64_t)grow * ldc, n_tile * BN + c * 16, N, f);
         }
+      } else {
+        uint32_t v[16];
+        ptx::tmem_ld_32x32b_x16(taddr, v);
+        ptx::tmem_ld_wait();
+        float f[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+        if (row_ok && n_tile * BN < N) store16(C, out_f32, (int64_t)grow * ldc + n_tile * BN, f);
       }
     } else if (ks_cluster) {
       // ---- split-K inside a cluster (1,1,S): park this CTA's fp32 partial tile in its own, now idle,
@@ -383,7 +376,7 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
 
 template <int BN, int KPS, int CL>
 int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M,
-           int N, int K, int splits, int ks_cluster, cudaStream_t stream, long long* trace) {
+           int N, int K, int splits, int ks_cluster, int epi, cudaStream_t stream, long long* trace) {
   using cfg = Cfg<BN, KPS>;
   CUtensorMap ta, tb;
   // a single partial m-tile only needs the rows that exist (rounded to the 8-row swizzle atom per
@@ -406,7 +399,7 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
                                           stream, dim3(CL, 1, ks ? eff_splits : 1), ta, tb, C, ldc, out_f32, M, N, kb_total,
                                           kb_per, a_rows / CL,
                                           (g_nvc_gemm_prefetch && M <= BM) ? 1 : 0,   // helps latency-bound decode, hurts M >= 256
-                                          ks, ctx->gemm_ws, ctx->gemm_counters, trace));
+                                          ks, epi, ctx->gemm_ws, ctx->gemm_counters, trace));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -484,14 +477,17 @@ extern "C" int nvc_gemm_init(nvc_ctx* ctx) {
 }
 
 static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
-                     int out_dtype, int M, int Nout, int K, int force_bn, int force_splits,
+                     int out_dtype, int M, int Nout, int K, int force_bn, int force_splits, int epi,
                      void* stream, long long* trace) {
   NVC_REQUIRE(ctx, ctx && A && W && C, NVC_EINVAL, "null pointer");
   NVC_REQUIRE(ctx, M >= 0 && Nout > 0 && K > 0, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, K % 64 == 0, NVC_ESHAPE, "K must be a multiple of 64");
   NVC_REQUIRE(ctx, Nout % 16 == 0, NVC_ESHAPE, "Nout must be a multiple of 16");
   NVC_REQUIRE(ctx, lda % 8 == 0 && lda >= K, NVC_ESHAPE, "lda must be >= K and a multiple of 8");
-  NVC_REQUIRE(ctx, ldc >= Nout && ldc % 8 == 0, NVC_ESHAPE, "ldc must be >= Nout and a multiple of 8");
+  NVC_REQUIRE(ctx, ldc >= (epi == NVC_EPI_SILU_MUL ? Nout / 2 : Nout) && ldc % 8 == 0, NVC_ESHAPE,
+              "ldc must be >= the output width and a multiple of 8");
+  NVC_REQUIRE(ctx, epi == NVC_EPI_NONE || (epi == NVC_EPI_SILU_MUL && Nout % 32 == 0 && out_dtype == NVC_DT_BF16),
+              NVC_ESHAPE, "fused SiLU-mul epilogue needs Nout % 32 == 0 and bf16 output");
   NVC_REQUIRE(ctx, out_dtype == NVC_DT_BF16 || out_dtype == NVC_DT_F32, NVC_EINVAL, "bad out_dtype");
   NVC_REQUIRE(ctx, ((uintptr_t)A % 16) == 0 && ((uintptr_t)W % 16) == 0 && ((uintptr_t)C % 16) == 0, NVC_EINVAL,
               "pointers must be 16-byte aligned");
@@ -499,7 +495,7 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   if (M == 0) return NVC_OK;
   // M > 128: CTA-pair kernel (gemm_pair.cu); force_bn = 512 selects it explicitly, any other force_bn the 1-CTA tiles
   if (force_bn == 512 || (force_bn == 0 && M > BM && g_nvc_gemm_pair))
-    return nvc_gemm_pair(ctx, A, lda, W, C, ldc, out_dtype == NVC_DT_F32, M, Nout, K, force_splits, stream, trace);
+    return nvc_gemm_pair(ctx, A, lda, W, C, ldc, out_dtype == NVC_DT_F32, M, Nout, K, force_splits, epi, stream, trace);
   int bn, kps, splits, cl = 1, ks = 0;
   choose_config(ctx, M, Nout, K, &bn, &kps, &splits, &cl, &ks);
   if (force_bn) {          // force_bn = BN + 1000 * KPS + 10000 * CL (KPS 0: the first instantiation of that BN)
@@ -515,6 +511,12 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   if (force_splits >= 100) { splits = force_splits - 100; ks = 1; cl = 1; }
   else if (force_splits) { splits = force_splits; ks = 0; }
   NVC_REQUIRE(ctx, !ks || splits <= 8, NVC_EINVAL, "cluster split-K supports at most 8 splits");
+  if (epi != NVC_EPI_NONE) {       // the fused epilogue lives in the direct-store path: no split-K, tiles of >= 32 columns
+    NVC_REQUIRE(ctx, force_splits == 0 || force_splits == 1, NVC_EINVAL, "fused epilogue cannot be combined with split-K");
+    splits = 1;
+    ks = 0;
+    if (bn < 32) { bn = 32; kps = 4; cl = 1; }
+  }
   if (splits > K / BK) splits = K / BK;
   const int tiles = ((M + BM - 1) / BM) * ((Nout + bn - 1) / bn);
   if (splits > 1 && !ks) {
@@ -524,7 +526,7 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   cudaStream_t st = nvc_stream(stream);
   const int f32 = out_dtype == NVC_DT_F32;
 #define X(BN, KPS, CL) \
-  if (bn == BN && kps == KPS && cl == CL) return launch<BN, KPS, CL>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, ks, st, trace);
+  if (bn == BN && kps == KPS && cl == CL) return launch<BN, KPS, CL>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, ks, epi, st, trace);
   NVC_GEMM_CONFIGS(X)
 #undef X
   NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported tile configuration");
@@ -534,17 +536,31 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
 extern "C" int nvc_gemm_bf16_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
                                 int out_dtype, int M, int Nout, int K, int force_bn, int force_splits,
                                 void* stream) {
-  return gemm_impl(ctx, A, lda, W, C, ldc, out_dtype, M, Nout, K, force_bn, force_splits, stream, nullptr);
+  return gemm_impl(ctx, A, lda, W, C, ldc, out_dtype, M, Nout, K, force_bn, force_splits, NVC_EPI_NONE, stream, nullptr);
 }
 
 // Debug: same GEMM, CTA (0,0,0) writes clock64() phase stamps to trace_d[0..128) (device memory).
 extern "C" int nvc_gemm_bf16_trace(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
                                    int out_dtype, int M, int Nout, int K, int force_bn, int force_splits,
                                    void* stream, long long* trace_d) {
-  return gemm_impl(ctx, A, lda, W, C, ldc, out_dtype, M, Nout, K, force_bn, force_splits, stream, trace_d);
+  return gemm_impl(ctx, A, lda, W, C, ldc, out_dtype, M, Nout, K, force_bn, force_splits, NVC_EPI_NONE, stream, trace_d);
 }
 
 extern "C" int nvc_gemm_bf16(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
                              int out_dtype, int M, int Nout, int K, void* stream) {
   return nvc_gemm_bf16_ex(ctx, A, lda, W, C, ldc, out_dtype, M, Nout, K, 0, 0, stream);
+}
+
+// K3 + K6 fused (Qwen3MLP::forward, src/models/qwen3.rs:323-327): act = silu(A Wg^T) * (A Wu^T) with the
+// gate/up rows of W interleaved in groups of 16 (see include/nvc_b200.h).
+extern "C" int nvc_gemm_bf16_silu_mul_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W_gu16, nvc_bf16* act,
+                                         int ldc, int M, int I, int K, int force_bn, int force_splits, void* stream) {
+  NVC_REQUIRE(ctx, I > 0 && I % 16 == 0, NVC_ESHAPE, "I must be a multiple of 16");
+  return gemm_impl(ctx, A, lda, W_gu16, act, ldc, NVC_DT_BF16, M, 2 * I, K, force_bn, force_splits, NVC_EPI_SILU_MUL,
+                   stream, nullptr);
+}
+
+extern "C" int nvc_gemm_bf16_silu_mul(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W_gu16, nvc_bf16* act,
+                                      int ldc, int M, int I, int K, void* stream) {
+  return nvc_gemm_bf16_silu_mul_ex(ctx, A, lda, W_gu16, act, ldc, M, I, K, 0, 0, stream);
 }

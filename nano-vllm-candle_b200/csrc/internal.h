@@ -14,6 +14,8 @@ int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc
 int nvc_pack_argmax_pairs(nvc_ctx* ctx, const float* val, const int32_t* idx, float* pairs, int B, void* stream);
 int nvc_gemm_bf16_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_dtype,
                      int M, int Nout, int K, int force_bn, int force_splits, void* stream);
+int nvc_gemm_bf16_silu_mul_ex(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W_gu16, nvc_bf16* act, int ldc,
+                              int M, int I, int K, int force_bn, int force_splits, void* stream);
 int nvc_gemm_bf16_trace(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_dtype,
                         int M, int Nout, int K, int force_bn, int force_splits, void* stream, long long* trace_d);
 // set max-dynamic-smem attributes of every kernel instantiation (called once per context)
@@ -21,7 +23,7 @@ int nvc_gemm_init(nvc_ctx* ctx);
 int nvc_gemm_pair_init(nvc_ctx* ctx);
 // CTA-pair (cta_group::2) GEMM for M > 128; force_splits 0 = choose the in-cluster split-K factor
 int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M,
-                  int N, int K, int force_splits, void* stream, long long* trace);
+                  int N, int K, int force_splits, int epi, void* stream, long long* trace);
 int nvc_prefill_attn_init(nvc_ctx* ctx);
 int nvc_paged_decode_init(nvc_ctx* ctx);
 }

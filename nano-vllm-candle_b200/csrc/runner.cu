@@ -5,7 +5,7 @@
 //
 // Per layer (prefill and decode differ only in the attention kernel):
 //   fused_add_rmsnorm -> qkv GEMM -> qk_norm_rope_store -> attention -> o_proj GEMM [-> all-reduce]
-//   -> fused_add_rmsnorm -> gate_up GEMM -> silu_and_mul -> down GEMM [-> all-reduce]
+//   -> fused_add_rmsnorm -> gate_up GEMM (+ SiLU-mul epilogue) -> down GEMM [-> all-reduce]
 // then: gather last rows -> final fused_add_rmsnorm -> lm_head GEMM (fp32) -> argmax.
 #include "common.cuh"
 #include "internal.h"
@@ -44,7 +44,7 @@ struct nvc_runner {
   int64_t weight_bytes = 0;
   std::vector<void*> allocs;
   // activations
-  nvc_bf16 *x = nullptr, *xn = nullptr, *qkv = nullptr, *attn = nullptr, *gu = nullptr, *act = nullptr;
+  nvc_bf16 *x = nullptr, *xn = nullptr, *qkv = nullptr, *attn = nullptr, *act = nullptr;
   float* residual = nullptr;
   nvc_bf16 *x_last = nullptr, *xn_last = nullptr;
   float *res_last = nullptr, *logits = nullptr;
@@ -79,7 +79,6 @@ int dev_alloc(nvc_runner* r, T** p, size_t count) {
   return NVC_OK;
 }
 
-int launch_count_layer(const nvc_runner* r) { return r->tp > 1 ? 11 : 9; }
 
 // The transformer body over N tokens already embedded in r->x.  decode: attention over the
 // paged cache; prefill: varlen causal flash over the tokens of this step.
@@ -135,9 +134,8 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
       rc = nvc_fused_add_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
     }
     if (rc) return rc;
-    rc = nvc_gemm_bf16(ctx, r->xn, H, Ly.w_gu, r->gu, 2 * r->I_l, NVC_DT_BF16, N, 2 * r->I_l, H, st);
-    if (rc) return rc;
-    rc = nvc_silu_and_mul(ctx, r->gu, r->act, N, r->I_l, st);
+    // gate_up projection with SiluAndMul fused into the epilogue (w_gu rows interleaved in groups of 16 at load)
+    rc = nvc_gemm_bf16_silu_mul(ctx, r->xn, H, Ly.w_gu, r->act, r->I_l, N, r->I_l, H, st);
     if (rc) return rc;
     // down_proj (row-parallel) -> [all-reduce, N4]
     rc = nvc_gemm_bf16(ctx, r->act, r->I_l, Ly.w_down, p2p ? slot1 : r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
@@ -282,7 +280,6 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if ((rc = dev_alloc(r, &r->residual, T * H))) return rc;
   if ((rc = dev_alloc(r, &r->qkv, T * r->qkv_l))) return rc;
   if ((rc = dev_alloc(r, &r->attn, T * r->nh_l * hd))) return rc;
-  if ((rc = dev_alloc(r, &r->gu, T * 2 * r->I_l))) return rc;
   if ((rc = dev_alloc(r, &r->act, T * r->I_l))) return rc;
   if ((rc = dev_alloc(r, &r->x_last, Bm * H))) return rc;
   if ((rc = dev_alloc(r, &r->xn_last, Bm * H))) return rc;
@@ -346,6 +343,13 @@ int copy_cols(nvc_runner* r, nvc_bf16* dst, const nvc_bf16* src, int64_t rows, i
   return NVC_OK;
 }
 
+// dst rows [32g, 32g+16) = src rows [16g, 16g+16): groups of 16 rows, one group skipped between them
+int copy_rows_grouped(nvc_runner* r, nvc_bf16* dst, const nvc_bf16* src, int64_t nrows, int64_t cols) {
+  R_CUDA(cudaMemcpy2D(dst, (size_t)32 * cols * 2, src, (size_t)16 * cols * 2, (size_t)16 * cols * 2, (size_t)(nrows / 16),
+                      cudaMemcpyDefault));
+  return NVC_OK;
+}
+
 }  // namespace
 
 extern "C" int nvc_runner_load_weight(nvc_runner* r, const char* hf_name, const nvc_bf16* data, int64_t rows,
@@ -401,12 +405,12 @@ extern "C" int nvc_runner_load_weight(nvc_runner* r, const char* hf_name, const 
     } else if (sub == "self_attn.k_norm.weight") {
       if (!shape_is(hd, 1)) return bad_shape();
       rc = copy_rows(r, L.k_norm, data, 0, hd, 1);
-    } else if (sub == "mlp.gate_proj.weight") {        // fused rows [gate; up], qwen3.rs:310
-      if (!shape_is(I, H)) return bad_shape();
-      rc = copy_rows(r, L.w_gu, data, (int64_t)r->rank * r->I_l, r->I_l, H);
+    } else if (sub == "mlp.gate_proj.weight") {        // fused gate_up (qwen3.rs:310), rows interleaved in groups of 16:
+      if (!shape_is(I, H)) return bad_shape();         // [32g, 32g+16) = gate rows, [32g+16, 32g+32) = up rows (nvc_gemm_bf16_silu_mul)
+      rc = copy_rows_grouped(r, L.w_gu, data + (int64_t)r->rank * r->I_l * H, r->I_l, H);
     } else if (sub == "mlp.up_proj.weight") {
       if (!shape_is(I, H)) return bad_shape();
-      rc = copy_rows(r, L.w_gu + (int64_t)r->I_l * H, data, (int64_t)r->rank * r->I_l, r->I_l, H);
+      rc = copy_rows_grouped(r, L.w_gu + 16 * H, data + (int64_t)r->rank * r->I_l * H, r->I_l, H);
     } else if (sub == "mlp.down_proj.weight") {
       if (!shape_is(H, I)) return bad_shape();
       rc = copy_cols(r, L.w_down, data, H, I, (int64_t)r->rank * r->I_l, r->I_l);
@@ -653,7 +657,7 @@ extern "C" int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_pe
           rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, L.w_o, r->x, H, NVC_DT_BF16, B, H, r->nh_l * hd, st);
           break;
         case NVC_OP_GEMM_GATE_UP:
-          rc = nvc_gemm_bf16(ctx, r->xn, H, L.w_gu, r->gu, 2 * r->I_l, NVC_DT_BF16, B, 2 * r->I_l, H, st);
+          rc = nvc_gemm_bf16_silu_mul(ctx, r->xn, H, L.w_gu, r->act, r->I_l, B, r->I_l, H, st);
           break;
         case NVC_OP_GEMM_DOWN:
           rc = nvc_gemm_bf16(ctx, r->act, r->I_l, L.w_down, r->x, H, NVC_DT_BF16, B, H, r->I_l, st);
@@ -667,7 +671,7 @@ extern "C" int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_pe
                                       nullptr, nullptr, B, r->nh_l, r->kv_l, hd, st);
           break;
         case NVC_OP_SILU_MUL:
-          rc = nvc_silu_and_mul(ctx, r->gu, r->act, B, r->I_l, st);
+          rc = nvc_silu_and_mul(ctx, r->qkv, r->act, B, r->qkv_l / 2, st);   // stand-alone K6 (not on the step any more)
           break;
         case NVC_OP_NOOP:   // smallest possible kernel: the per-launch floor inside a graph
           rc = nvc_gather_rows(ctx, r->x, nullptr, r->d_last_rows, r->x_last, nullptr, 1, H, st);

@@ -128,6 +128,27 @@ class Context:
                                          M, N, K, force_bn, force_splits, _stream()), "nvc_gemm_bf16")
         return out
 
+    @staticmethod
+    def interleave_gate_up(w_gu: torch.Tensor) -> torch.Tensor:
+        """[gate; up] rows (reference layout, qwen3.rs:310) -> groups of 16 gate rows then 16 up rows,
+        the layout nvc_gemm_bf16_silu_mul expects."""
+        two_i, k = w_gu.shape
+        i = two_i // 2
+        assert i % 16 == 0
+        return torch.stack([w_gu[:i].reshape(i // 16, 16, k), w_gu[i:].reshape(i // 16, 16, k)], dim=1).reshape(two_i, k).contiguous()
+
+    def gemm_silu_mul(self, a: torch.Tensor, w_gu16: torch.Tensor, out=None, force_bn=0, force_splits=0):
+        """act = silu(a @ Wgate.T) * (a @ Wup.T); w_gu16 = interleave_gate_up([gate; up])."""
+        _req(a, BF16, "a"); _req(w_gu16, BF16, "w_gu16")
+        M, K = a.shape
+        I = w_gu16.shape[0] // 2
+        assert w_gu16.shape[1] == K and w_gu16.is_contiguous() and a.stride(1) == 1
+        if out is None:
+            out = torch.empty((M, I), dtype=BF16, device=a.device)
+        self._ck(self.l.nvc_gemm_bf16_silu_mul_ex(self.h, _ptr(a), a.stride(0), _ptr(w_gu16), _ptr(out), out.stride(0),
+                                                  M, I, K, force_bn, force_splits, _stream()), "nvc_gemm_bf16_silu_mul")
+        return out
+
     def rope_table(self, theta: float, head_dim: int, max_pos: int, device=None):
         dev = torch.device("cuda", self.device) if device is None else device
         tab = torch.empty((max_pos, head_dim), dtype=torch.float32, device=dev)

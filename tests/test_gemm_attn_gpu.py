@@ -71,6 +71,15 @@ GEMM_SHAPES = [
     (256, 512, 64, 512, 4),        # more splits than k-blocks: clamps to 1
     (256, 4096, 4096, 512, 0),     # auto split choice
     (512, 151936 // 8, 1024, 512, 0),   # lm_head shard, ragged last n-tile
+    # wide pair tiles (two MMAs of N = NT/2 per k-step, one accumulator stage): force_splits = 1000 + NT
+    (256, 1056, 256, 512, 1352),   # 3 tiles of 352
+    (256, 704, 512, 512, 1320),    # NT = 320, ragged last tile
+    (300, 2000, 192, 512, 1512),   # NT = 512, ragged M and N
+    (512, 768, 320, 512, 1384),    # NT = 384, two m-tiles
+    (256, 896, 1024, 512, 1448),   # NT = 448, ring wraps
+    (4096, 4096, 128, 512, 1512),  # 128 wide tiles: two per cluster through the single accumulator stage
+    (256, 24576, 4096, 512, 1352), # 8B gate_up at batch 256: 70 tiles, one wave
+    (256, 24576, 4096, 0, 0),      # the same through the schedule choice
 ]
 
 
@@ -107,6 +116,34 @@ def test_gemm_reference_goldens(ctx):
         ws = torch.zeros(16, 64); ws[:3, :4] = w[3 * r:3 * r + 3]
         o = ctx.gemm(xp.to(BF16).cuda(), ws.to(BF16).cuda(), out_dtype=torch.float32).cpu()
         assert torch.equal(o[:, :3] + bias[3 * r:3 * r + 3], want[:, 3 * r:3 * r + 3])
+
+
+SILU_SHAPES = [
+    # (M, I, K, force_bn, force_splits)
+    (64, 3072, 1024, 0, 0),        # 0.6B gate_up at batch 64 (1-CTA tiles)
+    (1, 128, 64, 0, 0),
+    (100, 1008, 192, 2064, 1),     # ragged: last 64-wide tile holds 32 valid columns
+    (128, 1024, 512, 1256, 1),     # BN = 256
+    (64, 768, 512, 42096, 1),      # BN = 96, activation multicast cluster of 4
+    (256, 12288, 4096, 0, 0),      # 8B gate_up at batch 256 (pair kernel, schedule chosen)
+    (256, 1600, 1024, 512, 2),     # pair kernel, split-K 2 (32B/TP8-like shard), ragged last tile
+    (300, 512, 448, 512, 3),       # pair kernel, split-K 3, ragged M
+    (256, 704, 256, 512, 1352),    # wide pair tile: unit straddles the two accumulators
+    (2048, 3072, 1024, 0, 0),      # prefill-sized, persistent pair schedule
+]
+
+
+@pytest.mark.parametrize("M,I,K,bn,splits", SILU_SHAPES)
+def test_gemm_silu_mul_fused(ctx, M, I, K, bn, splits):
+    """K3 + K6 fused: the oracle computes silu(x Wg^T) * (x Wu^T) in fp32 (qwen3.rs:323-327, activation.rs:13-18)."""
+    g = torch.Generator().manual_seed(M * 17 + I * 3 + K)
+    a = torch.randn(M, K, generator=g).to(BF16)
+    w = (torch.randn(2 * I, K, generator=g) / math.sqrt(K)).to(BF16)
+    gu = O.linear(a.float(), w.float())
+    ref = O.silu_and_mul(gu)
+    out = ctx.gemm_silu_mul(a.cuda(), ctx.interleave_gate_up(w.cuda()), force_bn=bn, force_splits=splits)
+    torch.cuda.synchronize()
+    _close(out, ref, 2e-3, 2 ** -8, f"gemm+silu_mul M={M} I={I} K={K} bn={bn} s={splits}")
 
 
 def test_gemm_pair_split_determinism(ctx):

@@ -102,14 +102,14 @@ def trace_pair(M, N, K, splits):
     torch.cuda.synchronize()
     t = t.cpu().tolist()
     t0 = t[0]
-    kb = min(32, K // 64 // max(splits, 1))
+    kb = min(32, K // 64 // (splits if 1 <= splits <= 4 else 1))
     print(f"pair trace M={M} N={N} K={K} splits={splits} (cycles from kernel start, CTA 0)")
     print("  cluster set up    ", t[1] - t0, " pdl wait done", t[2] - t0)
     print("  tma issued  kb:   ", [t[3 + i] - t0 for i in range(kb)])
     print("  full waited kb:   ", [t[40 + i] - t0 for i in range(kb)])
     print("  mma all committed ", t[80] - t0)
     print("  epilogue start    ", t[81] - t0)
-    if splits > 1:
+    if 1 < splits <= 4:
         print("  partials parked   ", t[82] - t0, " cluster barrier passed", t[85] - t0)
     print("  epilogue end      ", t[83] - t0)
     print("  kernel end        ", t[84] - t0)
@@ -137,8 +137,9 @@ if __name__ == "__main__":
         for (M, N, K) in shapes:
             us, tf = bench_cublas(M, N, K)
             print(f"{M:6d} {N:6d} {K:6d} cuBLAS                 -> {us:9.2f} us {tf:8.1f} TF/s", flush=True)
-            for bn, sp in [(2064, 1), (2128, 1), (1256, 1), (512, 0), (512, 1), (512, 2), (512, 3), (512, 4)]:
-                if M > 512 and (bn == 2064 or sp > 1):
+            for bn, sp in [(2064, 1), (2128, 1), (1256, 1), (512, 0), (512, 1), (512, 2), (512, 3), (512, 4),
+                           (512, 1320), (512, 1352), (512, 1384), (512, 1448), (512, 1512)]:
+                if (M > 512 and (bn == 2064 or sp > 1)) or (sp > 1000 and -(-N // (sp - 1000)) * -(-M // 256) > 74):
                     continue
                 try:
                     us, gbs, tf = bench(M, N, K, bn, sp)
@@ -148,6 +149,7 @@ if __name__ == "__main__":
         for sp in (1, 2, 3):
             trace_pair(256, 4096, 4096, sp)
         trace_pair(256, 24576, 4096, 1)
+        trace_pair(256, 24576, 4096, 1352)
         sys.exit(0)
     if "--ks" in sys.argv:          # cluster split-K (DSMEM) for the narrow decode GEMMs vs the plain tiles vs cuBLAS
         for (M, N, K) in [(64, 1024, 2048), (64, 1024, 3072), (64, 4096, 1024), (64, 6144, 1024), (1, 1024, 2048),

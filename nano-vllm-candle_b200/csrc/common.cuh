@@ -47,6 +47,7 @@ struct nvc_ctx {
   size_t gemm_ws_bytes = 0;
   int* gemm_counters = nullptr;
   int gemm_num_counters = 0;
+  int* pd_counters = nullptr;   // arrival tickets of the work-balanced paged decode kernel (zero between launches)
   int pair_clusters[5] = {0, 0, 0, 0, 0};   // co-resident clusters of 2S CTAs of the pair GEMM, S = 1..4
   // tensor-parallel communicator (NULL when tp_size == 1)
   nvc_nccl_api* nccl = nullptr;

@@ -98,6 +98,7 @@ extern "C" int nvc_ctx_create(int device, int tp_rank, int tp_size, nvc_ctx** ou
     nvc_set_error(nullptr, "nvc_ctx_create: kernel attribute setup failed: " + ctx->last_error);
     cudaFree(ctx->gemm_ws);
     cudaFree(ctx->gemm_counters);
+    if (ctx->pd_counters) cudaFree(ctx->pd_counters);
     delete ctx;
     return rc;
   }
@@ -114,6 +115,7 @@ extern "C" int nvc_ctx_destroy(nvc_ctx* ctx) {
   nvc_collectives_destroy(ctx);
   if (ctx->gemm_ws) cudaFree(ctx->gemm_ws);
   if (ctx->gemm_counters) cudaFree(ctx->gemm_counters);
+  if (ctx->pd_counters) cudaFree(ctx->pd_counters);
   delete ctx;
   return NVC_OK;
 }

@@ -260,3 +260,72 @@ def test_paged_decode_attn(ctx, nh, kv, block_size, ctx_lens):
     torch.cuda.synchronize()
     assert not torch.isnan(out.float()).any(), "poisoned (unwritten) cache slots leaked into the output"
     _close(out, ref, 1e-2, 2 ** -7, f"paged decode nh={nh} kv={kv} bs={block_size} ctx={ctx_lens}")
+
+
+def _paged_case(nh, kv, block_size, ctx_lens, seed):
+    """random paged KV cache (poisoned where unwritten) + the oracle's attention of q over each sequence's cache"""
+    hd = 128
+    B = len(ctx_lens)
+    g = torch.Generator().manual_seed(seed)
+    nblk_per = [(c + block_size - 1) // block_size for c in ctx_lens]
+    total_blk = sum(nblk_per) + 3
+    perm = torch.randperm(total_blk, generator=g)
+    bt = torch.full((B, max(max(nblk_per), 1)), -1, dtype=torch.int32)
+    kc = torch.full((total_blk * block_size, kv, hd), float("nan")).to(BF16)
+    vc = torch.full((total_blk * block_size, kv, hd), float("nan")).to(BF16)
+    q = torch.randn(B, nh, hd, generator=g).to(BF16)
+    ref = torch.zeros(B, nh * hd)
+    scale = hd ** -0.5
+    p = 0
+    for b, c in enumerate(ctx_lens):
+        blocks = perm[p:p + nblk_per[b]]; p += nblk_per[b]
+        bt[b, :len(blocks)] = blocks.to(torch.int32)
+        if c == 0:
+            continue
+        k = torch.randn(c, kv, hd, generator=g).to(BF16)
+        v = torch.randn(c, kv, hd, generator=g).to(BF16)
+        t = torch.arange(c)
+        slots = blocks[t // block_size] * block_size + t % block_size
+        kc[slots], vc[slots] = k, v
+        kh = O.gqa_expand(k.permute(1, 0, 2)[None].float(), nh // kv)[0]
+        vh = O.gqa_expand(v.permute(1, 0, 2)[None].float(), nh // kv)[0]
+        sc = torch.einsum("hd,htd->ht", q[b].float(), kh) * scale
+        ref[b] = torch.einsum("ht,htd->hd", torch.softmax(sc, dim=-1), vh).reshape(-1)
+    return q, kc, vc, bt, ref, scale
+
+
+@pytest.mark.parametrize("nh,kv,block_size,lens_spec", [
+    (16, 8, 256, ("uniform", 48, 1, 700, 1)),        # ragged batch: CTA ranges cross many (kv head, sequence) pairs
+    (16, 8, 256, ("const", 64, 581)),                # the bench shape: 512 pairs of 10 tiles on 296 CTAs
+    (32, 8, 64, ("uniform", 20, 60, 3000, 2)),       # long ragged contexts: pairs cut between several CTAs
+    (8, 1, 256, ("uniform", 100, 1, 300, 3)),        # one kv head (a TP=8 shard), group 8
+    (16, 8, 256, ("list", [300, 0, 5, 0, 129])),     # empty sequences: zero rows, no ticket taken
+    (40, 8, 16, ("uniform", 9, 1, 200, 4)),          # group 5, small blocks
+])
+def test_paged_decode_balanced(ctx, nvc, nh, kv, block_size, lens_spec):
+    """work-balanced paged decode (flat item ranges + last-arriver merge) against the oracle, twice:
+    the second call proves that the arrival tickets were re-armed and that the merge order is deterministic"""
+    if lens_spec[0] == "uniform":
+        _, n, lo, hi, seed = lens_spec
+        lens = torch.randint(lo, hi + 1, (n,), generator=torch.Generator().manual_seed(seed)).tolist()
+    elif lens_spec[0] == "const":
+        lens = [lens_spec[2]] * lens_spec[1]
+    else:
+        lens = lens_spec[1]
+    q, kc, vc, bt, ref, scale = _paged_case(nh, kv, block_size, lens, 7 + len(lens))
+    B = len(lens)
+    args = (q.reshape(B, nh * 128).cuda(), kc.cuda(), vc.cuda(), bt.cuda(), torch.tensor(lens, dtype=torch.int32).cuda(),
+            nh, kv, 128, block_size, scale)
+    nvc.lib().nvc_debug_set(1, 1)            # opt into the work-balanced kernel (off by default: see paged_decode.cu)
+    try:
+        o1 = ctx.paged_decode_attn(*args).clone()
+        o2 = ctx.paged_decode_attn(*args).clone()
+        torch.cuda.synchronize()
+    finally:
+        nvc.lib().nvc_debug_set(1, 0)
+    o3 = ctx.paged_decode_attn(*args)        # the default per-(head, sequence) grid on the same case
+    torch.cuda.synchronize()
+    _close(o3, ref, 1e-2, 2 ** -7, f"default paged decode nh={nh} kv={kv} bs={block_size} B={B}")
+    assert not torch.isnan(o1.float()).any(), "poisoned (unwritten) cache slots leaked into the output"
+    _close(o1, ref, 1e-2, 2 ** -7, f"balanced paged decode nh={nh} kv={kv} bs={block_size} B={B}")
+    assert torch.equal(o1, o2), "balanced paged decode must be bit-identical between launches"

@@ -319,23 +319,36 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     // no global workspace, no atomics.
     ptx::cluster_sync_all();             // all partials parked (release / acquire at cluster scope)
     if (warp >= 2) {
-      const int r = (warp & 3) * 32 + lane;
-      const int grow = m_tile * BM + r;
-      if (grow < M) {
-        for (int g = split; g < BN / 4; g += num_splits) {
-          const int n0 = n_tile * BN + g * 4;
-          if (n0 >= N) break;
-          const uint32_t mine = smem_base + (uint32_t)((g * BM + r) * 16);
-          // request every split's copy before the first add: one DSMEM round trip per column group
-          float4 t[8];
+      // work items = (owned column group, valid row), spread over all 128 epilogue threads (the partials sit in
+      // shared memory, so any thread can sum any element; consecutive threads take consecutive rows of a group:
+      // contiguous DSMEM reads).  Two items per round trip: DSMEM latency, not bandwidth, bounds this phase.
+      const int et = threadIdx.x - 64;
+      const int rows_valid = min(BM, M - m_tile * BM);
+      const int cols_valid = min(BN, N - n_tile * BN);
+      const int owned = (BN / 4 - split + num_splits - 1) / num_splits;        // groups split, split + S, ...
+      const int items = owned * rows_valid;
+      for (int i0 = et; i0 < items; i0 += 2 * kEpilogueThreads) {
+        float4 t[2][8];
+        int rr[2], gg[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int idx = min(i0 + u * kEpilogueThreads, items - 1);           // clamped: a redundant load, no branch
+          const int gk = idx / rows_valid;
+          rr[u] = idx - gk * rows_valid;
+          gg[u] = split + gk * num_splits;
+          const uint32_t mine = smem_base + (uint32_t)((gg[u] * BM + rr[u]) * 16);
 #pragma unroll
           for (int z = 0; z < 8; ++z)
-            if (z < num_splits) t[z] = ptx::ld_cluster_f4(ptx::mapa_u32(mine, (uint32_t)z));
+            if (z < num_splits) t[u][z] = ptx::ld_cluster_f4(ptx::mapa_u32(mine, (uint32_t)z));
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          if (i0 + u * kEpilogueThreads >= items || gg[u] * 4 >= cols_valid) continue;
           float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-          for (int z = 0; z < 8; ++z)
-            if (z < num_splits) { acc.x += t[z].x; acc.y += t[z].y; acc.z += t[z].z; acc.w += t[z].w; }
-          const int64_t o = (int64_t)grow * ldc + n0;
+          for (int z = 0; z < 8; ++z)                                          // split order: deterministic
+            if (z < num_splits) { acc.x += t[u][z].x; acc.y += t[u][z].y; acc.z += t[u][z].z; acc.w += t[u][z].w; }
+          const int64_t o = (int64_t)(m_tile * BM + rr[u]) * ldc + n_tile * BN + gg[u] * 4;
           if (out_f32) {
             *reinterpret_cast<float4*>(reinterpret_cast<float*>(C) + o) = acc;
           } else {
@@ -419,32 +432,47 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
 //  * decode (M <= 128): one wave, as many CTAs as the N dimension gives (up to ~all SMs), several
 //    k-blocks per pipeline stage; split-K through the L2 workspace costs >= 6 us (ticket atomic +
 //    reduction round trips) and never won in the sweep, so it is only used when forced.
-void choose_config(const nvc_ctx* ctx, int M, int N, int K, int* bn_out, int* kps_out, int* splits_out, int* cl_out,
-                   int* ks_out) {
+void choose_config(const nvc_ctx* ctx, int M, int N, int K, bool allow_split, int* bn_out, int* kps_out, int* splits_out,
+                   int* cl_out, int* ks_out) {
   *splits_out = 1;
   *cl_out = 1;
   *ks_out = 0;
-  if (M <= BM && g_nvc_gemm_ks && (N + 31) / 32 <= 48 && K >= 1024) {
-    // narrow, deep decode GEMM (o_proj / down_proj of the small models): too few n-tiles to stream the
-    // weights from more than ~32 SMs -> split K inside clusters (1,1,S), partials reduced over DSMEM
-    const int tiles = (N + 31) / 32;
-    int s = 8;
-    while (s > 1 && (tiles * s > 160 || K / BK / s < 4)) s >>= 1;
-    if (s > 1) {
-      *bn_out = 32;
-      *kps_out = 4;
-      *splits_out = s;
-      *ks_out = 1;
-      return;
-    }
-  }
   if (M <= BM) {
-    int bn = 32;
-    const int cands[3] = {256, 128, 64};
-    for (int i = 0; i < 3; ++i)
-      if ((N + cands[i] - 1) / cands[i] >= 96) { bn = cands[i]; break; }
-    *bn_out = bn;
-    *kps_out = bn == 256 ? 1 : (bn == 128 ? 2 : 4);
+    // Decode (one m-tile).  Cycle model fitted to CTA phase traces (tools/gemm_microbench.py --trace-decode):
+    // the TMA unit of an SM moves ~90 B/clk plus ~30 cycles per box (two loads + one L2 prefetch per k-block),
+    // whatever the source (the L2 prefetch before the PDL wait hides HBM), and the activation rows are re-read
+    // by every n-tile, so a k-block costs (rows + BN) * 128 / 90 + 90 cycles; ~2200 cycles of prologue +
+    // first-load latency; epilogue 300 + 6 * BN, or, with split-K inside a cluster (1,1,S), ~2300 + the DSMEM
+    // exchange at ~17 B/clk.  The winners are always ONE wave of ~96-132 CTAs with the widest tile that allows it
+    // (co-resident: 148 CTAs, 74 clusters of 2, 33 clusters of 4).
+    const int rows = ((M + 7) / 8) * 8;
+    const int kb = K / BK;
+    const int bns[4] = {32, 64, 128, 256};
+    const int ss[3] = {1, 2, 4};
+    double best = 1e30;
+    int best_bn = 32, best_s = 1;
+    const double hbm_floor = (double)N * K * 2 / 3400.0 + 3000.0;     // 6.5 TB/s at 1.9 GHz
+    for (int i = 0; i < 4; ++i) {
+      for (int j = 0; j < 3; ++j) {
+        const int bn = bns[i], S = ss[j];
+        if (S > 1 && (!allow_split || !g_nvc_gemm_ks || kb / S < 4)) continue;
+        if (bn / 2 >= N) continue;
+        const int tiles = (N + bn - 1) / bn;
+        const int cap = S == 1 ? ctx->num_sms : (S == 2 ? 2 * (ctx->pair_clusters[1] > 0 ? ctx->pair_clusters[1] : ctx->num_sms / 2)
+                                                       : 4 * (ctx->pair_clusters[2] > 0 ? ctx->pair_clusters[2] : ctx->num_sms / 5));
+        const double waves = ceil((double)tiles * S / cap);
+        const double per_kb = (double)(rows + bn) * 128.0 / 90.0 + 90.0;
+        const double tail = S == 1 ? 300.0 + 6.0 * bn : 2300.0 + (double)(S - 1) * rows * (bn / S) * 4.0 / 17.0;
+        const double t = waves * (2200.0 + per_kb * ((kb + S - 1) / S) + tail);
+        // below the HBM floor every candidate takes the floor: rank those by the modeled CTA time (most slack)
+        const double key = t > hbm_floor ? t : hbm_floor * (1.0 + 1e-3 * t / hbm_floor);
+        if (key < best * 0.98 || (key < best && t < hbm_floor)) { best = key; best_bn = bn; best_s = S; }
+      }
+    }
+    *bn_out = best_bn;
+    *kps_out = best_bn == 256 ? 1 : (best_bn == 128 ? 2 : 4);
+    *splits_out = best_s;
+    *ks_out = best_s > 1 ? 1 : 0;
     return;
   }
   const int kb = K / BK;
@@ -497,7 +525,7 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   if (force_bn == 512 || (force_bn == 0 && M > BM && g_nvc_gemm_pair))
     return nvc_gemm_pair(ctx, A, lda, W, C, ldc, out_dtype == NVC_DT_F32, M, Nout, K, force_splits, epi, stream, trace);
   int bn, kps, splits, cl = 1, ks = 0;
-  choose_config(ctx, M, Nout, K, &bn, &kps, &splits, &cl, &ks);
+  choose_config(ctx, M, Nout, K, epi == NVC_EPI_NONE, &bn, &kps, &splits, &cl, &ks);
   if (force_bn) {          // force_bn = BN + 1000 * KPS + 10000 * CL (KPS 0: the first instantiation of that BN)
     bn = force_bn % 1000;
     kps = (force_bn / 1000) % 10;

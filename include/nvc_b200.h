@@ -176,6 +176,19 @@ int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_
                             int total_tokens, int max_seqlen, int nh, int kv, int hd, float scale,
                             nvc_bf16* out, void* stream);
 
+/* K4 (paged). The same kernel for sequences with a cached prefix (prefix caching, SURVEY.md 8f.1;
+ * upstream nano-vllm passes block_table to flash_attn_varlen_func for this): q rows of sequence b
+ * are the LAST q_len_b = cu_seqlens_q[b+1] - cu_seqlens_q[b] positions of a context of
+ * context_lens[b] tokens whose K / V are read from the paged cache through block_tables
+ * [B, bt_stride] (this step's k / v must already be stored there).  Causal: q row i sees keys
+ * 0 .. context_lens[b] - q_len_b + i.  Cache rows past the context may hold anything (NaN included).
+ * block_size in {16, 32, 64} or a multiple of 128. */
+int nvc_prefill_attn_paged(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
+                           const nvc_bf16* v_cache, const int32_t* block_tables, int bt_stride,
+                           const int32_t* context_lens, const int32_t* cu_seqlens_q, int B,
+                           int total_q_tokens, int max_seqlen_q, int nh, int kv, int hd, int block_size,
+                           int num_blocks, float scale, nvc_bf16* out, void* stream);
+
 /* K5. Decode: paged attention over block_tables (N2) with GQA head grouping.
  * q: [B, nh, hd] row stride ldq; caches [num_blocks, block_size, kv, hd];
  * block_tables: i32 [B, max_blocks] (-1 padded); context_lens: i32 [B] (tokens in the cache

@@ -72,6 +72,13 @@ int nvc_runner_finalize(nvc_runner* r);
  * src/engine/llm_engine.rs:135-142). */
 int nvc_runner_prefill(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* cu_seqlens,
                        const int32_t* slot_mapping, int B, int N, int max_seqlen, int32_t* out_tokens);
+/* Prefill step whose sequences may have a cached prefix (prefix caching): the N new
+ * tokens of sequence b are positions context_lens[b] - q_len_b .. context_lens[b] - 1 and attend
+ * to ALL context_lens[b] tokens, read from the paged cache through block_tables [B, max_blocks]
+ * (the new tokens' K/V are scattered to slot_mapping first, as in every step). */
+int nvc_runner_prefill_paged(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* cu_seqlens,
+                             const int32_t* slot_mapping, const int32_t* block_tables, int max_blocks,
+                             const int32_t* context_lens, int B, int N, int max_seqlen, int32_t* out_tokens);
 /* One decode step: one new token per sequence, attention over the paged cache. */
 int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* slot_mapping,
                       const int32_t* block_tables, int max_blocks, const int32_t* context_lens, int B,
@@ -103,6 +110,10 @@ typedef struct nvc_scheduler_config {
   int32_t eos;
   int32_t num_kvcache_blocks;
   int32_t kvcache_block_size;
+  /* Beyond the reference; 0 = the reference's behaviour. */
+  int32_t enable_prefix_caching;   /* 8f.1: hash-chained dedup of full KV blocks (upstream nano-vllm's
+                                      BlockManager, which block_manager.rs:24-29 says it will mirror)     */
+  int32_t reserved[3];
 } nvc_scheduler_config;
 
 typedef struct nvc_schedule_info {
@@ -148,6 +159,8 @@ int nvc_engine_get_output(const nvc_engine* e, int64_t seq_id, int32_t* tokens, 
 /* Introspection for the contract tests. */
 int nvc_engine_seq_block_table(const nvc_engine* e, int64_t seq_id, int32_t* blocks, int capacity, int* n_blocks);
 int nvc_engine_num_free_blocks(const nvc_engine* e);
+/* Prefix cache counters in blocks: full blocks looked up / found by BlockManager::allocate. */
+int nvc_engine_prefix_cache_stats(const nvc_engine* e, int64_t* hit_blocks, int64_t* queried_blocks);
 int nvc_engine_num_waiting(const nvc_engine* e);
 int nvc_engine_num_running(const nvc_engine* e);
 

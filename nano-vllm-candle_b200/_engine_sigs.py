@@ -21,7 +21,8 @@ class RunnerOptionsC(C.Structure):
 
 class SchedulerConfigC(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("max_num_seqs", "max_num_batched_tokens", "eos",
-                                         "num_kvcache_blocks", "kvcache_block_size")]
+                                         "num_kvcache_blocks", "kvcache_block_size",
+                                         "enable_prefix_caching")] + [("reserved", C.c_int32 * 3)]
 
 
 class ScheduleInfoC(C.Structure):
@@ -39,6 +40,7 @@ def declare(l: C.CDLL) -> None:
         "nvc_runner_load_weight": [_vp, C.c_char_p, _vp, _i64, _i64],
         "nvc_runner_finalize": [_vp],
         "nvc_runner_prefill": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+        "nvc_runner_prefill_paged": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp],
         "nvc_runner_decode": [_vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp],
         "nvc_runner_last_logits": [_vp, _vp, _i],
         "nvc_runner_time_decode": [_vp, _i, C.POINTER(C.c_float), C.POINTER(C.c_int)],
@@ -55,6 +57,7 @@ def declare(l: C.CDLL) -> None:
         "nvc_engine_get_output": [_vp, _i64, _vp, _i, C.POINTER(C.c_int)],
         "nvc_engine_seq_block_table": [_vp, _i64, _vp, _i, C.POINTER(C.c_int)],
         "nvc_engine_num_free_blocks": [_vp],
+        "nvc_engine_prefix_cache_stats": [_vp, C.POINTER(C.c_int64), C.POINTER(C.c_int64)],
         "nvc_engine_num_waiting": [_vp],
         "nvc_engine_num_running": [_vp],
     }

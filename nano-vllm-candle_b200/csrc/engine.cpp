@@ -17,6 +17,7 @@
 #include <map>
 #include <memory>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "../../include/nvc_b200_engine.h"
@@ -53,27 +54,133 @@ struct Sequence {
 };
 using SeqPtr = std::shared_ptr<Sequence>;
 
+// One KV block's book-keeping for prefix caching (upstream nano-vllm's Block: ref_count, hash,
+// token_ids).  Without prefix caching only ref_count is used.
+struct Block {
+  int ref_count = 0;
+  bool has_hash = false;
+  uint64_t hash = 0;
+  std::vector<int32_t> token_ids;
+};
+
+// 64-bit chained block hash: FNV-1a over (prefix hash, token ids) + a splitmix finaliser.  The
+// reference reserves `ahash` for this (Cargo.toml:19-22), whose values are not portable; only
+// equality of hashes is observable, and a hit is confirmed by comparing the token ids.
+uint64_t chain_hash(const int32_t* toks, size_t n, bool has_prefix, uint64_t prefix) {
+  uint64_t h = 0xcbf29ce484222325ull;
+  auto eat = [&h](uint64_t v, int bytes) {
+    for (int i = 0; i < bytes; ++i) {
+      h ^= (v >> (8 * i)) & 0xffu;
+      h *= 0x100000001b3ull;
+    }
+  };
+  if (has_prefix) eat(prefix, 8);
+  for (size_t i = 0; i < n; ++i) eat((uint32_t)toks[i], 4);
+  h ^= h >> 30; h *= 0xbf58476d1ce4e5b9ull;
+  h ^= h >> 27; h *= 0x94d049bb133111ebull;
+  h ^= h >> 31;
+  return h;
+}
+
+// FIFO of free block ids with O(1) removal from the middle (a cached block that is free is
+// revived in place): doubly linked through prev/next arrays.
+struct FreeList {
+  std::vector<int32_t> prev, next;
+  std::vector<uint8_t> in;
+  int32_t head = -1, tail = -1;
+  size_t count = 0;
+  explicit FreeList(int n) : prev(n, -1), next(n, -1), in(n, 0) {}
+  size_t size() const { return count; }
+  int32_t front() const { return head; }
+  void push_back(int32_t b) {
+    prev[b] = tail; next[b] = -1;
+    if (tail >= 0) next[tail] = b; else head = b;
+    tail = b; in[b] = 1; ++count;
+  }
+  void remove(int32_t b) {
+    if (prev[b] >= 0) next[prev[b]] = next[b]; else head = next[b];
+    if (next[b] >= 0) prev[next[b]] = prev[b]; else tail = prev[b];
+    prev[b] = next[b] = -1; in[b] = 0; --count;
+  }
+};
+
+// BlockManager (block_manager.rs:31-99).  The reference's is an admitted stub (:24-29); this one
+// keeps its method set and follows upstream nano-vllm's allocator, which the reference says its
+// API mirrors: FIFO free list, ref-counted blocks and - when `prefix_caching` is on -
+// hash-chained dedup of FULL blocks.  One rule is added to upstream's: a block is taken from the
+// cache only if at least one token of the sequence is left to compute ((i+1)*block_size < len),
+// otherwise a fully cached prompt would schedule a prefill step with no query tokens.
 struct BlockManager {
   int num_blocks_;
   int block_size_;
-  std::deque<int32_t> free_;
+  bool prefix_caching;
+  std::vector<Block> blocks;
+  FreeList free_;
+  std::unordered_map<uint64_t, int32_t> hash_to_block;
+  int64_t cache_hits = 0, cache_queries = 0;   // in blocks
 
-  BlockManager(int num_blocks, int block_size) : num_blocks_(num_blocks), block_size_(block_size) {
+  BlockManager(int num_blocks, int block_size, bool prefix)
+      : num_blocks_(num_blocks), block_size_(block_size), prefix_caching(prefix), blocks(num_blocks), free_(num_blocks) {
     for (int i = 0; i < num_blocks; ++i) free_.push_back(i);
   }
   int block_size() const { return block_size_; }
   int num_blocks() const { return num_blocks_; }
+
+  Block& take(int32_t id) {            // upstream _allocate_block
+    Block& b = blocks[id];
+    b.ref_count = 1;
+    b.has_hash = false;
+    b.token_ids.clear();
+    free_.remove(id);
+    return b;
+  }
+  void set_hash(int32_t id, uint64_t h, const int32_t* toks, size_t n) {
+    Block& b = blocks[id];
+    b.has_hash = true;
+    b.hash = h;
+    b.token_ids.assign(toks, toks + n);
+    hash_to_block[h] = id;
+  }
+
   bool can_allocate(const Sequence& s) const { return free_.size() >= s.num_blocks(); }
   void allocate(Sequence& s) {
     s.block_table.clear();
-    for (size_t i = 0; i < s.num_blocks(); ++i) {
-      s.block_table.push_back(free_.front());
-      free_.pop_front();
+    s.num_cached_tokens = 0;
+    const size_t bs = (size_t)block_size_, nb = s.num_blocks();
+    bool has_h = false, miss = !prefix_caching;
+    uint64_t h = 0;
+    for (size_t i = 0; i < nb; ++i) {
+      const int32_t* toks = s.token_ids.data() + i * bs;
+      const size_t n = std::min(bs, s.num_tokens - i * bs);
+      int32_t id = -1;
+      if (prefix_caching) {
+        if (n == bs) { h = chain_hash(toks, n, has_h, h); has_h = true; } else { has_h = false; }
+        if (has_h) {
+          ++cache_queries;
+          auto it = hash_to_block.find(h);
+          if (it != hash_to_block.end()) id = it->second;
+        }
+        if (id < 0 || !blocks[id].has_hash || blocks[id].hash != h || blocks[id].token_ids.size() != n ||
+            !std::equal(toks, toks + n, blocks[id].token_ids.begin()) || (i + 1) * bs >= s.num_tokens)
+          miss = true;
+      }
+      if (miss) {
+        id = free_.front();
+        take(id);
+      } else {
+        ++cache_hits;
+        s.num_cached_tokens += bs;
+        if (free_.in[id]) take(id); else blocks[id].ref_count += 1;
+      }
+      if (prefix_caching && has_h) set_hash(id, h, toks, n);
+      s.block_table.push_back(id);
     }
-    s.num_cached_tokens = 0;   // no prefix cache: nothing of this sequence is cached yet
   }
   void deallocate(Sequence& s) {
-    for (auto it = s.block_table.rbegin(); it != s.block_table.rend(); ++it) free_.push_back(*it);
+    for (auto it = s.block_table.rbegin(); it != s.block_table.rend(); ++it) {
+      Block& b = blocks[*it];
+      if (--b.ref_count == 0) free_.push_back(*it);   // keeps its hash: still a cache candidate until re-taken
+    }
     s.block_table.clear();
     s.num_cached_tokens = 0;
   }
@@ -81,9 +188,22 @@ struct BlockManager {
     return free_.size() >= (size_t)((s.len() % block_size_ == 1) ? 1 : 0);
   }
   void may_append(Sequence& s) {
-    if (s.len() % block_size_ == 1 && s.block_table.size() < s.num_blocks()) {
-      s.block_table.push_back(free_.front());
-      free_.pop_front();
+    const size_t bs = (size_t)block_size_;
+    if (s.len() % bs == 1 && s.block_table.size() < s.num_blocks()) {
+      const int32_t id = free_.front();
+      take(id);
+      s.block_table.push_back(id);
+    } else if (prefix_caching && s.len() % bs == 0 && !s.block_table.empty()) {
+      // the last block becomes full with this step's token: register it (upstream may_append)
+      const int32_t id = s.block_table.back();
+      if (!blocks[id].has_hash) {
+        const size_t nb = s.block_table.size();
+        const bool has_prefix = nb > 1 && blocks[s.block_table[nb - 2]].has_hash;
+        if (nb == 1 || has_prefix) {
+          const int32_t* toks = s.token_ids.data() + (nb - 1) * bs;
+          set_hash(id, chain_hash(toks, bs, has_prefix, has_prefix ? blocks[s.block_table[nb - 2]].hash : 0), toks, bs);
+        }
+      }
     }
   }
 };
@@ -97,7 +217,7 @@ struct Scheduler {
 
   explicit Scheduler(const nvc_scheduler_config& c)
       : max_num_seqs(c.max_num_seqs), max_num_batched_tokens(c.max_num_batched_tokens),
-        block_manager(c.num_kvcache_blocks, c.kvcache_block_size), eos(c.eos) {}
+        block_manager(c.num_kvcache_blocks, c.kvcache_block_size, c.enable_prefix_caching != 0), eos(c.eos) {}
 
   bool is_finished() const { return waiting.empty() && running.empty(); }
   void add(const SeqPtr& s) { waiting.push_back(s); }
@@ -367,8 +487,15 @@ int nvc_engine_step(nvc_engine* e, nvc_step_output* out) {
   if (e->runner == nullptr) {
     for (int i = 0; i < B; ++i) e->out_tokens[i] = e->batch[i]->last_token + 1;   // DummyModelRunner
   } else if (e->batch_is_prefill) {
-    rc = nvc_runner_prefill(e->runner, e->ids.data(), e->positions.data(), e->cu_seqlens.data(),
-                            e->slot_mapping.data(), B, (int)e->ids.size(), e->max_seqlen, e->out_tokens.data());
+    bool cached_prefix = false;   // some sequence skips a cached prefix: attention must read it from the paged cache
+    for (auto& s : e->batch) cached_prefix |= s->num_cached_tokens > 0;
+    if (cached_prefix)
+      rc = nvc_runner_prefill_paged(e->runner, e->ids.data(), e->positions.data(), e->cu_seqlens.data(),
+                                    e->slot_mapping.data(), e->block_tables.data(), e->max_blocks, e->context_lens.data(),
+                                    B, (int)e->ids.size(), e->max_seqlen, e->out_tokens.data());
+    else
+      rc = nvc_runner_prefill(e->runner, e->ids.data(), e->positions.data(), e->cu_seqlens.data(),
+                              e->slot_mapping.data(), B, (int)e->ids.size(), e->max_seqlen, e->out_tokens.data());
   } else {
     rc = nvc_runner_decode(e->runner, e->ids.data(), e->positions.data(), e->slot_mapping.data(),
                            e->block_tables.data(), e->max_blocks, e->context_lens.data(), B, e->out_tokens.data());
@@ -443,6 +570,12 @@ int nvc_engine_seq_block_table(const nvc_engine* e, int64_t seq_id, int32_t* blo
 }
 
 int nvc_engine_num_free_blocks(const nvc_engine* e) { return e ? (int)e->scheduler.block_manager.free_.size() : 0; }
+int nvc_engine_prefix_cache_stats(const nvc_engine* e, int64_t* hit_blocks, int64_t* queried_blocks) {
+  if (!e) return NVC_EINVAL;
+  if (hit_blocks) *hit_blocks = e->scheduler.block_manager.cache_hits;
+  if (queried_blocks) *queried_blocks = e->scheduler.block_manager.cache_queries;
+  return NVC_OK;
+}
 int nvc_engine_num_waiting(const nvc_engine* e) { return e ? (int)e->scheduler.waiting.size() : 0; }
 int nvc_engine_num_running(const nvc_engine* e) { return e ? (int)e->scheduler.running.size() : 0; }
 

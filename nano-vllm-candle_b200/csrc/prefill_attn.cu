@@ -13,6 +13,13 @@
 //              P -> bf16 -> swizzled smem (A operand of the second MMA), then
 //              acc = acc * alpha + O_j with the output accumulator in registers
 // FLOPs per (sequence, head): 4 * 128 * T^2 / 2 (causal).
+//
+// kPaged = true (prefix caching): the q rows of sequence b are its LAST q_len
+// positions of a context of context_lens[b] tokens; K / V tiles are read from the paged cache
+// through block_tables (one TMA box per block, or per 128 tokens when block_size >= 128), after
+// qk_norm_rope_store has scattered this step's k / v there.  Cache rows past the context may
+// be uninitialised memory: their S columns are masked by the causal rule and their V rows are
+// zeroed in shared memory before the P V product (0 * NaN would poison the row).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "internal.h"
@@ -43,10 +50,20 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
+struct PagedKV {                              // kPaged only
+  const int32_t* block_tables;                // [B, bt_stride], -1 padded
+  const int32_t* context_lens;                // [B]
+  int bt_stride;
+  int block_size;
+  int box_rows;                               // token rows per K / V TMA box = min(128, block_size)
+};
+
+template <bool kPaged>
 __global__ void __launch_bounds__(kThreads, 1)
 prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
                     const __grid_constant__ CUtensorMap tma_v, const int32_t* __restrict__ cu_seqlens,
-                    int nh, int group, float scale_log2e, nvc_bf16* __restrict__ out, int v_lbo, int v_sbo) {
+                    int nh, int group, float scale_log2e, nvc_bf16* __restrict__ out, int v_lbo, int v_sbo,
+                    const PagedKV pk) {
   const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
   pdl_trigger();
   pdl_wait();      // cu_seqlens is read right away, so there is no prologue to overlap here
@@ -54,7 +71,11 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
   const int seq_len = __ldg(cu_seqlens + b + 1) - seq_start;
   if (qt * 128 >= seq_len) return;            // whole CTA exits before any allocation
   const int kvh = h / group;
-  const int n_tiles = qt + 1;                 // causal: kv tiles 0..qt
+  // kPaged: q row i of the tile is context position off + qt*128 + i and sees keys 0..that position
+  const int kv_len = kPaged ? __ldg(pk.context_lens + b) : seq_len;
+  const int off = kPaged ? kv_len - seq_len : 0;
+  const int n_tiles = kPaged ? (min(kv_len, off + qt * 128 + 128) + 127) / 128
+                             : qt + 1;        // causal: kv tiles 0..qt
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -105,13 +126,31 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
       const int s = j & 1;
       ptx::mbar_wait(kv_empty(s), ((j >> 1) & 1) ^ 1u);
       if (ptx::elect_one()) {
-        ptx::mbar_arrive_expect_tx(kv_full(s), kKVStageBytes);
         const uint32_t kdst = base + kOffKV + s * kKVStageBytes, vdst = kdst + kQBytes;
-        const int row = seq_start + j * 128;
-        ptx::tma_load_3d(kdst, &tma_k, kv_full(s), 0, kvh, row);
-        ptx::tma_load_3d(kdst + 16384, &tma_k, kv_full(s), 64, kvh, row);
-        ptx::tma_load_3d(vdst, &tma_v, kv_full(s), 0, kvh, row);
-        ptx::tma_load_3d(vdst + 16384, &tma_v, kv_full(s), 64, kvh, row);
+        if constexpr (kPaged) {
+          // boxes of box_rows tokens; only those that start inside the context are loaded (the
+          // rest of the stage keeps stale bytes: masked in S, zeroed in V by the softmax warps)
+          const int rows = pk.box_rows, tok0 = j * 128;
+          const int nbox = min(128 / rows, (kv_len - tok0 + rows - 1) / rows);
+          ptx::mbar_arrive_expect_tx(kv_full(s), (uint32_t)(nbox * rows * 512));   // K + V, two 64-wide halves each
+          const int32_t* bt = pk.block_tables + (int64_t)b * pk.bt_stride;
+          for (int i = 0; i < nbox; ++i) {
+            const int tok = tok0 + i * rows;
+            const int slot = __ldg(bt + tok / pk.block_size) * pk.block_size + tok % pk.block_size;
+            const uint32_t o = (uint32_t)(i * rows * 128);
+            ptx::tma_load_3d(kdst + o, &tma_k, kv_full(s), 0, kvh, slot);
+            ptx::tma_load_3d(kdst + 16384 + o, &tma_k, kv_full(s), 64, kvh, slot);
+            ptx::tma_load_3d(vdst + o, &tma_v, kv_full(s), 0, kvh, slot);
+            ptx::tma_load_3d(vdst + 16384 + o, &tma_v, kv_full(s), 64, kvh, slot);
+          }
+        } else {
+          ptx::mbar_arrive_expect_tx(kv_full(s), kKVStageBytes);
+          const int row = seq_start + j * 128;
+          ptx::tma_load_3d(kdst, &tma_k, kv_full(s), 0, kvh, row);
+          ptx::tma_load_3d(kdst + 16384, &tma_k, kv_full(s), 64, kvh, row);
+          ptx::tma_load_3d(vdst, &tma_v, kv_full(s), 0, kvh, row);
+          ptx::tma_load_3d(vdst + 16384, &tma_v, kv_full(s), 64, kvh, row);
+        }
       }
       __syncwarp();
     }
@@ -175,7 +214,9 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
     for (int j = 0; j < n_tiles; ++j) {
       ptx::mbar_wait(s_full, j & 1);
       ptx::tcgen05_fence_after();
-      const bool diag = (j == qt);
+      // diag: the tile holds keys past some row's position; lim = last visible column of this row
+      const bool diag = kPaged ? (j * 128 + 127 > off + qt * 128) : (j == qt);
+      const int lim = kPaged ? off + qt * 128 + r - j * 128 : r;
       // pass 1: row max
       float mx = -INFINITY;
 #pragma unroll 1
@@ -186,7 +227,7 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           const float x = __uint_as_float(v[i]);
-          if (!diag || (c * 32 + i) <= r) mx = fmaxf(mx, x);
+          if (!diag || (c * 32 + i) <= lim) mx = fmaxf(mx, x);
         }
       }
       const float m_new = fmaxf(m, mx * scale_log2e);
@@ -202,7 +243,7 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
           const float x = __uint_as_float(v[i]) * scale_log2e - m_new;
-          p[i] = (!diag || (c * 32 + i) <= r) ? fast_exp2(x) : 0.f;
+          p[i] = (!diag || (c * 32 + i) <= lim) ? fast_exp2(x) : 0.f;
           psum += p[i];
         }
         // columns [c*32, c*32+32) = half (c>>1), 16-byte chunks ((c&1)*4 .. +4) of this row
@@ -215,6 +256,19 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
       }
       l = l * alpha + psum;
       m = m_new;
+      if constexpr (kPaged) {
+        // V rows at / past the end of the context: zero them (every P column there is 0, but the
+        // cache bytes may be NaN).  s_full(j) implies the stage's TMA has landed; the proxy fence
+        // below orders these generic stores before the P V MMA.
+        if (j * 128 + r >= kv_len) {
+          uint8_t* v_row = gen + kOffKV + (j & 1) * kKVStageBytes + kQBytes + r * 128;
+#pragma unroll
+          for (int k16 = 0; k16 < 8; ++k16) {
+            *reinterpret_cast<uint4*>(v_row + (k16 << 4)) = make_uint4(0, 0, 0, 0);
+            *reinterpret_cast<uint4*>(v_row + 16384 + (k16 << 4)) = make_uint4(0, 0, 0, 0);
+          }
+        }
+      }
       ptx::fence_proxy_async_smem();
       ptx::tcgen05_fence_before();
       ptx::mbar_arrive(p_full);
@@ -253,10 +307,10 @@ prefill_attn_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_cons
   }
 }
 
-int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, int64_t tokens, int ld) {
+int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, int64_t tokens, int ld, int box_rows = 128) {
   cuuint64_t gdim[3] = {128, (cuuint64_t)heads, (cuuint64_t)tokens};
   cuuint64_t gstr[2] = {128 * 2, (cuuint64_t)ld * 2};
-  cuuint32_t box[3] = {64, 1, 128};
+  cuuint32_t box[3] = {64, 1, (cuuint32_t)box_rows};
   cuuint32_t estr[3] = {1, 1, 1};
   CUresult r = ctx->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(base), gdim, gstr, box,
                                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -271,7 +325,8 @@ int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, 
 }  // namespace
 
 extern "C" int nvc_prefill_attn_init(nvc_ctx* ctx) {
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   return NVC_OK;
 }
 
@@ -301,8 +356,43 @@ extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq,
   int v_lbo = 16384, v_sbo = 1024;
   if (g_nvc_debug[0] == 1) { v_lbo = 1024; v_sbo = 16384; }
   dim3 grid((max_seqlen + 127) / 128, nh, B);
-  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, prefill_attn_kernel, grid, dim3(kThreads), kSmemBytes, nvc_stream(stream), tq, tk, tv,
-                                 cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out, v_lbo, v_sbo));
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, prefill_attn_kernel<false>, grid, dim3(kThreads), kSmemBytes, nvc_stream(stream), tq, tk, tv,
+                                 cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out, v_lbo, v_sbo, PagedKV{}));
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
+  return NVC_OK;
+}
+
+extern "C" int nvc_prefill_attn_paged(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
+                                      const nvc_bf16* v_cache, const int32_t* block_tables, int bt_stride,
+                                      const int32_t* context_lens, const int32_t* cu_seqlens_q, int B,
+                                      int total_q_tokens, int max_seqlen_q, int nh, int kv, int hd, int block_size,
+                                      int num_blocks, float scale, nvc_bf16* out, void* stream) {
+  NVC_REQUIRE(ctx, ctx && q && k_cache && v_cache && block_tables && context_lens && cu_seqlens_q && out, NVC_EINVAL,
+              "null pointer");
+  NVC_REQUIRE(ctx, B >= 0 && total_q_tokens >= 0 && max_seqlen_q >= 0 && nh > 0 && kv > 0 && bt_stride > 0 &&
+                       num_blocks > 0, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, hd == 128, NVC_ESHAPE, "head_dim must be 128");
+  NVC_REQUIRE(ctx, nh % kv == 0, NVC_ESHAPE, "nh must be a multiple of kv");
+  NVC_REQUIRE(ctx, block_size >= 16 && (block_size >= 128 ? block_size % 128 == 0 : 128 % block_size == 0), NVC_ESHAPE,
+              "paged prefill needs block_size in {16, 32, 64} or a multiple of 128");
+  NVC_REQUIRE(ctx, ldq % 8 == 0 && ldq >= nh * hd, NVC_ESHAPE, "q row stride must cover the heads and be a multiple of 8");
+  NVC_REQUIRE(ctx, ((uintptr_t)q % 16) == 0 && ((uintptr_t)k_cache % 16) == 0 && ((uintptr_t)v_cache % 16) == 0,
+              NVC_EINVAL, "pointers must be 16-byte aligned");
+  NVC_REQUIRE(ctx, ctx->encode_tiled != nullptr, NVC_EDEVICE, "cuTensorMapEncodeTiled unavailable");
+  if (B == 0 || total_q_tokens == 0 || max_seqlen_q == 0) return NVC_OK;
+  const int box_rows = block_size < 128 ? block_size : 128;
+  CUtensorMap tq, tk, tv;
+  int rc = make_tma_heads(ctx, &tq, q, nh, total_q_tokens, ldq);
+  if (rc) return rc;
+  rc = make_tma_heads(ctx, &tk, k_cache, kv, (int64_t)num_blocks * block_size, kv * hd, box_rows);   // cache = [slots, kv, hd]
+  if (rc) return rc;
+  rc = make_tma_heads(ctx, &tv, v_cache, kv, (int64_t)num_blocks * block_size, kv * hd, box_rows);
+  if (rc) return rc;
+  PagedKV pk{block_tables, context_lens, bt_stride, block_size, box_rows};
+  dim3 grid((max_seqlen_q + 127) / 128, nh, B);
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, prefill_attn_kernel<true>, grid, dim3(kThreads), kSmemBytes, nvc_stream(stream), tq, tk, tv,
+                                 cu_seqlens_q, nh, nh / kv, scale * 1.4426950408889634f, out, 16384, 1024, pk));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;

@@ -87,7 +87,8 @@ int dev_alloc(nvc_runner* r, T** p, size_t count) {
 // up, by ONE kernel that reads the peers' partials and applies residual add + RMSNorm
 // (p2p_allreduce.cu).  In that mode the norm that opens layer l+1 is produced at the end of layer
 // l, and the final norm by the last layer (*final_norm_done).
-int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blocks_hint, bool* final_norm_done) {
+int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blocks_hint, bool* final_norm_done,
+               bool paged_prefill = false) {
   const nvc_qwen3_config& c = r->cfg;
   nvc_ctx* ctx = r->ctx;
   void* st = r->stream;
@@ -118,6 +119,11 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
       rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
                                     r->d_ctx, B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
                                     r->decode_ws, r->decode_ws_bytes, st);
+    } else if (paged_prefill) {
+      // cached prefix: K / V of the whole context come from the paged cache (this step's were just stored)
+      rc = nvc_prefill_attn_paged(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, r->d_ctx,
+                                  r->d_cu, B, N, max_seqlen, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size,
+                                  r->opt.num_kvcache_blocks, scale, r->attn, st);
     } else {
       rc = nvc_prefill_attn_varlen(ctx, r->qkv, r->qkv_l, r->qkv + (size_t)r->nh_l * hd, r->qkv_l,
                                    r->qkv + (size_t)(r->nh_l + r->kv_l) * hd, r->qkv_l, r->d_cu, B, N, max_seqlen,
@@ -446,21 +452,41 @@ extern "C" int nvc_runner_finalize(nvc_runner* r) {
 // ------------------------------------------------------------------------------------------
 // steps
 // ------------------------------------------------------------------------------------------
-extern "C" int nvc_runner_prefill(nvc_runner* r, const int32_t* ids, const int32_t* positions,
-                                  const int32_t* cu_seqlens, const int32_t* slot_mapping, int B, int N, int max_seqlen,
-                                  int32_t* out_tokens) {
+namespace {
+
+// block_tables == nullptr: no cached prefix, attention over this step's own k / v (K4);
+// otherwise attention over the paged cache through block_tables / context_lens (K4 paged).
+int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* cu_seqlens,
+                 const int32_t* slot_mapping, const int32_t* block_tables, int max_blocks, const int32_t* context_lens,
+                 int B, int N, int max_seqlen, int32_t* out_tokens) {
   if (!r) return NVC_EINVAL;
   nvc_ctx* ctx = r->ctx;
+  const bool paged = block_tables != nullptr;
   NVC_REQUIRE(ctx, r->finalized, NVC_ESTATE, "nvc_runner_finalize not called");
   NVC_REQUIRE(ctx, ids && positions && cu_seqlens && slot_mapping && out_tokens, NVC_EINVAL, "null pointer");
   NVC_REQUIRE(ctx, B > 0 && N > 0 && B <= r->opt.max_num_seqs && N <= r->opt.max_num_batched_tokens, NVC_ENOMEM,
               "prefill step exceeds max_num_seqs / max_num_batched_tokens");
   NVC_REQUIRE(ctx, cu_seqlens[0] == 0 && cu_seqlens[B] == N, NVC_EINVAL, "cu_seqlens does not cover N tokens");
-  const int64_t nslots = (int64_t)r->opt.num_kvcache_blocks * r->opt.kvcache_block_size;
+  const int bs = r->opt.kvcache_block_size;
+  const int64_t nslots = (int64_t)r->opt.num_kvcache_blocks * bs;
   for (int i = 0; i < N; ++i) {
     NVC_REQUIRE(ctx, ids[i] >= 0 && ids[i] < r->cfg.vocab_size, NVC_EINVAL, "token id out of range");
     NVC_REQUIRE(ctx, positions[i] >= 0 && positions[i] < r->opt.max_model_len, NVC_EINVAL, "position out of range");
     NVC_REQUIRE(ctx, slot_mapping[i] >= -1 && slot_mapping[i] < nslots, NVC_EINVAL, "slot out of range");
+  }
+  const int cap = r->max_blocks_cap;
+  if (paged) {
+    NVC_REQUIRE(ctx, context_lens, NVC_EINVAL, "null pointer");
+    NVC_REQUIRE(ctx, max_blocks > 0 && max_blocks <= cap, NVC_ENOMEM, "block table wider than max_model_len allows");
+    for (int b = 0; b < B; ++b) {
+      const int qlen = cu_seqlens[b + 1] - cu_seqlens[b], nb = (context_lens[b] + bs - 1) / bs;
+      NVC_REQUIRE(ctx, context_lens[b] >= qlen && nb <= max_blocks, NVC_EINVAL, "context_len vs q_len / block table");
+      NVC_REQUIRE(ctx, qlen <= 0 || positions[cu_seqlens[b + 1] - 1] == context_lens[b] - 1, NVC_EINVAL,
+                  "the new tokens must be the last positions of the context");
+      for (int j = 0; j < nb; ++j)
+        NVC_REQUIRE(ctx, block_tables[(size_t)b * max_blocks + j] >= 0 &&
+                             block_tables[(size_t)b * max_blocks + j] < r->opt.num_kvcache_blocks, NVC_EINVAL, "block id out of range");
+    }
   }
   NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
   int32_t* h = r->h_stage;
@@ -480,15 +506,46 @@ extern "C" int nvc_runner_prefill(nvc_runner* r, const int32_t* ids, const int32
   R_CUDA(cudaMemcpyAsync(r->d_slots, h + 2 * N, N * 4, cudaMemcpyHostToDevice, st));
   R_CUDA(cudaMemcpyAsync(r->d_cu, h + 3 * N, (B + 1) * 4, cudaMemcpyHostToDevice, st));
   R_CUDA(cudaMemcpyAsync(r->d_last_rows, last, B * 4, cudaMemcpyHostToDevice, st));
+  if (paged) {
+    int32_t* hctx = last + B;
+    int32_t* hbt = hctx + B;
+    memcpy(hctx, context_lens, B * 4);
+    for (int b = 0; b < B; ++b) {
+      memcpy(hbt + (size_t)b * cap, block_tables + (size_t)b * max_blocks, max_blocks * 4);
+      for (int j = max_blocks; j < cap; ++j) hbt[(size_t)b * cap + j] = -1;
+    }
+    R_CUDA(cudaMemcpyAsync(r->d_ctx, hctx, B * 4, cudaMemcpyHostToDevice, st));
+    R_CUDA(cudaMemcpyAsync(r->d_bt, hbt, (size_t)B * cap * 4, cudaMemcpyHostToDevice, st));
+  }
   int rc = nvc_embed_gather(ctx, r->d_ids, r->embed, r->x, N, r->cfg.hidden_size, r->cfg.vocab_size, st);
   if (rc) return rc;
   bool fnd = false;
-  rc = run_layers(r, N, false, B, max_seqlen, 0, &fnd);
+  rc = run_layers(r, N, false, B, max_seqlen, 0, &fnd, paged);
   if (rc) return rc;
   rc = run_head(r, B, false, fnd);
   if (rc) return rc;
   r->last_B = B;
   return finish_tokens(r, B, out_tokens);
+}
+
+}  // namespace
+
+extern "C" int nvc_runner_prefill(nvc_runner* r, const int32_t* ids, const int32_t* positions,
+                                  const int32_t* cu_seqlens, const int32_t* slot_mapping, int B, int N, int max_seqlen,
+                                  int32_t* out_tokens) {
+  return prefill_impl(r, ids, positions, cu_seqlens, slot_mapping, nullptr, 0, nullptr, B, N, max_seqlen, out_tokens);
+}
+
+extern "C" int nvc_runner_prefill_paged(nvc_runner* r, const int32_t* ids, const int32_t* positions,
+                                        const int32_t* cu_seqlens, const int32_t* slot_mapping,
+                                        const int32_t* block_tables, int max_blocks, const int32_t* context_lens, int B,
+                                        int N, int max_seqlen, int32_t* out_tokens) {
+  if (r && !block_tables) {
+    nvc_set_error(r->ctx, "nvc_runner_prefill_paged: null block_tables");
+    return NVC_EINVAL;
+  }
+  return prefill_impl(r, ids, positions, cu_seqlens, slot_mapping, block_tables, max_blocks, context_lens, B, N,
+                      max_seqlen, out_tokens);
 }
 
 extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_t* positions,

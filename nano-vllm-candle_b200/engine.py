@@ -53,6 +53,11 @@ class SchedulerConfig:
     eos: int = 0
     num_kvcache_blocks: int = 0
     kvcache_block_size: int = 256
+    enable_prefix_caching: bool = False      # beyond the reference; off = reference behaviour
+
+    def with_prefix_caching(self, on: bool = True):
+        self.enable_prefix_caching = on
+        return self
 
     def with_max_num_seqs(self, n):
         self.max_num_seqs = n
@@ -317,7 +322,7 @@ class LLMEngine:
         self.model_runner = model_runner
         cfg = scheduler.config
         c = SchedulerConfigC(cfg.max_num_seqs, cfg.max_num_batched_tokens, cfg.eos, cfg.num_kvcache_blocks,
-                             cfg.kvcache_block_size)
+                             cfg.kvcache_block_size, int(bool(cfg.enable_prefix_caching)))
         h = C.c_void_p()
         rh = getattr(model_runner, "handle", None)
         check(self.l.nvc_engine_create(C.byref(c), rh, C.byref(h)), "nvc_engine_create")
@@ -425,6 +430,12 @@ class LLMEngine:
 
     def num_free_blocks(self) -> int:
         return self.l.nvc_engine_num_free_blocks(self.h)
+
+    def prefix_cache_stats(self) -> Tuple[int, int]:
+        """(full blocks found in the prefix cache, full blocks looked up) since the engine was created."""
+        hit, q = C.c_int64(), C.c_int64()
+        self._ck(self.l.nvc_engine_prefix_cache_stats(self.h, C.byref(hit), C.byref(q)), "nvc_engine_prefix_cache_stats")
+        return hit.value, q.value
 
     def num_waiting(self) -> int:
         return self.l.nvc_engine_num_waiting(self.h)

@@ -183,6 +183,22 @@ class Context:
                                                 _ptr(out), _stream()), "nvc_prefill_attn_varlen")
         return out
 
+    def prefill_attn_paged(self, q, k_cache, v_cache, block_tables, context_lens, cu_seqlens_q, max_seqlen_q,
+                           nh, kv, hd, block_size, scale, out=None):
+        """K4 over the paged cache (cached prefix): q [N, nh*hd] = the last q_len_b positions of each
+        context; k_cache / v_cache [num_blocks, block_size, kv, hd] already hold the whole context."""
+        _req(q, BF16, "q"); _req(cu_seqlens_q, torch.int32, "cu_seqlens_q")
+        _req(block_tables, torch.int32, "block_tables"); _req(context_lens, torch.int32, "context_lens")
+        N = q.shape[0]
+        B = cu_seqlens_q.numel() - 1
+        out = torch.empty((N, nh * hd), dtype=BF16, device=q.device) if out is None else out
+        self._ck(self.l.nvc_prefill_attn_paged(self.h, _ptr(q), q.stride(0), _ptr(k_cache), _ptr(v_cache),
+                                               _ptr(block_tables), block_tables.shape[1], _ptr(context_lens),
+                                               _ptr(cu_seqlens_q), B, N, max_seqlen_q, nh, kv, hd, block_size,
+                                               k_cache.shape[0], float(scale), _ptr(out), _stream()),
+                 "nvc_prefill_attn_paged")
+        return out
+
     def paged_decode_attn(self, q, k_cache, v_cache, block_tables, context_lens, nh, kv, hd, block_size, scale, out=None):
         _req(q, BF16, "q"); _req(block_tables, torch.int32, "block_tables"); _req(context_lens, torch.int32, "context_lens")
         B = q.shape[0]

@@ -10,7 +10,8 @@ The reference BlockManager is an admitted stub (block_manager.rs:24-29: identity
 block_table, always-true capacity).  `BlockManagerStub` restates it as written;
 `BlockManager` is the real allocator the north_star contract needs (free list,
 disjoint ids), following upstream nano-vllm's rule which the reference says its API
-mirrors (block_manager.rs:26-29), without prefix caching.
+mirrors (block_manager.rs:26-29); `BlockManagerPrefix` adds upstream's hash-chained
+prefix cache.
 The slot_mapping rule (N1) is expressed only with the Sequence helpers the reference
 exposes (sequence.rs:73-91).
 """
@@ -193,6 +194,88 @@ class BlockManager:
     def may_append(self, seq):
         if len(seq) % self.block_size_ == 1 and len(seq.block_table) < seq.num_blocks():
             seq.block_table.append(self.free.popleft())
+
+
+class BlockManagerPrefix(BlockManager):
+    """Upstream nano-vllm's BlockManager with prefix caching (the "block deduplication" that
+    block_manager.rs:24-29 says the reference leaves out and will plug in behind the same API):
+    ref-counted blocks, a chained hash per FULL block, hash -> block id map, a hit confirmed
+    by comparing token ids; freed blocks keep their hash until they are handed out again.
+    One rule is added: a block is taken from the cache only if (i + 1) * block_size < len(seq),
+    so at least one token is left to compute (upstream would schedule an empty prefill).
+    The hash key here is Python's hash of (prefix key, tokens): only equality is observable."""
+
+    def __init__(self, num_blocks: int, block_size: int = 256):
+        super().__init__(num_blocks, block_size)
+        self.ref = [0] * num_blocks
+        self.key: List[Optional[int]] = [None] * num_blocks
+        self.tokens: List[List[int]] = [[] for _ in range(num_blocks)]
+        self.key_to_block: Dict[int, int] = {}
+        self.hits = 0
+        self.queries = 0
+
+    def _take(self, b):
+        assert self.ref[b] == 0
+        self.ref[b] = 1
+        self.key[b] = None
+        self.tokens[b] = []
+        self.free.remove(b)
+
+    def _set_key(self, b, key, toks):
+        self.key[b] = key
+        self.tokens[b] = list(toks)
+        self.key_to_block[key] = b
+
+    def allocate(self, seq):
+        assert not seq.block_table
+        seq.num_cached_tokens = 0
+        bs = self.block_size_
+        key, miss = None, False
+        for i in range(seq.num_blocks()):
+            toks = seq.block(i)
+            key = hash((key, tuple(toks))) if len(toks) == bs else None
+            b = -1
+            if key is not None:
+                self.queries += 1
+                b = self.key_to_block.get(key, -1)
+            if b == -1 or self.key[b] != key or self.tokens[b] != toks or (i + 1) * bs >= len(seq):
+                miss = True
+            if miss:
+                b = self.free[0]
+                self._take(b)
+            else:
+                self.hits += 1
+                seq.num_cached_tokens += bs
+                if self.ref[b] == 0:
+                    self._take(b)
+                else:
+                    self.ref[b] += 1
+            if key is not None:
+                self._set_key(b, key, toks)
+            seq.block_table.append(b)
+
+    def deallocate(self, seq):
+        for b in reversed(seq.block_table):
+            self.ref[b] -= 1
+            if self.ref[b] == 0:
+                self.free.append(b)
+        seq.block_table = []
+        seq.num_cached_tokens = 0
+
+    def may_append(self, seq):
+        bs = self.block_size_
+        if len(seq) % bs == 1 and len(seq.block_table) < seq.num_blocks():
+            b = self.free[0]
+            self._take(b)
+            seq.block_table.append(b)
+        elif len(seq) % bs == 0 and seq.block_table:
+            b = seq.block_table[-1]
+            if self.key[b] is None:
+                nb = len(seq.block_table)
+                prefix = self.key[seq.block_table[-2]] if nb > 1 else None
+                if nb == 1 or prefix is not None:
+                    toks = seq.block(nb - 1)
+                    self._set_key(b, hash((prefix, tuple(toks))), toks)
 
 
 # ----------------------------------------------------------------- integer contract N1/N2/N3

@@ -11,13 +11,14 @@ from oracle import engine_oracle as E
 eng = importlib.import_module("nano-vllm-candle_b200.engine")
 
 
-def _mk(max_num_seqs, max_tokens_batched, nblocks, bs, eos=0):
+def _mk(max_num_seqs, max_tokens_batched, nblocks, bs, eos=0, prefix=False):
     cfg = eng.SchedulerConfig().with_max_num_seqs(max_num_seqs).with_max_num_batched_tokens(max_tokens_batched) \
-        .with_eos(eos).with_kvcache(nblocks, bs)
+        .with_eos(eos).with_kvcache(nblocks, bs).with_prefix_caching(prefix)
     cpp = eng.LLMEngine(eng.Scheduler(cfg), eng.DummyModelRunner())
     E.Sequence._counter = 0
     ocfg = E.SchedulerConfig(max_num_seqs, max_tokens_batched, eos, nblocks, bs)
-    orc = E.LLMEngine(E.Scheduler(ocfg, E.BlockManager(nblocks, bs)), E.DummyModelRunner(), block_size=bs)
+    bm = E.BlockManagerPrefix(nblocks, bs) if prefix else E.BlockManager(nblocks, bs)
+    orc = E.LLMEngine(E.Scheduler(ocfg, bm), E.DummyModelRunner(), block_size=bs)
     return cpp, orc
 
 
@@ -135,3 +136,87 @@ def test_kv_pool_exhaustion_is_an_error_not_an_abort():
     cpp.step()                       # prefill fills the only block
     with pytest.raises(eng.NvcError):
         cpp.step()                   # the reference asserts here (scheduler.rs:175-178)
+
+
+# ----------------------------------------------------------------------------- prefix caching
+def _shared_prefix_prompts(rng, bs, n, n_prefixes=3):
+    """Prompts that share block-aligned and unaligned prefixes, plus exact duplicates."""
+    prefixes = [rng.integers(10, 1000, size=int(rng.integers(1, 5)) * bs + int(rng.integers(0, bs))).tolist()
+                for _ in range(n_prefixes)]
+    out = []
+    for i in range(n):
+        p = prefixes[int(rng.integers(0, n_prefixes))]
+        kind = int(rng.integers(0, 4))
+        if kind == 0:
+            out.append(list(p))                                              # exact duplicate
+        elif kind == 1:
+            out.append(p[:(len(p) // bs) * bs])                              # exactly the full blocks
+        else:
+            out.append(p + rng.integers(10, 1000, size=int(rng.integers(1, 3 * bs))).tolist())
+    return out
+
+
+@pytest.mark.parametrize("bs,nblocks,max_seqs,seed", [(16, 64, 4, 0), (16, 40, 8, 1), (32, 48, 3, 2), (256, 40, 6, 3)])
+def test_prefix_caching_matches_oracle_step_by_step(bs, nblocks, max_seqs, seed):
+    """Block ids, num_cached_tokens (through ids / positions / cu_seqlens), slot_mapping and
+    block_tables of the C++ prefix-caching allocator against the restatement of upstream
+    nano-vllm's BlockManager, including preemption and cache reuse after deallocation."""
+    rng = np.random.default_rng(seed)
+    cpp, orc = _mk(max_seqs, 8 * bs * max_seqs, nblocks, bs, eos=7, prefix=True)
+    prompts = _shared_prefix_prompts(rng, bs, 20)
+    steps, prefills = _lockstep(cpp, orc, prompts, eng.SamplingParams(1.0, 2 * bs + 5, True),
+                                E.SamplingParams(1.0, 2 * bs + 5, True))
+    hit, queried = cpp.prefix_cache_stats()
+    bm = orc.scheduler.block_manager
+    assert (hit, queried) == (bm.hits, bm.queries) and hit > 0
+    assert cpp.num_free_blocks() == nblocks
+
+
+def test_prefix_caching_skips_cached_blocks_and_keeps_one_token():
+    bs = 16
+    cpp, _ = _mk(1, 4096, 32, bs, prefix=True)
+    sp = eng.SamplingParams(1.0, 1, True)
+    a = list(range(100, 100 + 3 * bs))                  # exactly three full blocks
+    cpp.add_request(a, sp)
+    si = cpp.schedule()
+    assert si.cu_seqlens.tolist() == [0, 3 * bs] and si.positions[0] == 0
+    first_table = si.block_tables[0].tolist()
+    cpp.post_process([5])                                 # finished (max_tokens 1): blocks freed, hashes kept
+    cpp.add_request(a, sp)                                # same prompt: blocks 0 and 1 hit, the last one is recomputed
+    si = cpp.schedule()
+    assert si.is_prefill and si.cu_seqlens.tolist() == [0, bs]
+    assert si.positions.tolist() == list(range(2 * bs, 3 * bs))
+    assert si.context_lens.tolist() == [3 * bs]
+    assert si.block_tables[0, :2].tolist() == first_table[:2]
+    assert si.slot_mapping.tolist() == [si.block_tables[0, 2] * bs + i for i in range(bs)]
+    cpp.post_process([5])
+    cpp.add_request(a + [1, 2, 3], sp)                    # longer prompt: all three full blocks hit
+    si = cpp.schedule()
+    assert si.cu_seqlens.tolist() == [0, 3] and si.positions.tolist() == [3 * bs, 3 * bs + 1, 3 * bs + 2]
+    assert cpp.prefix_cache_stats() == (5, 9)
+
+
+def test_prefix_caching_shares_blocks_between_running_sequences():
+    bs = 16
+    cpp, _ = _mk(4, 4096, 32, bs, prefix=True)
+    sp = eng.SamplingParams(1.0, 4, True)
+    base = list(range(50, 50 + 2 * bs))
+    cpp.add_request(base + [1], sp)
+    cpp.add_request(base + [2, 3], sp)                    # scheduled in the same step: hits the blocks just registered
+    si = cpp.schedule()
+    assert si.block_tables[0, :2].tolist() == si.block_tables[1, :2].tolist()
+    assert si.block_tables[0, 2] != si.block_tables[1, 2]
+    assert si.cu_seqlens.tolist() == [0, 2 * bs + 1, 2 * bs + 3]
+    assert cpp.num_free_blocks() == 32 - 4               # two shared + two private
+    cpp.post_process([9, 9])
+    assert cpp.num_free_blocks() == 32 - 4
+
+
+def test_prefix_caching_off_is_the_default_and_never_caches():
+    cpp, _ = _mk(2, 4096, 16, 16)
+    sp = eng.SamplingParams(1.0, 1, True)
+    a = list(range(40))
+    cpp.add_request(a, sp); cpp.schedule(); cpp.post_process([1])
+    cpp.add_request(a, sp)
+    si = cpp.schedule()
+    assert si.cu_seqlens.tolist() == [0, 40] and cpp.prefix_cache_stats() == (0, 0)

@@ -129,6 +129,61 @@ def test_greedy_generation_with_preemption_tiny(tiny):
         _teacher_forced_check(fp32, p, g, 4e-2, f"e2e tiny preemption seq {b}")
 
 
+def test_prefix_caching_generation_matches_oracle_tiny(tiny):
+    """with prefix caching on, sequences that share full KV blocks skip them in
+    prefill (paged K4 reads the prefix through block_tables); every token must still be the
+    oracle's full-recompute greedy choice up to numerical ties, and the cache must have hit."""
+    cfg, runner, fp32, _ = tiny
+    bs = 16
+    base = synth.make_prompts(1, 5 * bs + 3, cfg.vocab_size, 900)[0]
+    prompts = [base[:3 * bs + 5] + synth.make_prompts(1, 9, cfg.vocab_size, 901)[0],      # shares 3 blocks
+               base,                                                                       # shares 3 blocks, longer
+               base[:2 * bs],                                                              # exactly 2 full blocks: last one recomputed
+               base + synth.make_prompts(1, 40, cfg.vocab_size, 902)[0],                   # shares 5 blocks with `base`
+               synth.make_prompts(1, 21, cfg.vocab_size, 903)[0]]                          # unrelated
+    sch = eng.Scheduler(eng.SchedulerConfig(2, 2048, cfg.eos_token_id, 64, bs, enable_prefix_caching=True))
+    e = eng.LLMEngine(sch, runner)        # max_num_seqs 2: later prompts arrive when earlier ones have finished or are running
+    outs = e.generate(prompts, eng.SamplingParams(1.0, 20, True))
+    hit, queried = e.prefix_cache_stats()
+    diag(f"[e2e tiny prefix caching] cache hits {hit} of {queried} full blocks; prefill tokens {e.prefill_tokens}")
+    assert hit >= 3 + 1 + 5 - 2, "shared prefixes must have been served from the cache"
+    for b, (p, o) in enumerate(zip(prompts, outs)):
+        assert len(o.token_ids) == 20
+        _teacher_forced_check(fp32, p, o.token_ids, 4e-2, f"e2e tiny prefix caching seq {b}")
+
+
+def test_prefix_cached_prefill_logits_match_uncached(tiny):
+    """The same prompt prefilled twice, the second time with its first blocks served from the
+    cache: last-token logits agree with the uncached run to bf16 rounding and with the oracle
+    within the north_star tolerance."""
+    cfg, runner, fp32, _ = tiny
+    bs = 16
+    prompt = synth.make_prompts(1, 4 * bs + 7, cfg.vocab_size, 950)[0]
+    sch = eng.Scheduler(eng.SchedulerConfig(1, 2048, cfg.eos_token_id, 64, bs, enable_prefix_caching=True))
+    e = eng.LLMEngine(sch, runner)
+    logits = []
+    for rnd in range(2):
+        e.add_request(prompt, eng.SamplingParams(1.0, 1, True))
+        si = e.schedule()
+        assert si.is_prefill and len(si.ids) == (len(prompt) if rnd == 0 else 7)
+        if rnd == 0:
+            toks = runner.prefill(si.ids, si.positions, si.cu_seqlens, si.slot_mapping)
+        else:
+            st = runner.l.nvc_runner_prefill_paged(
+                runner.handle, eng._p(si.ids), eng._p(si.positions), eng._p(si.cu_seqlens), eng._p(si.slot_mapping),
+                eng._p(np.ascontiguousarray(si.block_tables)), si.block_tables.shape[1], eng._p(si.context_lens), 1,
+                len(si.ids), len(si.ids), eng._p(np.empty(1, np.int32)))
+            assert st == 0, runner.l.nvc_last_error(runner.ctx.h).decode()
+            toks = np.asarray([0], np.int32)
+        logits.append(torch.from_numpy(runner.last_logits(1))[0].clone())
+        e.post_process(toks)
+    ref = _oracle_last_logits(fp32, [prompt])[0]
+    d01 = (logits[0] - logits[1]).abs().max().item()
+    err = (logits[1] - ref).abs().max().item()
+    diag(f"[e2e tiny prefix logits] cached vs uncached max-abs {d01:.4e}; cached vs fp32 oracle {err:.4e}")
+    assert err <= 2e-2 and d01 <= 2e-2
+
+
 def test_causality_property(tiny):
     """tests/layer_test.rs:164-202: logits of a prefix do not depend on later tokens -
     here: last-token logits of [a] equal position-0 logits of [a, b] in the oracle, and the

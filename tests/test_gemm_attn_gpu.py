@@ -219,6 +219,81 @@ def test_prefill_attn_varlen(ctx, nvc, lens, nh, kv):
     _close(out, ref, 2e-2, 2 ** -6, f"prefill lens={lens} nh={nh} kv={kv}")
 
 
+@pytest.mark.parametrize("nh,kv,block_size,cases", [
+    # cases: (context_len, q_len) per sequence; the q rows are the LAST q_len positions of the context
+    (4, 2, 16, [(48, 16), (33, 1), (200, 200), (131, 3), (16, 16)]),
+    (4, 2, 32, [(300, 44), (128, 128), (129, 1)]),
+    (16, 8, 256, [(768, 256), (1000, 232), (256, 1), (257, 257), (640, 130)]),   # block-aligned and unaligned prefixes
+    (8, 1, 128, [(1500, 476), (5, 5)]),
+    (2, 2, 64, [(513, 385)]),
+])
+def test_prefill_attn_paged(ctx, nh, kv, block_size, cases):
+    """K4 over the paged cache (prefix caching): rows of dense causal attention over the whole
+    context (qwen3.rs:236-277) for the last q_len positions; unwritten cache slots are NaN."""
+    hd = 128
+    B = len(cases)
+    g = torch.Generator().manual_seed(nh * 1000 + block_size + B)
+    nblk_per = [(c + block_size - 1) // block_size for c, _ in cases]
+    total_blk = sum(nblk_per) + 2
+    perm = torch.randperm(total_blk, generator=g)
+    bt = torch.full((B, max(nblk_per) + 1), -1, dtype=torch.int32)
+    kc = torch.full((total_blk * block_size, kv, hd), float("nan")).to(BF16)
+    vc = torch.full((total_blk * block_size, kv, hd), float("nan")).to(BF16)
+    scale = hd ** -0.5
+    qs, refs, p = [], [], 0
+    for b, (c, ql) in enumerate(cases):
+        blocks = perm[p:p + nblk_per[b]]; p += nblk_per[b]
+        bt[b, :len(blocks)] = blocks.to(torch.int32)
+        q = torch.randn(c, nh, hd, generator=g).to(BF16)
+        k = torch.randn(c, kv, hd, generator=g).to(BF16)
+        v = torch.randn(c, kv, hd, generator=g).to(BF16)
+        t = torch.arange(c)
+        slots = blocks[t // block_size] * block_size + t % block_size
+        kc[slots], vc[slots] = k, v
+        refs.append(_dense_causal_ref(q, k, v, nh, kv, scale)[c - ql:])
+        qs.append(q[c - ql:].reshape(ql, nh * hd))
+    qd = torch.cat(qs).cuda()
+    ref = torch.cat(refs)
+    cu = torch.tensor([0] + list(np.cumsum([ql for _, ql in cases])), dtype=torch.int32)
+    ctx_lens = torch.tensor([c for c, _ in cases], dtype=torch.int32)
+    out = ctx.prefill_attn_paged(qd, kc.reshape(total_blk, block_size, kv, hd).cuda(),
+                                 vc.reshape(total_blk, block_size, kv, hd).cuda(), bt.cuda(), ctx_lens.cuda(), cu.cuda(),
+                                 max(ql for _, ql in cases), nh, kv, hd, block_size, scale)
+    torch.cuda.synchronize()
+    assert not torch.isnan(out.float()).any(), "poisoned (unwritten) cache slots leaked into the output"
+    err = (out.float().cpu() - ref).abs().max().item()
+    diag(f"[prefill paged nh={nh} kv={kv} bs={block_size} cases={cases}] max_err={err:.4e}")
+    _close(out, ref, 2e-2, 2 ** -6, f"paged prefill nh={nh} kv={kv} bs={block_size} cases={cases}")
+
+
+def test_prefill_attn_paged_equals_varlen_without_prefix(ctx):
+    """With no cached prefix the paged kernel must reproduce the in-place varlen kernel bit for bit
+    (same tiles, same order of operations)."""
+    hd, nh, kv, bs = 128, 8, 4, 256
+    lens = [300, 128, 77, 513]
+    N = sum(lens)
+    g = torch.Generator().manual_seed(7)
+    qkv = torch.randn(N, (nh + 2 * kv) * hd, generator=g).to(BF16).cuda()
+    cu = torch.tensor([0] + list(np.cumsum(lens)), dtype=torch.int32).cuda()
+    scale = hd ** -0.5
+    a = ctx.prefill_attn(qkv[:, :nh * hd], qkv[:, nh * hd:(nh + kv) * hd], qkv[:, (nh + kv) * hd:], cu, max(lens), nh, kv, hd, scale)
+    nblk = [(l + bs - 1) // bs for l in lens]
+    total = sum(nblk)
+    kc = torch.zeros(total * bs, kv * hd, dtype=BF16, device="cuda")
+    vc = torch.zeros(total * bs, kv * hd, dtype=BF16, device="cuda")
+    bt = torch.full((len(lens), max(nblk)), -1, dtype=torch.int32)
+    blk, s = 0, 0
+    for b, l in enumerate(lens):
+        bt[b, :nblk[b]] = torch.arange(blk, blk + nblk[b], dtype=torch.int32)
+        kc[blk * bs:blk * bs + l] = qkv[s:s + l, nh * hd:(nh + kv) * hd]
+        vc[blk * bs:blk * bs + l] = qkv[s:s + l, (nh + kv) * hd:]
+        blk += nblk[b]; s += l
+    b_out = ctx.prefill_attn_paged(qkv[:, :nh * hd], kc.reshape(total, bs, kv, hd), vc.reshape(total, bs, kv, hd), bt.cuda(),
+                                   torch.tensor(lens, dtype=torch.int32).cuda(), cu, max(lens), nh, kv, hd, bs, scale)
+    torch.cuda.synchronize()
+    assert torch.equal(a, b_out)
+
+
 # ----------------------------------------------------------------------------- K5 decode
 @pytest.mark.parametrize("nh,kv,block_size,ctx_lens", [
     (16, 8, 256, [1, 16, 17, 255, 256, 257, 1000, 64]),

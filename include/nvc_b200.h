@@ -216,6 +216,19 @@ int nvc_gather_rows(nvc_ctx* ctx, const nvc_bf16* x, const float* residual, cons
 int nvc_argmax_last(nvc_ctx* ctx, const float* logits, int ld, int32_t* idx, float* val,
                     int B, int V, int index_offset, void* stream);
 
+/* K8s. Replaces Qwen3ModelRunner::sample_token (src/engine/llm_engine.rs:97-133) on device.  The
+ * reference draws from softmax((l - max) / max(T, 1e-6)) with an unseeded rand::rng() (:128); this is
+ * the Gumbel-max form of the same categorical distribution with counter-based, reproducible noise:
+ *   idx[b] = argmax_i( logits[b, i] / max(T_b, 1e-6) + g ),  g = -log(-log(u)),
+ *   u = ((x >> 8) + 0.5) * 2^-24,  x = word (gi % 4) of Philox4x32-10(key = seed,
+ *   counter = (gi / 4, streams[b] lo, streams[b] hi, 0)),  gi = index_offset + i  (global vocab index),
+ * ties -> last index.  val[b] = the winning perturbed score, so tensor-parallel vocab shards merge
+ * like the greedy (max, idx) pairs.  temperatures: f32 [B]; streams: u64 [B] (one value per
+ * (sequence, step)); V, ld, index_offset multiples of 4. */
+int nvc_sample_gumbel(nvc_ctx* ctx, const float* logits, int ld, const float* temperatures,
+                      const uint64_t* streams, uint64_t seed, int32_t* idx, float* val, int B, int V,
+                      int index_offset, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

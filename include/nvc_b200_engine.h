@@ -83,6 +83,11 @@ int nvc_runner_prefill_paged(nvc_runner* r, const int32_t* ids, const int32_t* p
 int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* slot_mapping,
                       const int32_t* block_tables, int max_blocks, const int32_t* context_lens, int B,
                       int32_t* out_tokens);
+/* Arms on-device temperature sampling (K8s, nvc_sample_gumbel) for the NEXT prefill / decode step
+ * only: temperatures f32 [B] (> 0), streams u64 [B] (one noise stream per (sequence, step)), seed =
+ * Philox key.  temperatures == NULL disarms.  Without this call a step is greedy (argmax, ties ->
+ * last index).  Replaces the host loop of Qwen3ModelRunner::sample_token (llm_engine.rs:97-133). */
+int nvc_runner_set_sampling(nvc_runner* r, const float* temperatures, const uint64_t* streams, int B, uint64_t seed);
 /* fp32 logits [B, vocab] of the sequences of the last step (parity checks; gathers TP shards). */
 int nvc_runner_last_logits(nvc_runner* r, float* out, int B);
 /* Device-resident timing hook for bench.py: replays the last decode step `iters` times on the
@@ -151,6 +156,11 @@ int nvc_engine_post_process(nvc_engine* e, const int32_t* token_ids, int n);
 /* LLMEngine::step (:239-264): schedule -> runner -> post_process. */
 int nvc_engine_step(nvc_engine* e, nvc_step_output* out);
 int nvc_engine_is_finished(const nvc_engine* e);
+/* enabled != 0: every nvc_engine_step samples with each sequence's SamplingParams.temperature
+ * (sampling_params.rs:6) on device, noise stream = (seq_id << 32 | completion tokens so far), so
+ * a sequence's tokens do not depend on batching, preemption or tensor-parallel size.  enabled == 0
+ * (default): greedy argmax, the mode the parity tests and the benchmark use. */
+int nvc_engine_set_sampling(nvc_engine* e, int enabled, uint64_t seed);
 /* Scheduler::preempt on the running sequence `seq_id` (:200-211). */
 int nvc_engine_preempt(nvc_engine* e, int64_t seq_id);
 /* Finished outputs (GenerationOutput, :192-207): completion tokens of seq_id. */

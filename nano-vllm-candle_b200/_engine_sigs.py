@@ -42,6 +42,7 @@ def declare(l: C.CDLL) -> None:
         "nvc_runner_prefill": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
         "nvc_runner_prefill_paged": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp],
         "nvc_runner_decode": [_vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp],
+        "nvc_runner_set_sampling": [_vp, _vp, _vp, _i, C.c_uint64],
         "nvc_runner_last_logits": [_vp, _vp, _i],
         "nvc_runner_time_decode": [_vp, _i, C.POINTER(C.c_float), C.POINTER(C.c_int)],
         "nvc_runner_time_op": [_vp, _i, _i, C.POINTER(C.c_float), C.POINTER(C.c_int)],
@@ -52,6 +53,7 @@ def declare(l: C.CDLL) -> None:
         "nvc_engine_post_process": [_vp, _vp, _i],
         "nvc_engine_step": [_vp, C.POINTER(StepOutputC)],
         "nvc_engine_is_finished": [_vp],
+        "nvc_engine_set_sampling": [_vp, _i, C.c_uint64],
         "nvc_engine_preempt": [_vp, _i64],
         "nvc_engine_num_finished": [_vp],
         "nvc_engine_get_output": [_vp, _i64, _vp, _i, C.POINTER(C.c_int)],

@@ -84,6 +84,7 @@ def _declare(l: C.CDLL) -> None:
         "nvc_silu_and_mul": [_vp, _vp, _vp, _i, _i, _vp],
         "nvc_gather_rows": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
         "nvc_argmax_last": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp],
+        "nvc_sample_gumbel": [_vp, _vp, _i, _vp, _vp, C.c_uint64, _vp, _vp, _i, _i, _i, _vp],
         "nvc_debug_set": [_i, _i],
     }
     for name, args in sigs.items():

@@ -478,6 +478,102 @@ extern "C" int nvc_argmax_last(nvc_ctx* ctx, const float* logits, int ld, int32_
   return NVC_OK;
 }
 
+// ------------------------------------------------------------------------------------
+// K8s temperature sampling on device.  Replaces Qwen3ModelRunner::sample_token
+// (llm_engine.rs:97-133: softmax((l - max) / max(T, 1e-6)) then WeightedIndex with an UNSEEDED
+// rand::rng(), i.e. not reproducible) by the Gumbel-max form of the same categorical draw:
+//   token = argmax_i ( l_i / T + g_i ),  g_i = -log(-log(u_i)),  u_i uniform in (0, 1)
+// with counter-based noise: Philox4x32-10, key = seed, counter = (i / 4, stream_lo, stream_hi, 0),
+// word i % 4, where i is the GLOBAL vocab index and stream identifies (sequence, step).  The draw
+// therefore does not depend on batch composition or on the tensor-parallel vocab split, and the
+// (value, index) pair per shard merges exactly like the greedy argmax.
+// ------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += 0x9E3779B9u;
+    k.y += 0xBB67AE85u;
+  }
+  return c;
+}
+
+__device__ __forceinline__ float gumbel_from_bits(uint32_t x) {
+  const float u = (float)(x >> 8) * 5.9604644775390625e-08f + 2.98023223876953125e-08f;   // (x >> 8) * 2^-24 + 2^-25, exact
+  return -logf(-logf(u));
+}
+
+__global__ void __launch_bounds__(1024)
+sample_gumbel_kernel(const float* __restrict__ logits, int ld, const float* __restrict__ temperatures,
+                     const uint64_t* __restrict__ streams, uint64_t seed, int32_t* __restrict__ idx,
+                     float* __restrict__ val, int V, int index_offset) {
+  pdl_trigger();
+  pdl_wait();
+  __shared__ float sv[32];
+  __shared__ int si[32];
+  const int b = blockIdx.x;
+  const float* row = logits + (int64_t)b * ld;
+  const float T = fmaxf(__ldg(temperatures + b), 1e-6f);          // llm_engine.rs:104
+  const uint64_t stream = __ldg(streams + b);
+  const uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+  const uint32_t s_lo = (uint32_t)stream, s_hi = (uint32_t)(stream >> 32);
+  float bv = -INFINITY;
+  int bi = -1;
+  // index_offset % 4 == 0 and V % 4 == 0: one Philox block covers the float4 at local index 4j
+  const int v4 = V >> 2;
+  const float4* row4 = reinterpret_cast<const float4*>(row);
+  for (int j = threadIdx.x; j < v4; j += blockDim.x) {
+    const float4 f = __ldg(row4 + j);
+    const uint4 n = philox4x32_10(make_uint4((uint32_t)((index_offset >> 2) + j), s_lo, s_hi, 0u), key);
+    const int base = j << 2;
+    argmax_combine(bv, bi, __fdiv_rn(f.x, T) + gumbel_from_bits(n.x), base);
+    argmax_combine(bv, bi, __fdiv_rn(f.y, T) + gumbel_from_bits(n.y), base + 1);
+    argmax_combine(bv, bi, __fdiv_rn(f.z, T) + gumbel_from_bits(n.z), base + 2);
+    argmax_combine(bv, bi, __fdiv_rn(f.w, T) + gumbel_from_bits(n.w), base + 3);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    argmax_combine(bv, bi, ov, oi);
+  }
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  if (lane == 0) { sv[wid] = bv; si[wid] = bi; }
+  __syncthreads();
+  if (wid == 0) {
+    const int nw = (blockDim.x + 31) >> 5;
+    bv = lane < nw ? sv[lane] : -INFINITY;
+    bi = lane < nw ? si[lane] : -1;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      argmax_combine(bv, bi, ov, oi);
+    }
+    if (lane == 0) {
+      idx[b] = bi + index_offset;
+      if (val) val[b] = bv;
+    }
+  }
+}
+
+extern "C" int nvc_sample_gumbel(nvc_ctx* ctx, const float* logits, int ld, const float* temperatures,
+                                 const uint64_t* streams, uint64_t seed, int32_t* idx, float* val, int B, int V,
+                                 int index_offset, void* stream) {
+  NVC_REQUIRE(ctx, ctx && logits && temperatures && streams && idx, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, B >= 0 && V > 0 && ld >= V, NVC_EINVAL, "bad sizes");
+  NVC_REQUIRE(ctx, ld % 4 == 0 && V % 4 == 0 && index_offset % 4 == 0 && index_offset >= 0, NVC_ESHAPE,
+              "ld, V and index_offset must be multiples of 4");
+  if (B == 0) return NVC_OK;
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, sample_gumbel_kernel, dim3(B), dim3(1024), 0, nvc_stream(stream), logits, ld,
+                                 temperatures, streams, seed, idx, val, V, index_offset));
+  NVC_CUDA_CHECK(ctx, cudaGetLastError());
+  ctx->launches++;
+  return NVC_OK;
+}
+
 // (max, idx) of a vocab shard as one 8-byte record per sequence (TP argmax exchange)
 __global__ void pack_argmax_pairs_kernel(const float* __restrict__ val, const int32_t* __restrict__ idx,
                                          float2* __restrict__ pairs, int B) {

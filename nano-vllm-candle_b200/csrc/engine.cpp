@@ -314,6 +314,10 @@ struct nvc_engine {
   std::vector<int32_t> ids, positions, cu_seqlens, slot_mapping, block_tables, context_lens, out_tokens;
   std::vector<int64_t> seq_ids;
   int max_blocks = 0, max_seqlen = 0;
+  bool sampling = false;                       // on-device temperature sampling
+  uint64_t sampling_seed = 0;
+  std::vector<float> temps;
+  std::vector<uint64_t> streams;
 
   nvc_engine(const nvc_scheduler_config& c, nvc_runner* r) : scheduler(c), runner(r), block_size(c.kvcache_block_size) {}
 };
@@ -389,6 +393,17 @@ int do_schedule(nvc_engine* e) {
   build_inputs(e);
   e->batch_valid = true;
   return NVC_OK;
+}
+
+// per-sequence temperature + noise stream (seq_id, completion tokens so far) for the step about to run
+int arm_sampling(nvc_engine* e) {
+  e->temps.clear();
+  e->streams.clear();
+  for (auto& s : e->batch) {
+    e->temps.push_back((float)s->temperature);
+    e->streams.push_back(((uint64_t)(uint32_t)s->seq_id << 32) | (uint32_t)s->num_completion_tokens());
+  }
+  return nvc_runner_set_sampling(e->runner, e->temps.data(), e->streams.data(), (int)e->batch.size(), e->sampling_seed);
 }
 
 int do_post_process(nvc_engine* e, const int32_t* toks, int n, int* finished_out) {
@@ -486,6 +501,9 @@ int nvc_engine_step(nvc_engine* e, nvc_step_output* out) {
   e->out_tokens.assign(B, 0);
   if (e->runner == nullptr) {
     for (int i = 0; i < B; ++i) e->out_tokens[i] = e->batch[i]->last_token + 1;   // DummyModelRunner
+  } else if (e->sampling && (rc = arm_sampling(e)) != NVC_OK) {
+    e->err = "nvc_runner_set_sampling failed";
+    return rc;
   } else if (e->batch_is_prefill) {
     bool cached_prefix = false;   // some sequence skips a cached prefix: attention must read it from the paged cache
     for (auto& s : e->batch) cached_prefix |= s->num_cached_tokens > 0;
@@ -523,6 +541,13 @@ int nvc_engine_step(nvc_engine* e, nvc_step_output* out) {
 }
 
 int nvc_engine_is_finished(const nvc_engine* e) { return e ? (e->scheduler.is_finished() ? 1 : 0) : 1; }
+
+int nvc_engine_set_sampling(nvc_engine* e, int enabled, uint64_t seed) {
+  if (!e) return NVC_EINVAL;
+  e->sampling = enabled != 0;
+  e->sampling_seed = seed;
+  return NVC_OK;
+}
 
 int nvc_engine_preempt(nvc_engine* e, int64_t seq_id) {
   if (!e) return NVC_EINVAL;

@@ -60,10 +60,19 @@ struct nvc_runner {
   ArgPair* h_pairs = nullptr;   // pinned
   int32_t* h_tok = nullptr;     // pinned
   int last_B = 0;
-  // decode graphs keyed by (B, blocks hint)
+  // on-device temperature sampling (K8s), armed per step by nvc_runner_set_sampling
+  float* d_temps = nullptr;
+  uint64_t* d_streams = nullptr;
+  float* h_temps = nullptr;        // pinned
+  uint64_t* h_streams = nullptr;   // pinned
+  bool sampling_armed = false;
+  int last_sampling_B = 0;
+  uint64_t sampling_seed = 0;
+  // decode graphs keyed by (B, 2 * blocks hint + sampling)
   std::map<std::pair<int, int>, cudaGraphExec_t> graphs;
   int launches_per_decode = 0;
   int last_decode_hint = 0;
+  int last_decode_key2 = 0;
 };
 
 namespace {
@@ -182,7 +191,11 @@ int run_head(nvc_runner* r, int B, bool decode, bool final_norm_done) {
   }
   rc = nvc_gemm_bf16(ctx, r->xn_last, H, r->lm_head, r->logits, r->V_l, NVC_DT_F32, B, r->V_l, H, st);     // qwen3.rs:548
   if (rc) return rc;
-  rc = nvc_argmax_last(ctx, r->logits, r->V_l, r->d_tok, r->d_tok_val, B, r->V_l, r->rank * r->V_l, st);    // llm_engine.rs:135-142
+  if (r->sampling_armed)   // llm_engine.rs:97-133, seeded and on device
+    rc = nvc_sample_gumbel(ctx, r->logits, r->V_l, r->d_temps, r->d_streams, r->sampling_seed, r->d_tok, r->d_tok_val, B,
+                           r->V_l, r->rank * r->V_l, st);
+  else
+    rc = nvc_argmax_last(ctx, r->logits, r->V_l, r->d_tok, r->d_tok_val, B, r->V_l, r->rank * r->V_l, st);    // llm_engine.rs:135-142
   if (rc || r->tp == 1) return rc;
   // TP: every rank holds (max, idx) of its vocab shard; gather the 8-byte pairs
   rc = nvc_pack_argmax_pairs(ctx, r->d_tok_val, r->d_tok, reinterpret_cast<float*>(r->d_pairs + (size_t)r->rank * B), B, st);
@@ -222,6 +235,15 @@ int decode_body(nvc_runner* r, int B, int blocks_hint) {
 }
 
 int next_pow2(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+// H2D of the armed step's temperatures / noise streams (no-op for a greedy step)
+int stage_sampling(nvc_runner* r, int B) {
+  if (!r->sampling_armed) return NVC_OK;
+  NVC_REQUIRE(r->ctx, r->last_sampling_B == B, NVC_ESTATE, "nvc_runner_set_sampling was armed for a different batch size");
+  R_CUDA(cudaMemcpyAsync(r->d_temps, r->h_temps, B * sizeof(float), cudaMemcpyHostToDevice, r->stream));
+  R_CUDA(cudaMemcpyAsync(r->d_streams, r->h_streams, B * sizeof(uint64_t), cudaMemcpyHostToDevice, r->stream));
+  return NVC_OK;
+}
 
 }  // namespace
 
@@ -305,6 +327,10 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if ((rc = dev_alloc(r, &r->d_tok, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_tok_val, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_pairs, Bm * tp))) return rc;
+  if ((rc = dev_alloc(r, &r->d_temps, Bm))) return rc;
+  if ((rc = dev_alloc(r, &r->d_streams, Bm))) return rc;
+  R_CUDA(cudaMallocHost(&r->h_temps, Bm * sizeof(float)));
+  R_CUDA(cudaMallocHost(&r->h_streams, Bm * sizeof(uint64_t)));
   r->h_stage_ints = 3 * T + (Bm + 1) + Bm * r->max_blocks_cap + 2 * Bm;
   R_CUDA(cudaMallocHost(&r->h_stage, r->h_stage_ints * sizeof(int32_t)));
   R_CUDA(cudaMallocHost(&r->h_pairs, Bm * tp * sizeof(ArgPair)));
@@ -321,6 +347,8 @@ int nvc_runner_destroy(nvc_runner* r) {
   if (r->h_stage) cudaFreeHost(r->h_stage);
   if (r->h_pairs) cudaFreeHost(r->h_pairs);
   if (r->h_tok) cudaFreeHost(r->h_tok);
+  if (r->h_temps) cudaFreeHost(r->h_temps);
+  if (r->h_streams) cudaFreeHost(r->h_streams);
   if (r->stream) cudaStreamDestroy(r->stream);
   delete r;
   return NVC_OK;
@@ -517,12 +545,15 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
     R_CUDA(cudaMemcpyAsync(r->d_ctx, hctx, B * 4, cudaMemcpyHostToDevice, st));
     R_CUDA(cudaMemcpyAsync(r->d_bt, hbt, (size_t)B * cap * 4, cudaMemcpyHostToDevice, st));
   }
-  int rc = nvc_embed_gather(ctx, r->d_ids, r->embed, r->x, N, r->cfg.hidden_size, r->cfg.vocab_size, st);
+  int rc = stage_sampling(r, B);
+  if (rc) return rc;
+  rc = nvc_embed_gather(ctx, r->d_ids, r->embed, r->x, N, r->cfg.hidden_size, r->cfg.vocab_size, st);
   if (rc) return rc;
   bool fnd = false;
   rc = run_layers(r, N, false, B, max_seqlen, 0, &fnd, paged);
   if (rc) return rc;
   rc = run_head(r, B, false, fnd);
+  r->sampling_armed = false;
   if (rc) return rc;
   r->last_B = B;
   return finish_tokens(r, B, out_tokens);
@@ -587,9 +618,11 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
   R_CUDA(cudaMemcpyAsync(r->d_ctx, h + 3 * B, B * 4, cudaMemcpyHostToDevice, st));
   R_CUDA(cudaMemcpyAsync(r->d_bt, hbt, (size_t)B * cap * 4, cudaMemcpyHostToDevice, st));
   const int hint = std::min(next_pow2(max_blocks), cap);
-  int rc;
+  int rc = stage_sampling(r, B);
+  if (rc) return rc;
+  const int key2 = 2 * hint + (r->sampling_armed ? 1 : 0);
   if (r->opt.use_cuda_graph) {
-    const auto key = std::make_pair(B, hint);
+    const auto key = std::make_pair(B, key2);
     auto it = r->graphs.find(key);
     if (it == r->graphs.end()) {
       // capture this (batch size, context bucket) once; pointers and shapes are fixed inside
@@ -598,7 +631,7 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
       rc = decode_body(r, B, hint);
       cudaGraph_t graph = nullptr;
       cudaError_t ce = cudaStreamEndCapture(st, &graph);
-      if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+      if (rc) { r->sampling_armed = false; if (graph) cudaGraphDestroy(graph); return rc; }
       R_CUDA(ce);
       cudaGraphExec_t exec = nullptr;
       ce = cudaGraphInstantiate(&exec, graph, 0);
@@ -611,12 +644,41 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
   } else {
     const uint64_t l0 = ctx->launches;
     rc = decode_body(r, B, hint);
-    if (rc) return rc;
+    if (rc) { r->sampling_armed = false; return rc; }
     r->launches_per_decode = (int)(ctx->launches - l0);
   }
+  r->sampling_armed = false;
   r->last_B = B;
   r->last_decode_hint = hint;
+  r->last_decode_key2 = key2;
   return finish_tokens(r, B, out_tokens);
+}
+
+extern "C" int nvc_runner_set_sampling(nvc_runner* r, const float* temperatures, const uint64_t* streams, int B,
+                                       uint64_t seed) {
+  if (!r) return NVC_EINVAL;
+  nvc_ctx* ctx = r->ctx;
+  if (!temperatures) {   // disarm: the next step is greedy
+    r->sampling_armed = false;
+    return NVC_OK;
+  }
+  NVC_REQUIRE(ctx, streams && B > 0 && B <= r->opt.max_num_seqs, NVC_EINVAL, "bad sampling arguments");
+  for (int b = 0; b < B; ++b) NVC_REQUIRE(ctx, temperatures[b] > 0.f, NVC_EINVAL, "temperature must be positive");
+  if (seed != r->sampling_seed) {
+    // the seed is a kernel argument baked into the captured decode graphs of sampling steps
+    NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
+    R_CUDA(cudaStreamSynchronize(r->stream));
+    for (auto it = r->graphs.begin(); it != r->graphs.end();) {
+      if (it->first.second & 1) { cudaGraphExecDestroy(it->second); it = r->graphs.erase(it); } else { ++it; }
+    }
+    r->sampling_seed = seed;
+  }
+  R_CUDA(cudaStreamSynchronize(r->stream));   // the previous step's H2D out of the pinned buffers has completed
+  memcpy(r->h_temps, temperatures, B * sizeof(float));
+  memcpy(r->h_streams, streams, B * sizeof(uint64_t));
+  r->last_sampling_B = B;
+  r->sampling_armed = true;
+  return NVC_OK;
 }
 
 extern "C" int nvc_runner_last_logits(nvc_runner* r, float* out, int B) {
@@ -639,7 +701,7 @@ extern "C" int nvc_runner_time_decode(nvc_runner* r, int iters, float* ms_per_st
   R_CUDA(cudaEventCreate(&e0));
   R_CUDA(cudaEventCreate(&e1));
   cudaStream_t st = r->stream;
-  auto it = r->graphs.find(std::make_pair(r->last_B, r->last_decode_hint));
+  auto it = r->graphs.find(std::make_pair(r->last_B, r->last_decode_key2));
   R_CUDA(cudaStreamSynchronize(st));
   R_CUDA(cudaEventRecord(e0, st));
   int rc = NVC_OK;

@@ -253,6 +253,16 @@ class Qwen3ModelRunner:
         check(st, "nvc_runner_decode", self.ctx.h)
         return out
 
+    def set_sampling(self, temperatures, streams, seed: int) -> None:
+        """Arms on-device temperature sampling for the next step (None disarms -> greedy)."""
+        if temperatures is None:
+            check(self.l.nvc_runner_set_sampling(self.handle, None, None, 0, 0), "nvc_runner_set_sampling", self.ctx.h)
+            return
+        t = np.ascontiguousarray(np.asarray(temperatures, dtype=np.float32))
+        s = np.ascontiguousarray(np.asarray(streams, dtype=np.uint64))
+        check(self.l.nvc_runner_set_sampling(self.handle, _p(t), _p(s), len(t), C.c_uint64(seed & (2 ** 64 - 1))),
+              "nvc_runner_set_sampling", self.ctx.h)
+
     def last_logits(self, B: int) -> np.ndarray:
         """fp32 logits [B, vocab / tp_size] of this rank's vocab shard for the last step."""
         v_l = self.cfg.vocab_size // self.ctx.tp_size
@@ -359,6 +369,12 @@ class LLMEngine:
 
     def is_finished(self) -> bool:
         return bool(self.l.nvc_engine_is_finished(self.h))
+
+    def set_sampling(self, enabled: bool, seed: int = 0) -> None:
+        """On-device temperature sampling with each request's SamplingParams.temperature
+        (seeded, reproducible per sequence); off (default) = greedy argmax."""
+        self._ck(self.l.nvc_engine_set_sampling(self.h, int(enabled), C.c_uint64(seed & (2 ** 64 - 1))),
+                 "nvc_engine_set_sampling")
 
     def output_of(self, seq_id: int) -> Tuple[List[int], bool]:
         n = C.c_int()

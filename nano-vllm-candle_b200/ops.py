@@ -236,3 +236,15 @@ class Context:
         self._ck(self.l.nvc_argmax_last(self.h, _ptr(logits), logits.stride(0), _ptr(idx), _ptr(val), B, V,
                                         index_offset, _stream()), "nvc_argmax_last")
         return idx, val
+
+    def sample_gumbel(self, logits, temperatures, streams, seed: int, index_offset=0):
+        """K8s: seeded Gumbel-max draw per row; streams: int64 tensor holding the u64 stream ids."""
+        _req(logits, torch.float32, "logits"); _req(temperatures, torch.float32, "temperatures")
+        _req(streams, torch.int64, "streams")
+        B, V = logits.shape
+        idx = torch.empty((B,), dtype=torch.int32, device=logits.device)
+        val = torch.empty((B,), dtype=torch.float32, device=logits.device)
+        self._ck(self.l.nvc_sample_gumbel(self.h, _ptr(logits), logits.stride(0), _ptr(temperatures), _ptr(streams),
+                                          C.c_uint64(seed & (2 ** 64 - 1)), _ptr(idx), _ptr(val), B, V, index_offset,
+                                          _stream()), "nvc_sample_gumbel")
+        return idx, val

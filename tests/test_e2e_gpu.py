@@ -184,6 +184,41 @@ def test_prefix_cached_prefill_logits_match_uncached(tiny):
     assert err <= 2e-2 and d01 <= 2e-2
 
 
+def test_on_device_sampling_is_reproducible_and_follows_the_oracle(tiny):
+    """SURVEY 8f.3: temperature sampling on device (seeded Gumbel-max).  Same seed -> same tokens;
+    every sampled token, teacher-forced through the fp32 oracle with the same Philox stream
+    (seq_id, step), must be within tolerance of the oracle's best perturbed score."""
+    from oracle import sampling_oracle as S
+    cfg, runner, fp32, _ = tiny
+    prompts = [synth.make_prompts(1, n, cfg.vocab_size, 300 + n)[0] for n in (9, 40, 17)]
+    seed, T, steps = 20261104, 0.8, 12
+
+    def run(sd):
+        e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, 16)), runner)
+        e.set_sampling(True, sd)
+        return [o.token_ids for o in e.generate(prompts, eng.SamplingParams(T, steps, True))]
+
+    a, b, c = run(seed), run(seed), run(seed + 1)
+    assert a == b, "same seed must reproduce the same tokens"
+    assert a != c, "a different seed must change the draws"
+    greedy = [o.token_ids for o in eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, 16)),
+                                                 runner).generate(prompts, eng.SamplingParams(T, steps, True))]
+    assert a != greedy, "sampling at T = 0.8 over a flat random-init distribution must leave the greedy path"
+    exact = total = 0
+    for sid, (p, toks) in enumerate(zip(prompts, a)):
+        ids = torch.tensor([list(p) + list(toks[:-1])])
+        logits = fp32.compute_logits(fp32.forward(ids))[0]
+        for i, t in enumerate(toks):
+            row = logits[len(p) - 1 + i].numpy()
+            sc = S.gumbel_scores(row, T, seed, S.stream_id(sid, i))
+            # logits within 2e-2 of the oracle (north_star) -> scores within 2e-2 / T, both sides
+            assert sc.max() - sc[t] <= 2 * 2e-2 / T + 1e-4, f"seq {sid} step {i}: token {t} is {sc.max() - sc[t]:.4f} below the best draw"
+            exact += int(S.sample(row, T, seed, S.stream_id(sid, i)) == t)
+            total += 1
+    diag(f"[e2e tiny sampling] {exact}/{total} sampled tokens identical to the fp32 oracle's draw")
+    assert exact >= total * 0.8
+
+
 def test_causality_property(tiny):
     """tests/layer_test.rs:164-202: logits of a prefix do not depend on later tokens -
     here: last-token logits of [a] equal position-0 logits of [a, b] in the oracle, and the

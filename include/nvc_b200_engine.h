@@ -66,6 +66,30 @@ int nvc_runner_load_weight(nvc_runner* r, const char* hf_name, const nvc_bf16* d
 /* Verifies every tensor arrived, builds the rope table.  Must be called before any step. */
 int nvc_runner_finalize(nvc_runner* r);
 
+/* ---- native HF checkpoint loading (host side; error text in nvc_hf_last_error, thread-local) ---- */
+const char* nvc_hf_last_error(void);
+/* Qwen3Config::from_hf_dir (src/models/qwen3.rs:77-101): <model_dir>/config.json, same required
+ * fields, head_dim defaults to hidden_size / num_attention_heads, rope_theta to 1e6.
+ * *tie_word_embeddings (optional) = that flag of config.json (absent = 0). */
+int nvc_qwen3_config_from_hf_dir(const char* model_dir, nvc_qwen3_config* out, int* tie_word_embeddings);
+/* Qwen3ForCausalLM::from_hf_dir (src/models/qwen3.rs:515-536) for an existing runner: reads
+ * model.safetensors, or every shard named by model.safetensors.index.json, through mmap; BF16 is
+ * handed over as is, F16 / F32 are rounded to bf16 (nearest even) on the host; every tensor goes
+ * through nvc_runner_load_weight; a checkpoint without lm_head.weight uses embed_tokens (tied
+ * embeddings; the reference fails there, :525-528); ends with nvc_runner_finalize. */
+int nvc_runner_load_hf_dir(nvc_runner* r, const char* model_dir);
+/* safetensors inspection (what the loader sees), also used by the CPU tests. */
+typedef struct nvc_safetensors nvc_safetensors;
+enum { NVC_ST_BF16 = 0, NVC_ST_F16 = 1, NVC_ST_F32 = 2, NVC_ST_OTHER = 3 };
+int nvc_safetensors_open(const char* path, nvc_safetensors** out);
+int nvc_safetensors_close(nvc_safetensors* st);
+int nvc_safetensors_num_tensors(const nvc_safetensors* st);
+/* shape4: up to 4 dims, padded with 1. */
+int nvc_safetensors_tensor_info(const nvc_safetensors* st, int i, const char** name, int* dtype, int* ndim,
+                                int64_t* shape4);
+/* Converts tensor `name` to bf16 into the HOST buffer `out` (capacity in elements). */
+int nvc_safetensors_read_bf16(const nvc_safetensors* st, const char* name, nvc_bf16* out, int64_t capacity_elems);
+
 /* One prefill step over B sequences / N new tokens (flat varlen layout replacing build_batch's
  * right-padded [B, max_len], src/engine/llm_engine.rs:60-95).  Synchronous: returns the greedy
  * next token of every sequence in out_tokens[B] (argmax, ties -> last index,

@@ -39,6 +39,14 @@ def declare(l: C.CDLL) -> None:
         "nvc_runner_destroy": [_vp],
         "nvc_runner_load_weight": [_vp, C.c_char_p, _vp, _i64, _i64],
         "nvc_runner_finalize": [_vp],
+        "nvc_qwen3_config_from_hf_dir": [C.c_char_p, C.POINTER(Qwen3ConfigC), C.POINTER(C.c_int)],
+        "nvc_runner_load_hf_dir": [_vp, C.c_char_p],
+        "nvc_safetensors_open": [C.c_char_p, C.POINTER(_vp)],
+        "nvc_safetensors_close": [_vp],
+        "nvc_safetensors_num_tensors": [_vp],
+        "nvc_safetensors_tensor_info": [_vp, _i, C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                        C.POINTER(C.c_int64)],
+        "nvc_safetensors_read_bf16": [_vp, C.c_char_p, _vp, _i64],
         "nvc_runner_prefill": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
         "nvc_runner_prefill_paged": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp],
         "nvc_runner_decode": [_vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp],
@@ -69,6 +77,8 @@ def declare(l: C.CDLL) -> None:
         fn.restype = _i
     l.nvc_engine_add_request.argtypes = [_vp, _vp, _i, C.c_double, _i, _i]
     l.nvc_engine_add_request.restype = _i64
+    l.nvc_hf_last_error.argtypes = []
+    l.nvc_hf_last_error.restype = C.c_char_p
     l.nvc_engine_last_error.argtypes = [_vp]
     l.nvc_engine_last_error.restype = C.c_char_p
     l.nvc_runner_weight_bytes.argtypes = [_vp]

@@ -470,7 +470,7 @@ extern "C" int nvc_runner_finalize(nvc_runner* r) {
   const size_t want = 3 + 11 * (size_t)r->cfg.num_hidden_layers;
   NVC_REQUIRE(ctx, r->loaded.size() == want, NVC_ESTATE,
               "missing weights: " + std::to_string(r->loaded.size()) + " of " + std::to_string(want) +
-                  " tensors loaded (lm_head.weight has no tied-embedding fallback, qwen3.rs:525-528)");
+                  " tensors loaded (nvc_runner_load_weight takes lm_head.weight explicitly; nvc_runner_load_hf_dir ties it to embed_tokens when absent)");
   int rc = nvc_rope_table_init_sync(ctx, r->cfg.rope_theta, r->cfg.head_dim, r->opt.max_model_len, r->rope);
   if (rc) return rc;
   r->finalized = true;

@@ -100,24 +100,24 @@ class Qwen3Config:
     rope_theta: float = 1e6
     bos_token_id: int = 151643
     eos_token_id: int = 151645
+    tie_word_embeddings: bool = False
 
     @staticmethod
     def from_hf_dir(model_dir: str) -> "Qwen3Config":
-        with open(os.path.join(model_dir, "config.json")) as f:
-            d = json.load(f)
-        return Qwen3Config(
-            vocab_size=d["vocab_size"], hidden_size=d["hidden_size"],
-            head_dim=d.get("head_dim") or d["hidden_size"] // d["num_attention_heads"],
-            num_hidden_layers=d["num_hidden_layers"], num_attention_heads=d["num_attention_heads"],
-            num_key_value_heads=d["num_key_value_heads"], intermediate_size=d["intermediate_size"],
-            max_position_embeddings=d["max_position_embeddings"], rms_norm_eps=d["rms_norm_eps"],
-            hidden_act=d["hidden_act"], rope_theta=d.get("rope_theta") or 1e6,
-            bos_token_id=d["bos_token_id"], eos_token_id=d["eos_token_id"])
+        """Qwen3Config::from_hf_dir (qwen3.rs:77-101), parsed by the native loader."""
+        l = _lib.lib()
+        c, tie = Qwen3ConfigC(), C.c_int()
+        st = l.nvc_qwen3_config_from_hf_dir(os.fsencode(model_dir), C.byref(c), C.byref(tie))
+        if st != 0:
+            raise NvcError(st, "nvc_qwen3_config_from_hf_dir", l.nvc_hf_last_error().decode())
+        cfg = Qwen3Config(**{n: getattr(c, n) for n in Qwen3Config.__dataclass_fields__ if n not in ("hidden_act", "tie_word_embeddings")})
+        cfg.tie_word_embeddings = bool(tie.value)
+        return cfg
 
     @staticmethod
     def from_any(cfg) -> "Qwen3Config":
         names = [f for f in Qwen3Config.__dataclass_fields__]
-        return Qwen3Config(**{n: getattr(cfg, n) for n in names})
+        return Qwen3Config(**{n: getattr(cfg, n) for n in names if hasattr(cfg, n)})
 
     def to_c(self) -> Qwen3ConfigC:
         return Qwen3ConfigC(self.vocab_size, self.hidden_size, self.head_dim, self.num_hidden_layers,
@@ -200,15 +200,17 @@ class Qwen3ModelRunner:
 
     @classmethod
     def from_hf_dir(cls, ctx, model_dir: str, **kw) -> "Qwen3ModelRunner":
-        """Qwen3ModelRunner::from_hf_dir (llm_engine.rs:43-58): config.json + single
-        model.safetensors (qwen3.rs:515-536)."""
-        from safetensors import safe_open
+        """Qwen3ModelRunner::from_hf_dir (llm_engine.rs:43-58): config.json + model.safetensors
+        (qwen3.rs:515-536), read by the native loader (mmap, sharded index, bf16 / f16 / f32, tied
+        embeddings) - no Python tensor library on this path."""
         cfg = Qwen3Config.from_hf_dir(model_dir)
         r = cls(ctx, cfg, **kw)
-        with safe_open(os.path.join(model_dir, "model.safetensors"), framework="pt", device="cpu") as f:
-            for name in f.keys():
-                r.load_weight(name, f.get_tensor(name))
-        r.finalize()
+        st = r.l.nvc_runner_load_hf_dir(r.handle, os.fsencode(model_dir))
+        if st != 0:
+            msg = r.l.nvc_hf_last_error().decode() + " | " + r.l.nvc_last_error(ctx.h).decode()
+            r.close()
+            raise NvcError(st, "nvc_runner_load_hf_dir", msg)
+        r._final = True
         return r
 
     def load_weight(self, name: str, t) -> None:

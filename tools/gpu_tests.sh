@@ -17,7 +17,7 @@ run() {  # name, timeout, pytest args...
   echo "exit $r" | tee -a gpurun_out/summary.txt
   [ $r -ne 0 ] && rc=1
 }
-groups=${@:-elementwise gemm decode prefill layers e2e tp}
+groups=${@:-elementwise gemm decode prefill layers e2e loader tp}
 for g in $groups; do
   case $g in
     elementwise) run elementwise 300 tests/test_kernels_gpu.py ;;
@@ -26,6 +26,7 @@ for g in $groups; do
     prefill) run prefill 300 tests/test_gemm_attn_gpu.py -k prefill ;;
     e2e) run e2e 900 tests/test_e2e_gpu.py ;;
     layers) run layers 300 tests/test_layers_gpu.py ;;
+    loader) run loader 300 tests/test_hf_loader.py ;;
     tp) run tp 700 tests/test_tp_gpu.py ;;
     *) run "$(basename "$g" .py)" 900 "$g" ;;
   esac

@@ -43,6 +43,17 @@ BLOCK_SIZE = 256
 CPU_SAMPLE_SEQS = 1          # sequences of the batch the CPU legs process per step
 
 
+def _ncu_traffic():
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the paged decode kernel on this
+    workload, from the committed `ncu --set full` capture (profiles/paged_decode_ncu_traffic.json,
+    written by tools/ncu_summarize.py); None if no capture has been committed."""
+    p = os.path.join(ROOT, "profiles", "paged_decode_ncu_traffic.json")
+    try:
+        return float(json.load(open(p))["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def _peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -265,8 +276,8 @@ def run_ours(args):
         "e2e": {"value": BATCH * K / t_e2e, "unit": "tok/s", "ms_per_step": t_e2e / K * 1e3,
                 "h2d_bytes_per_step": BATCH * 4 * 4 + BATCH * cap * 4, "d2h_bytes_per_step": BATCH * 4},
         "gpu_launches": launches_per_step * K,
-        "roofline": {"kernel": "paged_decode_kernel<2> (K5)", "bound": "hbm", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+        "roofline": {"kernel": "pdmma::paged_decode_mma_kernel (K5)", "bound": "hbm", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": _ncu_traffic(), "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": attn_bytes, "us_per_launch": breakdown["paged_decode_us"],
                      "whole_step_hbm_frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
         "breakdown": breakdown,

@@ -220,7 +220,7 @@ int nvc_argmax_last(nvc_ctx* ctx, const float* logits, int ld, int32_t* idx, flo
  * reference draws from softmax((l - max) / max(T, 1e-6)) with an unseeded rand::rng() (:128); this is
  * the Gumbel-max form of the same categorical distribution with counter-based, reproducible noise:
  *   idx[b] = argmax_i( logits[b, i] / max(T_b, 1e-6) + g ),  g = -log(-log(u)),
- *   u = ((x >> 8) + 0.5) * 2^-24,  x = word (gi % 4) of Philox4x32-10(key = seed,
+ *   u = (2 * (x >> 9) + 1) * 2^-24 (exact in fp32, never 0 or 1),  x = word (gi % 4) of Philox4x32-10(key = seed,
  *   counter = (gi / 4, streams[b] lo, streams[b] hi, 0)),  gi = index_offset + i  (global vocab index),
  * ties -> last index.  val[b] = the winning perturbed score, so tensor-parallel vocab shards merge
  * like the greedy (max, idx) pairs.  temperatures: f32 [B]; streams: u64 [B] (one value per

@@ -501,7 +501,9 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 }
 
 __device__ __forceinline__ float gumbel_from_bits(uint32_t x) {
-  const float u = (float)(x >> 8) * 5.9604644775390625e-08f + 2.98023223876953125e-08f;   // (x >> 8) * 2^-24 + 2^-25, exact
+  // u = (2 * (x >> 9) + 1) * 2^-24: an odd 24-bit integer over 2^24, exact in fp32, in [2^-24, 1 - 2^-24]
+  // (a 24-bit draw + half a step would round to 1.0f at the top and make g = +inf)
+  const float u = (float)(((x >> 9) << 1) | 1u) * 5.9604644775390625e-08f;
   return -logf(-logf(u));
 }
 

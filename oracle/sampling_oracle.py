@@ -41,7 +41,8 @@ def uniforms(V: int, seed: int, stream: int, index_offset: int = 0) -> np.ndarra
     ctr[:, 1] = stream & 0xFFFFFFFF
     ctr[:, 2] = (stream >> 32) & 0xFFFFFFFF
     x = philox4x32_10(ctr, (seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)).reshape(-1)
-    return ((x >> np.uint32(8)).astype(np.float32) * np.float32(2.0 ** -24) + np.float32(2.0 ** -25)).astype(np.float32)
+    # (2 * (x >> 9) + 1) * 2^-24: odd 24-bit integer over 2^24, exact in float32, never 0 or 1
+    return ((((x >> np.uint32(9)) << np.uint32(1)) | np.uint32(1)).astype(np.float32) * np.float32(2.0 ** -24)).astype(np.float32)
 
 
 def gumbel_scores(logits: np.ndarray, temperature: float, seed: int, stream: int, index_offset: int = 0) -> np.ndarray:

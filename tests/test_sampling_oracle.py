@@ -32,6 +32,10 @@ def test_philox4x32_10_known_answers():
 def test_uniforms_are_open_interval_and_depend_on_global_index_only():
     u = S.uniforms(4096, seed=1234, stream=S.stream_id(7, 3))
     assert u.dtype == np.float32 and (u > 0).all() and (u < 1).all()
+    # the extreme noise words still give finite Gumbel values (a 24-bit draw + 2^-25 rounds to 1.0f)
+    ext = ((((np.array([0, 0xFFFFFFFF], np.uint32) >> np.uint32(9)) << np.uint32(1)) | np.uint32(1)).astype(np.float32)
+           * np.float32(2.0 ** -24))
+    assert ext[0] == np.float32(2.0 ** -24) and ext[1] == np.float32(1 - 2.0 ** -24) and ext[1] < 1
     # a vocab shard sees the same noise as the full row (tensor-parallel invariance)
     shard = S.uniforms(1024, seed=1234, stream=S.stream_id(7, 3), index_offset=2048)
     assert np.array_equal(shard, u[2048:3072])

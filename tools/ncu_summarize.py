@@ -2,6 +2,9 @@
 
     python tools/ncu_summarize.py launches <launches.csv>       # --metrics gpu__time_duration.sum --csv log
     python tools/ncu_summarize.py full <raw.csv>                 # ncu -i x.ncu-rep --page raw --csv
+    python tools/ncu_summarize.py traffic <raw.csv> <kernel regex> <out.json> [note]
+        # dram__bytes_read.sum + dram__bytes_write.sum per launch of the matching kernels -> the
+        # file bench.py's roofline.traffic reads (profiles/paged_decode_ncu_traffic.json)
 """
 import collections
 import csv
@@ -51,5 +54,26 @@ def full(path):
         print("| " + " | ".join(cells) + " |")
 
 
+def _bytes(v, unit):
+    v = float(v.replace(",", ""))
+    return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
+
+
+def traffic(path, pattern, out, note=""):
+    import json
+    rows = list(csv.reader(open(path)))
+    hdr, units, data = rows[0], rows[1], rows[2:]
+    ik, ir, iw, it = (hdr.index(n) for n in ("Kernel Name", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__time_duration.sum"))
+    sel = [d for d in data if re.search(pattern, d[ik])]
+    rd = [_bytes(d[ir], units[ir]) for d in sel]
+    wr = [_bytes(d[iw], units[iw]) for d in sel]
+    json.dump({"kernel": pattern, "launches": len(sel), "grid": sel[0][hdr.index("Grid Size")],
+               "dram_bytes_read_per_launch": sum(rd) / len(rd), "dram_bytes_write_per_launch": sum(wr) / len(wr),
+               "dram_bytes_per_launch": (sum(rd) + sum(wr)) / len(sel),
+               "gpu_time_us_under_ncu": [float(d[it].replace(",", "")) for d in sel], "note": note},
+              open(out, "w"), indent=1)
+    print(open(out).read())
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2])
+    {"launches": launches, "full": full, "traffic": traffic}[sys.argv[1]](*sys.argv[2:])

@@ -29,6 +29,8 @@
 #include <cmath>
 #include <cstdlib>
 
+extern int g_nvc_debug[8];
+
 namespace {
 
 constexpr int kTileM = 256, kHalf = 128, BK = 64;
@@ -42,9 +44,12 @@ constexpr int kRingBudget = 200 * 1024;
 // tensor-memory columns [0, NT/2) and [256, 256 + NT/2), one accumulator stage - used when a
 // decode GEMM has between #pairs and 2 x #pairs 256-wide tiles, so that wider tiles finish in ONE
 // wave (Qwen3-8B gate_up at batch 256: 96 tiles of 256 -> 70 tiles of 352 on 74 pairs).
+// NT in [128, 256): one narrower MMA per k-step, two accumulator stages - more, smaller tiles when
+// 256-wide ones quantise badly onto the 74 pairs (96 tiles = two waves of which the second is 30 %
+// full; 128 tiles of 192 = two full waves of 3/4 the work each).
 template <int NT>
 struct PairCfg {
-  static_assert(NT == 256 || (NT > 256 && NT <= 512 && NT % 32 == 0), "tile width");
+  static_assert(NT >= 128 && NT <= 512 && NT % 32 == 0, "tile width");
   static constexpr bool kTwo = NT > 256;
   static constexpr int NH = kTwo ? NT / 2 : NT;          // N of one tcgen05.mma
   static constexpr int kBoxRowsB = NH / 2;               // rows of W one CTA supplies per MMA (multiple of 8)
@@ -73,6 +78,17 @@ __device__ __forceinline__ void tma_load_2d_pair(uint32_t smem_dst, const CUtens
   asm volatile(
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
+}
+// 4-D forms for atom-packed weights (see launch_pair): coordinates {k in block, row in atom, k-block, atom row}
+__device__ __forceinline__ void tma_load_4d_pair(uint32_t smem_dst, const CUtensorMap* m, uint32_t leader_bar,
+                                                 int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
+      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_l2_4d(const CUtensorMap* m, int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
+  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"
+               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_dst, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
@@ -180,7 +196,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total, int kb_per_split,
                  int num_tiles, int n_tiles, int prefetch_w, int epi, float4* __restrict__ ws,
-                 long long* __restrict__ trace) {
+                 long long* __restrict__ trace, int w_packed) {
   using cfg = PairCfg<NT>;
   constexpr int kStages = cfg::kStages;
   constexpr int kStageBytes = cfg::kStageBytes;
@@ -250,8 +266,11 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       const int n = min(num_kb, kPrefetchKb);
       for (int kb = 0; kb < n; ++kb) {
 #pragma unroll
-        for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i)
-          ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, n_tile * NT + i * cfg::NH + h * cfg::kBoxRowsB);
+        for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i) {
+          const int row = n_tile * NT + i * cfg::NH + h * cfg::kBoxRowsB;
+          if (w_packed) tma_prefetch_l2_4d(&tma_b, 0, 0, kb_begin + kb, row >> 3);
+          else ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, row);
+        }
       }
     }
     __syncwarp();
@@ -276,13 +295,17 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           const int k0 = (kb_begin + kb) * BK;
           tma_load_2d_pair(dst, &tma_a, leader_full0 + 8u * s, k0, a_row);
 #pragma unroll
-          for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i)     // this CTA's rows of each MMA's weight tile
-            tma_load_2d_pair(dst + kBytesA + i * (cfg::kBoxRowsB * BK * 2), &tma_b, leader_full0 + 8u * s, k0,
-                             b_row + i * cfg::NH);
+          for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i) {   // this CTA's rows of each MMA's weight tile
+            const uint32_t bdst = dst + kBytesA + i * (cfg::kBoxRowsB * BK * 2);
+            if (w_packed) tma_load_4d_pair(bdst, &tma_b, leader_full0 + 8u * s, 0, 0, kb_begin + kb, (b_row + i * cfg::NH) >> 3);
+            else tma_load_2d_pair(bdst, &tma_b, leader_full0 + 8u * s, k0, b_row + i * cfg::NH);
+          }
           if (prefetch_w && kb + kPrefetchKb < num_kb) {
 #pragma unroll
-            for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i)
-              ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb + kPrefetchKb) * BK, b_row + i * cfg::NH);
+            for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i) {
+              if (w_packed) tma_prefetch_l2_4d(&tma_b, 0, 0, kb_begin + kb + kPrefetchKb, (b_row + i * cfg::NH) >> 3);
+              else ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb + kPrefetchKb) * BK, b_row + i * cfg::NH);
+            }
           }
           if (tr && it < 32) trace[3 + it] = clock64();
         }
@@ -413,16 +436,36 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
   return NVC_OK;
 }
 
-#define NVC_PAIR_WIDTHS(X) X(256) X(320) X(352) X(384) X(448) X(512)
+#define NVC_PAIR_WIDTHS(X) X(128) X(160) X(192) X(224) X(256) X(320) X(352) X(384) X(448) X(512)
+
+// Atom-packed weights: W[N, K] stored as [N/8][K/64][8][64], i.e. every 8-row x 128-byte swizzle atom
+// (1 KB) is contiguous in HBM instead of eight 128-byte pieces K*2 bytes apart.  A TMA box of R rows of
+// one k-block is R/8 contiguous kilobytes spaced (K/64) KB apart; it lands in shared memory exactly
+// like the 2-D box [R][64] of the row-major layout.
+int make_tma_packed(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t K, uint64_t N, uint32_t box_rows) {
+  cuuint64_t gdim[4] = {64, 8, K / 64, N / 8};
+  cuuint64_t gstr[3] = {128, 1024, (K / 64) * 1024};
+  cuuint32_t box[4] = {64, 8, 1, box_rows / 8};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = ctx->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstr, box,
+                                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    nvc_set_error(ctx, "cuTensorMapEncodeTiled (packed weights) failed with CUresult " + std::to_string((int)r));
+    return NVC_EINVAL;
+  }
+  return NVC_OK;
+}
 
 template <int NT>
 int launch_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M, int N,
-                int K, int S, int epi, cudaStream_t stream, long long* trace) {
+                int K, int S, int epi, cudaStream_t stream, long long* trace, bool packed) {
   using cfg = PairCfg<NT>;
   CUtensorMap ta, tb;
   int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, kHalf);
   if (rc) return rc;
-  rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, cfg::kBoxRowsB);
+  rc = packed ? make_tma_packed(ctx, &tb, W, (uint64_t)K, (uint64_t)N, cfg::kBoxRowsB)
+              : make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, cfg::kBoxRowsB);
   if (rc) return rc;
   const int kb_total = K / BK;
   const int m_tiles = (M + kTileM - 1) / kTileM, n_tiles = (N + NT - 1) / NT;
@@ -440,7 +483,8 @@ int launch_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, voi
   dim3 grid(clusters * 2 * S);
   NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, gemm_pair_kernel<NT>, grid, dim3(kThreads), cfg::kSmemBytes, stream, 2 * S,
                                          ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, tiles, n_tiles,
-                                         (M <= kTileM) ? 1 : 0, epi, reinterpret_cast<float4*>(ctx->gemm_ws), trace));
+                                         (M <= kTileM) ? 1 : 0, epi, reinterpret_cast<float4*>(ctx->gemm_ws), trace,
+                                         packed ? 1 : 0));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -481,17 +525,43 @@ extern "C" int nvc_gemm_pair_init(nvc_ctx* ctx) {
   return NVC_OK;
 }
 
-// Schedule choice (cycle model fitted to tools/gemm_microbench.py --pair on B200):
-//  * a k-block costs ~2 * NT tensor cycles per pair (~600 for NT = 256 once the weights stream from HBM);
-//  * the persistent schedule (S = 1) pays ~10k cycles once (prologue, first loads, last epilogue);
-//    a split-K cluster pays ~12k (prologue, drain, publish, cluster barrier, reduce);
-//  * waves = ceil(tiles / co-resident clusters of that size).
-// Between one and two waves of 256-wide tiles, the narrowest wider tile that fits ONE wave wins.
+// Schedule choice.
 static void choose_schedule(const nvc_ctx* ctx, int M, int N, int kb, int* nt_out, int* s_out) {
   const int m_tiles = (M + kTileM - 1) / kTileM;
+  auto avail = [&](int S) { return ctx->pair_clusters[S] > 0 ? ctx->pair_clusters[S] : ctx->num_sms / (2 * S); };
+  if (m_tiles == 1) {
+    // Decode (one m-tile): tile width x in-cluster split-K from a linear cost model fitted to
+    // tools/gemm_microbench.py --narrow on B200 (profiles/r01_gemm_narrow_sweep_s12.txt: 146 measured
+    // configurations of 11 shapes, the model's pick is within 1 % of the best measured on every shape):
+    //   t[us] = waves * (ceil(kb / S) * (0.0738 + 0.00105 * NT) + 6.23 + [S > 1] * (1.99 + 0.161 * S))
+    // Narrow tiles win where 256-wide ones quantise badly onto the 74 pairs (8B gate_up: 96 tiles = two
+    // waves, the second 30 % full, vs 128 tiles of 192 = two full waves of 3/4 the work) and where a
+    // split-K cluster would otherwise leave a third of the SMs idle (8B o_proj: 16 tiles x 3 splits
+    // = 96 SMs vs 22 tiles of 192 x 3 = 132).
+    double best = 1e30;
+    int best_s = 1, best_nt = 256;
+    static const int kWidths[] = {256, 224, 192, 160, 128};
+    for (int nt : kWidths) {
+      const int tiles = (N + nt - 1) / nt;
+      for (int S = 1; S <= 4 && S <= kb; ++S) {
+        const double waves = ceil((double)tiles / avail(S));
+        if (S > 1 && waves > 2) continue;            // not measured: several waves of split-K clusters
+        const double kbs = ceil((double)kb / S);
+        const double t = waves * (kbs * (0.0738 + 0.00105 * nt) + 6.23 + (S > 1 ? 1.99 + 0.161 * S : 0.0));
+        if (t < best * 0.995) { best = t; best_s = S; best_nt = nt; }
+      }
+    }
+    *nt_out = best_nt;
+    *s_out = best_s;
+    return;
+  }
+  // Prefill (several m-tiles): 256-wide tiles; cycle model fitted to tools/gemm_microbench.py --pair:
+  //  * a k-block costs ~2 * NT tensor cycles per pair (~600 for NT = 256 once the weights stream from HBM);
+  //  * the persistent schedule (S = 1) pays ~10k cycles once (prologue, first loads, last epilogue);
+  //    a split-K cluster pays ~12k (prologue, drain, publish, cluster barrier, reduce);
+  //  * waves = ceil(tiles / co-resident clusters of that size).
   double best = 1e30;
   int best_s = 1, best_nt = 256;
-  auto avail = [&](int S) { return ctx->pair_clusters[S] > 0 ? ctx->pair_clusters[S] : ctx->num_sms / (2 * S); };
   for (int S = 1; S <= 4 && S <= kb; ++S) {
     const int tiles = m_tiles * ((N + 255) / 256);
     const double waves = ceil((double)tiles / avail(S));
@@ -500,9 +570,8 @@ static void choose_schedule(const nvc_ctx* ctx, int M, int N, int kb, int* nt_ou
     if (t < best * 0.98) { best = t; best_s = S; best_nt = 256; }
   }
   // Wide tiles (NT > 256, one wave instead of two for 75..148 tiles) are NOT chosen automatically: measured on
-  // Qwen3-8B gate_up at batch 256 (N 24576: 70 tiles of 352) 53.1 us vs 53.6 us for two waves of 256-wide tiles -
-  // at M = 256 the GEMM sits on the HBM / L2-fabric ridge (k-block pace 808 cycles vs 704 of MMA), and the single
-  // accumulator stage exposes the 11k-cycle epilogue.  They stay selectable (force_splits = 1000 + NT) and tested.
+  // Qwen3-8B gate_up at batch 256 (N 24576: 70 tiles of 352) 53.1 us vs 53.6 us for two waves of 256-wide tiles;
+  // the single accumulator stage exposes the 11k-cycle epilogue.  They stay selectable and tested.
   *nt_out = best_nt;
   *s_out = best_s;
 }
@@ -510,12 +579,14 @@ static void choose_schedule(const nvc_ctx* ctx, int M, int N, int kb, int* nt_ou
 // force_splits: 0 = choose; 1..4 = in-cluster split-K factor with 256-wide tiles; 1000 + NT = one-wave wide tiles
 extern "C" int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32,
                              int M, int N, int K, int force_splits, int epi, void* stream, long long* trace) {
+  const bool packed = g_nvc_debug[2] == 1;   // experiment: W is atom-packed (make_tma_packed)
+  // force_splits >= 1000: 10000 * S + 1000 + NT (S omitted = 1)
   int nt = 256, S = 1;
-  if (force_splits >= 1000) { nt = force_splits - 1000; S = 1; }
+  if (force_splits >= 1000) { nt = force_splits % 10000 - 1000; S = force_splits / 10000; S = S < 1 ? 1 : (S > 4 ? 4 : S); }
   else if (force_splits > 0) { S = force_splits > 4 ? 4 : force_splits; }
   else choose_schedule(ctx, M, N, K / BK, &nt, &S);
 #define X(NT) \
-  if (nt == NT) return launch_pair<NT>(ctx, A, lda, W, C, ldc, out_f32, M, N, K, S, epi, nvc_stream(stream), trace);
+  if (nt == NT) return launch_pair<NT>(ctx, A, lda, W, C, ldc, out_f32, M, N, K, S, epi, nvc_stream(stream), trace, packed);
   NVC_PAIR_WIDTHS(X)
 #undef X
   NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported pair tile width");

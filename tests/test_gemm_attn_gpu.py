@@ -80,6 +80,16 @@ GEMM_SHAPES = [
     (4096, 4096, 128, 512, 1512),  # 128 wide tiles: two per cluster through the single accumulator stage
     (256, 24576, 4096, 512, 1352), # 8B gate_up at batch 256: 70 tiles, one wave
     (256, 24576, 4096, 0, 0),      # the same through the schedule choice
+    # narrow pair tiles (one MMA of N = NT < 256, two accumulator stages): force_splits = 10000 * S + 1000 + NT
+    (256, 1536, 512, 512, 1192),   # 8 tiles of 192
+    (300, 2240, 192, 512, 1224),   # NT = 224, ragged M, exact N
+    (256, 1040, 256, 512, 1160),   # NT = 160, ragged last tile (80 valid columns)
+    (512, 1024, 1024, 512, 1128),  # NT = 128, two m-tiles, ring wraps
+    (4096, 3072, 256, 512, 1192),  # 256 tiles of 192: persistent, accumulator stages alternate
+    (256, 4096, 4096, 512, 31192), # 8B o_proj: 22 tiles of 192 (last one 64 wide) x split 3
+    (256, 6144, 4096, 512, 21192), # 8B qkv: 32 tiles x split 2
+    (256, 4096, 12288, 512, 41128),# 8B down: NT 128, split 4
+    (256, 24576, 4096, 512, 1192), # 8B gate_up shape: 128 tiles, two full waves
 ]
 
 
@@ -130,6 +140,9 @@ SILU_SHAPES = [
     (300, 512, 448, 512, 3),       # pair kernel, split-K 3, ragged M
     (256, 704, 256, 512, 1352),    # wide pair tile: unit straddles the two accumulators
     (2048, 3072, 1024, 0, 0),      # prefill-sized, persistent pair schedule
+    (256, 12288, 4096, 512, 1192), # 8B gate_up at batch 256 on 192-wide pair tiles (6 gate/up groups per tile)
+    (256, 880, 256, 512, 21160),   # NT = 160 (5 units), split 2, ragged last tile
+    (300, 448, 320, 512, 1224),    # NT = 224, ragged M
 ]
 
 

@@ -13,20 +13,38 @@ ctx = ops.Context(0)
 BF16 = torch.bfloat16
 
 
-def bench(M, N, K, bn=0, splits=0, out_dtype=BF16, iters=20):
+def pack_atoms(w):
+    """[N, K] row-major -> [N/8][K/64][8][64]: every 8-row x 128-byte swizzle atom contiguous (gemm_pair.cu make_tma_packed)."""
+    N, K = w.shape
+    return w.view(N // 8, 8, K // 64, 64).permute(0, 2, 1, 3).contiguous().view(N, K)
+
+
+def bench(M, N, K, bn=0, splits=0, out_dtype=BF16, iters=20, packed=False, check=False):
     """GPU time per GEMM: `iters` launches over rotating (cold) weight copies captured in ONE CUDA
     graph, so host launch cost (python + 2 tensor-map encodes, ~11 us) is not what is measured."""
     ncopies = max(2, min(64, int(300e6 // (N * K * 2)) + 1))
     a = torch.randn(M, K, device="cuda").to(BF16)
     ws = [torch.randn(N, K, device="cuda").to(BF16) for _ in range(ncopies)]
     out = torch.empty(M, N, device="cuda", dtype=out_dtype)
+    if check or packed:
+        want = ctx.gemm(a, ws[0], force_bn=bn, force_splits=splits).clone()
+    if packed:
+        ws = [pack_atoms(w) for w in ws]
+        ctx.l.nvc_debug_set(2, 1)
     for w in ws[:2]:
         ctx.gemm(a, w, out=out, force_bn=bn, force_splits=splits)
     torch.cuda.synchronize()
+    if packed:
+        got = ctx.gemm(a, ws[0], force_bn=bn, force_splits=splits)
+        torch.cuda.synchronize()
+        if not torch.equal(got, want):
+            print(f"  !! packed result differs: max abs {(got.float() - want.float()).abs().max().item():.4e}")
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g):
         for i in range(iters):
             ctx.gemm(a, ws[i % ncopies], out=out, force_bn=bn, force_splits=splits)
+    if packed:
+        ctx.l.nvc_debug_set(2, 0)
     g.replay()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -120,13 +138,50 @@ if __name__ == "__main__":
     if "--single" in sys.argv:      # one shape, a few plain launches (for ncu)
         i = sys.argv.index("--single")
         M, N, K, bn = [int(x) for x in sys.argv[i + 1:i + 5]]
+        sp = int(sys.argv[i + 5]) if len(sys.argv) > i + 5 else 1
         a = torch.randn(M, K, device="cuda").to(BF16)
         ws = [torch.randn(N, K, device="cuda").to(BF16) for _ in range(6)]
         out = torch.empty(M, N, device="cuda", dtype=BF16)
         for w in ws:
-            ctx.gemm(a, w, out=out, force_bn=bn, force_splits=1)
+            ctx.gemm(a, w, out=out, force_bn=bn, force_splits=sp)
         torch.cuda.synchronize()
         print("single ok")
+        sys.exit(0)
+    if "--packed" in sys.argv:      # atom-packed weights vs row-major on the decode shapes (pair kernel)
+        cases = [(256, 6144, 4096, [21192, 21256]), (256, 4096, 4096, [21128, 31192, 31256]),
+                 (256, 24576, 4096, [1192, 1256, 1224]), (256, 4096, 12288, [31192, 31256, 21128]),
+                 (256, 151936, 4096, [1256]), (4096, 4096, 4096, [1256])]
+        for (M, N, K, cfgs) in cases:
+            us, tf = bench_cublas(M, N, K)
+            print(f"{M:6d} {N:6d} {K:6d} cuBLAS               -> {us:9.2f} us {tf:8.1f} TF/s", flush=True)
+            for sp in cfgs:
+                for packed in (False, True):
+                    us, gbs, tf = bench(M, N, K, 512, sp, packed=packed)
+                    print(f"{M:6d} {N:6d} {K:6d} cfg={sp:5d} packed={int(packed)} -> {us:9.2f} us {tf:8.1f} TF/s {gbs:8.1f} GB/s", flush=True)
+        sys.exit(0)
+    if "--narrow" in sys.argv:      # narrow pair tiles x in-cluster split-K on the decode (M = 256) shapes
+        shapes = [(256, 6144, 4096), (256, 4096, 4096), (256, 24576, 4096), (256, 4096, 12288), (256, 151936, 4096),
+                  (256, 5120, 5120), (256, 7168, 5120), (256, 34816, 5120), (256, 5120, 17408),
+                  (128 + 64, 24576, 4096), (512, 24576, 4096)]
+        for (M, N, K) in shapes:
+            us, tf = bench_cublas(M, N, K)
+            print(f"{M:6d} {N:6d} {K:6d} cuBLAS        -> {us:9.2f} us {tf:8.1f} TF/s", flush=True)
+            us, gbs, tf = bench(M, N, K, 512, 0)
+            print(f"{M:6d} {N:6d} {K:6d} auto          -> {us:9.2f} us {tf:8.1f} TF/s", flush=True)
+            res = []
+            for nt in (128, 160, 192, 224, 256):
+                for S in (1, 2, 3, 4):
+                    tiles = -(-N // nt) * -(-M // 256)
+                    if S > 1 and tiles > (0, 74, 33, 22, 15)[S] * 2:
+                        continue
+                    try:
+                        us, gbs, tf = bench(M, N, K, 512, 10000 * S + 1000 + nt)
+                        res.append((us, nt, S))
+                        print(f"{M:6d} {N:6d} {K:6d} nt={nt:3d} S={S} tiles={tiles:4d} -> {us:9.2f} us {tf:8.1f} TF/s {gbs:8.1f} GB/s", flush=True)
+                    except Exception as ex:
+                        print(f"{M} {N} {K} nt={nt} S={S} failed: {ex}")
+            res.sort()
+            print(f"{M:6d} {N:6d} {K:6d} best: " + ", ".join(f"nt={n} S={s} {u:.2f}us" for u, n, s in res[:4]), flush=True)
         sys.exit(0)
     if "--pair" in sys.argv:        # CTA-pair kernel vs the best 1-CTA tiles vs cuBLAS, M > 128
         shapes = [(256, 6144, 4096), (256, 4096, 4096), (256, 24576, 4096), (256, 4096, 12288), (256, 151936, 4096),

@@ -120,16 +120,19 @@ def trace_pair(M, N, K, splits):
     torch.cuda.synchronize()
     t = t.cpu().tolist()
     t0 = t[0]
-    kb = min(32, K // 64 // (splits if 1 <= splits <= 4 else 1))
+    S = splits if 1 <= splits <= 4 else (max(1, splits // 10000) if splits >= 1000 else 1)
+    kb = min(32, K // 64 // S)
     print(f"pair trace M={M} N={N} K={K} splits={splits} (cycles from kernel start, CTA 0)")
     print("  cluster set up    ", t[1] - t0, " pdl wait done", t[2] - t0)
     print("  tma issued  kb:   ", [t[3 + i] - t0 for i in range(kb)])
     print("  full waited kb:   ", [t[40 + i] - t0 for i in range(kb)])
     print("  mma all committed ", t[80] - t0)
     print("  epilogue start    ", t[81] - t0)
-    if 1 < splits <= 4:
+    if S > 1:
         print("  partials parked   ", t[82] - t0, " cluster barrier passed", t[85] - t0)
     print("  epilogue end      ", t[83] - t0)
+    if S == 1:
+        print("  last tile epilogue", t[86] - t0, "->", t[87] - t0)
     print("  kernel end        ", t[84] - t0)
 
 
@@ -146,6 +149,10 @@ if __name__ == "__main__":
             ctx.gemm(a, w, out=out, force_bn=bn, force_splits=sp)
         torch.cuda.synchronize()
         print("single ok")
+        sys.exit(0)
+    if "--trace-pair" in sys.argv:
+        for sp in (1256, 1192, 31192, 21192, 21128):
+            trace_pair(256, 24576 if sp < 10000 else 4096, 4096, sp)
         sys.exit(0)
     if "--packed" in sys.argv:      # atom-packed weights vs row-major on the decode shapes (pair kernel)
         cases = [(256, 6144, 4096, [21192, 21256]), (256, 4096, 4096, [21128, 31192, 31256]),
@@ -169,10 +176,10 @@ if __name__ == "__main__":
             us, gbs, tf = bench(M, N, K, 512, 0)
             print(f"{M:6d} {N:6d} {K:6d} auto          -> {us:9.2f} us {tf:8.1f} TF/s", flush=True)
             res = []
-            for nt in (128, 160, 192, 224, 256):
+            for nt in (128, 160, 192, 224, 256, 320, 352, 384, 448, 512):
                 for S in (1, 2, 3, 4):
                     tiles = -(-N // nt) * -(-M // 256)
-                    if S > 1 and tiles > (0, 74, 33, 22, 15)[S] * 2:
+                    if (S > 1 and tiles > (0, 74, 33, 22, 15)[S] * 2) or (nt > 256 and S > 1):
                         continue
                     try:
                         us, gbs, tf = bench(M, N, K, 512, 10000 * S + 1000 + nt)

@@ -103,6 +103,17 @@ int nvc_runner_prefill(nvc_runner* r, const int32_t* ids, const int32_t* positio
 int nvc_runner_prefill_paged(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* cu_seqlens,
                              const int32_t* slot_mapping, const int32_t* block_tables, int max_blocks,
                              const int32_t* context_lens, int B, int N, int max_seqlen, int32_t* out_tokens);
+/* Mixed step (chunked prefill): the first num_decode sequences have exactly one query
+ * token (cu_seqlens[b] == b) and attend through the paged DECODE kernel (K5); the other B -
+ * num_decode sequences are prompt chunks of any length through the paged PREFILL kernel (K4
+ * paged); everything else (embedding, norms, GEMMs, KV store, head) runs once over all N tokens.
+ * out_tokens[B]: next token of every sequence from its last query row (the caller ignores it for
+ * a chunk that does not end its prompt).  num_decode == B is a decode step without a CUDA graph;
+ * num_decode == 0 is nvc_runner_prefill_paged. */
+int nvc_runner_step_mixed(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* cu_seqlens,
+                          const int32_t* slot_mapping, const int32_t* block_tables, int max_blocks,
+                          const int32_t* context_lens, int num_decode, int B, int N, int max_seqlen,
+                          int32_t* out_tokens);
 /* One decode step: one new token per sequence, attention over the paged cache. */
 int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* slot_mapping,
                       const int32_t* block_tables, int max_blocks, const int32_t* context_lens, int B,
@@ -142,7 +153,12 @@ typedef struct nvc_scheduler_config {
   /* Beyond the reference; 0 = the reference's behaviour. */
   int32_t enable_prefix_caching;   /* 8f.1: hash-chained dedup of full KV blocks (upstream nano-vllm's
                                       BlockManager, which block_manager.rs:24-29 says it will mirror)     */
-  int32_t reserved[3];
+  int32_t enable_chunked_prefill;  /* 8f.2: one step = the decode tokens of the running sequences + as many prompt
+                                      tokens of waiting sequences as the token budget allows; long prompts are
+                                      split over steps; max_num_seqs bounds ALL running sequences and the budget
+                                      counts only tokens actually computed (the two scheduler.rs quirks fixed).
+                                      Needs max_num_batched_tokens >= max_num_seqs.                             */
+  int32_t reserved[2];
 } nvc_scheduler_config;
 
 typedef struct nvc_schedule_info {
@@ -151,6 +167,9 @@ typedef struct nvc_schedule_info {
   int32_t num_tokens;     /* prefill: new tokens in the step; decode: num_seqs */
   int32_t max_blocks;     /* width of block_tables                             */
   int32_t max_seqlen;
+  int32_t num_decode_seqs; /* chunked mode: the first num_decode_seqs sequences have one query token each and
+                              go through paged decode attention; without chunked prefill: num_seqs of a decode
+                              step, 0 of a prefill step                                                        */
 } nvc_schedule_info;
 
 /* StepOutput (src/engine/llm_engine.rs:328-333). */
@@ -159,6 +178,9 @@ typedef struct nvc_step_output {
   int32_t num_tokens;     /* reference convention: prefill = sum of seq lens AFTER the append, decode = -num_seqs */
   int32_t num_seqs;
   int32_t num_finished;   /* sequences that finished in this step */
+  int32_t num_query_tokens;  /* tokens computed in this step (sum of q_len)                                    */
+  int32_t num_sampled;       /* sequences that received a token (chunked mode: not the unfinished chunks)      */
+  int32_t num_decode_seqs;   /* leading one-token sequences of the step (= num_seqs of a decode step)          */
 } nvc_step_output;
 
 /* runner may be NULL: the engine then behaves like DummyModelRunner (next = last_token + 1,
@@ -175,6 +197,9 @@ int nvc_engine_schedule(nvc_engine* e, nvc_schedule_info* info);
 int nvc_engine_step_inputs(const nvc_engine* e, const int32_t** ids, const int32_t** positions,
                            const int32_t** cu_seqlens, const int32_t** slot_mapping,
                            const int32_t** block_tables, const int32_t** context_lens, const int64_t** seq_ids);
+/* Chunked mode: emit[b] != 0 when sequence b of the last schedule ends its pending tokens in this
+ * step and takes the sampled token (always 1 without chunked prefill). */
+int nvc_engine_step_emit_mask(const nvc_engine* e, const int32_t** emit);
 /* Scheduler::post_process (:213-249) for the batch of the last schedule. */
 int nvc_engine_post_process(nvc_engine* e, const int32_t* token_ids, int n);
 /* LLMEngine::step (:239-264): schedule -> runner -> post_process. */

@@ -22,15 +22,17 @@ class RunnerOptionsC(C.Structure):
 class SchedulerConfigC(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("max_num_seqs", "max_num_batched_tokens", "eos",
                                          "num_kvcache_blocks", "kvcache_block_size",
-                                         "enable_prefix_caching")] + [("reserved", C.c_int32 * 3)]
+                                         "enable_prefix_caching", "enable_chunked_prefill")] + [("reserved", C.c_int32 * 2)]
 
 
 class ScheduleInfoC(C.Structure):
-    _fields_ = [(n, C.c_int32) for n in ("is_prefill", "num_seqs", "num_tokens", "max_blocks", "max_seqlen")]
+    _fields_ = [(n, C.c_int32) for n in ("is_prefill", "num_seqs", "num_tokens", "max_blocks", "max_seqlen",
+                                         "num_decode_seqs")]
 
 
 class StepOutputC(C.Structure):
-    _fields_ = [(n, C.c_int32) for n in ("is_prefill", "num_tokens", "num_seqs", "num_finished")]
+    _fields_ = [(n, C.c_int32) for n in ("is_prefill", "num_tokens", "num_seqs", "num_finished",
+                                         "num_query_tokens", "num_sampled", "num_decode_seqs")]
 
 
 def declare(l: C.CDLL) -> None:
@@ -50,6 +52,7 @@ def declare(l: C.CDLL) -> None:
         "nvc_runner_prefill": [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
         "nvc_runner_prefill_paged": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _vp],
         "nvc_runner_decode": [_vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _vp],
+        "nvc_runner_step_mixed": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _vp],
         "nvc_runner_set_sampling": [_vp, _vp, _vp, _i, C.c_uint64],
         "nvc_runner_last_logits": [_vp, _vp, _i],
         "nvc_runner_time_decode": [_vp, _i, C.POINTER(C.c_float), C.POINTER(C.c_int)],
@@ -58,6 +61,7 @@ def declare(l: C.CDLL) -> None:
         "nvc_engine_destroy": [_vp],
         "nvc_engine_schedule": [_vp, C.POINTER(ScheduleInfoC)],
         "nvc_engine_step_inputs": [_vp] + [C.POINTER(_pi32)] * 6 + [C.POINTER(C.POINTER(C.c_int64))],
+        "nvc_engine_step_emit_mask": [_vp, C.POINTER(_pi32)],
         "nvc_engine_post_process": [_vp, _vp, _i],
         "nvc_engine_step": [_vp, C.POINTER(StepOutputC)],
         "nvc_engine_is_finished": [_vp],

@@ -36,6 +36,7 @@ struct Sequence {
   size_t num_tokens = 0;
   size_t num_prompt_tokens = 0;
   size_t num_cached_tokens = 0;
+  size_t num_computed_tokens = 0;   // chunked prefill: tokens whose K / V are in the cache
   double temperature = 1.0;
   size_t max_tokens = 64;
   bool ignore_eos = false;
@@ -59,6 +60,7 @@ using SeqPtr = std::shared_ptr<Sequence>;
 struct Block {
   int ref_count = 0;
   bool has_hash = false;
+  bool ready = false;   // chunked prefill: the block's K / V have been computed (a hit needs it)
   uint64_t hash = 0;
   std::vector<int32_t> token_ids;
 };
@@ -114,6 +116,7 @@ struct BlockManager {
   int num_blocks_;
   int block_size_;
   bool prefix_caching;
+  bool chunked = false;   // chunked prefill: blocks are registered at allocation but computed over several steps
   std::vector<Block> blocks;
   FreeList free_;
   std::unordered_map<uint64_t, int32_t> hash_to_block;
@@ -130,6 +133,7 @@ struct BlockManager {
     Block& b = blocks[id];
     b.ref_count = 1;
     b.has_hash = false;
+    b.ready = false;
     b.token_ids.clear();
     free_.remove(id);
     return b;
@@ -161,7 +165,8 @@ struct BlockManager {
           if (it != hash_to_block.end()) id = it->second;
         }
         if (id < 0 || !blocks[id].has_hash || blocks[id].hash != h || blocks[id].token_ids.size() != n ||
-            !std::equal(toks, toks + n, blocks[id].token_ids.begin()) || (i + 1) * bs >= s.num_tokens)
+            !std::equal(toks, toks + n, blocks[id].token_ids.begin()) || (i + 1) * bs >= s.num_tokens ||
+            (chunked && !blocks[id].ready))
           miss = true;
       }
       if (miss) {
@@ -185,7 +190,9 @@ struct BlockManager {
     s.num_cached_tokens = 0;
   }
   bool can_append(const Sequence& s) const {
-    return free_.size() >= (size_t)((s.len() % block_size_ == 1) ? 1 : 0);
+    // a block is missing only when the newest token opens one (len % block_size == 1) and the table
+    // does not hold it yet (it does when that token is still part of the prompt: chunked prefill)
+    return free_.size() >= (size_t)((s.len() % block_size_ == 1 && s.block_table.size() < s.num_blocks()) ? 1 : 0);
   }
   void may_append(Sequence& s) {
     const size_t bs = (size_t)block_size_;
@@ -217,7 +224,9 @@ struct Scheduler {
 
   explicit Scheduler(const nvc_scheduler_config& c)
       : max_num_seqs(c.max_num_seqs), max_num_batched_tokens(c.max_num_batched_tokens),
-        block_manager(c.num_kvcache_blocks, c.kvcache_block_size, c.enable_prefix_caching != 0), eos(c.eos) {}
+        block_manager(c.num_kvcache_blocks, c.kvcache_block_size, c.enable_prefix_caching != 0), eos(c.eos) {
+    block_manager.chunked = c.enable_chunked_prefill != 0;
+  }
 
   bool is_finished() const { return waiting.empty() && running.empty(); }
   void add(const SeqPtr& s) { waiting.push_back(s); }
@@ -276,7 +285,79 @@ struct Scheduler {
   void preempt(const SeqPtr& seq) {
     seq->status = Status::Waiting;
     block_manager.deallocate(*seq);
+    seq->num_computed_tokens = 0;
     waiting.push_front(seq);
+  }
+
+  // Chunked prefill (no counterpart in the reference, whose schedule() is either a
+  // whole-prompt prefill step or a decode step, scheduler.rs:106-111).  One step =
+  //   1. every running sequence, in queue order as schedule_decode visits them: a sequence with one
+  //      pending token (decode, or the last token of its prompt) appends exactly as in
+  //      scheduler.rs:159-198 (victims are preempted from the back of the queue); a sequence in the
+  //      middle of its prompt reserves one token of the budget;
+  //   2. the rest of the token budget goes to those prompt chunks in order, then
+  //   3. to waiting sequences while running.size() < max_num_seqs (the bound holds over ALL running
+  //      sequences, not per round) - unless this step preempted, which means the pool is full.
+  // The batch lists the one-token sequences first (they take the paged decode kernel).
+  // q_lens[i] = tokens of out[i] computed in this step; it emits a token iff q_lens[i] == pending.
+  bool schedule_chunked(std::vector<SeqPtr>& out, std::vector<int32_t>& q_lens, int* num_decode) {
+    std::vector<SeqPtr> ones, chunks, visited;
+    size_t budget = max_num_batched_tokens;
+    bool preempted = false;
+    while (!running.empty() && visited.size() < max_num_seqs && budget > 0) {
+      SeqPtr seq = running.front();
+      running.pop_front();
+      const size_t pending = seq->len() - seq->num_computed_tokens;
+      if (pending == 1) {
+        const size_t before = waiting.size();
+        const bool ok = ensure_can_append(seq);
+        preempted |= waiting.size() != before;
+        if (!ok) continue;
+        block_manager.may_append(*seq);
+        ones.push_back(seq);
+      } else {
+        chunks.push_back(seq);
+      }
+      budget -= 1;
+      visited.push_back(seq);
+    }
+    for (auto it = visited.rbegin(); it != visited.rend(); ++it) running.push_front(*it);
+    std::vector<int32_t> chunk_q;
+    for (auto& seq : chunks) {
+      const size_t pending = seq->len() - seq->num_computed_tokens;
+      const size_t extra = std::min(pending - 1, budget);
+      chunk_q.push_back((int32_t)(1 + extra));
+      budget -= extra;
+    }
+    while (!preempted && !waiting.empty() && running.size() < max_num_seqs && budget > 0) {
+      SeqPtr seq = waiting.front();
+      if (!block_manager.can_allocate(*seq)) break;
+      block_manager.allocate(*seq);
+      seq->num_computed_tokens = seq->num_cached_tokens;
+      const size_t q = std::min(seq->len() - seq->num_computed_tokens, budget);
+      budget -= q;
+      seq->status = Status::Running;
+      waiting.pop_front();
+      running.push_back(seq);
+      chunks.push_back(seq);
+      chunk_q.push_back((int32_t)q);
+    }
+    out = ones;
+    q_lens.assign(ones.size(), 1);
+    out.insert(out.end(), chunks.begin(), chunks.end());
+    q_lens.insert(q_lens.end(), chunk_q.begin(), chunk_q.end());
+    *num_decode = (int)ones.size();
+    return !out.empty();
+  }
+
+  // After a chunked step: the K / V of q more tokens of `seq` are in the cache; blocks that became
+  // complete may now serve prefix-cache hits.
+  void mark_computed(const SeqPtr& seq, size_t q) {
+    const size_t bs = (size_t)block_manager.block_size();
+    const size_t b0 = seq->num_computed_tokens / bs;
+    seq->num_computed_tokens += q;
+    for (size_t i = b0; i < seq->num_computed_tokens / bs && i < seq->block_table.size(); ++i)
+      block_manager.blocks[seq->block_table[i]].ready = true;
   }
 
   // scheduler.rs:219-249; returns true when the sequence finished
@@ -311,6 +392,9 @@ struct nvc_engine {
   std::vector<SeqPtr> batch;
   bool batch_is_prefill = false;
   bool batch_valid = false;
+  bool chunked = false;                        // chunked prefill / mixed steps
+  int num_decode = 0;                          // leading one-token sequences of the batch
+  std::vector<int32_t> q_lens, emit;           // per sequence of the batch
   std::vector<int32_t> ids, positions, cu_seqlens, slot_mapping, block_tables, context_lens, out_tokens;
   std::vector<int64_t> seq_ids;
   int max_blocks = 0, max_seqlen = 0;
@@ -319,7 +403,8 @@ struct nvc_engine {
   std::vector<float> temps;
   std::vector<uint64_t> streams;
 
-  nvc_engine(const nvc_scheduler_config& c, nvc_runner* r) : scheduler(c), runner(r), block_size(c.kvcache_block_size) {}
+  nvc_engine(const nvc_scheduler_config& c, nvc_runner* r)
+      : scheduler(c), runner(r), block_size(c.kvcache_block_size), chunked(c.enable_chunked_prefill != 0) {}
 };
 
 namespace {
@@ -340,7 +425,25 @@ void build_inputs(nvc_engine* e) {
   e->block_tables.clear(); e->context_lens.clear(); e->seq_ids.clear();
   e->max_blocks = 0; e->max_seqlen = 0;
   for (auto& s : e->batch) e->seq_ids.push_back(s->seq_id);
-  if (e->batch_is_prefill) {
+  if (e->chunked) {
+    // tokens [num_computed, num_computed + q) of every sequence; slot of token t = N1's rule per token:
+    // block_table[t / BS] * BS + t % BS
+    e->cu_seqlens.push_back(0);
+    e->emit.clear();
+    for (size_t b = 0; b < e->batch.size(); ++b) {
+      const Sequence& s = *e->batch[b];
+      const size_t start = s.num_computed_tokens, q = (size_t)e->q_lens[b];
+      for (size_t t = start; t < start + q; ++t) {
+        e->ids.push_back(s.token_ids[t]);
+        e->positions.push_back((int32_t)t);
+        e->slot_mapping.push_back(s.block_table[t / s.block_size] * s.block_size + (int32_t)(t % s.block_size));
+      }
+      e->cu_seqlens.push_back(e->cu_seqlens.back() + (int32_t)q);
+      e->max_seqlen = std::max(e->max_seqlen, (int)q);
+      e->context_lens.push_back((int32_t)(start + q));
+      e->emit.push_back(start + q == s.len() ? 1 : 0);
+    }
+  } else if (e->batch_is_prefill) {
     e->cu_seqlens.push_back(0);
     for (auto& sp : e->batch) {
       const Sequence& s = *sp;
@@ -365,6 +468,10 @@ void build_inputs(nvc_engine* e) {
     }
     e->max_seqlen = 1;
   }
+  if (!e->chunked) {
+    e->emit.assign(e->batch.size(), 1);
+    e->num_decode = e->batch_is_prefill ? 0 : (int)e->batch.size();
+  }
   // N2: [B, max_blocks] padded with -1
   for (auto& sp : e->batch) e->max_blocks = std::max(e->max_blocks, (int)sp->block_table.size());
   e->block_tables.assign((size_t)e->batch.size() * e->max_blocks, -1);
@@ -380,7 +487,13 @@ int do_schedule(nvc_engine* e) {
     e->err = "schedule: no waiting or running sequences";
     return NVC_ESTATE;
   }
-  if (e->scheduler.try_schedule_prefill(e->batch)) {
+  if (e->chunked) {
+    if (!e->scheduler.schedule_chunked(e->batch, e->q_lens, &e->num_decode)) {
+      e->err = "no sequence could be scheduled (KV pool exhausted)";
+      return NVC_ENOMEM;
+    }
+    e->batch_is_prefill = e->num_decode < (int)e->batch.size();
+  } else if (e->scheduler.try_schedule_prefill(e->batch)) {
     e->batch_is_prefill = true;
   } else {
     e->batch.clear();
@@ -412,7 +525,10 @@ int do_post_process(nvc_engine* e, const int32_t* toks, int n, int* finished_out
     return NVC_ESTATE;
   }
   int fin = 0;
-  for (int i = 0; i < n; ++i) fin += e->scheduler.process_single(e->batch[i], toks[i]) ? 1 : 0;
+  for (int i = 0; i < n; ++i) {
+    if (e->chunked) e->scheduler.mark_computed(e->batch[i], (size_t)e->q_lens[i]);
+    if (e->emit[i]) fin += e->scheduler.process_single(e->batch[i], toks[i]) ? 1 : 0;
+  }
   e->num_finished += fin;
   e->batch_valid = false;
   if (finished_out) *finished_out = fin;
@@ -428,6 +544,7 @@ int nvc_engine_create(const nvc_scheduler_config* cfg, nvc_runner* runner, nvc_e
   if (cfg->max_num_seqs <= 0 || cfg->max_num_batched_tokens <= 0 || cfg->kvcache_block_size <= 0 ||
       cfg->num_kvcache_blocks < 0)
     return NVC_EINVAL;
+  if (cfg->enable_chunked_prefill && cfg->max_num_batched_tokens < cfg->max_num_seqs) return NVC_EINVAL;
   *out = new nvc_engine(*cfg, runner);
   return NVC_OK;
 }
@@ -470,6 +587,7 @@ int nvc_engine_schedule(nvc_engine* e, nvc_schedule_info* info) {
   info->num_tokens = (int)e->ids.size();
   info->max_blocks = e->max_blocks;
   info->max_seqlen = e->max_seqlen;
+  info->num_decode_seqs = e->num_decode;
   return NVC_OK;
 }
 
@@ -485,6 +603,13 @@ int nvc_engine_step_inputs(const nvc_engine* e, const int32_t** ids, const int32
   if (block_tables) *block_tables = e->block_tables.data();
   if (context_lens) *context_lens = e->context_lens.data();
   if (seq_ids) *seq_ids = e->seq_ids.data();
+  return NVC_OK;
+}
+
+int nvc_engine_step_emit_mask(const nvc_engine* e, const int32_t** emit) {
+  if (!e || !emit) return NVC_EINVAL;
+  if (!e->batch_valid) return NVC_ESTATE;
+  *emit = e->emit.data();
   return NVC_OK;
 }
 
@@ -504,6 +629,10 @@ int nvc_engine_step(nvc_engine* e, nvc_step_output* out) {
   } else if (e->sampling && (rc = arm_sampling(e)) != NVC_OK) {
     e->err = "nvc_runner_set_sampling failed";
     return rc;
+  } else if (e->chunked) {
+    rc = nvc_runner_step_mixed(e->runner, e->ids.data(), e->positions.data(), e->cu_seqlens.data(), e->slot_mapping.data(),
+                               e->block_tables.data(), e->max_blocks, e->context_lens.data(), e->num_decode, B,
+                               (int)e->ids.size(), e->max_seqlen, e->out_tokens.data());
   } else if (e->batch_is_prefill) {
     bool cached_prefix = false;   // some sequence skips a cached prefix: attention must read it from the paged cache
     for (auto& s : e->batch) cached_prefix |= s->num_cached_tokens > 0;
@@ -524,13 +653,19 @@ int nvc_engine_step(nvc_engine* e, nvc_step_output* out) {
   }
   const bool is_prefill = e->batch_is_prefill;
   std::vector<SeqPtr> seqs = e->batch;
+  out->num_query_tokens = (int)e->ids.size();
+  out->num_decode_seqs = e->num_decode;
+  out->num_sampled = 0;
+  for (int32_t m : e->emit) out->num_sampled += m ? 1 : 0;
   int fin = 0;
   rc = do_post_process(e, e->out_tokens.data(), B, &fin);
   if (rc) return rc;
   out->is_prefill = is_prefill;
   out->num_seqs = B;
   out->num_finished = fin;
-  if (is_prefill) {
+  if (e->chunked) {
+    out->num_tokens = is_prefill ? out->num_query_tokens : -B;   // a mixed step reports the tokens it computed
+  } else if (is_prefill) {
     int tot = 0;
     for (auto& s : seqs) tot += (int)s->len();   // llm_engine.rs:253-254 (counted after the append)
     out->num_tokens = tot;

@@ -51,6 +51,7 @@ struct nvc_runner {
   void* decode_ws = nullptr;
   size_t decode_ws_bytes = 0;
   // step inputs on device + pinned staging
+  int32_t* d_cu2 = nullptr;     // mixed step: cu_seqlens of the prompt chunks, relative to their first token
   int32_t *d_ids = nullptr, *d_pos = nullptr, *d_cu = nullptr, *d_slots = nullptr, *d_bt = nullptr, *d_ctx = nullptr,
           *d_last_rows = nullptr, *d_tok = nullptr;
   float* d_tok_val = nullptr;
@@ -96,8 +97,11 @@ int dev_alloc(nvc_runner* r, T** p, size_t count) {
 // up, by ONE kernel that reads the peers' partials and applies residual add + RMSNorm
 // (p2p_allreduce.cu).  In that mode the norm that opens layer l+1 is produced at the end of layer
 // l, and the final norm by the last layer (*final_norm_done).
+// paged_prefill with num_decode > 0 is a mixed step (chunked prefill): the first num_decode
+// sequences are single tokens (rows 0 .. num_decode-1) and go through the paged decode kernel,
+// the other sequences through the paged prefill kernel with their own cu_seqlens (r->d_cu2).
 int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blocks_hint, bool* final_norm_done,
-               bool paged_prefill = false) {
+               bool paged_prefill = false, int num_decode = 0) {
   const nvc_qwen3_config& c = r->cfg;
   nvc_ctx* ctx = r->ctx;
   void* st = r->stream;
@@ -130,9 +134,17 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
                                     r->decode_ws, r->decode_ws_bytes, st);
     } else if (paged_prefill) {
       // cached prefix: K / V of the whole context come from the paged cache (this step's were just stored)
-      rc = nvc_prefill_attn_paged(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, r->d_ctx,
-                                  r->d_cu, B, N, max_seqlen, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size,
-                                  r->opt.num_kvcache_blocks, scale, r->attn, st);
+      rc = NVC_OK;
+      if (num_decode > 0)
+        rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
+                                      r->d_ctx, num_decode, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
+                                      r->decode_ws, r->decode_ws_bytes, st);
+      if (rc == NVC_OK && B > num_decode)
+        rc = nvc_prefill_attn_paged(ctx, r->qkv + (size_t)num_decode * r->qkv_l, r->qkv_l, Ly.k_cache, Ly.v_cache,
+                                    r->d_bt + (size_t)num_decode * r->max_blocks_cap, r->max_blocks_cap, r->d_ctx + num_decode,
+                                    num_decode ? r->d_cu2 : r->d_cu, B - num_decode, N - num_decode, max_seqlen, r->nh_l,
+                                    r->kv_l, hd, r->opt.kvcache_block_size, r->opt.num_kvcache_blocks, scale,
+                                    r->attn + (size_t)num_decode * r->nh_l * hd, st);
     } else {
       rc = nvc_prefill_attn_varlen(ctx, r->qkv, r->qkv_l, r->qkv + (size_t)r->nh_l * hd, r->qkv_l,
                                    r->qkv + (size_t)(r->nh_l + r->kv_l) * hd, r->qkv_l, r->d_cu, B, N, max_seqlen,
@@ -321,6 +333,7 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if ((rc = dev_alloc(r, &r->d_pos, T))) return rc;
   if ((rc = dev_alloc(r, &r->d_slots, T))) return rc;
   if ((rc = dev_alloc(r, &r->d_cu, Bm + 1))) return rc;
+  if ((rc = dev_alloc(r, &r->d_cu2, Bm + 1))) return rc;
   if ((rc = dev_alloc(r, &r->d_bt, Bm * r->max_blocks_cap))) return rc;
   if ((rc = dev_alloc(r, &r->d_ctx, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_last_rows, Bm))) return rc;
@@ -331,7 +344,7 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if ((rc = dev_alloc(r, &r->d_streams, Bm))) return rc;
   R_CUDA(cudaMallocHost(&r->h_temps, Bm * sizeof(float)));
   R_CUDA(cudaMallocHost(&r->h_streams, Bm * sizeof(uint64_t)));
-  r->h_stage_ints = 3 * T + (Bm + 1) + Bm * r->max_blocks_cap + 2 * Bm;
+  r->h_stage_ints = 3 * T + 2 * (Bm + 1) + Bm * r->max_blocks_cap + 2 * Bm;
   R_CUDA(cudaMallocHost(&r->h_stage, r->h_stage_ints * sizeof(int32_t)));
   R_CUDA(cudaMallocHost(&r->h_pairs, Bm * tp * sizeof(ArgPair)));
   R_CUDA(cudaMallocHost(&r->h_tok, Bm * sizeof(int32_t)));
@@ -486,7 +499,7 @@ namespace {
 // otherwise attention over the paged cache through block_tables / context_lens (K4 paged).
 int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* cu_seqlens,
                  const int32_t* slot_mapping, const int32_t* block_tables, int max_blocks, const int32_t* context_lens,
-                 int B, int N, int max_seqlen, int32_t* out_tokens) {
+                 int B, int N, int max_seqlen, int32_t* out_tokens, int num_decode = 0) {
   if (!r) return NVC_EINVAL;
   nvc_ctx* ctx = r->ctx;
   const bool paged = block_tables != nullptr;
@@ -503,6 +516,10 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
     NVC_REQUIRE(ctx, slot_mapping[i] >= -1 && slot_mapping[i] < nslots, NVC_EINVAL, "slot out of range");
   }
   const int cap = r->max_blocks_cap;
+  NVC_REQUIRE(ctx, num_decode >= 0 && num_decode <= B && (paged || num_decode == 0), NVC_EINVAL, "bad num_decode");
+  for (int b = 0; b < num_decode; ++b)
+    NVC_REQUIRE(ctx, cu_seqlens[b] == b && cu_seqlens[b + 1] == b + 1 && slot_mapping[b] >= 0, NVC_EINVAL,
+                "the first num_decode sequences must have exactly one query token and a slot");
   if (paged) {
     NVC_REQUIRE(ctx, context_lens, NVC_EINVAL, "null pointer");
     NVC_REQUIRE(ctx, max_blocks > 0 && max_blocks <= cap, NVC_ENOMEM, "block table wider than max_model_len allows");
@@ -544,13 +561,26 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
     }
     R_CUDA(cudaMemcpyAsync(r->d_ctx, hctx, B * 4, cudaMemcpyHostToDevice, st));
     R_CUDA(cudaMemcpyAsync(r->d_bt, hbt, (size_t)B * cap * 4, cudaMemcpyHostToDevice, st));
+    if (num_decode > 0 && num_decode < B) {
+      int32_t* hcu2 = hbt + (size_t)B * cap;
+      for (int b = num_decode; b <= B; ++b) hcu2[b - num_decode] = cu_seqlens[b] - num_decode;
+      R_CUDA(cudaMemcpyAsync(r->d_cu2, hcu2, (B - num_decode + 1) * 4, cudaMemcpyHostToDevice, st));
+    }
+  }
+  int hint = 0, max_seqlen_chunks = max_seqlen;
+  if (num_decode > 0) {
+    int mb = 1;
+    for (int b = 0; b < num_decode; ++b) mb = std::max(mb, (context_lens[b] + bs - 1) / bs);
+    hint = std::min(next_pow2(mb), cap);
+    max_seqlen_chunks = 1;
+    for (int b = num_decode; b < B; ++b) max_seqlen_chunks = std::max(max_seqlen_chunks, cu_seqlens[b + 1] - cu_seqlens[b]);
   }
   int rc = stage_sampling(r, B);
   if (rc) return rc;
   rc = nvc_embed_gather(ctx, r->d_ids, r->embed, r->x, N, r->cfg.hidden_size, r->cfg.vocab_size, st);
   if (rc) return rc;
   bool fnd = false;
-  rc = run_layers(r, N, false, B, max_seqlen, 0, &fnd, paged);
+  rc = run_layers(r, N, false, B, max_seqlen_chunks, hint, &fnd, paged, num_decode);
   if (rc) return rc;
   rc = run_head(r, B, false, fnd);
   r->sampling_armed = false;
@@ -577,6 +607,18 @@ extern "C" int nvc_runner_prefill_paged(nvc_runner* r, const int32_t* ids, const
   }
   return prefill_impl(r, ids, positions, cu_seqlens, slot_mapping, block_tables, max_blocks, context_lens, B, N,
                       max_seqlen, out_tokens);
+}
+
+extern "C" int nvc_runner_step_mixed(nvc_runner* r, const int32_t* ids, const int32_t* positions,
+                                     const int32_t* cu_seqlens, const int32_t* slot_mapping, const int32_t* block_tables,
+                                     int max_blocks, const int32_t* context_lens, int num_decode, int B, int N,
+                                     int max_seqlen, int32_t* out_tokens) {
+  if (r && !block_tables) {
+    nvc_set_error(r->ctx, "nvc_runner_step_mixed: null block_tables");
+    return NVC_EINVAL;
+  }
+  return prefill_impl(r, ids, positions, cu_seqlens, slot_mapping, block_tables, max_blocks, context_lens, B, N,
+                      max_seqlen, out_tokens, num_decode);
 }
 
 extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_t* positions,

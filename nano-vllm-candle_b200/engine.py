@@ -55,6 +55,12 @@ class SchedulerConfig:
     kvcache_block_size: int = 256
     enable_prefix_caching: bool = False      # beyond the reference; off = reference behaviour
 
+    enable_chunked_prefill: bool = False     # beyond the reference: mixed prefill / decode steps
+
+    def with_chunked_prefill(self, on: bool = True):
+        self.enable_chunked_prefill = on
+        return self
+
     def with_prefix_caching(self, on: bool = True):
         self.enable_prefix_caching = on
         return self
@@ -255,6 +261,18 @@ class Qwen3ModelRunner:
         check(st, "nvc_runner_decode", self.ctx.h)
         return out
 
+    def step_mixed(self, ids, positions, cu_seqlens, slot_mapping, block_tables, context_lens, num_decode: int) -> np.ndarray:
+        """One chunked-prefill step: the first num_decode sequences have one query token (paged
+        decode attention), the others are prompt chunks (paged prefill attention)."""
+        ids, positions, cu, slots, ctxl = _i32(ids), _i32(positions), _i32(cu_seqlens), _i32(slot_mapping), _i32(context_lens)
+        bt = _i32(block_tables)
+        B, N = len(cu) - 1, len(ids)
+        out = np.empty(B, dtype=np.int32)
+        st = self.l.nvc_runner_step_mixed(self.handle, _p(ids), _p(positions), _p(cu), _p(slots), _p(bt), bt.shape[1],
+                                          _p(ctxl), num_decode, B, N, int(np.max(np.diff(cu))) if B else 0, _p(out))
+        check(st, "nvc_runner_step_mixed", self.ctx.h)
+        return out
+
     def set_sampling(self, temperatures, streams, seed: int) -> None:
         """Arms on-device temperature sampling for the next step (None disarms -> greedy)."""
         if temperatures is None:
@@ -311,6 +329,9 @@ class StepOutput:
     outputs: List[Tuple[int, List[int]]]
     is_prefill: bool
     num_tokens: int
+    num_query_tokens: int = 0      # tokens computed in the step
+    num_decode_seqs: int = 0       # one-token sequences of the step
+    num_sampled: int = 0           # sequences that received a token
 
 
 @dataclass
@@ -323,6 +344,8 @@ class StepInputs:
     slot_mapping: np.ndarray
     block_tables: np.ndarray
     context_lens: np.ndarray
+    num_decode_seqs: int = 0                  # chunked mode: leading one-token sequences
+    emit: Optional[np.ndarray] = None         # chunked mode: which sequences take the sampled token
 
 
 class LLMEngine:
@@ -334,7 +357,9 @@ class LLMEngine:
         self.model_runner = model_runner
         cfg = scheduler.config
         c = SchedulerConfigC(cfg.max_num_seqs, cfg.max_num_batched_tokens, cfg.eos, cfg.num_kvcache_blocks,
-                             cfg.kvcache_block_size, int(bool(cfg.enable_prefix_caching)))
+                             cfg.kvcache_block_size, int(bool(cfg.enable_prefix_caching)),
+                             int(bool(cfg.enable_chunked_prefill)))
+        self.chunked = bool(cfg.enable_chunked_prefill)
         h = C.c_void_p()
         rh = getattr(model_runner, "handle", None)
         check(self.l.nvc_engine_create(C.byref(c), rh, C.byref(h)), "nvc_engine_create")
@@ -398,7 +423,8 @@ class LLMEngine:
                 else:
                     still.append(sid)
             self._live = still
-        return StepOutput(outputs, bool(so.is_prefill), so.num_tokens)
+        return StepOutput(outputs, bool(so.is_prefill), so.num_tokens, so.num_query_tokens, so.num_decode_seqs,
+                          so.num_sampled)
 
     def generate(self, prompts: Seq[Seq[int]], sampling_params: SamplingParams) -> List[GenerationOutput]:
         for p in prompts:
@@ -406,7 +432,10 @@ class LLMEngine:
         outs: Dict[int, List[int]] = {}
         while not self.is_finished():
             s = self.step()
-            if s.is_prefill:
+            if self.chunked:     # a mixed step: prompt tokens computed + decode tokens, counted exactly
+                self.prefill_tokens += s.num_query_tokens - s.num_decode_seqs
+                self.decode_tokens += s.num_decode_seqs
+            elif s.is_prefill:
                 self.prefill_tokens += s.num_tokens
             else:
                 self.decode_tokens += -s.num_tokens
@@ -425,10 +454,13 @@ class LLMEngine:
 
         def arr(p, n):
             return np.ctypeslib.as_array(p, shape=(n,)).copy() if n else np.empty(0, np.int32)
+        ep = C.POINTER(C.c_int32)()
+        self._ck(self.l.nvc_engine_step_emit_mask(self.h, C.byref(ep)), "nvc_engine_step_emit_mask")
         return StepInputs(
+            num_decode_seqs=info.num_decode_seqs, emit=arr(ep, B),
             is_prefill=bool(info.is_prefill), seq_ids=np.ctypeslib.as_array(sp, shape=(B,)).copy(),
             ids=arr(ptrs[0], N), positions=arr(ptrs[1], N),
-            cu_seqlens=arr(ptrs[2], B + 1) if info.is_prefill else np.empty(0, np.int32),
+            cu_seqlens=arr(ptrs[2], B + 1) if (info.is_prefill or self.chunked) else np.empty(0, np.int32),
             slot_mapping=arr(ptrs[3], N), block_tables=arr(ptrs[4], B * info.max_blocks).reshape(B, info.max_blocks),
             context_lens=arr(ptrs[5], B))
 

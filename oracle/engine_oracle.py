@@ -87,6 +87,7 @@ class Sequence:
         self.num_tokens = len(token_ids)
         self.num_prompt_tokens = len(token_ids)
         self.num_cached_tokens = 0
+        self.num_computed_tokens = 0      # chunked prefill only (SchedulerChunked): tokens whose K / V are stored
         self.temperature = sp.temperature
         self.max_tokens = sp.max_tokens
         self.ignore_eos = sp.ignore_eos
@@ -189,7 +190,9 @@ class BlockManager:
         seq.num_cached_tokens = 0
 
     def can_append(self, seq):
-        return len(self.free) >= (1 if len(seq) % self.block_size_ == 1 else 0)
+        # a block is missing only when the newest token opens one and the table does not hold it yet
+        need = len(seq) % self.block_size_ == 1 and len(seq.block_table) < seq.num_blocks()
+        return len(self.free) >= (1 if need else 0)
 
     def may_append(self, seq):
         if len(seq) % self.block_size_ == 1 and len(seq.block_table) < seq.num_blocks():
@@ -211,6 +214,8 @@ class BlockManagerPrefix(BlockManager):
         self.key: List[Optional[int]] = [None] * num_blocks
         self.tokens: List[List[int]] = [[] for _ in range(num_blocks)]
         self.key_to_block: Dict[int, int] = {}
+        self.chunked = False                 # chunked prefill: a hit needs a block whose K / V are computed
+        self.ready = [False] * num_blocks
         self.hits = 0
         self.queries = 0
 
@@ -218,6 +223,7 @@ class BlockManagerPrefix(BlockManager):
         assert self.ref[b] == 0
         self.ref[b] = 1
         self.key[b] = None
+        self.ready[b] = False
         self.tokens[b] = []
         self.free.remove(b)
 
@@ -238,7 +244,8 @@ class BlockManagerPrefix(BlockManager):
             if key is not None:
                 self.queries += 1
                 b = self.key_to_block.get(key, -1)
-            if b == -1 or self.key[b] != key or self.tokens[b] != toks or (i + 1) * bs >= len(seq):
+            if b == -1 or self.key[b] != key or self.tokens[b] != toks or (i + 1) * bs >= len(seq) \
+                    or (self.chunked and not self.ready[b]):
                 miss = True
             if miss:
                 b = self.free[0]
@@ -429,6 +436,103 @@ class Scheduler:
                 seq.status = FINISHED
                 self.block_manager.deallocate(seq)
                 self.running = deque(s for s in self.running if s.seq_id != seq.seq_id)
+
+
+class SchedulerChunked(Scheduler):
+    """Chunked prefill with mixed prefill / decode steps.  The reference
+    has no such mode (scheduler.rs:106-111 is prefill-step-or-decode-step); this restates the
+    rule the C++ engine implements, written independently from the same specification:
+
+      1. visit the running queue in order (as scheduler.rs:159-186 does).  A sequence with ONE
+         pending token appends exactly as in decode (:166-170, victims preempted from the back of
+         the queue, :188-198).  A sequence in the middle of its prompt reserves one budget token.
+      2. the remaining budget goes to those prompt chunks in order,
+      3. then to waiting sequences while len(running) < max_num_seqs (bound over ALL running
+         sequences - the fix of :118) and blocks can be allocated; the budget counts the tokens
+         actually computed (the fix of :134-138).  No admission in a step that preempted.
+    Batch order: one-token sequences first, then chunks.  A sequence receives the sampled token
+    only in the step that computes its last pending token."""
+
+    def __init__(self, cfg: SchedulerConfig, block_manager):
+        assert cfg.max_num_batched_tokens >= cfg.max_num_seqs
+        super().__init__(cfg, block_manager)
+        if hasattr(block_manager, "chunked"):
+            block_manager.chunked = True
+
+    def preempt(self, seq):
+        super().preempt(seq)
+        seq.num_computed_tokens = 0
+
+    def schedule_chunked(self):
+        """-> (seqs, q_lens, num_decode)."""
+        ones, chunks, visited = [], [], []
+        budget = self.max_num_batched_tokens
+        preempted = False
+        while self.running and len(visited) < self.max_num_seqs and budget > 0:
+            seq = self.running.popleft()
+            pending = len(seq) - getattr(seq, "num_computed_tokens", 0)
+            if pending == 1:
+                before = len(self.waiting)
+                ok = self._ensure_can_append(seq)
+                preempted |= len(self.waiting) != before
+                if not ok:
+                    continue
+                self.block_manager.may_append(seq)
+                ones.append(seq)
+            else:
+                chunks.append(seq)
+            budget -= 1
+            visited.append(seq)
+        for seq in reversed(visited):
+            self.running.appendleft(seq)
+        chunk_q = []
+        for seq in chunks:
+            extra = min(len(seq) - seq.num_computed_tokens - 1, budget)
+            chunk_q.append(1 + extra)
+            budget -= extra
+        while not preempted and self.waiting and len(self.running) < self.max_num_seqs and budget > 0:
+            seq = self.waiting[0]
+            if not self.block_manager.can_allocate(seq):
+                break
+            self.block_manager.allocate(seq)
+            seq.num_computed_tokens = seq.num_cached_tokens
+            q = min(len(seq) - seq.num_computed_tokens, budget)
+            budget -= q
+            seq.status = RUNNING
+            self.waiting.popleft()
+            self.running.append(seq)
+            chunks.append(seq)
+            chunk_q.append(q)
+        seqs = ones + chunks
+        assert seqs, "no sequence could be scheduled"
+        return seqs, [1] * len(ones) + chunk_q, len(ones)
+
+    def post_process_chunked(self, seqs, q_lens, token_ids):
+        bm, bs = self.block_manager, self.block_manager.block_size_
+        for seq, q, tok in zip(seqs, q_lens, token_ids):
+            b0 = seq.num_computed_tokens // bs
+            seq.num_computed_tokens += q
+            if hasattr(bm, "ready"):
+                for i in range(b0, min(seq.num_computed_tokens // bs, len(seq.block_table))):
+                    bm.ready[seq.block_table[i]] = True
+            if seq.num_computed_tokens == len(seq):
+                self.post_process([seq], [tok])
+
+
+def prepare_mixed(seqs: List[Sequence], q_lens: List[int]):
+    """Step inputs of a chunked step: tokens [num_computed, num_computed + q) of every sequence;
+    the slot of token t is N1's rule per token, block_table[t // BS] * BS + t % BS."""
+    ids, pos, cu, slots, ctx, emit = [], [], [0], [], [], []
+    for s, q in zip(seqs, q_lens):
+        a = s.num_computed_tokens
+        ids.extend(s.token_ids[a:a + q])
+        pos.extend(range(a, a + q))
+        slots.extend(s.block_table[t // s.block_size] * s.block_size + t % s.block_size for t in range(a, a + q))
+        cu.append(cu[-1] + q)
+        ctx.append(a + q)
+        emit.append(int(a + q == len(s)))
+    i32 = lambda x: np.asarray(x, np.int32)
+    return i32(ids), i32(pos), i32(cu), i32(slots), i32(ctx), build_block_tables(seqs), i32(emit)
 
 
 # ----------------------------------------------------------------- engine

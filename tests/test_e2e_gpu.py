@@ -184,6 +184,86 @@ def test_prefix_cached_prefill_logits_match_uncached(tiny):
     assert err <= 2e-2 and d01 <= 2e-2
 
 
+def test_chunked_prefill_generation_matches_oracle_tiny(tiny):
+    """mixed steps (decode tokens through paged decode attention next to prompt chunks
+    through paged prefill attention, one pass of everything else over all tokens).  Prompts longer
+    than the 24-token budget are split over steps while earlier sequences keep decoding; every
+    token must be the fp32 oracle's full-recompute greedy choice up to numerical ties."""
+    cfg, runner, fp32, _ = tiny
+    prompts = [synth.make_prompts(1, n, cfg.vocab_size, 700 + n)[0] for n in (9, 70, 33, 100, 5, 48)]
+    sch = eng.Scheduler(eng.SchedulerConfig(4, 24, cfg.eos_token_id, 64, 16, enable_chunked_prefill=True))
+    e = eng.LLMEngine(sch, runner)
+    for p in prompts:
+        e.add_request(p, eng.SamplingParams(1.0, 20, True))
+    mixed = steps = 0
+    while not e.is_finished():
+        s = e.step()
+        assert s.num_query_tokens <= 24
+        mixed += int(s.num_decode_seqs > 0 and s.num_query_tokens > s.num_decode_seqs)
+        steps += 1
+    diag(f"[e2e tiny chunked prefill] {steps} steps, {mixed} of them mixed decode + prompt chunk")
+    assert mixed >= 5
+    for b, p in enumerate(prompts):
+        got, fin = e.output_of(b)
+        assert fin and len(got) == 20
+        _teacher_forced_check(fp32, p, got, 4e-2, f"e2e tiny chunked prefill seq {b}")
+
+
+def test_mixed_step_logits_match_whole_prompt_prefill(tiny):
+    """One prompt prefilled whole (K4 varlen) and again in three chunks riding along with two
+    decoding sequences (nvc_runner_step_mixed): last-token logits agree to bf16 rounding and with
+    the fp32 oracle within the north_star tolerance; the decode rows of the mixed step equal a
+    plain decode step's logits for the same state within the same tolerance."""
+    cfg, runner, fp32, _ = tiny
+    bs = 16
+    prompt = synth.make_prompts(1, 3 * bs + 11, cfg.vocab_size, 990)[0]
+    others = [synth.make_prompts(1, n, cfg.vocab_size, 991 + n)[0] for n in (21, 40)]
+    # whole-prompt reference on the CUDA path
+    e0 = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, bs)), runner)
+    e0.add_request(prompt, eng.SamplingParams(1.0, 1, True))
+    si = e0.schedule()
+    runner.prefill(si.ids, si.positions, si.cu_seqlens, si.slot_mapping)
+    whole = torch.from_numpy(runner.last_logits(1))[0].clone()
+    # chunked, 27-token budget: two sequences prefilled first, then the long prompt arrives (25 tokens per step are left)
+    e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 27, cfg.eos_token_id, 64, bs, enable_chunked_prefill=True)), runner)
+    for p in others:
+        e.add_request(p, eng.SamplingParams(1.0, 8, True))
+    gen = [list(p) for p in others]
+    while True:                                                # prefill the two short prompts (27-token budget: 2 steps)
+        si = e.schedule()
+        toks = runner.step_mixed(si.ids, si.positions, si.cu_seqlens, si.slot_mapping, si.block_tables, si.context_lens,
+                                 si.num_decode_seqs)
+        for sid, t, m in zip(si.seq_ids.tolist(), toks.tolist(), si.emit.tolist()):
+            if m:
+                gen[sid].append(t)
+        e.post_process(toks)
+        if all(len(g) > len(p) for g, p in zip(gen, others)):
+            break
+    e.add_request(prompt, eng.SamplingParams(1.0, 1, True))
+    chunks = []
+    for _ in range(3):
+        si = e.schedule()
+        assert si.num_decode_seqs == 2 and si.seq_ids.tolist() == [0, 1, 2]
+        chunks.append(int(si.cu_seqlens[3] - si.cu_seqlens[2]))
+        toks = runner.step_mixed(si.ids, si.positions, si.cu_seqlens, si.slot_mapping, si.block_tables, si.context_lens,
+                                 si.num_decode_seqs)
+        lg = torch.from_numpy(runner.last_logits(3)).clone()
+        # decode rows against the oracle's full recompute of the same sequences
+        ref_dec = _oracle_last_logits(fp32, gen)
+        err_dec = (lg[:2] - ref_dec).abs().max().item()
+        assert err_dec <= 2e-2, f"decode rows of a mixed step: max-abs {err_dec:.4e}"
+        for sid in (0, 1):
+            gen[sid].append(int(toks[sid]))
+        e.post_process(toks)
+    assert chunks == [25, 25, 9] and si.emit.tolist() == [1, 1, 1]
+    ref = _oracle_last_logits(fp32, [prompt])[0]
+    d = (lg[2] - whole).abs().max().item()
+    err = (lg[2] - ref).abs().max().item()
+    diag(f"[e2e tiny mixed step] chunked vs whole-prompt logits max-abs {d:.4e}; chunked vs fp32 oracle {err:.4e}; "
+         f"decode rows vs oracle {err_dec:.4e}")
+    assert err <= 2e-2 and d <= 2e-2
+
+
 def test_on_device_sampling_is_reproducible_and_follows_the_oracle(tiny):
     """SURVEY 8f.3: temperature sampling on device (seeded Gumbel-max).  Same seed -> same tokens;
     every sampled token, teacher-forced through the fp32 oracle with the same Philox stream

@@ -220,3 +220,191 @@ def test_prefix_caching_off_is_the_default_and_never_caches():
     cpp.add_request(a, sp)
     si = cpp.schedule()
     assert si.cu_seqlens.tolist() == [0, 40] and cpp.prefix_cache_stats() == (0, 0)
+
+
+# ----------------------------------------------------------------------------- chunked prefill
+def _mk_chunked(max_num_seqs, budget, nblocks, bs, eos=0, prefix=False):
+    cfg = eng.SchedulerConfig().with_max_num_seqs(max_num_seqs).with_max_num_batched_tokens(budget) \
+        .with_eos(eos).with_kvcache(nblocks, bs).with_prefix_caching(prefix).with_chunked_prefill(True)
+    cpp = eng.LLMEngine(eng.Scheduler(cfg), eng.DummyModelRunner())
+    E.Sequence._counter = 0
+    ocfg = E.SchedulerConfig(max_num_seqs, budget, eos, nblocks, bs)
+    bm = E.BlockManagerPrefix(nblocks, bs) if prefix else E.BlockManager(nblocks, bs)
+    return cpp, E.SchedulerChunked(ocfg, bm)
+
+
+def _lockstep_chunked(cpp, sch, prompts, max_tokens, budget, max_num_seqs, bs, nblocks, arrivals=None, max_steps=100000):
+    """Drives the C++ engine and the oracle's SchedulerChunked step by step: identical batches and
+    step inputs (bit-exact), plus the invariants of the mode.  arrivals[i] = step at which prompt i
+    is added (default: all at step 0).  Returns per-step (num_decode, num_chunk_tokens)."""
+    arrivals = arrivals or [0] * len(prompts)
+    seqs_by_id, added, log = {}, 0, []
+    stored = {}                                            # seq_id -> positions whose K / V are in the cache
+    steps = 0
+    while added < len(prompts) or not sch.is_finished():
+        while added < len(prompts) and arrivals[added] <= steps:
+            cpp.add_request(prompts[added], eng.SamplingParams(1.0, max_tokens, True))
+            s = E.Sequence(list(prompts[added]), E.SamplingParams(1.0, max_tokens, True), bs)
+            seqs_by_id[s.seq_id] = s
+            sch.add(s)
+            added += 1
+        if sch.is_finished():
+            steps += 1
+            continue
+        si = cpp.schedule()
+        seqs, q_lens, nd = sch.schedule_chunked()
+        ids, pos, cu, slots, ctx, bt, emit = E.prepare_mixed(seqs, q_lens)
+        assert si.seq_ids.tolist() == [s.seq_id for s in seqs], f"step {steps}: batch differs"
+        assert si.num_decode_seqs == nd and si.is_prefill == (nd < len(seqs))
+        for name, got, want in (("ids", si.ids, ids), ("positions", si.positions, pos), ("cu_seqlens", si.cu_seqlens, cu),
+                                ("slot_mapping", si.slot_mapping, slots), ("block_tables", si.block_tables, bt),
+                                ("context_lens", si.context_lens, ctx), ("emit", si.emit, emit)):
+            assert got.dtype == np.int32 and np.array_equal(got, want), f"step {steps}: {name} differs"
+        # invariants: token budget, sequence bound, one-token sequences first, slots unique within the step
+        assert len(ids) <= budget and len(seqs) <= max_num_seqs and len(sch.running) <= max_num_seqs
+        assert all(q == 1 for q in q_lens[:nd]) and all(q >= 1 for q in q_lens)
+        assert len(set(slots.tolist())) == len(slots) and slots.min() >= 0 and slots.max() < nblocks * bs
+        # every position is computed exactly once per residency, in order, behind a fully stored context
+        for s, q in zip(seqs, q_lens):
+            have = stored.setdefault(s.seq_id, 0)
+            start = s.num_computed_tokens
+            assert start == max(have, s.num_cached_tokens) or have == 0, f"step {steps}: seq {s.seq_id} skips or repeats tokens"
+            stored[s.seq_id] = start + q
+        toks = [s.last_token + 1 for s in seqs]            # DummyModelRunner (llm_engine.rs:20-33)
+        cpp.post_process(toks)
+        before = {s.seq_id for s in sch.waiting}
+        sch.post_process_chunked(seqs, q_lens, toks)
+        for s in sch.waiting:                               # preempted: its K / V are gone
+            stored[s.seq_id] = 0
+        assert cpp.num_free_blocks() == sch.block_manager.num_free_blocks()
+        assert cpp.num_waiting() == len(sch.waiting) and cpp.num_running() == len(sch.running)
+        log.append((nd, len(ids) - nd))
+        steps += 1
+        assert steps < max_steps
+    assert cpp.is_finished()
+    for sid, s in seqs_by_id.items():
+        got, fin = cpp.output_of(sid)
+        assert fin and got == s.completion_token_ids() == [prompts[sid][-1] + 1 + i for i in range(max_tokens)]
+    return log
+
+
+@pytest.mark.parametrize("bs,nblocks,max_seqs,budget,seed", [(16, 64, 4, 48, 0), (16, 30, 6, 20, 1), (32, 64, 8, 100, 2),
+                                                             (256, 24, 5, 300, 3), (16, 25, 16, 16, 4)])
+def test_chunked_prefill_matches_oracle_step_by_step(bs, nblocks, max_seqs, budget, seed):
+    """Mixed steps: batches, ids / positions / cu_seqlens / slot_mapping / block_tables / context_lens
+    and the emit mask of the C++ scheduler against the oracle's SchedulerChunked, with staggered
+    arrivals, prompts longer than the budget and KV pressure (preemption of half-computed prompts)."""
+    rng = np.random.default_rng(seed)
+    cpp, sch = _mk_chunked(max_seqs, budget, nblocks, bs, eos=7)
+    cap = (nblocks // 2) * bs - 45
+    prompts = [rng.integers(10, 1000, size=int(rng.integers(1, 5 * bs))).tolist()[:cap] for _ in range(20)]
+    arrivals = sorted(int(rng.integers(0, 40)) for _ in prompts)
+    log = _lockstep_chunked(cpp, sch, prompts, 37, budget, max_seqs, bs, nblocks, arrivals)
+    assert any(nd > 0 and nc > 0 for nd, nc in log), "no step mixed decode tokens with prompt chunks"
+    assert cpp.num_free_blocks() == nblocks
+
+
+def test_chunked_prefill_splits_a_long_prompt_and_samples_once():
+    bs = 16
+    cpp, _ = _mk_chunked(2, 10, 16, bs)
+    p = list(range(100, 135))                               # 35 tokens, budget 10 -> chunks 10, 10, 10, 5
+    cpp.add_request(p, eng.SamplingParams(1.0, 2, True))
+    sizes, emits = [], []
+    for _ in range(4):
+        si = cpp.schedule()
+        sizes.append(len(si.ids)); emits.append(si.emit.tolist())
+        assert si.positions.tolist() == list(range(si.context_lens[0] - len(si.ids), si.context_lens[0]))
+        assert si.slot_mapping.tolist() == [si.block_tables[0, t // bs] * bs + t % bs for t in si.positions.tolist()]
+        cpp.post_process([777])
+    assert sizes == [10, 10, 10, 5] and emits == [[0], [0], [0], [1]]
+    si = cpp.schedule()                                     # now a pure decode step of the sampled token
+    assert not si.is_prefill and si.num_decode_seqs == 1 and si.ids.tolist() == [777] and si.positions.tolist() == [35]
+    cpp.post_process([778])
+    assert cpp.is_finished() and cpp.output_of(0) == ([777, 778], True)
+
+
+def test_chunked_prefill_decode_tokens_ride_along_with_a_new_prompt():
+    """A running sequence keeps decoding while a newly arrived prompt is prefilled in chunks: the
+    reference would stall it for a whole-prompt prefill step (scheduler.rs:106-111)."""
+    bs = 16
+    cpp, _ = _mk_chunked(4, 12, 32, bs)
+    sp = eng.SamplingParams(1.0, 8, True)
+    cpp.add_request([5, 6, 7], sp)
+    si = cpp.schedule(); cpp.post_process([50])
+    assert si.cu_seqlens.tolist() == [0, 3] and si.emit.tolist() == [1]
+    cpp.add_request(list(range(200, 230)), sp)              # 30 tokens -> 11 + 11 + 8 next to one decode token
+    seen = []
+    for step in range(3):
+        si = cpp.schedule()
+        assert si.num_decode_seqs == 1 and si.seq_ids.tolist() == [0, 1]
+        seen.append(int(si.cu_seqlens[2] - si.cu_seqlens[1]))
+        cpp.post_process([51 + step, 900])
+    assert seen == [11, 11, 8]
+    si = cpp.schedule()
+    assert not si.is_prefill and si.num_decode_seqs == 2 and si.ids.tolist() == [53, 900]
+
+
+def test_chunked_prefill_bounds_all_running_sequences():
+    """max_num_seqs bounds the running set, not one scheduling round (scheduler.rs:118)."""
+    cpp, _ = _mk_chunked(2, 64, 32, 16)
+    sp = eng.SamplingParams(1.0, 4, True)
+    for i in range(5):
+        cpp.add_request([10 + i, 20 + i], sp)
+    while not cpp.is_finished():
+        si = cpp.schedule()
+        assert len(si.seq_ids) <= 2 and cpp.num_running() <= 2
+        cpp.post_process([1] * len(si.seq_ids))
+    ref, _ = _mk(2, 64, 32, 16)                              # the reference rule admits two more every prefill round
+    for i in range(5):
+        ref.add_request([10 + i, 20 + i], sp)
+    ref.schedule(); ref.post_process([1, 1]); ref.schedule()
+    assert ref.num_running() == 4
+
+
+@pytest.mark.parametrize("bs,nblocks,max_seqs,budget,seed", [(16, 64, 4, 40, 0), (16, 40, 8, 24, 1), (32, 48, 3, 50, 2)])
+def test_chunked_prefill_with_prefix_caching_matches_oracle(bs, nblocks, max_seqs, budget, seed):
+    """Prefix caching under chunked prefill: a block registered at allocation serves hits only once
+    its K / V have been computed (it is filled over several steps)."""
+    rng = np.random.default_rng(seed)
+    cpp, sch = _mk_chunked(max_seqs, budget, nblocks, bs, eos=7, prefix=True)
+    prompts = _shared_prefix_prompts(rng, bs, 20)
+    arrivals = sorted(int(rng.integers(0, 60)) for _ in prompts)
+    _lockstep_chunked(cpp, sch, prompts, 2 * bs + 5, budget, max_seqs, bs, nblocks, arrivals)
+    hit, queried = cpp.prefix_cache_stats()
+    bm = sch.block_manager
+    assert (hit, queried) == (bm.hits, bm.queries) and hit > 0
+    assert cpp.num_free_blocks() == nblocks
+
+
+def test_chunked_prefill_never_hits_a_block_that_is_not_computed_yet():
+    bs = 16
+    cpp, _ = _mk_chunked(4, 30, 32, bs, prefix=True)
+    sp = eng.SamplingParams(1.0, 1, True)
+    a = list(range(100, 100 + 3 * bs + 4))
+    cpp.add_request(a, sp)
+    si = cpp.schedule(); cpp.post_process([0])             # 30 of 52 tokens: block 0 complete, block 1 partly
+    cpp.add_request(a, sp)                                  # same prompt arrives: only block 0 may be shared
+    si = cpp.schedule()
+    assert si.seq_ids.tolist() == [0, 1]
+    assert si.block_tables[1, 0] == si.block_tables[0, 0] and si.block_tables[1, 1] != si.block_tables[0, 1]
+    assert si.positions[int(si.cu_seqlens[1])] == bs        # the newcomer starts right after the shared block
+    assert cpp.prefix_cache_stats()[0] == 1
+
+
+def test_chunked_prefill_needs_a_budget_of_at_least_max_num_seqs():
+    cfg = eng.SchedulerConfig(8, 4, 0, 16, 16, enable_chunked_prefill=True)
+    with pytest.raises(eng.NvcError):
+        eng.LLMEngine(eng.Scheduler(cfg), eng.DummyModelRunner())
+
+
+def test_chunked_step_output_counts_computed_and_sampled_tokens():
+    cpp, _ = _mk_chunked(4, 6, 16, 16)
+    sp = eng.SamplingParams(1.0, 3, True)
+    cpp.add_request([1, 2, 3], sp)
+    cpp.add_request(list(range(10, 18)), sp)                # 8 tokens: 3 now, 5 in the next step
+    s = cpp.step()
+    assert s.is_prefill and (s.num_query_tokens, s.num_decode_seqs, s.num_sampled, s.num_tokens) == (6, 0, 1, 6)
+    s = cpp.step()
+    assert s.is_prefill and (s.num_query_tokens, s.num_decode_seqs, s.num_sampled) == (6, 1, 2)
+    s = cpp.step()
+    assert not s.is_prefill and (s.num_query_tokens, s.num_decode_seqs, s.num_sampled, s.num_tokens) == (2, 2, 2, -2)

@@ -629,6 +629,10 @@ int nvc_engine_step(nvc_engine* e, nvc_step_output* out) {
   } else if (e->sampling && (rc = arm_sampling(e)) != NVC_OK) {
     e->err = "nvc_runner_set_sampling failed";
     return rc;
+  } else if (e->chunked && e->num_decode == B) {
+    // nothing but one-token sequences: the decode step proper (captured CUDA graph, fused peer all-reduce)
+    rc = nvc_runner_decode(e->runner, e->ids.data(), e->positions.data(), e->slot_mapping.data(),
+                           e->block_tables.data(), e->max_blocks, e->context_lens.data(), B, e->out_tokens.data());
   } else if (e->chunked) {
     rc = nvc_runner_step_mixed(e->runner, e->ids.data(), e->positions.data(), e->cu_seqlens.data(), e->slot_mapping.data(),
                                e->block_tables.data(), e->max_blocks, e->context_lens.data(), e->num_decode, B,

@@ -88,6 +88,40 @@ def _free_port():
     return p
 
 
+def _rank_main_chunked(rank, world, port, q):
+    """Chunked prefill under TP: the scheduler is replicated, so every rank must build
+    the same mixed batches (ids / positions / cu_seqlens / slots / block tables / emit mask) with
+    requests arriving while others are mid-prompt."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, ROOT)
+    import zlib
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    eng = importlib.import_module("nano-vllm-candle_b200.engine")
+    cfg = eng.SchedulerConfig(6, 40, 0, 20, 16, enable_prefix_caching=True, enable_chunked_prefill=True)
+    e = eng.LLMEngine(eng.Scheduler(cfg), eng.DummyModelRunner())
+    rng = np.random.default_rng(11)
+    base = rng.integers(1, 500, size=50).tolist()
+    pending = [base[:int(rng.integers(20, 50))] + rng.integers(1, 500, size=int(rng.integers(1, 70))).tolist() for _ in range(12)]
+    digest, step = [], 0
+    while pending or not e.is_finished():
+        if pending and step % 3 == 0:
+            e.add_request(pending.pop(0), eng.SamplingParams(1.0, 21, True))
+        step += 1
+        if e.is_finished():
+            continue
+        si = e.schedule()
+        digest.append(zlib.crc32(bytes([si.is_prefill, si.num_decode_seqs]) + si.ids.tobytes() + si.positions.tobytes() +
+                                 si.cu_seqlens.tobytes() + si.slot_mapping.tobytes() + si.block_tables.tobytes() +
+                                 si.context_lens.tobytes() + si.emit.tobytes()))
+        e.post_process(np.asarray([si.ids[c - 1] + 1 for c in si.cu_seqlens[1:]], np.int32))
+    t = torch.tensor(digest, dtype=torch.int64)
+    out = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(out, t)
+    q.put((rank, all(torch.equal(o, t) for o in out), len(digest)))
+    dist.destroy_process_group()
+
+
 def _rank_main(rank, world, port, q):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
     sys.path.insert(0, ROOT)
@@ -113,12 +147,13 @@ def _rank_main(rank, world, port, q):
     dist.destroy_process_group()
 
 
-def test_replicated_scheduler_world_size_2_gloo():
+@pytest.mark.parametrize("main", ["reference", "chunked"])
+def test_replicated_scheduler_world_size_2_gloo(main):
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    ps = [ctx.Process(target=_rank_main, args=(r, 2, port, q)) for r in range(2)]
+    ps = [ctx.Process(target=_rank_main if main == "reference" else _rank_main_chunked, args=(r, 2, port, q)) for r in range(2)]
     for p in ps:
         p.start()
     res = [q.get(timeout=120) for _ in ps]

@@ -26,6 +26,8 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--model", default="qwen3-tiny")
     ap.add_argument("--max-tokens", type=int, default=24)
+    ap.add_argument("--chunked", type=int, default=0, metavar="BUDGET",
+                    help="chunked prefill with this token budget (mixed steps; all-reduce through NCCL)")
     ap.add_argument("--out", default=None)
     a = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
@@ -43,9 +45,22 @@ def main():
     runner = eng.Qwen3ModelRunner.from_weights(ctx, cfg, w.items(), num_kvcache_blocks=64, kvcache_block_size=bs,
                                                max_num_seqs=8, max_num_batched_tokens=2048, max_model_len=64 * bs // 8)
     prompts = [synth.make_prompts(1, n, cfg.vocab_size, 300 + n)[0] for n in (9, 40, 33, 17)]
-    e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(8, 2048, cfg.eos_token_id, 64, bs)), runner)
+    sc = eng.SchedulerConfig(8, a.chunked or 2048, cfg.eos_token_id, 64, bs, enable_chunked_prefill=a.chunked > 0)
+    e = eng.LLMEngine(eng.Scheduler(sc), runner)
     t0 = time.perf_counter()
-    outs = [o.token_ids for o in e.generate(prompts, eng.SamplingParams(1.0, a.max_tokens, True))]
+    mixed = 0
+    if a.chunked:           # step by step to count the mixed steps (decode tokens next to prompt chunks)
+        for i, p in enumerate(prompts):
+            e.add_request(p, eng.SamplingParams(1.0, a.max_tokens, True))
+            if i == 1:      # two sequences are already decoding when the others arrive
+                for _ in range(3):
+                    e.step()
+        while not e.is_finished():
+            s = e.step()
+            mixed += int(0 < s.num_decode_seqs < s.num_query_tokens)
+        outs = [e.output_of(i)[0] for i in range(len(prompts))]
+    else:
+        outs = [o.token_ids for o in e.generate(prompts, eng.SamplingParams(1.0, a.max_tokens, True))]
     dt = time.perf_counter() - t0
     # all ranks must agree token for token (replicated scheduler + identical argmax merge)
     mine = torch.tensor(outs, dtype=torch.int64, device="cuda")
@@ -53,6 +68,9 @@ def main():
     dist.all_gather(gathered, mine)
     same = all(torch.equal(g, mine) for g in gathered)
     result = {"model": a.model, "tp": world, "ranks_agree": bool(same), "seconds": dt}
+    if a.chunked:
+        result.update(chunked_budget=a.chunked, mixed_steps=mixed)
+        same = same and mixed > 0
     ok = same
     if rank == 0:
         from oracle import qwen3_oracle as O

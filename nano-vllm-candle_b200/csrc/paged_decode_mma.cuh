@@ -63,7 +63,9 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
                         float* __restrict__ part_ml, int num_splits) {
   extern __shared__ __align__(128) uint8_t smem[];
   pdl_trigger();
-  pdl_wait();
+  // The dependency wait comes AFTER the first K / V tiles are in flight (see below): context_lens and
+  // block_tables are step inputs (copied before the step's first kernel), and the only cache rows a
+  // kernel of this step writes are the newest token's (position ctx_len - 1, K2 of this layer).
   const int chunks = (group_total + gchunk - 1) / gchunk;
   const int kvh = blockIdx.x / chunks;
   const int chunk = blockIdx.x - kvh * chunks;
@@ -79,21 +81,6 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
   const int t_begin = split * tiles_per_split;
   const int t_end = min(n_tiles, t_begin + tiles_per_split);
 
-  // ---- Q as A fragments: 8 k-steps of 16 dims; rows >= G are zero
-  uint32_t qa[8][4];
-  {
-    const nvc_bf16* qrow0 = q + (int64_t)b * ldq + (int64_t)(head0 + quad) * 128;
-    const nvc_bf16* qrow1 = qrow0 + 8 * 128;
-    const bool r0 = quad < G, r1 = quad + 8 < G;
-#pragma unroll
-    for (int ks = 0; ks < 8; ++ks) {
-      const int d = ks * 16 + 2 * tq;
-      qa[ks][0] = r0 ? __ldg(reinterpret_cast<const uint32_t*>(qrow0 + d)) : 0u;
-      qa[ks][1] = r1 ? __ldg(reinterpret_cast<const uint32_t*>(qrow1 + d)) : 0u;
-      qa[ks][2] = r0 ? __ldg(reinterpret_cast<const uint32_t*>(qrow0 + d + 8)) : 0u;
-      qa[ks][3] = r1 ? __ldg(reinterpret_cast<const uint32_t*>(qrow1 + d + 8)) : 0u;
-    }
-  }
   float o[16][4];
 #pragma unroll
   for (int i = 0; i < 16; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
@@ -128,8 +115,40 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
   };
   (void)row_stride;
 
-  issue(0);
-  issue(1);
+  // Tiles that cannot hold the newest token are immutable during this step: start them while the
+  // predecessor (q/k-norm + RoPE + KV store) is still running.  A warp's tiles ascend in position, so
+  // "tile i is safe" is monotone in i; an out-of-range tile is an empty group.
+  auto safe = [&](int i) {
+    const int tok0 = (t_begin + i) * kCtaTok + warp * kTileTok;
+    return i >= my_tiles || tok0 >= ctx_len || tok0 + kTileTok <= ctx_len - 1;
+  };
+  int pre = 0;
+  if (safe(0)) {
+    issue(0);
+    pre = 1;
+    if (safe(1)) {
+      issue(1);
+      pre = 2;
+    }
+  }
+  pdl_wait();
+  // ---- Q as A fragments: 8 k-steps of 16 dims; rows >= G are zero
+  uint32_t qa[8][4];
+  {
+    const nvc_bf16* qrow0 = q + (int64_t)b * ldq + (int64_t)(head0 + quad) * 128;
+    const nvc_bf16* qrow1 = qrow0 + 8 * 128;
+    const bool r0 = quad < G, r1 = quad + 8 < G;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      const int d = ks * 16 + 2 * tq;
+      qa[ks][0] = r0 ? __ldg(reinterpret_cast<const uint32_t*>(qrow0 + d)) : 0u;
+      qa[ks][1] = r1 ? __ldg(reinterpret_cast<const uint32_t*>(qrow1 + d)) : 0u;
+      qa[ks][2] = r0 ? __ldg(reinterpret_cast<const uint32_t*>(qrow0 + d + 8)) : 0u;
+      qa[ks][3] = r1 ? __ldg(reinterpret_cast<const uint32_t*>(qrow1 + d + 8)) : 0u;
+    }
+  }
+  if (pre < 1) issue(0);
+  if (pre < 2) issue(1);
   for (int i = 0; i < my_tiles; ++i) {
     issue(i + 2);
     cp_async_wait<2>();                               // tile i has landed (two younger groups may be in flight)

@@ -322,9 +322,19 @@ int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, 
   return NVC_OK;
 }
 
+#include "prefill_attn_v2.cuh"
+
+// NVC_PREFILL_V1=1 (or nvc_debug_set(3, 1)) selects the first-generation kernel (one CTA per SM, 128-token kv tiles)
+bool use_v1() {
+  static const bool env = getenv("NVC_PREFILL_V1") && atoi(getenv("NVC_PREFILL_V1")) != 0;
+  return env || g_nvc_debug[3] == 1;
+}
+
 }  // namespace
 
 extern "C" int nvc_prefill_attn_init(nvc_ctx* ctx) {
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
   NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   return NVC_OK;
@@ -345,12 +355,22 @@ extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq,
   NVC_REQUIRE(ctx, ctx->encode_tiled != nullptr, NVC_EDEVICE, "cuTensorMapEncodeTiled unavailable");
   if (B == 0 || total_tokens == 0 || max_seqlen == 0) return NVC_OK;
   CUtensorMap tq, tk, tv;
+  const bool v1 = use_v1();
   int rc = make_tma_heads(ctx, &tq, q, nh, total_tokens, ldq);
   if (rc) return rc;
-  rc = make_tma_heads(ctx, &tk, k, kv, total_tokens, ldk);
+  rc = make_tma_heads(ctx, &tk, k, kv, total_tokens, ldk, v1 ? 128 : v2::kKT);
   if (rc) return rc;
-  rc = make_tma_heads(ctx, &tv, v, kv, total_tokens, ldv);
+  rc = make_tma_heads(ctx, &tv, v, kv, total_tokens, ldv, v1 ? 128 : v2::kKT);
   if (rc) return rc;
+  if (!v1) {
+    dim3 grid2((max_seqlen + 127) / 128, nh, B);
+    NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<false>, grid2, dim3(v2::kThreads), v2::kSmemBytes,
+                                   nvc_stream(stream), tq, tk, tv, cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out,
+                                   PagedKV{}));
+    NVC_CUDA_CHECK(ctx, cudaGetLastError());
+    ctx->launches++;
+    return NVC_OK;
+  }
   // V (B operand, MN-major, 128B swizzle): LBO = stride between the two 64-wide head-dim
   // halves (16 KB), SBO = stride between groups of 8 token rows (1 KB).
   int v_lbo = 16384, v_sbo = 1024;
@@ -381,7 +401,9 @@ extern "C" int nvc_prefill_attn_paged(nvc_ctx* ctx, const nvc_bf16* q, int ldq, 
               NVC_EINVAL, "pointers must be 16-byte aligned");
   NVC_REQUIRE(ctx, ctx->encode_tiled != nullptr, NVC_EDEVICE, "cuTensorMapEncodeTiled unavailable");
   if (B == 0 || total_q_tokens == 0 || max_seqlen_q == 0) return NVC_OK;
-  const int box_rows = block_size < 128 ? block_size : 128;
+  const bool v1 = use_v1();
+  const int tile = v1 ? 128 : v2::kKT;
+  const int box_rows = block_size < tile ? block_size : tile;
   CUtensorMap tq, tk, tv;
   int rc = make_tma_heads(ctx, &tq, q, nh, total_q_tokens, ldq);
   if (rc) return rc;
@@ -391,6 +413,13 @@ extern "C" int nvc_prefill_attn_paged(nvc_ctx* ctx, const nvc_bf16* q, int ldq, 
   if (rc) return rc;
   PagedKV pk{block_tables, context_lens, bt_stride, block_size, box_rows};
   dim3 grid((max_seqlen_q + 127) / 128, nh, B);
+  if (!v1) {
+    NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<true>, grid, dim3(v2::kThreads), v2::kSmemBytes,
+                                   nvc_stream(stream), tq, tk, tv, cu_seqlens_q, nh, nh / kv, scale * 1.4426950408889634f, out, pk));
+    NVC_CUDA_CHECK(ctx, cudaGetLastError());
+    ctx->launches++;
+    return NVC_OK;
+  }
   NVC_CUDA_CHECK(ctx, nvc_launch(ctx, prefill_attn_kernel<true>, grid, dim3(kThreads), kSmemBytes, nvc_stream(stream), tq, tk, tv,
                                  cu_seqlens_q, nh, nh / kv, scale * 1.4426950408889634f, out, 16384, 1024, pk));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());

@@ -279,6 +279,25 @@ def test_prefill_attn_paged(ctx, nh, kv, block_size, cases):
     _close(out, ref, 2e-2, 2 ** -6, f"paged prefill nh={nh} kv={kv} bs={block_size} cases={cases}")
 
 
+def test_prefill_attn_first_generation_kernel_still_matches(ctx, nvc):
+    """The 128-token-tile kernel (one CTA per SM) stays selectable (NVC_PREFILL_V1 / nvc_debug_set(3, 1))
+    and is held to the same reference as the default two-CTA-per-SM kernel."""
+    nvc.lib().nvc_debug_set(3, 1)
+    try:
+        test_prefill_attn_varlen(ctx, nvc, [17, 128, 129, 300, 1, 512], 4, 2)
+        test_prefill_attn_paged(ctx, 16, 8, 256, [(768, 256), (1000, 232), (256, 1), (257, 257), (640, 130)])
+        test_prefill_attn_paged(ctx, 4, 2, 16, [(48, 16), (33, 1), (200, 200), (131, 3), (16, 16)])
+    finally:
+        nvc.lib().nvc_debug_set(3, 0)
+
+
+@pytest.mark.parametrize("lens,nh,kv", [([2048, 1500], 8, 2), ([4096], 4, 1), ([64, 65, 63, 191, 192, 193], 2, 1)])
+def test_prefill_attn_long_sequences(ctx, nvc, lens, nh, kv):
+    """Many kv tiles per q tile: the tensor-memory output accumulator is rescaled across up to 64 tiles;
+    tile-boundary lengths around the 64-token kv tile."""
+    test_prefill_attn_varlen(ctx, nvc, lens, nh, kv)
+
+
 def test_prefill_attn_paged_equals_varlen_without_prefix(ctx):
     """With no cached prefix the paged kernel must reproduce the in-place varlen kernel bit for bit
     (same tiles, same order of operations)."""

@@ -12,6 +12,7 @@ for g in ${@:-decode e2e}; do
     e2e) t e2e 400 tests/test_e2e_gpu.py ;;
     layers) t layers 200 tests/test_layers_gpu.py ;;
     elementwise) t elementwise 240 tests/test_kernels_gpu.py ;;
+    pmicro) timeout 200 python tools/prefill_microbench.py gpurun_out/prefill_microbench.json > gpurun_out/prefill_microbench.log 2>&1; echo "pmicro exit $?"; tail -n 8 gpurun_out/prefill_microbench.log ;;
     micro) timeout 200 python tools/decode_microbench.py > gpurun_out/decode_microbench.log 2>&1; echo "micro exit $?"; tail -n 12 gpurun_out/decode_microbench.log ;;
     sweep8) timeout 300 python tools/sweep.py --model qwen3-8b --batches 1 64 256 --out gpurun_out/sweep_8b.json > gpurun_out/sweep_8b.log 2>&1; echo "sweep8 exit $?"; grep -o '"batch": [0-9]*\|"decode_tok_s": [0-9]*\|"paged_attn_frac": [0-9.]*' gpurun_out/sweep_8b.log | paste - - - ;;
   esac

@@ -26,11 +26,11 @@ constexpr int kOffQ = 0;
 constexpr int kOffKV = kQBytes;
 constexpr int kOffP = kOffKV + kStages * kStageBytes;
 constexpr int kOffBar = kOffP + kPBytes;       // 114688
-constexpr int kNumBars = 8;                    // q_full, kv_full[2], kv_empty[2], s_full, p_full, o_full
+constexpr int kNumBars = 9;                    // q_full, kv_full[2], kv_empty[2], s_full[2], p_full, o_full
 // two CTAs per SM: 2 x (request + 1 KB reserved) <= 228 KB; the alignment pad is <= 896 B for a 128-byte aligned base
 constexpr int kSmemBytes = 115712;
 static_assert(kOffBar + kNumBars * 8 + 16 + 896 <= kSmemBytes, "shared memory budget for two CTAs per SM");
-constexpr int kTmemCols = 256;                 // S: columns [0, 64); O: columns [128, 256)
+constexpr int kTmemCols = 256;                 // S (double-buffered): columns [0, 64) and [64, 128); O: columns [128, 256)
 
 template <bool kPaged>
 __global__ void __launch_bounds__(kThreads, 2)
@@ -56,7 +56,8 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
   const uint32_t q_full = bar0;
   auto kv_full = [&](int s) { return bar0 + 8u * (1 + s); };
   auto kv_empty = [&](int s) { return bar0 + 8u * (3 + s); };
-  const uint32_t s_full = bar0 + 8u * 5, p_full = bar0 + 8u * 6, o_full = bar0 + 8u * 7;
+  auto s_full = [&](int s) { return bar0 + 8u * (5 + s); };
+  const uint32_t p_full = bar0 + 8u * 7, o_full = bar0 + 8u * 8;
   const uint32_t tmem_slot = bar0 + 8u * kNumBars;
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen + kOffBar + kNumBars * 8);
 
@@ -70,7 +71,8 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     if (lane == 0) {
       ptx::mbar_init(q_full, 1);
       for (int s = 0; s < kStages; ++s) { ptx::mbar_init(kv_full(s), 1); ptx::mbar_init(kv_empty(s), 1); }
-      ptx::mbar_init(s_full, 1);
+      ptx::mbar_init(s_full(0), 1);
+      ptx::mbar_init(s_full(1), 1);
       ptx::mbar_init(p_full, 128);
       ptx::mbar_init(o_full, 1);
       ptx::fence_barrier_init();
@@ -143,19 +145,22 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
         for (int ks = 0; ks < 8; ++ks) {
           const uint32_t qoff = ((ks >> 2) * 16384 + (ks & 3) * 32) >> 4;
           const uint32_t koff = ((ks >> 2) * kHalfKV + (ks & 3) * 32) >> 4;
-          ptx::umma_bf16_ss(tmem_s, ptx::umma_desc(q_lo + qoff, hi_k), ptx::umma_desc(k_lo + koff, hi_k), idesc_qk, ks != 0);
+          ptx::umma_bf16_ss(tmem_s + s * kKT, ptx::umma_desc(q_lo + qoff, hi_k), ptx::umma_desc(k_lo + koff, hi_k), idesc_qk,
+                            ks != 0);
         }
-        ptx::umma_commit(s_full);
+        ptx::umma_commit(s_full(s));
       }
       __syncwarp();
     };
     ptx::mbar_wait(q_full, 0);
     issue_s(0);
     for (int j = 0; j < n_tiles; ++j) {
+      // S is double-buffered: S(j+1) goes into the buffer S(j-1) was read from (p_full(j-1) was awaited in the
+      // previous iteration), so the tensor pipe computes it while the softmax threads work on S(j)
+      if (j + 1 < n_tiles) issue_s(j + 1);
       // P(j) is in shared memory, S(j) has been read, O has been rescaled for tile j (all by the softmax threads)
       ptx::mbar_wait(p_full, j & 1);
       ptx::tcgen05_fence_after();
-      if (j + 1 < n_tiles) issue_s(j + 1);
       if (ptx::elect_one()) {
         // O += P V_j: A = P (K-major, 16 kv tokens per step); B = V (MN-major: LBO = 8 KB between the two
         // 64-wide head-dim halves, SBO = 1 KB between groups of 8 token rows, 16 token rows = 2048 bytes per step)
@@ -177,27 +182,31 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     float m = -INFINITY, l = 0.f;
     uint8_t* p_row = gen + kOffP + r * 128;
     for (int j = 0; j < n_tiles; ++j) {
-      ptx::mbar_wait(s_full, j & 1);
+      ptx::mbar_wait(s_full(j & 1), (j >> 1) & 1);
       ptx::tcgen05_fence_after();
-      // diag: the tile holds keys past some row's position; lim = last visible column of this row
-      const bool diag = j * kKT + kKT - 1 > q0;
-      const int lim = q0 + r - j * kKT;
       uint32_t sv[kKT];
-      ptx::tmem_ld_32x32b_x32(tmem_s + lane_addr, sv);
-      ptx::tmem_ld_32x32b_x32(tmem_s + lane_addr + 32, sv + 32);
+      ptx::tmem_ld_32x32b_x32(tmem_s + (j & 1) * kKT + lane_addr, sv);
+      ptx::tmem_ld_32x32b_x32(tmem_s + (j & 1) * kKT + lane_addr + 32, sv + 32);
       ptx::tmem_ld_wait();
+      // diagonal tiles only (the tile holds keys past some row's position): columns past this row's position
+      // become -inf, i.e. p = exp2(-inf) = 0; every other tile takes the mask-free path below
+      if (j * kKT + kKT - 1 > q0) {
+        const int lim = q0 + r - j * kKT;               // last visible column of this row
+#pragma unroll
+        for (int i = 0; i < kKT; ++i)
+          if (i > lim) sv[i] = 0xff800000u;
+      }
       float mx = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < kKT; ++i)
-        if (!diag || i <= lim) mx = fmaxf(mx, __uint_as_float(sv[i]));
+      for (int i = 0; i < kKT; ++i) mx = fmaxf(mx, __uint_as_float(sv[i]));
       const float m_new = fmaxf(m, mx * scale_log2e);     // finite from tile 0 on: key 0 is visible to every row
       const float alpha = fast_exp2(m - m_new);
       float psum = 0.f;
       uint32_t pk2[kKT / 2];
 #pragma unroll
       for (int i = 0; i < kKT; i += 2) {
-        const float p0 = (!diag || i <= lim) ? fast_exp2(__uint_as_float(sv[i]) * scale_log2e - m_new) : 0.f;
-        const float p1 = (!diag || i + 1 <= lim) ? fast_exp2(__uint_as_float(sv[i + 1]) * scale_log2e - m_new) : 0.f;
+        const float p0 = fast_exp2(__uint_as_float(sv[i]) * scale_log2e - m_new);
+        const float p1 = fast_exp2(__uint_as_float(sv[i + 1]) * scale_log2e - m_new);
         psum += p0 + p1;
         pk2[i >> 1] = pack_bf16(p0, p1);
       }

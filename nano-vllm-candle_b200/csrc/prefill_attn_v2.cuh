@@ -26,7 +26,7 @@ constexpr int kOffQ = 0;
 constexpr int kOffKV = kQBytes;
 constexpr int kOffP = kOffKV + kStages * kStageBytes;
 constexpr int kOffBar = kOffP + kPBytes;       // 114688
-constexpr int kNumBars = 9;                    // q_full, kv_full[2], kv_empty[2], s_full[2], p_full, o_full
+constexpr int kNumBars = 13;                   // q_full, k_full[2], k_empty[2], v_full[2], v_empty[2], s_full[2], p_full, o_full
 // two CTAs per SM: 2 x (request + 1 KB reserved) <= 228 KB; the alignment pad is <= 896 B for a 128-byte aligned base
 constexpr int kSmemBytes = 115712;
 static_assert(kOffBar + kNumBars * 8 + 16 + 896 <= kSmemBytes, "shared memory budget for two CTAs per SM");
@@ -54,10 +54,14 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
   uint8_t* gen = smem_v2 + (base - smem_u32(smem_v2));
   const uint32_t bar0 = base + kOffBar;
   const uint32_t q_full = bar0;
-  auto kv_full = [&](int s) { return bar0 + 8u * (1 + s); };
-  auto kv_empty = [&](int s) { return bar0 + 8u * (3 + s); };
-  auto s_full = [&](int s) { return bar0 + 8u * (5 + s); };
-  const uint32_t p_full = bar0 + 8u * 7, o_full = bar0 + 8u * 8;
+  // K and V have their own rings: a K slot is free as soon as S = Q K^T has read it (one tile ahead of the
+  // softmax), a V slot only after P V - so K(j+1) is requested a whole tile earlier than with (K, V) stages
+  auto k_full = [&](int s) { return bar0 + 8u * (1 + s); };
+  auto k_empty = [&](int s) { return bar0 + 8u * (3 + s); };
+  auto v_full = [&](int s) { return bar0 + 8u * (5 + s); };
+  auto v_empty = [&](int s) { return bar0 + 8u * (7 + s); };
+  auto s_full = [&](int s) { return bar0 + 8u * (9 + s); };
+  const uint32_t p_full = bar0 + 8u * 11, o_full = bar0 + 8u * 12;
   const uint32_t tmem_slot = bar0 + 8u * kNumBars;
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen + kOffBar + kNumBars * 8);
 
@@ -70,7 +74,10 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
   if (warp == 1) {
     if (lane == 0) {
       ptx::mbar_init(q_full, 1);
-      for (int s = 0; s < kStages; ++s) { ptx::mbar_init(kv_full(s), 1); ptx::mbar_init(kv_empty(s), 1); }
+      for (int s = 0; s < kStages; ++s) {
+        ptx::mbar_init(k_full(s), 1); ptx::mbar_init(k_empty(s), 1);
+        ptx::mbar_init(v_full(s), 1); ptx::mbar_init(v_empty(s), 1);
+      }
       ptx::mbar_init(s_full(0), 1);
       ptx::mbar_init(s_full(1), 1);
       ptx::mbar_init(p_full, 128);
@@ -96,37 +103,41 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       ptx::tma_load_3d(base + kOffQ + 16384, &tma_q, q_full, 64, h, seq_start + qt * 128);
     }
     __syncwarp();
-    for (int j = 0; j < n_tiles; ++j) {
+    // one K or V tile (is_v) of kv tile j into its ring slot
+    auto load_tile = [&](int j, bool is_v) {
       const int s = j & 1;
-      ptx::mbar_wait(kv_empty(s), ((j >> 1) & 1) ^ 1u);
+      ptx::mbar_wait(is_v ? v_empty(s) : k_empty(s), ((j >> 1) & 1) ^ 1u);
       if (ptx::elect_one()) {
-        const uint32_t kdst = base + kOffKV + s * kStageBytes, vdst = kdst + kKBytes;
+        const uint32_t dst = base + kOffKV + s * kStageBytes + (is_v ? kKBytes : 0);
+        const uint32_t bar = is_v ? v_full(s) : k_full(s);
+        const CUtensorMap* map = is_v ? &tma_v : &tma_k;
         if constexpr (kPaged) {
           // boxes of box_rows tokens; only those that start inside the context are loaded (the rest of
-          // the stage keeps stale bytes: masked in S, zeroed in V by the softmax warps)
+          // the slot keeps stale bytes: masked in S, zeroed in V by the softmax warps)
           const int rows = pk.box_rows, tok0 = j * kKT;
           const int nbox = min(kKT / rows, (kv_len - tok0 + rows - 1) / rows);
-          ptx::mbar_arrive_expect_tx(kv_full(s), (uint32_t)(nbox * rows * 512));   // K + V, two 64-wide halves each
+          ptx::mbar_arrive_expect_tx(bar, (uint32_t)(nbox * rows * 256));   // two 64-wide halves
           const int32_t* bt = pk.block_tables + (int64_t)b * pk.bt_stride;
           for (int i = 0; i < nbox; ++i) {
             const int tok = tok0 + i * rows;
             const int slot = __ldg(bt + tok / pk.block_size) * pk.block_size + tok % pk.block_size;
             const uint32_t o = (uint32_t)(i * rows * 128);
-            ptx::tma_load_3d(kdst + o, &tma_k, kv_full(s), 0, kvh, slot);
-            ptx::tma_load_3d(kdst + kHalfKV + o, &tma_k, kv_full(s), 64, kvh, slot);
-            ptx::tma_load_3d(vdst + o, &tma_v, kv_full(s), 0, kvh, slot);
-            ptx::tma_load_3d(vdst + kHalfKV + o, &tma_v, kv_full(s), 64, kvh, slot);
+            ptx::tma_load_3d(dst + o, map, bar, 0, kvh, slot);
+            ptx::tma_load_3d(dst + kHalfKV + o, map, bar, 64, kvh, slot);
           }
         } else {
-          ptx::mbar_arrive_expect_tx(kv_full(s), kStageBytes);
+          ptx::mbar_arrive_expect_tx(bar, kKBytes);
           const int row = seq_start + j * kKT;
-          ptx::tma_load_3d(kdst, &tma_k, kv_full(s), 0, kvh, row);
-          ptx::tma_load_3d(kdst + kHalfKV, &tma_k, kv_full(s), 64, kvh, row);
-          ptx::tma_load_3d(vdst, &tma_v, kv_full(s), 0, kvh, row);
-          ptx::tma_load_3d(vdst + kHalfKV, &tma_v, kv_full(s), 64, kvh, row);
+          ptx::tma_load_3d(dst, map, bar, 0, kvh, row);
+          ptx::tma_load_3d(dst + kHalfKV, map, bar, 64, kvh, row);
         }
       }
       __syncwarp();
+    };
+    load_tile(0, false);
+    for (int j = 0; j < n_tiles; ++j) {
+      if (j + 1 < n_tiles) load_tile(j + 1, false);   // K runs one tile ahead of V, as S = Q K^T runs ahead of P V
+      load_tile(j, true);
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer (whole warp loops, one lane issues)
@@ -137,7 +148,7 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     const uint32_t p_lo = ptx::umma_desc_lo(base + kOffP, 16);
     auto issue_s = [&](int j) {   // S = Q K_j^T : 8 k-steps of 16 over head_dim (two 64-wide swizzled halves)
       const int s = j & 1;
-      ptx::mbar_wait(kv_full(s), (j >> 1) & 1);
+      ptx::mbar_wait(k_full(s), (j >> 1) & 1);
       ptx::tcgen05_fence_after();
       if (ptx::elect_one()) {
         const uint32_t k_lo = ptx::umma_desc_lo(base + kOffKV + s * kStageBytes, 16);
@@ -149,6 +160,7 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
                             ks != 0);
         }
         ptx::umma_commit(s_full(s));
+        ptx::umma_commit(k_empty(s));          // the K slot is free as soon as these MMAs have read it
       }
       __syncwarp();
     };
@@ -160,6 +172,7 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       if (j + 1 < n_tiles) issue_s(j + 1);
       // P(j) is in shared memory, S(j) has been read, O has been rescaled for tile j (all by the softmax threads)
       ptx::mbar_wait(p_full, j & 1);
+      ptx::mbar_wait(v_full(j & 1), (j >> 1) & 1);
       ptx::tcgen05_fence_after();
       if (ptx::elect_one()) {
         // O += P V_j: A = P (K-major, 16 kv tokens per step); B = V (MN-major: LBO = 8 KB between the two
@@ -170,7 +183,7 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
           ptx::umma_bf16_ss(tmem_o, ptx::umma_desc(p_lo + ((ks * 32) >> 4), hi_k), ptx::umma_desc(v_lo + ks * (2048 >> 4), hi_k),
                             idesc_pv, (j | ks) != 0);
         ptx::umma_commit(o_full);
-        ptx::umma_commit(kv_empty(j & 1));
+        ptx::umma_commit(v_empty(j & 1));
       }
       __syncwarp();
     }
@@ -235,9 +248,10 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
         *reinterpret_cast<uint4*>(p_row + ((k8 ^ (r & 7)) << 4)) =
             make_uint4(pk2[4 * k8], pk2[4 * k8 + 1], pk2[4 * k8 + 2], pk2[4 * k8 + 3]);
       if constexpr (kPaged) {
-        // V rows at / past the end of the context: zero them (every P column there is 0, but the cache
-        // bytes may be NaN).  s_full(j) implies the stage's TMA has landed; the proxy fence below orders
-        // these generic stores before the P V MMA.
+        // V rows at / past the end of the context (last tile only): zero them (every P column there is 0,
+        // but the cache bytes may be NaN) once the slot's TMA has landed; the proxy fence below orders these
+        // generic stores before the P V MMA.
+        if (j * kKT + kKT > kv_len) ptx::mbar_wait(v_full(j & 1), (j >> 1) & 1);
         if (r < kKT && j * kKT + r >= kv_len) {
           uint8_t* v_row = gen + kOffKV + (j & 1) * kStageBytes + kKBytes + r * 128;
 #pragma unroll

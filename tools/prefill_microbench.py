@@ -50,13 +50,16 @@ def bench(name, B, T, nh, kv, iters=10, bufs=4):
     return row
 
 
-rows = [
-    bench("0.6B cfg2: 64 x 512", 64, 512, 16, 8),
-    bench("8B: 32 x 512", 32, 512, 32, 8),
-    bench("8B: 16 x 1024", 16, 1024, 32, 8),
-    bench("14B/TP2 cfg4: 8 x 2048", 8, 2048, 20, 4),
-    bench("32B/TP8 cfg5: 8 x 4096", 8, 4096, 8, 1),
-    bench("8B: 4 x 8192", 4, 8192, 32, 8, iters=4),
+SHAPES = [
+    ("0.6B cfg2: 64 x 512", 64, 512, 16, 8, 10),
+    ("8B: 32 x 512", 32, 512, 32, 8, 10),
+    ("8B: 16 x 1024", 16, 1024, 32, 8, 10),
+    ("14B/TP2 cfg4: 8 x 2048", 8, 2048, 20, 4, 10),
+    ("32B/TP8 cfg5: 8 x 4096", 8, 4096, 8, 1, 10),
+    ("8B: 4 x 8192", 4, 8192, 32, 8, 4),
 ]
+only = os.environ.get("PREFILL_SHAPE")          # index into SHAPES (used for the ncu capture of one shape)
+todo = [SHAPES[int(only)]] if only is not None else SHAPES
+rows = [bench(n, B, T, nh, kv, iters=it) for n, B, T, nh, kv, it in todo]
 if len(sys.argv) > 1:
     json.dump(rows, open(sys.argv[1], "w"), indent=1)

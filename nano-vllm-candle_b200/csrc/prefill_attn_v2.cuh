@@ -66,13 +66,44 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
   volatile uint32_t* tmem_slot_gen = reinterpret_cast<volatile uint32_t*>(gen + kOffBar + kNumBars * 8);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (warp == 0 && lane == 0) {
-    ptx::tma_prefetch_desc(&tma_q);
-    ptx::tma_prefetch_desc(&tma_k);
-    ptx::tma_prefetch_desc(&tma_v);
-  }
-  if (warp == 1) {
+  // one K or V tile (is_v) of kv tile j into its ring slot
+  auto load_tile = [&](int j, bool is_v) {
+    const int s = j & 1;
+    ptx::mbar_wait(is_v ? v_empty(s) : k_empty(s), ((j >> 1) & 1) ^ 1u);
+    if (ptx::elect_one()) {
+      const uint32_t dst = base + kOffKV + s * kStageBytes + (is_v ? kKBytes : 0);
+      const uint32_t bar = is_v ? v_full(s) : k_full(s);
+      const CUtensorMap* map = is_v ? &tma_v : &tma_k;
+      if constexpr (kPaged) {
+        // boxes of box_rows tokens; only those that start inside the context are loaded (the rest of
+        // the slot keeps stale bytes: masked in S, zeroed in V by the softmax warps)
+        const int rows = pk.box_rows, tok0 = j * kKT;
+        const int nbox = min(kKT / rows, (kv_len - tok0 + rows - 1) / rows);
+        ptx::mbar_arrive_expect_tx(bar, (uint32_t)(nbox * rows * 256));   // two 64-wide halves
+        const int32_t* bt = pk.block_tables + (int64_t)b * pk.bt_stride;
+        for (int i = 0; i < nbox; ++i) {
+          const int tok = tok0 + i * rows;
+          const int slot = __ldg(bt + tok / pk.block_size) * pk.block_size + tok % pk.block_size;
+          const uint32_t o = (uint32_t)(i * rows * 128);
+          ptx::tma_load_3d(dst + o, map, bar, 0, kvh, slot);
+          ptx::tma_load_3d(dst + kHalfKV + o, map, bar, 64, kvh, slot);
+        }
+      } else {
+        ptx::mbar_arrive_expect_tx(bar, kKBytes);
+        const int row = seq_start + j * kKT;
+        ptx::tma_load_3d(dst, map, bar, 0, kvh, row);
+        ptx::tma_load_3d(dst + kHalfKV, map, bar, 64, kvh, row);
+      }
+    }
+    __syncwarp();
+  };
+  if (warp == 0) {
+    // The producer warp initialises the barriers itself and requests Q and K(0) right away, while warp 1
+    // allocates tensor memory: the first loads do not wait for the CTA-wide sync.
     if (lane == 0) {
+      ptx::tma_prefetch_desc(&tma_q);
+      ptx::tma_prefetch_desc(&tma_k);
+      ptx::tma_prefetch_desc(&tma_v);
       ptx::mbar_init(q_full, 1);
       for (int s = 0; s < kStages; ++s) {
         ptx::mbar_init(k_full(s), 1); ptx::mbar_init(k_empty(s), 1);
@@ -85,6 +116,15 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       ptx::fence_barrier_init();
     }
     __syncwarp();
+    pdl_wait();    // q / k / v (or the cache rows of this step) are written by the predecessor
+    if (ptx::elect_one()) {
+      ptx::mbar_arrive_expect_tx(q_full, kQBytes);
+      ptx::tma_load_3d(base + kOffQ, &tma_q, q_full, 0, h, seq_start + qt * 128);
+      ptx::tma_load_3d(base + kOffQ + 16384, &tma_q, q_full, 64, h, seq_start + qt * 128);
+    }
+    __syncwarp();
+    load_tile(0, false);
+  } else if (warp == 1) {
     ptx::tmem_alloc(tmem_slot, kTmemCols);
     ptx::tmem_relinquish();
   }
@@ -93,48 +133,10 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
   ptx::tcgen05_fence_after();
   const uint32_t tmem = *tmem_slot_gen;
   const uint32_t tmem_s = tmem, tmem_o = tmem + 128;
-  pdl_wait();      // q / k / v (or the cache rows of this step) are written by the predecessor
+  pdl_wait();
 
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer (whole warp loops, one lane issues)
-    if (ptx::elect_one()) {
-      ptx::mbar_arrive_expect_tx(q_full, kQBytes);
-      ptx::tma_load_3d(base + kOffQ, &tma_q, q_full, 0, h, seq_start + qt * 128);
-      ptx::tma_load_3d(base + kOffQ + 16384, &tma_q, q_full, 64, h, seq_start + qt * 128);
-    }
-    __syncwarp();
-    // one K or V tile (is_v) of kv tile j into its ring slot
-    auto load_tile = [&](int j, bool is_v) {
-      const int s = j & 1;
-      ptx::mbar_wait(is_v ? v_empty(s) : k_empty(s), ((j >> 1) & 1) ^ 1u);
-      if (ptx::elect_one()) {
-        const uint32_t dst = base + kOffKV + s * kStageBytes + (is_v ? kKBytes : 0);
-        const uint32_t bar = is_v ? v_full(s) : k_full(s);
-        const CUtensorMap* map = is_v ? &tma_v : &tma_k;
-        if constexpr (kPaged) {
-          // boxes of box_rows tokens; only those that start inside the context are loaded (the rest of
-          // the slot keeps stale bytes: masked in S, zeroed in V by the softmax warps)
-          const int rows = pk.box_rows, tok0 = j * kKT;
-          const int nbox = min(kKT / rows, (kv_len - tok0 + rows - 1) / rows);
-          ptx::mbar_arrive_expect_tx(bar, (uint32_t)(nbox * rows * 256));   // two 64-wide halves
-          const int32_t* bt = pk.block_tables + (int64_t)b * pk.bt_stride;
-          for (int i = 0; i < nbox; ++i) {
-            const int tok = tok0 + i * rows;
-            const int slot = __ldg(bt + tok / pk.block_size) * pk.block_size + tok % pk.block_size;
-            const uint32_t o = (uint32_t)(i * rows * 128);
-            ptx::tma_load_3d(dst + o, map, bar, 0, kvh, slot);
-            ptx::tma_load_3d(dst + kHalfKV + o, map, bar, 64, kvh, slot);
-          }
-        } else {
-          ptx::mbar_arrive_expect_tx(bar, kKBytes);
-          const int row = seq_start + j * kKT;
-          ptx::tma_load_3d(dst, map, bar, 0, kvh, row);
-          ptx::tma_load_3d(dst + kHalfKV, map, bar, 64, kvh, row);
-        }
-      }
-      __syncwarp();
-    };
-    load_tile(0, false);
     for (int j = 0; j < n_tiles; ++j) {
       if (j + 1 < n_tiles) load_tile(j + 1, false);   // K runs one tile ahead of V, as S = Q K^T runs ahead of P V
       load_tile(j, true);

@@ -264,6 +264,26 @@ def test_mixed_step_logits_match_whole_prompt_prefill(tiny):
     assert err <= 2e-2 and d <= 2e-2
 
 
+def test_mixed_step_rejects_inconsistent_inputs(tiny):
+    """nvc_runner_step_mixed reports bad arguments as status codes (never aborts, never guesses)."""
+    cfg, runner, _, _ = tiny
+    bs = 16
+    e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 64, cfg.eos_token_id, 64, bs, enable_chunked_prefill=True)), runner)
+    e.add_request(synth.make_prompts(1, 20, cfg.vocab_size, 5)[0], eng.SamplingParams(1.0, 2, True))
+    si = e.schedule()
+    args = (si.ids, si.positions, si.cu_seqlens, si.slot_mapping, si.block_tables, si.context_lens)
+    with pytest.raises(eng.NvcError):        # the first "decode" sequence has 20 query tokens
+        runner.step_mixed(*args, 1)
+    with pytest.raises(eng.NvcError):        # more decode sequences than sequences
+        runner.step_mixed(*args, 2)
+    bad_ctx = si.context_lens.copy(); bad_ctx[0] = 5          # context shorter than the query
+    with pytest.raises(eng.NvcError):
+        runner.step_mixed(si.ids, si.positions, si.cu_seqlens, si.slot_mapping, si.block_tables, bad_ctx, 0)
+    toks = runner.step_mixed(*args, 0)        # the well-formed step still runs afterwards
+    assert len(toks) == 1
+    e.post_process(toks)
+
+
 def test_on_device_sampling_is_reproducible_and_follows_the_oracle(tiny):
     """SURVEY 8f.3: temperature sampling on device (seeded Gumbel-max).  Same seed -> same tokens;
     every sampled token, teacher-forced through the fp32 oracle with the same Philox stream

@@ -149,7 +149,7 @@ def run_reference(args):
         "e2e": {"value": toks, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference crate (Rust + candle 0.9.1) cannot be built on this image; timed: oracle/ restatement",
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def _config(n_gpus: int) -> dict:
@@ -292,16 +292,29 @@ def run_ours(args):
             "sample": f"2 decode steps (after 1 warm-up) of {CPU_SAMPLE_SEQS} of the {BATCH} sequences at context "
                       f"{PROMPT_LEN + 1}+, reference algorithm (full recompute per step), fp32, {sec:.1f} s/step"}
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_OUT = None
+
+
+def _emit(line) -> None:
+    """The one JSON line, on the process's ORIGINAL stdout."""
+    out = _OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
-    # stdout carries exactly one JSON line: keep NCCL's "NCCL version ..." banner (NCCL_DEBUG=VERSION) off it
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"
+    # stdout carries exactly one JSON line: everything else written to file descriptor 1 by libraries (NCCL
+    # prints its "NCCL version ..." banner there at NCCL_DEBUG=VERSION and above, WARN included) goes to stderr
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=64)

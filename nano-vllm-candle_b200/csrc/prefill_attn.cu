@@ -324,7 +324,16 @@ int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, 
 
 #include "prefill_attn_v2.cuh"
 
+constexpr int kDefaultWG = 1;
+
 // NVC_PREFILL_V1=1 (or nvc_debug_set(3, 1)) selects the first-generation kernel (one CTA per SM, 128-token kv tiles)
+// softmax warp-groups of the second-generation kernel: NVC_PREFILL_WG=1|2 or nvc_debug_set(4, 1|2); 0 = default
+int v2_wg() {
+  static const int env = getenv("NVC_PREFILL_WG") ? atoi(getenv("NVC_PREFILL_WG")) : 0;
+  const int w = g_nvc_debug[4] ? g_nvc_debug[4] : env;
+  return w == 2 ? 2 : (w == 1 ? 1 : kDefaultWG);
+}
+
 bool use_v1() {
   static const bool env = getenv("NVC_PREFILL_V1") && atoi(getenv("NVC_PREFILL_V1")) != 0;
   return env || g_nvc_debug[3] == 1;
@@ -333,8 +342,10 @@ bool use_v1() {
 }  // namespace
 
 extern "C" int nvc_prefill_attn_init(nvc_ctx* ctx) {
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
   NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   return NVC_OK;
@@ -364,9 +375,14 @@ extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq,
   if (rc) return rc;
   if (!v1) {
     dim3 grid2((max_seqlen + 127) / 128, nh, B);
-    NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<false>, grid2, dim3(v2::kThreads), v2::kSmemBytes,
-                                   nvc_stream(stream), tq, tk, tv, cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out,
-                                   PagedKV{}));
+    if (v2_wg() == 2)
+      NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<false, 2>, grid2, dim3(v2::kThreads + 128), v2::kSmemBytes,
+                                     nvc_stream(stream), tq, tk, tv, cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out,
+                                     PagedKV{}));
+    else
+      NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<false, 1>, grid2, dim3(v2::kThreads), v2::kSmemBytes,
+                                     nvc_stream(stream), tq, tk, tv, cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out,
+                                     PagedKV{}));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
     ctx->launches++;
     return NVC_OK;
@@ -414,8 +430,12 @@ extern "C" int nvc_prefill_attn_paged(nvc_ctx* ctx, const nvc_bf16* q, int ldq, 
   PagedKV pk{block_tables, context_lens, bt_stride, block_size, box_rows};
   dim3 grid((max_seqlen_q + 127) / 128, nh, B);
   if (!v1) {
-    NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<true>, grid, dim3(v2::kThreads), v2::kSmemBytes,
-                                   nvc_stream(stream), tq, tk, tv, cu_seqlens_q, nh, nh / kv, scale * 1.4426950408889634f, out, pk));
+    if (v2_wg() == 2)
+      NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<true, 2>, grid, dim3(v2::kThreads + 128), v2::kSmemBytes,
+                                     nvc_stream(stream), tq, tk, tv, cu_seqlens_q, nh, nh / kv, scale * 1.4426950408889634f, out, pk));
+    else
+      NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<true, 1>, grid, dim3(v2::kThreads), v2::kSmemBytes,
+                                     nvc_stream(stream), tq, tk, tv, cu_seqlens_q, nh, nh / kv, scale * 1.4426950408889634f, out, pk));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
     ctx->launches++;
     return NVC_OK;

@@ -14,7 +14,7 @@
 
 namespace v2 {
 
-constexpr int kThreads = 192;
+constexpr int kThreads = 192;                  // kWG = 1: TMA warp + MMA warp + 4 softmax warps; kWG = 2: + 4 more softmax warps
 constexpr int kKT = 64;                        // kv tokens per tile
 constexpr int kQBytes = 128 * 128 * 2;         // 32 KB: two [128 rows][64 dims] swizzled halves
 constexpr int kHalfKV = kKT * 128;             // 8 KB: [64 tokens][64 dims]
@@ -30,10 +30,18 @@ constexpr int kNumBars = 13;                   // q_full, k_full[2], k_empty[2],
 // two CTAs per SM: 2 x (request + 1 KB reserved) <= 228 KB; the alignment pad is <= 896 B for a 128-byte aligned base
 constexpr int kSmemBytes = 115712;
 static_assert(kOffBar + kNumBars * 8 + 16 + 896 <= kSmemBytes, "shared memory budget for two CTAs per SM");
+constexpr int kOffXch = kOffBar + kNumBars * 8 + 16;   // kWG = 2: 128 floats, row maxima exchanged between the column halves
+static_assert(kOffXch + 512 <= kSmemBytes, "exchange buffer (needs the 1024-byte alignment of the dynamic shared memory)");
+
+__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
+__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 constexpr int kTmemCols = 256;                 // S (double-buffered): columns [0, 64) and [64, 128); O: columns [128, 256)
 
-template <bool kPaged>
-__global__ void __launch_bounds__(kThreads, 2)
+// kWG = 2: eight softmax warps; warps w and w + 4 share the tensor-memory lane quadrant (rows) and split the kv
+// columns of S (32 each), the columns of O for the rescale / output (64 each) and the P chunks; the row maximum
+// is combined through shared memory once per tile (two named barriers per warp pair), the row sum once at the end.
+template <bool kPaged, int kWG>
+__global__ void __launch_bounds__(64 + 128 * kWG, 2)
 prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
                        const __grid_constant__ CUtensorMap tma_v, const int32_t* __restrict__ cu_seqlens,
                        int nh, int group, float scale_log2e, nvc_bf16* __restrict__ out, const PagedKV pk) {
@@ -111,7 +119,7 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       }
       ptx::mbar_init(s_full(0), 1);
       ptx::mbar_init(s_full(1), 1);
-      ptx::mbar_init(p_full, 128);
+      ptx::mbar_init(p_full, 128 * kWG);
       ptx::mbar_init(o_full, 1);
       ptx::fence_barrier_init();
     }
@@ -189,7 +197,118 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       }
       __syncwarp();
     }
+  } else if constexpr (kWG == 2) {
+    // ------------------------------------------------------------ softmax warps, two per lane quadrant
+    const int quad = warp & 3;                      // tensor-memory lane quadrant = warp % 4
+    const int half = (warp - 2) >> 2;               // column half of this warp
+    const int r = quad * 32 + lane;                 // row in the q tile
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    float* xch = reinterpret_cast<float*>(gen + kOffXch);
+    if ((base - smem_u32(smem_v2)) + kOffXch + 512 > (uint32_t)kSmemBytes) __trap();   // alignment not honoured
+    const int bar_a = 1 + quad, bar_b = 5 + quad;   // named barriers of the warp pair (64 threads)
+    // row-wise exchange: the upper half publishes, the lower half combines and publishes the result
+    auto combine = [&](float x, bool is_max) {
+      if (half == 1) {
+        xch[r] = x;
+        bar_sync(bar_a, 64);
+        bar_sync(bar_b, 64);
+        return xch[r];
+      }
+      bar_sync(bar_a, 64);
+      const float y = is_max ? fmaxf(x, xch[r]) : x + xch[r];
+      xch[r] = y;
+      __threadfence_block();
+      bar_arrive(bar_b, 64);
+      return y;
+    };
+    constexpr int kC = kKT / 2;                     // S columns per thread
+    float m = -INFINITY, l = 0.f;
+    uint8_t* p_row = gen + kOffP + r * 128;
+    for (int j = 0; j < n_tiles; ++j) {
+      ptx::mbar_wait(s_full(j & 1), (j >> 1) & 1);
+      ptx::tcgen05_fence_after();
+      uint32_t sv[kC];
+      ptx::tmem_ld_32x32b_x32(tmem_s + (j & 1) * kKT + half * kC + lane_addr, sv);
+      ptx::tmem_ld_wait();
+      if (j * kKT + kKT - 1 > q0) {                   // diagonal tile: columns past this row's position -> -inf
+        const int lim = q0 + r - j * kKT - half * kC;
+#pragma unroll
+        for (int i = 0; i < kC; ++i)
+          if (i > lim) sv[i] = 0xff800000u;
+      }
+      float mx = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < kC; ++i) mx = fmaxf(mx, __uint_as_float(sv[i]));
+      mx = combine(mx, true);
+      const float m_new = fmaxf(m, mx * scale_log2e);
+      const float alpha = fast_exp2(m - m_new);
+      float psum = 0.f;
+      uint32_t pk2[kC / 2];
+#pragma unroll
+      for (int i = 0; i < kC; i += 2) {
+        const float p0 = fast_exp2(__uint_as_float(sv[i]) * scale_log2e - m_new);
+        const float p1 = fast_exp2(__uint_as_float(sv[i + 1]) * scale_log2e - m_new);
+        psum += p0 + p1;
+        pk2[i >> 1] = pack_bf16(p0, p1);
+      }
+      l = l * alpha + psum;                           // partial row sum of this column half
+      m = m_new;
+      if (j > 0) {
+        ptx::mbar_wait(o_full, (j - 1) & 1);
+        ptx::tcgen05_fence_after();
+        if (__any_sync(0xffffffffu, alpha != 1.0f)) {
+#pragma unroll 1
+          for (int c = 0; c < 2; ++c) {
+            uint32_t v[32];
+            ptx::tmem_ld_32x32b_x32(tmem_o + lane_addr + half * 64 + c * 32, v);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+            ptx::tmem_st_32x32b_x32(tmem_o + lane_addr + half * 64 + c * 32, v);
+          }
+          ptx::tmem_st_wait();
+        }
+      }
+#pragma unroll
+      for (int k8 = 0; k8 < kC / 8; ++k8)
+        *reinterpret_cast<uint4*>(p_row + (((half * (kC / 8) + k8) ^ (r & 7)) << 4)) =
+            make_uint4(pk2[4 * k8], pk2[4 * k8 + 1], pk2[4 * k8 + 2], pk2[4 * k8 + 3]);
+      if constexpr (kPaged) {
+        if (j * kKT + kKT > kv_len) ptx::mbar_wait(v_full(j & 1), (j >> 1) & 1);
+        if (r < kKT && j * kKT + r >= kv_len) {       // this warp's head-dim half of the V row
+          uint8_t* v_row = gen + kOffKV + (j & 1) * kStageBytes + kKBytes + half * kHalfKV + r * 128;
+#pragma unroll
+          for (int k16 = 0; k16 < 8; ++k16) *reinterpret_cast<uint4*>(v_row + (k16 << 4)) = make_uint4(0, 0, 0, 0);
+        }
+      }
+      ptx::fence_proxy_async_smem();
+      ptx::tcgen05_fence_before();
+      ptx::mbar_arrive(p_full);
+    }
+    l = combine(l, false);
+    ptx::mbar_wait(o_full, (n_tiles - 1) & 1);
+    ptx::tcgen05_fence_after();
+    const int row_in_seq = qt * 128 + r;
+    const float inv = 1.0f / l;
+    uint4* dst = reinterpret_cast<uint4*>(out + ((int64_t)(seq_start + row_in_seq) * nh + h) * 128 + half * 64);
+#pragma unroll 1
+    for (int c = 0; c < 2; ++c) {
+      uint32_t v[32];
+      ptx::tmem_ld_32x32b_x32(tmem_o + lane_addr + half * 64 + c * 32, v);
+      ptx::tmem_ld_wait();
+      if (row_in_seq < seq_len) {
+#pragma unroll
+        for (int k8 = 0; k8 < 4; ++k8) {
+          float o[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) o[i] = __uint_as_float(v[k8 * 8 + i]) * inv;
+          dst[c * 4 + k8] = pack8(o);
+        }
+      }
+    }
+    ptx::tcgen05_fence_before();
   } else {
+
     // ------------------------------------------------------------ softmax / correction / output warps
     const int quad = warp & 3;
     const int r = quad * 32 + lane;                 // row in the q tile

@@ -291,6 +291,20 @@ def test_prefill_attn_first_generation_kernel_still_matches(ctx, nvc):
         nvc.lib().nvc_debug_set(3, 0)
 
 
+def test_prefill_attn_two_softmax_warp_groups(ctx, nvc):
+    """The variant of the second-generation kernel with eight softmax warps (column halves per warp pair, row
+    maxima combined through shared memory) against the same references (NVC_PREFILL_WG=2 / nvc_debug_set(4, 2))."""
+    nvc.lib().nvc_debug_set(4, 2)
+    try:
+        test_prefill_attn_varlen(ctx, nvc, [17, 128, 129, 300, 1, 512], 4, 2)
+        test_prefill_attn_varlen(ctx, nvc, [2048, 1500], 8, 2)
+        test_prefill_attn_varlen(ctx, nvc, [64, 65, 63, 191, 192, 193], 2, 1)
+        test_prefill_attn_paged(ctx, 16, 8, 256, [(768, 256), (1000, 232), (256, 1), (257, 257), (640, 130)])
+        test_prefill_attn_paged(ctx, 4, 2, 16, [(48, 16), (33, 1), (200, 200), (131, 3), (16, 16)])
+    finally:
+        nvc.lib().nvc_debug_set(4, 0)
+
+
 @pytest.mark.parametrize("lens,nh,kv", [([2048, 1500], 8, 2), ([4096], 4, 1), ([64, 65, 63, 191, 192, 193], 2, 1)])
 def test_prefill_attn_long_sequences(ctx, nvc, lens, nh, kv):
     """Many kv tiles per q tile: the tensor-memory output accumulator is rescaled across up to 64 tiles;

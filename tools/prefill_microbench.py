@@ -27,8 +27,9 @@ def bench(name, B, T, nh, kv, iters=10, bufs=4):
     out = torch.empty(N, nh * hd, dtype=BF16, device="cuda")
     flops = 4.0 * nh * hd * B * T * T / 2
     row = {"shape": name, "B": B, "T": T, "nh": nh, "kv": kv}
-    for gen in (1, 2):
+    for gen in (1, 2, 3):                      # 1: first kernel; 2: v2 with one softmax warp-group; 3: v2 with two
         lib.lib().nvc_debug_set(3, 1 if gen == 1 else 0)
+        lib.lib().nvc_debug_set(4, 2 if gen == 3 else 1)
         def run(d):
             ctx.prefill_attn(d[:, :nh * hd], d[:, nh * hd:(nh + kv) * hd], d[:, (nh + kv) * hd:], cu, T, nh, kv, hd, hd ** -0.5, out=out)
         for d in qkvs:
@@ -45,6 +46,7 @@ def bench(name, B, T, nh, kv, iters=10, bufs=4):
         row[f"v{gen}_tflops"] = round(flops / us / 1e6, 1)
         row[f"v{gen}_frac_of_bf16_sustained"] = round(flops / us / 1e6 / PEAK, 3)
     lib.lib().nvc_debug_set(3, 0)
+    lib.lib().nvc_debug_set(4, 0)
     row["speedup"] = round(row["v1_us"] / row["v2_us"], 2)
     print(json.dumps(row), flush=True)
     return row

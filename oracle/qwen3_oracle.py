@@ -288,6 +288,66 @@ class Qwen3Oracle:
         return (hidden.reshape(b * t, h) @ self.lm_head).reshape(b, t, self.cfg.vocab_size)
 
 
+class Qwen3OracleKVCached:
+    """The SAME arithmetic as Qwen3Oracle (fp32 mode), evaluated incrementally: K / V of earlier
+    positions are kept per layer, a step computes only the new positions and logits only for the
+    last one.  Not the reference's algorithm (it recomputes everything each step,
+    src/engine/llm_engine.rs:146-189) - it exists so that bench.py can separate the ALGORITHMIC
+    speed-up (KV cache, last-token logits) from the hardware speed-up, and
+    tests/test_oracle_goldens.py checks it against the full-recompute oracle."""
+
+    def __init__(self, model: Qwen3Oracle, max_len: int):
+        assert model.mode == "fp32"
+        self.m = model
+        cfg = model.cfg
+        self.cos, self.sin = build_cos_sin(max_len, cfg.head_dim, float(np.float32(cfg.rope_theta)))
+        self.k = [None] * cfg.num_hidden_layers      # [kv, T, hd] per layer
+        self.v = [None] * cfg.num_hidden_layers
+        self.len = 0
+
+    def step(self, new_ids) -> torch.Tensor:
+        """Appends the tokens `new_ids` (positions len .. len + n) and returns the fp32 logits [V]
+        of the last one."""
+        M, cfg = self.m, self.m.cfg
+        nh, kv, hd, eps = cfg.num_attention_heads, cfg.num_key_value_heads, cfg.head_dim, cfg.rms_norm_eps
+        ids = torch.as_tensor(new_ids, dtype=torch.long)
+        n, p0 = len(ids), self.len
+        cos = self.cos[p0:p0 + n].reshape(1, n, hd // 2)
+        sin = self.sin[p0:p0 + n].reshape(1, n, hd // 2)
+        scale = float(np.float32(hd) ** np.float32(-0.5))
+        h = M.embed[ids]
+        residual = None
+        for li, L in enumerate(M.layers):
+            if residual is not None:
+                x, residual = rms_norm(h, L["ln1"], eps, residual)
+            else:
+                x, _ = rms_norm(h, L["ln1"], eps, None)
+                residual = h.clone()
+            qkv = linear(x, L["w_qkv"])
+            q = qkv[:, :nh * hd].reshape(n, nh, hd).transpose(0, 1)                 # [nh, n, hd]
+            k = qkv[:, nh * hd:(nh + kv) * hd].reshape(n, kv, hd).transpose(0, 1)
+            v = qkv[:, (nh + kv) * hd:].reshape(n, kv, hd).transpose(0, 1)
+            q = rms_norm(q.reshape(nh * n, hd), L["q_norm"], eps)[0].reshape(nh, n, hd)
+            k = rms_norm(k.reshape(kv * n, hd), L["k_norm"], eps)[0].reshape(kv, n, hd)
+            q, k = apply_rotary(q, cos, sin), apply_rotary(k, cos, sin)
+            self.k[li] = k if self.k[li] is None else torch.cat([self.k[li], k], dim=1)
+            self.v[li] = v if self.v[li] is None else torch.cat([self.v[li], v], dim=1)
+            T = p0 + n
+            g = nh // kv
+            kk = self.k[li].unsqueeze(1).expand(kv, g, T, hd).reshape(nh, T, hd)     # gqa_expand order
+            vv = self.v[li].unsqueeze(1).expand(kv, g, T, hd).reshape(nh, T, hd)
+            scores = (q @ kk.transpose(1, 2)) * scale
+            qpos = torch.arange(p0, T).reshape(n, 1)
+            scores = scores + torch.where(torch.arange(T).reshape(1, T) > qpos, torch.tensor(-1e9), torch.tensor(0.0))
+            ctx = torch.softmax(scores, dim=-1) @ vv                                 # [nh, n, hd]
+            attn = linear(ctx.transpose(0, 1).reshape(n, nh * hd), L["w_o"])
+            x, residual = rms_norm(attn, L["ln2"], eps, residual)
+            h = linear(silu_and_mul(linear(x, L["w_gu"])), L["w_down"])
+        self.len += n
+        last, _ = rms_norm(h[-1:], M.norm, eps, residual[-1:])
+        return (last @ M.lm_head)[0]
+
+
 def argmax_last(logits_row) -> int:
     """src/engine/llm_engine.rs:135-142: Iterator::max_by returns the LAST maximal element."""
     a = np.asarray(logits_row, dtype=np.float32)

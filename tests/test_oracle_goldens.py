@@ -181,3 +181,21 @@ def test_hf_transformers_crosscheck():
     from oracle.crosscheck_hf import crosscheck
     err, cos, _ = crosscheck("qwen3-tiny", seed=0, batch=2, seqlen=24)
     assert err < 1e-4 and cos > 0.99999
+
+
+def test_kv_cached_cpu_variant_equals_full_recompute():
+    """the KV-cached CPU variant that bench.py times next to the reference algorithm is the
+    same arithmetic - prefill in two chunks + decode steps reproduce the full-recompute logits."""
+    import torch
+    from oracle import synth
+    cfg = O.MODEL_CONFIGS["qwen3-tiny"]
+    w = {k: v.float() for k, v in synth.make_weights(cfg, seed=3, norm_jitter=0.1).items()}
+    model = O.Qwen3Oracle(cfg, w, "fp32")
+    ids = synth.make_prompts(1, 37, cfg.vocab_size, 77)[0]
+    full = model.compute_logits(model.forward(torch.tensor([ids])))[0]
+    inc = O.Qwen3OracleKVCached(model, 64)
+    got = [inc.step(ids[:20]), inc.step(ids[20:30])] + [inc.step([t]) for t in ids[30:]]
+    want = [full[19], full[29]] + [full[i] for i in range(30, 37)]
+    for g, w_ in zip(got, want):
+        assert (g - w_).abs().max().item() < 2e-4
+        assert O.argmax_last(g.numpy()) == O.argmax_last(w_.numpy())

@@ -1,0 +1,44 @@
+"""lm_head GEMM at decode batch sizes ([M, H] x [V, H]^T -> fp32 logits): forced (BN, KPS) tiles of the 1-CTA
+kernel against the automatic choice; cold weights (two copies > L2), CUDA-graph timed."""
+import importlib
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+
+ops = importlib.import_module("nano-vllm-candle_b200.ops")
+ctx = ops.Context(0)
+BF16 = torch.bfloat16
+V = 151936
+
+
+def timed(M, K, force_bn, iters=8):
+    a = torch.randn(M, K, device="cuda").to(BF16)
+    ws = [torch.randn(V, K, device="cuda").to(BF16) for _ in range(2)]
+    out = torch.empty(M, V, device="cuda", dtype=torch.float32)
+    try:
+        for w in ws:
+            ctx.gemm(a, w, out=out, force_bn=force_bn)
+    except Exception as e:          # a (BN, KPS) pair that is not instantiated
+        return None
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for i in range(iters):
+            ctx.gemm(a, ws[i % 2], out=out, force_bn=force_bn)
+    g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(); g.replay(); e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e3 / iters
+
+
+for M, K in ((64, 1024), (1, 1024), (64, 4096), (128, 5120)):
+    gb = (V * K * 2 + M * V * 4) / 1e3
+    row = []
+    for fb in (0, 1256, 1128, 2128, 2064, 4064, 21256, 41128, 42128):
+        us = timed(M, K, fb)
+        row.append(f"{fb}:{'-' if us is None else f'{us:.1f}us/{gb / us:.0f}GB/s'}")
+    print(f"M={M} K={K}  " + "  ".join(row), flush=True)

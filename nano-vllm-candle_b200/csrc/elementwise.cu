@@ -198,7 +198,6 @@ qk_norm_rope_store_kernel(uint4* __restrict__ qkv, const uint4* __restrict__ qw,
                           const int32_t* __restrict__ slot_mapping, uint4* __restrict__ k_cache,
                           uint4* __restrict__ v_cache, int N, int nh, int kv) {
   pdl_trigger();
-  pdl_wait();
   const int units_per_tok = nh + 2 * kv;
   const int64_t unit = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
   const int l = threadIdx.x & 7;
@@ -208,6 +207,22 @@ qk_norm_rope_store_kernel(uint4* __restrict__ qkv, const uint4* __restrict__ qw,
   const int u = active ? (int)(unit - (int64_t)n * units_per_tok) : 0;
   uint4* row = qkv + ((int64_t)n * units_per_tok + u) * 16;   // 16 uint4 per 128-element head
   const int slot = (slot_mapping != nullptr && active) ? __ldg(slot_mapping + n) : -1;
+  // Everything that is not produced by a kernel of this step - slot, position, the rope row, the norm weight -
+  // is fetched BEFORE the dependency wait (two dependent loads, positions -> cos/sin, overlap the predecessor).
+  const bool is_qk = u < nh + kv;
+  const uint4* wp = u < nh ? qw : kw;
+  uint4 w_lo = make_uint4(0, 0, 0, 0), w_hi = w_lo;
+  float4 c0 = make_float4(0, 0, 0, 0), c1 = c0, s0 = c0, s1 = c0;
+  if (active && is_qk) {
+    if (wp != nullptr) {
+      w_lo = __ldg(wp + l);
+      w_hi = __ldg(wp + l + 8);
+    }
+    const float4* cs = cos_sin + (int64_t)__ldg(positions + n) * 32;   // 128 floats per position: cos[64], sin[64]
+    c0 = __ldg(cs + 2 * l); c1 = __ldg(cs + 2 * l + 1);
+    s0 = __ldg(cs + 16 + 2 * l); s1 = __ldg(cs + 16 + 2 * l + 1);
+  }
+  pdl_wait();
 
   if (u >= nh + kv) {   // V head: copy to the cache (bit-exact)
     if (active && slot >= 0) {
@@ -238,21 +253,16 @@ qk_norm_rope_store_kernel(uint4* __restrict__ qkv, const uint4* __restrict__ qw,
   ss += __shfl_xor_sync(mask, ss, 4);
   if (!active) return;
   const bool is_q = u < nh;
-  const uint4* wp = is_q ? qw : kw;
   float rstd = 1.0f;
   float wa[8], wb[8];
   if (wp != nullptr) {   // NULL weight: rope only (RotaryEmbedding::apply on its own)
     rstd = 1.0f / sqrtf(ss * (1.0f / 128.0f) + eps);
-    unpack8(__ldg(wp + l), wa);
-    unpack8(__ldg(wp + l + 8), wb);
+    unpack8(w_lo, wa);
+    unpack8(w_hi, wb);
   } else {
 #pragma unroll
     for (int i = 0; i < 8; ++i) wa[i] = wb[i] = 1.0f;
   }
-  const int pos = __ldg(positions + n);
-  const float4* cs = cos_sin + (int64_t)pos * 32;   // 128 floats per position: cos[64], sin[64]
-  float4 c0 = __ldg(cs + 2 * l), c1 = __ldg(cs + 2 * l + 1);
-  float4 s0 = __ldg(cs + 16 + 2 * l), s1 = __ldg(cs + 16 + 2 * l + 1);
   const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
   const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
   float y1[8], y2[8];

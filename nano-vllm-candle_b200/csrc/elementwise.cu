@@ -56,9 +56,12 @@ fused_add_rmsnorm_kernel(const uint4* __restrict__ x, const float4* __restrict__
                          uint4* __restrict__ out, int H) {
   __shared__ float red[32];
   pdl_trigger();
-  pdl_wait();
   const int row = blockIdx.x;
   const int nvec = H >> 3;
+  // the norm weight is not produced by a kernel: fetch it before the dependency wait (single-pass variant)
+  uint4 wv = make_uint4(0, 0, 0, 0);
+  if (!kLoop && (int)threadIdx.x < nvec) wv = __ldg(w + threadIdx.x);
+  pdl_wait();
   const int64_t vbase = (int64_t)row * nvec;
   float s[8];
   float ss = 0.f;
@@ -107,7 +110,7 @@ fused_add_rmsnorm_kernel(const uint4* __restrict__ x, const float4* __restrict__
     const int v = threadIdx.x;
     if (v < nvec) {
       float wf[8];
-      unpack8(__ldg(w + v), wf);
+      unpack8(wv, wf);
 #pragma unroll
       for (int i = 0; i < 8; ++i) s[i] = s[i] * rstd * wf[i];
       out[vbase + v] = pack8(s);

@@ -117,14 +117,26 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   // that far ahead of its shared-memory ring: a CTA's ring (~190 KB) covers only ~60 B/clk at HBM
   // latency, the L2 prefetch decouples the bytes in flight from the ring size.
   constexpr int kPrefetchKb = BN >= 256 ? 8 : (BN >= 128 ? 16 : 32);
+  // Decode (prefetch_w): the W sub-tiles of the first ring lap are not only prefetched but LOADED into shared
+  // memory before the wait - a K = 1024 GEMM has its whole weight tile on chip when the activations arrive, and
+  // only the A boxes (the larger share of the ingest at small BN) are left on the critical path.
+  const int w_pre = prefetch_w ? min(num_it, cfg::kStages) : 0;
   if (warp == 2 && prefetch_w) {
     if (ptx::elect_one()) {
-      const int n = min(num_kb, kPrefetchKb);
-      for (int kb = 0; kb < n; ++kb) ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, n_tile * BN);
+      for (int it = 0; it < w_pre; ++it) {
+        const int nsub = min(KPS, num_kb - it * KPS);
+        ptx::mbar_arrive_expect_tx(full_bar(it), (uint32_t)cfg::kBytesB * nsub);
+        const uint32_t dst = smem_base + it * cfg::kStageBytes + (uint32_t)(KPS * cfg::kBytesA);
+#pragma unroll
+        for (int j = 0; j < KPS; ++j)
+          if (j < nsub) ptx::tma_load_2d(dst + j * cfg::kBytesB, &tma_b, full_bar(it), (kb_begin + it * KPS + j) * BK, n_tile * BN);
+      }
+      const int k0 = w_pre * KPS, k1 = min(num_kb, k0 + kPrefetchKb);
+      for (int kb = k0; kb < k1; ++kb) ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, n_tile * BN);
     }
     __syncwarp();
   }
-  pdl_wait();      // everything above (barrier init, TMEM alloc, descriptor prefetch) overlapped the predecessor
+  pdl_wait();      // everything above (barrier init, TMEM alloc, descriptor prefetch, first W loads) overlapped the predecessor
   if (tr && threadIdx.x == 0) trace[1] = clock64();
 
   if (warp == 0 || warp == 2) {
@@ -136,7 +148,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const CUtensorMap* map = is_a ? &tma_a : &tma_b;
     const int row0 = is_a ? m_tile * BM + (int)cta_rank * a_box_rows : n_tile * BN;
     const uint32_t off = is_a ? cta_rank * (uint32_t)a_box_rows * (BK * 2) : (uint32_t)(KPS * cfg::kBytesA);
-    for (int it = 0; it < num_it; ++it) {
+    for (int it = is_a ? 0 : w_pre; it < num_it; ++it) {
       const int s = it % cfg::kStages;
       if (it >= cfg::kStages) ptx::mbar_wait(empty_bar(s), ((it / cfg::kStages) & 1) ^ 1u);   // first lap: slots are free
       if (ptx::elect_one()) {

@@ -114,9 +114,11 @@ def _rope_ref(qkv, qw, kw, eps, positions, nh, kv, hd, theta):
     return O.apply_rotary(qn.reshape(N, nh, hd), c, s), O.apply_rotary(kn.reshape(N, kv, hd), c, s)
 
 
-@pytest.mark.parametrize("N,nh,kv", [(1, 16, 8), (64, 16, 8), (37, 32, 8), (5, 4, 2), (3, 5, 1)])
+@pytest.mark.parametrize("N,nh,kv", [(1, 16, 8), (64, 16, 8), (37, 32, 8), (5, 4, 2), (3, 5, 1),
+                                     (1500, 16, 8)])   # > 1024 CTAs: the prefill ordering of the static loads
 def test_qk_norm_rope_store(ctx, N, nh, kv):
-    hd, bs, nblk, theta = 128, 16, 12, 1e6
+    hd, bs, theta = 128, 16, 1e6
+    nblk = max(12, (N + bs - 1) // bs + 2)                 # room for one slot per token
     g = torch.Generator().manual_seed(N + nh)
     qkv = torch.randn(N, (nh + 2 * kv) * hd, generator=g).to(BF16)
     qw = (1 + 0.2 * torch.randn(hd, generator=g)).to(BF16)

@@ -408,3 +408,38 @@ def test_chunked_step_output_counts_computed_and_sampled_tokens():
     assert s.is_prefill and (s.num_query_tokens, s.num_decode_seqs, s.num_sampled) == (6, 1, 2)
     s = cpp.step()
     assert not s.is_prefill and (s.num_query_tokens, s.num_decode_seqs, s.num_sampled, s.num_tokens) == (2, 2, 2, -2)
+
+
+# ----------------------------------------------------------------------------- property-based (hypothesis)
+def test_chunked_scheduler_fuzz_against_oracle():
+    """Random pool sizes, budgets, prompt lengths (shared prefixes included), arrival times and prefix caching
+    on / off: the C++ chunked scheduler and the oracle's SchedulerChunked must agree step by step and keep the
+    invariants of _lockstep_chunked (budget, sequence bound, unique slots, every position computed once per
+    residency, outputs of the unchunked engine)."""
+    hyp = pytest.importorskip("hypothesis")
+    st = hyp.strategies
+
+    @hyp.settings(max_examples=40, deadline=None, derandomize=True,
+                  suppress_health_check=list(hyp.HealthCheck))
+    @hyp.given(st.data())
+    def run(data):
+        bs = data.draw(st.sampled_from([16, 32]))
+        max_seqs = data.draw(st.integers(1, 6))
+        budget = data.draw(st.integers(max_seqs, 4 * bs))
+        nblocks = data.draw(st.integers(8, 40))
+        prefix = data.draw(st.booleans())
+        nseq = data.draw(st.integers(1, 8))
+        cap = max(1, (nblocks // 2) * bs - 30)               # a prompt + its completion always fits the pool
+        base = data.draw(st.lists(st.integers(10, 99), min_size=1, max_size=3 * bs))
+        prompts = []
+        for _ in range(nseq):
+            share = data.draw(st.integers(0, len(base)))
+            tail = data.draw(st.lists(st.integers(100, 999), min_size=0 if share else 1, max_size=2 * bs))
+            prompts.append((base[:share] + tail)[:cap])
+        arrivals = sorted(data.draw(st.lists(st.integers(0, 30), min_size=nseq, max_size=nseq)))
+        max_tokens = data.draw(st.integers(1, 20))
+        cpp, sch = _mk_chunked(max_seqs, budget, nblocks, bs, eos=7, prefix=prefix)
+        _lockstep_chunked(cpp, sch, prompts, max_tokens, budget, max_seqs, bs, nblocks, arrivals, max_steps=20000)
+        assert cpp.num_free_blocks() == nblocks
+
+    run()

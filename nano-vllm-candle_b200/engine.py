@@ -165,9 +165,11 @@ def _p(a: np.ndarray):
 class Qwen3ModelRunner:
     """Qwen3ModelRunner (src/engine/llm_engine.rs:35-189) on the B200 step executor.
 
-    Greedy only: `run` returns argmax with the reference's tie rule (last maximum).  The
+    Greedy by default: a step returns argmax with the reference's tie rule (last maximum).  The
     reference's temperature path draws from an unseeded RNG (llm_engine.rs:128) and cannot be
-    reproduced; on-device sampling is listed as a next item in DESIGN.md."""
+    reproduced; `set_sampling` / `LLMEngine.set_sampling` arm the seeded on-device sampler instead
+    (Gumbel-max on Philox noise).  Steps: `prefill` (whole prompts), `decode` (one token
+    per sequence, CUDA graph), `step_mixed` (chunked prefill: decode rows + prompt chunks)."""
 
     def __init__(self, ctx, cfg: Qwen3Config, num_kvcache_blocks: int, kvcache_block_size: int = 256,
                  max_num_seqs: int = 64, max_num_batched_tokens: int = 4096, max_model_len: Optional[int] = None,

@@ -443,3 +443,64 @@ def test_chunked_scheduler_fuzz_against_oracle():
         assert cpp.num_free_blocks() == nblocks
 
     run()
+
+
+def test_reference_scheduler_fuzz_against_oracle():
+    """The reference's scheduling mode (whole-prompt prefill step or decode step, scheduler.rs:106-249) with the
+    real allocator, prefix caching on / off, random pools / prompts: C++ engine == oracle, step by step."""
+    hyp = pytest.importorskip("hypothesis")
+    st = hyp.strategies
+
+    @hyp.settings(max_examples=40, deadline=None, derandomize=True, suppress_health_check=list(hyp.HealthCheck))
+    @hyp.given(st.data())
+    def run(data):
+        bs = data.draw(st.sampled_from([16, 32]))
+        max_seqs = data.draw(st.integers(1, 6))
+        nblocks = data.draw(st.integers(8, 40))
+        prefix = data.draw(st.booleans())
+        max_tokens = data.draw(st.integers(1, 20))
+        cap = max(1, (nblocks // 2) * bs - max_tokens - 5)   # one sequence always fits, so decode can always preempt its way out
+        base = data.draw(st.lists(st.integers(10, 99), min_size=1, max_size=3 * bs))
+        prompts = []
+        for _ in range(data.draw(st.integers(1, 8))):
+            share = data.draw(st.integers(0, len(base)))
+            tail = data.draw(st.lists(st.integers(100, 999), min_size=0 if share else 1, max_size=2 * bs))
+            prompts.append((base[:share] + tail)[:cap])
+        # every prompt fits one prefill step - also after a preemption, when the sequence is re-prefilled with its
+        # completion so far (a budget below that stalls the reference for good: prefill refuses, decode has nothing)
+        budget = max(len(p) for p in prompts) + max_tokens + data.draw(st.integers(0, 4 * bs))
+        cpp, orc = _mk(max_seqs, budget, nblocks, bs, eos=7, prefix=prefix)
+        _lockstep(cpp, orc, prompts, eng.SamplingParams(1.0, max_tokens, True), E.SamplingParams(1.0, max_tokens, True),
+                  max_steps=20000)
+        assert cpp.num_free_blocks() == nblocks
+        for sid, p in enumerate(prompts):
+            got, fin = cpp.output_of(sid)
+            assert fin and got == [p[-1] + 1 + i for i in range(max_tokens)]
+
+    run()
+
+
+def test_preempted_sequence_that_outgrew_the_budget_stalls_the_reference_but_not_chunked_prefill():
+    """Found by the fuzz test: with max_num_batched_tokens = 14, a 14-token prompt that is preempted after 19
+    generated tokens can never be prefilled again (33 > 14: scheduler.rs:125-130 refuses, then the decode stage has
+    nothing to schedule and the reference asserts, :175-178).  The C++ engine reports it as a status; the chunked
+    scheduler re-prefills the sequence in chunks and finishes."""
+    bs, nblocks, max_tokens = 16, 8, 20
+    prompts = [[100], [100], [100], [100] * 14]
+    cpp, orc = _mk(4, 14, nblocks, bs, eos=7)
+    sp, osp = eng.SamplingParams(1.0, max_tokens, True), E.SamplingParams(1.0, max_tokens, True)
+    for p in prompts:
+        cpp.add_request(p, sp)
+        orc.add_request(list(p), osp)
+    with pytest.raises(AssertionError):
+        for _ in range(200):
+            seqs, is_prefill = orc.scheduler.schedule()
+            orc.scheduler.post_process(seqs, orc.model_runner.run(seqs, is_prefill))
+    with pytest.raises(eng.NvcError):
+        for _ in range(200):
+            cpp.step()
+    assert cpp.num_waiting() == 1 and cpp.num_running() == 0          # the stalled sequence, like the oracle's
+    assert len(orc.scheduler.waiting) == 1 and not orc.scheduler.running
+    chunked, sch = _mk_chunked(4, 14, nblocks, bs, eos=7)
+    _lockstep_chunked(chunked, sch, prompts, max_tokens, 14, 4, bs, nblocks)
+    assert chunked.is_finished() and chunked.output_of(3) == ([101 + i for i in range(max_tokens)], True)

@@ -21,6 +21,15 @@
  *   - one nvc_ctx per (process, device); a context is used from one host thread at a
  *     time (the reference is single-threaded: Rc<RefCell<..>>, src/engine/llm_engine.rs:17).
  *   - bf16 = IEEE bfloat16 bit pattern in uint16_t storage.
+ *   - launch order: every kernel is launched with programmatic stream serialization (PDL) and signals its
+ *     dependents at its first instruction, so a kernel of this library may START while the previous kernels of
+ *     this library on the stream are still running.  It waits (griddepcontrol.wait) before reading anything
+ *     those kernels produce, but reads its STATIC operands earlier: weights, norm vectors, the rope table,
+ *     positions / slot_mapping / block_tables / context_lens / cu_seqlens, and - paged decode only - cache rows
+ *     other than the slot of each sequence's newest token.  Static operands must therefore be complete when the
+ *     call is enqueued in stream order by anything that is not a kernel of this library (memcpy, other
+ *     libraries' kernels: those never signal early, so plain stream order is enough) and must never be the
+ *     output of a kernel of this library in the same stream.
  *   - no CPU fallback: on a machine without a usable sm_100 device nvc_ctx_create fails.
  */
 #ifndef NVC_B200_H

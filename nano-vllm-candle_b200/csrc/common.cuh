@@ -69,7 +69,11 @@ static inline cudaStream_t nvc_stream(void* s) { return reinterpret_cast<cudaStr
 #ifdef __CUDACC__
 // Launch with programmatic stream serialization: the kernel may start (run its prologue up to
 // pdl_wait()) while its predecessor in the stream is still draining.  Every kernel of this
-// library calls pdl_wait() before it touches global memory and pdl_trigger() at its top.
+// library calls pdl_trigger() at its top and pdl_wait() before it reads or writes anything another
+// kernel of the step produces; operands no kernel of the step writes (weights, norm vectors, rope
+// table, positions / slot_mapping / block_tables / context_lens, older cache rows) may be fetched
+// ahead of the wait - the early-launch chain can be several kernels deep, so "written two kernels
+// ago" is NOT safe before the wait.
 template <typename... KArgs, typename... Args>
 static inline cudaError_t nvc_launch_cluster3(const nvc_ctx* ctx, void (*kernel)(KArgs...), dim3 grid, dim3 block,
                                               size_t smem, cudaStream_t stream, dim3 cluster, Args&&... args) {

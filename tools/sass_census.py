@@ -20,6 +20,10 @@ Counts of instructions whose opcode starts with the mnemonic: `UTCHMMA` = tcgen0
 `UTMALDG` = TMA tensor load, `UTMAPF` = TMA L2 prefetch, `UTCATOMSWS` = TMEM alloc/dealloc, `LDTM`/`STTM` = tcgen05.ld/st,
 `SYNCS` = mbarrier ops, `UCGABAR` = cluster barrier, `ACQBULK` = griddepcontrol.wait, `HMMA` = legacy mma.sync
 (none of the GEMM / prefill kernels use it; the paged decode kernel is the one deliberate mma.sync user, DESIGN.md 4.3).
+`regs / stack / static smem` is `cuobjdump -res-usage` (dynamic shared memory is not listed).  No kernel spills: the 8-24 B
+stack frames of the tcgen05 and peer-memory kernels are the argument buffer of the cold-path `printf` that reports an
+mbarrier / peer-flag wait that timed out before trapping (ptx.cuh `mbar_wait`, p2p_allreduce.cu); their only STL
+instructions sit in those blocks.
 """
 
 
@@ -47,9 +51,20 @@ def main():
                 if m.group(1).startswith(k):
                     per[fn][k] += 1
                     break
-    rows = [HEADER, "| kernel | total | " + " | ".join(MNEMONICS) + " |", "|---|---|" + "---|" * len(MNEMONICS)]
+    # registers / stack (spills) / static shared memory per kernel, from the same cubin
+    res, fn = {}, None
+    for line in subprocess.run(["cuobjdump", "-res-usage", LIB], capture_output=True, text=True, check=True).stdout.splitlines():
+        m = re.match(r"\s*Function (\S+):", line)
+        if m:
+            fn = m.group(1)
+            continue
+        m = re.search(r"REG:(\d+) STACK:(\d+) SHARED:(\d+) LOCAL:(\d+)", line)
+        if m and fn:
+            res[fn] = "%s / %s / %s" % (m.group(1), m.group(2), m.group(3))
+    rows = [HEADER, "| kernel | regs / stack B / static smem B | instrs | " + " | ".join(MNEMONICS) + " |",
+            "|---|---|---|" + "---|" * len(MNEMONICS)]
     for f, c in sorted(per.items(), key=lambda kv: demangle(kv[0])):
-        rows.append("| `%s` | %d | " % (demangle(f)[:110], c["_total"])
+        rows.append("| `%s` | %s | %d | " % (demangle(f)[:110], res.get(f, "?"), c["_total"])
                     + " | ".join(str(c[k]) if c[k] else "" for k in MNEMONICS) + " |")
     with open(out_path, "w") as fh:
         fh.write("\n".join(rows) + "\n")

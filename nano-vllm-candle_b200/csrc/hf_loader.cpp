@@ -102,10 +102,13 @@ struct JParser {
           case 'u': {
             uint32_t cp;
             if (!hex4(cp)) return false;
-            if (cp >= 0xD800 && cp < 0xDC00 && end - p >= 6 && p[0] == '\\' && p[1] == 'u') {
+            if (cp >= 0xDC00 && cp < 0xE000) return fail("lone trailing surrogate in \\u escape");
+            if (cp >= 0xD800 && cp < 0xDC00) {
+              if (end - p < 6 || p[0] != '\\' || p[1] != 'u') return fail("lone leading surrogate in \\u escape");
               p += 2;
               uint32_t lo;
               if (!hex4(lo)) return false;
+              if (lo < 0xDC00 || lo >= 0xE000) return fail("lone leading surrogate in \\u escape");
               cp = 0x10000 + ((cp - 0xD800) << 10) + (lo - 0xDC00);
             }
             utf8(out, cp);
@@ -114,7 +117,27 @@ struct JParser {
           default: return fail("bad escape");
         }
       } else {
-        out += *p++;
+        // raw bytes: no control characters, well-formed UTF-8 only (what serde_json / RFC 8259 accept)
+        const unsigned char c = (unsigned char)*p;
+        if (c < 0x20) return fail("control character in string");
+        int extra = 0;
+        uint32_t cp = c;
+        if (c >= 0x80) {
+          if (c >= 0xC2 && c <= 0xDF) { extra = 1; cp = c & 0x1F; }
+          else if (c >= 0xE0 && c <= 0xEF) { extra = 2; cp = c & 0x0F; }
+          else if (c >= 0xF0 && c <= 0xF4) { extra = 3; cp = c & 0x07; }
+          else return fail("invalid UTF-8 in string");
+          if (end - p <= extra) return fail("invalid UTF-8 in string");
+          for (int i = 1; i <= extra; ++i) {
+            const unsigned char cc = (unsigned char)p[i];
+            if ((cc & 0xC0) != 0x80) return fail("invalid UTF-8 in string");
+            cp = (cp << 6) | (cc & 0x3F);
+          }
+          if ((extra == 2 && (cp < 0x800 || (cp >= 0xD800 && cp < 0xE000))) || (extra == 3 && (cp < 0x10000 || cp > 0x10FFFF)))
+            return fail("invalid UTF-8 in string");
+        }
+        out.append(p, (size_t)extra + 1);
+        p += extra + 1;
       }
     }
     if (p >= end) return fail("unterminated string");
@@ -167,11 +190,21 @@ struct JParser {
     if (c == 'f') { v.kind = JValue::Bool; v.b = false; return lit("false"); }
     if (c == 'n') { v.kind = JValue::Null; return lit("null"); }
     // number
+    // number: -? (0 | [1-9][0-9]*) (. [0-9]+)? ([eE] [+-]? [0-9]+)?   (RFC 8259)
     const char* s = p;
-    while (p < end && (*p == '-' || *p == '+' || *p == '.' || *p == 'e' || *p == 'E' || (*p >= '0' && *p <= '9'))) ++p;
-    if (p == s) return fail("unexpected character");
+    auto digits = [&]() { const char* d = p; while (p < end && *p >= '0' && *p <= '9') ++p; return p > d; };
+    if (p < end && *p == '-') ++p;
+    if (p < end && *p == '0') ++p;
+    else if (!digits()) return fail(p == s ? "unexpected character" : "invalid number");
+    if (p < end && *p == '.') { ++p; if (!digits()) return fail("invalid number"); }
+    if (p < end && (*p == 'e' || *p == 'E')) {
+      ++p;
+      if (p < end && (*p == '+' || *p == '-')) ++p;
+      if (!digits()) return fail("invalid number");
+    }
     v.kind = JValue::Num;
     v.num = strtod(std::string(s, p).c_str(), nullptr);
+    if (!std::isfinite(v.num)) return fail("number out of range");
     return true;
   }
 };
@@ -298,14 +331,21 @@ int open_safetensors(const std::string& path, std::unique_ptr<nvc_safetensors>& 
     e.name = kv.first;
     e.dtype_name = dt->str;
     e.dtype = dt->str == "BF16" ? NVC_ST_BF16 : dt->str == "F16" ? NVC_ST_F16 : dt->str == "F32" ? NVC_ST_F32 : NVC_ST_OTHER;
+    // sizes and offsets are unsigned integers; a double holds them exactly up to 2^53 (8 PiB), beyond any file
+    auto as_u64 = [](const JValue& v, uint64_t& o) {
+      if (v.kind != JValue::Num || !(v.num >= 0.0 && v.num <= 9007199254740992.0) || v.num != std::floor(v.num)) return false;
+      o = (uint64_t)v.num;
+      return true;
+    };
     uint64_t count = 1;
     for (auto& d : sh->arr) {
-      if (d.kind != JValue::Num || d.num < 0) return hf_fail(NVC_EINVAL, path + ": bad shape for " + kv.first);
-      e.shape.push_back((int64_t)d.num);
-      count *= (uint64_t)d.num;
+      uint64_t dim;
+      if (!as_u64(d, dim) || (dim != 0 && count > (1ull << 62) / dim)) return hf_fail(NVC_EINVAL, path + ": bad shape for " + kv.first);
+      e.shape.push_back((int64_t)dim);
+      count *= dim;
     }
-    e.begin = (uint64_t)off->arr[0].num;
-    e.end = (uint64_t)off->arr[1].num;
+    if (!as_u64(off->arr[0], e.begin) || !as_u64(off->arr[1], e.end))
+      return hf_fail(NVC_EINVAL, path + ": data_offsets out of range for " + kv.first);
     if (e.begin > e.end || e.end > st->data_bytes) return hf_fail(NVC_EINVAL, path + ": data_offsets out of range for " + kv.first);
     if (e.dtype != NVC_ST_OTHER && e.end - e.begin != count * (uint64_t)elem_bytes(e.dtype))
       return hf_fail(NVC_EINVAL, path + ": byte size does not match shape for " + kv.first);
@@ -428,6 +468,9 @@ int nvc_qwen3_config_from_hf_dir(const char* model_dir, nvc_qwen3_config* out, i
   double v;
   for (auto& f : req) {
     if (!jnum(root, f.key, v)) return hf_fail(NVC_EINVAL, "Failed to parse HF config " + path + ": missing field `" + f.key + "`");
+    // serde reads these into usize / u32: negative, fractional or out-of-range numbers are parse errors there too
+    if (!(v >= 0.0 && v <= 2147483647.0) || v != (double)(int64_t)v)
+      return hf_fail(NVC_EINVAL, "Failed to parse HF config " + path + ": invalid value for `" + f.key + "`");
     *f.dst = (int32_t)v;
   }
   if (!jnum(root, "rms_norm_eps", v)) return hf_fail(NVC_EINVAL, "Failed to parse HF config " + path + ": missing field `rms_norm_eps`");
@@ -436,7 +479,13 @@ int nvc_qwen3_config_from_hf_dir(const char* model_dir, nvc_qwen3_config* out, i
   if (!act || act->kind != JValue::Str) return hf_fail(NVC_EINVAL, "Failed to parse HF config " + path + ": missing field `hidden_act`");
   if (act->str != "silu") return hf_fail(NVC_ENOTIMPL, "hidden_act " + act->str + " is not supported (SiluAndMul only, activation.rs:13-18)");
   if (out->num_attention_heads <= 0) return hf_fail(NVC_EINVAL, "num_attention_heads must be positive");
-  out->head_dim = jnum(root, "head_dim", v) ? (int32_t)v : out->hidden_size / out->num_attention_heads;   // :88-90
+  if (jnum(root, "head_dim", v)) {                                                                        // :88-90
+    if (!(v >= 1.0 && v <= 2147483647.0) || v != (double)(int64_t)v)
+      return hf_fail(NVC_EINVAL, "Failed to parse HF config " + path + ": invalid value for `head_dim`");
+    out->head_dim = (int32_t)v;
+  } else {
+    out->head_dim = out->hidden_size / out->num_attention_heads;
+  }
   out->rope_theta = jnum(root, "rope_theta", v) ? (float)v : 1e6f;                                        // :96
   if (tie_word_embeddings) {
     const JValue* t = root.get("tie_word_embeddings");

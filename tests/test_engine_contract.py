@@ -2,6 +2,7 @@
 the reference's Scheduler / BlockManager / Sequence / LLMEngine, and of the integer contract
 (N1 slot_mapping, N2 block_tables): everything bit-exact, step by step."""
 import importlib
+import os
 
 import numpy as np
 import pytest
@@ -411,6 +412,10 @@ def test_chunked_step_output_counts_computed_and_sampled_tokens():
 
 
 # ----------------------------------------------------------------------------- property-based (hypothesis)
+# 40 derandomised examples per property in the regular suite; NVC_FUZZ_EXAMPLES=5000 runs a deep, randomised search.
+_FUZZ_EXAMPLES = int(os.environ.get("NVC_FUZZ_EXAMPLES", "40"))
+
+
 def test_chunked_scheduler_fuzz_against_oracle():
     """Random pool sizes, budgets, prompt lengths (shared prefixes included), arrival times and prefix caching
     on / off: the C++ chunked scheduler and the oracle's SchedulerChunked must agree step by step and keep the
@@ -419,7 +424,7 @@ def test_chunked_scheduler_fuzz_against_oracle():
     hyp = pytest.importorskip("hypothesis")
     st = hyp.strategies
 
-    @hyp.settings(max_examples=40, deadline=None, derandomize=True,
+    @hyp.settings(max_examples=_FUZZ_EXAMPLES, deadline=None, derandomize=_FUZZ_EXAMPLES == 40,
                   suppress_health_check=list(hyp.HealthCheck))
     @hyp.given(st.data())
     def run(data):
@@ -451,7 +456,8 @@ def test_reference_scheduler_fuzz_against_oracle():
     hyp = pytest.importorskip("hypothesis")
     st = hyp.strategies
 
-    @hyp.settings(max_examples=40, deadline=None, derandomize=True, suppress_health_check=list(hyp.HealthCheck))
+    @hyp.settings(max_examples=_FUZZ_EXAMPLES, deadline=None, derandomize=_FUZZ_EXAMPLES == 40,
+                  suppress_health_check=list(hyp.HealthCheck))
     @hyp.given(st.data())
     def run(data):
         bs = data.draw(st.sampled_from([16, 32]))

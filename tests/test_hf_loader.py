@@ -133,6 +133,112 @@ def test_config_from_hf_dir(tmp_path):
         eng.Qwen3Config.from_hf_dir(str(tmp_path / "nope"))
 
 
+def test_config_json_is_parsed_strictly(tmp_path):
+    """The loader's JSON reader accepts what serde_json (the reference's parser, qwen3.rs:77-86) accepts: RFC 8259
+    numbers, no control characters / malformed UTF-8 / lone surrogates in strings, finite numbers only, and
+    non-negative integers where the reference deserialises into usize / u32."""
+    cfg = O.MODEL_CONFIGS["qwen3-tiny"]
+    _write_config(tmp_path, cfg)
+    good = open(tmp_path / "config.json", "rb").read()
+    eng.Qwen3Config.from_hf_dir(str(tmp_path))
+
+    def bad(old, new, match=None):
+        assert good.count(old) == 1, old
+        (tmp_path / "config.json").write_bytes(good.replace(old, new))
+        with pytest.raises(eng.NvcError, match=match):
+            eng.Qwen3Config.from_hf_dir(str(tmp_path))
+
+    h = str(cfg.hidden_size).encode()
+    for lit in (b"0" + h, h + b".", h + b"e", b"+" + h, b"." + h, b"--" + h, b"NaN", b"Infinity", b"0x10"):
+        bad(b'"hidden_size": ' + h, b'"hidden_size": ' + lit)
+    for lit in (b"-1", b"0.5", b"4294967296", b"1e400", b'"256"', b"null"):
+        bad(b'"hidden_size": ' + h, b'"hidden_size": ' + lit, "hidden_size|out of range")
+    bad(b'"silu"', b'"si\x01lu"', "control character")
+    bad(b'"silu"', b'"si\xfflu"', "UTF-8")
+    bad(b'"silu"', b'"si\xc3lu"', "UTF-8")
+    bad(b'"silu"', b'"si\\ud800lu"', "surrogate")
+    bad(b'"silu"', b'"si\\udc00lu"', "surrogate")
+    bad(b'"silu"', b'"gelu"', "not supported")
+    # escapes and multi-byte UTF-8 that ARE valid still parse
+    (tmp_path / "config.json").write_bytes(good.replace(b'"silu"', b'"s\\u0069lu"').replace(b'"Qwen3ForCausalLM"', '"Qwen3 \\ud83d\\ude00 é 漢"'.encode()))
+    assert eng.Qwen3Config.from_hf_dir(str(tmp_path)).hidden_size == cfg.hidden_size
+
+
+def test_loader_survives_mutated_headers(tmp_path):
+    """Seeded byte-level mutations of a valid safetensors file and a valid config.json (flipped bytes, truncation,
+    header-length field, replaced numbers, structural characters): every call returns a status - no crash, no
+    out-of-bounds read (each accepted file is read back in full) - and failures carry a message."""
+    import random
+    import re
+    l = _lib.lib()
+    save_file({"a": torch.randn(3, 8).to(torch.bfloat16), "b.c": torch.randn(17), "e": torch.arange(5)},
+              str(tmp_path / "ok.safetensors"), metadata={"format": "pt"})
+    blob = (tmp_path / "ok.safetensors").read_bytes()
+    hl = int.from_bytes(blob[:8], "little")
+    cfg = O.MODEL_CONFIGS["qwen3-tiny"]
+    _write_config(tmp_path, cfg, head_dim=64, rope_theta=1e6, tie_word_embeddings=False)
+    text = (tmp_path / "config.json").read_bytes()
+    numbers = ["0", "-1", "99999999999999999999999", "18446744073709551615", "9223372036854775807", "1e9", "4294967296",
+               "2147483648", "0.5", "1e400", "-1e400", "01", "1.", "1e", "NaN"]
+    rng = random.Random(1234)
+
+    def mutate(b, lo, hi):
+        b = bytearray(b)
+        kind = rng.randrange(4)
+        if kind == 0:
+            for _ in range(rng.randrange(1, 6)):
+                b[lo + rng.randrange(hi - lo)] = rng.randrange(256)
+        elif kind == 1:
+            b = b[:rng.randrange(len(b))]
+        elif kind == 2:
+            body = bytes(b[lo:hi]).decode("latin1")
+            m = rng.choice(list(re.finditer(r"\d+", body)))
+            body = (body[:m.start()] + rng.choice(numbers + [str(rng.randrange(1000))]) + body[m.end():]).encode("latin1")
+            b = bytearray(bytes(b[:lo]) if lo == 0 else len(body).to_bytes(8, "little")) + body + b[hi:]
+        else:
+            for _ in range(rng.randrange(1, 4)):
+                b[lo + rng.randrange(hi - lo)] = ord(rng.choice('{}[]",:\\ \x00'))
+        return bytes(b)
+
+    opened = 0
+    for it in range(1500):
+        if it % 10 == 9:
+            b = bytearray(blob)
+            b[:8] = rng.choice([0, 1, hl - 1, hl + 1, len(b), len(b) - 8, 2**31, 2**63, 2**64 - 1, rng.randrange(2**64)]).to_bytes(8, "little")
+            b = bytes(b)
+        else:
+            b = mutate(blob, 8, 8 + hl)
+        p = tmp_path / "m.safetensors"
+        p.write_bytes(b)
+        l2, h, st = _open(p)
+        if st != 0:
+            assert not h.value and l.nvc_hf_last_error() != b""
+            continue
+        opened += 1
+        for name, (dt, shape) in _infos(l, h).items():
+            n = int(np.prod(shape, dtype=np.float64))
+            if 0 <= n <= 1 << 16:
+                buf = np.empty(max(n, 1), dtype=np.uint16)
+                l.nvc_safetensors_read_bf16(h, name.encode("utf-8", "surrogateescape"), buf.ctypes.data_as(C.c_void_p), n)
+        l.nvc_safetensors_close(h)
+    assert opened > 20                                      # the mutations are not all trivially rejected
+    d = tmp_path / "cfg"
+    d.mkdir()
+    accepted = 0
+    for it in range(1500):
+        (d / "config.json").write_bytes(mutate(text, 0, len(text)))
+        c, tie = eng.Qwen3ConfigC(), C.c_int(0)
+        st = l.nvc_qwen3_config_from_hf_dir(os.fsencode(str(d)), C.byref(c), C.byref(tie))
+        if st != 0:
+            assert l.nvc_hf_last_error() != b""
+            continue
+        accepted += 1
+        json.loads((d / "config.json").read_bytes().decode("utf-8"))        # whatever we accept is valid JSON
+        assert min(c.vocab_size, c.hidden_size, c.num_hidden_layers, c.num_key_value_heads, c.intermediate_size) >= 0
+        assert c.num_attention_heads > 0 and c.head_dim >= 0
+    assert accepted > 20
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("layout", ["single_bf16", "sharded_f32_tied", "single_f16"])
 def test_runner_from_hf_dir_matches_from_weights(ctx, tmp_path, layout):

@@ -188,7 +188,8 @@ typedef struct nvc_step_output {
 int nvc_engine_create(const nvc_scheduler_config* cfg, nvc_runner* runner, nvc_engine** out);
 int nvc_engine_destroy(nvc_engine* e);
 const char* nvc_engine_last_error(const nvc_engine* e);
-/* LLMEngine::add_request (:228-237).  Returns the new seq_id (>= 0) or a negative status. */
+/* LLMEngine::add_request (:228-237).  Returns the new seq_id (>= 0) or a negative status (NVC_EINVAL for an
+ * empty prompt, max_tokens < 0, or a temperature the reference's SamplingParams refuses). */
 int64_t nvc_engine_add_request(nvc_engine* e, const int32_t* token_ids, int n, double temperature,
                                int max_tokens, int ignore_eos);
 /* Scheduler::schedule (:106-111) + step-input build (N1/N2).  Fails with NVC_ESTATE when idle. */

@@ -559,7 +559,13 @@ const char* nvc_engine_last_error(const nvc_engine* e) { return e ? e->err.c_str
 
 int64_t nvc_engine_add_request(nvc_engine* e, const int32_t* token_ids, int n, double temperature, int max_tokens,
                                int ignore_eos) {
-  if (!e || (n > 0 && !token_ids) || n < 0) return NVC_EINVAL;
+  if (!e) return NVC_EINVAL;
+  // Sequence::new (sequence.rs:31-47) takes an empty prompt and usize max_tokens; a zero-length sequence has no
+  // query token for the model to run on, so the C ABI refuses it (and a negative max_tokens) up front.
+  if (n <= 0 || !token_ids || max_tokens < 0) {
+    e->err = n <= 0 || !token_ids ? "empty prompt" : "max_tokens must be >= 0";
+    return NVC_EINVAL;
+  }
   if (!(temperature > 1e-10)) {   // sampling_params.rs:20,30
     e->err = "greedy sampling is not permitted (temperature must be > 1e-10)";
     return NVC_EINVAL;
@@ -568,7 +574,7 @@ int64_t nvc_engine_add_request(nvc_engine* e, const int32_t* token_ids, int n, d
   s->seq_id = e->next_seq_id++;
   s->block_size = e->block_size;
   s->token_ids.assign(token_ids, token_ids + n);
-  s->last_token = n ? token_ids[n - 1] : 0;
+  s->last_token = token_ids[n - 1];
   s->num_tokens = s->num_prompt_tokens = (size_t)n;
   s->temperature = temperature;
   s->max_tokens = (size_t)max_tokens;

@@ -510,3 +510,104 @@ def test_preempted_sequence_that_outgrew_the_budget_stalls_the_reference_but_not
     chunked, sch = _mk_chunked(4, 14, nblocks, bs, eos=7)
     _lockstep_chunked(chunked, sch, prompts, max_tokens, 14, 4, bs, nblocks)
     assert chunked.is_finished() and chunked.output_of(3) == ([101 + i for i in range(max_tokens)], True)
+
+
+# ----------------------------------------------------------------------------- C ABI misuse
+def test_add_request_refuses_what_the_model_cannot_run():
+    """Found by the call-sequence fuzz below: Sequence::new (sequence.rs:31-47) accepts an empty prompt, which has
+    no query token to run; in chunked mode it made the scheduler read past the prompt.  The C ABI refuses it."""
+    import ctypes as C
+    for chunked in (False, True):
+        cpp = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(2, 16, 7, 4, 16, enable_chunked_prefill=chunked)),
+                            eng.DummyModelRunner())
+        with pytest.raises(eng.NvcError, match="empty prompt"):
+            cpp.add_request([], eng.SamplingParams(1.0, 4, True))
+        l, h = cpp.l, cpp.h
+        one = (C.c_int32 * 1)(5)
+        assert l.nvc_engine_add_request(h, None, 0, 1.0, 4, 1) == -1
+        assert l.nvc_engine_add_request(h, None, 3, 1.0, 4, 1) == -1
+        assert l.nvc_engine_add_request(h, one, 1, 1.0, -1, 1) == -1
+        assert l.nvc_engine_add_request(h, one, 1, float("nan"), 4, 1) == -1
+        assert cpp.is_finished() and cpp.num_waiting() == 0
+        assert cpp.add_request([5], eng.SamplingParams(1.0, 0, True)) == 0       # max_tokens 0: one token, like :225
+        while not cpp.is_finished():
+            cpp.step()
+        assert cpp.output_of(0) == ([6], True)
+
+
+def test_engine_c_abi_survives_random_call_sequences():
+    """Seeded random call sequences straight at the C ABI (valid and invalid scheduler configurations, requests
+    with bad sizes / temperatures / NULL prompts, schedule and post_process out of order or with the wrong batch
+    size, preemption of unknown ids, tiny output buffers): every call returns a status, views handed out by
+    nvc_engine_step_inputs are readable over their whole documented extent, nothing crashes."""
+    import ctypes as C
+    import random
+    sig = importlib.import_module("nano-vllm-candle_b200._engine_sigs")
+    l = importlib.import_module("nano-vllm-candle_b200._lib").lib()
+    rng = random.Random(7)
+    created = steps_ok = 0
+    for it in range(500):
+        wild = it % 2 == 0                                   # half the engines get arbitrary configurations
+        cfg = sig.SchedulerConfigC()
+        cfg.max_num_seqs = rng.choice([-1, 0, 1, 2, 4, 8] if wild else [1, 2, 4, 8])
+        cfg.max_num_batched_tokens = rng.choice([-5, 0, 1, 7, 16, 64, 256] if wild else [8, 16, 40, 64, 256])
+        cfg.eos = rng.choice([-1, 0, 7])
+        cfg.num_kvcache_blocks = rng.choice([-1, 0, 1, 2, 8, 16] if wild else [1, 2, 3, 8, 16])
+        cfg.kvcache_block_size = rng.choice([-16, 0, 1, 3, 16, 256] if wild else [1, 3, 16, 16, 256])
+        cfg.enable_prefix_caching = rng.randrange(2)
+        cfg.enable_chunked_prefill = rng.randrange(2)
+        e = C.c_void_p()
+        if l.nvc_engine_create(C.byref(cfg), None, C.byref(e)) != 0:
+            assert not e.value
+            continue
+        created += 1
+        ids, scheduled = [], None
+        for _ in range(rng.randrange(1, 100)):
+            op = rng.randrange(10)
+            if op <= 2:
+                n = rng.choice([-1, 0, 1, 3, 15, 16, 17, 33, 40, 300])
+                toks = (C.c_int32 * max(n, 1))(*[rng.randrange(0, 50) for _ in range(max(n, 1))])
+                r = l.nvc_engine_add_request(e, toks if rng.random() > 0.05 else None, n,
+                                             rng.choice([1.0, 1.0, 0.0, -1.0, 1e-12, float("nan")]),
+                                             rng.choice([-1, 0, 1, 5, 30]), rng.randrange(2))
+                assert r >= 0 or r == -1
+                if r >= 0:
+                    ids.append(r)
+            elif op == 3:
+                info = sig.ScheduleInfoC()
+                st = l.nvc_engine_schedule(e, C.byref(info))
+                scheduled = info if st == 0 else None
+                if st == 0:
+                    ps = [C.POINTER(C.c_int32)() for _ in range(6)]
+                    sid, em = C.POINTER(C.c_int64)(), C.POINTER(C.c_int32)()
+                    assert l.nvc_engine_step_inputs(e, *[C.byref(p) for p in ps], C.byref(sid)) == 0
+                    assert l.nvc_engine_step_emit_mask(e, C.byref(em)) == 0
+                    nt = info.num_tokens if info.is_prefill else info.num_seqs
+                    assert nt > 0 and info.num_seqs > 0
+                    touched = sum(ps[0][i] + ps[1][i] + ps[3][i] for i in range(nt))
+                    touched += sum(ps[2][i] for i in range(info.num_seqs + 1)) if info.is_prefill else 0
+                    if info.max_blocks and ps[4]:
+                        touched += sum(ps[4][i] for i in range(info.num_seqs * info.max_blocks))
+                    touched += sum(em[i] + sid[i] for i in range(info.num_seqs))
+            elif op == 4:
+                n = scheduled.num_seqs if scheduled is not None and rng.random() < 0.8 else rng.choice([-1, 0, 1, 5, 100])
+                toks = (C.c_int32 * max(n, 1))(*[rng.randrange(0, 50) for _ in range(max(n, 1))])
+                l.nvc_engine_post_process(e, toks, n)
+                scheduled = None
+            elif op <= 7:
+                out = sig.StepOutputC()
+                steps_ok += l.nvc_engine_step(e, C.byref(out)) == 0
+                scheduled = None
+            elif op == 8:
+                assert l.nvc_engine_preempt(e, rng.choice(ids + [-1, 10**9])) <= 0
+            else:
+                sid = rng.choice(ids + [-1, 10**9])
+                cap = rng.choice([0, 1, 4, 64])
+                buf, n = (C.c_int32 * max(cap, 1))(), C.c_int(0)
+                l.nvc_engine_get_output(e, sid, buf, cap, C.byref(n))
+                l.nvc_engine_seq_block_table(e, sid, buf, cap, C.byref(n))
+                assert l.nvc_engine_num_free_blocks(e) >= 0 and l.nvc_engine_num_waiting(e) >= 0
+                assert l.nvc_engine_num_running(e) >= 0 and l.nvc_engine_is_finished(e) in (0, 1)
+                l.nvc_engine_last_error(e)
+        assert l.nvc_engine_destroy(e) == 0
+    assert created > 250 and steps_ok > 1000

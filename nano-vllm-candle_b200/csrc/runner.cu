@@ -508,6 +508,9 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
   NVC_REQUIRE(ctx, B > 0 && N > 0 && B <= r->opt.max_num_seqs && N <= r->opt.max_num_batched_tokens, NVC_ENOMEM,
               "prefill step exceeds max_num_seqs / max_num_batched_tokens");
   NVC_REQUIRE(ctx, cu_seqlens[0] == 0 && cu_seqlens[B] == N, NVC_EINVAL, "cu_seqlens does not cover N tokens");
+  for (int b = 0; b < B; ++b)   // strictly increasing from 0 to N: every entry is a valid row index below
+    NVC_REQUIRE(ctx, cu_seqlens[b + 1] > cu_seqlens[b] && cu_seqlens[b + 1] - cu_seqlens[b] <= max_seqlen, NVC_EINVAL,
+                "bad cu_seqlens / max_seqlen");
   const int bs = r->opt.kvcache_block_size;
   const int64_t nslots = (int64_t)r->opt.num_kvcache_blocks * bs;
   for (int i = 0; i < N; ++i) {
@@ -524,8 +527,10 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
     NVC_REQUIRE(ctx, context_lens, NVC_EINVAL, "null pointer");
     NVC_REQUIRE(ctx, max_blocks > 0 && max_blocks <= cap, NVC_ENOMEM, "block table wider than max_model_len allows");
     for (int b = 0; b < B; ++b) {
-      const int qlen = cu_seqlens[b + 1] - cu_seqlens[b], nb = (context_lens[b] + bs - 1) / bs;
-      NVC_REQUIRE(ctx, context_lens[b] >= qlen && nb <= max_blocks, NVC_EINVAL, "context_len vs q_len / block table");
+      const int qlen = cu_seqlens[b + 1] - cu_seqlens[b];
+      NVC_REQUIRE(ctx, context_lens[b] >= qlen && (int64_t)context_lens[b] <= (int64_t)max_blocks * bs, NVC_EINVAL,
+                  "context_len vs q_len / block table");
+      const int nb = (context_lens[b] + bs - 1) / bs;
       NVC_REQUIRE(ctx, qlen <= 0 || positions[cu_seqlens[b + 1] - 1] == context_lens[b] - 1, NVC_EINVAL,
                   "the new tokens must be the last positions of the context");
       for (int j = 0; j < nb; ++j)
@@ -540,11 +545,7 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
   memcpy(h + 2 * N, slot_mapping, N * 4);
   memcpy(h + 3 * N, cu_seqlens, (B + 1) * 4);
   int32_t* last = h + 3 * N + B + 1;
-  for (int b = 0; b < B; ++b) {
-    NVC_REQUIRE(ctx, cu_seqlens[b + 1] > cu_seqlens[b] && cu_seqlens[b + 1] - cu_seqlens[b] <= max_seqlen, NVC_EINVAL,
-                "bad cu_seqlens / max_seqlen");
-    last[b] = cu_seqlens[b + 1] - 1;
-  }
+  for (int b = 0; b < B; ++b) last[b] = cu_seqlens[b + 1] - 1;
   cudaStream_t st = r->stream;
   R_CUDA(cudaMemcpyAsync(r->d_ids, h, N * 4, cudaMemcpyHostToDevice, st));
   R_CUDA(cudaMemcpyAsync(r->d_pos, h + N, N * 4, cudaMemcpyHostToDevice, st));
@@ -636,7 +637,7 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
     NVC_REQUIRE(ctx, ids[b] >= 0 && ids[b] < r->cfg.vocab_size, NVC_EINVAL, "token id out of range");
     NVC_REQUIRE(ctx, positions[b] >= 0 && positions[b] < r->opt.max_model_len, NVC_EINVAL, "position out of range");
     NVC_REQUIRE(ctx, slot_mapping[b] >= 0 && slot_mapping[b] < nslots, NVC_EINVAL, "slot out of range");
-    NVC_REQUIRE(ctx, context_lens[b] > 0 && (context_lens[b] + bs - 1) / bs <= max_blocks, NVC_EINVAL, "context_len vs block table");
+    NVC_REQUIRE(ctx, context_lens[b] > 0 && (int64_t)context_lens[b] <= (int64_t)max_blocks * bs, NVC_EINVAL, "context_len vs block table");
     for (int j = 0; j < (context_lens[b] + bs - 1) / bs; ++j)
       NVC_REQUIRE(ctx, block_tables[(size_t)b * max_blocks + j] >= 0 &&
                            block_tables[(size_t)b * max_blocks + j] < r->opt.num_kvcache_blocks, NVC_EINVAL, "block id out of range");

@@ -541,7 +541,10 @@ extern "C" {
 
 int nvc_engine_create(const nvc_scheduler_config* cfg, nvc_runner* runner, nvc_engine** out) {
   if (!cfg || !out) return NVC_EINVAL;
-  if (cfg->max_num_seqs <= 0 || cfg->max_num_batched_tokens <= 0 || cfg->kvcache_block_size <= 0 ||
+  // block size 1 is refused: the append rule `len % block_size == 1` (block_manager.rs / scheduler.rs:159-198) never
+  // fires there, so decode would write past the block table (the reference fixes 256, sequence.rs:35; the runner
+  // wants a multiple of 16)
+  if (cfg->max_num_seqs <= 0 || cfg->max_num_batched_tokens <= 0 || cfg->kvcache_block_size < 2 ||
       cfg->num_kvcache_blocks < 0)
     return NVC_EINVAL;
   if (cfg->enable_chunked_prefill && cfg->max_num_batched_tokens < cfg->max_num_seqs) return NVC_EINVAL;

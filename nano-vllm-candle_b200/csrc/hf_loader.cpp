@@ -349,7 +349,8 @@ int open_safetensors(const std::string& path, std::unique_ptr<nvc_safetensors>& 
     if (e.begin > e.end || e.end > st->data_bytes) return hf_fail(NVC_EINVAL, path + ": data_offsets out of range for " + kv.first);
     if (e.dtype != NVC_ST_OTHER && e.end - e.begin != count * (uint64_t)elem_bytes(e.dtype))
       return hf_fail(NVC_EINVAL, path + ": byte size does not match shape for " + kv.first);
-    st->by_name[e.name] = (int)st->entries.size();
+    if (!st->by_name.emplace(e.name, (int)st->entries.size()).second)
+      return hf_fail(NVC_EINVAL, path + ": tensor " + kv.first + " is listed twice");
     st->entries.push_back(std::move(e));
   }
   out = std::move(st);

@@ -89,6 +89,13 @@ def test_safetensors_rejects_malformed_files(tmp_path):
     cases["badoffsets.safetensors"] = len(hdr).to_bytes(8, "little") + hdr + b"\0" * 16
     hdr = json.dumps({"x": {"dtype": "F32", "shape": [3], "data_offsets": [0, 16]}}).encode()
     cases["sizemismatch.safetensors"] = len(hdr).to_bytes(8, "little") + hdr + b"\0" * 16
+    # found by tests/native/engine_fuzz.cpp: the same tensor listed twice (tensor_info and read_bf16 disagreed)
+    hdr = b'{"x":{"dtype":"F32","shape":[2],"data_offsets":[0,8]},"x":{"dtype":"I64","shape":[1],"data_offsets":[8,16]}}'
+    cases["duplicate.safetensors"] = len(hdr).to_bytes(8, "little") + hdr + b"\0" * 16
+    hdr = json.dumps({"x": {"dtype": "F32", "shape": [2 ** 40, 2 ** 40], "data_offsets": [0, 0]}}).encode()   # product wraps
+    cases["overflow.safetensors"] = len(hdr).to_bytes(8, "little") + hdr + b"\0" * 16
+    hdr = json.dumps({"x": {"dtype": "F32", "shape": [2.5], "data_offsets": [0, 10]}}).encode()
+    cases["fractional.safetensors"] = len(hdr).to_bytes(8, "little") + hdr + b"\0" * 16
     for name, blob in cases.items():
         p = tmp_path / name
         p.write_bytes(blob)

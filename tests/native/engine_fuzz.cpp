@@ -246,9 +246,10 @@ int main(int argc, char** argv) {
         REQUIRE(id >= 0 || id == NVC_EINVAL);
         if (id >= 0) reqs.push_back({id, toks, mt, ign != 0});
         if (id >= 0) g_trace += " add(n=" + std::to_string(n) + ",max=" + std::to_string(mt) + ",ign=" + std::to_string(ign) + ")";
-      } else if (op == 3) {
+      } else if (op == 3 || op == 7) {
+        // op 7 is a whole step done by hand: schedule, check the inputs, answer last + 1, post_process
         scheduled = nvc_engine_schedule(e, &info) == 0;
-        g_trace += scheduled ? " sched" : " sched!";
+        g_trace += scheduled ? (op == 3 ? " sched" : " manual") : " sched!";
         if (scheduled) {
           const int32_t *ids, *pos, *cu, *slots, *bt, *ctx, *emit;
           const int64_t* sid;
@@ -261,6 +262,31 @@ int main(int argc, char** argv) {
           if (bt && info.max_blocks) for (int i = 0; i < info.num_seqs * info.max_blocks; ++i) touched += bt[i];
           for (int b = 0; b < info.num_seqs; ++b) touched += emit[b] + sid[b];
           checked += touched != -1;
+          // a block that receives K / V in this step belongs to exactly one live sequence (blocks shared through
+          // the prefix cache are complete and never written again); block tables never hold a block twice
+          std::vector<int> owners((size_t)cfg.num_kvcache_blocks, 0);
+          for (auto& rq : reqs) {
+            std::vector<int32_t> tbl((size_t)cfg.num_kvcache_blocks + 1);
+            int nb = 0;
+            REQUIRE(nvc_engine_seq_block_table(e, rq.id, tbl.data(), (int)tbl.size(), &nb) == 0);
+            std::set<int32_t> own(tbl.begin(), tbl.begin() + nb);
+            REQUIRE((int)own.size() == nb);
+            for (int32_t b : own) {
+              REQUIRE(b >= 0 && b < cfg.num_kvcache_blocks);
+              ++owners[(size_t)b];
+            }
+          }
+          for (int i = 0; i < nt; ++i)
+            if (slots[i] >= 0) REQUIRE(owners[(size_t)(slots[i] / cfg.kvcache_block_size)] == 1);
+          if (op == 7) {
+            std::vector<int32_t> next((size_t)info.num_seqs);
+            for (int b = 0; b < info.num_seqs; ++b) {
+              const int32_t last = info.is_prefill ? ids[cu[b + 1] - 1] : ids[b];
+              next[(size_t)b] = with_runner ? (last + 1) % 64 : last + 1;
+            }
+            REQUIRE(nvc_engine_post_process(e, next.data(), info.num_seqs) == 0);
+            scheduled = false;
+          }
         }
       } else if (op == 4) {
         const int n = scheduled && rng() % 5 ? info.num_seqs : pick({-1, 0, 1, 5, 100});
@@ -270,7 +296,7 @@ int main(int argc, char** argv) {
         if (prc == 0) clean = false;                                 // arbitrary tokens entered a sequence
         g_trace += prc == 0 ? " post" : " post!";
         scheduled = false;
-      } else if (op <= 7) {
+      } else if (op <= 6) {
         nvc_step_output out;
         g_trace += " step";
         steps_ok += nvc_engine_step(e, &out) == 0;

@@ -33,6 +33,12 @@ static std::string g_trace;   // configuration + calls of the current engine, pr
     }                                                                                                    \
   } while (0)
 
+// Model of the paged KV cache: what (token, position) each slot holds.  Every step writes its new tokens and then
+// requires that the whole context of every sequence, read through its block table, is there at the right positions -
+// this is what catches a prefix-cache hit on a block that is not computed yet, a block freed while still in use, or
+// two sequences writing the same block.
+static std::vector<std::pair<int32_t, int32_t>> g_kv;
+
 static void check_step(nvc_runner* r, const int32_t* ids, const int32_t* pos, const int32_t* cu, const int32_t* slots,
                        const int32_t* bt, int max_blocks, const int32_t* ctx, int num_decode, int B, int N, int max_seqlen,
                        int32_t* out) {
@@ -63,6 +69,12 @@ static void check_step(nvc_runner* r, const int32_t* ids, const int32_t* pos, co
     }
     out[b] = (ids[cu[b + 1] - 1] + 1) % r->vocab;
   }
+  for (int i = 0; i < N; ++i)
+    if (slots[i] >= 0) g_kv[(size_t)slots[i]] = {ids[i], pos[i]};
+  if (bt)
+    for (int b = 0; b < B; ++b)
+      for (int p = 0; p < ctx[b]; ++p)
+        REQUIRE(g_kv[(size_t)bt[(size_t)b * max_blocks + p / r->bs] * r->bs + p % r->bs].second == p);
 }
 
 extern "C" {
@@ -224,6 +236,7 @@ int main(int argc, char** argv) {
       continue;
     }
     ++created;
+    g_kv.assign((size_t)cfg.num_kvcache_blocks * cfg.kvcache_block_size, {-1, -1});
     if (rng() % 3 == 0) nvc_engine_set_sampling(e, 1, rng());
     struct Req { int64_t id; std::vector<int32_t> prompt; int max_tokens; bool ignore_eos; };
     std::vector<Req> reqs;
@@ -278,6 +291,23 @@ int main(int argc, char** argv) {
           }
           for (int i = 0; i < nt; ++i)
             if (slots[i] >= 0) REQUIRE(owners[(size_t)(slots[i] / cfg.kvcache_block_size)] == 1);
+          if (with_runner)                                           // whoever scheduled is assumed to run the model
+            for (int i = 0; i < nt; ++i)
+              if (slots[i] >= 0) g_kv[(size_t)slots[i]] = {ids[i], pos[i]};
+          if (op == 7 && with_runner) {
+            // the hand-made step knows the sequences: the cache must hold exactly their tokens
+            for (int b = 0; b < info.num_seqs && bt && clean; ++b) {
+              const Req* rq = nullptr;
+              for (auto& q : reqs) if (q.id == sid[b]) rq = &q;
+              REQUIRE(rq != nullptr);
+              for (int p = 0; p < ctx[b]; ++p) {
+                const int np = (int)rq->prompt.size();
+                const int32_t want = p < np ? rq->prompt[(size_t)p] : (rq->prompt.back() + 1 + (p - np)) % 64;
+                const auto& cell = g_kv[(size_t)bt[(size_t)b * info.max_blocks + p / cfg.kvcache_block_size] * cfg.kvcache_block_size + p % cfg.kvcache_block_size];
+                REQUIRE(cell.first == want && cell.second == p);
+              }
+            }
+          }
           if (op == 7) {
             std::vector<int32_t> next((size_t)info.num_seqs);
             for (int b = 0; b < info.num_seqs; ++b) {

@@ -275,22 +275,26 @@ int main(int argc, char** argv) {
           if (bt && info.max_blocks) for (int i = 0; i < info.num_seqs * info.max_blocks; ++i) touched += bt[i];
           for (int b = 0; b < info.num_seqs; ++b) touched += emit[b] + sid[b];
           checked += touched != -1;
-          // a block that receives K / V in this step belongs to exactly one live sequence (blocks shared through
-          // the prefix cache are complete and never written again); block tables never hold a block twice
-          std::vector<int> owners((size_t)cfg.num_kvcache_blocks, 0);
-          for (auto& rq : reqs) {
+          // a block that receives K / V in this step is written by exactly one sequence of the batch and sits in that
+          // sequence's block table (others may hold it as a cached prefix: upstream registers a block's hash at
+          // allocation, so a prompt admitted in the same prefill step may already share it - its attention reads it
+          // after this step's K / V scatter); block tables never hold a block twice
+          std::vector<int> writer((size_t)cfg.num_kvcache_blocks, -1);
+          for (int b2 = 0; b2 < info.num_seqs; ++b2) {
             std::vector<int32_t> tbl((size_t)cfg.num_kvcache_blocks + 1);
             int nb = 0;
-            REQUIRE(nvc_engine_seq_block_table(e, rq.id, tbl.data(), (int)tbl.size(), &nb) == 0);
+            REQUIRE(nvc_engine_seq_block_table(e, sid[b2], tbl.data(), (int)tbl.size(), &nb) == 0);
             std::set<int32_t> own(tbl.begin(), tbl.begin() + nb);
             REQUIRE((int)own.size() == nb);
-            for (int32_t b : own) {
-              REQUIRE(b >= 0 && b < cfg.num_kvcache_blocks);
-              ++owners[(size_t)b];
+            const int lo = info.is_prefill ? cu[b2] : b2, hi = info.is_prefill ? cu[b2 + 1] : b2 + 1;
+            for (int i = lo; i < hi; ++i) {
+              if (slots[i] < 0) continue;
+              const int32_t blk = slots[i] / cfg.kvcache_block_size;
+              REQUIRE(own.count(blk) == 1);
+              REQUIRE(writer[(size_t)blk] == -1 || writer[(size_t)blk] == b2);
+              writer[(size_t)blk] = b2;
             }
           }
-          for (int i = 0; i < nt; ++i)
-            if (slots[i] >= 0) REQUIRE(owners[(size_t)(slots[i] / cfg.kvcache_block_size)] == 1);
           if (with_runner)                                           // whoever scheduled is assumed to run the model
             for (int i = 0; i < nt; ++i)
               if (slots[i] >= 0) g_kv[(size_t)slots[i]] = {ids[i], pos[i]};

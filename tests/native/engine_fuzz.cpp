@@ -221,7 +221,7 @@ int main(int argc, char** argv) {
     cfg.max_num_batched_tokens = wild ? pick({-5, 0, 1, 7, 16, 64, 256}) : pick({8, 16, 40, 64, 256});
     cfg.eos = pick({-1, 0, 7});
     cfg.num_kvcache_blocks = wild ? pick({-1, 0, 1, 2, 8, 16}) : pick({2, 3, 8, 16, 40});
-    cfg.kvcache_block_size = wild ? pick({-16, 0, 1, 3, 16, 256}) : pick({1, 3, 16, 16, 256});
+    cfg.kvcache_block_size = wild ? pick({-16, 0, 1, 3, 16, 256}) : pick({2, 3, 16, 16, 256});
     cfg.enable_prefix_caching = rng() % 2;
     cfg.enable_chunked_prefill = rng() % 2;
     nvc_runner runner{cfg.num_kvcache_blocks, cfg.kvcache_block_size, cfg.max_num_seqs, cfg.max_num_batched_tokens, 64};

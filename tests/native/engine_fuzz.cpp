@@ -4,8 +4,9 @@
 // engine -> runner call path (which the Python CPU tests cannot reach: a real runner needs a device) is exercised:
 // the stub checks every step's inputs against the integer contract of SURVEY 8 N1-N3 (slot_mapping, block_tables,
 // context_lens, cu_seqlens) exactly as csrc/runner.cu validates them, and answers next = last token + 1 like
-// DummyModelRunner (llm_engine.rs:20-33).  Random valid and invalid call sequences; any contract violation,
-// sanitizer report or wrong output aborts.
+// DummyModelRunner (llm_engine.rs:20-33).  It also keeps a model of the paged KV cache (g_kv below).  Random valid and
+// invalid call sequences; any contract violation, sanitizer report or wrong output aborts.  test_native_asan.py also
+// builds it against deliberately broken copies of engine.cpp and requires a failure.
 #include <cctype>
 #include <cstdint>
 #include <cstdio>

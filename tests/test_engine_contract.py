@@ -428,7 +428,7 @@ def test_chunked_scheduler_fuzz_against_oracle():
                   suppress_health_check=list(hyp.HealthCheck))
     @hyp.given(st.data())
     def run(data):
-        bs = data.draw(st.sampled_from([16, 32]))
+        bs = data.draw(st.sampled_from([3, 16, 32]))
         max_seqs = data.draw(st.integers(1, 6))
         budget = data.draw(st.integers(max_seqs, 4 * bs))
         nblocks = data.draw(st.integers(8, 40))
@@ -460,7 +460,7 @@ def test_reference_scheduler_fuzz_against_oracle():
                   suppress_health_check=list(hyp.HealthCheck))
     @hyp.given(st.data())
     def run(data):
-        bs = data.draw(st.sampled_from([16, 32]))
+        bs = data.draw(st.sampled_from([3, 16, 32]))
         max_seqs = data.draw(st.integers(1, 6))
         nblocks = data.draw(st.integers(8, 40))
         prefix = data.draw(st.booleans())

@@ -5,10 +5,10 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
         --master-port P bench.py --gpus N --steps K --warmup W
 
-Workload (N = 1): BASELINE.json configs[1] - Qwen3-0.6B bf16, batch 64, 512-token prompts,
-decode with ignore_eos, paged KV cache block size 256, random-init (synthetic seeded) weights.
-A "step" is ONE decode step of the whole batch.  N > 1 runs the same batch tensor-parallel
-(TP = N, one process per GPU, NCCL all-reduce after each row-parallel linear): strong scaling.
+Headline workload: BASELINE.json configs[1] - Qwen3-0.6B bf16, batch 64, 512-token prompts, decode
+with ignore_eos, paged KV cache block size 256, random-init (synthetic seeded) weights.  A "step" is
+ONE decode step of the whole batch.  N > 1 runs the same batch tensor-parallel (TP = N, one process
+per GPU, all-reduce after each row-parallel linear): strong scaling.
 
 One JSON line on stdout (rank 0):
   value     decode tok/s with the step's inputs already resident in HBM (CUDA events on the
@@ -16,6 +16,13 @@ One JSON line on stdout (rank 0):
   e2e       decode tok/s through LLMEngine.step(): host scheduler -> pinned H2D of ids / positions /
             slots / context lens / block tables -> step -> D2H of the sampled tokens, K timed steps
   roofline  the dominant kernel (paged decode attention) against the measured HBM peak
+  parity    AFTER the timed region: sequences of the benchmarked batch, teacher-forced through the
+            fp32 oracle (one full-recompute forward each; every generated token must be within 4e-2
+            of the oracle's best logit at its step), and - under TP - whether all ranks produced the
+            same tokens.  A failed check makes the process exit non-zero.
+  north_star  sub-record: BASELINE.json configs[2]'s decode phase - Qwen3-8B, batch 256, context
+            ~1024, device-generated weights - with its own value / clocks and TWO rooflines (paged
+            decode vs HBM, layer GEMMs vs the bf16 tensor peak, burst and sustained)
   cpu_baseline  the oracle's restatement of the reference algorithm on the host cores (bounded sample)
 
 --impl reference times that CPU restatement alone (the reference crate is Rust + candle and cannot
@@ -41,25 +48,46 @@ BATCH = 64
 PROMPT_LEN = 512
 BLOCK_SIZE = 256
 CPU_SAMPLE_SEQS = 1          # sequences of the batch the CPU legs process per step
+PARITY_SEQS = 2              # sequences of the benchmarked batch checked against the fp32 oracle
+PARITY_TOL = 4e-2            # worst allowed logit deficit of a generated token (same as tests/test_e2e_gpu.py)
+
+NS_MODEL = "qwen3-8b"        # north-star sub-record (BASELINE.json configs[2], decode phase)
+NS_BATCH = 256
+NS_PROMPT_LEN = 1000         # + warm-up + timed steps = context ~1024 at timing
 
 
-def _ncu_traffic():
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the paged decode kernel on this
-    workload, from the committed `ncu --set full` capture (profiles/paged_decode_ncu_traffic.json,
-    written by tools/ncu_summarize.py); None if no capture has been committed."""
+def _ncu_traffic(batch: int, kv_local: int, ctx_len: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the paged decode kernel from the
+    committed `ncu --set full` capture (profiles/paged_decode_ncu_traffic.json, written by
+    tools/ncu_summarize.py) - but only when that capture was taken on THIS run's shape (batch, kv heads
+    per rank, context length); otherwise None: a capture of another shape is not evidence for this run."""
     p = os.path.join(ROOT, "profiles", "paged_decode_ncu_traffic.json")
     try:
-        return float(json.load(open(p))["dram_bytes_per_launch"])
+        d = json.load(open(p))
+        if (int(d["batch"]), int(d["kv_heads_local"]), int(d["context_len"])) != (batch, kv_local, ctx_len):
+            return None
+        return float(d["dram_bytes_per_launch"])
     except Exception:
         return None
 
 
-def _peaks():
+def _peaks() -> dict:
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         d = json.load(open(p))
-        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-    return 6650.0, "fallback (B200_PROFILING.md)"
+        return {"hbm_gbs": float(d["hbm_gbs"]), "bf16_burst": float(d["bf16_tflops"]),
+                "bf16_sustained": float(d.get("bf16_tflops_sustained", d["bf16_tflops"])),
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def _host_threads() -> int:
+    """All host cores for the CPU legs, whatever the launcher put into OMP_NUM_THREADS
+    (torch.distributed.run sets it to 1 for every rank)."""
+    import torch
+    n = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    torch.set_num_threads(max(1, n))
+    return torch.get_num_threads()
 
 
 class ClockSampler:
@@ -104,9 +132,17 @@ class ClockSampler:
 
 
 # --------------------------------------------------------------------------------------------
-# CPU restatement of the reference (oracle/) - the ONLY place bench.py touches oracle/
+# CPU restatement of the reference (oracle/) - the ONLY place bench.py touches oracle/: as the
+# checker of the finished run (parity) and as the timed CPU baseline, never inside a GPU-timed region
 # --------------------------------------------------------------------------------------------
-def cpu_reference_decode(steps: int, warmup: int, sample_seqs: int):
+def _oracle_model():
+    from oracle import qwen3_oracle as O
+    synth = importlib.import_module("nano-vllm-candle_b200.synth")
+    cfg = O.MODEL_CONFIGS[MODEL]
+    return O.Qwen3Oracle(cfg, {k: v.float() for k, v in synth.iter_weights(cfg, 0)}, "fp32")
+
+
+def cpu_reference_decode(steps: int, warmup: int, sample_seqs: int, model=None):
     """The reference's algorithm for one decode step (src/engine/llm_engine.rs:146-189): right-padded
     [B, T] batch, FULL forward of every sequence, logits at all positions, host argmax; fp32, all host
     threads.  Returns (tok/s, threads, seconds per step)."""
@@ -114,9 +150,9 @@ def cpu_reference_decode(steps: int, warmup: int, sample_seqs: int):
     from oracle import qwen3_oracle as O
     from oracle.engine_oracle import OracleModelRunner, SamplingParams, Sequence
     synth = importlib.import_module("nano-vllm-candle_b200.synth")
+    threads = _host_threads()
     cfg = O.MODEL_CONFIGS[MODEL]
-    w = {k: v.float() for k, v in synth.iter_weights(cfg, 0)}
-    model = O.Qwen3Oracle(cfg, w, "fp32")
+    model = model or _oracle_model()
     runner = OracleModelRunner(model, cfg.eos_token_id)
     prompts = synth.make_prompts(BATCH, PROMPT_LEN, cfg.vocab_size, 2)[:sample_seqs]
     seqs = [Sequence(p + [p[-1]], SamplingParams(1.0, 10 ** 6, True)) for p in prompts]   # ctx 513 = first decode step
@@ -129,10 +165,10 @@ def cpu_reference_decode(steps: int, warmup: int, sample_seqs: int):
             for s, t in zip(seqs, runner.run(seqs, False)):
                 s.append_token(t)
         dt = time.perf_counter() - t0
-    return sample_seqs * steps / dt, torch.get_num_threads(), dt / steps
+    return sample_seqs * steps / dt, threads, dt / steps
 
 
-def cpu_kv_cached_decode(steps: int):
+def cpu_kv_cached_decode(steps: int, model=None):
     """The same fp32 arithmetic on the same host cores WITH a KV cache and last-token logits
     (oracle.Qwen3OracleKVCached - not the reference's algorithm): one sequence, 512-token prompt prefilled once
     (untimed), `steps` timed single-token decode steps.  Separates the algorithmic speed-up (what a KV cache buys
@@ -140,8 +176,9 @@ def cpu_kv_cached_decode(steps: int):
     import torch
     from oracle import qwen3_oracle as O
     synth = importlib.import_module("nano-vllm-candle_b200.synth")
+    _host_threads()
     cfg = O.MODEL_CONFIGS[MODEL]
-    model = O.Qwen3Oracle(cfg, {k: v.float() for k, v in synth.iter_weights(cfg, 0)}, "fp32")
+    model = model or _oracle_model()
     prompt = synth.make_prompts(BATCH, PROMPT_LEN, cfg.vocab_size, 2)[0]
     with torch.no_grad():
         inc = O.Qwen3OracleKVCached(model, PROMPT_LEN + steps + 2)
@@ -152,6 +189,28 @@ def cpu_kv_cached_decode(steps: int):
             tok = O.argmax_last(inc.step([tok]).numpy())
         dt = time.perf_counter() - t0
     return steps / dt
+
+
+def oracle_parity(model, prompts, generated) -> dict:
+    """Teacher-forced greedy consistency of sequences the benchmarked engine generated: the oracle
+    (reference algorithm: dense causal full recompute, fp32) runs each sequence once and every generated
+    token must be within PARITY_TOL of the oracle's best logit at its step."""
+    import torch
+    from oracle import qwen3_oracle as O
+    _host_threads()
+    worst, exact, total = 0.0, 0, 0
+    with torch.no_grad():
+        for p, g in zip(prompts, generated):
+            ids = torch.tensor([list(p) + list(g[:-1])])
+            hidden = model.forward(ids)[:, len(p) - 1:]                 # positions that predict the generated tokens
+            logits = model.compute_logits(hidden)[0]
+            for i, t in enumerate(g):
+                row = logits[i]
+                worst = max(worst, float(row.max() - row[t]))
+                exact += int(O.argmax_last(row.numpy()) == t)
+                total += 1
+    return {"seqs": len(prompts), "tokens_checked": total, "tokens_exact_argmax": exact,
+            "worst_logit_deficit": worst, "tolerance": PARITY_TOL}
 
 
 def run_reference(args):
@@ -178,138 +237,216 @@ def _config(n_gpus: int) -> dict:
     return {"workload": f"{MODEL} bf16 decode, batch {BATCH}, {PROMPT_LEN}-token prompts, ignore_eos, paged KV block "
                         f"{BLOCK_SIZE} (BASELINE.json configs[1])",
             "parallelism": f"tp{n_gpus}", "global_batch": BATCH, "prompt_len": PROMPT_LEN,
+            "cpu_sample_seqs": CPU_SAMPLE_SEQS,
             "l2": "per-step working set (weights 1.5 GB + KV 4+ GB) is far larger than the 126 MB L2"}
 
 
 # --------------------------------------------------------------------------------------------
 # the product arm
 # --------------------------------------------------------------------------------------------
-def run_ours(args):
-    import numpy as np
-    import torch
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run --nproc-per-node N")
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
-    torch.cuda.set_device(local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    ops = importlib.import_module("nano-vllm-candle_b200.ops")
-    eng = importlib.import_module("nano-vllm-candle_b200.engine")
-    synth = importlib.import_module("nano-vllm-candle_b200.synth")
+class _Env:
+    """What every measurement of this process shares: device, ranks, library context."""
 
-    ctx = ops.Context(local, rank, world)
-    if world > 1:
-        ctx.init_tp(dist)                  # NCCL communicator + NVLink peer buffers
-    cfg = eng.MODEL_CONFIGS[MODEL]
-    K, W = args.steps, args.warmup
-    total_len = PROMPT_LEN + W + K + 16
+    def __init__(self, args):
+        import torch
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world != args.gpus and self.world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run --nproc-per-node N")
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py needs a CUDA device: the hot path has no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+            self.dist = dist
+        self.ops = importlib.import_module("nano-vllm-candle_b200.ops")
+        self.eng = importlib.import_module("nano-vllm-candle_b200.engine")
+        self.synth = importlib.import_module("nano-vllm-candle_b200.synth")
+        self.ctx = self.ops.Context(self.local, self.rank, self.world)
+        if self.world > 1:
+            self.ctx.init_tp(self.dist)        # NCCL communicator + NVLink peer / multicast buffers
+        self.peaks = _peaks()
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, vals):
+        if self.dist is None:
+            return [float(v) for v in vals]
+        t = self.torch.tensor(list(vals), device="cuda", dtype=self.torch.float64)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(x) for x in t]
+
+
+def measure(env: _Env, model: str, batch: int, prompt_len: int, K: int, W: int, device_weights: bool,
+            max_batched_tokens: int, keep_outputs: int = 0) -> dict:
+    """Prefill the batch, warm up, time K decode steps through the engine (e2e) and K replays of the
+    captured step (device), then each kernel family alone.  Returns the pieces of a bench record."""
+    eng, synth, ctx, torch = env.eng, env.synth, env.ctx, env.torch
+    world = env.world
+    cfg = eng.MODEL_CONFIGS[model]
+    W = max(W, 3)
+    total_len = prompt_len + 16 + W + K + 16          # head-room for the extra prefill steps of a split batch
     blocks_per_seq = -(-total_len // BLOCK_SIZE)
-    nblocks = BATCH * blocks_per_seq + 8
+    nblocks = batch * blocks_per_seq + 8
     t0 = time.perf_counter()
+    weights = (synth.iter_weights_device(cfg, 0, device=f"cuda:{env.local}") if device_weights
+               else synth.iter_weights(cfg, 0))
     runner = eng.Qwen3ModelRunner.from_weights(
-        ctx, cfg, synth.iter_weights(cfg, 0), num_kvcache_blocks=nblocks, kvcache_block_size=BLOCK_SIZE,
-        max_num_seqs=BATCH, max_num_batched_tokens=BATCH * PROMPT_LEN, max_model_len=blocks_per_seq * BLOCK_SIZE)
+        ctx, cfg, weights, num_kvcache_blocks=nblocks, kvcache_block_size=BLOCK_SIZE, max_num_seqs=batch,
+        max_num_batched_tokens=max_batched_tokens, max_model_len=blocks_per_seq * BLOCK_SIZE)
+    torch.cuda.empty_cache()
     t_load = time.perf_counter() - t0
-    engine = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(BATCH, BATCH * PROMPT_LEN, cfg.eos_token_id, nblocks,
-                                                             BLOCK_SIZE)), runner)
-    prompts = synth.make_prompts(BATCH, PROMPT_LEN, cfg.vocab_size, 2)
-    # untimed warm-up: two short sequences through prefill + one decode step (module load, NCCL
-    # connection setup, first-launch costs), finished and freed before the timed batch is queued
-    for p in prompts[:2]:
-        engine.add_request(p[:64], eng.SamplingParams(1.0, 2, True))
+    engine = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(batch, max_batched_tokens, cfg.eos_token_id, nblocks,
+                                                             BLOCK_SIZE)), runner, greedy=True)
+    prompts = synth.make_prompts(batch, prompt_len, cfg.vocab_size, 2)
+    # untimed warm-up: the first prompts through a full-size prefill step + one decode step (module load,
+    # first-launch costs, NCCL channel set-up at the prefill message size), finished and freed before the
+    # timed batch is queued
+    n_warm = max(1, min(batch, max_batched_tokens // prompt_len))
+    for p in prompts[:n_warm]:
+        engine.add_request(p, eng.SamplingParams(1.0, 2, True))
     while not engine.is_finished():
         engine.step()
-    sp = eng.SamplingParams(1.0, W + K + 8, True)
-    for p in prompts:
-        engine.add_request(p, sp)
+    sp = eng.SamplingParams(1.0, 16 + W + K + 8, True)
+    sids = [engine.add_request(p, sp) for p in prompts]
 
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- prefill (one step over 64 x 512 tokens), reported as an extra
-    barrier()
+    # ---- prefill (as many steps as max_num_batched_tokens needs), reported as an extra
+    env.barrier()
     t0 = time.perf_counter()
-    s = engine.step()
-    barrier()
+    n_prefill_steps = 0
+    while True:
+        s = engine.step()
+        assert s.is_prefill
+        n_prefill_steps += 1
+        if engine.num_waiting() == 0:
+            break
+    env.barrier()
     t_prefill = time.perf_counter() - t0
-    assert s.is_prefill
     # ---- warm-up decode steps (also captures the CUDA graph)
-    for _ in range(max(W, 3)):
+    for _ in range(W):
         s = engine.step()
         assert not s.is_prefill
     # ---- e2e: K decode steps through the public API, host buffers, H2D + D2H inside
-    sampler = ClockSampler(local)
-    l0 = ctx.l.nvc_ctx_launch_count(ctx.h)
-    barrier()
+    sampler = ClockSampler(env.local)
+    env.barrier()
     sampler.start()
     t0 = time.perf_counter()
     for _ in range(K):
         engine.step()
-    barrier()
+    env.barrier()
     t_e2e = time.perf_counter() - t0
     # ---- device-resident: replay the step K times with inputs already in HBM (CUDA events)
     ms_step, launches_per_step = runner.time_decode(K)
-    barrier()
+    env.barrier()
     clocks = sampler.stop()
-    if dist is not None:
-        t = torch.tensor([t_e2e, ms_step], device="cuda", dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t_e2e, ms_step = float(t[0]), float(t[1])
+    t_e2e, ms_step, t_prefill = env.max_over_ranks([t_e2e, ms_step, t_prefill])
 
-    # ---- per-kernel timing (each family over all 28 layers' own weights / KV pools)
-    ctx_len = PROMPT_LEN + max(W, 3) + K
+    # ---- per-kernel timing (each family over all layers' own weights / KV pools)
+    ctx_len = prompt_len + W + K         # context of the last timed step (every sequence: same prompt length)
     nh_l, kv_l = cfg.num_attention_heads // world, cfg.num_key_value_heads // world
     breakdown = {}
     # gemm_gate_up includes the fused SiLU-mul epilogue (K3 + K6 in one kernel)
-    ops_list = ["paged_decode", "gemm_qkv", "gemm_o", "gemm_gate_up", "gemm_down", "rmsnorm", "qk_norm_rope",
-                "lm_head", "argmax", "noop"] + (["allreduce"] if world > 1 else [])
+    ops_list = [op for op in ("paged_decode", "gemm_qkv", "gemm_o", "gemm_gate_up", "gemm_down", "rmsnorm", "qk_norm_rope",
+                              "lm_head", "argmax", "noop") if op in runner.OPS] + (["allreduce"] if world > 1 else [])
     for op in ops_list:
         ms, _ = runner.time_op(op, 5)
         breakdown[op + "_us"] = round(ms * 1e3, 2)
-    attn_bytes = BATCH * ctx_len * 2 * kv_l * 128 * 2 + 2 * BATCH * nh_l * 128 * 2     # K+V once per kv head, q in, out
-    peak, peak_src = _peaks()
-    attn_s = breakdown["paged_decode_us"] * 1e-6
-    achieved = attn_bytes / attn_s / 1e9
-    L = cfg.num_hidden_layers
-    per_layer = sum(breakdown[k] for k in ("paged_decode_us", "gemm_qkv_us", "gemm_o_us", "gemm_gate_up_us",
-                                           "gemm_down_us", "qk_norm_rope_us")) + 2 * breakdown["rmsnorm_us"]
+    attn_bytes = batch * ctx_len * 2 * kv_l * 128 * 2 + 2 * batch * nh_l * 128 * 2     # K+V once per kv head, q in, out
+    pk = env.peaks
+    achieved = attn_bytes / (breakdown["paged_decode_us"] * 1e-6) / 1e9
+    L, H, I = cfg.num_hidden_layers, cfg.hidden_size, cfg.intermediate_size
+    layer_params = (H * (cfg.num_attention_heads + 2 * cfg.num_key_value_heads) * 128 + cfg.num_attention_heads * 128 * H
+                    + 3 * H * I) // world
+    gemm_us = sum(breakdown[k] for k in ("gemm_qkv_us", "gemm_o_us", "gemm_gate_up_us", "gemm_down_us"))
+    gemm_tflops = 2.0 * batch * layer_params / gemm_us / 1e6
     if world > 1:
-        per_layer += 2 * breakdown["allreduce_us"]
         breakdown["allreduce_exposed_ms_per_step"] = round(2 * L * breakdown["allreduce_us"] / 1e3, 3)
-    breakdown["sum_of_kernels_ms"] = round((per_layer * L + breakdown["lm_head_us"] + breakdown["argmax_us"]) / 1e3, 3)
     breakdown["paged_decode_share_of_step"] = round(breakdown["paged_decode_us"] * L / 1e3 / ms_step, 3)
-    step_bytes = runner.weight_bytes() - 2 * cfg.vocab_size * cfg.hidden_size + L * attn_bytes   # embed table is gathered, not streamed
-
-    cap = blocks_per_seq
-    line = {
-        "metric": "decode tok/s", "value": BATCH / (ms_step * 1e-3), "unit": "tok/s", "n_gpus": world, "steps": K,
-        "warmup": max(W, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
-        "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": _config(world), "clocks": clocks,
-        "e2e": {"value": BATCH * K / t_e2e, "unit": "tok/s", "ms_per_step": t_e2e / K * 1e3,
-                "h2d_bytes_per_step": BATCH * 4 * 4 + BATCH * cap * 4, "d2h_bytes_per_step": BATCH * 4},
+    step_bytes = runner.weight_bytes() - 2 * cfg.vocab_size * H + L * attn_bytes   # embed table is gathered, not streamed
+    outputs = [engine.output_of(sid)[0] for sid in sids] if keep_outputs else []
+    rec = {
+        "value": batch / (ms_step * 1e-3), "ms_per_step": ms_step, "clocks": clocks,
+        "e2e": {"value": batch * K / t_e2e, "unit": "tok/s", "ms_per_step": t_e2e / K * 1e3,
+                "h2d_bytes_per_step": runner.h2d_bytes_last_step(), "d2h_bytes_per_step": batch * 4},
         "gpu_launches": launches_per_step * K,
-        "roofline": {"kernel": "pdmma::paged_decode_mma_kernel (K5)", "bound": "hbm", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": _ncu_traffic(), "peak_source": peak_src,
+        "roofline": {"kernel": "pdmma::paged_decode_mma_kernel (K5)", "bound": "hbm", "achieved": achieved,
+                     "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],
+                     "traffic": _ncu_traffic(batch, kv_l, ctx_len), "peak_source": pk["source"] + " hbm_gbs",
                      "algorithmic_bytes_per_launch": attn_bytes, "us_per_launch": breakdown["paged_decode_us"],
-                     "whole_step_hbm_frac": step_bytes / (ms_step * 1e-3) / 1e9 / peak},
+                     "whole_step_hbm_frac": step_bytes / (ms_step * 1e-3) / 1e9 / pk["hbm_gbs"]},
+        "roofline_layer_gemms": {
+            "kernels": "qkv + o_proj + gate_up(+SiLU-mul) + down of one layer (K3), timed back to back over all layers' weights",
+            "bound": "tensor" if batch >= 256 else "hbm (weights) below M ~ 213; tensor fraction shown for reference",
+            "achieved": gemm_tflops, "unit": "TFLOP/s", "us_per_layer": round(gemm_us, 2),
+            "peak": pk["bf16_burst"], "frac": gemm_tflops / pk["bf16_burst"],
+            "peak_sustained": pk["bf16_sustained"], "frac_of_sustained": gemm_tflops / pk["bf16_sustained"],
+            "weights_gbs": layer_params * 2 / gemm_us / 1e3, "weights_frac_of_hbm": layer_params * 2 / gemm_us / 1e3 / pk["hbm_gbs"],
+            "peak_source": pk["source"] + " bf16_tflops (burst: the GEMMs are timed alone) / bf16_tflops_sustained"},
         "breakdown": breakdown,
-        "prefill": {"tokens": BATCH * PROMPT_LEN, "tok_per_s": BATCH * PROMPT_LEN / t_prefill, "ms": t_prefill * 1e3},
+        "prefill": {"tokens": batch * prompt_len, "steps": n_prefill_steps, "tok_per_s": batch * prompt_len / t_prefill,
+                    "ms": t_prefill * 1e3},
         "context_len_at_timing": ctx_len, "kernels_per_step": launches_per_step, "weights_load_s": round(t_load, 1),
     }
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        runner.close()
-        toks, threads, sec = cpu_reference_decode(2, 1, CPU_SAMPLE_SEQS)
-        kv_toks = cpu_kv_cached_decode(16)
+    engine.close()
+    runner.close()
+    torch.cuda.empty_cache()
+    return rec, prompts, outputs
+
+
+def run_ours(args):
+    env = _Env(args)
+    K, W = args.steps, args.warmup
+    rec, prompts, outputs = measure(env, MODEL, BATCH, PROMPT_LEN, K, W, device_weights=False,
+                                    max_batched_tokens=BATCH * PROMPT_LEN, keep_outputs=PARITY_SEQS)
+    line = {
+        "metric": "decode tok/s", "value": rec.pop("value"), "unit": "tok/s", "n_gpus": env.world, "steps": K,
+        "warmup": max(W, 3), "ms_per_step": rec.pop("ms_per_step"), "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": _config(env.world),
+    }
+    line.update(rec)
+
+    # ---- parity of what was just timed (outside every timed region)
+    parity = {"ok": False}
+    ranks_agree = True
+    if env.dist is not None:
+        allo = [None] * env.world
+        env.dist.all_gather_object(allo, outputs)
+        ranks_agree = all(o == allo[0] for o in allo)
+    model = None
+    if env.rank == 0:
+        pick = [0, BATCH - 1][:PARITY_SEQS]
+        model = _oracle_model()
+        parity = oracle_parity(model, [prompts[i] for i in pick], [outputs[i] for i in pick])
+        parity["batch_rows"] = pick
+        parity["ranks_agree"] = ranks_agree
+        parity["ranks_compared"] = env.world
+        parity["ok"] = bool(parity["worst_logit_deficit"] <= PARITY_TOL and ranks_agree and parity["tokens_checked"] > 0)
+    line["parity"] = parity
+
+    # ---- north-star sub-record: Qwen3-8B, batch 256, context ~1024 (own clocks, two rooflines)
+    if not args.no_north_star:
+        try:
+            ns, _, _ = measure(env, NS_MODEL, NS_BATCH, NS_PROMPT_LEN, min(K, 16), W, device_weights=True,
+                               max_batched_tokens=32 * 1024)
+            ns = {"workload": f"{NS_MODEL} bf16 decode, batch {NS_BATCH}, {NS_PROMPT_LEN}-token prompts, paged KV block "
+                              f"{BLOCK_SIZE}, device-generated weights (BASELINE.json configs[2], decode phase; targets: paged "
+                              f"decode >= 0.70 of HBM, GEMMs >= 0.60 of bf16 peak)",
+                  "metric": "decode tok/s", "unit": "tok/s", "steps": min(K, 16), "parallelism": f"tp{env.world}", **ns}
+        except Exception as ex:                       # the headline stands on its own
+            ns = {"error": f"{type(ex).__name__}: {ex}"}
+        line["north_star"] = ns
+
+    if env.rank == 0 and env.world == 1 and not args.no_cpu_baseline:
+        toks, threads, sec = cpu_reference_decode(2, 1, CPU_SAMPLE_SEQS, model)
+        kv_toks = cpu_kv_cached_decode(16, model)
         line["cpu_baseline_kv_cached"] = {
             "value": kv_toks, "unit": "tok/s", "cores": threads, "kind": "port",
             "sample": "16 single-token decode steps of 1 sequence at context 514+, same fp32 arithmetic with a KV cache "
@@ -318,11 +455,19 @@ def run_ours(args):
             "value": toks, "unit": "tok/s", "cores": threads, "kind": "port",
             "sample": f"2 decode steps (after 1 warm-up) of {CPU_SAMPLE_SEQS} of the {BATCH} sequences at context "
                       f"{PROMPT_LEN + 1}+, reference algorithm (full recompute per step), fp32, {sec:.1f} s/step"}
-    if rank == 0:
+    ok = True
+    if env.rank == 0:
         _emit(line)
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+        ok = parity["ok"]
+    if env.dist is not None:
+        flag = [ok]
+        env.dist.broadcast_object_list(flag, src=0)
+        ok = flag[0]
+        env.dist.barrier()
+        env.dist.destroy_process_group()
+    if not ok:
+        sys.stderr.write("bench.py: PARITY FAILED: " + json.dumps(parity) + "\n")
+        sys.exit(3)
 
 
 _OUT = None
@@ -348,6 +493,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-north-star", action="store_true", help="skip the Qwen3-8B batch-256 sub-record")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

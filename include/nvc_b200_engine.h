@@ -68,6 +68,8 @@ int nvc_runner_finalize(nvc_runner* r);
 
 /* ---- native HF checkpoint loading (host side; error text in nvc_hf_last_error, thread-local) ---- */
 const char* nvc_hf_last_error(void);
+/* Non-fatal notes of the last nvc_runner_load_hf_dir on this thread (tensors the model does not use were skipped). */
+const char* nvc_hf_last_warning(void);
 /* Qwen3Config::from_hf_dir (src/models/qwen3.rs:77-101): <model_dir>/config.json, same required
  * fields, head_dim defaults to hidden_size / num_attention_heads, rope_theta to 1e6.
  * *tie_word_embeddings (optional) = that flag of config.json (absent = 0). */
@@ -76,7 +78,9 @@ int nvc_qwen3_config_from_hf_dir(const char* model_dir, nvc_qwen3_config* out, i
  * model.safetensors, or every shard named by model.safetensors.index.json, through mmap; BF16 is
  * handed over as is, F16 / F32 are rounded to bf16 (nearest even) on the host; every tensor goes
  * through nvc_runner_load_weight; a checkpoint without lm_head.weight uses embed_tokens (tied
- * embeddings; the reference fails there, :525-528); ends with nvc_runner_finalize. */
+ * embeddings; the reference fails there, :525-528); ends with nvc_runner_finalize.  Like the reference's
+ * VarBuilder it takes only the tensors the model names: others are skipped (nvc_hf_last_warning); shard names of
+ * the index must be plain file names inside model_dir; overlapping data_offsets are refused. */
 int nvc_runner_load_hf_dir(nvc_runner* r, const char* model_dir);
 /* safetensors inspection (what the loader sees), also used by the CPU tests. */
 typedef struct nvc_safetensors nvc_safetensors;
@@ -138,6 +142,10 @@ enum {
   NVC_OP_NOOP = 10, NVC_OP_ALLREDUCE = 11
 };
 int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_per_launch, int* launches);
+/* The options the runner was created with (nvc_engine_create checks its scheduler config against them). */
+int nvc_runner_get_options(const nvc_runner* r, nvc_runner_options* out);
+/* Host-to-device bytes the last step copied (ids / positions / slots / context lens / block-table rows). */
+int64_t nvc_runner_h2d_bytes_last_step(const nvc_runner* r);
 int64_t nvc_runner_weight_bytes(const nvc_runner* r);
 int64_t nvc_runner_kv_bytes_per_token(const nvc_runner* r);
 
@@ -158,7 +166,10 @@ typedef struct nvc_scheduler_config {
                                       split over steps; max_num_seqs bounds ALL running sequences and the budget
                                       counts only tokens actually computed (the two scheduler.rs quirks fixed).
                                       Needs max_num_batched_tokens >= max_num_seqs.                             */
-  int32_t reserved[2];
+  int32_t max_model_len;           /* longest sequence (prompt + completion) the runner holds; a sequence that reaches it
+                                      finishes like one that reached max_tokens, a longer prompt is refused by
+                                      nvc_engine_add_request.  0 = take the runner's (no limit without a runner).    */
+  int32_t reserved[1];
 } nvc_scheduler_config;
 
 typedef struct nvc_schedule_info {
@@ -184,7 +195,13 @@ typedef struct nvc_step_output {
 } nvc_step_output;
 
 /* runner may be NULL: the engine then behaves like DummyModelRunner (next = last_token + 1,
- * src/engine/llm_engine.rs:20-33). */
+ * src/engine/llm_engine.rs:20-33).  With a runner the scheduler config must agree with the runner's options:
+ * the block size must be equal and num_kvcache_blocks must not exceed the runner's pool (NVC_EINVAL otherwise: a
+ * mismatch would read the wrong KV rows); num_kvcache_blocks == 0 and max_model_len == 0 take the runner's values;
+ * max_num_seqs / max_num_batched_tokens / max_model_len are clamped to what the runner can execute.
+ * When a runner step fails, nvc_engine_step returns its status AFTER rolling the batch back: its sequences go back
+ * to the waiting queue as if preempted and the prefix-cache entries of their blocks are dropped (their K / V were
+ * never written), so the caller may retry or continue. */
 int nvc_engine_create(const nvc_scheduler_config* cfg, nvc_runner* runner, nvc_engine** out);
 int nvc_engine_destroy(nvc_engine* e);
 const char* nvc_engine_last_error(const nvc_engine* e);

@@ -22,7 +22,8 @@ class RunnerOptionsC(C.Structure):
 class SchedulerConfigC(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("max_num_seqs", "max_num_batched_tokens", "eos",
                                          "num_kvcache_blocks", "kvcache_block_size",
-                                         "enable_prefix_caching", "enable_chunked_prefill")] + [("reserved", C.c_int32 * 2)]
+                                         "enable_prefix_caching", "enable_chunked_prefill", "max_model_len")] + \
+               [("reserved", C.c_int32 * 1)]
 
 
 class ScheduleInfoC(C.Structure):
@@ -57,6 +58,7 @@ def declare(l: C.CDLL) -> None:
         "nvc_runner_last_logits": [_vp, _vp, _i],
         "nvc_runner_time_decode": [_vp, _i, C.POINTER(C.c_float), C.POINTER(C.c_int)],
         "nvc_runner_time_op": [_vp, _i, _i, C.POINTER(C.c_float), C.POINTER(C.c_int)],
+        "nvc_runner_get_options": [_vp, C.POINTER(RunnerOptionsC)],
         "nvc_engine_create": [C.POINTER(SchedulerConfigC), _vp, C.POINTER(_vp)],
         "nvc_engine_destroy": [_vp],
         "nvc_engine_schedule": [_vp, C.POINTER(ScheduleInfoC)],
@@ -83,10 +85,14 @@ def declare(l: C.CDLL) -> None:
     l.nvc_engine_add_request.restype = _i64
     l.nvc_hf_last_error.argtypes = []
     l.nvc_hf_last_error.restype = C.c_char_p
+    l.nvc_hf_last_warning.argtypes = []
+    l.nvc_hf_last_warning.restype = C.c_char_p
     l.nvc_engine_last_error.argtypes = [_vp]
     l.nvc_engine_last_error.restype = C.c_char_p
     l.nvc_runner_weight_bytes.argtypes = [_vp]
     l.nvc_runner_weight_bytes.restype = _i64
+    l.nvc_runner_h2d_bytes_last_step.argtypes = [_vp]
+    l.nvc_runner_h2d_bytes_last_step.restype = _i64
     l.nvc_runner_kv_bytes_per_token.argtypes = [_vp]
     l.nvc_runner_kv_bytes_per_token.restype = _i64
     l.nvc_ctx_launch_count.argtypes = [_vp]

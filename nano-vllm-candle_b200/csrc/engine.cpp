@@ -175,7 +175,15 @@ struct BlockManager {
       } else {
         ++cache_hits;
         s.num_cached_tokens += bs;
-        if (free_.in[id]) take(id); else blocks[id].ref_count += 1;
+        if (free_.in[id]) {
+          // a free block revived from the cache still holds its K / V: it stays ready (take() clears the flag,
+          // and mark_computed never revisits a cached block, so the next request with this prefix would miss)
+          const bool was_ready = blocks[id].ready;
+          take(id);
+          blocks[id].ready = was_ready;
+        } else {
+          blocks[id].ref_count += 1;
+        }
       }
       if (prefix_caching && has_h) set_hash(id, h, toks, n);
       s.block_table.push_back(id);
@@ -188,6 +196,20 @@ struct BlockManager {
     }
     s.block_table.clear();
     s.num_cached_tokens = 0;
+  }
+  // A step that failed in the runner never wrote the K / V of its sequences: their blocks must not
+  // serve prefix-cache hits.  (A block shared with a sequence outside the batch only loses its cache entry.)
+  void forget_hashes(const Sequence& s) {
+    for (int32_t id : s.block_table) {
+      Block& b = blocks[id];
+      if (b.has_hash) {
+        auto it = hash_to_block.find(b.hash);
+        if (it != hash_to_block.end() && it->second == id) hash_to_block.erase(it);
+      }
+      b.has_hash = false;
+      b.ready = false;
+      b.token_ids.clear();
+    }
   }
   bool can_append(const Sequence& s) const {
     // a block is missing only when the newest token opens one (len % block_size == 1) and the table
@@ -221,6 +243,7 @@ struct Scheduler {
   BlockManager block_manager;
   std::deque<SeqPtr> waiting, running;
   int32_t eos;
+  size_t max_model_len = 0;   // longest sequence the runner can hold (0 = unknown: no limit enforced here)
 
   explicit Scheduler(const nvc_scheduler_config& c)
       : max_num_seqs(c.max_num_seqs), max_num_batched_tokens(c.max_num_batched_tokens),
@@ -364,7 +387,10 @@ struct Scheduler {
   bool process_single(const SeqPtr& seq, int32_t tok) {
     seq->append_token(tok);
     const bool is_eos = tok == eos;
-    const bool reached_max = seq->num_completion_tokens() >= seq->max_tokens;
+    // the appended token sits at position len - 1; the runner holds positions < max_model_len, so a sequence that
+    // has grown past it can not take another decode step: it ends here like one that reached max_tokens
+    const bool reached_max = seq->num_completion_tokens() >= seq->max_tokens ||
+                             (max_model_len > 0 && seq->len() > max_model_len);
     const bool finished = (!seq->ignore_eos && is_eos) || reached_max;
     if (finished) {
       seq->status = Status::Finished;
@@ -519,6 +545,20 @@ int arm_sampling(nvc_engine* e) {
   return nvc_runner_set_sampling(e->runner, e->temps.data(), e->streams.data(), (int)e->batch.size(), e->sampling_seed);
 }
 
+void rollback_failed_step(nvc_engine* e) {
+  auto& run = e->scheduler.running;
+  for (auto it = e->batch.rbegin(); it != e->batch.rend(); ++it) {   // reverse: preempt() pushes to the FRONT of waiting
+    const SeqPtr& seq = *it;
+    auto pos = std::find(run.begin(), run.end(), seq);
+    if (pos == run.end()) continue;
+    run.erase(pos);
+    e->scheduler.block_manager.forget_hashes(*seq);
+    e->scheduler.preempt(seq);
+  }
+  e->batch.clear();
+  e->batch_valid = false;
+}
+
 int do_post_process(nvc_engine* e, const int32_t* toks, int n, int* finished_out) {
   if (!e->batch_valid || n != (int)e->batch.size()) {
     e->err = "post_process: no scheduled batch of that size";
@@ -548,7 +588,23 @@ int nvc_engine_create(const nvc_scheduler_config* cfg, nvc_runner* runner, nvc_e
       cfg->num_kvcache_blocks < 0)
     return NVC_EINVAL;
   if (cfg->enable_chunked_prefill && cfg->max_num_batched_tokens < cfg->max_num_seqs) return NVC_EINVAL;
-  *out = new nvc_engine(*cfg, runner);
+  if (cfg->max_model_len < 0) return NVC_EINVAL;
+  nvc_scheduler_config c = *cfg;
+  if (runner != nullptr) {
+    // The engine's integer contract (slot = block * block_size + offset, block ids < num_kvcache_blocks) is only
+    // meaningful against the pool the runner owns: a different block size would pass the runner's range checks and
+    // read the wrong KV rows.  Sizes the runner cannot execute are clamped instead of failing at the first big step.
+    nvc_runner_options ro;
+    if (nvc_runner_get_options(runner, &ro) != NVC_OK) return NVC_EINVAL;
+    if (c.kvcache_block_size != ro.kvcache_block_size || c.num_kvcache_blocks > ro.num_kvcache_blocks) return NVC_EINVAL;
+    if (c.num_kvcache_blocks == 0) c.num_kvcache_blocks = ro.num_kvcache_blocks;
+    c.max_num_seqs = std::min(c.max_num_seqs, ro.max_num_seqs);
+    c.max_num_batched_tokens = std::min(c.max_num_batched_tokens, ro.max_num_batched_tokens);
+    c.max_model_len = c.max_model_len == 0 ? ro.max_model_len : std::min(c.max_model_len, ro.max_model_len);
+    if (c.enable_chunked_prefill && c.max_num_batched_tokens < c.max_num_seqs) return NVC_EINVAL;
+  }
+  *out = new nvc_engine(c, runner);
+  (*out)->scheduler.max_model_len = (size_t)c.max_model_len;
   return NVC_OK;
 }
 
@@ -567,6 +623,10 @@ int64_t nvc_engine_add_request(nvc_engine* e, const int32_t* token_ids, int n, d
   // query token for the model to run on, so the C ABI refuses it (and a negative max_tokens) up front.
   if (n <= 0 || !token_ids || max_tokens < 0) {
     e->err = n <= 0 || !token_ids ? "empty prompt" : "max_tokens must be >= 0";
+    return NVC_EINVAL;
+  }
+  if (e->scheduler.max_model_len > 0 && (size_t)n > e->scheduler.max_model_len) {
+    e->err = "prompt of " + std::to_string(n) + " tokens exceeds max_model_len " + std::to_string(e->scheduler.max_model_len);
     return NVC_EINVAL;
   }
   if (!(temperature > 1e-10)) {   // sampling_params.rs:20,30
@@ -661,8 +721,12 @@ int nvc_engine_step(nvc_engine* e, nvc_step_output* out) {
                            e->block_tables.data(), e->max_blocks, e->context_lens.data(), B, e->out_tokens.data());
   }
   if (rc) {
-    e->err = "runner step failed";
-    return rc;   // errors propagate; the reference would emit eos for every sequence (llm_engine.rs:153-175)
+    // errors propagate; the reference would emit eos for every sequence (llm_engine.rs:153-175).  The scheduler had
+    // already moved the batch to `running`, allocated and hash-registered its blocks: undo that, or a caller who
+    // continues would decode (and take prefix-cache hits) over K / V that was never written.
+    rollback_failed_step(e);
+    e->err = "runner step failed (the batch was put back on the waiting queue)";
+    return rc;
   }
   const bool is_prefill = e->batch_is_prefill;
   std::vector<SeqPtr> seqs = e->batch;

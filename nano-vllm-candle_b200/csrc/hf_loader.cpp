@@ -14,6 +14,7 @@
 #include <sys/stat.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -255,6 +256,7 @@ struct nvc_safetensors {
 namespace {
 
 thread_local std::string g_hf_error;
+thread_local std::string g_hf_warning;   // non-fatal notes of the last nvc_runner_load_hf_dir (skipped tensors)
 
 int hf_fail(int code, const std::string& msg) {
   g_hf_error = msg;
@@ -353,6 +355,14 @@ int open_safetensors(const std::string& path, std::unique_ptr<nvc_safetensors>& 
       return hf_fail(NVC_EINVAL, path + ": tensor " + kv.first + " is listed twice");
     st->entries.push_back(std::move(e));
   }
+  {   // the format stores tensors back to back: two entries sharing bytes mean a damaged (or hostile) header
+    std::vector<std::pair<uint64_t, uint64_t>> spans;
+    for (auto& e : st->entries)
+      if (e.end > e.begin) spans.emplace_back(e.begin, e.end);
+    std::sort(spans.begin(), spans.end());
+    for (size_t i = 1; i < spans.size(); ++i)
+      if (spans[i].first < spans[i - 1].second) return hf_fail(NVC_EINVAL, path + ": overlapping data_offsets");
+  }
   out = std::move(st);
   return NVC_OK;
 }
@@ -367,6 +377,7 @@ bool file_exists(const std::string& p) {
 extern "C" {
 
 const char* nvc_hf_last_error(void) { return g_hf_error.c_str(); }
+const char* nvc_hf_last_warning(void) { return g_hf_warning.c_str(); }
 
 int nvc_safetensors_open(const char* path, nvc_safetensors** out) {
   if (!path || !out) return hf_fail(NVC_EINVAL, "null pointer");
@@ -422,6 +433,26 @@ bool jnum(const JValue& root, const char* key, double& out) {
   return true;
 }
 
+// The tensors Qwen3ForCausalLM::from_hf_dir fetches (qwen3.rs:146-187,301-314,351-363,431-447,525-528).  The reference's
+// VarBuilder only asks for these names, so anything else in a checkpoint (buffers of other exports) is skipped, with a
+// note in nvc_hf_last_warning(); that every needed tensor arrived is checked by nvc_runner_finalize's count.
+bool is_model_tensor(const std::string& name) {
+  if (name == "model.embed_tokens.weight" || name == "model.norm.weight" || name == "lm_head.weight") return true;
+  static const char* kPrefix = "model.layers.";
+  if (name.compare(0, strlen(kPrefix), kPrefix) != 0) return false;
+  size_t p = strlen(kPrefix), digits = 0;
+  while (p < name.size() && name[p] >= '0' && name[p] <= '9') { ++p; ++digits; }
+  if (digits == 0 || digits > 6 || p >= name.size() || name[p] != '.') return false;
+  static const char* kSub[] = {"self_attn.q_proj.weight", "self_attn.k_proj.weight", "self_attn.v_proj.weight",
+                               "self_attn.o_proj.weight", "self_attn.q_norm.weight", "self_attn.k_norm.weight",
+                               "mlp.gate_proj.weight", "mlp.up_proj.weight", "mlp.down_proj.weight",
+                               "input_layernorm.weight", "post_attention_layernorm.weight"};
+  const std::string sub = name.substr(p + 1);
+  for (const char* k : kSub)
+    if (sub == k) return true;
+  return false;
+}
+
 // names of a safetensors file -> runner, through one pinned-size-agnostic host staging buffer
 int load_file_into_runner(nvc_runner* r, const nvc_safetensors& st, const std::set<std::string>* only,
                           std::set<std::string>& seen, std::vector<uint16_t>& stage) {
@@ -429,6 +460,10 @@ int load_file_into_runner(nvc_runner* r, const nvc_safetensors& st, const std::s
     if (only && !only->count(e.name)) continue;
     static const std::string kInvFreq = "rotary_emb.inv_freq";   // legacy buffer of older exports, not a weight
     if (e.name.size() >= kInvFreq.size() && e.name.compare(e.name.size() - kInvFreq.size(), kInvFreq.size(), kInvFreq) == 0) continue;
+    if (!is_model_tensor(e.name)) {
+      if (g_hf_warning.size() < 2000) g_hf_warning += "skipped unknown tensor " + e.name + " in " + st.path + "; ";
+      continue;
+    }
     if (e.dtype == NVC_ST_OTHER) return hf_fail(NVC_ENOTIMPL, e.name + ": unsupported dtype " + e.dtype_name + " in " + st.path);
     if (e.shape.empty() || e.shape.size() > 2) return hf_fail(NVC_ESHAPE, e.name + ": expected a vector or a matrix");
     const int64_t rows = e.shape[0], cols = e.shape.size() == 2 ? e.shape[1] : 1;
@@ -498,6 +533,7 @@ int nvc_qwen3_config_from_hf_dir(const char* model_dir, nvc_qwen3_config* out, i
 int nvc_runner_load_hf_dir(nvc_runner* r, const char* model_dir) {
   if (!r || !model_dir) return hf_fail(NVC_EINVAL, "null pointer");
   const std::string dir(model_dir);
+  g_hf_warning.clear();
   std::set<std::string> seen;
   std::vector<uint16_t> stage;
   const std::string index = dir + "/model.safetensors.index.json";
@@ -512,6 +548,11 @@ int nvc_runner_load_hf_dir(nvc_runner* r, const char* model_dir) {
     if (!wm || wm->kind != JValue::Obj) return hf_fail(NVC_EINVAL, index + ": no weight_map");
     for (auto& kv : wm->obj) {
       if (kv.second.kind != JValue::Str) return hf_fail(NVC_EINVAL, index + ": weight_map values must be file names");
+      // shard names are joined onto the model directory: a plain file name only, never a path out of it
+      const std::string& fn = kv.second.str;
+      if (fn.empty() || fn.find('/') != std::string::npos || fn.find('\\') != std::string::npos || fn == "." || fn == ".." ||
+          fn.find('\0') != std::string::npos)
+        return hf_fail(NVC_EINVAL, index + ": shard name \"" + fn + "\" is not a plain file name");
       auto it = plan.begin();
       for (; it != plan.end(); ++it)
         if (it->first == kv.second.str) break;

@@ -72,6 +72,7 @@ struct nvc_runner {
   // decode graphs keyed by (B, 2 * blocks hint + sampling)
   std::map<std::pair<int, int>, cudaGraphExec_t> graphs;
   int launches_per_decode = 0;
+  int64_t last_h2d_bytes = 0;      // host-to-device bytes of the last step's inputs
   int last_decode_hint = 0;
   int last_decode_key2 = 0;
 };
@@ -272,7 +273,11 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   NVC_REQUIRE(ctx, cfg->intermediate_size % (tp * 64) == 0, NVC_ESHAPE, "intermediate_size must divide by tp_size*64");
   NVC_REQUIRE(ctx, cfg->vocab_size % (tp * 16) == 0, NVC_ESHAPE, "vocab_size must divide by tp_size*16");
   NVC_REQUIRE(ctx, cfg->hidden_size % 64 == 0, NVC_ESHAPE, "hidden_size must be a multiple of 64");
-  NVC_REQUIRE(ctx, opt->kvcache_block_size > 0 && opt->kvcache_block_size % 16 == 0, NVC_ESHAPE, "block size % 16");
+  // the paged prefill kernel (prefix caching, mixed steps) reads a 64-token kv tile as 64 / block_size boxes or as one
+  // box of a block that is a multiple of 128 tokens: apply its rule here, not at the first cached-prefix step
+  NVC_REQUIRE(ctx, opt->kvcache_block_size == 16 || opt->kvcache_block_size == 32 || opt->kvcache_block_size == 64 ||
+                       (opt->kvcache_block_size > 0 && opt->kvcache_block_size % 128 == 0), NVC_ESHAPE,
+              "kvcache_block_size must be 16, 32, 64 or a multiple of 128");
   NVC_REQUIRE(ctx, opt->allreduce_f32 == 0, NVC_ENOTIMPL, "allreduce_f32 is not implemented");
   NVC_REQUIRE(ctx, opt->num_kvcache_blocks > 0 && opt->max_num_seqs > 0 && opt->max_num_batched_tokens > 0 &&
                        opt->max_model_len > 0, NVC_EINVAL, "bad runner options");
@@ -368,6 +373,12 @@ int nvc_runner_destroy(nvc_runner* r) {
 }
 
 int64_t nvc_runner_weight_bytes(const nvc_runner* r) { return r ? r->weight_bytes : 0; }
+int64_t nvc_runner_h2d_bytes_last_step(const nvc_runner* r) { return r ? r->last_h2d_bytes : 0; }
+int nvc_runner_get_options(const nvc_runner* r, nvc_runner_options* out) {
+  if (!r || !out) return NVC_EINVAL;
+  *out = r->opt;
+  return NVC_OK;
+}
 int64_t nvc_runner_kv_bytes_per_token(const nvc_runner* r) {
   return r ? (int64_t)2 * r->cfg.num_hidden_layers * r->kv_l * r->cfg.head_dim * 2 : 0;
 }
@@ -552,6 +563,8 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
   R_CUDA(cudaMemcpyAsync(r->d_slots, h + 2 * N, N * 4, cudaMemcpyHostToDevice, st));
   R_CUDA(cudaMemcpyAsync(r->d_cu, h + 3 * N, (B + 1) * 4, cudaMemcpyHostToDevice, st));
   R_CUDA(cudaMemcpyAsync(r->d_last_rows, last, B * 4, cudaMemcpyHostToDevice, st));
+  r->last_h2d_bytes = (int64_t)N * 12 + (int64_t)(B + 1) * 4 + (int64_t)B * 4 +
+                      (paged ? (int64_t)B * 4 + (int64_t)B * r->max_blocks_cap * 4 : 0);
   if (paged) {
     int32_t* hctx = last + B;
     int32_t* hbt = hctx + B;
@@ -660,6 +673,7 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
   R_CUDA(cudaMemcpyAsync(r->d_slots, h + 2 * B, B * 4, cudaMemcpyHostToDevice, st));
   R_CUDA(cudaMemcpyAsync(r->d_ctx, h + 3 * B, B * 4, cudaMemcpyHostToDevice, st));
   R_CUDA(cudaMemcpyAsync(r->d_bt, hbt, (size_t)B * cap * 4, cudaMemcpyHostToDevice, st));
+  r->last_h2d_bytes = (int64_t)B * 16 + (int64_t)B * cap * 4;
   const int hint = std::min(next_pow2(max_blocks), cap);
   int rc = stage_sampling(r, B);
   if (rc) return rc;

@@ -56,6 +56,7 @@ class SchedulerConfig:
     enable_prefix_caching: bool = False      # beyond the reference; off = reference behaviour
 
     enable_chunked_prefill: bool = False     # beyond the reference: mixed prefill / decode steps
+    max_model_len: int = 0                   # 0 = the runner's: a sequence that reaches it finishes, a longer prompt is refused
 
     def with_chunked_prefill(self, on: bool = True):
         self.enable_chunked_prefill = on
@@ -310,6 +311,10 @@ class Qwen3ModelRunner:
     def weight_bytes(self) -> int:
         return self.l.nvc_runner_weight_bytes(self.handle)
 
+    def h2d_bytes_last_step(self) -> int:
+        """Host-to-device bytes the last step copied (counted where the copies are issued)."""
+        return self.l.nvc_runner_h2d_bytes_last_step(self.handle)
+
     def kv_bytes_per_token(self) -> int:
         return self.l.nvc_runner_kv_bytes_per_token(self.handle)
 
@@ -351,21 +356,33 @@ class StepInputs:
 
 
 class LLMEngine:
-    """LLMEngine<R: ModelRunner> (src/engine/llm_engine.rs:209-326)."""
+    """LLMEngine<R: ModelRunner> (src/engine/llm_engine.rs:209-326).
 
-    def __init__(self, scheduler: Scheduler, model_runner):
+    Like the reference, a step DRAWS the next token from softmax(logits / temperature) with each
+    request's SamplingParams.temperature (llm_engine.rs:97-133) - here on the device and seeded
+    (`seed`), so a run can be reproduced, which the reference's unseeded RNG cannot.  `greedy=True` is the
+    explicit opt-in to argmax decoding (ties -> last index, llm_engine.rs:135-142), the mode the parity
+    tests and the benchmark use; temperatures are then ignored by construction, not silently."""
+
+    def __init__(self, scheduler: Scheduler, model_runner, greedy: bool = False, seed: int = 0):
         self.l = _lib.lib()
         self.scheduler = scheduler
         self.model_runner = model_runner
         cfg = scheduler.config
         c = SchedulerConfigC(cfg.max_num_seqs, cfg.max_num_batched_tokens, cfg.eos, cfg.num_kvcache_blocks,
                              cfg.kvcache_block_size, int(bool(cfg.enable_prefix_caching)),
-                             int(bool(cfg.enable_chunked_prefill)))
+                             int(bool(cfg.enable_chunked_prefill)), int(cfg.max_model_len))
         self.chunked = bool(cfg.enable_chunked_prefill)
         h = C.c_void_p()
         rh = getattr(model_runner, "handle", None)
-        check(self.l.nvc_engine_create(C.byref(c), rh, C.byref(h)), "nvc_engine_create")
+        st = self.l.nvc_engine_create(C.byref(c), rh, C.byref(h))
+        if st != 0:
+            raise NvcError(st, "nvc_engine_create", "scheduler config refused (sizes must be positive, block size >= 2; with a "
+                           "runner: kvcache_block_size equal to the runner's and num_kvcache_blocks <= the runner's pool)")
         self.h = h
+        self.greedy = bool(greedy)
+        if rh is not None and not greedy:
+            self.set_sampling(True, seed)
         self._live: List[int] = []          # unfinished seq ids, to report outputs per step
         self.prefill_tokens = 0
         self.decode_tokens = 0
@@ -401,7 +418,7 @@ class LLMEngine:
 
     def set_sampling(self, enabled: bool, seed: int = 0) -> None:
         """On-device temperature sampling with each request's SamplingParams.temperature
-        (seeded, reproducible per sequence); off (default) = greedy argmax."""
+        (seeded, reproducible per sequence); off = greedy argmax (see the class docstring)."""
         self._ck(self.l.nvc_engine_set_sampling(self.h, int(enabled), C.c_uint64(seed & (2 ** 64 - 1))),
                  "nvc_engine_set_sampling")
 

@@ -254,7 +254,9 @@ class BlockManagerPrefix(BlockManager):
                 self.hits += 1
                 seq.num_cached_tokens += bs
                 if self.ref[b] == 0:
+                    was_ready = self.ready[b]      # a revived cached block still holds its K / V
                     self._take(b)
+                    self.ready[b] = was_ready
                 else:
                     self.ref[b] += 1
             if key is not None:

@@ -39,6 +39,20 @@ static std::string g_trace;   // configuration + calls of the current engine, pr
 // this is what catches a prefix-cache hit on a block that is not computed yet, a block freed while still in use, or
 // two sequences writing the same block.
 static std::vector<std::pair<int32_t, int32_t>> g_kv;
+// Failure injection: when set, the next runner step returns an error BEFORE it touches the cache model (a step that
+// failed in the runner wrote nothing).  nvc_engine_step must then roll its batch back (sequences re-queued, the
+// prefix-cache entries of their blocks dropped): otherwise a later step reads context that was never written and
+// the cache model below goes red.
+static bool g_fail_next = false;
+static long g_injected = 0;
+#define MAYBE_FAIL()            \
+  do {                          \
+    if (g_fail_next) {          \
+      g_fail_next = false;      \
+      ++g_injected;             \
+      return NVC_EINVAL;        \
+    }                           \
+  } while (0)
 
 static void check_step(nvc_runner* r, const int32_t* ids, const int32_t* pos, const int32_t* cu, const int32_t* slots,
                        const int32_t* bt, int max_blocks, const int32_t* ctx, int num_decode, int B, int N, int max_seqlen,
@@ -81,6 +95,7 @@ static void check_step(nvc_runner* r, const int32_t* ids, const int32_t* pos, co
 extern "C" {
 int nvc_runner_prefill(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* cu_seqlens,
                        const int32_t* slot_mapping, int B, int N, int max_seqlen, int32_t* out_tokens) {
+  MAYBE_FAIL();
   ++r->prefill;
   check_step(r, ids, positions, cu_seqlens, slot_mapping, nullptr, 0, nullptr, 0, B, N, max_seqlen, out_tokens);
   return 0;
@@ -88,6 +103,7 @@ int nvc_runner_prefill(nvc_runner* r, const int32_t* ids, const int32_t* positio
 int nvc_runner_prefill_paged(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* cu_seqlens,
                              const int32_t* slot_mapping, const int32_t* block_tables, int max_blocks,
                              const int32_t* context_lens, int B, int N, int max_seqlen, int32_t* out_tokens) {
+  MAYBE_FAIL();
   ++r->paged;
   REQUIRE(block_tables);
   check_step(r, ids, positions, cu_seqlens, slot_mapping, block_tables, max_blocks, context_lens, 0, B, N, max_seqlen, out_tokens);
@@ -96,6 +112,7 @@ int nvc_runner_prefill_paged(nvc_runner* r, const int32_t* ids, const int32_t* p
 int nvc_runner_step_mixed(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* cu_seqlens,
                           const int32_t* slot_mapping, const int32_t* block_tables, int max_blocks,
                           const int32_t* context_lens, int num_decode, int B, int N, int max_seqlen, int32_t* out_tokens) {
+  MAYBE_FAIL();
   ++r->mixed;
   REQUIRE(block_tables && num_decode >= 0 && num_decode <= B);
   check_step(r, ids, positions, cu_seqlens, slot_mapping, block_tables, max_blocks, context_lens, num_decode, B, N, max_seqlen, out_tokens);
@@ -103,6 +120,7 @@ int nvc_runner_step_mixed(nvc_runner* r, const int32_t* ids, const int32_t* posi
 }
 int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_t* positions, const int32_t* slot_mapping,
                       const int32_t* block_tables, int max_blocks, const int32_t* context_lens, int B, int32_t* out_tokens) {
+  MAYBE_FAIL();
   ++r->decode;
   REQUIRE(block_tables && B > 0 && B <= r->max_seqs);
   std::vector<int32_t> cu(B + 1);
@@ -116,6 +134,15 @@ int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_t* position
 int nvc_runner_set_sampling(nvc_runner*, const float* t, const uint64_t* s, int B, uint64_t) {
   REQUIRE(t && s && B > 0);
   for (int b = 0; b < B; ++b) REQUIRE(t[b] > 1e-10f);
+  return 0;
+}
+int nvc_runner_get_options(const nvc_runner* r, nvc_runner_options* o) {
+  memset(o, 0, sizeof(*o));
+  o->num_kvcache_blocks = r->num_blocks;
+  o->kvcache_block_size = r->bs;
+  o->max_num_seqs = r->max_seqs;
+  o->max_num_batched_tokens = r->budget;
+  o->max_model_len = 1 << 30;
   return 0;
 }
 int nvc_runner_load_weight(nvc_runner*, const char*, const nvc_bf16*, int64_t, int64_t) { return 0; }
@@ -333,8 +360,10 @@ int main(int argc, char** argv) {
         scheduled = false;
       } else if (op <= 6) {
         nvc_step_output out;
-        g_trace += " step";
+        g_fail_next = with_runner && rng() % 8 == 0;
+        g_trace += g_fail_next ? " step(fail)" : " step";
         steps_ok += nvc_engine_step(e, &out) == 0;
+        g_fail_next = false;
         scheduled = false;
       } else if (op == 8) {
         const int64_t id = reqs.empty() || rng() % 4 == 0 ? pick({-1, 1000000000}) : reqs[rng() % reqs.size()].id;
@@ -378,7 +407,7 @@ int main(int argc, char** argv) {
     REQUIRE(nvc_engine_destroy(e) == 0);
     totals.prefill += runner.prefill; totals.paged += runner.paged; totals.mixed += runner.mixed; totals.decode += runner.decode;
   }
-  printf("ok engines %ld steps %ld verified outputs %ld views %ld runner calls: prefill %ld paged %ld mixed %ld decode %ld\n",
-         created, steps_ok, finished, checked, totals.prefill, totals.paged, totals.mixed, totals.decode);
+  printf("ok engines %ld steps %ld verified outputs %ld views %ld injected %ld runner calls: prefill %ld paged %ld mixed %ld decode %ld\n",
+         created, steps_ok, finished, checked, g_injected, totals.prefill, totals.paged, totals.mixed, totals.decode);
   return 0;
 }

@@ -67,7 +67,7 @@ def test_prefill_logits_within_tolerance(tiny):
     lens = [1, 5, 16, 17, 130, 257, 64]
     prompts = [synth.make_prompts(1, n, cfg.vocab_size, 10 + n)[0] for n in lens]
     sch = eng.Scheduler(eng.SchedulerConfig(16, 2048, cfg.eos_token_id, 64, 16))
-    e = eng.LLMEngine(sch, runner)
+    e = eng.LLMEngine(sch, runner, greedy=True)
     for p in prompts:
         e.add_request(p, eng.SamplingParams(1.0, 2, True))
     si = e.schedule()
@@ -90,7 +90,7 @@ def test_prefill_logits_within_tolerance(tiny):
 
 def _generate_cuda(runner, cfg, prompts, max_tokens, max_num_seqs, nblocks, bs):
     sch = eng.Scheduler(eng.SchedulerConfig(max_num_seqs, 2048, cfg.eos_token_id, nblocks, bs))
-    e = eng.LLMEngine(sch, runner)
+    e = eng.LLMEngine(sch, runner, greedy=True)
     outs = e.generate(prompts, eng.SamplingParams(1.0, max_tokens, True))
     return [o.token_ids for o in outs], e
 
@@ -142,7 +142,7 @@ def test_prefix_caching_generation_matches_oracle_tiny(tiny):
                base + synth.make_prompts(1, 40, cfg.vocab_size, 902)[0],                   # shares 5 blocks with `base`
                synth.make_prompts(1, 21, cfg.vocab_size, 903)[0]]                          # unrelated
     sch = eng.Scheduler(eng.SchedulerConfig(2, 2048, cfg.eos_token_id, 64, bs, enable_prefix_caching=True))
-    e = eng.LLMEngine(sch, runner)        # max_num_seqs 2: later prompts arrive when earlier ones have finished or are running
+    e = eng.LLMEngine(sch, runner, greedy=True)        # max_num_seqs 2: later prompts arrive when earlier ones have finished or are running
     outs = e.generate(prompts, eng.SamplingParams(1.0, 20, True))
     hit, queried = e.prefix_cache_stats()
     diag(f"[e2e tiny prefix caching] cache hits {hit} of {queried} full blocks; prefill tokens {e.prefill_tokens}")
@@ -160,7 +160,7 @@ def test_prefix_cached_prefill_logits_match_uncached(tiny):
     bs = 16
     prompt = synth.make_prompts(1, 4 * bs + 7, cfg.vocab_size, 950)[0]
     sch = eng.Scheduler(eng.SchedulerConfig(1, 2048, cfg.eos_token_id, 64, bs, enable_prefix_caching=True))
-    e = eng.LLMEngine(sch, runner)
+    e = eng.LLMEngine(sch, runner, greedy=True)
     logits = []
     for rnd in range(2):
         e.add_request(prompt, eng.SamplingParams(1.0, 1, True))
@@ -192,7 +192,7 @@ def test_chunked_prefill_generation_matches_oracle_tiny(tiny):
     cfg, runner, fp32, _ = tiny
     prompts = [synth.make_prompts(1, n, cfg.vocab_size, 700 + n)[0] for n in (9, 70, 33, 100, 5, 48)]
     sch = eng.Scheduler(eng.SchedulerConfig(4, 24, cfg.eos_token_id, 64, 16, enable_chunked_prefill=True))
-    e = eng.LLMEngine(sch, runner)
+    e = eng.LLMEngine(sch, runner, greedy=True)
     for p in prompts:
         e.add_request(p, eng.SamplingParams(1.0, 20, True))
     mixed = steps = 0
@@ -219,13 +219,13 @@ def test_mixed_step_logits_match_whole_prompt_prefill(tiny):
     prompt = synth.make_prompts(1, 3 * bs + 11, cfg.vocab_size, 990)[0]
     others = [synth.make_prompts(1, n, cfg.vocab_size, 991 + n)[0] for n in (21, 40)]
     # whole-prompt reference on the CUDA path
-    e0 = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, bs)), runner)
+    e0 = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, bs)), runner, greedy=True)
     e0.add_request(prompt, eng.SamplingParams(1.0, 1, True))
     si = e0.schedule()
     runner.prefill(si.ids, si.positions, si.cu_seqlens, si.slot_mapping)
     whole = torch.from_numpy(runner.last_logits(1))[0].clone()
     # chunked, 27-token budget: two sequences prefilled first, then the long prompt arrives (25 tokens per step are left)
-    e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 27, cfg.eos_token_id, 64, bs, enable_chunked_prefill=True)), runner)
+    e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 27, cfg.eos_token_id, 64, bs, enable_chunked_prefill=True)), runner, greedy=True)
     for p in others:
         e.add_request(p, eng.SamplingParams(1.0, 8, True))
     gen = [list(p) for p in others]
@@ -268,7 +268,7 @@ def test_mixed_step_rejects_inconsistent_inputs(tiny):
     """nvc_runner_step_mixed reports bad arguments as status codes (never aborts, never guesses)."""
     cfg, runner, _, _ = tiny
     bs = 16
-    e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 64, cfg.eos_token_id, 64, bs, enable_chunked_prefill=True)), runner)
+    e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 64, cfg.eos_token_id, 64, bs, enable_chunked_prefill=True)), runner, greedy=True)
     e.add_request(synth.make_prompts(1, 20, cfg.vocab_size, 5)[0], eng.SamplingParams(1.0, 2, True))
     si = e.schedule()
     args = (si.ids, si.positions, si.cu_seqlens, si.slot_mapping, si.block_tables, si.context_lens)
@@ -294,15 +294,14 @@ def test_on_device_sampling_is_reproducible_and_follows_the_oracle(tiny):
     seed, T, steps = 20261104, 0.8, 12
 
     def run(sd):
-        e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, 16)), runner)
-        e.set_sampling(True, sd)
+        e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, 16)), runner, seed=sd)   # default: sampling
         return [o.token_ids for o in e.generate(prompts, eng.SamplingParams(T, steps, True))]
 
     a, b, c = run(seed), run(seed), run(seed + 1)
     assert a == b, "same seed must reproduce the same tokens"
     assert a != c, "a different seed must change the draws"
     greedy = [o.token_ids for o in eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, 16)),
-                                                 runner).generate(prompts, eng.SamplingParams(T, steps, True))]
+                                                 runner, greedy=True).generate(prompts, eng.SamplingParams(T, steps, True))]
     assert a != greedy, "sampling at T = 0.8 over a flat random-init distribution must leave the greedy path"
     exact = total = 0
     for sid, (p, toks) in enumerate(zip(prompts, a)):
@@ -324,7 +323,7 @@ def test_causality_property(tiny):
     here: last-token logits of [a] equal position-0 logits of [a, b] in the oracle, and the
     CUDA path reproduces the 1-token logits."""
     cfg, runner, fp32, _ = tiny
-    e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, 16)), runner)
+    e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(4, 2048, cfg.eos_token_id, 64, 16)), runner, greedy=True)
     e.add_request([971], eng.SamplingParams(1.0, 1, True))
     si = e.schedule()
     runner.prefill(si.ids, si.positions, si.cu_seqlens, si.slot_mapping)
@@ -351,7 +350,7 @@ def test_config0_golden_tokens(ctx, name):
     try:
         for case in g["cases"]:
             sch = eng.Scheduler(eng.SchedulerConfig(1, 4096, cfg.eos_token_id, 8, 256))
-            e = eng.LLMEngine(sch, runner)
+            e = eng.LLMEngine(sch, runner, greedy=True)
             e.add_request(case["prompt"], eng.SamplingParams(1.0, g["max_tokens"], True))
             si = e.schedule()
             tok0 = runner.prefill(si.ids, si.positions, si.cu_seqlens, si.slot_mapping)

@@ -611,3 +611,46 @@ def test_engine_c_abi_survives_random_call_sequences():
                 l.nvc_engine_last_error(e)
         assert l.nvc_engine_destroy(e) == 0
     assert created > 200 and steps_ok > 500, (created, steps_ok)
+
+
+
+def test_revived_cached_block_stays_ready_for_later_hits():
+    """chunked prefill + prefix caching.  A finishes (its blocks go to the free list, hashes kept); B takes
+    them back from the cache; C, admitted while B is still running, must hit the same blocks - a revived block keeps
+    its `ready` flag (its K / V are still there).  The oracle mirrors the rule; both must count the same hits."""
+    bs = 4
+    cfg = eng.SchedulerConfig(4, 64, 0, 16, bs, enable_prefix_caching=True, enable_chunked_prefill=True)
+    cpp = eng.LLMEngine(eng.Scheduler(cfg), eng.DummyModelRunner())
+    prompt = [5, 6, 7, 8, 9, 10, 11, 12, 13, 14, 15, 16, 17]          # 3 full blocks + 1 token
+    sp = eng.SamplingParams(1.0, 1, True)
+    cpp.add_request(prompt, sp)
+    while not cpp.is_finished():
+        cpp.step()
+    assert cpp.prefix_cache_stats() == (0, 3)
+    cpp.add_request(prompt, eng.SamplingParams(1.0, 8, True))          # B: revives A's three blocks
+    cpp.step()
+    assert cpp.prefix_cache_stats() == (3, 6)
+    cpp.add_request(prompt, eng.SamplingParams(1.0, 8, True))          # C: admitted while B runs
+    cpp.step()
+    assert cpp.prefix_cache_stats() == (6, 9), "a revived block must keep serving prefix-cache hits"
+    assert cpp.block_table_of(2)[:3] == cpp.block_table_of(1)[:3]
+    while not cpp.is_finished():
+        cpp.step()
+
+
+def test_max_model_len_finishes_sequences_and_refuses_long_prompts():
+    """the engine knows the longest sequence the runner holds.  A sequence that grows to it finishes like
+    one that reached max_tokens (instead of failing a later step with 'position out of range'); a prompt that is
+    longer is refused at add_request."""
+    cfg = eng.SchedulerConfig(4, 256, -1, 32, 16)
+    cfg.max_model_len = 40
+    e = eng.LLMEngine(eng.Scheduler(cfg), eng.DummyModelRunner())
+    with pytest.raises(eng.NvcError):
+        e.add_request(list(range(41)), eng.SamplingParams(1.0, 4, True))
+    a = e.add_request(list(range(30)), eng.SamplingParams(1.0, 100, True))      # would run to 130 tokens
+    b = e.add_request(list(range(40)), eng.SamplingParams(1.0, 100, True))      # fits exactly: one token from the prefill
+    c = e.add_request(list(range(10)), eng.SamplingParams(1.0, 5, True))        # unaffected
+    outs = {o.seq_id: o.token_ids for o in e.generate([], eng.SamplingParams(1.0, 1, True))}
+    assert len(outs[a]) == 11          # positions 30..39 computed, the token appended after position 39 ends it
+    assert len(outs[b]) == 1 and len(outs[c]) == 5
+    assert e.num_free_blocks() == 32

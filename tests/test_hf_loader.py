@@ -96,6 +96,9 @@ def test_safetensors_rejects_malformed_files(tmp_path):
     cases["overflow.safetensors"] = len(hdr).to_bytes(8, "little") + hdr + b"\0" * 16
     hdr = json.dumps({"x": {"dtype": "F32", "shape": [2.5], "data_offsets": [0, 10]}}).encode()
     cases["fractional.safetensors"] = len(hdr).to_bytes(8, "little") + hdr + b"\0" * 16
+    hdr = json.dumps({"x": {"dtype": "F32", "shape": [3], "data_offsets": [0, 12]},          # two tensors sharing bytes
+                      "y": {"dtype": "F32", "shape": [2], "data_offsets": [8, 16]}}).encode()
+    cases["overlap.safetensors"] = len(hdr).to_bytes(8, "little") + hdr + b"\0" * 16
     for name, blob in cases.items():
         p = tmp_path / name
         p.write_bytes(blob)
@@ -246,6 +249,19 @@ def test_loader_survives_mutated_headers(tmp_path):
     assert accepted > 20
 
 
+def test_sharded_index_refuses_paths_outside_the_model_dir(tmp_path):
+    """weight_map file names are joined onto the model directory: '../x', 'a/b' and absolute names are refused before
+    any file is opened (no runner or device needed: the check precedes the first nvc_runner_load_weight)."""
+    l = _lib.lib()
+    d = tmp_path / "model"
+    d.mkdir()
+    save_file({"model.norm.weight": torch.ones(4)}, str(tmp_path / "outside.safetensors"))
+    for bad in ("../outside.safetensors", "sub/x.safetensors", "/etc/passwd", "..", ""):
+        json.dump({"weight_map": {"model.norm.weight": bad}}, open(d / "model.safetensors.index.json", "w"))
+        st = l.nvc_runner_load_hf_dir(C.c_void_p(1), os.fsencode(str(d)))       # the handle is never dereferenced on this path
+        assert st != 0 and "plain file name" in l.nvc_hf_last_error().decode(), bad
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("layout", ["single_bf16", "sharded_f32_tied", "single_f16"])
 def test_runner_from_hf_dir_matches_from_weights(ctx, tmp_path, layout):
@@ -258,7 +274,9 @@ def test_runner_from_hf_dir_matches_from_weights(ctx, tmp_path, layout):
         w["lm_head.weight"] = w["model.embed_tokens.weight"].clone()
     _write_config(tmp_path, cfg, head_dim=cfg.head_dim, tie_word_embeddings=tied)
     if layout == "single_bf16":
-        save_file({k: v.to(torch.bfloat16).contiguous() for k, v in w.items()}, str(tmp_path / "model.safetensors"))
+        d = {k: v.to(torch.bfloat16).contiguous() for k, v in w.items()}
+        d["model.layers.0.mlp.some_export_buffer"] = torch.ones(3)            # not a model tensor: skipped with a warning
+        save_file(d, str(tmp_path / "model.safetensors"))
     elif layout == "single_f16":
         w = {k: v.to(torch.float16) for k, v in w.items()}
         save_file({k: v.contiguous() for k, v in w.items()}, str(tmp_path / "model.safetensors"))
@@ -275,12 +293,14 @@ def test_runner_from_hf_dir_matches_from_weights(ctx, tmp_path, layout):
         json.dump({"metadata": {"total_size": 0}, "weight_map": wm}, open(tmp_path / "model.safetensors.index.json", "w"))
     kw = dict(num_kvcache_blocks=16, kvcache_block_size=16, max_num_seqs=2, max_num_batched_tokens=256, max_model_len=256)
     a = eng.Qwen3ModelRunner.from_hf_dir(ctx, str(tmp_path), **kw)
+    warn = a.l.nvc_hf_last_warning().decode()
+    assert ("some_export_buffer" in warn) == (layout == "single_bf16"), warn
     b = eng.Qwen3ModelRunner.from_weights(ctx, cfg, w.items(), **kw)
     try:
         prompt = synth.make_prompts(1, 37, cfg.vocab_size, 5)[0]
         outs = []
         for r in (a, b):
-            e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(2, 256, cfg.eos_token_id, 16, 16)), r)
+            e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(2, 256, cfg.eos_token_id, 16, 16)), r, greedy=True)
             e.add_request(prompt, eng.SamplingParams(1.0, 6, True))
             si = e.schedule()
             tok = r.prefill(si.ids, si.positions, si.cu_seqlens, si.slot_mapping)

@@ -36,6 +36,7 @@ def test_engine_and_loader_fuzz_under_sanitizers(fuzz_binary, tmp_path, seed):
     # the run reached every runner entry point and verified finished outputs, not just error paths
     assert stats["engines"] > 100 and stats["steps"] > 1000 and stats["outputs"] > 20, r.stdout
     assert min(stats["prefill"], stats["paged"], stats["mixed"], stats["decode"]) > 0, r.stdout
+    assert stats["injected"] > 20, r.stdout            # runner failures were injected and rolled back
     assert "loader:" in r.stdout
 
 
@@ -44,6 +45,8 @@ MUTANTS = {
     "hit_before_ready": ("(chunked && !blocks[id].ready))", "(false))"),
     # a shared block returned to the free list while another sequence still holds it
     "freed_while_shared": ("if (--b.ref_count == 0) free_.push_back", "if (--b.ref_count >= 0) free_.push_back"),
+    # a step that failed in the runner leaves its batch scheduled (running, blocks allocated and hash-registered)
+    "no_rollback": ("    rollback_failed_step(e);", "    // (mutant)"),
     # a re-admitted (preempted) sequence keeps its old progress although its blocks are new
     "stale_progress": ("      seq->num_computed_tokens = seq->num_cached_tokens;", "      // (mutant)",
                        "    seq->num_computed_tokens = 0;", "    // (mutant)"),

@@ -26,7 +26,7 @@ import torch
 
 def run(eng, runner, cfg, prompts, arrivals, decode_tokens, nblocks, budget, chunked):
     sc = eng.SchedulerConfig(len(prompts), budget, cfg.eos_token_id, nblocks, 256, enable_chunked_prefill=chunked)
-    e = eng.LLMEngine(eng.Scheduler(sc), runner)
+    e = eng.LLMEngine(eng.Scheduler(sc), runner, greedy=True)
     sp = eng.SamplingParams(1.0, decode_tokens, True)
     added, step = 0, 0
     last_tok_time, gaps = {}, []

@@ -62,7 +62,7 @@ def main():
         torch.cuda.synchronize()
 
     for B in a.batches:
-        e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(B, max_tokens_batched, cfg.eos_token_id, nblocks, 256)), runner)
+        e = eng.LLMEngine(eng.Scheduler(eng.SchedulerConfig(B, max_tokens_batched, cfg.eos_token_id, nblocks, 256)), runner, greedy=True)
         prompts = synth.make_prompts(B, T, cfg.vocab_size, 10 + B)
         if B == a.batches[0]:           # warm-up
             for p in prompts[:1]:

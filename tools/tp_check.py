@@ -46,7 +46,7 @@ def main():
                                                max_num_seqs=8, max_num_batched_tokens=2048, max_model_len=64 * bs // 8)
     prompts = [synth.make_prompts(1, n, cfg.vocab_size, 300 + n)[0] for n in (9, 40, 33, 17)]
     sc = eng.SchedulerConfig(8, a.chunked or 2048, cfg.eos_token_id, 64, bs, enable_chunked_prefill=a.chunked > 0)
-    e = eng.LLMEngine(eng.Scheduler(sc), runner)
+    e = eng.LLMEngine(eng.Scheduler(sc), runner, greedy=True)
     t0 = time.perf_counter()
     mixed = 0
     if a.chunked:           # step by step to count the mixed steps (decode tokens next to prompt chunks)

@@ -53,6 +53,7 @@ enum {
   NVC_ENOMEM = -5,     /* workspace / KV pool too small                                 */
   NVC_EDEVICE = -6,    /* no sm_100 device / driver entry point missing                 */
   NVC_ENCCL = -7,      /* NCCL library not loadable                                     */
+  NVC_ENVLS = -8,      /* NVSwitch multicast not available (nvc_ctx_nvls_status says why) */
   NVC_CUDA_ERROR_BASE = 1000,
   NVC_NCCL_ERROR_BASE = 2000
 };
@@ -109,6 +110,38 @@ size_t nvc_ctx_p2p_slot_bytes(const nvc_ctx* ctx);
 void* nvc_ctx_p2p_slot(nvc_ctx* ctx, int slot);
 int nvc_p2p_allreduce_rmsnorm(nvc_ctx* ctx, int slot, const float* residual_in, float* residual_out,
                               const nvc_bf16* w, float eps, nvc_bf16* out, int N, int H, void* stream);
+
+/* In-switch (NVLS) all-reduce over the NVSwitch multicast object of the TP group, fused with the residual add +
+ * RMSNorm that follow every row-parallel linear (same contract as nvc_p2p_allreduce_rmsnorm).
+ *   nvc_ctx_nvls_init: COLLECTIVE - every rank of the group calls it with the same sizes, after
+ *     nvc_ctx_init_nccl (whose unique id names the group; `group_name` may be NULL to use that name).  Allocates
+ *     one buffer per rank [flags | slot | 3 LL buffers], binds it into one multicast object (cuMulticastCreate on
+ *     rank 0; the POSIX descriptor travels to the peers over an abstract unix socket of the library's own) and maps
+ *     it at a unicast and a multicast address.  Returns NVC_ENVLS on every rank alike when any rank cannot do its
+ *     part (no multicast support, creation refused); nvc_ctx_nvls_status then says why and the caller stays on the
+ *     peer-memory / NCCL path.
+ *   nvc_ctx_nvls_slot: this rank's slot (device pointer, slot_bytes): where the row-parallel GEMM writes its
+ *     partial [N, H] bf16 result when the two-shot kernel is to reduce it.
+ *   nvc_nvls_allreduce_rmsnorm: x_partial = this rank's partial sums.  mode 0 chooses by size; 1 = LL one-shot
+ *     (rank r multimem.st's its rows into every rank's LL buffer, readers spin on the data; x_partial anywhere;
+ *     tp * N * H * 2 <= ll_buf_bytes); 2 = two-shot in the switch (multimem.ld_reduce of 1/tp of the slot,
+ *     multimem.st of the sums in place, two flag barriers; x_partial must be nvc_ctx_nvls_slot); 3 = two-shot with
+ *     the sums broadcast into an LL buffer (one barrier; N * H * 2 <= ll_buf_bytes).  Results are bit-identical on
+ *     all ranks in every mode.  tp_size in {2, 4, 8}; H % 64 == 0, H <= 8192. */
+int nvc_ctx_nvls_init(nvc_ctx* ctx, size_t slot_bytes, size_t ll_buf_bytes, const char* group_name);
+int nvc_ctx_nvls_ready(const nvc_ctx* ctx);
+const char* nvc_ctx_nvls_status(const nvc_ctx* ctx);
+size_t nvc_ctx_nvls_slot_bytes(const nvc_ctx* ctx);
+size_t nvc_ctx_nvls_ll_bytes(const nvc_ctx* ctx);
+void* nvc_ctx_nvls_slot(nvc_ctx* ctx);
+int nvc_nvls_allreduce_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x_partial, const float* residual_in, float* residual_out,
+                               const nvc_bf16* w, float eps, nvc_bf16* out, int N, int H, int mode, void* stream);
+/* End of a TP step (vocab-parallel lm_head + per-shard argmax / sample): all-gather of the ranks' (best value,
+ * token) candidates through the multicast LL buffers and merge - largest value, ties -> the larger token id
+ * (llm_engine.rs:135-142 "last maximum") - in one kernel; out_tok [B] is identical on every rank.  out_val may be
+ * NULL.  Replaces nvc_pack_argmax_pairs + nvc_allgather_bytes + the host-side merge. */
+int nvc_nvls_argmax_merge(nvc_ctx* ctx, const float* best_val, const int32_t* best_tok, int32_t* out_tok, float* out_val,
+                          int B, void* stream);
 
 /* ------------------------------------------------------------------ kernels */
 

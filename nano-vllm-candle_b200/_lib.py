@@ -68,6 +68,10 @@ def _declare(l: C.CDLL) -> None:
         "nvc_ctx_p2p_import": [_vp, _vp],
         "nvc_ctx_p2p_ready": [_vp],
         "nvc_p2p_allreduce_rmsnorm": [_vp, _i, _vp, _vp, _vp, _f, _vp, _i, _i, _vp],
+        "nvc_ctx_nvls_init": [_vp, _sz, _sz, C.c_char_p],
+        "nvc_ctx_nvls_ready": [_vp],
+        "nvc_nvls_allreduce_rmsnorm": [_vp, _vp, _vp, _vp, _vp, _f, _vp, _i, _i, _i, _vp],
+        "nvc_nvls_argmax_merge": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
         "nvc_embed_gather": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp],
         "nvc_fused_add_rmsnorm": [_vp, _vp, _vp, _vp, _vp, _f, _vp, _i, _i, _vp],
         "nvc_gemm_bf16": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp],
@@ -95,6 +99,14 @@ def _declare(l: C.CDLL) -> None:
     l.nvc_ctx_p2p_slot.argtypes = [_vp, _i]
     l.nvc_ctx_p2p_slot_bytes.restype = _sz
     l.nvc_ctx_p2p_slot_bytes.argtypes = [_vp]
+    l.nvc_ctx_nvls_slot.restype = _vp
+    l.nvc_ctx_nvls_slot.argtypes = [_vp]
+    l.nvc_ctx_nvls_slot_bytes.restype = _sz
+    l.nvc_ctx_nvls_slot_bytes.argtypes = [_vp]
+    l.nvc_ctx_nvls_ll_bytes.restype = _sz
+    l.nvc_ctx_nvls_ll_bytes.argtypes = [_vp]
+    l.nvc_ctx_nvls_status.restype = C.c_char_p
+    l.nvc_ctx_nvls_status.argtypes = [_vp]
     l.nvc_paged_decode_workspace_bytes.restype = _sz
     l.nvc_paged_decode_workspace_bytes.argtypes = [_i, _i, _i, _i]
     from . import _engine_sigs

@@ -86,6 +86,12 @@ extern "C" int nvc_ctx_init_nccl(nvc_ctx* ctx, const void* unique_id_128B) {
   NVC_NCCL_CHECK(ctx, api, api->CommInitRank(&comm, ctx->tp_size, id, ctx->tp_rank));
   ctx->nccl = api;
   ctx->nccl_comm = comm;
+  // a name every rank of this group derives identically (rendezvous of the NVLS set-up)
+  uint64_t h = 1469598103934665603ull;
+  for (size_t i = 0; i < sizeof(id); ++i) h = (h ^ (uint8_t)id.internal[i]) * 1099511628211ull;
+  char nm[32];
+  snprintf(nm, sizeof(nm), "%016llx", (unsigned long long)h);
+  ctx->tp_group_name = nm;
   return NVC_OK;
 }
 

@@ -32,6 +32,7 @@ typedef CUresult (*nvc_encode_tiled_fn)(CUtensorMap*, CUtensorMapDataType, cuuin
                                         CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
 struct nvc_nccl_api;  // collectives.cu
+struct nvc_nvls;      // nvls_allreduce.cu
 
 struct nvc_ctx {
   int device = 0;
@@ -60,6 +61,12 @@ struct nvc_ctx {
   uint32_t* p2p_state = nullptr;         // device: [0] epoch, [1] CTAs done
   size_t p2p_slot_bytes = 0;
   bool p2p_ready = false;
+  // NVLS (NVSwitch multicast) all-reduce (nvls_allreduce.cu): one buffer per rank bound into a multicast object
+  nvc_nvls* nvls = nullptr;
+  bool nvls_ready = false;
+  int nvls_generation = 0;               // set-ups so far on this context (part of the rendezvous name)
+  std::string nvls_status = "not initialised";
+  std::string tp_group_name;             // unique per TP group (from the NCCL unique id), same on every rank
 };
 
 void nvc_set_error(nvc_ctx* ctx, const std::string& msg);

@@ -7,6 +7,7 @@
 
 void nvc_collectives_destroy(nvc_ctx* ctx);   // collectives.cu
 void nvc_p2p_destroy(nvc_ctx* ctx);           // p2p_allreduce.cu
+void nvc_nvls_destroy(nvc_ctx* ctx);          // nvls_allreduce.cu
 
 static thread_local std::string g_null_ctx_error;
 
@@ -27,6 +28,7 @@ extern "C" const char* nvc_status_string(int status) {
     case NVC_ENOMEM: return "workspace or KV pool too small";
     case NVC_EDEVICE: return "no usable sm_100 device";
     case NVC_ENCCL: return "NCCL unavailable";
+    case NVC_ENVLS: return "NVLS multicast unavailable";
     default: break;
   }
   if (status >= NVC_NCCL_ERROR_BASE) return "NCCL error";
@@ -111,6 +113,7 @@ extern "C" uint64_t nvc_ctx_launch_count(const nvc_ctx* ctx) { return ctx ? ctx-
 extern "C" int nvc_ctx_destroy(nvc_ctx* ctx) {
   if (!ctx) return NVC_EINVAL;
   cudaSetDevice(ctx->device);
+  nvc_nvls_destroy(ctx);
   nvc_p2p_destroy(ctx);
   nvc_collectives_destroy(ctx);
   if (ctx->gemm_ws) cudaFree(ctx->gemm_ws);

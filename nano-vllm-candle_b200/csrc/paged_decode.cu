@@ -309,6 +309,9 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
     part_ml = part_o + (size_t)B * nh * splits * hd;
   }
   dim3 grid(kv * chunks, B, splits);
+  // splits merged by the last CTA to arrive (tickets in pd_counters) instead of a second kernel
+  const bool fused_merge = !use_simt && splits > 1 && ctx->pd_counters != nullptr && (int64_t)kv * chunks * B <= kFlatMaxPairs &&
+                           !(getenv("NVC_PD_COMBINE_KERNEL") && atoi(getenv("NVC_PD_COMBINE_KERNEL")) != 0);
   auto kc = reinterpret_cast<const uint4*>(k_cache);
   auto vc = reinterpret_cast<const uint4*>(v_cache);
 #define NVC_LAUNCH_PD(GV)                                                                                   \
@@ -318,7 +321,7 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
   if (!use_simt) {
     NVC_CUDA_CHECK(ctx, nvc_launch(ctx, pdmma::paged_decode_mma_kernel, grid, dim3(pdmma::kThreads), pdmma::kSmemBytes, st,
                                    q, ldq, k_cache, v_cache, block_tables, max_blocks, context_lens, nh, kv, group, G,
-                                   block_size, scale_log2e, out, part_o, part_ml, splits));
+                                   block_size, scale_log2e, out, part_o, part_ml, splits, fused_merge ? ctx->pd_counters : nullptr));
   } else {
     switch (G) {
       case 4: NVC_LAUNCH_PD(4); break;
@@ -330,7 +333,7 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
 #undef NVC_LAUNCH_PD
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
-  if (splits > 1) {
+  if (splits > 1 && !fused_merge) {
     NVC_CUDA_CHECK(ctx, nvc_launch(ctx, paged_decode_combine_kernel, dim3(nh, B), dim3(128), 0, st, part_o, part_ml, out,
                                    nh, splits));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());

@@ -54,14 +54,23 @@ __device__ __forceinline__ void mma_bf16(float* d, const uint32_t* a, uint32_t b
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+__device__ __forceinline__ int atomic_add_acq_rel(int* p, int v) {
+  int old;
+  asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
+  return old;
+}
+
 // group: query heads per kv head handled by this CTA (<= 16); head0: first query head.
+// num_splits > 1: every split parks its (m, l, o) partial; with `counters` (one zeroed int per (sequence, blockIdx.x))
+// the CTA that takes the last ticket merges the partials in split order - no second kernel.
 __global__ void __launch_bounds__(kThreads, 2)
 paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16* __restrict__ k_cache,
                         const nvc_bf16* __restrict__ v_cache, const int32_t* __restrict__ block_tables, int max_blocks,
                         const int32_t* __restrict__ context_lens, int nh, int kv, int group_total, int gchunk,
                         int block_size, float scale_log2e, nvc_bf16* __restrict__ out, float* __restrict__ part_o,
-                        float* __restrict__ part_ml, int num_splits) {
+                        float* __restrict__ part_ml, int num_splits, int* __restrict__ counters) {
   extern __shared__ __align__(128) uint8_t smem[];
+  __shared__ int ticket_sm;
   pdl_trigger();
   // The dependency wait comes AFTER the first K / V tiles are in flight (see below): context_lens and
   // block_tables are step inputs (copied before the step's first kernel), and the only cache rows a
@@ -276,8 +285,34 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
       out[((int64_t)b * nh + head) * 128 + d] = __bfloat16_as_ushort(__float2bfloat16_rn(r));
     } else {
       const int64_t p = ((int64_t)b * nh + head) * num_splits + split;
-      part_o[p * 128 + d] = O;
-      if (d == 0) { part_ml[p * 2] = M; part_ml[p * 2 + 1] = L; }
+      __stcg(part_o + p * 128 + d, O);
+      if (d == 0) { __stcg(part_ml + p * 2, M); __stcg(part_ml + p * 2 + 1, L); }
+    }
+  }
+  if (num_splits > 1 && counters != nullptr) {
+    // CTA barrier orders every thread's partial stores before thread 0's release; the acquire half of the same
+    // atomic plus the second barrier orders the last CTA's loads after the other splits' stores.
+    const int pair = b * gridDim.x + blockIdx.x;
+    __syncthreads();
+    if (threadIdx.x == 0) ticket_sm = atomic_add_acq_rel(counters + pair, 1);
+    __syncthreads();
+    if (ticket_sm == num_splits - 1) {
+      for (int g = 0; g < G; ++g) {
+        const int64_t p0 = ((int64_t)b * nh + head0 + g) * num_splits;
+        float M = -INFINITY;
+        for (int s = 0; s < num_splits; ++s) M = fmaxf(M, __ldcg(part_ml + (p0 + s) * 2));
+        float L = 0.f, O = 0.f;
+        if (M != -INFINITY) {
+          for (int s = 0; s < num_splits; ++s) {                       // split order whoever merges: deterministic
+            const float wt = fast_exp2(__ldcg(part_ml + (p0 + s) * 2) - M);
+            L += __ldcg(part_ml + (p0 + s) * 2 + 1) * wt;
+            O += __ldcg(part_o + (p0 + s) * 128 + d) * wt;
+          }
+        }
+        const float r = L > 0.f ? O / L : 0.f;
+        out[((int64_t)b * nh + head0 + g) * 128 + d] = __bfloat16_as_ushort(__float2bfloat16_rn(r));
+      }
+      if (threadIdx.x == 0) counters[pair] = 0;                        // re-arm for the next launch
     }
   }
 }
@@ -295,12 +330,6 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
 // second kernel.  Everything is derived from context_lens on the device: CUDA-graph replayable.
 // ---------------------------------------------------------------------------------------------
 constexpr int kMaxFlatBatch = 1024;
-
-__device__ __forceinline__ int atomic_add_acq_rel(int* p, int v) {
-  int old;
-  asm volatile("atom.acq_rel.gpu.global.add.s32 %0, [%1], %2;" : "=r"(old) : "l"(p), "r"(v) : "memory");
-  return old;
-}
 
 __global__ void __launch_bounds__(kThreads, 2)
 paged_decode_flat_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16* __restrict__ k_cache,

@@ -73,6 +73,7 @@ struct nvc_runner {
   std::map<std::pair<int, int>, cudaGraphExec_t> graphs;
   int launches_per_decode = 0;
   int64_t last_h2d_bytes = 0;      // host-to-device bytes of the last step's inputs
+  bool x_nvls = false;             // r->x is the context's NVLS slot: all-reduces go through the switch
   int last_decode_hint = 0;
   int last_decode_key2 = 0;
 };
@@ -109,7 +110,10 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
   const int H = c.hidden_size, hd = c.head_dim, L = c.num_hidden_layers;
   const float scale = 1.0f / sqrtf((float)hd);   // (head_dim as f32).powf(-0.5), qwen3.rs:132
   static const bool p2p_env = !(getenv("NVC_P2P_AR") && atoi(getenv("NVC_P2P_AR")) == 0);
-  const bool p2p = r->tp > 1 && decode && p2p_env && nvc_ctx_p2p_ready(ctx) &&
+  // NVLS (in-switch) all-reduce + residual + norm for every step kind; else the peer-load kernel for decode-sized
+  // messages; else NCCL + the norm kernel
+  const bool nvls = r->tp > 1 && r->x_nvls && nvc_ctx_nvls_ready(ctx);
+  const bool p2p = !nvls && r->tp > 1 && decode && p2p_env && nvc_ctx_p2p_ready(ctx) &&
                    (size_t)N * H * 2 <= nvc_ctx_p2p_slot_bytes(ctx);
   nvc_bf16* slot0 = p2p ? reinterpret_cast<nvc_bf16*>(nvc_ctx_p2p_slot(ctx, 0)) : nullptr;
   nvc_bf16* slot1 = p2p ? reinterpret_cast<nvc_bf16*>(nvc_ctx_p2p_slot(ctx, 1)) : nullptr;
@@ -155,7 +159,9 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     // o_proj (row-parallel) -> [all-reduce, N4] -> post_attention_layernorm with residual add
     rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, Ly.w_o, p2p ? slot0 : r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
     if (rc) return rc;
-    if (p2p) {
+    if (nvls) {
+      rc = nvc_nvls_allreduce_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, 0, st);
+    } else if (p2p) {
       rc = nvc_p2p_allreduce_rmsnorm(ctx, 0, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
     } else {
       if (r->tp > 1) { rc = nvc_allreduce_bf16(ctx, r->x, (size_t)N * H, st); if (rc) return rc; }
@@ -168,7 +174,16 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     // down_proj (row-parallel) -> [all-reduce, N4]
     rc = nvc_gemm_bf16(ctx, r->act, r->I_l, Ly.w_down, p2p ? slot1 : r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
     if (rc) return rc;
-    if (p2p) {
+    if (nvls) {
+      // the norm that opens layer l+1 (or the final norm) comes out of the same kernel; a prefill step keeps all
+      // N normed rows in xn and run_head gathers the last-token rows from there
+      const bool last = li + 1 == L;
+      rc = nvc_nvls_allreduce_rmsnorm(ctx, r->x, r->residual, r->residual, last ? r->final_norm : r->layers[li + 1].ln1,
+                                      c.rms_norm_eps, last && decode ? r->xn_last : r->xn, N, H, 0, st);
+      if (rc) return rc;
+      xn_ready = !last;
+      *final_norm_done = last;
+    } else if (p2p) {
       const bool last = li + 1 == L;
       rc = nvc_p2p_allreduce_rmsnorm(ctx, 1, r->residual, r->residual, last ? r->final_norm : r->layers[li + 1].ln1,
                                      c.rms_norm_eps, last ? r->xn_last : r->xn, N, H, st);
@@ -192,7 +207,10 @@ int run_head(nvc_runner* r, int B, bool decode, bool final_norm_done) {
   int rc;
   const nvc_bf16* xs = r->x;
   const float* rs = r->residual;
-  if (!decode) {
+  if (!decode && final_norm_done) {           // prefill through the fused all-reduce: xn holds the normed rows
+    rc = nvc_gather_rows(ctx, r->xn, nullptr, r->d_last_rows, r->xn_last, nullptr, B, H, st);
+    if (rc) return rc;
+  } else if (!decode) {
     rc = nvc_gather_rows(ctx, r->x, r->residual, r->d_last_rows, r->x_last, r->res_last, B, H, st);
     if (rc) return rc;
     xs = r->x_last;
@@ -210,14 +228,17 @@ int run_head(nvc_runner* r, int B, bool decode, bool final_norm_done) {
   else
     rc = nvc_argmax_last(ctx, r->logits, r->V_l, r->d_tok, r->d_tok_val, B, r->V_l, r->rank * r->V_l, st);    // llm_engine.rs:135-142
   if (rc || r->tp == 1) return rc;
-  // TP: every rank holds (max, idx) of its vocab shard; gather the 8-byte pairs
+  // TP: every rank holds (max, idx) of its vocab shard.  Through the switch: one kernel gathers and merges them
+  // (d_tok then holds the winning tokens on every rank); else gather the 8-byte pairs with NCCL, merged on the host
+  if (r->x_nvls && nvc_ctx_nvls_ready(ctx) && (size_t)B * r->tp * 16 <= nvc_ctx_nvls_ll_bytes(ctx))
+    return nvc_nvls_argmax_merge(ctx, r->d_tok_val, r->d_tok, r->d_tok, nullptr, B, st);
   rc = nvc_pack_argmax_pairs(ctx, r->d_tok_val, r->d_tok, reinterpret_cast<float*>(r->d_pairs + (size_t)r->rank * B), B, st);
   if (rc) return rc;
   return nvc_allgather_bytes(ctx, r->d_pairs, (size_t)B * sizeof(ArgPair), st);
 }
 
 int finish_tokens(nvc_runner* r, int B, int32_t* out_tokens) {
-  if (r->tp == 1) {
+  if (r->tp == 1 || (r->x_nvls && nvc_ctx_nvls_ready(r->ctx) && (size_t)B * r->tp * 16 <= nvc_ctx_nvls_ll_bytes(r->ctx))) {
     R_CUDA(cudaMemcpyAsync(r->h_tok, r->d_tok, B * sizeof(int32_t), cudaMemcpyDeviceToHost, r->stream));
     R_CUDA(cudaStreamSynchronize(r->stream));
     memcpy(out_tokens, r->h_tok, B * sizeof(int32_t));
@@ -320,7 +341,20 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if ((rc = dev_alloc(r, &r->lm_head, (size_t)r->V_l * H))) return rc;
   r->weight_bytes += 2 * ((int64_t)cfg->vocab_size * H + H + (int64_t)r->V_l * H);
   if ((rc = dev_alloc(r, &r->rope, (size_t)opt->max_model_len * hd))) return rc;
-  if ((rc = dev_alloc(r, &r->x, T * H))) return rc;
+  // under TP the row-parallel GEMMs write their partial sums where the switch can reduce them: x is the context's
+  // NVLS slot when the multicast set-up succeeds (collective: every rank takes the same branch)
+  static const bool nvls_env = !(getenv("NVC_NVLS") && atoi(getenv("NVC_NVLS")) == 0);
+  if (tp > 1 && nvls_env && !ctx->tp_group_name.empty()) {
+    const size_t slot = (T * H * 2 + 255) / 256 * 256;
+    const size_t ll = (size_t)4 << 20;
+    if (!(nvc_ctx_nvls_ready(ctx) && nvc_ctx_nvls_slot_bytes(ctx) >= slot && nvc_ctx_nvls_ll_bytes(ctx) >= ll))
+      (void)nvc_ctx_nvls_init(ctx, slot, ll, nullptr);       // on refusal: nvc_ctx_nvls_status, and the paths below
+    if (nvc_ctx_nvls_ready(ctx)) {
+      r->x = reinterpret_cast<nvc_bf16*>(nvc_ctx_nvls_slot(ctx));
+      r->x_nvls = true;
+    }
+  }
+  if (!r->x_nvls && (rc = dev_alloc(r, &r->x, T * H))) return rc;
   if ((rc = dev_alloc(r, &r->xn, T * H))) return rc;
   if ((rc = dev_alloc(r, &r->residual, T * H))) return rc;
   if ((rc = dev_alloc(r, &r->qkv, T * r->qkv_l))) return rc;
@@ -852,8 +886,10 @@ extern "C" int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_pe
         case NVC_OP_NOOP:   // smallest possible kernel: the per-launch floor inside a graph
           rc = nvc_gather_rows(ctx, r->x, nullptr, r->d_last_rows, r->x_last, nullptr, 1, H, st);
           break;
-        case NVC_OP_ALLREDUCE:     // what the decode step uses: fused peer all-reduce + norm, or NCCL
-          if (nvc_ctx_p2p_ready(ctx) && (size_t)B * H * 2 <= nvc_ctx_p2p_slot_bytes(ctx) &&
+        case NVC_OP_ALLREDUCE:     // what the decode step uses: fused in-switch / peer all-reduce + norm, or NCCL
+          if (r->x_nvls && nvc_ctx_nvls_ready(ctx))
+            rc = nvc_nvls_allreduce_rmsnorm(ctx, r->x, r->residual, r->residual, L.ln2, c.rms_norm_eps, r->xn, B, H, 0, st);
+          else if (nvc_ctx_p2p_ready(ctx) && (size_t)B * H * 2 <= nvc_ctx_p2p_slot_bytes(ctx) &&
               !(getenv("NVC_P2P_AR") && atoi(getenv("NVC_P2P_AR")) == 0))
             rc = nvc_p2p_allreduce_rmsnorm(ctx, li & 1, r->residual, r->residual, L.ln2, c.rms_norm_eps, r->xn, B, H, st);
           else

@@ -90,6 +90,39 @@ class Context:
         dist.all_gather_object(allh, mine)
         self.p2p_import(allh)
 
+    def nvls_init(self, slot_bytes: int, ll_buf_bytes: int = 4 << 20, group_name: Optional[str] = None) -> bool:
+        """COLLECTIVE: the NVSwitch multicast buffers of the TP group (nvc_ctx_nvls_init).  False (on every rank
+        alike) when multicast is not available on this box; nvls_status() then says why."""
+        st = self.l.nvc_ctx_nvls_init(self.h, slot_bytes, ll_buf_bytes, None if group_name is None else group_name.encode())
+        if st == -8:
+            return False
+        self._ck(st, "nvc_ctx_nvls_init")
+        return True
+
+    def nvls_ready(self) -> bool:
+        return bool(self.l.nvc_ctx_nvls_ready(self.h))
+
+    def nvls_status(self) -> str:
+        return self.l.nvc_ctx_nvls_status(self.h).decode()
+
+    def nvls_slot(self, rows: int, cols: int) -> torch.Tensor:
+        """This rank's NVLS slot viewed as a bf16 [rows, cols] tensor (memory owned by the context)."""
+        nbytes = rows * cols * 2
+        assert nbytes <= self.l.nvc_ctx_nvls_slot_bytes(self.h)
+        ptr = self.l.nvc_ctx_nvls_slot(self.h)
+        iface = {"shape": (rows, cols), "typestr": "<u2", "data": (ptr, False), "version": 3}
+        holder = type("_Slot", (), {"__cuda_array_interface__": iface})()
+        return torch.as_tensor(holder, device=f"cuda:{self.device}").view(BF16)
+
+    def nvls_allreduce_rmsnorm(self, x_partial, w=None, eps=1e-6, residual_in=None, residual_out=None, out=None, mode=0):
+        """sum over ranks of x_partial [N, H] (+ residual, RMSNorm when w is given) through the switch."""
+        _req(x_partial, BF16, "x_partial")
+        N, H = x_partial.shape
+        out = torch.empty((N, H), dtype=BF16, device=x_partial.device) if out is None else out
+        self._ck(self.l.nvc_nvls_allreduce_rmsnorm(self.h, _ptr(x_partial), _ptr(residual_in), _ptr(residual_out), _ptr(w),
+                                                   float(eps), _ptr(out), N, H, mode, _stream()), "nvc_nvls_allreduce_rmsnorm")
+        return out
+
     def allreduce(self, buf: torch.Tensor):
         if buf.dtype == BF16:
             self._ck(self.l.nvc_allreduce_bf16(self.h, _ptr(buf), buf.numel(), _stream()), "nvc_allreduce_bf16")

@@ -67,7 +67,8 @@ def main():
     gathered = [torch.empty_like(mine) for _ in range(world)]
     dist.all_gather(gathered, mine)
     same = all(torch.equal(g, mine) for g in gathered)
-    result = {"model": a.model, "tp": world, "ranks_agree": bool(same), "seconds": dt}
+    result = {"model": a.model, "tp": world, "ranks_agree": bool(same), "seconds": dt,
+              "nvls": ctx.nvls_ready(), "nvls_status": ctx.nvls_status()}
     if a.chunked:
         result.update(chunked_budget=a.chunked, mixed_steps=mixed)
         same = same and mixed > 0

@@ -264,7 +264,11 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
   else G = 1;
   const int chunks = (group + G - 1) / G;
   const int max_tiles = (int)(((int64_t)max_blocks_hint * block_size + kTile - 1) / kTile);
-  int splits = (2 * ctx->num_sms + B * kv * chunks - 1) / (B * kv * chunks);
+  // KV splits: only when the (sequence, kv head) grid leaves most of the 2 x 148 resident slots empty, and never
+  // beyond them (tools/decode_microbench.py --splits, profiles/r02_pd_split_sweep.txt: 64 CTAs -> 4 splits 10.3 ->
+  // 7.6 us, 128 -> 2, 256 and up -> 1; rounding the split count UP to cover the slots cost 3 - 5 us on the
+  // TP-sharded shapes through the second wave it created)
+  int splits = 2 * ctx->num_sms / (B * kv * chunks);
   const int cap = max_splits_for_batch(B, ctx->num_sms);
   if (splits > cap) splits = cap;
   if (splits > max_tiles) splits = max_tiles;
@@ -309,9 +313,11 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
     part_ml = part_o + (size_t)B * nh * splits * hd;
   }
   dim3 grid(kv * chunks, B, splits);
-  // splits merged by the last CTA to arrive (tickets in pd_counters) instead of a second kernel
+  // splits merged by the last CTA to arrive (tickets in pd_counters) instead of the combine kernel
+  // (opt-in, NVC_PD_FUSED_MERGE=1: measured 2 - 4 us SLOWER than the combine kernel on every shape of the sweep - the
+  // last arriver walks heads x splits dependent L2 loads alone, the combine kernel spreads them over nh x B CTAs)
   const bool fused_merge = !use_simt && splits > 1 && ctx->pd_counters != nullptr && (int64_t)kv * chunks * B <= kFlatMaxPairs &&
-                           !(getenv("NVC_PD_COMBINE_KERNEL") && atoi(getenv("NVC_PD_COMBINE_KERNEL")) != 0);
+                           getenv("NVC_PD_FUSED_MERGE") && atoi(getenv("NVC_PD_FUSED_MERGE")) != 0;
   auto kc = reinterpret_cast<const uint4*>(k_cache);
   auto vc = reinterpret_cast<const uint4*>(v_cache);
 #define NVC_LAUNCH_PD(GV)                                                                                   \

@@ -58,6 +58,9 @@ struct nvc_runner {
   ArgPair* d_pairs = nullptr;
   int32_t* h_stage = nullptr;   // pinned
   size_t h_stage_ints = 0;
+  size_t in_pitch = 0;             // ints between d_ids / d_pos / d_slots / d_ctx (one block: a decode step uploads all four in ONE 2-D copy)
+  std::vector<int32_t> bt_mirror;  // the padded block table the device holds (decode steps re-upload it only when it changed)
+  int bt_mirror_B = -1;            // rows of bt_mirror that are valid; -1: unknown (a prefill / mixed step wrote d_bt)
   ArgPair* h_pairs = nullptr;   // pinned
   int32_t* h_tok = nullptr;     // pinned
   int last_B = 0;
@@ -237,17 +240,28 @@ int run_head(nvc_runner* r, int B, bool decode, bool final_norm_done) {
   return nvc_allgather_bytes(ctx, r->d_pairs, (size_t)B * sizeof(ArgPair), st);
 }
 
-int finish_tokens(nvc_runner* r, int B, int32_t* out_tokens) {
-  if (r->tp == 1 || (r->x_nvls && nvc_ctx_nvls_ready(r->ctx) && (size_t)B * r->tp * 16 <= nvc_ctx_nvls_ll_bytes(r->ctx))) {
+bool merged_on_device(const nvc_runner* r, int B) {
+  return r->tp == 1 || (r->x_nvls && nvc_ctx_nvls_ready(r->ctx) && (size_t)B * r->tp * 16 <= nvc_ctx_nvls_ll_bytes(r->ctx));
+}
+
+// device -> pinned host copy of the step's result (capturable: the decode graph ends with it)
+int enqueue_token_readback(nvc_runner* r, int B) {
+  if (merged_on_device(r, B)) {
     R_CUDA(cudaMemcpyAsync(r->h_tok, r->d_tok, B * sizeof(int32_t), cudaMemcpyDeviceToHost, r->stream));
-    R_CUDA(cudaStreamSynchronize(r->stream));
+  } else {
+    R_CUDA(cudaMemcpyAsync(r->h_pairs, r->d_pairs, (size_t)r->tp * B * sizeof(ArgPair), cudaMemcpyDeviceToHost, r->stream));
+  }
+  return NVC_OK;
+}
+
+// after the stream has drained
+int collect_tokens(nvc_runner* r, int B, int32_t* out_tokens) {
+  if (merged_on_device(r, B)) {
     memcpy(out_tokens, r->h_tok, B * sizeof(int32_t));
     return NVC_OK;
   }
-  // TP: pick the largest value over the gathered shard maxima, ties -> the larger index
+  // TP without the switch: pick the largest value over the gathered shard maxima, ties -> the larger index
   // (= the reference's "last maximum" over the full row).
-  R_CUDA(cudaMemcpyAsync(r->h_pairs, r->d_pairs, (size_t)r->tp * B * sizeof(ArgPair), cudaMemcpyDeviceToHost, r->stream));
-  R_CUDA(cudaStreamSynchronize(r->stream));
   for (int b = 0; b < B; ++b) {
     ArgPair best = r->h_pairs[b];
     for (int k = 1; k < r->tp; ++k) {
@@ -257,6 +271,13 @@ int finish_tokens(nvc_runner* r, int B, int32_t* out_tokens) {
     out_tokens[b] = best.idx;
   }
   return NVC_OK;
+}
+
+int finish_tokens(nvc_runner* r, int B, int32_t* out_tokens) {
+  int rc = enqueue_token_readback(r, B);
+  if (rc) return rc;
+  R_CUDA(cudaStreamSynchronize(r->stream));
+  return collect_tokens(r, B, out_tokens);
 }
 
 int decode_body(nvc_runner* r, int B, int blocks_hint) {
@@ -368,13 +389,18 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   for (int b = 1; b <= opt->max_num_seqs; ++b)
     r->decode_ws_bytes = std::max(r->decode_ws_bytes, nvc_paged_decode_workspace_bytes(b, r->nh_l, hd, ctx->num_sms));
   if ((rc = dev_alloc(r, reinterpret_cast<uint8_t**>(&r->decode_ws), r->decode_ws_bytes))) return rc;
-  if ((rc = dev_alloc(r, &r->d_ids, T))) return rc;
-  if ((rc = dev_alloc(r, &r->d_pos, T))) return rc;
-  if ((rc = dev_alloc(r, &r->d_slots, T))) return rc;
+  {
+    r->in_pitch = (std::max(T, Bm) + 3) / 4 * 4;
+    int32_t* blk = nullptr;
+    if ((rc = dev_alloc(r, &blk, 4 * r->in_pitch))) return rc;
+    r->d_ids = blk;
+    r->d_pos = blk + r->in_pitch;
+    r->d_slots = blk + 2 * r->in_pitch;
+    r->d_ctx = blk + 3 * r->in_pitch;
+  }
   if ((rc = dev_alloc(r, &r->d_cu, Bm + 1))) return rc;
   if ((rc = dev_alloc(r, &r->d_cu2, Bm + 1))) return rc;
   if ((rc = dev_alloc(r, &r->d_bt, Bm * r->max_blocks_cap))) return rc;
-  if ((rc = dev_alloc(r, &r->d_ctx, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_last_rows, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_tok, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_tok_val, Bm))) return rc;
@@ -385,6 +411,7 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   R_CUDA(cudaMallocHost(&r->h_streams, Bm * sizeof(uint64_t)));
   r->h_stage_ints = 3 * T + 2 * (Bm + 1) + Bm * r->max_blocks_cap + 2 * Bm;
   R_CUDA(cudaMallocHost(&r->h_stage, r->h_stage_ints * sizeof(int32_t)));
+  r->bt_mirror.assign(Bm * r->max_blocks_cap, -1);
   R_CUDA(cudaMallocHost(&r->h_pairs, Bm * tp * sizeof(ArgPair)));
   R_CUDA(cudaMallocHost(&r->h_tok, Bm * sizeof(int32_t)));
   return NVC_OK;
@@ -608,6 +635,7 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
       for (int j = max_blocks; j < cap; ++j) hbt[(size_t)b * cap + j] = -1;
     }
     R_CUDA(cudaMemcpyAsync(r->d_ctx, hctx, B * 4, cudaMemcpyHostToDevice, st));
+    r->bt_mirror_B = -1;           // the decode path's cached copy no longer describes d_bt
     R_CUDA(cudaMemcpyAsync(r->d_bt, hbt, (size_t)B * cap * 4, cudaMemcpyHostToDevice, st));
     if (num_decode > 0 && num_decode < B) {
       int32_t* hcu2 = hbt + (size_t)B * cap;
@@ -685,9 +713,8 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
     NVC_REQUIRE(ctx, positions[b] >= 0 && positions[b] < r->opt.max_model_len, NVC_EINVAL, "position out of range");
     NVC_REQUIRE(ctx, slot_mapping[b] >= 0 && slot_mapping[b] < nslots, NVC_EINVAL, "slot out of range");
     NVC_REQUIRE(ctx, context_lens[b] > 0 && (int64_t)context_lens[b] <= (int64_t)max_blocks * bs, NVC_EINVAL, "context_len vs block table");
-    for (int j = 0; j < (context_lens[b] + bs - 1) / bs; ++j)
-      NVC_REQUIRE(ctx, block_tables[(size_t)b * max_blocks + j] >= 0 &&
-                           block_tables[(size_t)b * max_blocks + j] < r->opt.num_kvcache_blocks, NVC_EINVAL, "block id out of range");
+    for (int j = 0; j < (context_lens[b] + bs - 1) / bs; ++j)     // the blocks the context needs exist (range: below, on upload)
+      NVC_REQUIRE(ctx, block_tables[(size_t)b * max_blocks + j] >= 0, NVC_EINVAL, "block id out of range");
   }
   NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
   int32_t* h = r->h_stage;
@@ -695,23 +722,46 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
   memcpy(h + B, positions, B * 4);
   memcpy(h + 2 * B, slot_mapping, B * 4);
   memcpy(h + 3 * B, context_lens, B * 4);
+  cudaStream_t st = r->stream;
+  // block table: the device copy is kept between decode steps; a row changes only when a sequence crosses a block
+  // boundary or the batch changes, so most steps upload (and validate) nothing but the 4 x B scalars above
   int32_t* hbt = h + 4 * B;
   const int cap = r->max_blocks_cap;
+  bool bt_changed = r->bt_mirror_B != B;
   for (int b = 0; b < B; ++b) {
-    memcpy(hbt + (size_t)b * cap, block_tables + (size_t)b * max_blocks, max_blocks * 4);
-    for (int j = max_blocks; j < cap; ++j) hbt[(size_t)b * cap + j] = -1;
+    int32_t* row = hbt + (size_t)b * cap;
+    memcpy(row, block_tables + (size_t)b * max_blocks, max_blocks * 4);
+    for (int j = max_blocks; j < cap; ++j) row[j] = -1;
+    bt_changed = bt_changed || memcmp(row, r->bt_mirror.data() + (size_t)b * cap, (size_t)cap * 4) != 0;
   }
-  cudaStream_t st = r->stream;
-  R_CUDA(cudaMemcpyAsync(r->d_ids, h, B * 4, cudaMemcpyHostToDevice, st));
-  R_CUDA(cudaMemcpyAsync(r->d_pos, h + B, B * 4, cudaMemcpyHostToDevice, st));
-  R_CUDA(cudaMemcpyAsync(r->d_slots, h + 2 * B, B * 4, cudaMemcpyHostToDevice, st));
-  R_CUDA(cudaMemcpyAsync(r->d_ctx, h + 3 * B, B * 4, cudaMemcpyHostToDevice, st));
-  R_CUDA(cudaMemcpyAsync(r->d_bt, hbt, (size_t)B * cap * 4, cudaMemcpyHostToDevice, st));
-  r->last_h2d_bytes = (int64_t)B * 16 + (int64_t)B * cap * 4;
+  r->last_h2d_bytes = (int64_t)B * 16;
+  if (bt_changed) {
+    for (int b = 0; b < B; ++b)
+      for (int j = 0; j < max_blocks; ++j) {
+        const int32_t id = hbt[(size_t)b * cap + j];
+        NVC_REQUIRE(ctx, id >= -1 && id < r->opt.num_kvcache_blocks, NVC_EINVAL, "block id out of range");
+      }
+    R_CUDA(cudaMemcpyAsync(r->d_bt, hbt, (size_t)B * cap * 4, cudaMemcpyHostToDevice, st));
+    memcpy(r->bt_mirror.data(), hbt, (size_t)B * cap * 4);
+    r->bt_mirror_B = B;
+    r->last_h2d_bytes += (int64_t)B * cap * 4;
+  }
   const int hint = std::min(next_pow2(max_blocks), cap);
-  int rc = stage_sampling(r, B);
-  if (rc) return rc;
+  if (r->sampling_armed)
+    NVC_REQUIRE(ctx, r->last_sampling_B == B, NVC_ESTATE, "nvc_runner_set_sampling was armed for a different batch size");
   const int key2 = 2 * hint + (r->sampling_armed ? 1 : 0);
+  // the whole step - one strided H2D of the four input rows, the sampling parameters, the kernels, the D2H of the
+  // tokens - is ONE graph launch: the host touches pinned memory, launches, and waits
+  auto whole_step = [&]() -> int {
+    cudaError_t ce = cudaMemcpy2DAsync(r->d_ids, r->in_pitch * 4, h, (size_t)B * 4, (size_t)B * 4, 4, cudaMemcpyHostToDevice, st);
+    if (ce != cudaSuccess) return NVC_CUDA_ERROR_BASE + (int)ce;
+    int rc2 = stage_sampling(r, B);
+    if (rc2) return rc2;
+    rc2 = decode_body(r, B, hint);
+    if (rc2) return rc2;
+    return enqueue_token_readback(r, B);
+  };
+  int rc = NVC_OK;
   if (r->opt.use_cuda_graph) {
     const auto key = std::make_pair(B, key2);
     auto it = r->graphs.find(key);
@@ -719,7 +769,7 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
       // capture this (batch size, context bucket) once; pointers and shapes are fixed inside
       const uint64_t l0 = ctx->launches;
       R_CUDA(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-      rc = decode_body(r, B, hint);
+      rc = whole_step();
       cudaGraph_t graph = nullptr;
       cudaError_t ce = cudaStreamEndCapture(st, &graph);
       if (rc) { r->sampling_armed = false; if (graph) cudaGraphDestroy(graph); return rc; }
@@ -734,7 +784,7 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
     R_CUDA(cudaGraphLaunch(it->second, st));
   } else {
     const uint64_t l0 = ctx->launches;
-    rc = decode_body(r, B, hint);
+    rc = whole_step();
     if (rc) { r->sampling_armed = false; return rc; }
     r->launches_per_decode = (int)(ctx->launches - l0);
   }
@@ -742,7 +792,8 @@ extern "C" int nvc_runner_decode(nvc_runner* r, const int32_t* ids, const int32_
   r->last_B = B;
   r->last_decode_hint = hint;
   r->last_decode_key2 = key2;
-  return finish_tokens(r, B, out_tokens);
+  R_CUDA(cudaStreamSynchronize(st));
+  return collect_tokens(r, B, out_tokens);
 }
 
 extern "C" int nvc_runner_set_sampling(nvc_runner* r, const float* temperatures, const uint64_t* streams, int B,

@@ -450,3 +450,32 @@ def test_paged_decode_balanced(ctx, nvc, nh, kv, block_size, lens_spec):
     assert not torch.isnan(o1.float()).any(), "poisoned (unwritten) cache slots leaked into the output"
     _close(o1, ref, 1e-2, 2 ** -7, f"balanced paged decode nh={nh} kv={kv} bs={block_size} B={B}")
     assert torch.equal(o1, o2), "balanced paged decode must be bit-identical between launches"
+
+
+@pytest.mark.parametrize("nh,kv,block_size,lens,splits", [
+    (16, 8, 256, [2048], 8),                    # one sequence: the small-batch case the splits exist for
+    (2, 1, 256, [581] * 64, 4),                 # a TP=8 shard of the bench shape: 64 CTAs -> 4 splits
+    (32, 8, 64, [700, 3, 1025, 64, 65], 3),     # ragged: some splits own no tile at all
+])
+def test_paged_decode_split_merge_variants(ctx, nh, kv, block_size, lens, splits):
+    """KV splits: the separate combine kernel (default) and the merge by the last CTA to arrive (opt-in) sum the
+    partial (m, l, o) states in split order, so both must match the oracle and each other bit for bit; the second
+    fused call proves the tickets were re-armed."""
+    import os
+    q, kc, vc, bt, ref, scale = _paged_case(nh, kv, block_size, lens, 11 + len(lens))
+    B = len(lens)
+    args = (q.reshape(B, nh * 128).cuda(), kc.cuda(), vc.cuda(), bt.cuda(), torch.tensor(lens, dtype=torch.int32).cuda(),
+            nh, kv, 128, block_size, scale)
+    os.environ["NVC_PD_SPLITS"] = str(splits)
+    try:
+        a = ctx.paged_decode_attn(*args).clone()
+        os.environ["NVC_PD_FUSED_MERGE"] = "1"
+        b1 = ctx.paged_decode_attn(*args).clone()
+        b2 = ctx.paged_decode_attn(*args).clone()
+        torch.cuda.synchronize()
+    finally:
+        os.environ.pop("NVC_PD_SPLITS", None)
+        os.environ.pop("NVC_PD_FUSED_MERGE", None)
+    assert not torch.isnan(a.float()).any() and not torch.isnan(b1.float()).any()
+    _close(a, ref, 1e-2, 2 ** -7, f"split paged decode (combine kernel) nh={nh} kv={kv} S={splits}")
+    assert torch.equal(a, b1) and torch.equal(b1, b2), "fused merge must equal the combine kernel bit for bit"

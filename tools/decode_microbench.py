@@ -66,7 +66,7 @@ def sweep_splits():
                                ("0.6B bs1 ctx2048", 1, 16, 8, 2048), ("8B bs1 ctx1024", 1, 32, 8, 1024), ("8B bs16 ctx1024", 16, 32, 8, 1024)]:
         row = []
         for comb in (0, 1):
-            os.environ["NVC_PD_COMBINE_KERNEL"] = str(comb)
+            os.environ["NVC_PD_FUSED_MERGE"] = str(1 - comb)
             for s in (0, 1, 2, 3, 4, 5, 6, 8, 12, 16):
                 if s:
                     os.environ["NVC_PD_SPLITS"] = str(s)
@@ -77,7 +77,7 @@ def sweep_splits():
                 us, gbs = bench(B, nh, kv, c, pools=8)
                 row.append(f"{'comb' if comb else 'fused'} S={s or 'auto'}: {us:.2f}")
         os.environ.pop("NVC_PD_SPLITS", None)
-        os.environ.pop("NVC_PD_COMBINE_KERNEL", None)
+        os.environ.pop("NVC_PD_FUSED_MERGE", None)
         print(f"{name:24s} " + " | ".join(row), flush=True)
 
 

@@ -223,3 +223,92 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
     s0 = __ldg(cs + 16 + 2 * l8); s1 = __ldg(cs + 16 + 2 * l8 + 1);
   }
   pdl_wait();
+  // ---- Q as A fragments: 8 k-steps of 16 dims; rows >= G are zero
+  uint32_t qa[8][4];
+  if (kFused) {
+    // 8 lanes per head: normalise + rotate the raw q rows of the group into shared memory (16-byte chunk c of row u
+    // at chunk c ^ (u & 7)), rows >= G as zeros
+    for (int u = warp * 4 + (lane >> 3); u < 16; u += kWarps * 4) {
+      const bool act = u < G;
+      const uint4* row = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(head0 + (act ? u : 0)) * 128);
+      uint4 o1, o2;
+      norm_rope_unit(act, row, l8, mask8, qw_lo, qw_hi, c0, c1, s0, s1, fa.eps, o1, o2);
+      st_shared_u4(q_sm + u * 256 + ((l8 ^ (u & 7)) << 4), o1);
+      st_shared_u4(q_sm + u * 256 + (((l8 + 8) ^ (u & 7)) << 4), o2);
+    }
+    if (owner) {
+      // the step's new k row (lanes 0..7, same unit arithmetic) and v row (lanes 16..31, one 16-byte chunk each):
+      // kept in registers for the tile patch below; the CTA of the group's first chunk writes them to the cache
+      const uint4* krow = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(nh + kvh) * 128);
+      const uint4* vrow = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(nh + kv + kvh) * 128);
+      norm_rope_unit(lane < 8, krow, l8, mask8, kw_lo, kw_hi, c0, c1, s0, s1, fa.eps, k_new1, k_new2);
+      if (lane >= 16) v_new = vrow[lane - 16];
+      const int slot = __ldg(fa.slot_mapping + b);
+      if (chunk == 0 && slot >= 0) {
+        if (lane < 8) {
+          uint4* dst = reinterpret_cast<uint4*>(fa.k_cache_w) + ((int64_t)slot * kv + kvh) * 16;
+          dst[lane] = k_new1;
+          dst[lane + 8] = k_new2;
+        } else if (lane >= 16) {
+          reinterpret_cast<uint4*>(fa.v_cache_w)[((int64_t)slot * kv + kvh) * 16 + (lane - 16)] = v_new;
+        }
+      }
+    }
+    __syncthreads();
+    // ldmatrix.x4: matrices (rows 0-7, k lo), (rows 8-15, k lo), (rows 0-7, k hi), (rows 8-15, k hi) = a0..a3
+    const int mi = lane >> 3;
+    const int row = (lane & 7) + ((mi & 1) << 3);
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      const int c = 2 * ks + (mi >> 1);
+      ldmatrix_x4(q_sm + row * 256 + ((c ^ (row & 7)) << 4), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
+    }
+  } else {
+    const nvc_bf16* qrow0 = q + (int64_t)b * ldq + (int64_t)(head0 + quad) * 128;
+    const nvc_bf16* qrow1 = qrow0 + 8 * 128;
+    const bool r0 = quad < G, r1 = quad + 8 < G;
+#pragma unroll
+    for (int ks = 0; ks < 8; ++ks) {
+      const int d = ks * 16 + 2 * tq;
+      qa[ks][0] = r0 ? __ldg(reinterpret_cast<const uint32_t*>(qrow0 + d)) : 0u;
+      qa[ks][1] = r1 ? __ldg(reinterpret_cast<const uint32_t*>(qrow1 + d)) : 0u;
+      qa[ks][2] = r0 ? __ldg(reinterpret_cast<const uint32_t*>(qrow0 + d + 8)) : 0u;
+      qa[ks][3] = r1 ? __ldg(reinterpret_cast<const uint32_t*>(qrow1 + d + 8)) : 0u;
+    }
+  }
+  if (pre < 1) issue(0);
+  if (pre < 2) issue(1);
+  for (int i = 0; i < my_tiles; ++i) {
+    issue(i + 2);
+    cp_async_wait<2>();                               // tile i has landed (two younger groups may be in flight)
+    __syncwarp();
+    const int tok0 = (t_begin + i) * kCtaTok + warp * kTileTok;
+    if (tok0 < ctx_len) {                             // warp-uniform
+      const uint32_t st = ring + (i % kStages) * kStageBytes;
+      if (kFused && owner && tok0 + r_new == pos_new) {
+        // the zero-filled row of the new token becomes the k / v computed above
+        if (lane < 8) {
+          st_shared_u4(st + r_new * 256 + ((lane ^ (r_new & 7)) << 4), k_new1);
+          st_shared_u4(st + r_new * 256 + (((lane + 8) ^ (r_new & 7)) << 4), k_new2);
+        } else if (lane >= 16) {
+          st_shared_u4(st + kTileTok * 256 + r_new * 256 + (((lane - 16) ^ (r_new & 7)) << 4), v_new);
+        }
+        __syncwarp();
+      }
+      // ---- S = Q K^T: two n-tiles of 8 tokens, fp32
+      float s[2][4];
+#pragma unroll
+      for (int j = 0; j < 2; ++j) s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f;
+      {
+        // ldmatrix.x4: matrices (tok 0-7, d lo), (tok 0-7, d hi), (tok 8-15, d lo), (tok 8-15, d hi)
+        const int r = (lane & 7) + ((lane >> 4) << 3);
+        const int chi = (lane >> 3) & 1;
+#pragma unroll
+        for (int ks = 0; ks < 8; ++ks) {
+          const int c = 2 * ks + chi;
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4(st + r * 256 + ((c ^ (r & 7)) << 4), b0, b1, b2, b3);
+          mma_bf16(s[0], qa[ks], b0, b1);
+          mma_bf16(s[1], qa[ks], b2, b3);
+        }
+      }

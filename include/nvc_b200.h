@@ -243,6 +243,21 @@ int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf
                           float scale, nvc_bf16* out, void* workspace, size_t workspace_bytes,
                           void* stream);
 
+/* K2 + K5 in one launch for a pure decode step (one new token per sequence; replaces the q_norm / k_norm / RoPE /
+ * cache-store / attention sequence of src/models/qwen3.rs:205-277 for that step kind).  qkv: RAW fused projection
+ * rows [B, (nh + 2 kv) * hd] (row stride ldq), not modified.  q and the new k are RMS-normalised (q_norm_w, k_norm_w,
+ * eps) and rotated with the cos / sin row of positions[b] exactly as nvc_qk_norm_rope_store does (bit-identical);
+ * the new k / v rows are written to the caches at slot_mapping[b], which must be the slot of position
+ * context_lens[b] - 1 in block_tables.  Other arguments as nvc_paged_decode_attn; max_blocks_hint bounds the
+ * blocks any sequence uses (split choice; pass max_blocks when unknown). */
+int nvc_paged_decode_attn_fused(nvc_ctx* ctx, const nvc_bf16* qkv, int ldq, const nvc_bf16* q_norm_w,
+                                const nvc_bf16* k_norm_w, float eps, const float* cos_sin,
+                                const int32_t* positions, const int32_t* slot_mapping, nvc_bf16* k_cache,
+                                nvc_bf16* v_cache, const int32_t* block_tables, int max_blocks,
+                                int max_blocks_hint, const int32_t* context_lens, int B, int nh, int kv, int hd,
+                                int block_size, float scale, nvc_bf16* out, void* workspace,
+                                size_t workspace_bytes, void* stream);
+
 /* K6. Replaces SiluAndMul::forward (src/layers/activation.rs:13-18):
  * out[n, i] = silu(x[n, i]) * x[n, I + i]. */
 int nvc_silu_and_mul(nvc_ctx* ctx, const nvc_bf16* x, nvc_bf16* out, int N, int I, void* stream);

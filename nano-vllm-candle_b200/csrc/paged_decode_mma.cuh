@@ -312,3 +312,114 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
           mma_bf16(s[1], qa[ks], b2, b3);
         }
       }
+      // ---- online softmax on the fragments (rows quad and quad + 8; columns tok0 + 8j + 2tq + {0,1})
+      float mx0 = -INFINITY, mx1 = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int t0 = tok0 + 8 * j + 2 * tq;
+        const bool v0 = t0 < ctx_len, v1 = t0 + 1 < ctx_len;
+        s[j][0] = v0 ? s[j][0] * scale_log2e : -INFINITY;
+        s[j][1] = v1 ? s[j][1] * scale_log2e : -INFINITY;
+        s[j][2] = v0 ? s[j][2] * scale_log2e : -INFINITY;
+        s[j][3] = v1 ? s[j][3] * scale_log2e : -INFINITY;
+        mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
+        mx1 = fmaxf(mx1, fmaxf(s[j][2], s[j][3]));
+      }
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+      mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+      mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+      const float mn0 = fmaxf(m0, mx0), mn1 = fmaxf(m1, mx1);      // tok0 < ctx_len: token tok0 is valid, so finite
+      const float al0 = fast_exp2(m0 - mn0), al1 = fast_exp2(m1 - mn1);
+      m0 = mn0;
+      m1 = mn1;
+      uint32_t pa[4];
+      float ps0 = 0.f, ps1 = 0.f;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const float p0 = fast_exp2(s[j][0] - mn0), p1 = fast_exp2(s[j][1] - mn0);
+        const float p2 = fast_exp2(s[j][2] - mn1), p3 = fast_exp2(s[j][3] - mn1);
+        ps0 += p0 + p1;
+        ps1 += p2 + p3;
+        pa[2 * j] = pack_bf16(p0, p1);                 // A fragment of P: a0/a2 = row quad, a1/a3 = row quad + 8
+        pa[2 * j + 1] = pack_bf16(p2, p3);
+      }
+      l0 = l0 * al0 + ps0;
+      l1 = l1 * al1 + ps1;
+#pragma unroll
+      for (int nt = 0; nt < 16; ++nt) {
+        o[nt][0] *= al0; o[nt][1] *= al0;
+        o[nt][2] *= al1; o[nt][3] *= al1;
+      }
+      // ---- O += P V: ldmatrix.trans: matrices (tok 0-7, d-chunk nt), (tok 8-15, nt), (tok 0-7, nt+1), (tok 8-15, nt+1)
+      {
+        const uint32_t vs = st + kTileTok * 256;
+        const int r = (lane & 7) + (((lane >> 3) & 1) << 3);
+        const int cadd = lane >> 4;
+#pragma unroll
+        for (int np = 0; np < 8; ++np) {
+          const int c = 2 * np + cadd;
+          uint32_t b0, b1, b2, b3;
+          ldmatrix_x4_trans(vs + r * 256 + ((c ^ (r & 7)) << 4), b0, b1, b2, b3);
+          mma_bf16(o[2 * np], pa, b0, b1);
+          mma_bf16(o[2 * np + 1], pa, b2, b3);
+        }
+      }
+    }
+    __syncwarp();                                     // everyone is done with stage i % kStages before it is refilled
+  }
+  cp_async_wait<0>();
+  // row sums live per lane of a quad: finish them
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+
+
+  // ---- merge the warps through shared memory (the rings are dead now; the fused q rows sit behind them)
+  __syncthreads();
+  float* sm_m = reinterpret_cast<float*>(smem);                    // [kWarps][16]
+  float* sm_l = sm_m + kWarps * 16;                                // [kWarps][16]
+  float* sm_o = sm_l + kWarps * 16;                                // [kWarps][16][128]
+  if (tq == 0) {
+    sm_m[warp * 16 + quad] = m0;
+    sm_m[warp * 16 + quad + 8] = m1;
+    sm_l[warp * 16 + quad] = l0;
+    sm_l[warp * 16 + quad + 8] = l1;
+  }
+#pragma unroll
+  for (int nt = 0; nt < 16; ++nt) {
+    const int d = nt * 8 + 2 * tq;
+    float* r0 = sm_o + (warp * 16 + quad) * 128 + d;
+    float* r1 = sm_o + (warp * 16 + quad + 8) * 128 + d;
+    r0[0] = o[nt][0]; r0[1] = o[nt][1];
+    r1[0] = o[nt][2]; r1[1] = o[nt][3];
+  }
+  __syncthreads();
+  for (int idx = threadIdx.x; idx < G * 128; idx += kThreads) {
+    const int g = idx >> 7, d = idx & 127;
+    float M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) M = fmaxf(M, sm_m[w * 16 + g]);
+    float L = 0.f, O = 0.f;
+    if (M != -INFINITY) {
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) {
+        const float wt = fast_exp2(sm_m[w * 16 + g] - M);
+        L += sm_l[w * 16 + g] * wt;
+        O += sm_o[(w * 16 + g) * 128 + d] * wt;
+      }
+    }
+    const int head = head0 + g;
+    if (num_splits == 1) {
+      const float r = L > 0.f ? O / L : 0.f;
+      out[((int64_t)b * nh + head) * 128 + d] = __bfloat16_as_ushort(__float2bfloat16_rn(r));
+    } else {
+      const int64_t p = ((int64_t)b * nh + head) * num_splits + split;
+      __stcg(part_o + p * 128 + d, O);
+      if (d == 0) { __stcg(part_ml + p * 2, M); __stcg(part_ml + p * 2 + 1, L); }
+    }
+  }
+}
+
+}  // namespace pdmma

@@ -53,7 +53,7 @@ struct nvc_runner {
   // step inputs on device + pinned staging
   int32_t* d_cu2 = nullptr;     // mixed step: cu_seqlens of the prompt chunks, relative to their first token
   int32_t *d_ids = nullptr, *d_pos = nullptr, *d_cu = nullptr, *d_slots = nullptr, *d_bt = nullptr, *d_ctx = nullptr,
-          *d_last_rows = nullptr, *d_tok = nullptr;
+          *d_last_rows = nullptr, *d_tok = nullptr, *d_neg = nullptr;   // d_neg: max_num_seqs x -1
   float* d_tok_val = nullptr;
   ArgPair* d_pairs = nullptr;
   int32_t* h_stage = nullptr;   // pinned
@@ -113,6 +113,7 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
   const int H = c.hidden_size, hd = c.head_dim, L = c.num_hidden_layers;
   const float scale = 1.0f / sqrtf((float)hd);   // (head_dim as f32).powf(-0.5), qwen3.rs:132
   static const bool p2p_env = !(getenv("NVC_P2P_AR") && atoi(getenv("NVC_P2P_AR")) == 0);
+  static const bool fused_k2 = !(getenv("NVC_FUSED_K2") && atoi(getenv("NVC_FUSED_K2")) == 0);
   // NVLS (in-switch) all-reduce + residual + norm for every step kind; else the peer-load kernel for decode-sized
   // messages; else NCCL + the norm kernel
   const bool nvls = r->tp > 1 && r->x_nvls && nvc_ctx_nvls_ready(ctx);
@@ -133,10 +134,18 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     xn_ready = false;
     rc = nvc_gemm_bf16(ctx, r->xn, H, Ly.w_qkv, r->qkv, r->qkv_l, NVC_DT_BF16, N, r->qkv_l, H, st);
     if (rc) return rc;
-    rc = nvc_qk_norm_rope_store(ctx, r->qkv, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos, r->d_slots,
-                                Ly.k_cache, Ly.v_cache, N, r->nh_l, r->kv_l, hd, st);
-    if (rc) return rc;
-    if (decode) {
+    // pure decode step: K2 (q/k-norm + RoPE + store of the new token) runs inside the paged decode kernel's prologue
+    if (!(decode && fused_k2)) {
+      rc = nvc_qk_norm_rope_store(ctx, r->qkv, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos, r->d_slots,
+                                  Ly.k_cache, Ly.v_cache, N, r->nh_l, r->kv_l, hd, st);
+      if (rc) return rc;
+    }
+    if (decode && fused_k2) {
+      rc = nvc_paged_decode_attn_fused(ctx, r->qkv, r->qkv_l, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos,
+                                       r->d_slots, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint, r->d_ctx,
+                                       B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn, r->decode_ws,
+                                       r->decode_ws_bytes, st);
+    } else if (decode) {
       rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
                                     r->d_ctx, B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
                                     r->decode_ws, r->decode_ws_bytes, st);
@@ -403,6 +412,8 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if ((rc = dev_alloc(r, &r->d_bt, Bm * r->max_blocks_cap))) return rc;
   if ((rc = dev_alloc(r, &r->d_last_rows, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_tok, Bm))) return rc;
+  if ((rc = dev_alloc(r, &r->d_neg, Bm))) return rc;
+  R_CUDA(cudaMemset(r->d_neg, 0xff, Bm * sizeof(int32_t)));
   if ((rc = dev_alloc(r, &r->d_tok_val, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_pairs, Bm * tp))) return rc;
   if ((rc = dev_alloc(r, &r->d_temps, Bm))) return rc;
@@ -907,6 +918,15 @@ extern "C" int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_pe
       Layer& L = r->layers[li];
       switch (op) {
         case NVC_OP_PAGED_DECODE:
+          // what the decode step launches: K2 folded in (slots of -1: the timing runs must not write the caches), or
+          // the plain kernel when NVC_FUSED_K2=0
+          if (!(getenv("NVC_FUSED_K2") && atoi(getenv("NVC_FUSED_K2")) == 0)) {
+            rc = nvc_paged_decode_attn_fused(ctx, r->qkv, r->qkv_l, L.q_norm, L.k_norm, c.rms_norm_eps, r->rope, r->d_pos,
+                                             r->d_neg, L.k_cache, L.v_cache, r->d_bt, r->max_blocks_cap, r->last_decode_hint,
+                                             r->d_ctx, B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
+                                             r->decode_ws, r->decode_ws_bytes, st);
+            break;
+          }
           rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, L.k_cache, L.v_cache, r->d_bt, r->max_blocks_cap,
                                         r->last_decode_hint, r->d_ctx, B, r->nh_l, r->kv_l, hd,
                                         r->opt.kvcache_block_size, scale, r->attn, r->decode_ws, r->decode_ws_bytes, st);

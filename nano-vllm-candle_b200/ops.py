@@ -245,6 +245,25 @@ class Context:
                                               self._ws.numel(), _stream()), "nvc_paged_decode_attn")
         return out
 
+    def paged_decode_attn_fused(self, qkv, q_norm_w, k_norm_w, eps, cos_sin, positions, slot_mapping, k_cache, v_cache,
+                                block_tables, context_lens, nh, kv, hd, block_size, scale, out=None):
+        """K2 + K5 in one launch (pure decode step): raw fused qkv rows in; the new k / v rows are written to the caches."""
+        _req(qkv, BF16, "qkv"); _req(block_tables, torch.int32, "block_tables"); _req(context_lens, torch.int32, "context_lens")
+        _req(positions, torch.int32, "positions"); _req(slot_mapping, torch.int32, "slot_mapping")
+        _req(cos_sin, torch.float32, "cos_sin")
+        B = qkv.shape[0]
+        out = torch.empty((B, nh * hd), dtype=BF16, device=qkv.device) if out is None else out
+        need = self.l.nvc_paged_decode_workspace_bytes(B, nh, hd, self.num_sms)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = torch.empty(max(need, 1), dtype=torch.uint8, device=qkv.device)
+        self._ck(self.l.nvc_paged_decode_attn_fused(self.h, _ptr(qkv), qkv.stride(0), _ptr(q_norm_w), _ptr(k_norm_w),
+                                                    float(eps), _ptr(cos_sin), _ptr(positions), _ptr(slot_mapping),
+                                                    _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), block_tables.shape[1],
+                                                    block_tables.shape[1], _ptr(context_lens), B, nh, kv, hd, block_size,
+                                                    float(scale), _ptr(out), _ptr(self._ws), self._ws.numel(), _stream()),
+                 "nvc_paged_decode_attn_fused")
+        return out
+
     def silu_and_mul(self, x, out=None):
         _req(x, BF16, "x")
         N, I2 = x.shape

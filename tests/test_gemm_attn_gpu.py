@@ -415,67 +415,119 @@ def _paged_case(nh, kv, block_size, ctx_lens, seed):
     return q, kc, vc, bt, ref, scale
 
 
-@pytest.mark.parametrize("nh,kv,block_size,lens_spec", [
-    (16, 8, 256, ("uniform", 48, 1, 700, 1)),        # ragged batch: CTA ranges cross many (kv head, sequence) pairs
-    (16, 8, 256, ("const", 64, 581)),                # the bench shape: 512 pairs of 10 tiles on 296 CTAs
-    (32, 8, 64, ("uniform", 20, 60, 3000, 2)),       # long ragged contexts: pairs cut between several CTAs
-    (8, 1, 256, ("uniform", 100, 1, 300, 3)),        # one kv head (a TP=8 shard), group 8
-    (16, 8, 256, ("list", [300, 0, 5, 0, 129])),     # empty sequences: zero rows, no ticket taken
-    (40, 8, 16, ("uniform", 9, 1, 200, 4)),          # group 5, small blocks
-])
-def test_paged_decode_balanced(ctx, nvc, nh, kv, block_size, lens_spec):
-    """work-balanced paged decode (flat item ranges + last-arriver merge) against the oracle, twice:
-    the second call proves that the arrival tickets were re-armed and that the merge order is deterministic"""
+def _lens(lens_spec):
     if lens_spec[0] == "uniform":
         _, n, lo, hi, seed = lens_spec
-        lens = torch.randint(lo, hi + 1, (n,), generator=torch.Generator().manual_seed(seed)).tolist()
-    elif lens_spec[0] == "const":
-        lens = [lens_spec[2]] * lens_spec[1]
-    else:
-        lens = lens_spec[1]
+        return torch.randint(lo, hi + 1, (n,), generator=torch.Generator().manual_seed(seed)).tolist()
+    if lens_spec[0] == "const":
+        return [lens_spec[2]] * lens_spec[1]
+    return lens_spec[1]
+
+
+@pytest.mark.parametrize("nh,kv,block_size,lens_spec,splits", [
+    (16, 8, 256, ("uniform", 48, 1, 700, 1), 0),     # ragged batch
+    (16, 8, 256, ("const", 64, 581), 0),             # the bench shape: 512 CTAs, one resident wave of 2-warp CTAs
+    (32, 8, 64, ("uniform", 20, 60, 3000, 2), 3),    # long ragged contexts, forced KV splits (some own no tile)
+    (8, 1, 256, ("uniform", 100, 1, 300, 3), 0),     # one kv head (a TP=8 shard), group 8
+    (16, 8, 256, ("list", [300, 0, 5, 0, 129]), 0),  # empty sequences: zero rows
+    (40, 8, 16, ("uniform", 9, 1, 200, 4), 2),       # group 5, small blocks
+    (40, 2, 256, ("list", [33, 700]), 0),            # group 20: two head chunks (16 + 4) per kv head
+    (16, 8, 256, ("list", [2048]), 8),               # one sequence: the small-batch case the splits exist for
+    (2, 1, 256, ("const", 64, 581), 4),              # a TP=8 shard of the bench shape
+])
+def test_paged_decode_warps_and_splits(ctx, nvc, nh, kv, block_size, lens_spec, splits):
+    """both CTA shapes (4 warps x 2 per SM, 2 warps x 4 per SM), with and without KV splits, against the oracle;
+    each configuration is launched twice and must be bit-identical between launches (fixed merge order)"""
+    import os
+    lens = _lens(lens_spec)
     q, kc, vc, bt, ref, scale = _paged_case(nh, kv, block_size, lens, 7 + len(lens))
     B = len(lens)
     args = (q.reshape(B, nh * 128).cuda(), kc.cuda(), vc.cuda(), bt.cuda(), torch.tensor(lens, dtype=torch.int32).cuda(),
             nh, kv, 128, block_size, scale)
-    nvc.lib().nvc_debug_set(1, 1)            # opt into the work-balanced kernel (off by default: see paged_decode.cu)
+    if splits:
+        os.environ["NVC_PD_SPLITS"] = str(splits)
     try:
-        o1 = ctx.paged_decode_attn(*args).clone()
-        o2 = ctx.paged_decode_attn(*args).clone()
-        torch.cuda.synchronize()
+        for warps in (2, 4):
+            nvc.lib().nvc_debug_set(5, warps)
+            o1 = ctx.paged_decode_attn(*args).clone()
+            o2 = ctx.paged_decode_attn(*args).clone()
+            torch.cuda.synchronize()
+            assert not torch.isnan(o1.float()).any(), "poisoned (unwritten) cache slots leaked into the output"
+            _close(o1, ref, 1e-2, 2 ** -7, f"paged decode warps={warps} splits={splits} nh={nh} kv={kv} bs={block_size} B={B}")
+            assert torch.equal(o1, o2), "paged decode must be bit-identical between launches"
     finally:
-        nvc.lib().nvc_debug_set(1, 0)
-    o3 = ctx.paged_decode_attn(*args)        # the default per-(head, sequence) grid on the same case
-    torch.cuda.synchronize()
-    _close(o3, ref, 1e-2, 2 ** -7, f"default paged decode nh={nh} kv={kv} bs={block_size} B={B}")
-    assert not torch.isnan(o1.float()).any(), "poisoned (unwritten) cache slots leaked into the output"
-    _close(o1, ref, 1e-2, 2 ** -7, f"balanced paged decode nh={nh} kv={kv} bs={block_size} B={B}")
-    assert torch.equal(o1, o2), "balanced paged decode must be bit-identical between launches"
-
-
-@pytest.mark.parametrize("nh,kv,block_size,lens,splits", [
-    (16, 8, 256, [2048], 8),                    # one sequence: the small-batch case the splits exist for
-    (2, 1, 256, [581] * 64, 4),                 # a TP=8 shard of the bench shape: 64 CTAs -> 4 splits
-    (32, 8, 64, [700, 3, 1025, 64, 65], 3),     # ragged: some splits own no tile at all
-])
-def test_paged_decode_split_merge_variants(ctx, nh, kv, block_size, lens, splits):
-    """KV splits: the separate combine kernel (default) and the merge by the last CTA to arrive (opt-in) sum the
-    partial (m, l, o) states in split order, so both must match the oracle and each other bit for bit; the second
-    fused call proves the tickets were re-armed."""
-    import os
-    q, kc, vc, bt, ref, scale = _paged_case(nh, kv, block_size, lens, 11 + len(lens))
-    B = len(lens)
-    args = (q.reshape(B, nh * 128).cuda(), kc.cuda(), vc.cuda(), bt.cuda(), torch.tensor(lens, dtype=torch.int32).cuda(),
-            nh, kv, 128, block_size, scale)
-    os.environ["NVC_PD_SPLITS"] = str(splits)
-    try:
-        a = ctx.paged_decode_attn(*args).clone()
-        os.environ["NVC_PD_FUSED_MERGE"] = "1"
-        b1 = ctx.paged_decode_attn(*args).clone()
-        b2 = ctx.paged_decode_attn(*args).clone()
-        torch.cuda.synchronize()
-    finally:
+        nvc.lib().nvc_debug_set(5, 0)
         os.environ.pop("NVC_PD_SPLITS", None)
-        os.environ.pop("NVC_PD_FUSED_MERGE", None)
-    assert not torch.isnan(a.float()).any() and not torch.isnan(b1.float()).any()
-    _close(a, ref, 1e-2, 2 ** -7, f"split paged decode (combine kernel) nh={nh} kv={kv} S={splits}")
-    assert torch.equal(a, b1) and torch.equal(b1, b2), "fused merge must equal the combine kernel bit for bit"
+
+
+@pytest.mark.parametrize("nh,kv,block_size,lens_spec,splits", [
+    (16, 8, 256, ("const", 64, 581), 0),             # the bench shape
+    (16, 8, 256, ("list", [1, 16, 17, 64, 65, 255, 256, 257, 1000, 33]), 0),   # new token first / last in a tile, a block
+    (32, 8, 64, ("uniform", 20, 1, 3000, 2), 3),     # KV splits: only the split that owns the last tile patches it
+    (40, 2, 256, ("list", [33, 700, 1]), 0),         # two head chunks per kv head: both patch, chunk 0 stores
+    (40, 8, 16, ("uniform", 9, 1, 200, 4), 0),       # group 5, block size 16
+    (8, 1, 256, ("uniform", 70, 1, 300, 3), 0),      # TP shard: 70 CTAs -> splits chosen by the launcher
+])
+def test_paged_decode_fused_qk_norm_rope(ctx, nvc, nh, kv, block_size, lens_spec, splits):
+    """K2 folded into the paged decode prologue vs the two-kernel sequence (nvc_qk_norm_rope_store, then
+    nvc_paged_decode_attn) on the same raw qkv rows: the new cache rows and the attention output must be
+    bit-identical, nothing else in the caches may change, and the output must match the fp32 oracle."""
+    import os
+    hd, theta, eps = 128, 1e6, 1e-6
+    lens = _lens(lens_spec)
+    B = len(lens)
+    g = torch.Generator().manual_seed(101 + nh + B)
+    _, kc, vc, bt, _, scale = _paged_case(nh, kv, block_size, lens, 23 + B)
+    qkv = torch.randn(B, (nh + 2 * kv) * hd, generator=g).to(BF16)
+    qw = (1 + 0.2 * torch.randn(hd, generator=g)).to(BF16).cuda()
+    kw = (1 + 0.2 * torch.randn(hd, generator=g)).to(BF16).cuda()
+    lens_t = torch.tensor(lens, dtype=torch.int32)
+    pos = (lens_t - 1).to(torch.int32)
+    slots = (bt[torch.arange(B), (pos // block_size).long()] * block_size + pos % block_size).to(torch.int32)
+    # the slot of the new token is unwritten (poison) before the step
+    kc[slots.long()] = float("nan")
+    vc[slots.long()] = float("nan")
+    tab = ctx.rope_table(theta, hd, 4096)
+    d_bt, d_lens, d_pos, d_slots = bt.cuda(), lens_t.cuda(), pos.cuda(), slots.cuda()
+    # two-kernel sequence
+    kc1, vc1, qkv1 = kc.cuda(), vc.cuda(), qkv.cuda().clone()
+    ctx.qk_norm_rope_store(qkv1, qw, kw, eps, tab, d_pos, nh, kv, hd, slot_mapping=d_slots, k_cache=kc1, v_cache=vc1)
+    o_ref = ctx.paged_decode_attn(qkv1[:, :nh * hd], kc1, vc1, d_bt, d_lens, nh, kv, hd, block_size, scale).clone()
+    torch.cuda.synchronize()
+    if splits:
+        os.environ["NVC_PD_SPLITS"] = str(splits)
+    try:
+        for warps in (2, 4):
+            nvc.lib().nvc_debug_set(5, warps)
+            kc2, vc2, qkv2 = kc.cuda(), vc.cuda(), qkv.cuda().clone()
+            o = ctx.paged_decode_attn_fused(qkv2, qw, kw, eps, tab, d_pos, d_slots, kc2, vc2, d_bt, d_lens, nh, kv, hd,
+                                            block_size, scale)
+            torch.cuda.synchronize()
+            assert torch.equal(qkv2, qkv.cuda()), "the fused kernel must not modify the qkv rows"
+            assert torch.equal(kc2.view(torch.int16), kc1.view(torch.int16)), f"k cache differs (warps={warps})"
+            assert torch.equal(vc2.view(torch.int16), vc1.view(torch.int16)), f"v cache differs (warps={warps})"
+            assert not torch.isnan(o.float()).any()
+            _close(o, o_ref.float().cpu(), 1e-2, 2 ** -7, f"fused vs two-kernel paged decode warps={warps}")
+    finally:
+        nvc.lib().nvc_debug_set(5, 0)
+        os.environ.pop("NVC_PD_SPLITS", None)
+    # same launcher choice as the reference launch -> bit-identical output
+    kc3, vc3 = kc.cuda(), vc.cuda()
+    o3 = ctx.paged_decode_attn_fused(qkv.cuda(), qw, kw, eps, tab, d_pos, d_slots, kc3, vc3, d_bt, d_lens, nh, kv, hd,
+                                     block_size, scale)
+    torch.cuda.synchronize()
+    if not splits:
+        assert torch.equal(o3, o_ref), "fused and two-kernel paged decode must agree bit for bit"
+    # fp32 oracle: normalise + rotate q / k, append k / v, attend (qwen3.rs:205-277)
+    from test_kernels_gpu import _rope_ref
+    q_ref, k_ref = _rope_ref(qkv, qw.cpu(), kw.cpu(), eps, pos, nh, kv, hd, theta)
+    ref = torch.zeros(B, nh * hd)
+    kcf, vcf = kc1.float().cpu(), vc1.float().cpu()
+    for b, c in enumerate(lens):
+        t = torch.arange(c)
+        sl = (bt[b, (t // block_size).long()] * block_size + t % block_size).long()
+        kh = O.gqa_expand(kcf[sl].permute(1, 0, 2)[None], nh // kv)[0]
+        vh = O.gqa_expand(vcf[sl].permute(1, 0, 2)[None], nh // kv)[0]
+        sc = torch.einsum("hd,htd->ht", torch.as_tensor(q_ref[b]).float().to(BF16).float(), kh) * scale
+        ref[b] = torch.einsum("ht,htd->hd", torch.softmax(sc, dim=-1), vh).reshape(-1)
+    _close(o3, ref, 1e-2, 2 ** -7, f"fused paged decode vs oracle nh={nh} kv={kv} bs={block_size}")

@@ -57,27 +57,31 @@ def bench(B, nh, kv, ctx_len, ragged=False, block_size=256, pools=None):
 
 
 def sweep_splits():
-    """--splits: KV-split count x (fused last-arriver merge | separate combine kernel) on the sharded / small-batch
-    shapes, where the per-(sequence, kv head) grid alone cannot fill 148 SMs."""
-    print(f"paged decode attention split sweep, peak {PEAK} GB/s")
+    """--splits: warps per CTA (4 warps x 2 CTAs per SM | 2 warps x 4 CTAs per SM) x KV-split count on the bench shape
+    and the sharded / small-batch shapes, where the per-(sequence, kv head) grid alone cannot fill 148 SMs."""
+    print(f"paged decode attention warps x split sweep, peak {PEAK} GB/s")
     for name, B, nh, kv, c in [("0.6B tp1 bs64 ctx581", 64, 16, 8, 581), ("0.6B tp2 bs64 ctx581", 64, 8, 4, 581),
                                ("0.6B tp4 bs64 ctx581", 64, 4, 2, 581), ("0.6B tp8 bs64 ctx581", 64, 2, 1, 581),
+                               ("0.6B bs32 ctx581", 32, 16, 8, 581), ("0.6B bs48 ctx581", 48, 16, 8, 581),
+                               ("0.6B bs128 ctx581", 128, 16, 8, 581), ("8B bs64 ctx1024", 64, 32, 8, 1024),
                                ("8B tp8 bs256 ctx1024", 256, 4, 1, 1024), ("8B tp4 bs256 ctx1024", 256, 8, 2, 1024),
+                               ("8B bs256 ctx1024", 256, 32, 8, 1024),
                                ("0.6B bs1 ctx2048", 1, 16, 8, 2048), ("8B bs1 ctx1024", 1, 32, 8, 1024), ("8B bs16 ctx1024", 16, 32, 8, 1024)]:
         row = []
-        for comb in (0, 1):
-            os.environ["NVC_PD_FUSED_MERGE"] = str(1 - comb)
-            for s in (0, 1, 2, 3, 4, 5, 6, 8, 12, 16):
+        for warps in (0, 4, 2):
+            if warps:
+                os.environ["NVC_PD_WARPS"] = str(warps)
+            else:
+                os.environ.pop("NVC_PD_WARPS", None)
+            for s in ((0,) if not warps else (1, 2, 3, 4, 6, 8, 16)):
                 if s:
                     os.environ["NVC_PD_SPLITS"] = str(s)
                 else:
                     os.environ.pop("NVC_PD_SPLITS", None)
-                if comb and s == 1:
-                    continue
                 us, gbs = bench(B, nh, kv, c, pools=8)
-                row.append(f"{'comb' if comb else 'fused'} S={s or 'auto'}: {us:.2f}")
+                row.append(f"w{warps or 'auto'} S={s or 'auto'}: {us:.2f}")
         os.environ.pop("NVC_PD_SPLITS", None)
-        os.environ.pop("NVC_PD_FUSED_MERGE", None)
+        os.environ.pop("NVC_PD_WARPS", None)
         print(f"{name:24s} " + " | ".join(row), flush=True)
 
 
@@ -85,7 +89,7 @@ if __name__ == "__main__":
     if "--splits" in sys.argv:
         sweep_splits()
         sys.exit(0)
-    print(f"paged decode attention, peak {PEAK} GB/s; env NVC_PD_SPLITS={os.environ.get('NVC_PD_SPLITS')}")
+    print(f"paged decode attention, peak {PEAK} GB/s; env NVC_PD_SPLITS={os.environ.get('NVC_PD_SPLITS')} NVC_PD_WARPS={os.environ.get('NVC_PD_WARPS')}")
     for name, B, nh, kv, c, rag in [("0.6B bs64 ctx581", 64, 16, 8, 581, False), ("0.6B bs64 ctx1024", 64, 16, 8, 1024, False),
                                     ("0.6B bs1 ctx2048", 1, 16, 8, 2048, False), ("0.6B bs256 ctx640", 256, 16, 8, 640, False),
                                     ("8B bs256 ctx512", 256, 32, 8, 512, False), ("8B bs256 ctx1024", 256, 32, 8, 1024, False),

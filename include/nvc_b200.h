@@ -160,6 +160,18 @@ int nvc_fused_add_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x, const float* residual
                           float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out,
                           int N, int H, void* stream);
 
+/* K1 over split-K partials (decode, M <= 128).  nvc_gemm_bf16_partial runs a row-parallel projection split along K
+ * and stores each split's fp32 partial to P[z][M][Nout] WITHOUT reducing them (no cluster exchange, no workspace
+ * round trip); nvc_fused_add_rmsnorm_partial sums the splits in order, rounds the sum to bf16 - the value the
+ * projection itself would have stored (src/layers/linear.rs:171-175) - and applies the same residual add + RMSNorm
+ * as nvc_fused_add_rmsnorm.  P capacity: max_splits * M * Nout floats; *splits_out = splits written.
+ * force_bn / force_splits: 0 = the library's choice (tuning hooks). */
+int nvc_gemm_bf16_partial(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, float* P, int max_splits,
+                          int M, int Nout, int K, int force_bn, int force_splits, int* splits_out, void* stream);
+int nvc_fused_add_rmsnorm_partial(nvc_ctx* ctx, const float* partials, int splits, const float* residual_in,
+                                  float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out,
+                                  int N, int H, void* stream);
+
 /* K3. Replaces candle_nn::Linear::forward inside every *ParallelLinear::forward
  * (src/layers/linear.rs:33-38,72-77,99-104,171-175,184-198) and compute_logits
  * (src/models/qwen3.rs:542-550):  C[M, Nout] = A[M, K] * W[Nout, K]^T  (W is the

@@ -26,6 +26,7 @@ struct Layer {
 };
 
 struct ArgPair { float val; int32_t idx; };
+constexpr int kMaxPartialSplits = 8;   // split-K partial buffer of the decode path (nvc_gemm_bf16_partial)
 
 }  // namespace
 
@@ -46,6 +47,7 @@ struct nvc_runner {
   // activations
   nvc_bf16 *x = nullptr, *xn = nullptr, *qkv = nullptr, *attn = nullptr, *act = nullptr;
   float* residual = nullptr;
+  float* xp = nullptr;              // decode at TP 1: fp32 split-K partials of o_proj / down_proj [splits][B][H]
   nvc_bf16 *x_last = nullptr, *xn_last = nullptr;
   float *res_last = nullptr, *logits = nullptr;
   void* decode_ws = nullptr;
@@ -113,6 +115,12 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
   const int H = c.hidden_size, hd = c.head_dim, L = c.num_hidden_layers;
   const float scale = 1.0f / sqrtf((float)hd);   // (head_dim as f32).powf(-0.5), qwen3.rs:132
   static const bool p2p_env = !(getenv("NVC_P2P_AR") && atoi(getenv("NVC_P2P_AR")) == 0);
+  // decode at TP 1: o_proj / down_proj split along K store their fp32 partials and the norm that follows sums them
+  // (no cluster exchange inside the GEMM); NVC_SPLITK_NORM=0 keeps the in-kernel reduction
+  static const bool splitk_env = !(getenv("NVC_SPLITK_NORM") && atoi(getenv("NVC_SPLITK_NORM")) == 0);
+  const bool part_ok = decode && r->tp == 1 && N <= 128 && splitk_env && r->xp != nullptr;
+  const bool part_o = part_ok && nvc_gemm_decode_splits(ctx, N, H, r->nh_l * hd) > 1;
+  const bool part_d = part_ok && nvc_gemm_decode_splits(ctx, N, H, r->I_l) > 1;
   static const bool fused_k2 = !(getenv("NVC_FUSED_K2") && atoi(getenv("NVC_FUSED_K2")) == 0);
   // NVLS (in-switch) all-reduce + residual + norm for every step kind; else the peer-load kernel for decode-sized
   // messages; else NCCL + the norm kernel
@@ -169,9 +177,18 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     }
     if (rc) return rc;
     // o_proj (row-parallel) -> [all-reduce, N4] -> post_attention_layernorm with residual add
+    if (part_o) {
+      int sp = 1;
+      rc = nvc_gemm_bf16_partial(ctx, r->attn, r->nh_l * hd, Ly.w_o, r->xp, kMaxPartialSplits, N, H, r->nh_l * hd, 0, 0, &sp, st);
+      if (rc) return rc;
+      rc = nvc_fused_add_rmsnorm_partial(ctx, r->xp, sp, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
+      if (rc) return rc;
+    } else {
     rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, Ly.w_o, p2p ? slot0 : r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
     if (rc) return rc;
-    if (nvls) {
+    }
+    if (part_o) {
+    } else if (nvls) {
       rc = nvc_nvls_allreduce_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, 0, st);
     } else if (p2p) {
       rc = nvc_p2p_allreduce_rmsnorm(ctx, 0, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
@@ -184,6 +201,19 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     rc = nvc_gemm_bf16_silu_mul(ctx, r->xn, H, Ly.w_gu, r->act, r->I_l, N, r->I_l, H, st);
     if (rc) return rc;
     // down_proj (row-parallel) -> [all-reduce, N4]
+    if (part_d) {
+      // the partials are summed by the norm that opens layer l+1 (or the final norm), launched here
+      const bool last = li + 1 == L;
+      int sp = 1;
+      rc = nvc_gemm_bf16_partial(ctx, r->act, r->I_l, Ly.w_down, r->xp, kMaxPartialSplits, N, H, r->I_l, 0, 0, &sp, st);
+      if (rc) return rc;
+      rc = nvc_fused_add_rmsnorm_partial(ctx, r->xp, sp, r->residual, r->residual, last ? r->final_norm : r->layers[li + 1].ln1,
+                                         c.rms_norm_eps, last ? r->xn_last : r->xn, N, H, st);
+      if (rc) return rc;
+      xn_ready = !last;
+      *final_norm_done = last;
+      continue;
+    }
     rc = nvc_gemm_bf16(ctx, r->act, r->I_l, Ly.w_down, p2p ? slot1 : r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
     if (rc) return rc;
     if (nvls) {
@@ -387,6 +417,7 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if (!r->x_nvls && (rc = dev_alloc(r, &r->x, T * H))) return rc;
   if ((rc = dev_alloc(r, &r->xn, T * H))) return rc;
   if ((rc = dev_alloc(r, &r->residual, T * H))) return rc;
+  if (tp == 1 && (rc = dev_alloc(r, &r->xp, (size_t)kMaxPartialSplits * std::min<size_t>(T, 128) * H))) return rc;
   if ((rc = dev_alloc(r, &r->qkv, T * r->qkv_l))) return rc;
   if ((rc = dev_alloc(r, &r->attn, T * r->nh_l * hd))) return rc;
   if ((rc = dev_alloc(r, &r->act, T * r->I_l))) return rc;

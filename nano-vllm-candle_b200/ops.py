@@ -161,6 +161,29 @@ class Context:
                                          M, N, K, force_bn, force_splits, _stream()), "nvc_gemm_bf16")
         return out
 
+    def gemm_partial(self, a: torch.Tensor, w: torch.Tensor, max_splits=8, force_bn=0, force_splits=0):
+        """split-K partials of a @ w.T (M <= 128): returns f32 [splits, M, N], unreduced."""
+        import ctypes
+        _req(a, BF16, "a"); _req(w, BF16, "w")
+        M, K = a.shape
+        N = w.shape[0]
+        assert w.shape[1] == K and w.is_contiguous() and a.stride(1) == 1
+        buf = torch.empty((max_splits, M, N), dtype=torch.float32, device=a.device)
+        used = ctypes.c_int(0)
+        self._ck(self.l.nvc_gemm_bf16_partial(self.h, _ptr(a), a.stride(0), _ptr(w), _ptr(buf), max_splits, M, N, K,
+                                              force_bn, force_splits, ctypes.byref(used), _stream()), "nvc_gemm_bf16_partial")
+        return buf[:used.value]
+
+    def fused_add_rmsnorm_partial(self, partials, w, eps, residual_in=None, residual_out=None, out=None):
+        _req(partials, torch.float32, "partials"); _req(w, BF16, "w")
+        S, N, H = partials.shape
+        assert partials.is_contiguous()
+        out = torch.empty((N, H), dtype=BF16, device=partials.device) if out is None else out
+        self._ck(self.l.nvc_fused_add_rmsnorm_partial(self.h, _ptr(partials), S, _ptr(residual_in), _ptr(residual_out),
+                                                      _ptr(w), float(eps), _ptr(out), N, H, _stream()),
+                 "nvc_fused_add_rmsnorm_partial")
+        return out
+
     @staticmethod
     def interleave_gate_up(w_gu: torch.Tensor) -> torch.Tensor:
         """[gate; up] rows (reference layout, qwen3.rs:310) -> groups of 16 gate rows then 16 up rows,

@@ -79,10 +79,11 @@ int paged_decode_impl(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* 
   const int G = group < 16 ? group : 16;
   const int chunks = (group + G - 1) / G;
   const int base = B * kv * chunks;                    // CTAs without KV splits
-  // Warps per CTA.  4 warps / 96 KB: 2 CTAs per SM; 2 warps / 48 KB: 4 CTAs per SM.  A grid that fits the 4-per-SM
-  // residency but not the 2-per-SM one (Qwen3-0.6B at batch 64: 512 CTAs on 148 SMs) runs as ONE resident wave of
-  // 2-warp CTAs instead of 1.7 waves of 4-warp ones.  NVC_PD_WARPS / nvc_debug_set(5, w) force it (microbench, tests).
-  int warps = (base > 2 * ctx->num_sms && base <= 4 * ctx->num_sms) ? 2 : 4;
+  // Warps per CTA.  4 warps / 96 KB: 2 CTAs per SM; 2 warps / 48 KB: 4 CTAs per SM.  A grid beyond the 2-per-SM
+  // residency runs as 2-warp CTAs: Qwen3-0.6B at batch 64 (512 CTAs on 148 SMs) is ONE resident wave instead of
+  // 1.7 waves of 4-warp CTAs (28.5 -> 26.6 us), 384 CTAs 26.5 -> 21.1 us, 1024 CTAs 54.7 -> 49.8 us, 2048 CTAs equal;
+  // below it the 4-warp CTAs (with KV splits) win (profiles/r02_pd_warps_split_sweep.txt).  NVC_PD_WARPS / nvc_debug_set(5, w) force it (microbench, tests).
+  int warps = base > 2 * ctx->num_sms ? 2 : 4;
   if (const char* e = getenv("NVC_PD_WARPS")) {
     const int f = atoi(e);
     if (f == 2 || f == 4) warps = f;

@@ -146,7 +146,26 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int quad = lane >> 2, tq = lane & 3;          // accumulator row (quad, quad + 8), column pair tq
 
+  // independent first loads, issued together: the context length, the first block id (the block of this warp's first
+  // tile whenever the CTA starts at tile 0) and, fused, the position that selects the cos / sin row
+  const int32_t* bt = block_tables + (int64_t)b * max_blocks;
+  const int pos_in = kFused ? __ldg(fa.positions + b) : 0;
+  const int blk_first = __ldg(bt);
   const int ctx_len = __ldg(context_lens + b);
+  const int l8 = lane & 7;
+  const unsigned mask8 = 0xffu << (lane & 24);
+  uint4 qw_lo, qw_hi, kw_lo, kw_hi, k_new1, k_new2, v_new;
+  float4 c0, c1, s0, s1;
+  if (kFused) {
+    // static operands of the q / k transform: in flight while the block table is walked
+    const uint4* qw = reinterpret_cast<const uint4*>(fa.q_norm_w);
+    const uint4* kw = reinterpret_cast<const uint4*>(fa.k_norm_w);
+    qw_lo = __ldg(qw + l8); qw_hi = __ldg(qw + l8 + 8);
+    kw_lo = __ldg(kw + l8); kw_hi = __ldg(kw + l8 + 8);
+    const float4* cs = reinterpret_cast<const float4*>(fa.cos_sin) + (int64_t)pos_in * 32;
+    c0 = __ldg(cs + 2 * l8); c1 = __ldg(cs + 2 * l8 + 1);
+    s0 = __ldg(cs + 16 + 2 * l8); s1 = __ldg(cs + 16 + 2 * l8 + 1);
+  }
   const int n_load = kFused ? ctx_len - 1 : ctx_len;  // cache rows [0, n_load) are loaded; fused: the last one is made here
   const int n_tiles = (ctx_len + kCtaTok - 1) / kCtaTok;
   const int tiles_per_split = (n_tiles + num_splits - 1) / num_splits;
@@ -160,7 +179,6 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
 
   const uint32_t ring = smem_u32(smem) + warp * (kStages * kStageBytes);
   const uint32_t q_sm = smem_u32(smem) + kWarps * (kStages * kStageBytes);     // fused only
-  const int32_t* bt = block_tables + (int64_t)b * max_blocks;
   const int my_tiles = t_end - t_begin;                // CTA tiles; this warp's tile i covers tokens (t_begin+i)*kCtaTok + 16w
 
   // issue the loads of warp tile i into ring stage i % kStages (empty group if i is out of range); rows at or past
@@ -169,7 +187,8 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
     if (i < my_tiles) {
       const int tok0 = (t_begin + i) * kCtaTok + warp * kTileTok;
       if (tok0 < ctx_len) {
-        const int blk = __ldg(bt + tok0 / block_size);
+        const int bi = tok0 / block_size;
+        const int blk = bi == 0 ? blk_first : __ldg(bt + bi);
         const int64_t slot0 = (int64_t)blk * block_size + (tok0 % block_size);
         const uint32_t st = ring + (i % kStages) * kStageBytes;
         const int c = lane & 15;                       // 16-byte chunk of the 256-byte row
@@ -209,19 +228,6 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
   const bool owner = kFused && ctx_len > 0 && pos_new / kCtaTok >= t_begin && pos_new / kCtaTok < t_end &&
                      (pos_new % kCtaTok) / kTileTok == warp;            // warp-uniform
   const int r_new = pos_new & (kTileTok - 1);
-  const int l8 = lane & 7;
-  const unsigned mask8 = 0xffu << (lane & 24);
-  uint4 qw_lo, qw_hi, kw_lo, kw_hi, k_new1, k_new2, v_new;
-  float4 c0, c1, s0, s1;
-  if (kFused) {
-    const uint4* qw = reinterpret_cast<const uint4*>(fa.q_norm_w);
-    const uint4* kw = reinterpret_cast<const uint4*>(fa.k_norm_w);
-    qw_lo = __ldg(qw + l8); qw_hi = __ldg(qw + l8 + 8);
-    kw_lo = __ldg(kw + l8); kw_hi = __ldg(kw + l8 + 8);
-    const float4* cs = reinterpret_cast<const float4*>(fa.cos_sin) + (int64_t)__ldg(fa.positions + b) * 32;
-    c0 = __ldg(cs + 2 * l8); c1 = __ldg(cs + 2 * l8 + 1);
-    s0 = __ldg(cs + 16 + 2 * l8); s1 = __ldg(cs + 16 + 2 * l8 + 1);
-  }
   pdl_wait();
   // ---- Q as A fragments: 8 k-steps of 16 dims; rows >= G are zero
   uint32_t qa[8][4];

@@ -108,6 +108,48 @@ def test_gemm_bf16(ctx, M, N, K, bn, splits, out_dtype):
     _close(out, ref, 2e-3, rtol, f"gemm M={M} N={N} K={K} bn={bn} s={splits} {out_dtype}")
 
 
+@pytest.mark.parametrize("M,N,K,bn,splits", [
+    (64, 1024, 2048, 0, 0),         # 0.6B o_proj: the decode schedule's own (BN, S)
+    (64, 1024, 3072, 0, 0),         # 0.6B down_proj
+    (64, 1024, 2048, 4032, 4),      # forced BN = 32, 4 splits: same k ranges as the cluster split-K case below
+    (64, 1024, 2048, 2064, 8),      # BN = 64, 8 splits
+    (1, 1024, 1024, 4032, 4),       # M = 1
+    (100, 2000, 1088, 4032, 4),     # ragged N, 17 k-blocks (5 + 5 + 5 + 2)
+    (128, 4096, 4096, 0, 0),        # 8B o_proj at batch 128 (the schedule may keep one split)
+    (64, 1024, 2048, 4032, 1),      # one split: fp32 output of the plain GEMM
+])
+def test_gemm_partial_and_norm(ctx, M, N, K, bn, splits):
+    """split-K partials left unreduced by the GEMM and summed by the RMSNorm that follows: the sum rounded to bf16 must
+    equal the GEMM's own cluster split-K result bit for bit (same splits, same order), and the norm over the partials
+    must equal nvc_fused_add_rmsnorm over that bf16 result bit for bit (src/layers/linear.rs:171-198, layernorm.rs:44-60)."""
+    g = torch.Generator().manual_seed(M * 13 + N * 5 + K)
+    a = torch.randn(M, K, generator=g).to(BF16).cuda()
+    w = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(BF16).cuda()
+    part = ctx.gemm_partial(a, w, max_splits=8, force_bn=bn, force_splits=splits)
+    torch.cuda.synchronize()
+    S = part.shape[0]
+    assert 1 <= S <= 8 and (splits == 0 or S == splits)
+    acc = torch.zeros(M, N, device="cuda")
+    for z in range(S):                       # split order, fp32: the order of both device-side reductions
+        acc = acc + part[z]
+    x_bf = acc.to(BF16)
+    _close(x_bf, O.linear(a.float().cpu(), w.float().cpu()), 2e-3, 2 ** -8, f"partial gemm M={M} N={N} K={K} S={S}")
+    if 1 < S <= 8 and bn:
+        same = ctx.gemm(a, w, force_bn=bn, force_splits=100 + S)     # split-K inside a cluster (1,1,S)
+        assert torch.equal(same, x_bf), "partials summed in split order must equal the in-kernel split-K reduction"
+    if N % 8 == 0 and N <= 8192:
+        res = torch.randn(M, N, generator=g).cuda()
+        wn = (1 + 0.2 * torch.randn(N, generator=g)).to(BF16).cuda()
+        r1, r2 = torch.empty_like(res), torch.empty_like(res)
+        o1 = ctx.fused_add_rmsnorm(x_bf, wn, 1e-6, residual_in=res, residual_out=r1)
+        o2 = ctx.fused_add_rmsnorm_partial(part.contiguous(), wn, 1e-6, residual_in=res, residual_out=r2)
+        torch.cuda.synchronize()
+        assert torch.equal(r1, r2) and torch.equal(o1, o2), "norm over partials differs from norm over the reduced bf16 rows"
+        o3 = ctx.fused_add_rmsnorm_partial(part.contiguous(), wn, 1e-6)           # no residual (layer 0 / final norm form)
+        o4 = ctx.fused_add_rmsnorm(x_bf, wn, 1e-6)
+        assert torch.equal(o3, o4)
+
+
 def test_gemm_reference_goldens(ctx):
     """src/layers/linear.rs:231-267 (replicated, exact small integers; bias added on the host
     here since the Qwen3 path has no biases) and :274-319 (two hand-sharded column ranks),

@@ -13,20 +13,20 @@ BF16 = torch.bfloat16
 V = 151936
 
 
-def timed(M, K, force_bn, iters=8):
+def timed(M, K, force_bn, iters=8, force_splits=0):
     a = torch.randn(M, K, device="cuda").to(BF16)
     ws = [torch.randn(V, K, device="cuda").to(BF16) for _ in range(2)]
     out = torch.empty(M, V, device="cuda", dtype=torch.float32)
     try:
         for w in ws:
-            ctx.gemm(a, w, out=out, force_bn=force_bn)
+            ctx.gemm(a, w, out=out, force_bn=force_bn, force_splits=force_splits)
     except Exception as e:          # a (BN, KPS) pair that is not instantiated
         return None
     torch.cuda.synchronize()
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g):
         for i in range(iters):
-            ctx.gemm(a, ws[i % 2], out=out, force_bn=force_bn)
+            ctx.gemm(a, ws[i % 2], out=out, force_bn=force_bn, force_splits=force_splits)
     g.replay()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -41,4 +41,8 @@ for M, K in ((64, 1024), (1, 1024), (64, 4096), (128, 5120)):
     for fb in (0, 1256, 1128, 2128, 2064, 4064, 21256, 41128, 42128):
         us = timed(M, K, fb)
         row.append(f"{fb}:{'-' if us is None else f'{us:.1f}us/{gb / us:.0f}GB/s'}")
+    # the CTA-pair kernel (persistent, two accumulator stages) on the same decode shape: force_bn 512, tile width NT
+    for nt in (256, 224, 208, 192, 160, 128):
+        us = timed(M, K, 512, force_splits=1000 + nt)
+        row.append(f"pair{nt}:{'-' if us is None else f'{us:.1f}us/{gb / us:.0f}GB/s'}")
     print(f"M={M} K={K}  " + "  ".join(row), flush=True)

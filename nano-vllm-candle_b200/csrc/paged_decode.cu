@@ -186,7 +186,7 @@ extern "C" int nvc_paged_decode_attn_fused(nvc_ctx* ctx, const nvc_bf16* qkv, in
                                            int block_size, float scale, nvc_bf16* out, void* workspace,
                                            size_t workspace_bytes, void* stream) {
   NVC_REQUIRE(ctx, ctx && q_norm_w && k_norm_w && cos_sin && positions && slot_mapping, NVC_EINVAL, "null pointer");
-  pdmma::FusedArgs fa{q_norm_w, k_norm_w, cos_sin, positions, slot_mapping, k_cache, v_cache, eps};
+  pdmma::FusedArgs fa{q_norm_w, k_norm_w, cos_sin, positions, slot_mapping, k_cache, v_cache, eps, g_nvc_debug[6]};
   return paged_decode_impl(ctx, qkv, ldq, k_cache, v_cache, block_tables, max_blocks, max_blocks_hint, context_lens, B, nh,
                            kv, hd, block_size, scale, out, workspace, workspace_bytes, stream, &fa);
 }

@@ -77,23 +77,18 @@ struct FusedArgs {
   nvc_bf16* k_cache_w;             // the same pools the kernel reads, writable
   nvc_bf16* v_cache_w;
   float eps;
+  int dbg;                         // TEMP bisect: 1 = skip the owner's k / v work, 2 = skip the q transform
 };
 
 // One 8-lane unit (lane l = 0..7 owns dims [8l, 8l+8) and [64+8l, 64+8l+8)) normalises and rotates one head row
 // with the arithmetic and the summation order of qk_norm_rope_store_kernel (elementwise.cu): the fused and the
 // stand-alone K2 give bit-identical q / k.  Inactive units contribute zeros and return zero rows.
-__device__ __forceinline__ void norm_rope_unit(bool active, const uint4* __restrict__ row, int l, unsigned mask, const uint4& w_lo,
+__device__ __forceinline__ void norm_rope_unit(bool active, const uint4& ra, const uint4& rb, unsigned mask, const uint4& w_lo,
                                                const uint4& w_hi, const float4& c0, const float4& c1, const float4& s0,
                                                const float4& s1, float eps, uint4& o1, uint4& o2) {
-  float a[8], b[8];
-  if (active) {
-    const uint4 ra = row[l], rb = row[l + 8];
-    unpack8(ra, a);
-    unpack8(rb, b);
-  } else {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) a[i] = b[i] = 0.f;
-  }
+  float a[8], b[8];                                    // ra / rb: this lane's two 16-byte pieces (zeros when inactive)
+  unpack8(ra, a);
+  unpack8(rb, b);
   float ss = 0.f;
 #pragma unroll
   for (int i = 0; i < 8; ++i) ss += a[i] * a[i] + b[i] * b[i];
@@ -232,24 +227,41 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
   // ---- Q as A fragments: 8 k-steps of 16 dims; rows >= G are zero
   uint32_t qa[8][4];
   if (kFused) {
-    // 8 lanes per head: normalise + rotate the raw q rows of the group into shared memory (16-byte chunk c of row u
-    // at chunk c ^ (u & 7)), rows >= G as zeros
-    for (int u = warp * 4 + (lane >> 3); u < 16; u += kWarps * 4) {
-      const bool act = u < G;
-      const uint4* row = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(head0 + (act ? u : 0)) * 128);
+    // every load first: the raw q rows of this lane's units (8 lanes per head), the owner's new k / v rows and slot
+    constexpr int kUnits = 16 / (kWarps * 4);         // head rows per 8-lane unit: 1 (4 warps) or 2 (2 warps)
+    uint4 qa_raw[kUnits], qb_raw[kUnits], ka_raw = make_uint4(0, 0, 0, 0), kb_raw = ka_raw;
+    int slot = -1;
+#pragma unroll
+    for (int i = 0; i < kUnits; ++i) {
+      const int u = warp * 4 + (lane >> 3) + i * kWarps * 4;
+      qa_raw[i] = qb_raw[i] = make_uint4(0, 0, 0, 0);
+      if (u < G) {
+        const uint4* row = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(head0 + u) * 128);
+        qa_raw[i] = row[l8];
+        qb_raw[i] = row[l8 + 8];
+      }
+    }
+    if (owner && !(fa.dbg & 1)) {
+      const uint4* krow = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(nh + kvh) * 128);
+      const uint4* vrow = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(nh + kv + kvh) * 128);
+      if (lane < 8) { ka_raw = krow[l8]; kb_raw = krow[l8 + 8]; }
+      if (lane >= 16) v_new = vrow[lane - 16];
+      slot = __ldg(fa.slot_mapping + b);
+    }
+    // normalise + rotate into shared memory (16-byte chunk c of row u at chunk c ^ (u & 7)); rows >= G are zeros
+#pragma unroll
+    for (int i = 0; i < kUnits; ++i) {
+      const int u = warp * 4 + (lane >> 3) + i * kWarps * 4;
       uint4 o1, o2;
-      norm_rope_unit(act, row, l8, mask8, qw_lo, qw_hi, c0, c1, s0, s1, fa.eps, o1, o2);
+      if (fa.dbg & 2) { o1 = qa_raw[i]; o2 = qb_raw[i]; }
+      else norm_rope_unit(u < G, qa_raw[i], qb_raw[i], mask8, qw_lo, qw_hi, c0, c1, s0, s1, fa.eps, o1, o2);
       st_shared_u4(q_sm + u * 256 + ((l8 ^ (u & 7)) << 4), o1);
       st_shared_u4(q_sm + u * 256 + (((l8 + 8) ^ (u & 7)) << 4), o2);
     }
-    if (owner) {
+    if (owner && !(fa.dbg & 1)) {
       // the step's new k row (lanes 0..7, same unit arithmetic) and v row (lanes 16..31, one 16-byte chunk each):
       // kept in registers for the tile patch below; the CTA of the group's first chunk writes them to the cache
-      const uint4* krow = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(nh + kvh) * 128);
-      const uint4* vrow = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(nh + kv + kvh) * 128);
-      norm_rope_unit(lane < 8, krow, l8, mask8, kw_lo, kw_hi, c0, c1, s0, s1, fa.eps, k_new1, k_new2);
-      if (lane >= 16) v_new = vrow[lane - 16];
-      const int slot = __ldg(fa.slot_mapping + b);
+      norm_rope_unit(lane < 8, ka_raw, kb_raw, mask8, kw_lo, kw_hi, c0, c1, s0, s1, fa.eps, k_new1, k_new2);
       if (chunk == 0 && slot >= 0) {
         if (lane < 8) {
           uint4* dst = reinterpret_cast<uint4*>(fa.k_cache_w) + ((int64_t)slot * kv + kvh) * 16;

@@ -160,18 +160,6 @@ int nvc_fused_add_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x, const float* residual
                           float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out,
                           int N, int H, void* stream);
 
-/* K1 over split-K partials (decode, M <= 128).  nvc_gemm_bf16_partial runs a row-parallel projection split along K
- * and stores each split's fp32 partial to P[z][M][Nout] WITHOUT reducing them (no cluster exchange, no workspace
- * round trip); nvc_fused_add_rmsnorm_partial sums the splits in order, rounds the sum to bf16 - the value the
- * projection itself would have stored (src/layers/linear.rs:171-175) - and applies the same residual add + RMSNorm
- * as nvc_fused_add_rmsnorm.  P capacity: max_splits * M * Nout floats; *splits_out = splits written.
- * force_bn / force_splits: 0 = the library's choice (tuning hooks). */
-int nvc_gemm_bf16_partial(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, float* P, int max_splits,
-                          int M, int Nout, int K, int force_bn, int force_splits, int* splits_out, void* stream);
-int nvc_fused_add_rmsnorm_partial(nvc_ctx* ctx, const float* partials, int splits, const float* residual_in,
-                                  float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out,
-                                  int N, int H, void* stream);
-
 /* K3. Replaces candle_nn::Linear::forward inside every *ParallelLinear::forward
  * (src/layers/linear.rs:33-38,72-77,99-104,171-175,184-198) and compute_logits
  * (src/models/qwen3.rs:542-550):  C[M, Nout] = A[M, K] * W[Nout, K]^T  (W is the
@@ -254,21 +242,6 @@ int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf
                           const int32_t* context_lens, int B, int nh, int kv, int hd, int block_size,
                           float scale, nvc_bf16* out, void* workspace, size_t workspace_bytes,
                           void* stream);
-
-/* K2 + K5 in one launch for a pure decode step (one new token per sequence; replaces the q_norm / k_norm / RoPE /
- * cache-store / attention sequence of src/models/qwen3.rs:205-277 for that step kind).  qkv: RAW fused projection
- * rows [B, (nh + 2 kv) * hd] (row stride ldq), not modified.  q and the new k are RMS-normalised (q_norm_w, k_norm_w,
- * eps) and rotated with the cos / sin row of positions[b] exactly as nvc_qk_norm_rope_store does (bit-identical);
- * the new k / v rows are written to the caches at slot_mapping[b], which must be the slot of position
- * context_lens[b] - 1 in block_tables.  Other arguments as nvc_paged_decode_attn; max_blocks_hint bounds the
- * blocks any sequence uses (split choice; pass max_blocks when unknown). */
-int nvc_paged_decode_attn_fused(nvc_ctx* ctx, const nvc_bf16* qkv, int ldq, const nvc_bf16* q_norm_w,
-                                const nvc_bf16* k_norm_w, float eps, const float* cos_sin,
-                                const int32_t* positions, const int32_t* slot_mapping, nvc_bf16* k_cache,
-                                nvc_bf16* v_cache, const int32_t* block_tables, int max_blocks,
-                                int max_blocks_hint, const int32_t* context_lens, int B, int nh, int kv, int hd,
-                                int block_size, float scale, nvc_bf16* out, void* workspace,
-                                size_t workspace_bytes, void* stream);
 
 /* K6. Replaces SiluAndMul::forward (src/layers/activation.rs:13-18):
  * out[n, i] = silu(x[n, i]) * x[n, I + i]. */

@@ -74,8 +74,6 @@ def _declare(l: C.CDLL) -> None:
         "nvc_nvls_argmax_merge": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
         "nvc_embed_gather": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp],
         "nvc_fused_add_rmsnorm": [_vp, _vp, _vp, _vp, _vp, _f, _vp, _i, _i, _vp],
-        "nvc_gemm_bf16_partial": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _vp],
-        "nvc_fused_add_rmsnorm_partial": [_vp, _vp, _i, _vp, _vp, _vp, _f, _vp, _i, _i, _vp],
         "nvc_gemm_bf16": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp],
         "nvc_gemm_bf16_ex": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp],
         "nvc_gemm_bf16_silu_mul": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp],
@@ -87,8 +85,6 @@ def _declare(l: C.CDLL) -> None:
         "nvc_prefill_attn_varlen": [_vp, _vp, _i, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _vp],
         "nvc_prefill_attn_paged": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp],
         "nvc_paged_decode_attn": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp, _sz, _vp],
-        "nvc_paged_decode_attn_fused": [_vp, _vp, _i, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp, _i, _i, _i, _i, _i, _f,
-                                        _vp, _vp, _sz, _vp],
         "nvc_silu_and_mul": [_vp, _vp, _vp, _i, _i, _vp],
         "nvc_gather_rows": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
         "nvc_argmax_last": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp],

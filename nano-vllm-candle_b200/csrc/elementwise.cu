@@ -163,80 +163,6 @@ extern "C" int nvc_fused_add_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x, const floa
   return NVC_OK;
 }
 
-// K1 over split-K partials: x = bf16(sum over splits, in split order, of the fp32 partials P[z][row][:]) - the value
-// the GEMM's own split-K reduction would have stored - then the same add + norm.  One 8-vector per thread (H <= 8192).
-__global__ void __launch_bounds__(1024)
-fused_add_rmsnorm_partial_kernel(const float4* __restrict__ part, int splits, int64_t split_stride_vec4,
-                                 const float4* __restrict__ res_in, float4* __restrict__ res_out,
-                                 const uint4* __restrict__ w, float eps, uint4* __restrict__ out, int H) {
-  __shared__ float red[32];
-  pdl_trigger();
-  const int row = blockIdx.x;
-  const int nvec = H >> 3;
-  const int v = threadIdx.x;
-  uint4 wv = make_uint4(0, 0, 0, 0);
-  if (v < nvec) wv = __ldg(w + v);
-  pdl_wait();
-  const int64_t vbase = (int64_t)row * nvec;
-  float s[8];
-  float ss = 0.f;
-  if (v < nvec) {
-    float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
-    const float4* p = part + (vbase + v) * 2;
-    for (int z = 0; z < splits; ++z) {                  // split order: the bits of the in-kernel reduction
-      const float4 pa = __ldcg(p + z * split_stride_vec4), pb = __ldcg(p + z * split_stride_vec4 + 1);
-      a.x += pa.x; a.y += pa.y; a.z += pa.z; a.w += pa.w;
-      b.x += pb.x; b.y += pb.y; b.z += pb.z; b.w += pb.w;
-    }
-    const float f[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-    unpack8(pack8(f), s);                               // the projection's output is bf16 (linear.rs:171-175)
-    if (res_in) {
-      const float4 ra = res_in[(vbase + v) * 2], rb = res_in[(vbase + v) * 2 + 1];
-      s[0] += ra.x; s[1] += ra.y; s[2] += ra.z; s[3] += ra.w;
-      s[4] += rb.x; s[5] += rb.y; s[6] += rb.z; s[7] += rb.w;
-    }
-    if (res_out) {
-      res_out[(vbase + v) * 2] = make_float4(s[0], s[1], s[2], s[3]);
-      res_out[(vbase + v) * 2 + 1] = make_float4(s[4], s[5], s[6], s[7]);
-    }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) ss += s[i] * s[i];
-  }
-  ss = warp_sum(ss);
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  if (lane == 0) red[wid] = ss;
-  __syncthreads();
-  const int nw = (blockDim.x + 31) >> 5;
-  float tot = (lane < nw) ? red[lane] : 0.f;
-  tot = warp_sum(tot);
-  const float rstd = 1.0f / sqrtf(tot / (float)H + eps);
-  if (v < nvec) {
-    float wf[8];
-    unpack8(wv, wf);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) s[i] = s[i] * rstd * wf[i];
-    out[vbase + v] = pack8(s);
-  }
-}
-
-extern "C" int nvc_fused_add_rmsnorm_partial(nvc_ctx* ctx, const float* partials, int splits, const float* residual_in,
-                                             float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out,
-                                             int N, int H, void* stream) {
-  NVC_REQUIRE(ctx, ctx && partials && w && out, NVC_EINVAL, "null pointer");
-  NVC_REQUIRE(ctx, N >= 0 && H > 0 && splits >= 1, NVC_EINVAL, "bad sizes");
-  NVC_REQUIRE(ctx, H % 8 == 0 && H <= 8192, NVC_ESHAPE, "H must be a multiple of 8 and <= 8192");
-  if (N == 0) return NVC_OK;
-  const int nvec = H / 8;
-  const int threads = ((nvec + 31) / 32) * 32;
-  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, fused_add_rmsnorm_partial_kernel, dim3(N), dim3(threads), 0, nvc_stream(stream),
-                                 reinterpret_cast<const float4*>(partials), splits, (int64_t)N * H / 4,
-                                 reinterpret_cast<const float4*>(residual_in), reinterpret_cast<float4*>(residual_out),
-                                 reinterpret_cast<const uint4*>(w), eps, reinterpret_cast<uint4*>(out), H));
-  NVC_CUDA_CHECK(ctx, cudaGetLastError());
-  ctx->launches++;
-  return NVC_OK;
-}
-
 // ------------------------------------------------------------------------------------
 // rope table (host math = the reference's f32 powf/cos/sin)   (rotary_embedding.rs:56-80)
 // ------------------------------------------------------------------------------------

@@ -3,9 +3,7 @@
 #pragma once
 #include "common.cuh"
 
-// NVC_EPI_PARTIAL: split-K without a reduction - split z stores its fp32 partial tile to C + z * M * ldc (C: f32
-// [splits][M][ldc]); the consumer (nvc_fused_add_rmsnorm_partial) sums the splits in order.
-enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1, NVC_EPI_PARTIAL = 2 };
+enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1 };
 
 // 16 accumulator columns of one row -> C (bf16 or f32), 16-byte stores
 __device__ __forceinline__ void store16(void* C, int out_f32, int64_t off, const float* f) {

@@ -223,11 +223,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
     const int tile_id = m_tile * gridDim.x + n_tile;
 
-    if (num_splits == 1 || epi == NVC_EPI_PARTIAL) {
-      if (epi == NVC_EPI_PARTIAL) {      // this split's fp32 partial, row-major: summed by the consumer
-        C = reinterpret_cast<float*>(C) + (int64_t)split * M * ldc;
-        out_f32 = 1;
-      }
+    if (num_splits == 1) {
       if constexpr (BN >= 32) {
 #pragma unroll 1
         for (int c = 0; c < BN / 16; c += 2) {          // two 16-column chunks per tensor-memory round trip
@@ -530,7 +526,7 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   NVC_REQUIRE(ctx, lda % 8 == 0 && lda >= K, NVC_ESHAPE, "lda must be >= K and a multiple of 8");
   NVC_REQUIRE(ctx, ldc >= (epi == NVC_EPI_SILU_MUL ? Nout / 2 : Nout) && ldc % 8 == 0, NVC_ESHAPE,
               "ldc must be >= the output width and a multiple of 8");
-  NVC_REQUIRE(ctx, epi == NVC_EPI_NONE || epi == NVC_EPI_PARTIAL || (epi == NVC_EPI_SILU_MUL && Nout % 32 == 0 && out_dtype == NVC_DT_BF16),
+  NVC_REQUIRE(ctx, epi == NVC_EPI_NONE || (epi == NVC_EPI_SILU_MUL && Nout % 32 == 0 && out_dtype == NVC_DT_BF16),
               NVC_ESHAPE, "fused SiLU-mul epilogue needs Nout % 32 == 0 and bf16 output");
   NVC_REQUIRE(ctx, out_dtype == NVC_DT_BF16 || out_dtype == NVC_DT_F32, NVC_EINVAL, "bad out_dtype");
   NVC_REQUIRE(ctx, ((uintptr_t)A % 16) == 0 && ((uintptr_t)W % 16) == 0 && ((uintptr_t)C % 16) == 0, NVC_EINVAL,
@@ -538,11 +534,16 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   NVC_REQUIRE(ctx, ctx->encode_tiled != nullptr, NVC_EDEVICE, "cuTensorMapEncodeTiled unavailable");
   if (M == 0) return NVC_OK;
   // M > 128: CTA-pair kernel (gemm_pair.cu); force_bn = 512 selects it explicitly, any other force_bn the 1-CTA tiles
-  NVC_REQUIRE(ctx, epi != NVC_EPI_PARTIAL || (M <= BM && force_bn != 512), NVC_ESHAPE, "partial split-K output needs M <= 128");
-  if (force_bn == 512 || (force_bn == 0 && M > BM && g_nvc_gemm_pair))
+  // lm_head at decode batch sizes (vocabulary-sized N, short K): hundreds of one-k-loop tiles per SM pair leave the
+  // 1-CTA kernel's per-tile prologue / epilogue exposed; the pair kernel's persistent schedule overlaps the epilogue
+  // with the next tile (M 64, N 151936, K 1024: 75.1 -> 67.3 us; slower at M = 1 and at K = 4096,
+  // profiles/r02_lm_head_sweep_pair.txt)
+  const bool vocab_pair = force_bn == 0 && force_splits == 0 && epi == NVC_EPI_NONE && M >= 32 && M <= BM && Nout >= 65536 &&
+                          K <= 1024 && g_nvc_gemm_pair;
+  if (force_bn == 512 || vocab_pair || (force_bn == 0 && M > BM && g_nvc_gemm_pair))
     return nvc_gemm_pair(ctx, A, lda, W, C, ldc, out_dtype == NVC_DT_F32, M, Nout, K, force_splits, epi, stream, trace);
   int bn, kps, splits, cl = 1, ks = 0;
-  choose_config(ctx, M, Nout, K, epi == NVC_EPI_NONE || epi == NVC_EPI_PARTIAL, &bn, &kps, &splits, &cl, &ks);
+  choose_config(ctx, M, Nout, K, epi == NVC_EPI_NONE, &bn, &kps, &splits, &cl, &ks);
   if (force_bn) {          // force_bn = BN + 1000 * KPS + 10000 * CL (KPS 0: the first instantiation of that BN)
     bn = force_bn % 1000;
     kps = (force_bn / 1000) % 10;
@@ -556,11 +557,7 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   if (force_splits >= 100) { splits = force_splits - 100; ks = 1; cl = 1; }
   else if (force_splits) { splits = force_splits; ks = 0; }
   NVC_REQUIRE(ctx, !ks || splits <= 8, NVC_EINVAL, "cluster split-K supports at most 8 splits");
-  if (epi == NVC_EPI_PARTIAL) {    // split-K partials for the consumer to sum: the cluster schedule's (BN, S), no exchange
-    NVC_REQUIRE(ctx, M <= BM && out_dtype == NVC_DT_F32, NVC_ESHAPE, "partial split-K output needs M <= 128 and f32");
-    ks = 0;
-    cl = 1;
-  } else if (epi != NVC_EPI_NONE) {       // the fused epilogue lives in the direct-store path: no split-K, tiles of >= 32 columns
+  if (epi != NVC_EPI_NONE) {       // the fused epilogue lives in the direct-store path: no split-K, tiles of >= 32 columns
     NVC_REQUIRE(ctx, force_splits == 0 || force_splits == 1, NVC_EINVAL, "fused epilogue cannot be combined with split-K");
     splits = 1;
     ks = 0;
@@ -568,7 +565,7 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   }
   if (splits > K / BK) splits = K / BK;
   const int tiles = ((M + BM - 1) / BM) * ((Nout + bn - 1) / bn);
-  if (splits > 1 && !ks && epi != NVC_EPI_PARTIAL) {
+  if (splits > 1 && !ks) {
     NVC_REQUIRE(ctx, (size_t)tiles * splits * BM * bn * 4 <= ctx->gemm_ws_bytes && tiles <= ctx->gemm_num_counters,
                 NVC_ENOMEM, "split-K workspace too small");
   }
@@ -612,31 +609,4 @@ extern "C" int nvc_gemm_bf16_silu_mul_ex(nvc_ctx* ctx, const nvc_bf16* A, int ld
 extern "C" int nvc_gemm_bf16_silu_mul(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W_gu16, nvc_bf16* act,
                                       int ldc, int M, int I, int K, void* stream) {
   return nvc_gemm_bf16_silu_mul_ex(ctx, A, lda, W_gu16, act, ldc, M, I, K, 0, 0, stream);
-}
-
-// Split-K WITHOUT the reduction, for M <= 128: split z writes its fp32 partial of A W^T to P + z * M * Nout (P: f32
-// [splits][M][Nout], capacity max_splits).  *splits_out = the splits written (>= 1); the consumer sums them in order
-// (nvc_fused_add_rmsnorm_partial), which gives the bits of the in-kernel split-K reduction without its cluster
-// exchange.  force_bn / force_splits as nvc_gemm_bf16_ex (0 = the decode schedule's choice; force_splits = S).
-extern "C" int nvc_gemm_bf16_partial(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, float* P, int max_splits,
-                                     int M, int Nout, int K, int force_bn, int force_splits, int* splits_out, void* stream) {
-  NVC_REQUIRE(ctx, ctx && splits_out && max_splits >= 1, NVC_EINVAL, "bad arguments");
-  NVC_REQUIRE(ctx, K > 0 && K % 64 == 0, NVC_ESHAPE, "K must be a multiple of 64");
-  int bn, kps, splits, cl = 1, ks = 0;
-  choose_config(ctx, M > BM ? BM : M, Nout, K, true, &bn, &kps, &splits, &cl, &ks);
-  if (force_splits > 0) splits = force_splits;
-  if (splits > max_splits) splits = max_splits;
-  if (splits > K / BK) splits = K / BK;
-  if (splits < 1) splits = 1;
-  const int kb_total = K / BK, kb_per = (kb_total + splits - 1) / splits;
-  *splits_out = (kb_total + kb_per - 1) / kb_per;
-  return gemm_impl(ctx, A, lda, W, P, Nout, NVC_DT_F32, M, Nout, K, force_bn, splits, NVC_EPI_PARTIAL, stream, nullptr);
-}
-
-// the split-K factor the decode schedule picks for this shape (1: no split; the runner then keeps the plain GEMM)
-extern "C" int nvc_gemm_decode_splits(nvc_ctx* ctx, int M, int Nout, int K) {
-  if (!ctx || M <= 0 || M > BM || K % BK != 0) return 1;
-  int bn, kps, splits, cl = 1, ks = 0;
-  choose_config(ctx, M, Nout, K, true, &bn, &kps, &splits, &cl, &ks);
-  return splits;
 }

@@ -52,28 +52,26 @@ int max_splits_for_batch(int B, int num_sms) {
   return s < 1 ? 1 : (s > 64 ? 64 : s);
 }
 
-template <int kWarps, bool kFused>
+template <int kWarps>
 cudaError_t launch_pd(nvc_ctx* ctx, dim3 grid, cudaStream_t st, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
                       const nvc_bf16* v_cache, const int32_t* block_tables, int max_blocks, const int32_t* context_lens,
                       int nh, int kv, int group, int G, int block_size, float scale_log2e, nvc_bf16* out, float* part_o,
-                      float* part_ml, int splits, const pdmma::FusedArgs& fa) {
-  return nvc_launch(ctx, pdmma::paged_decode_mma_kernel<kWarps, kFused>, grid, dim3(kWarps * 32),
-                    (size_t)pdmma::smem_bytes<kWarps, kFused>(), st, q, ldq, k_cache, v_cache, block_tables, max_blocks,
-                    context_lens, nh, kv, group, G, block_size, scale_log2e, out, part_o, part_ml, splits, fa);
+                      float* part_ml, int splits) {
+  return nvc_launch(ctx, pdmma::paged_decode_mma_kernel<kWarps>, grid, dim3(kWarps * 32),
+                    (size_t)pdmma::smem_bytes<kWarps>(), st, q, ldq, k_cache, v_cache, block_tables, max_blocks,
+                    context_lens, nh, kv, group, G, block_size, scale_log2e, out, part_o, part_ml, splits);
 }
 
-// fa == nullptr: q holds the final (normalised, rotated) query rows and the cache already holds the step's token.
 int paged_decode_impl(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache, const nvc_bf16* v_cache,
                       const int32_t* block_tables, int max_blocks, int max_blocks_hint, const int32_t* context_lens, int B,
                       int nh, int kv, int hd, int block_size, float scale, nvc_bf16* out, void* workspace,
-                      size_t workspace_bytes, void* stream, const pdmma::FusedArgs* fa) {
+                      size_t workspace_bytes, void* stream) {
   NVC_REQUIRE(ctx, ctx && q && k_cache && v_cache && block_tables && context_lens && out, NVC_EINVAL, "null pointer");
   NVC_REQUIRE(ctx, B >= 0 && nh > 0 && kv > 0 && max_blocks > 0 && max_blocks_hint > 0, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, hd == 128, NVC_ESHAPE, "head_dim must be 128");
   NVC_REQUIRE(ctx, nh % kv == 0, NVC_ESHAPE, "nh must be a multiple of kv");
   NVC_REQUIRE(ctx, block_size > 0 && block_size % 16 == 0, NVC_ESHAPE, "block_size must be a multiple of 16");
-  NVC_REQUIRE(ctx, ldq % 8 == 0 && ldq >= (fa ? nh + 2 * kv : nh) * hd, NVC_ESHAPE,
-              "ldq must cover the row (q heads; fused: q, k and v heads) and be a multiple of 8");
+  NVC_REQUIRE(ctx, ldq % 8 == 0 && ldq >= nh * hd, NVC_ESHAPE, "ldq must be >= nh*hd and a multiple of 8");
   if (B == 0) return NVC_OK;
   const int group = nh / kv;
   const int G = group < 16 ? group : 16;
@@ -115,13 +113,10 @@ int paged_decode_impl(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* 
     part_ml = part_o + (size_t)B * nh * splits * hd;
   }
   dim3 grid(kv * chunks, B, splits);
-  pdmma::FusedArgs none{};
-  const pdmma::FusedArgs& a = fa ? *fa : none;
 #define NVC_PD_ARGS ctx, grid, st, q, ldq, k_cache, v_cache, block_tables, max_blocks, context_lens, nh, kv, group, G, \
-                    block_size, scale_log2e, out, part_o, part_ml, splits, a
+                    block_size, scale_log2e, out, part_o, part_ml, splits
   cudaError_t ce;
-  if (fa) ce = warps == 2 ? launch_pd<2, true>(NVC_PD_ARGS) : launch_pd<4, true>(NVC_PD_ARGS);
-  else ce = warps == 2 ? launch_pd<2, false>(NVC_PD_ARGS) : launch_pd<4, false>(NVC_PD_ARGS);
+  ce = warps == 2 ? launch_pd<2>(NVC_PD_ARGS) : launch_pd<4>(NVC_PD_ARGS);
 #undef NVC_PD_ARGS
   NVC_CUDA_CHECK(ctx, ce);
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
@@ -138,14 +133,10 @@ int paged_decode_impl(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* 
 }  // namespace
 
 extern "C" int nvc_paged_decode_init(nvc_ctx* ctx) {
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(pdmma::paged_decode_mma_kernel<4, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           pdmma::smem_bytes<4, false>()));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(pdmma::paged_decode_mma_kernel<4, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           pdmma::smem_bytes<4, true>()));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(pdmma::paged_decode_mma_kernel<2, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           pdmma::smem_bytes<2, false>()));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(pdmma::paged_decode_mma_kernel<2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           pdmma::smem_bytes<2, true>()));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(pdmma::paged_decode_mma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           pdmma::smem_bytes<4>()));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(pdmma::paged_decode_mma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           pdmma::smem_bytes<2>()));
   return NVC_OK;
 }
 
@@ -162,7 +153,7 @@ extern "C" int nvc_paged_decode_attn_ex(nvc_ctx* ctx, const nvc_bf16* q, int ldq
                                         int hd, int block_size, float scale, nvc_bf16* out, void* workspace,
                                         size_t workspace_bytes, void* stream) {
   return paged_decode_impl(ctx, q, ldq, k_cache, v_cache, block_tables, max_blocks, max_blocks_hint, context_lens, B, nh, kv,
-                           hd, block_size, scale, out, workspace, workspace_bytes, stream, nullptr);
+                           hd, block_size, scale, out, workspace, workspace_bytes, stream);
 }
 
 extern "C" int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
@@ -172,21 +163,4 @@ extern "C" int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, c
                                      void* stream) {
   return nvc_paged_decode_attn_ex(ctx, q, ldq, k_cache, v_cache, block_tables, max_blocks, max_blocks, context_lens, B,
                                   nh, kv, hd, block_size, scale, out, workspace, workspace_bytes, stream);
-}
-
-// K2 + K5 in one launch for a pure decode step (one new token per sequence): qkv holds the RAW fused projection rows
-// [q heads | k heads | v heads]; q and the new k are RMS-normalised (q_norm_w / k_norm_w, eps) and rotated with the
-// cos / sin row of positions[b] inside the kernel, the new k / v rows are written to the cache at slot_mapping[b]
-// (which must be the slot of position context_lens[b] - 1) and attended to from registers.  qkv is not modified.
-extern "C" int nvc_paged_decode_attn_fused(nvc_ctx* ctx, const nvc_bf16* qkv, int ldq, const nvc_bf16* q_norm_w,
-                                           const nvc_bf16* k_norm_w, float eps, const float* cos_sin,
-                                           const int32_t* positions, const int32_t* slot_mapping, nvc_bf16* k_cache,
-                                           nvc_bf16* v_cache, const int32_t* block_tables, int max_blocks,
-                                           int max_blocks_hint, const int32_t* context_lens, int B, int nh, int kv, int hd,
-                                           int block_size, float scale, nvc_bf16* out, void* workspace,
-                                           size_t workspace_bytes, void* stream) {
-  NVC_REQUIRE(ctx, ctx && q_norm_w && k_norm_w && cos_sin && positions && slot_mapping, NVC_EINVAL, "null pointer");
-  pdmma::FusedArgs fa{q_norm_w, k_norm_w, cos_sin, positions, slot_mapping, k_cache, v_cache, eps, g_nvc_debug[6]};
-  return paged_decode_impl(ctx, qkv, ldq, k_cache, v_cache, block_tables, max_blocks, max_blocks_hint, context_lens, B, nh,
-                           kv, hd, block_size, scale, out, workspace, workspace_bytes, stream, &fa);
 }

@@ -16,13 +16,6 @@
 // kWarps = 4: 96 KB of rings, 2 CTAs per SM (296 resident).  kWarps = 2: 48 KB, 4 CTAs per SM (592
 // resident): the same bytes in flight per SM, but a grid of 297..592 CTAs (Qwen3-0.6B at batch 64:
 // 512) is resident at once instead of running 1.7 waves with a synchronised bubble between them.
-//
-// kFused = true folds K2 (q/k RMSNorm + RoPE + KV-cache store of the step's new token,
-// src/models/qwen3.rs:206-234, src/layers/rotary_embedding.rs:82-107) into the prologue: q is read raw
-// from the fused qkv row, normalised and rotated into shared memory with the arithmetic (and summation
-// order) of qk_norm_rope_store_kernel, and the warp whose tile holds position ctx_len - 1 computes the
-// new k / v row, writes it to the cache and patches it into its shared-memory tile.  Every cache row
-// the kernel LOADS is then older than this step, so all of them may be requested before the PDL wait.
 #pragma once
 #include "common.cuh"
 
@@ -31,9 +24,8 @@ namespace pdmma {
 constexpr int kTileTok = 16;                         // tokens per warp tile
 constexpr int kStages = 3;
 constexpr int kStageBytes = 2 * kTileTok * 256;      // K tile + V tile, 256 B per token row
-constexpr int kQBytes = 16 * 256;                    // fused: the group's normalised q rows (bf16, swizzled)
-template <int kWarps, bool kFused>
-constexpr int smem_bytes() { return kWarps * kStages * kStageBytes + (kFused ? kQBytes : 0); }
+template <int kWarps>
+constexpr int smem_bytes() { return kWarps * kStages * kStageBytes; }
 
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;
@@ -61,77 +53,22 @@ __device__ __forceinline__ void mma_bf16(float* d, const uint32_t* a, uint32_t b
       : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
       : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
-__device__ __forceinline__ void st_shared_u4(uint32_t addr, const uint4& v) {
-  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-
-// The step's new token of a fused launch (kFused): raw fused qkv rows in, normalised + rotated k and the raw v out
-// to the cache.  positions / slot_mapping / rope / norm weights are step inputs or weights (no kernel of the step
-// writes them).
-struct FusedArgs {
-  const nvc_bf16* q_norm_w;
-  const nvc_bf16* k_norm_w;
-  const float* cos_sin;            // [max_pos][128]: cos[64], sin[64]
-  const int32_t* positions;        // [B]
-  const int32_t* slot_mapping;     // [B]
-  nvc_bf16* k_cache_w;             // the same pools the kernel reads, writable
-  nvc_bf16* v_cache_w;
-  float eps;
-  int dbg;                         // TEMP bisect: 1 = skip the owner's k / v work, 2 = skip the q transform
-};
-
-// One 8-lane unit (lane l = 0..7 owns dims [8l, 8l+8) and [64+8l, 64+8l+8)) normalises and rotates one head row
-// with the arithmetic and the summation order of qk_norm_rope_store_kernel (elementwise.cu): the fused and the
-// stand-alone K2 give bit-identical q / k.  Inactive units contribute zeros and return zero rows.
-__device__ __forceinline__ void norm_rope_unit(bool active, const uint4& ra, const uint4& rb, unsigned mask, const uint4& w_lo,
-                                               const uint4& w_hi, const float4& c0, const float4& c1, const float4& s0,
-                                               const float4& s1, float eps, uint4& o1, uint4& o2) {
-  float a[8], b[8];                                    // ra / rb: this lane's two 16-byte pieces (zeros when inactive)
-  unpack8(ra, a);
-  unpack8(rb, b);
-  float ss = 0.f;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) ss += a[i] * a[i] + b[i] * b[i];
-  ss += __shfl_xor_sync(mask, ss, 1);
-  ss += __shfl_xor_sync(mask, ss, 2);
-  ss += __shfl_xor_sync(mask, ss, 4);
-  const float rstd = 1.0f / sqrtf(ss * (1.0f / 128.0f) + eps);
-  float wa[8], wb[8];
-  unpack8(w_lo, wa);
-  unpack8(w_hi, wb);
-  const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-  const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-  float y1[8], y2[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const float x1 = a[i] * rstd * wa[i];
-    const float x2 = b[i] * rstd * wb[i];
-    y1[i] = x1 * c[i] - x2 * s[i];
-    y2[i] = x2 * c[i] + x1 * s[i];
-  }
-  o1 = pack8(y1);
-  o2 = pack8(y2);
-  if (!active) o1 = o2 = make_uint4(0u, 0u, 0u, 0u);
-}
-
 // group_total: query heads per kv head; gchunk: heads of the group handled by one CTA (<= 16).
 // num_splits > 1: every split parks its (m, l, o) partial in part_o / part_ml for paged_decode_combine_kernel.
-// kFused: q points at the fused qkv rows ([q heads | k heads | v heads], ldq elements per sequence).
-template <int kWarps, bool kFused>
+template <int kWarps>
 __global__ void __launch_bounds__(kWarps * 32, kWarps == 4 ? 2 : 4)
 paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16* __restrict__ k_cache,
                         const nvc_bf16* __restrict__ v_cache, const int32_t* __restrict__ block_tables, int max_blocks,
                         const int32_t* __restrict__ context_lens, int nh, int kv, int group_total, int gchunk,
                         int block_size, float scale_log2e, nvc_bf16* __restrict__ out, float* __restrict__ part_o,
-                        float* __restrict__ part_ml, int num_splits, FusedArgs fa) {
+                        float* __restrict__ part_ml, int num_splits) {
   constexpr int kThreads = kWarps * 32;
   constexpr int kCtaTok = kWarps * kTileTok;          // tokens per CTA iteration
   extern __shared__ __align__(128) uint8_t smem[];
   pdl_trigger();
   // The dependency wait comes AFTER the first K / V tiles are in flight (see below): context_lens and
   // block_tables are step inputs (copied before the step's first kernel), and the only cache rows a
-  // kernel of this step writes are the newest token's (position ctx_len - 1: K2 of this layer, or, fused, this
-  // kernel itself - which then never loads that row).
+  // kernel of this step writes are the newest token's (position ctx_len - 1: K2 of this layer).
   const int chunks = (group_total + gchunk - 1) / gchunk;
   const int kvh = blockIdx.x / chunks;
   const int chunk = blockIdx.x - kvh * chunks;
@@ -141,27 +78,11 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int quad = lane >> 2, tq = lane & 3;          // accumulator row (quad, quad + 8), column pair tq
 
-  // independent first loads, issued together: the context length, the first block id (the block of this warp's first
-  // tile whenever the CTA starts at tile 0) and, fused, the position that selects the cos / sin row
+  // independent first loads, issued together: the context length and the first block id (the block of this warp's
+  // first tile whenever the CTA starts at tile 0) - one load latency instead of two before the first cp.async
   const int32_t* bt = block_tables + (int64_t)b * max_blocks;
-  const int pos_in = kFused ? __ldg(fa.positions + b) : 0;
   const int blk_first = __ldg(bt);
   const int ctx_len = __ldg(context_lens + b);
-  const int l8 = lane & 7;
-  const unsigned mask8 = 0xffu << (lane & 24);
-  uint4 qw_lo, qw_hi, kw_lo, kw_hi, k_new1, k_new2, v_new;
-  float4 c0, c1, s0, s1;
-  if (kFused) {
-    // static operands of the q / k transform: in flight while the block table is walked
-    const uint4* qw = reinterpret_cast<const uint4*>(fa.q_norm_w);
-    const uint4* kw = reinterpret_cast<const uint4*>(fa.k_norm_w);
-    qw_lo = __ldg(qw + l8); qw_hi = __ldg(qw + l8 + 8);
-    kw_lo = __ldg(kw + l8); kw_hi = __ldg(kw + l8 + 8);
-    const float4* cs = reinterpret_cast<const float4*>(fa.cos_sin) + (int64_t)pos_in * 32;
-    c0 = __ldg(cs + 2 * l8); c1 = __ldg(cs + 2 * l8 + 1);
-    s0 = __ldg(cs + 16 + 2 * l8); s1 = __ldg(cs + 16 + 2 * l8 + 1);
-  }
-  const int n_load = kFused ? ctx_len - 1 : ctx_len;  // cache rows [0, n_load) are loaded; fused: the last one is made here
   const int n_tiles = (ctx_len + kCtaTok - 1) / kCtaTok;
   const int tiles_per_split = (n_tiles + num_splits - 1) / num_splits;
   const int t_begin = split * tiles_per_split;
@@ -173,11 +94,10 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
 
   const uint32_t ring = smem_u32(smem) + warp * (kStages * kStageBytes);
-  const uint32_t q_sm = smem_u32(smem) + kWarps * (kStages * kStageBytes);     // fused only
   const int my_tiles = t_end - t_begin;                // CTA tiles; this warp's tile i covers tokens (t_begin+i)*kCtaTok + 16w
 
-  // issue the loads of warp tile i into ring stage i % kStages (empty group if i is out of range); rows at or past
-  // n_load are zero-filled (a fused launch zero-fills the new token's row and patches it after the copy has landed)
+  // issue the loads of warp tile i into ring stage i % kStages (empty group if i is out of range); rows past the
+  // context are zero-filled
   auto issue = [&](int i) {
     if (i < my_tiles) {
       const int tok0 = (t_begin + i) * kCtaTok + warp * kTileTok;
@@ -190,7 +110,7 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
 #pragma unroll
         for (int rr = 0; rr < 8; ++rr) {
           const int r = rr * 2 + (lane >> 4);          // token row inside the tile
-          const uint32_t ok = (tok0 + r < n_load) ? 16u : 0u;
+          const uint32_t ok = (tok0 + r < ctx_len) ? 16u : 0u;
           const int64_t goff = ((slot0 + (ok ? r : 0)) * kv + kvh) * 256 + c * 16;
           const uint32_t soff = r * 256 + ((c ^ (r & 7)) << 4);
           cp_async16(st + soff, reinterpret_cast<const uint8_t*>(k_cache) + goff, ok);
@@ -203,9 +123,8 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
 
   // Tiles that cannot hold the newest token are immutable during this step: start them while the
   // predecessor is still running.  A warp's tiles ascend in position, so "tile i is safe" is monotone in i; an
-  // out-of-range tile is an empty group.  Fused: every row that is loaded is older than the step.
+  // out-of-range tile is an empty group.
   auto safe = [&](int i) {
-    if (kFused) return true;
     const int tok0 = (t_begin + i) * kCtaTok + warp * kTileTok;
     return i >= my_tiles || tok0 >= ctx_len || tok0 + kTileTok <= ctx_len - 1;
   };
@@ -218,70 +137,10 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
       pre = 2;
     }
   }
-  // fused: the new token's position / tile owner, and the static operands of the q / k transform
-  const int pos_new = ctx_len - 1;
-  const bool owner = kFused && ctx_len > 0 && pos_new / kCtaTok >= t_begin && pos_new / kCtaTok < t_end &&
-                     (pos_new % kCtaTok) / kTileTok == warp;            // warp-uniform
-  const int r_new = pos_new & (kTileTok - 1);
   pdl_wait();
   // ---- Q as A fragments: 8 k-steps of 16 dims; rows >= G are zero
   uint32_t qa[8][4];
-  if (kFused) {
-    // every load first: the raw q rows of this lane's units (8 lanes per head), the owner's new k / v rows and slot
-    constexpr int kUnits = 16 / (kWarps * 4);         // head rows per 8-lane unit: 1 (4 warps) or 2 (2 warps)
-    uint4 qa_raw[kUnits], qb_raw[kUnits], ka_raw = make_uint4(0, 0, 0, 0), kb_raw = ka_raw;
-    int slot = -1;
-#pragma unroll
-    for (int i = 0; i < kUnits; ++i) {
-      const int u = warp * 4 + (lane >> 3) + i * kWarps * 4;
-      qa_raw[i] = qb_raw[i] = make_uint4(0, 0, 0, 0);
-      if (u < G) {
-        const uint4* row = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(head0 + u) * 128);
-        qa_raw[i] = row[l8];
-        qb_raw[i] = row[l8 + 8];
-      }
-    }
-    if (owner && !(fa.dbg & 1)) {
-      const uint4* krow = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(nh + kvh) * 128);
-      const uint4* vrow = reinterpret_cast<const uint4*>(q + (int64_t)b * ldq + (int64_t)(nh + kv + kvh) * 128);
-      if (lane < 8) { ka_raw = krow[l8]; kb_raw = krow[l8 + 8]; }
-      if (lane >= 16) v_new = vrow[lane - 16];
-      slot = __ldg(fa.slot_mapping + b);
-    }
-    // normalise + rotate into shared memory (16-byte chunk c of row u at chunk c ^ (u & 7)); rows >= G are zeros
-#pragma unroll
-    for (int i = 0; i < kUnits; ++i) {
-      const int u = warp * 4 + (lane >> 3) + i * kWarps * 4;
-      uint4 o1, o2;
-      if (fa.dbg & 2) { o1 = qa_raw[i]; o2 = qb_raw[i]; }
-      else norm_rope_unit(u < G, qa_raw[i], qb_raw[i], mask8, qw_lo, qw_hi, c0, c1, s0, s1, fa.eps, o1, o2);
-      st_shared_u4(q_sm + u * 256 + ((l8 ^ (u & 7)) << 4), o1);
-      st_shared_u4(q_sm + u * 256 + (((l8 + 8) ^ (u & 7)) << 4), o2);
-    }
-    if (owner && !(fa.dbg & 1)) {
-      // the step's new k row (lanes 0..7, same unit arithmetic) and v row (lanes 16..31, one 16-byte chunk each):
-      // kept in registers for the tile patch below; the CTA of the group's first chunk writes them to the cache
-      norm_rope_unit(lane < 8, ka_raw, kb_raw, mask8, kw_lo, kw_hi, c0, c1, s0, s1, fa.eps, k_new1, k_new2);
-      if (chunk == 0 && slot >= 0) {
-        if (lane < 8) {
-          uint4* dst = reinterpret_cast<uint4*>(fa.k_cache_w) + ((int64_t)slot * kv + kvh) * 16;
-          dst[lane] = k_new1;
-          dst[lane + 8] = k_new2;
-        } else if (lane >= 16) {
-          reinterpret_cast<uint4*>(fa.v_cache_w)[((int64_t)slot * kv + kvh) * 16 + (lane - 16)] = v_new;
-        }
-      }
-    }
-    __syncthreads();
-    // ldmatrix.x4: matrices (rows 0-7, k lo), (rows 8-15, k lo), (rows 0-7, k hi), (rows 8-15, k hi) = a0..a3
-    const int mi = lane >> 3;
-    const int row = (lane & 7) + ((mi & 1) << 3);
-#pragma unroll
-    for (int ks = 0; ks < 8; ++ks) {
-      const int c = 2 * ks + (mi >> 1);
-      ldmatrix_x4(q_sm + row * 256 + ((c ^ (row & 7)) << 4), qa[ks][0], qa[ks][1], qa[ks][2], qa[ks][3]);
-    }
-  } else {
+  {
     const nvc_bf16* qrow0 = q + (int64_t)b * ldq + (int64_t)(head0 + quad) * 128;
     const nvc_bf16* qrow1 = qrow0 + 8 * 128;
     const bool r0 = quad < G, r1 = quad + 8 < G;
@@ -303,16 +162,6 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
     const int tok0 = (t_begin + i) * kCtaTok + warp * kTileTok;
     if (tok0 < ctx_len) {                             // warp-uniform
       const uint32_t st = ring + (i % kStages) * kStageBytes;
-      if (kFused && owner && tok0 + r_new == pos_new) {
-        // the zero-filled row of the new token becomes the k / v computed above
-        if (lane < 8) {
-          st_shared_u4(st + r_new * 256 + ((lane ^ (r_new & 7)) << 4), k_new1);
-          st_shared_u4(st + r_new * 256 + (((lane + 8) ^ (r_new & 7)) << 4), k_new2);
-        } else if (lane >= 16) {
-          st_shared_u4(st + kTileTok * 256 + r_new * 256 + (((lane - 16) ^ (r_new & 7)) << 4), v_new);
-        }
-        __syncwarp();
-      }
       // ---- S = Q K^T: two n-tiles of 8 tokens, fp32
       float s[2][4];
 #pragma unroll
@@ -394,7 +243,7 @@ paged_decode_mma_kernel(const nvc_bf16* __restrict__ q, int ldq, const nvc_bf16*
   l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
 
 
-  // ---- merge the warps through shared memory (the rings are dead now; the fused q rows sit behind them)
+  // ---- merge the warps through shared memory (the rings are dead now)
   __syncthreads();
   float* sm_m = reinterpret_cast<float*>(smem);                    // [kWarps][16]
   float* sm_l = sm_m + kWarps * 16;                                // [kWarps][16]

@@ -26,7 +26,6 @@ struct Layer {
 };
 
 struct ArgPair { float val; int32_t idx; };
-constexpr int kMaxPartialSplits = 8;   // split-K partial buffer of the decode path (nvc_gemm_bf16_partial)
 
 }  // namespace
 
@@ -47,7 +46,6 @@ struct nvc_runner {
   // activations
   nvc_bf16 *x = nullptr, *xn = nullptr, *qkv = nullptr, *attn = nullptr, *act = nullptr;
   float* residual = nullptr;
-  float* xp = nullptr;              // decode at TP 1: fp32 split-K partials of o_proj / down_proj [splits][B][H]
   nvc_bf16 *x_last = nullptr, *xn_last = nullptr;
   float *res_last = nullptr, *logits = nullptr;
   void* decode_ws = nullptr;
@@ -55,7 +53,7 @@ struct nvc_runner {
   // step inputs on device + pinned staging
   int32_t* d_cu2 = nullptr;     // mixed step: cu_seqlens of the prompt chunks, relative to their first token
   int32_t *d_ids = nullptr, *d_pos = nullptr, *d_cu = nullptr, *d_slots = nullptr, *d_bt = nullptr, *d_ctx = nullptr,
-          *d_last_rows = nullptr, *d_tok = nullptr, *d_neg = nullptr;   // d_neg: max_num_seqs x -1
+          *d_last_rows = nullptr, *d_tok = nullptr;
   float* d_tok_val = nullptr;
   ArgPair* d_pairs = nullptr;
   int32_t* h_stage = nullptr;   // pinned
@@ -115,13 +113,6 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
   const int H = c.hidden_size, hd = c.head_dim, L = c.num_hidden_layers;
   const float scale = 1.0f / sqrtf((float)hd);   // (head_dim as f32).powf(-0.5), qwen3.rs:132
   static const bool p2p_env = !(getenv("NVC_P2P_AR") && atoi(getenv("NVC_P2P_AR")) == 0);
-  // decode at TP 1: o_proj / down_proj split along K store their fp32 partials and the norm that follows sums them
-  // (no cluster exchange inside the GEMM); NVC_SPLITK_NORM=0 keeps the in-kernel reduction
-  static const bool splitk_env = !(getenv("NVC_SPLITK_NORM") && atoi(getenv("NVC_SPLITK_NORM")) == 0);
-  const bool part_ok = decode && r->tp == 1 && N <= 128 && splitk_env && r->xp != nullptr;
-  const bool part_o = part_ok && nvc_gemm_decode_splits(ctx, N, H, r->nh_l * hd) > 1;
-  const bool part_d = part_ok && nvc_gemm_decode_splits(ctx, N, H, r->I_l) > 1;
-  static const bool fused_k2 = !(getenv("NVC_FUSED_K2") && atoi(getenv("NVC_FUSED_K2")) == 0);
   // NVLS (in-switch) all-reduce + residual + norm for every step kind; else the peer-load kernel for decode-sized
   // messages; else NCCL + the norm kernel
   const bool nvls = r->tp > 1 && r->x_nvls && nvc_ctx_nvls_ready(ctx);
@@ -142,18 +133,10 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     xn_ready = false;
     rc = nvc_gemm_bf16(ctx, r->xn, H, Ly.w_qkv, r->qkv, r->qkv_l, NVC_DT_BF16, N, r->qkv_l, H, st);
     if (rc) return rc;
-    // pure decode step: K2 (q/k-norm + RoPE + store of the new token) runs inside the paged decode kernel's prologue
-    if (!(decode && fused_k2)) {
-      rc = nvc_qk_norm_rope_store(ctx, r->qkv, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos, r->d_slots,
-                                  Ly.k_cache, Ly.v_cache, N, r->nh_l, r->kv_l, hd, st);
-      if (rc) return rc;
-    }
-    if (decode && fused_k2) {
-      rc = nvc_paged_decode_attn_fused(ctx, r->qkv, r->qkv_l, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos,
-                                       r->d_slots, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint, r->d_ctx,
-                                       B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn, r->decode_ws,
-                                       r->decode_ws_bytes, st);
-    } else if (decode) {
+    rc = nvc_qk_norm_rope_store(ctx, r->qkv, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos, r->d_slots,
+                                Ly.k_cache, Ly.v_cache, N, r->nh_l, r->kv_l, hd, st);
+    if (rc) return rc;
+    if (decode) {
       rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
                                     r->d_ctx, B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
                                     r->decode_ws, r->decode_ws_bytes, st);
@@ -177,18 +160,9 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     }
     if (rc) return rc;
     // o_proj (row-parallel) -> [all-reduce, N4] -> post_attention_layernorm with residual add
-    if (part_o) {
-      int sp = 1;
-      rc = nvc_gemm_bf16_partial(ctx, r->attn, r->nh_l * hd, Ly.w_o, r->xp, kMaxPartialSplits, N, H, r->nh_l * hd, 0, 0, &sp, st);
-      if (rc) return rc;
-      rc = nvc_fused_add_rmsnorm_partial(ctx, r->xp, sp, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
-      if (rc) return rc;
-    } else {
     rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, Ly.w_o, p2p ? slot0 : r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
     if (rc) return rc;
-    }
-    if (part_o) {
-    } else if (nvls) {
+    if (nvls) {
       rc = nvc_nvls_allreduce_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, 0, st);
     } else if (p2p) {
       rc = nvc_p2p_allreduce_rmsnorm(ctx, 0, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
@@ -201,19 +175,6 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     rc = nvc_gemm_bf16_silu_mul(ctx, r->xn, H, Ly.w_gu, r->act, r->I_l, N, r->I_l, H, st);
     if (rc) return rc;
     // down_proj (row-parallel) -> [all-reduce, N4]
-    if (part_d) {
-      // the partials are summed by the norm that opens layer l+1 (or the final norm), launched here
-      const bool last = li + 1 == L;
-      int sp = 1;
-      rc = nvc_gemm_bf16_partial(ctx, r->act, r->I_l, Ly.w_down, r->xp, kMaxPartialSplits, N, H, r->I_l, 0, 0, &sp, st);
-      if (rc) return rc;
-      rc = nvc_fused_add_rmsnorm_partial(ctx, r->xp, sp, r->residual, r->residual, last ? r->final_norm : r->layers[li + 1].ln1,
-                                         c.rms_norm_eps, last ? r->xn_last : r->xn, N, H, st);
-      if (rc) return rc;
-      xn_ready = !last;
-      *final_norm_done = last;
-      continue;
-    }
     rc = nvc_gemm_bf16(ctx, r->act, r->I_l, Ly.w_down, p2p ? slot1 : r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
     if (rc) return rc;
     if (nvls) {
@@ -417,7 +378,6 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if (!r->x_nvls && (rc = dev_alloc(r, &r->x, T * H))) return rc;
   if ((rc = dev_alloc(r, &r->xn, T * H))) return rc;
   if ((rc = dev_alloc(r, &r->residual, T * H))) return rc;
-  if (tp == 1 && (rc = dev_alloc(r, &r->xp, (size_t)kMaxPartialSplits * std::min<size_t>(T, 128) * H))) return rc;
   if ((rc = dev_alloc(r, &r->qkv, T * r->qkv_l))) return rc;
   if ((rc = dev_alloc(r, &r->attn, T * r->nh_l * hd))) return rc;
   if ((rc = dev_alloc(r, &r->act, T * r->I_l))) return rc;
@@ -443,8 +403,6 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if ((rc = dev_alloc(r, &r->d_bt, Bm * r->max_blocks_cap))) return rc;
   if ((rc = dev_alloc(r, &r->d_last_rows, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_tok, Bm))) return rc;
-  if ((rc = dev_alloc(r, &r->d_neg, Bm))) return rc;
-  R_CUDA(cudaMemset(r->d_neg, 0xff, Bm * sizeof(int32_t)));
   if ((rc = dev_alloc(r, &r->d_tok_val, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_pairs, Bm * tp))) return rc;
   if ((rc = dev_alloc(r, &r->d_temps, Bm))) return rc;
@@ -949,15 +907,6 @@ extern "C" int nvc_runner_time_op(nvc_runner* r, int op, int iters, float* ms_pe
       Layer& L = r->layers[li];
       switch (op) {
         case NVC_OP_PAGED_DECODE:
-          // what the decode step launches: K2 folded in (slots of -1: the timing runs must not write the caches), or
-          // the plain kernel when NVC_FUSED_K2=0
-          if (!(getenv("NVC_FUSED_K2") && atoi(getenv("NVC_FUSED_K2")) == 0)) {
-            rc = nvc_paged_decode_attn_fused(ctx, r->qkv, r->qkv_l, L.q_norm, L.k_norm, c.rms_norm_eps, r->rope, r->d_pos,
-                                             r->d_neg, L.k_cache, L.v_cache, r->d_bt, r->max_blocks_cap, r->last_decode_hint,
-                                             r->d_ctx, B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
-                                             r->decode_ws, r->decode_ws_bytes, st);
-            break;
-          }
           rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, L.k_cache, L.v_cache, r->d_bt, r->max_blocks_cap,
                                         r->last_decode_hint, r->d_ctx, B, r->nh_l, r->kv_l, hd,
                                         r->opt.kvcache_block_size, scale, r->attn, r->decode_ws, r->decode_ws_bytes, st);

@@ -161,29 +161,6 @@ class Context:
                                          M, N, K, force_bn, force_splits, _stream()), "nvc_gemm_bf16")
         return out
 
-    def gemm_partial(self, a: torch.Tensor, w: torch.Tensor, max_splits=8, force_bn=0, force_splits=0):
-        """split-K partials of a @ w.T (M <= 128): returns f32 [splits, M, N], unreduced."""
-        import ctypes
-        _req(a, BF16, "a"); _req(w, BF16, "w")
-        M, K = a.shape
-        N = w.shape[0]
-        assert w.shape[1] == K and w.is_contiguous() and a.stride(1) == 1
-        buf = torch.empty((max_splits, M, N), dtype=torch.float32, device=a.device)
-        used = ctypes.c_int(0)
-        self._ck(self.l.nvc_gemm_bf16_partial(self.h, _ptr(a), a.stride(0), _ptr(w), _ptr(buf), max_splits, M, N, K,
-                                              force_bn, force_splits, ctypes.byref(used), _stream()), "nvc_gemm_bf16_partial")
-        return buf[:used.value]
-
-    def fused_add_rmsnorm_partial(self, partials, w, eps, residual_in=None, residual_out=None, out=None):
-        _req(partials, torch.float32, "partials"); _req(w, BF16, "w")
-        S, N, H = partials.shape
-        assert partials.is_contiguous()
-        out = torch.empty((N, H), dtype=BF16, device=partials.device) if out is None else out
-        self._ck(self.l.nvc_fused_add_rmsnorm_partial(self.h, _ptr(partials), S, _ptr(residual_in), _ptr(residual_out),
-                                                      _ptr(w), float(eps), _ptr(out), N, H, _stream()),
-                 "nvc_fused_add_rmsnorm_partial")
-        return out
-
     @staticmethod
     def interleave_gate_up(w_gu: torch.Tensor) -> torch.Tensor:
         """[gate; up] rows (reference layout, qwen3.rs:310) -> groups of 16 gate rows then 16 up rows,
@@ -266,25 +243,6 @@ class Context:
                                               _ptr(block_tables), block_tables.shape[1], _ptr(context_lens), B, nh, kv,
                                               hd, block_size, float(scale), _ptr(out), _ptr(self._ws),
                                               self._ws.numel(), _stream()), "nvc_paged_decode_attn")
-        return out
-
-    def paged_decode_attn_fused(self, qkv, q_norm_w, k_norm_w, eps, cos_sin, positions, slot_mapping, k_cache, v_cache,
-                                block_tables, context_lens, nh, kv, hd, block_size, scale, out=None):
-        """K2 + K5 in one launch (pure decode step): raw fused qkv rows in; the new k / v rows are written to the caches."""
-        _req(qkv, BF16, "qkv"); _req(block_tables, torch.int32, "block_tables"); _req(context_lens, torch.int32, "context_lens")
-        _req(positions, torch.int32, "positions"); _req(slot_mapping, torch.int32, "slot_mapping")
-        _req(cos_sin, torch.float32, "cos_sin")
-        B = qkv.shape[0]
-        out = torch.empty((B, nh * hd), dtype=BF16, device=qkv.device) if out is None else out
-        need = self.l.nvc_paged_decode_workspace_bytes(B, nh, hd, self.num_sms)
-        if self._ws is None or self._ws.numel() < need:
-            self._ws = torch.empty(max(need, 1), dtype=torch.uint8, device=qkv.device)
-        self._ck(self.l.nvc_paged_decode_attn_fused(self.h, _ptr(qkv), qkv.stride(0), _ptr(q_norm_w), _ptr(k_norm_w),
-                                                    float(eps), _ptr(cos_sin), _ptr(positions), _ptr(slot_mapping),
-                                                    _ptr(k_cache), _ptr(v_cache), _ptr(block_tables), block_tables.shape[1],
-                                                    block_tables.shape[1], _ptr(context_lens), B, nh, kv, hd, block_size,
-                                                    float(scale), _ptr(out), _ptr(self._ws), self._ws.numel(), _stream()),
-                 "nvc_paged_decode_attn_fused")
         return out
 
     def silu_and_mul(self, x, out=None):

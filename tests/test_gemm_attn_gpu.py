@@ -108,48 +108,6 @@ def test_gemm_bf16(ctx, M, N, K, bn, splits, out_dtype):
     _close(out, ref, 2e-3, rtol, f"gemm M={M} N={N} K={K} bn={bn} s={splits} {out_dtype}")
 
 
-@pytest.mark.parametrize("M,N,K,bn,splits", [
-    (64, 1024, 2048, 0, 0),         # 0.6B o_proj: the decode schedule's own (BN, S)
-    (64, 1024, 3072, 0, 0),         # 0.6B down_proj
-    (64, 1024, 2048, 4032, 4),      # forced BN = 32, 4 splits: same k ranges as the cluster split-K case below
-    (64, 1024, 2048, 2064, 8),      # BN = 64, 8 splits
-    (1, 1024, 1024, 4032, 4),       # M = 1
-    (100, 2000, 1088, 4032, 4),     # ragged N, 17 k-blocks (5 + 5 + 5 + 2)
-    (128, 4096, 4096, 0, 0),        # 8B o_proj at batch 128 (the schedule may keep one split)
-    (64, 1024, 2048, 4032, 1),      # one split: fp32 output of the plain GEMM
-])
-def test_gemm_partial_and_norm(ctx, M, N, K, bn, splits):
-    """split-K partials left unreduced by the GEMM and summed by the RMSNorm that follows: the sum rounded to bf16 must
-    equal the GEMM's own cluster split-K result bit for bit (same splits, same order), and the norm over the partials
-    must equal nvc_fused_add_rmsnorm over that bf16 result bit for bit (src/layers/linear.rs:171-198, layernorm.rs:44-60)."""
-    g = torch.Generator().manual_seed(M * 13 + N * 5 + K)
-    a = torch.randn(M, K, generator=g).to(BF16).cuda()
-    w = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(BF16).cuda()
-    part = ctx.gemm_partial(a, w, max_splits=8, force_bn=bn, force_splits=splits)
-    torch.cuda.synchronize()
-    S = part.shape[0]
-    assert 1 <= S <= 8 and (splits == 0 or S == splits)
-    acc = torch.zeros(M, N, device="cuda")
-    for z in range(S):                       # split order, fp32: the order of both device-side reductions
-        acc = acc + part[z]
-    x_bf = acc.to(BF16)
-    _close(x_bf, O.linear(a.float().cpu(), w.float().cpu()), 2e-3, 2 ** -8, f"partial gemm M={M} N={N} K={K} S={S}")
-    if 1 < S <= 8 and bn:
-        same = ctx.gemm(a, w, force_bn=bn, force_splits=100 + S)     # split-K inside a cluster (1,1,S)
-        assert torch.equal(same, x_bf), "partials summed in split order must equal the in-kernel split-K reduction"
-    if N % 8 == 0 and N <= 8192:
-        res = torch.randn(M, N, generator=g).cuda()
-        wn = (1 + 0.2 * torch.randn(N, generator=g)).to(BF16).cuda()
-        r1, r2 = torch.empty_like(res), torch.empty_like(res)
-        o1 = ctx.fused_add_rmsnorm(x_bf, wn, 1e-6, residual_in=res, residual_out=r1)
-        o2 = ctx.fused_add_rmsnorm_partial(part.contiguous(), wn, 1e-6, residual_in=res, residual_out=r2)
-        torch.cuda.synchronize()
-        assert torch.equal(r1, r2) and torch.equal(o1, o2), "norm over partials differs from norm over the reduced bf16 rows"
-        o3 = ctx.fused_add_rmsnorm_partial(part.contiguous(), wn, 1e-6)           # no residual (layer 0 / final norm form)
-        o4 = ctx.fused_add_rmsnorm(x_bf, wn, 1e-6)
-        assert torch.equal(o3, o4)
-
-
 def test_gemm_reference_goldens(ctx):
     """src/layers/linear.rs:231-267 (replicated, exact small integers; bias added on the host
     here since the Qwen3 path has no biases) and :274-319 (two hand-sharded column ranks),
@@ -502,74 +460,3 @@ def test_paged_decode_warps_and_splits(ctx, nvc, nh, kv, block_size, lens_spec, 
         os.environ.pop("NVC_PD_SPLITS", None)
 
 
-@pytest.mark.parametrize("nh,kv,block_size,lens_spec,splits", [
-    (16, 8, 256, ("const", 64, 581), 0),             # the bench shape
-    (16, 8, 256, ("list", [1, 16, 17, 64, 65, 255, 256, 257, 1000, 33]), 0),   # new token first / last in a tile, a block
-    (32, 8, 64, ("uniform", 20, 1, 3000, 2), 3),     # KV splits: only the split that owns the last tile patches it
-    (40, 2, 256, ("list", [33, 700, 1]), 0),         # two head chunks per kv head: both patch, chunk 0 stores
-    (40, 8, 16, ("uniform", 9, 1, 200, 4), 0),       # group 5, block size 16
-    (8, 1, 256, ("uniform", 70, 1, 300, 3), 0),      # TP shard: 70 CTAs -> splits chosen by the launcher
-])
-def test_paged_decode_fused_qk_norm_rope(ctx, nvc, nh, kv, block_size, lens_spec, splits):
-    """K2 folded into the paged decode prologue vs the two-kernel sequence (nvc_qk_norm_rope_store, then
-    nvc_paged_decode_attn) on the same raw qkv rows: the new cache rows and the attention output must be
-    bit-identical, nothing else in the caches may change, and the output must match the fp32 oracle."""
-    import os
-    hd, theta, eps = 128, 1e6, 1e-6
-    lens = _lens(lens_spec)
-    B = len(lens)
-    g = torch.Generator().manual_seed(101 + nh + B)
-    _, kc, vc, bt, _, scale = _paged_case(nh, kv, block_size, lens, 23 + B)
-    qkv = torch.randn(B, (nh + 2 * kv) * hd, generator=g).to(BF16)
-    qw = (1 + 0.2 * torch.randn(hd, generator=g)).to(BF16).cuda()
-    kw = (1 + 0.2 * torch.randn(hd, generator=g)).to(BF16).cuda()
-    lens_t = torch.tensor(lens, dtype=torch.int32)
-    pos = (lens_t - 1).to(torch.int32)
-    slots = (bt[torch.arange(B), (pos // block_size).long()] * block_size + pos % block_size).to(torch.int32)
-    # the slot of the new token is unwritten (poison) before the step
-    kc[slots.long()] = float("nan")
-    vc[slots.long()] = float("nan")
-    tab = ctx.rope_table(theta, hd, 4096)
-    d_bt, d_lens, d_pos, d_slots = bt.cuda(), lens_t.cuda(), pos.cuda(), slots.cuda()
-    # two-kernel sequence
-    kc1, vc1, qkv1 = kc.cuda(), vc.cuda(), qkv.cuda().clone()
-    ctx.qk_norm_rope_store(qkv1, qw, kw, eps, tab, d_pos, nh, kv, hd, slot_mapping=d_slots, k_cache=kc1, v_cache=vc1)
-    o_ref = ctx.paged_decode_attn(qkv1[:, :nh * hd], kc1, vc1, d_bt, d_lens, nh, kv, hd, block_size, scale).clone()
-    torch.cuda.synchronize()
-    if splits:
-        os.environ["NVC_PD_SPLITS"] = str(splits)
-    try:
-        for warps in (2, 4):
-            nvc.lib().nvc_debug_set(5, warps)
-            kc2, vc2, qkv2 = kc.cuda(), vc.cuda(), qkv.cuda().clone()
-            o = ctx.paged_decode_attn_fused(qkv2, qw, kw, eps, tab, d_pos, d_slots, kc2, vc2, d_bt, d_lens, nh, kv, hd,
-                                            block_size, scale)
-            torch.cuda.synchronize()
-            assert torch.equal(qkv2, qkv.cuda()), "the fused kernel must not modify the qkv rows"
-            assert torch.equal(kc2.view(torch.int16), kc1.view(torch.int16)), f"k cache differs (warps={warps})"
-            assert torch.equal(vc2.view(torch.int16), vc1.view(torch.int16)), f"v cache differs (warps={warps})"
-            assert not torch.isnan(o.float()).any()
-            _close(o, o_ref.float().cpu(), 1e-2, 2 ** -7, f"fused vs two-kernel paged decode warps={warps}")
-    finally:
-        nvc.lib().nvc_debug_set(5, 0)
-        os.environ.pop("NVC_PD_SPLITS", None)
-    # same launcher choice as the reference launch -> bit-identical output
-    kc3, vc3 = kc.cuda(), vc.cuda()
-    o3 = ctx.paged_decode_attn_fused(qkv.cuda(), qw, kw, eps, tab, d_pos, d_slots, kc3, vc3, d_bt, d_lens, nh, kv, hd,
-                                     block_size, scale)
-    torch.cuda.synchronize()
-    if not splits:
-        assert torch.equal(o3, o_ref), "fused and two-kernel paged decode must agree bit for bit"
-    # fp32 oracle: normalise + rotate q / k, append k / v, attend (qwen3.rs:205-277)
-    from test_kernels_gpu import _rope_ref
-    q_ref, k_ref = _rope_ref(qkv, qw.cpu(), kw.cpu(), eps, pos, nh, kv, hd, theta)
-    ref = torch.zeros(B, nh * hd)
-    kcf, vcf = kc1.float().cpu(), vc1.float().cpu()
-    for b, c in enumerate(lens):
-        t = torch.arange(c)
-        sl = (bt[b, (t // block_size).long()] * block_size + t % block_size).long()
-        kh = O.gqa_expand(kcf[sl].permute(1, 0, 2)[None], nh // kv)[0]
-        vh = O.gqa_expand(vcf[sl].permute(1, 0, 2)[None], nh // kv)[0]
-        sc = torch.einsum("hd,htd->ht", torch.as_tensor(q_ref[b]).float().to(BF16).float(), kh) * scale
-        ref[b] = torch.einsum("ht,htd->hd", torch.softmax(sc, dim=-1), vh).reshape(-1)
-    _close(o3, ref, 1e-2, 2 ** -7, f"fused paged decode vs oracle nh={nh} kv={kv} bs={block_size}")

@@ -16,7 +16,7 @@ if os.path.exists("MEASURED_PEAKS.json"):
     PEAK = json.load(open("MEASURED_PEAKS.json"))["hbm_gbs"]
 
 
-def bench(B, nh, kv, ctx_len, ragged=False, block_size=256, pools=None, fused=False):
+def bench(B, nh, kv, ctx_len, ragged=False, block_size=256, pools=None):
     hd = 128
     g = torch.Generator().manual_seed(0)
     lens = torch.randint(max(1, ctx_len // 8), ctx_len + 1, (B,), generator=g) if ragged else torch.full((B,), ctx_len)
@@ -36,17 +36,7 @@ def bench(B, nh, kv, ctx_len, ragged=False, block_size=256, pools=None, fused=Fa
     out = torch.empty(B, nh * hd, device="cuda", dtype=BF16)
     btd, ld = bt.cuda(), lens.to(torch.int32).cuda()
     scale = hd ** -0.5
-    if fused:
-        # K2 folded into the prologue: raw fused qkv rows, slots of -1 (the timing runs must not write the pools)
-        qkv = torch.randn(B, (nh + 2 * kv) * hd, device="cuda").to(BF16)
-        qw = torch.ones(hd, device="cuda", dtype=BF16)
-        tab = ctx.rope_table(1e6, hd, 8192)
-        pos = (ld - 1).to(torch.int32)
-        neg = torch.full((B,), -1, dtype=torch.int32, device="cuda")
-        call = lambda i: ctx.paged_decode_attn_fused(qkv, qw, qw, 1e-6, tab, pos, neg, kcs[i], vcs[i], btd, ld, nh, kv, hd,
-                                                     block_size, scale, out=out)
-    else:
-        call = lambda i: ctx.paged_decode_attn(q, kcs[i], vcs[i], btd, ld, nh, kv, hd, block_size, scale, out=out)
+    call = lambda i: ctx.paged_decode_attn(q, kcs[i], vcs[i], btd, ld, nh, kv, hd, block_size, scale, out=out)
     for i in range(2):
         call(i % pools)
     torch.cuda.synchronize()
@@ -96,24 +86,7 @@ def sweep_splits():
         print(f"{name:24s} " + " | ".join(row), flush=True)
 
 
-def fused_bisect():
-    """--fused: the fused-prologue kernel against the plain one on the bench shapes, with pieces of the prologue
-    switched off (nvc_debug_set(6, bits): 1 = no owner k / v work, 2 = no q transform) to see where its time goes."""
-    nvc = importlib.import_module("nano-vllm-candle_b200")
-    for name, B, nh, kv, c in [("0.6B bs64 ctx581", 64, 16, 8, 581), ("8B bs256 ctx1024", 256, 32, 8, 1024),
-                               ("0.6B tp8 bs64 ctx581", 64, 2, 1, 581)]:
-        row = [f"plain {bench(B, nh, kv, c, pools=8)[0]:.2f}"]
-        for bits in (0, 1, 2, 3):
-            nvc.lib().nvc_debug_set(6, bits)
-            row.append(f"fused dbg={bits} {bench(B, nh, kv, c, pools=8, fused=True)[0]:.2f}")
-        nvc.lib().nvc_debug_set(6, 0)
-        print(f"{name:24s} " + " | ".join(row), flush=True)
-
-
 if __name__ == "__main__":
-    if "--fused" in sys.argv:
-        fused_bisect()
-        sys.exit(0)
     if "--splits" in sys.argv:
         sweep_splits()
         sys.exit(0)

@@ -324,14 +324,27 @@ int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, 
 
 #include "prefill_attn_v2.cuh"
 
-constexpr int kDefaultWG = 1;
+// Variant of the second-generation kernel: P through tensor memory (nvc_debug_set(4, 1|2) = off|on) and the share of
+// exponentials on the FMA pipe (nvc_debug_set(6, n): every n-th, n in {2, 3, 4}; -1: none); 0 = the defaults below.
+constexpr bool kDefaultPT = true;
+constexpr int kDefaultPoly = 4;
+bool v2_pt() { return g_nvc_debug[4] == 1 ? false : (g_nvc_debug[4] == 2 ? true : kDefaultPT); }
+int v2_poly() {
+  const int v = g_nvc_debug[6];
+  return v == -1 ? 0 : ((v == 2 || v == 3 || v == 4) ? v : kDefaultPoly);
+}
 
-// NVC_PREFILL_V1=1 (or nvc_debug_set(3, 1)) selects the first-generation kernel (one CTA per SM, 128-token kv tiles)
-// softmax warp-groups of the second-generation kernel: NVC_PREFILL_WG=1|2 or nvc_debug_set(4, 1|2); 0 = default
-int v2_wg() {
-  static const int env = getenv("NVC_PREFILL_WG") ? atoi(getenv("NVC_PREFILL_WG")) : 0;
-  const int w = g_nvc_debug[4] ? g_nvc_debug[4] : env;
-  return w == 2 ? 2 : (w == 1 ? 1 : kDefaultWG);
+template <bool kPaged, typename... Args>
+cudaError_t launch_v2(nvc_ctx* ctx, dim3 grid, cudaStream_t st, Args... args) {
+  const bool pt = v2_pt();
+  const int poly = v2_poly();
+#define NVC_V2(PT, POLY) \
+  if (pt == PT && poly == POLY) \
+    return nvc_launch(ctx, v2::prefill_attn_v2_kernel<kPaged, PT, POLY>, grid, dim3(v2::kThreads), v2::kSmemBytes, st, args...);
+  NVC_V2(true, 0) NVC_V2(true, 2) NVC_V2(true, 3) NVC_V2(true, 4)
+  NVC_V2(false, 0) NVC_V2(false, 2) NVC_V2(false, 3) NVC_V2(false, 4)
+#undef NVC_V2
+  return cudaErrorInvalidValue;
 }
 
 bool use_v1() {
@@ -342,10 +355,13 @@ bool use_v1() {
 }  // namespace
 
 extern "C" int nvc_prefill_attn_init(nvc_ctx* ctx) {
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
+#define NVC_V2_ATTR(PG, PT, POLY) \
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<PG, PT, POLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
+#define NVC_V2_ALL(PG) NVC_V2_ATTR(PG, true, 0) NVC_V2_ATTR(PG, true, 2) NVC_V2_ATTR(PG, true, 3) NVC_V2_ATTR(PG, true, 4) \
+                       NVC_V2_ATTR(PG, false, 0) NVC_V2_ATTR(PG, false, 2) NVC_V2_ATTR(PG, false, 3) NVC_V2_ATTR(PG, false, 4)
+  NVC_V2_ALL(false) NVC_V2_ALL(true)
+#undef NVC_V2_ALL
+#undef NVC_V2_ATTR
   NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   return NVC_OK;
@@ -375,14 +391,8 @@ extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq,
   if (rc) return rc;
   if (!v1) {
     dim3 grid2((max_seqlen + 127) / 128, nh, B);
-    if (v2_wg() == 2)
-      NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<false, 2>, grid2, dim3(v2::kThreads + 128), v2::kSmemBytes,
-                                     nvc_stream(stream), tq, tk, tv, cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out,
-                                     PagedKV{}));
-    else
-      NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<false, 1>, grid2, dim3(v2::kThreads), v2::kSmemBytes,
-                                     nvc_stream(stream), tq, tk, tv, cu_seqlens, nh, nh / kv, scale * 1.4426950408889634f, out,
-                                     PagedKV{}));
+    NVC_CUDA_CHECK(ctx, launch_v2<false>(ctx, grid2, nvc_stream(stream), tq, tk, tv, cu_seqlens, nh, nh / kv,
+                                         scale * 1.4426950408889634f, out, PagedKV{}));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
     ctx->launches++;
     return NVC_OK;
@@ -430,12 +440,8 @@ extern "C" int nvc_prefill_attn_paged(nvc_ctx* ctx, const nvc_bf16* q, int ldq, 
   PagedKV pk{block_tables, context_lens, bt_stride, block_size, box_rows};
   dim3 grid((max_seqlen_q + 127) / 128, nh, B);
   if (!v1) {
-    if (v2_wg() == 2)
-      NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<true, 2>, grid, dim3(v2::kThreads + 128), v2::kSmemBytes,
-                                     nvc_stream(stream), tq, tk, tv, cu_seqlens_q, nh, nh / kv, scale * 1.4426950408889634f, out, pk));
-    else
-      NVC_CUDA_CHECK(ctx, nvc_launch(ctx, v2::prefill_attn_v2_kernel<true, 1>, grid, dim3(v2::kThreads), v2::kSmemBytes,
-                                     nvc_stream(stream), tq, tk, tv, cu_seqlens_q, nh, nh / kv, scale * 1.4426950408889634f, out, pk));
+    NVC_CUDA_CHECK(ctx, launch_v2<true>(ctx, grid, nvc_stream(stream), tq, tk, tv, cu_seqlens_q, nh, nh / kv,
+                                        scale * 1.4426950408889634f, out, pk));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
     ctx->launches++;
     return NVC_OK;

@@ -14,7 +14,7 @@
 
 namespace v2 {
 
-constexpr int kThreads = 192;                  // kWG = 1: TMA warp + MMA warp + 4 softmax warps; kWG = 2: + 4 more softmax warps
+constexpr int kThreads = 192;                  // TMA warp + MMA warp + 4 softmax warps
 constexpr int kKT = 64;                        // kv tokens per tile
 constexpr int kQBytes = 128 * 128 * 2;         // 32 KB: two [128 rows][64 dims] swizzled halves
 constexpr int kHalfKV = kKT * 128;             // 8 KB: [64 tokens][64 dims]
@@ -30,18 +30,26 @@ constexpr int kNumBars = 13;                   // q_full, k_full[2], k_empty[2],
 // two CTAs per SM: 2 x (request + 1 KB reserved) <= 228 KB; the alignment pad is <= 896 B for a 128-byte aligned base
 constexpr int kSmemBytes = 115712;
 static_assert(kOffBar + kNumBars * 8 + 16 + 896 <= kSmemBytes, "shared memory budget for two CTAs per SM");
-constexpr int kOffXch = kOffBar + kNumBars * 8 + 16;   // kWG = 2: 128 floats, row maxima exchanged between the column halves
-static_assert(kOffXch + 512 <= kSmemBytes, "exchange buffer (needs the 1024-byte alignment of the dynamic shared memory)");
-
-__device__ __forceinline__ void bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
-__device__ __forceinline__ void bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 constexpr int kTmemCols = 256;                 // S (double-buffered): columns [0, 64) and [64, 128); O: columns [128, 256)
 
-// kWG = 2: eight softmax warps; warps w and w + 4 share the tensor-memory lane quadrant (rows) and split the kv
-// columns of S (32 each), the columns of O for the rescale / output (64 each) and the P chunks; the row maximum
-// is combined through shared memory once per tile (two named barriers per warp pair), the row sum once at the end.
-template <bool kPaged, int kWG>
-__global__ void __launch_bounds__(64 + 128 * kWG, 2)
+// 2^x for x <= 0 on the FMA pipe (Cody-Waite split + degree-3 minimax polynomial, relative error 9e-5 - below half a
+// bf16 ulp, and P is rounded to bf16): the MUFU unit (16 ex2 per clock per SM) is as loaded as the tensor pipe in this
+// kernel (512 cycles each per 128 x 64 tile), so a fraction of the exponentials is computed here instead.
+__device__ __forceinline__ float exp2_poly(float x) {
+  x = fmaxf(x, -126.0f);
+  const float xr = __fadd_rd(x, 12582912.0f);          // 1.5 * 2^23: floor(x) lands in the low mantissa bits
+  const float f = x - (xr - 12582912.0f);               // [0, 1)
+  float p = fmaf(f, 0.0771190897f, 0.227564394f);
+  p = fmaf(p, f, 0.695146143f);
+  p = fmaf(p, f, 1.0f);
+  return __int_as_float(__float_as_int(p) + (__float_as_int(xr) << 23));
+}
+
+// kPT: P goes back into tensor memory (bf16 pairs over the first 32 columns of the S buffer it came from) and is the
+// A operand of the P V MMA from there - no shared-memory round trip, no proxy fence per tile.
+// kPoly = n > 0: every n-th exponential of a row on the FMA pipe (exp2_poly), the others on the MUFU unit.
+template <bool kPaged, bool kPT, int kPoly>
+__global__ void __launch_bounds__(192, 2)
 prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
                        const __grid_constant__ CUtensorMap tma_v, const int32_t* __restrict__ cu_seqlens,
                        int nh, int group, float scale_log2e, nvc_bf16* __restrict__ out, const PagedKV pk) {
@@ -119,7 +127,7 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       }
       ptx::mbar_init(s_full(0), 1);
       ptx::mbar_init(s_full(1), 1);
-      ptx::mbar_init(p_full, 128 * kWG);
+      ptx::mbar_init(p_full, 128);
       ptx::mbar_init(o_full, 1);
       ptx::fence_barrier_init();
     }
@@ -189,126 +197,20 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
         // 64-wide head-dim halves, SBO = 1 KB between groups of 8 token rows, 16 token rows = 2048 bytes per step)
         const uint32_t v_lo = ptx::umma_desc_lo(base + kOffKV + (j & 1) * kStageBytes + kKBytes, (uint32_t)kHalfKV);
 #pragma unroll
-        for (int ks = 0; ks < kKT / 16; ++ks)
-          ptx::umma_bf16_ss(tmem_o, ptx::umma_desc(p_lo + ((ks * 32) >> 4), hi_k), ptx::umma_desc(v_lo + ks * (2048 >> 4), hi_k),
-                            idesc_pv, (j | ks) != 0);
+        for (int ks = 0; ks < kKT / 16; ++ks) {
+          if constexpr (kPT)     // P(j) sits in the first 32 columns of S buffer j & 1: 8 columns per 16 kv tokens
+            ptx::umma_bf16_ts(tmem_o, tmem_s + (j & 1) * kKT + ks * 8, ptx::umma_desc(v_lo + ks * (2048 >> 4), hi_k), idesc_pv,
+                              (j | ks) != 0);
+          else
+            ptx::umma_bf16_ss(tmem_o, ptx::umma_desc(p_lo + ((ks * 32) >> 4), hi_k), ptx::umma_desc(v_lo + ks * (2048 >> 4), hi_k),
+                              idesc_pv, (j | ks) != 0);
+        }
         ptx::umma_commit(o_full);
         ptx::umma_commit(v_empty(j & 1));
       }
       __syncwarp();
     }
-  } else if constexpr (kWG == 2) {
-    // ------------------------------------------------------------ softmax warps, two per lane quadrant
-    const int quad = warp & 3;                      // tensor-memory lane quadrant = warp % 4
-    const int half = (warp - 2) >> 2;               // column half of this warp
-    const int r = quad * 32 + lane;                 // row in the q tile
-    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
-    float* xch = reinterpret_cast<float*>(gen + kOffXch);
-    if ((base - smem_u32(smem_v2)) + kOffXch + 512 > (uint32_t)kSmemBytes) __trap();   // alignment not honoured
-    const int bar_a = 1 + quad, bar_b = 5 + quad;   // named barriers of the warp pair (64 threads)
-    // row-wise exchange: the upper half publishes, the lower half combines and publishes the result
-    auto combine = [&](float x, bool is_max) {
-      if (half == 1) {
-        xch[r] = x;
-        bar_sync(bar_a, 64);
-        bar_sync(bar_b, 64);
-        return xch[r];
-      }
-      bar_sync(bar_a, 64);
-      const float y = is_max ? fmaxf(x, xch[r]) : x + xch[r];
-      xch[r] = y;
-      __threadfence_block();
-      bar_arrive(bar_b, 64);
-      return y;
-    };
-    constexpr int kC = kKT / 2;                     // S columns per thread
-    float m = -INFINITY, l = 0.f;
-    uint8_t* p_row = gen + kOffP + r * 128;
-    for (int j = 0; j < n_tiles; ++j) {
-      ptx::mbar_wait(s_full(j & 1), (j >> 1) & 1);
-      ptx::tcgen05_fence_after();
-      uint32_t sv[kC];
-      ptx::tmem_ld_32x32b_x32(tmem_s + (j & 1) * kKT + half * kC + lane_addr, sv);
-      ptx::tmem_ld_wait();
-      if (j * kKT + kKT - 1 > q0) {                   // diagonal tile: columns past this row's position -> -inf
-        const int lim = q0 + r - j * kKT - half * kC;
-#pragma unroll
-        for (int i = 0; i < kC; ++i)
-          if (i > lim) sv[i] = 0xff800000u;
-      }
-      float mx = -INFINITY;
-#pragma unroll
-      for (int i = 0; i < kC; ++i) mx = fmaxf(mx, __uint_as_float(sv[i]));
-      mx = combine(mx, true);
-      const float m_new = fmaxf(m, mx * scale_log2e);
-      const float alpha = fast_exp2(m - m_new);
-      float psum = 0.f;
-      uint32_t pk2[kC / 2];
-#pragma unroll
-      for (int i = 0; i < kC; i += 2) {
-        const float p0 = fast_exp2(__uint_as_float(sv[i]) * scale_log2e - m_new);
-        const float p1 = fast_exp2(__uint_as_float(sv[i + 1]) * scale_log2e - m_new);
-        psum += p0 + p1;
-        pk2[i >> 1] = pack_bf16(p0, p1);
-      }
-      l = l * alpha + psum;                           // partial row sum of this column half
-      m = m_new;
-      if (j > 0) {
-        ptx::mbar_wait(o_full, (j - 1) & 1);
-        ptx::tcgen05_fence_after();
-        if (__any_sync(0xffffffffu, alpha != 1.0f)) {
-#pragma unroll 1
-          for (int c = 0; c < 2; ++c) {
-            uint32_t v[32];
-            ptx::tmem_ld_32x32b_x32(tmem_o + lane_addr + half * 64 + c * 32, v);
-            ptx::tmem_ld_wait();
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
-            ptx::tmem_st_32x32b_x32(tmem_o + lane_addr + half * 64 + c * 32, v);
-          }
-          ptx::tmem_st_wait();
-        }
-      }
-#pragma unroll
-      for (int k8 = 0; k8 < kC / 8; ++k8)
-        *reinterpret_cast<uint4*>(p_row + (((half * (kC / 8) + k8) ^ (r & 7)) << 4)) =
-            make_uint4(pk2[4 * k8], pk2[4 * k8 + 1], pk2[4 * k8 + 2], pk2[4 * k8 + 3]);
-      if constexpr (kPaged) {
-        if (j * kKT + kKT > kv_len) ptx::mbar_wait(v_full(j & 1), (j >> 1) & 1);
-        if (r < kKT && j * kKT + r >= kv_len) {       // this warp's head-dim half of the V row
-          uint8_t* v_row = gen + kOffKV + (j & 1) * kStageBytes + kKBytes + half * kHalfKV + r * 128;
-#pragma unroll
-          for (int k16 = 0; k16 < 8; ++k16) *reinterpret_cast<uint4*>(v_row + (k16 << 4)) = make_uint4(0, 0, 0, 0);
-        }
-      }
-      ptx::fence_proxy_async_smem();
-      ptx::tcgen05_fence_before();
-      ptx::mbar_arrive(p_full);
-    }
-    l = combine(l, false);
-    ptx::mbar_wait(o_full, (n_tiles - 1) & 1);
-    ptx::tcgen05_fence_after();
-    const int row_in_seq = qt * 128 + r;
-    const float inv = 1.0f / l;
-    uint4* dst = reinterpret_cast<uint4*>(out + ((int64_t)(seq_start + row_in_seq) * nh + h) * 128 + half * 64);
-#pragma unroll 1
-    for (int c = 0; c < 2; ++c) {
-      uint32_t v[32];
-      ptx::tmem_ld_32x32b_x32(tmem_o + lane_addr + half * 64 + c * 32, v);
-      ptx::tmem_ld_wait();
-      if (row_in_seq < seq_len) {
-#pragma unroll
-        for (int k8 = 0; k8 < 4; ++k8) {
-          float o[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) o[i] = __uint_as_float(v[k8 * 8 + i]) * inv;
-          dst[c * 4 + k8] = pack8(o);
-        }
-      }
-    }
-    ptx::tcgen05_fence_before();
   } else {
-
     // ------------------------------------------------------------ softmax / correction / output warps
     const int quad = warp & 3;
     const int r = quad * 32 + lane;                 // row in the q tile
@@ -339,8 +241,9 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       uint32_t pk2[kKT / 2];
 #pragma unroll
       for (int i = 0; i < kKT; i += 2) {
-        const float p0 = fast_exp2(__uint_as_float(sv[i]) * scale_log2e - m_new);
-        const float p1 = fast_exp2(__uint_as_float(sv[i + 1]) * scale_log2e - m_new);
+        const float x0 = __uint_as_float(sv[i]) * scale_log2e - m_new, x1 = __uint_as_float(sv[i + 1]) * scale_log2e - m_new;
+        const float p0 = (kPoly > 0 && i % kPoly == kPoly - 1) ? exp2_poly(x0) : fast_exp2(x0);
+        const float p1 = (kPoly > 0 && (i + 1) % kPoly == kPoly - 1) ? exp2_poly(x1) : fast_exp2(x1);
         psum += p0 + p1;
         pk2[i >> 1] = pack_bf16(p0, p1);
       }
@@ -363,11 +266,17 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
           ptx::tmem_st_wait();
         }
       }
-      // P -> bf16, swizzled store (16-byte chunk ^= row % 8): the A operand of the second MMA
+      if constexpr (kPT) {
+        // P -> bf16 pairs over the S columns this thread has just read (its own lane): the A operand of the second MMA
+        ptx::tmem_st_32x32b_x32(tmem_s + (j & 1) * kKT + lane_addr, pk2);
+        ptx::tmem_st_wait();
+      } else {
+        // P -> bf16, swizzled store (16-byte chunk ^= row % 8): the A operand of the second MMA
 #pragma unroll
-      for (int k8 = 0; k8 < kKT / 8; ++k8)
-        *reinterpret_cast<uint4*>(p_row + ((k8 ^ (r & 7)) << 4)) =
-            make_uint4(pk2[4 * k8], pk2[4 * k8 + 1], pk2[4 * k8 + 2], pk2[4 * k8 + 3]);
+        for (int k8 = 0; k8 < kKT / 8; ++k8)
+          *reinterpret_cast<uint4*>(p_row + ((k8 ^ (r & 7)) << 4)) =
+              make_uint4(pk2[4 * k8], pk2[4 * k8 + 1], pk2[4 * k8 + 2], pk2[4 * k8 + 3]);
+      }
       if constexpr (kPaged) {
         // V rows at / past the end of the context (last tile only): zero them (every P column there is 0,
         // but the cache bytes may be NaN) once the slot's TMA has landed; the proxy fence below orders these
@@ -382,7 +291,7 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
           }
         }
       }
-      ptx::fence_proxy_async_smem();
+      if (!kPT || kPaged) ptx::fence_proxy_async_smem();    // generic shared-memory stores (P, zeroed V rows) before the MMA reads them
       ptx::tcgen05_fence_before();
       ptx::mbar_arrive(p_full);
     }

@@ -324,27 +324,12 @@ int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, 
 
 #include "prefill_attn_v2.cuh"
 
-// Variant of the second-generation kernel: P through tensor memory (nvc_debug_set(4, 1|2) = off|on) and the share of
-// exponentials on the FMA pipe (nvc_debug_set(6, n): every n-th, n in {2, 3, 4}; -1: none); 0 = the defaults below.
-constexpr bool kDefaultPT = true;
-constexpr int kDefaultPoly = 4;
-bool v2_pt() { return g_nvc_debug[4] == 1 ? false : (g_nvc_debug[4] == 2 ? true : kDefaultPT); }
-int v2_poly() {
-  const int v = g_nvc_debug[6];
-  return v == -1 ? 0 : ((v == 2 || v == 3 || v == 4) ? v : kDefaultPoly);
-}
-
+// persistent grid of the second-generation kernel: two CTAs per SM, or one CTA per work item when there are fewer
 template <bool kPaged, typename... Args>
-cudaError_t launch_v2(nvc_ctx* ctx, dim3 grid, cudaStream_t st, Args... args) {
-  const bool pt = v2_pt();
-  const int poly = v2_poly();
-#define NVC_V2(PT, POLY) \
-  if (pt == PT && poly == POLY) \
-    return nvc_launch(ctx, v2::prefill_attn_v2_kernel<kPaged, PT, POLY>, grid, dim3(v2::kThreads), v2::kSmemBytes, st, args...);
-  NVC_V2(true, 0) NVC_V2(true, 2) NVC_V2(true, 3) NVC_V2(true, 4)
-  NVC_V2(false, 0) NVC_V2(false, 2) NVC_V2(false, 3) NVC_V2(false, 4)
-#undef NVC_V2
-  return cudaErrorInvalidValue;
+cudaError_t launch_v2(nvc_ctx* ctx, int QT, int nh, int B, cudaStream_t st, Args... args) {
+  const long long items = (long long)QT * nh * B;
+  const int grid = (int)(items < 2LL * ctx->num_sms ? items : 2LL * ctx->num_sms);
+  return nvc_launch(ctx, v2::prefill_attn_v2_kernel<kPaged>, dim3(grid), dim3(v2::kThreads), v2::kSmemBytes, st, args...);
 }
 
 bool use_v1() {
@@ -355,13 +340,8 @@ bool use_v1() {
 }  // namespace
 
 extern "C" int nvc_prefill_attn_init(nvc_ctx* ctx) {
-#define NVC_V2_ATTR(PG, PT, POLY) \
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<PG, PT, POLY>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
-#define NVC_V2_ALL(PG) NVC_V2_ATTR(PG, true, 0) NVC_V2_ATTR(PG, true, 2) NVC_V2_ATTR(PG, true, 3) NVC_V2_ATTR(PG, true, 4) \
-                       NVC_V2_ATTR(PG, false, 0) NVC_V2_ATTR(PG, false, 2) NVC_V2_ATTR(PG, false, 3) NVC_V2_ATTR(PG, false, 4)
-  NVC_V2_ALL(false) NVC_V2_ALL(true)
-#undef NVC_V2_ALL
-#undef NVC_V2_ATTR
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(v2::prefill_attn_v2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, v2::kSmemBytes));
   NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(prefill_attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
   return NVC_OK;
@@ -390,8 +370,8 @@ extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq,
   rc = make_tma_heads(ctx, &tv, v, kv, total_tokens, ldv, v1 ? 128 : v2::kKT);
   if (rc) return rc;
   if (!v1) {
-    dim3 grid2((max_seqlen + 127) / 128, nh, B);
-    NVC_CUDA_CHECK(ctx, launch_v2<false>(ctx, grid2, nvc_stream(stream), tq, tk, tv, cu_seqlens, nh, nh / kv,
+    const int QT = (max_seqlen + 127) / 128;
+    NVC_CUDA_CHECK(ctx, launch_v2<false>(ctx, QT, nh, B, nvc_stream(stream), tq, tk, tv, cu_seqlens, QT, B, nh, nh / kv,
                                          scale * 1.4426950408889634f, out, PagedKV{}));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
     ctx->launches++;
@@ -440,7 +420,8 @@ extern "C" int nvc_prefill_attn_paged(nvc_ctx* ctx, const nvc_bf16* q, int ldq, 
   PagedKV pk{block_tables, context_lens, bt_stride, block_size, box_rows};
   dim3 grid((max_seqlen_q + 127) / 128, nh, B);
   if (!v1) {
-    NVC_CUDA_CHECK(ctx, launch_v2<true>(ctx, grid, nvc_stream(stream), tq, tk, tv, cu_seqlens_q, nh, nh / kv,
+    const int QT = (max_seqlen_q + 127) / 128;
+    NVC_CUDA_CHECK(ctx, launch_v2<true>(ctx, QT, nh, B, nvc_stream(stream), tq, tk, tv, cu_seqlens_q, QT, B, nh, nh / kv,
                                         scale * 1.4426950408889634f, out, pk));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
     ctx->launches++;

@@ -34,9 +34,10 @@ constexpr int kOffV = kOffK + kKStages * kKBytes;
 constexpr int kOffBar = kOffV + kVStages * kKBytes;     // 114688
 // q_full, q_empty, k_full[3], k_empty[3], v_full[2], v_empty[2], s_full[2], p_full, o_full, o_free
 constexpr int kNumBars = 2 + 2 * kKStages + 2 * kVStages + 2 + 3;
-// two CTAs per SM: 2 x (request + 1 KB reserved) <= 228 KB; the alignment pad is <= 896 B for a 128-byte aligned base
+// two CTAs per SM: 2 x (request + 1 KB reserved) <= 228 KB; the dynamic shared memory is requested 1024-byte aligned
+// (no static shared memory in this kernel: the pad is 0 in practice), a pad of up to 768 B fits, beyond that the kernel traps
 constexpr int kSmemBytes = 115712;
-static_assert(kOffBar + kNumBars * 8 + 16 + 896 <= kSmemBytes, "shared memory budget for two CTAs per SM");
+static_assert(kOffBar + kNumBars * 8 + 16 + 768 <= kSmemBytes, "shared memory budget for two CTAs per SM");
 constexpr int kTmemCols = 256;                 // S / P (double-buffered): columns [0, 64) and [64, 128); O: [128, 256)
 constexpr float kRescaleLog2 = 8.0f;           // rescale O only when a row's maximum grew by more than 2^8
 
@@ -63,6 +64,7 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
   extern __shared__ __align__(1024) uint8_t smem_v2[];
   const uint32_t base = (smem_u32(smem_v2) + 1023u) & ~1023u;   // no-op when the alignment is honoured; pad <= 896 otherwise
   uint8_t* gen = smem_v2 + (base - smem_u32(smem_v2));
+  if ((base - smem_u32(smem_v2)) + kOffBar + kNumBars * 8 + 16 > (uint32_t)kSmemBytes) __trap();   // alignment not honoured
   const uint32_t bar0 = base + kOffBar;
   const uint32_t q_full = bar0, q_empty = bar0 + 8u;
   // K and V have their own rings: a K slot is free as soon as S = Q K^T has read it (one tile ahead of the
@@ -236,3 +238,140 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       ++n_done;
     }
   } else {
+    // ------------------------------------------------------------ softmax / correction / output warps
+    const int quad = warp & 3;
+    const int r = quad * 32 + lane;                 // row in the q tile
+    const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
+    uint32_t g = 0;
+    for (int it = blockIdx.x; it < num_items; it += gridDim.x) {
+      const Item x = item_of(it, QT, nh, B);
+      const Geo ge = geo_of(x);
+      if (ge.n_tiles == 0) continue;
+      const int n = ge.n_tiles;
+      float m = -INFINITY, l = 0.f;                 // m: the maximum the exponentials are taken against (may lag the true one)
+      for (int j = 0; j < n; ++j) {
+        const uint32_t gi = g + j;
+        const uint32_t s_addr = tmem_s + (gi & 1) * kKT + lane_addr;
+        ptx::mbar_wait(s_full(gi & 1), (gi >> 1) & 1);
+        ptx::tcgen05_fence_after();
+        uint32_t sv[kKT];
+        ptx::tmem_ld_32x32b_x32(s_addr, sv);
+        ptx::tmem_ld_32x32b_x32(s_addr + 32, sv + 32);
+        ptx::tmem_ld_wait();
+        // diagonal tiles only (the tile holds keys past some row's position): columns past this row's position
+        // become -inf, i.e. p = exp2(-inf) = 0; every other tile takes the mask-free path below
+        if (j * kKT + kKT - 1 > ge.q0) {
+          const int lim = ge.q0 + r - j * kKT;            // last visible column of this row
+#pragma unroll
+          for (int i = 0; i < kKT; ++i)
+            if (i > lim) sv[i] = 0xff800000u;
+        }
+        // row maximum over four independent chains
+        float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
+#pragma unroll
+        for (int i = 0; i < kKT; i += 4) {
+          mx0 = fmaxf(mx0, __uint_as_float(sv[i]));
+          mx1 = fmaxf(mx1, __uint_as_float(sv[i + 1]));
+          mx2 = fmaxf(mx2, __uint_as_float(sv[i + 2]));
+          mx3 = fmaxf(mx3, __uint_as_float(sv[i + 3]));
+        }
+        const float mt = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3)) * scale_log2e;   // finite on tile 0: key 0 is visible to every row
+        // lazy rescale: move the reference maximum (and pay the O round trip) only when some row of this warp outgrew it
+        // by more than 2^kRescaleLog2; m = -inf on the first tile, so that one always moves
+        const bool move = __any_sync(0xffffffffu, mt > m + kRescaleLog2);
+        float alpha = 1.0f;
+        if (move) {
+          const float m_new = fmaxf(m, mt);
+          alpha = fast_exp2(m - m_new);
+          m = m_new;
+        }
+        // exponentials: 64 independent FFMA, then 64 independent MUFU, in place
+#pragma unroll
+        for (int i = 0; i < kKT; ++i) sv[i] = __float_as_uint(fmaf(__uint_as_float(sv[i]), scale_log2e, -m));
+#pragma unroll
+        for (int i = 0; i < kKT; ++i) sv[i] = __float_as_uint(fast_exp2(__uint_as_float(sv[i])));
+        float ps0 = 0.f, ps1 = 0.f, ps2 = 0.f, ps3 = 0.f;
+        uint32_t pk2[kKT / 2];
+#pragma unroll
+        for (int i = 0; i < kKT; i += 4) {
+          const float p0 = __uint_as_float(sv[i]), p1 = __uint_as_float(sv[i + 1]);
+          const float p2 = __uint_as_float(sv[i + 2]), p3 = __uint_as_float(sv[i + 3]);
+          ps0 += p0; ps1 += p1; ps2 += p2; ps3 += p3;
+          pk2[i >> 1] = pack_bf16(p0, p1);
+          pk2[(i >> 1) + 1] = pack_bf16(p2, p3);
+        }
+        l = l * alpha + ((ps0 + ps1) + (ps2 + ps3));
+        if (j > 0 && move) {
+          // P V(j-1) has completed: O holds the sum over tiles < j; O *= alpha (warp-collective; alpha = 1 for rows that
+          // did not move).  Tile j is never ahead of o_full by more than one phase, so skipped waits cannot alias.
+          ptx::mbar_wait(o_full, (gi - 1) & 1);
+          ptx::tcgen05_fence_after();
+#pragma unroll 1
+          for (int c = 0; c < 4; ++c) {
+            uint32_t v[32];
+            ptx::tmem_ld_32x32b_x32(tmem_o + lane_addr + c * 32, v);
+            ptx::tmem_ld_wait();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+            ptx::tmem_st_32x32b_x32(tmem_o + lane_addr + c * 32, v);
+          }
+        }
+        // P -> bf16 pairs over the S columns this thread has just read (its own lane): the A operand of the second MMA
+        ptx::tmem_st_32x32b_x32(s_addr, pk2);
+        ptx::tmem_st_wait();
+        if constexpr (kPaged) {
+          // V rows at / past the end of the context (last tile only): zero them (every P column there is 0,
+          // but the cache bytes may be NaN) once the slot's TMA has landed; the proxy fence orders these
+          // generic stores before the P V MMA.
+          if (j * kKT + kKT > ge.kv_len) {
+            const int vs = (int)(gi % kVStages);
+            ptx::mbar_wait(v_full(vs), (gi / kVStages) & 1);
+            if (r < kKT && j * kKT + r >= ge.kv_len) {
+              uint8_t* v_row = gen + kOffV + vs * kKBytes + r * 128;
+#pragma unroll
+              for (int k16 = 0; k16 < 8; ++k16) {
+                *reinterpret_cast<uint4*>(v_row + (k16 << 4)) = make_uint4(0, 0, 0, 0);
+                *reinterpret_cast<uint4*>(v_row + kHalfKV + (k16 << 4)) = make_uint4(0, 0, 0, 0);
+              }
+            }
+            ptx::fence_proxy_async_smem();
+          }
+        }
+        ptx::tcgen05_fence_before();
+        ptx::mbar_arrive(p_full);
+      }
+      // ---- O / l -> bf16 rows of the output
+      ptx::mbar_wait(o_full, (g + n - 1) & 1);
+      ptx::tcgen05_fence_after();
+      const int row_in_seq = x.qt * 128 + r;
+      const float inv = 1.0f / l;
+      uint4* dst = reinterpret_cast<uint4*>(out + ((int64_t)(ge.seq_start + row_in_seq) * nh + x.h) * 128);
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        ptx::tmem_ld_32x32b_x32(tmem_o + lane_addr + c * 32, v);
+        ptx::tmem_ld_wait();
+        if (row_in_seq < ge.seq_len) {
+#pragma unroll
+          for (int k8 = 0; k8 < 4; ++k8) {
+            float o[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i] = __uint_as_float(v[k8 * 8 + i]) * inv;
+            dst[c * 4 + k8] = pack8(o);
+          }
+        }
+      }
+      ptx::tcgen05_fence_before();
+      ptx::mbar_arrive(o_free);                      // the next item's first P V may overwrite O
+      g += n;
+    }
+  }
+  ptx::tcgen05_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tcgen05_fence_after();
+    ptx::tmem_dealloc(tmem, kTmemCols);
+  }
+}
+
+}  // namespace v2

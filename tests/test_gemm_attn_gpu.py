@@ -291,22 +291,11 @@ def test_prefill_attn_first_generation_kernel_still_matches(ctx, nvc):
         nvc.lib().nvc_debug_set(3, 0)
 
 
-@pytest.mark.parametrize("pt,poly", [(1, -1), (2, -1), (1, 4), (2, 4), (2, 2), (2, 3)])
-def test_prefill_attn_variants(ctx, nvc, pt, poly):
-    """P through shared memory (pt = 1) or through tensor memory as the A operand of the P V MMA (pt = 2), with none /
-    every 4th / 3rd / 2nd exponential on the FMA pipe (degree-3 polynomial, relative error 9e-5), against the same
-    references as the default configuration (nvc_debug_set(4, pt), nvc_debug_set(6, poly))."""
-    nvc.lib().nvc_debug_set(4, pt)
-    nvc.lib().nvc_debug_set(6, poly)
-    try:
-        test_prefill_attn_varlen(ctx, nvc, [17, 128, 129, 300, 1, 512], 4, 2)
-        test_prefill_attn_varlen(ctx, nvc, [2048, 1500], 8, 2)
-        test_prefill_attn_varlen(ctx, nvc, [64, 65, 63, 191, 192, 193], 2, 1)
-        test_prefill_attn_paged(ctx, 16, 8, 256, [(768, 256), (1000, 232), (256, 1), (257, 257), (640, 130)])
-        test_prefill_attn_paged(ctx, 4, 2, 16, [(48, 16), (33, 1), (200, 200), (131, 3), (16, 16)])
-    finally:
-        nvc.lib().nvc_debug_set(4, 0)
-        nvc.lib().nvc_debug_set(6, 0)
+def test_prefill_attn_persistent_many_items(ctx, nvc):
+    """more work items than resident CTAs (2 per SM): every CTA of the persistent grid walks several (q tile, head,
+    sequence) items - ragged lengths, q tiles past the end of short sequences (skipped items), GQA groups."""
+    test_prefill_attn_varlen(ctx, nvc, [513, 1, 700, 128, 129, 64, 1024, 300, 257, 33, 900, 512], 16, 8)
+    test_prefill_attn_varlen(ctx, nvc, [200] * 40, 8, 2)
 
 
 @pytest.mark.parametrize("lens,nh,kv", [([2048, 1500], 8, 2), ([4096], 4, 1), ([64, 65, 63, 191, 192, 193], 2, 1)])

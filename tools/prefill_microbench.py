@@ -27,15 +27,12 @@ def bench(name, B, T, nh, kv, iters=10, bufs=4):
     out = torch.empty(N, nh * hd, dtype=BF16, device="cuda")
     flops = 4.0 * nh * hd * B * T * T / 2
     row = {"shape": name, "B": B, "T": T, "nh": nh, "kv": kv}
-    # (label, first-generation kernel, P through tensor memory 1 = off / 2 = on, every n-th exponential on the FMA pipe)
-    variants = [("v1", 1, 1, -1), ("smem", 0, 1, -1), ("smem_p4", 0, 1, 4), ("tmem", 0, 2, -1), ("tmem_p4", 0, 2, 4),
-                ("tmem_p3", 0, 2, 3), ("tmem_p2", 0, 2, 2)]
+    # (label, first-generation kernel)
+    variants = [("v1", 1), ("v2", 0)]
     if os.environ.get("PREFILL_VARIANTS"):
         variants = [v for v in variants if v[0] in os.environ["PREFILL_VARIANTS"].split(",")]
-    for label, v1, pt, poly in variants:
+    for label, v1 in variants:
         lib.lib().nvc_debug_set(3, v1)
-        lib.lib().nvc_debug_set(4, pt)
-        lib.lib().nvc_debug_set(6, poly)
         def run(d):
             ctx.prefill_attn(d[:, :nh * hd], d[:, nh * hd:(nh + kv) * hd], d[:, (nh + kv) * hd:], cu, T, nh, kv, hd, hd ** -0.5, out=out)
         for d in qkvs:
@@ -52,8 +49,6 @@ def bench(name, B, T, nh, kv, iters=10, bufs=4):
         row[f"{label}_tflops"] = round(flops / us / 1e6, 1)
         row[f"{label}_frac"] = round(flops / us / 1e6 / PEAK, 3)
     lib.lib().nvc_debug_set(3, 0)
-    lib.lib().nvc_debug_set(4, 0)
-    lib.lib().nvc_debug_set(6, 0)
     print(json.dumps(row), flush=True)
     return row
 

@@ -301,10 +301,15 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
           pk2[(i >> 1) + 1] = pack_bf16(p2, p3);
         }
         l = l * alpha + ((ps0 + ps1) + (ps2 + ps3));
-        if (j > 0 && move) {
-          // P V(j-1) has completed: O holds the sum over tiles < j; O *= alpha (warp-collective; alpha = 1 for rows that
-          // did not move).  Tile j is never ahead of o_full by more than one phase, so skipped waits cannot alias.
+        if (j > 0) {
+          // P V(j-1) has completed: O holds the sum over tiles < j.  Waited for on EVERY tile, moved or not: a parity
+          // wait is only meaningful within one phase of the barrier, so the softmax threads must observe each o_full
+          // phase in turn (skipping them let the final wait take an older phase for the last one).  The MMA was issued a
+          // whole softmax pass ago, so the wait falls through.
           ptx::mbar_wait(o_full, (gi - 1) & 1);
+        }
+        if (j > 0 && move) {
+          // O *= alpha (warp-collective; alpha = 1 for rows that did not move)
           ptx::tcgen05_fence_after();
 #pragma unroll 1
           for (int c = 0; c < 4; ++c) {

@@ -322,14 +322,19 @@ int make_tma_heads(nvc_ctx* ctx, CUtensorMap* map, const void* base, int heads, 
   return NVC_OK;
 }
 
+#include "gemm_epilogue.cuh"
 #include "prefill_attn_v2.cuh"
 
 // persistent grid of the second-generation kernel: two CTAs per SM, or one CTA per work item when there are fewer
-template <bool kPaged, typename... Args>
-cudaError_t launch_v2(nvc_ctx* ctx, int QT, int nh, int B, cudaStream_t st, Args... args) {
+template <bool kPaged>
+cudaError_t launch_v2(nvc_ctx* ctx, int QT, int nh, int kv, int B, cudaStream_t st, const CUtensorMap& tq, const CUtensorMap& tk,
+                      const CUtensorMap& tv, const int32_t* cu_seqlens, float scale_log2e, nvc_bf16* out, const PagedKV& pk) {
   const long long items = (long long)QT * nh * B;
+  if (items > 0x7fffffffLL) return cudaErrorInvalidValue;
   const int grid = (int)(items < 2LL * ctx->num_sms ? items : 2LL * ctx->num_sms);
-  return nvc_launch(ctx, v2::prefill_attn_v2_kernel<kPaged>, dim3(grid), dim3(v2::kThreads), v2::kSmemBytes, st, args...);
+  v2::Sched sc{v2::make_fastdiv(nh * B), v2::make_fastdiv(nh), v2::make_fastdiv(nh / kv), QT, (int)items};
+  return nvc_launch(ctx, v2::prefill_attn_v2_kernel<kPaged>, dim3(grid), dim3(v2::kThreads), v2::kSmemBytes, st, tq, tk, tv,
+                    cu_seqlens, sc, scale_log2e, out, pk);
 }
 
 bool use_v1() {
@@ -371,7 +376,7 @@ extern "C" int nvc_prefill_attn_varlen(nvc_ctx* ctx, const nvc_bf16* q, int ldq,
   if (rc) return rc;
   if (!v1) {
     const int QT = (max_seqlen + 127) / 128;
-    NVC_CUDA_CHECK(ctx, launch_v2<false>(ctx, QT, nh, B, nvc_stream(stream), tq, tk, tv, cu_seqlens, QT, B, nh, nh / kv,
+    NVC_CUDA_CHECK(ctx, launch_v2<false>(ctx, QT, nh, kv, B, nvc_stream(stream), tq, tk, tv, cu_seqlens,
                                          scale * 1.4426950408889634f, out, PagedKV{}));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
     ctx->launches++;
@@ -421,7 +426,7 @@ extern "C" int nvc_prefill_attn_paged(nvc_ctx* ctx, const nvc_bf16* q, int ldq, 
   dim3 grid((max_seqlen_q + 127) / 128, nh, B);
   if (!v1) {
     const int QT = (max_seqlen_q + 127) / 128;
-    NVC_CUDA_CHECK(ctx, launch_v2<true>(ctx, QT, nh, B, nvc_stream(stream), tq, tk, tv, cu_seqlens_q, QT, B, nh, nh / kv,
+    NVC_CUDA_CHECK(ctx, launch_v2<true>(ctx, QT, nh, kv, B, nvc_stream(stream), tq, tk, tv, cu_seqlens_q,
                                         scale * 1.4426950408889634f, out, pk));
     NVC_CUDA_CHECK(ctx, cudaGetLastError());
     ctx->launches++;

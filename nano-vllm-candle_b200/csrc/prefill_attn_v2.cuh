@@ -4,7 +4,10 @@
 //     (the last q tile of a causal sequence has the most kv tiles), keeping its barriers and tensor memory; the
 //     producer warp requests the next item's Q / K while the softmax warps still drain the current one, so the
 //     ~6 us of per-CTA start-up that a one-item grid pays per ~5 tiles at T = 512 is paid once per CTA;
-//   * kv tiles of 64 tokens: Q 32 KB + K ring 3 x 16 KB + V ring 2 x 16 KB = 112 KB of shared memory;
+//   * kv tiles of 64 tokens: Q 32 KB + K ring 2 x 16 KB + V ring 2 x 16 KB + 16 KB of output staging = 112 KB;
+//   * the output rows leave through a per-warp staging buffer (RowStage, gemm_epilogue.cuh): one thread owns one row, so
+//     direct 16-byte stores touched 32 lines per instruction and the LSU throttled the epilogue (14 % of the stall
+//     samples at T = 512); staged, every store instruction covers 4 rows x 128 contiguous bytes;
 //   * S is double-buffered in tensor memory; P goes BACK into tensor memory (bf16 pairs over the first 32 columns
 //     of the S buffer it came from) and is the A operand of the P V MMA from there: no shared-memory round trip,
 //     no proxy fence per tile (measured +8 % on every shape, profiles/r02_prefill_attn_variants_tmem_poly.json);
@@ -27,12 +30,13 @@ constexpr int kKT = 64;                        // kv tokens per tile
 constexpr int kQBytes = 128 * 128 * 2;         // 32 KB: two [128 rows][64 dims] swizzled halves
 constexpr int kHalfKV = kKT * 128;             // 8 KB: [64 tokens][64 dims]
 constexpr int kKBytes = 2 * kHalfKV;           // 16 KB: one K or V tile
-constexpr int kKStages = 3, kVStages = 2;
+constexpr int kKStages = 2, kVStages = 2;
 constexpr int kOffQ = 0;
 constexpr int kOffK = kQBytes;
 constexpr int kOffV = kOffK + kKStages * kKBytes;
-constexpr int kOffBar = kOffV + kVStages * kKBytes;     // 114688
-// q_full, q_empty, k_full[3], k_empty[3], v_full[2], v_empty[2], s_full[2], p_full, o_full, o_free
+constexpr int kOffStage = kOffV + kVStages * kKBytes;   // 4 softmax warps x 4 KB row staging for the output
+constexpr int kOffBar = kOffStage + 4 * 4096;           // 114688
+// q_full, q_empty, k_full[2], k_empty[2], v_full[2], v_empty[2], s_full[2], p_full, o_full, o_free
 constexpr int kNumBars = 2 + 2 * kKStages + 2 * kVStages + 2 + 3;
 // two CTAs per SM: 2 x (request + 1 KB reserved) <= 228 KB; the dynamic shared memory is requested 1024-byte aligned
 // (no static shared memory in this kernel: the pad is 0 in practice), a pad of up to 768 B fits, beyond that the kernel traps
@@ -43,24 +47,41 @@ constexpr float kRescaleLog2 = 8.0f;           // rescale O only when a row's ma
 
 // work item -> (q tile, head, sequence): q tiles in DESCENDING order (longest first), heads fastest (the heads of a GQA
 // group run side by side and share their K / V tiles through L2)
-struct Item { int qt, h, b; };
-__device__ __forceinline__ Item item_of(int it, int QT, int nh, int B) {
-  const int per = nh * B;
-  const int q = it / per, rem = it - q * per;
+// n / d for n < 2^32 by a host-made multiplier: floor(n * ceil(2^(32+s) / d) / 2^(32+s)), s = ceil(log2 d) (exact: Granlund -
+// Montgomery); the runtime divisions of the item decomposition were 12 % of the stall samples at T = 512
+struct FastDiv {
+  unsigned long long mul;
+  int shift, d;
+  __device__ __forceinline__ int div(int n) const { return (int)(((unsigned long long)(unsigned)n * mul) >> shift); }
+};
+inline FastDiv make_fastdiv(int d) {
+  FastDiv f;
+  int s = 0;
+  while ((1ll << s) < d) ++s;
+  f.shift = 32 + s;
+  f.mul = ((1ull << f.shift) + (unsigned long long)d - 1) / (unsigned long long)d;
+  f.d = d;
+  return f;
+}
+struct Sched { FastDiv per, nh, group; int QT, num_items; };   // per = nh * B
+struct Item { int qt, h, b, kvh; };
+__device__ __forceinline__ Item item_of(int it, const Sched& sc) {
+  const int q = sc.per.div(it), rem = it - q * sc.per.d;
   Item x;
-  x.qt = QT - 1 - q;
-  x.b = rem / nh;
-  x.h = rem - x.b * nh;
+  x.qt = sc.QT - 1 - q;
+  x.b = sc.nh.div(rem);
+  x.h = rem - x.b * sc.nh.d;
+  x.kvh = sc.group.div(x.h);
   return x;
 }
 
 template <bool kPaged>
 __global__ void __launch_bounds__(192, 2)
 prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_constant__ CUtensorMap tma_k,
-                       const __grid_constant__ CUtensorMap tma_v, const int32_t* __restrict__ cu_seqlens, int QT, int B,
-                       int nh, int group, float scale_log2e, nvc_bf16* __restrict__ out, const PagedKV pk) {
+                       const __grid_constant__ CUtensorMap tma_v, const int32_t* __restrict__ cu_seqlens, const Sched sc,
+                       float scale_log2e, nvc_bf16* __restrict__ out, const PagedKV pk) {
   pdl_trigger();
-  const int num_items = QT * nh * B;
+  const int num_items = sc.num_items, nh = sc.nh.d;
   extern __shared__ __align__(1024) uint8_t smem_v2[];
   const uint32_t base = (smem_u32(smem_v2) + 1023u) & ~1023u;   // no-op when the alignment is honoured; pad <= 896 otherwise
   uint8_t* gen = smem_v2 + (base - smem_u32(smem_v2));
@@ -131,7 +152,7 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
         const uint32_t dst = base + (is_v ? kOffV : kOffK) + s * kKBytes;
         const uint32_t bar = is_v ? v_full(s) : k_full(s);
         const CUtensorMap* map = is_v ? &tma_v : &tma_k;
-        const int kvh = x.h / group;
+        const int kvh = x.kvh;
         if constexpr (kPaged) {
           // boxes of box_rows tokens; only those that start inside the context are loaded (the rest of
           // the slot keeps stale bytes: masked in S, zeroed in V by the softmax warps)
@@ -156,9 +177,15 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       __syncwarp();
     };
     uint32_t g = 0, n_done = 0;
+    Item xn = item_of(blockIdx.x, sc);               // gridDim.x <= num_items
+    Geo gn = geo_of(xn);
     for (int it = blockIdx.x; it < num_items; it += gridDim.x) {
-      const Item x = item_of(it, QT, nh, B);
-      const Geo ge = geo_of(x);
+      const Item x = xn;
+      const Geo ge = gn;
+      if (it + (int)gridDim.x < num_items) {          // the next item's geometry: its loads fly under this item
+        xn = item_of(it + gridDim.x, sc);
+        gn = geo_of(xn);
+      }
       if (ge.n_tiles == 0) continue;
       // Q: the previous item's last S MMA has read it (first item: the barrier is fresh, the wait falls through)
       ptx::mbar_wait(q_empty, (n_done & 1) ^ 1u);
@@ -204,9 +231,15 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       __syncwarp();
     };
     uint32_t g = 0, n_done = 0;
+    Item xn = item_of(blockIdx.x, sc);               // gridDim.x <= num_items
+    Geo gn = geo_of(xn);
     for (int it = blockIdx.x; it < num_items; it += gridDim.x) {
-      const Item x = item_of(it, QT, nh, B);
-      const Geo ge = geo_of(x);
+      const Item x = xn;
+      const Geo ge = gn;
+      if (it + (int)gridDim.x < num_items) {          // the next item's geometry: its loads fly under this item
+        xn = item_of(it + gridDim.x, sc);
+        gn = geo_of(xn);
+      }
       if (ge.n_tiles == 0) continue;
       const int n = ge.n_tiles;
       ptx::mbar_wait(q_full, n_done & 1);
@@ -243,9 +276,15 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
     const int r = quad * 32 + lane;                 // row in the q tile
     const uint32_t lane_addr = (uint32_t)(quad * 32) << 16;
     uint32_t g = 0;
+    Item xn = item_of(blockIdx.x, sc);               // gridDim.x <= num_items
+    Geo gn = geo_of(xn);
     for (int it = blockIdx.x; it < num_items; it += gridDim.x) {
-      const Item x = item_of(it, QT, nh, B);
-      const Geo ge = geo_of(x);
+      const Item x = xn;
+      const Geo ge = gn;
+      if (it + (int)gridDim.x < num_items) {          // the next item's geometry: its loads fly under this item
+        xn = item_of(it + gridDim.x, sc);
+        gn = geo_of(xn);
+      }
       if (ge.n_tiles == 0) continue;
       const int n = ge.n_tiles;
       float m = -INFINITY, l = 0.f;                 // m: the maximum the exponentials are taken against (may lag the true one)
@@ -348,24 +387,21 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
       // ---- O / l -> bf16 rows of the output
       ptx::mbar_wait(o_full, (g + n - 1) & 1);
       ptx::tcgen05_fence_after();
-      const int row_in_seq = x.qt * 128 + r;
       const float inv = 1.0f / l;
-      uint4* dst = reinterpret_cast<uint4*>(out + ((int64_t)(ge.seq_start + row_in_seq) * nh + x.h) * 128);
+      // this warp's 32 rows x 128 head dims leave through its staging buffer: 8 lanes per row, 128 contiguous bytes each
+      RowStage st = make_row_stage(gen + kOffStage + quad * 4096, out, 0, NVC_EPI_NONE, (int64_t)nh * 128,
+                                   ge.seq_start + x.qt * 128 + quad * 32, ge.seq_start + ge.seq_len, x.h * 128, 128, nh * 128);
 #pragma unroll 1
       for (int c = 0; c < 4; ++c) {
         uint32_t v[32];
         ptx::tmem_ld_32x32b_x32(tmem_o + lane_addr + c * 32, v);
         ptx::tmem_ld_wait();
-        if (row_in_seq < ge.seq_len) {
+        float f[32];
 #pragma unroll
-          for (int k8 = 0; k8 < 4; ++k8) {
-            float o[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) o[i] = __uint_as_float(v[k8 * 8 + i]) * inv;
-            dst[c * 4 + k8] = pack8(o);
-          }
-        }
+        for (int i = 0; i < 32; ++i) f[i] = __uint_as_float(v[i]) * inv;
+        st.emit32(lane, 0, NVC_EPI_NONE, f);
       }
+      st.finish(lane);
       ptx::tcgen05_fence_before();
       ptx::mbar_arrive(o_free);                      // the next item's first P V may overwrite O
       g += n;

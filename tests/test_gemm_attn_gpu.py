@@ -217,15 +217,6 @@ def test_prefill_attn_varlen(ctx, nvc, lens, nh, kv):
         qkv[s:e, :nh * hd].reshape(-1, nh, hd), qkv[s:e, nh * hd:(nh + kv) * hd].reshape(-1, kv, hd),
         qkv[s:e, (nh + kv) * hd:].reshape(-1, kv, hd), nh, kv, scale) for s, e in zip(cu[:-1], cu[1:])])
     d = qkv.cuda()
-    results = {}
-    for variant in (0, 1):
-        nvc.lib().nvc_debug_set(0, variant)
-        out = ctx.prefill_attn(d[:, :nh * hd], d[:, nh * hd:(nh + kv) * hd], d[:, (nh + kv) * hd:],
-                               cu.cuda(), max(lens), nh, kv, hd, scale)
-        torch.cuda.synchronize()
-        results[variant] = (out.float().cpu() - ref).abs().max().item()
-    nvc.lib().nvc_debug_set(0, 0)
-    diag(f"[prefill lens={lens} nh={nh} kv={kv}] max_err variant0={results[0]:.4e} variant1={results[1]:.4e}")
     out = ctx.prefill_attn(d[:, :nh * hd], d[:, nh * hd:(nh + kv) * hd], d[:, (nh + kv) * hd:],
                            cu.cuda(), max(lens), nh, kv, hd, scale)
     # P is rounded to bf16 before P*V and the output is bf16: 2e-2 abs on O(1) values
@@ -277,18 +268,6 @@ def test_prefill_attn_paged(ctx, nh, kv, block_size, cases):
     err = (out.float().cpu() - ref).abs().max().item()
     diag(f"[prefill paged nh={nh} kv={kv} bs={block_size} cases={cases}] max_err={err:.4e}")
     _close(out, ref, 2e-2, 2 ** -6, f"paged prefill nh={nh} kv={kv} bs={block_size} cases={cases}")
-
-
-def test_prefill_attn_first_generation_kernel_still_matches(ctx, nvc):
-    """The 128-token-tile kernel (one CTA per SM) stays selectable (NVC_PREFILL_V1 / nvc_debug_set(3, 1))
-    and is held to the same reference as the default two-CTA-per-SM kernel."""
-    nvc.lib().nvc_debug_set(3, 1)
-    try:
-        test_prefill_attn_varlen(ctx, nvc, [17, 128, 129, 300, 1, 512], 4, 2)
-        test_prefill_attn_paged(ctx, 16, 8, 256, [(768, 256), (1000, 232), (256, 1), (257, 257), (640, 130)])
-        test_prefill_attn_paged(ctx, 4, 2, 16, [(48, 16), (33, 1), (200, 200), (131, 3), (16, 16)])
-    finally:
-        nvc.lib().nvc_debug_set(3, 0)
 
 
 def test_prefill_attn_persistent_many_items(ctx, nvc):

@@ -17,13 +17,14 @@ run() {  # name, timeout, pytest args...
   echo "exit $r" | tee -a gpurun_out/summary.txt
   [ $r -ne 0 ] && rc=1
 }
-groups=${@:-elementwise gemm decode prefill layers e2e loader tp}
+groups=${@:-elementwise gemm decode prefill guard layers e2e loader tp}
 for g in $groups; do
   case $g in
     elementwise) run elementwise 300 tests/test_kernels_gpu.py ;;
     gemm) run gemm 400 tests/test_gemm_attn_gpu.py -k gemm ;;
     decode) run decode 300 tests/test_gemm_attn_gpu.py -k paged_decode ;;
     prefill) run prefill 300 tests/test_gemm_attn_gpu.py -k prefill ;;
+    guard) run guard 300 tests/test_guard_bands_gpu.py ;;
     e2e) run e2e 900 tests/test_e2e_gpu.py ;;
     layers) run layers 300 tests/test_layers_gpu.py ;;
     loader) run loader 300 tests/test_hf_loader.py ;;

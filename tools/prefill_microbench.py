@@ -28,11 +28,10 @@ def bench(name, B, T, nh, kv, iters=10, bufs=4):
     flops = 4.0 * nh * hd * B * T * T / 2
     row = {"shape": name, "B": B, "T": T, "nh": nh, "kv": kv}
     # (label, first-generation kernel)
-    variants = [("v1", 1), ("v2", 0)]
+    variants = [("v2", 0)]
     if os.environ.get("PREFILL_VARIANTS"):
         variants = [v for v in variants if v[0] in os.environ["PREFILL_VARIANTS"].split(",")]
     for label, v1 in variants:
-        lib.lib().nvc_debug_set(3, v1)
         def run(d):
             ctx.prefill_attn(d[:, :nh * hd], d[:, nh * hd:(nh + kv) * hd], d[:, (nh + kv) * hd:], cu, T, nh, kv, hd, hd ** -0.5, out=out)
         for d in qkvs:
@@ -48,7 +47,6 @@ def bench(name, B, T, nh, kv, iters=10, bufs=4):
         row[f"{label}_us"] = round(us, 1)
         row[f"{label}_tflops"] = round(flops / us / 1e6, 1)
         row[f"{label}_frac"] = round(flops / us / 1e6 / PEAK, 3)
-    lib.lib().nvc_debug_set(3, 0)
     print(json.dumps(row), flush=True)
     return row
 

@@ -3,7 +3,39 @@
 #pragma once
 #include "common.cuh"
 
-enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1 };
+// NVC_EPI_LL_PUSH: the output rows (this rank's partial sums of a row-parallel projection) are not written to C but pushed
+// straight into range `rank` of the current low-latency buffer of the NVLS all-reduce with multimem.st - one store per 16
+// bytes reaches every rank - so the transfer starts in the GEMM's epilogue and the all-reduce kernel that follows only
+// waits for the data (nvls_allreduce.cu, mode 4).
+enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1, NVC_EPI_LL_PUSH = 2 };
+
+struct LLPush {
+  uint8_t* mc_ll = nullptr;          // multicast address of LL buffer 0
+  size_t ll_buf_bytes = 0;           // bytes per LL buffer (three rotate by epoch)
+  const uint32_t* state = nullptr;   // [0] = epoch of the last completed LL call (device memory of this rank)
+  uint32_t epoch_mod = 0;
+  int rank = 0;
+};
+
+// words of 0xFFFF / 0xFFFFFFFF are the LL protocol's "not arrived yet": a bf16 NaN with that payload is sent as 0x7FFF
+__device__ __forceinline__ uint32_t ll_scrub(uint32_t w) {
+  if ((w & 0xFFFFu) == 0xFFFFu) w &= ~0x8000u;
+  if ((w >> 16) == 0xFFFFu) w &= ~0x80000000u;
+  return w;
+}
+// 16 accumulator columns [n0, n0 + 16) of row `row` (M rows, N columns in the message) -> two multicast vectors
+__device__ __forceinline__ void ll_push16(const LLPush& push, uint32_t epoch, int M, int N, int row, int n0, const float* f) {
+  const uint32_t nvec = (uint32_t)N >> 3;
+  const size_t T = (size_t)M * nvec;
+  uint8_t* base = push.mc_ll + (size_t)(epoch % 3) * push.ll_buf_bytes + ((size_t)push.rank * T + (size_t)row * nvec + (n0 >> 3)) * 16;
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint4 p = pack8(f + 8 * h);
+    p.x = ll_scrub(p.x); p.y = ll_scrub(p.y); p.z = ll_scrub(p.z); p.w = ll_scrub(p.w);
+    asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(base + 16 * h), "r"(p.x), "r"(p.y),
+                 "r"(p.z), "r"(p.w) : "memory");
+  }
+}
 
 // 16 accumulator columns of one row -> C (bf16 or f32), 16-byte stores
 __device__ __forceinline__ void store16(void* C, int out_f32, int64_t off, const float* f) {

@@ -105,6 +105,39 @@ def main():
                     lines.append(rec)
                     if rank == 0 and not good:
                         print(json.dumps(rec), flush=True)
+    # ---- fused form: row-parallel GEMM whose epilogue pushes its rows into the LL buffers + all-reduce mode 4, against
+    # the unfused sequence (GEMM -> memory -> LL one-shot) on the same operands: bit-identical outputs required
+    if ok_nvls:
+        for (M, H, K) in [(64, 1024, 256), (64, 1024, 384), (1, 1024, 1024), (37, 1024, 2048), (128, 4096, 512), (64, 5120, 640),
+                          (64, 1024, 256), (16, 2048, 192)]:
+            if M * H * 2 * world > ll_bytes or M * H * 2 * (world - 1) > (3 << 20):
+                continue
+            call += 1
+            gen.manual_seed(5000 * call + rank)
+            a_in = (torch.randn((M, K), device=dev, generator=gen) * 0.5).bfloat16()
+            wt = (torch.randn((H, K), device=dev, generator=gen) / K ** 0.5).bfloat16()
+            gen.manual_seed(91 * call)
+            res = torch.randn((M, H), device=dev, generator=gen)
+            wn = (1 + 0.1 * torch.randn((H,), device=dev, generator=gen)).bfloat16()
+            x = ctx.gemm(a_in, wt)
+            r1, r2 = torch.empty_like(res), torch.empty_like(res)
+            torch.cuda.synchronize(); dist.barrier()
+            o1 = ctx.nvls_allreduce_rmsnorm(x, wn, eps, res, r1, mode=1)
+            torch.cuda.synchronize(); dist.barrier()
+            ctx.gemm_ll_push(a_in, wt)
+            o2 = ctx.nvls_allreduce_rmsnorm_pushed(M, H, wn, eps, res, r2, device=dev)
+            torch.cuda.synchronize()
+            good = bool(torch.equal(o1.view(torch.int16), o2.view(torch.int16))) and bool(torch.equal(r1, r2))
+            flag = torch.tensor([int(good)], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            good = bool(flag[0])
+            fails += int(not good)
+            rec = {"what": "parity", "N": M, "H": H, "K": K, "mode": 4, "picked": "gemm_ll_push", "norm": True,
+                   "max_err": float((o1.float() - o2.float()).abs().max()), "res_err": float((r1 - r2).abs().max()), "scale": 1.0,
+                   "ranks_bit_identical": good, "ok": good}
+            lines.append(rec)
+            if rank == 0:
+                print(json.dumps(rec), flush=True)
     # ---- timing
     if not a.no_timing:
         tshapes = [(1, 1024), (64, 1024), (256, 1024), (64, 4096), (256, 4096), (256, 5120), (256, 8192), (1024, 4096), (4096, 4096),
@@ -129,6 +162,21 @@ def main():
                     ctx._ck(L.nvc_p2p_allreduce_rmsnorm(ctx.h, k[0], ops._ptr(res), ops._ptr(res), ops._ptr(w), eps, ops._ptr(out), N, H,
                                                         ops._stream()), "p2p")
                 variants.append(("p2p_oneshot_r01", p2p))
+            if ok_nvls and N <= 128 and msg * world <= ll_bytes and msg * (world - 1) <= (3 << 20):
+                Kg = 2048 // world if H == 1024 else 4096 // world
+                ag = torch.zeros((N, Kg), device=dev, dtype=torch.bfloat16)
+                wg = torch.zeros((H, Kg), device=dev, dtype=torch.bfloat16)
+                xg = torch.empty((N, H), device=dev, dtype=torch.bfloat16)
+
+                def gemm_then_ll():
+                    ctx.gemm(ag, wg, out=xg)
+                    ctx.nvls_allreduce_rmsnorm(xg, w, eps, res, res, out=out, mode=1)
+
+                def gemm_push_ll():
+                    ctx.gemm_ll_push(ag, wg)
+                    ctx.nvls_allreduce_rmsnorm_pushed(N, H, w, eps, res, res, out=out)
+                variants.append((f"gemm_k{Kg}_then_ll_oneshot", gemm_then_ll))
+                variants.append((f"gemm_k{Kg}_ll_push_fused", gemm_push_ll))
             xb = torch.zeros((N, H), device=dev, dtype=torch.bfloat16)
 
             def nccl():

@@ -3,38 +3,67 @@
 #pragma once
 #include "common.cuh"
 
-// NVC_EPI_LL_PUSH: the output rows (this rank's partial sums of a row-parallel projection) are not written to C but pushed
-// straight into range `rank` of the current low-latency buffer of the NVLS all-reduce with multimem.st - one store per 16
-// bytes reaches every rank - so the transfer starts in the GEMM's epilogue and the all-reduce kernel that follows only
-// waits for the data (nvls_allreduce.cu, mode 4).
-enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1, NVC_EPI_LL_PUSH = 2 };
+// NVC_EPI_LL_ALLREDUCE (tensor parallel, decode): the GEMM is a row-parallel projection and its epilogue IS the all-reduce.
+// Every epilogue thread multimem.st's its 16-byte pieces of this rank's partial rows into range `rank` of the current
+// low-latency buffer of the NVLS multicast object (one store reaches every rank), then waits for the same pieces of the
+// other ranks to land in its OWN copy of the buffer (spinning on the data: the buffers are kept filled with a sentinel no
+// partial can contain), sums the tp pieces in rank order (bit-identical on every rank) and stores the bf16 sums to C.
+// The NVLink transfer therefore overlaps the GEMM's own tail and no separate all-reduce kernel runs (a kernel boundary
+// would wait for the remote stores to drain: pushing from the epilogue but reducing in a second kernel measured no gain,
+// profiles/r02_nvls_gemm_push_tp2.jsonl).  Protocol state as in nvls_allreduce.cu (same buffers, same epochs).
+enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1, NVC_EPI_LL_ALLREDUCE = 2 };
 
-struct LLPush {
+struct LLReduce {
   uint8_t* mc_ll = nullptr;          // multicast address of LL buffer 0
+  uint8_t* uc_ll = nullptr;          // this rank's copy of LL buffer 0
   size_t ll_buf_bytes = 0;           // bytes per LL buffer (three rotate by epoch)
-  const uint32_t* state = nullptr;   // [0] = epoch of the last completed LL call (device memory of this rank)
+  uint32_t* state = nullptr;         // [0] epoch of the last completed LL call, [1] CTAs finished, [2..4] vectors in use per buffer
   uint32_t epoch_mod = 0;
-  int rank = 0;
+  int rank = 0, tp = 1;
 };
 
+constexpr uint32_t kLLSentinel = 0xFFFFFFFFu;
+constexpr unsigned kLLSpinLimit = 1u << 24;
 // words of 0xFFFF / 0xFFFFFFFF are the LL protocol's "not arrived yet": a bf16 NaN with that payload is sent as 0x7FFF
 __device__ __forceinline__ uint32_t ll_scrub(uint32_t w) {
   if ((w & 0xFFFFu) == 0xFFFFu) w &= ~0x8000u;
   if ((w >> 16) == 0xFFFFu) w &= ~0x80000000u;
   return w;
 }
-// 16 accumulator columns [n0, n0 + 16) of row `row` (M rows, N columns in the message) -> two multicast vectors
-__device__ __forceinline__ void ll_push16(const LLPush& push, uint32_t epoch, int M, int N, int row, int n0, const float* f) {
-  const uint32_t nvec = (uint32_t)N >> 3;
-  const size_t T = (size_t)M * nvec;
-  uint8_t* base = push.mc_ll + (size_t)(epoch % 3) * push.ll_buf_bytes + ((size_t)push.rank * T + (size_t)row * nvec + (n0 >> 3)) * 16;
+__device__ __forceinline__ uint4 ll_ld_volatile(const void* p) {     // written by peers through NVLink: never from L1
+  uint4 r;
+  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+  return r;
+}
+// vector index of 8 columns [n0, n0 + 8) of row `row` inside one rank's [M, N] message
+__device__ __forceinline__ size_t ll_vec(int N, int row, int n0) { return (size_t)row * ((uint32_t)N >> 3) + (n0 >> 3); }
+// push 8 columns (16 bytes) of this rank's partial row to every rank
+__device__ __forceinline__ void ll_push8(const LLReduce& ll, uint32_t epoch, size_t T, size_t vec, const float* f) {
+  uint4 p = pack8(f);
+  p.x = ll_scrub(p.x); p.y = ll_scrub(p.y); p.z = ll_scrub(p.z); p.w = ll_scrub(p.w);
+  uint8_t* dst = ll.mc_ll + (size_t)(epoch % 3) * ll.ll_buf_bytes + ((size_t)ll.rank * T + vec) * 16;
+  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(p.x), "r"(p.y), "r"(p.z),
+               "r"(p.w) : "memory");
+}
+// wait for the tp pieces of one vector and sum them in rank order (fp32); false: timed out
+__device__ __forceinline__ bool ll_wait_sum8(const LLReduce& ll, uint32_t epoch, size_t T, size_t vec, float* s) {
+  const uint8_t* cur = ll.uc_ll + (size_t)(epoch % 3) * ll.ll_buf_bytes + vec * 16;
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    uint4 p = pack8(f + 8 * h);
-    p.x = ll_scrub(p.x); p.y = ll_scrub(p.y); p.z = ll_scrub(p.z); p.w = ll_scrub(p.w);
-    asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(base + 16 * h), "r"(p.x), "r"(p.y),
-                 "r"(p.z), "r"(p.w) : "memory");
+  for (int k = 0; k < 8; ++k) s[k] = 0.f;
+  for (int p = 0; p < ll.tp; ++p) {
+    const void* src = cur + (size_t)p * T * 16;
+    uint4 v = ll_ld_volatile(src);
+    unsigned spins = 0;
+    while (v.x == kLLSentinel || v.y == kLLSentinel || v.z == kLLSentinel || v.w == kLLSentinel) {
+      v = ll_ld_volatile(src);
+      if (++spins > kLLSpinLimit) return false;
+    }
+    float f[8];
+    unpack8(v, f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[k] += f[k];
   }
+  return true;
 }
 
 // 16 accumulator columns of one row -> C (bf16 or f32), 16-byte stores

@@ -132,9 +132,7 @@ __device__ __forceinline__ void row_epilogue(float (&s)[8], const Epilogue& ep, 
 }
 
 // LL one-shot.  grid = N rows, block = H / 8 threads rounded up to a warp.  x = this rank's partial [N, H] bf16.
-// kPushed: the producer GEMM's epilogue has already multimem.st'ed this rank's rows into range my_rank of the current
-// buffer (NVC_EPI_LL_PUSH, gemm_epilogue.cuh): no load of x, no store here - the call only waits for the tp ranges.
-template <int TP, bool kPushed>
+template <int TP>
 __global__ void __launch_bounds__(1024)
 nvls_ll_allreduce_rmsnorm_kernel(const uint4* __restrict__ x, uint8_t* __restrict__ uc_ll, uint8_t* __restrict__ mc_ll,
                                  size_t ll_buf_bytes, uint32_t* __restrict__ state, int my_rank, Epilogue ep, int H) {
@@ -147,7 +145,7 @@ nvls_ll_allreduce_rmsnorm_kernel(const uint4* __restrict__ x, uint8_t* __restric
   const int row = blockIdx.x, v = threadIdx.x;
   const uint32_t i = (uint32_t)row * nvec + v;
   uint4 p = make_uint4(0u, 0u, 0u, 0u);
-  if (!kPushed && v < nvec) p = x[i];          // in flight while thread 0 fetches the epoch
+  if (v < nvec) p = x[i];                      // in flight while thread 0 fetches the epoch
   if (threadIdx.x == 0) {                      // one L2 round trip; the epoch is published at the END of a call
     const volatile uint32_t* vs = state;
     const uint32_t e = (vs[0] + 1) % kEpochMod;
@@ -158,7 +156,7 @@ nvls_ll_allreduce_rmsnorm_kernel(const uint4* __restrict__ x, uint8_t* __restric
   const uint32_t e = s_epoch;
   uint8_t* mine_mc = mc_ll + (size_t)(e % 3) * ll_buf_bytes;
   const uint8_t* cur = uc_ll + (size_t)(e % 3) * ll_buf_bytes;
-  if (!kPushed && v < nvec) {                  // push: one store, tp destinations
+  if (v < nvec) {                              // push: one store, tp destinations
     p.x = scrub(p.x); p.y = scrub(p.y); p.z = scrub(p.z); p.w = scrub(p.w);
     mm_st_u4(mine_mc + ((size_t)my_rank * T + i) * 16, p);
   }
@@ -789,29 +787,32 @@ extern "C" int nvc_ctx_nvls_init(nvc_ctx* ctx, size_t slot_bytes, size_t ll_buf_
 }
 
 // mode 0 = choose by size, 1 = LL one-shot, 2 = two-shot (flag barriers), 3 = two-shot with LL broadcast
-// what a producer GEMM needs to push its rows into the LL buffers (nvc_gemm_bf16_ll_push); fails unless the automatic
-// choice for an [N, H] bf16 message is the LL one-shot kernel
-extern "C" int nvc_nvls_ll_push_info(nvc_ctx* ctx, int N, int H, uint8_t** mc_ll, size_t* ll_buf_bytes, const uint32_t** state,
-                                     uint32_t* epoch_mod, int* rank) {
+// what a GEMM with the all-reduce epilogue needs (nvc_gemm_bf16_allreduce, gemm_epilogue.cuh); fails unless the automatic
+// choice for an [N, H] bf16 message is the LL one-shot protocol
+extern "C" int nvc_nvls_ll_info(nvc_ctx* ctx, int N, int H, uint8_t** mc_ll, uint8_t** uc_ll, size_t* ll_buf_bytes, uint32_t** state,
+                                uint32_t* epoch_mod, int* rank, int* tp_out) {
   NVC_REQUIRE(ctx, ctx && ctx->nvls_ready && ctx->nvls, NVC_ESTATE, "NVLS buffers not set up (nvc_ctx_nvls_init)");
   nvc_nvls* n = ctx->nvls;
   const int tp = ctx->tp_size;
   const size_t msg = (size_t)N * H * 2;
+  NVC_REQUIRE(ctx, tp == 2 || tp == 4 || tp == 8, NVC_ESHAPE, "NVLS all-reduce supports tp_size 2, 4, 8");
   NVC_REQUIRE(ctx, N > 0 && H > 0 && H % 64 == 0 && H / 8 <= 1024, NVC_ESHAPE, "H must be a multiple of 64 and <= 8192");
   NVC_REQUIRE(ctx, msg * tp <= n->ll_buf_bytes && msg * (tp - 1) <= ((size_t)3 << 20), NVC_ESHAPE,
               "message too large for the LL one-shot all-reduce");
   *mc_ll = reinterpret_cast<uint8_t*>(n->mc_va) + kNvlsFlagBytes + n->slot_bytes;
+  *uc_ll = reinterpret_cast<uint8_t*>(n->uc_va) + kNvlsFlagBytes + n->slot_bytes;
   *ll_buf_bytes = n->ll_buf_bytes;
   *state = n->state;
   *epoch_mod = kEpochMod;
   *rank = ctx->tp_rank;
+  *tp_out = tp;
   return NVC_OK;
 }
 
 extern "C" int nvc_nvls_allreduce_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x_partial, const float* residual_in,
                                           float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out, int N, int H,
                                           int mode, void* stream) {
-  NVC_REQUIRE(ctx, ctx && out && (x_partial || mode == 4), NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, ctx && out && x_partial, NVC_EINVAL, "null pointer");
   NVC_REQUIRE(ctx, ctx->nvls_ready, NVC_ESTATE, "NVLS buffers not set up (nvc_ctx_nvls_init)");
   NVC_REQUIRE(ctx, N > 0 && H > 0 && H % 64 == 0 && H / 8 <= 1024, NVC_ESHAPE, "H must be a multiple of 64 and <= 8192");
   nvc_nvls* n = ctx->nvls;
@@ -835,30 +836,21 @@ extern "C" int nvc_nvls_allreduce_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x_partia
   cudaStream_t st = nvc_stream(stream);
   Epilogue ep{reinterpret_cast<const float4*>(residual_in), reinterpret_cast<float4*>(residual_out),
               reinterpret_cast<const uint4*>(w), eps, reinterpret_cast<uint4*>(out)};
-  if (mode == 1 || mode == 4) {     // 4: the rows were pushed by nvc_gemm_bf16_ll_push
+  if (mode == 1) {
     NVC_REQUIRE(ctx, msg * tp <= n->ll_buf_bytes, NVC_ENOMEM, "message larger than the LL buffer");
-#define NVC_LL(TPV, PUSHED)                                                                                            \
-  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, nvls_ll_allreduce_rmsnorm_kernel<TPV, PUSHED>, dim3(N), dim3(threads), 0, st,     \
+#define NVC_LL(TPV)                                                                                                    \
+  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, nvls_ll_allreduce_rmsnorm_kernel<TPV>, dim3(N), dim3(threads), 0, st,             \
                                  reinterpret_cast<const uint4*>(x_partial), uc_ll, mc_ll, n->ll_buf_bytes, n->state,   \
                                  ctx->tp_rank, ep, H))
-    if (mode == 4) {
-      switch (tp) {
-        case 2: NVC_LL(2, true); break;
-        case 4: NVC_LL(4, true); break;
-        case 8: NVC_LL(8, true); break;
-        default: NVC_REQUIRE(ctx, false, NVC_ESHAPE, "NVLS all-reduce supports tp_size 2, 4, 8");
-      }
-    } else {
-      switch (tp) {
-        case 2: NVC_LL(2, false); break;
-        case 4: NVC_LL(4, false); break;
-        case 8: NVC_LL(8, false); break;
-        default: NVC_REQUIRE(ctx, false, NVC_ESHAPE, "NVLS all-reduce supports tp_size 2, 4, 8");
-      }
+    switch (tp) {
+      case 2: NVC_LL(2); break;
+      case 4: NVC_LL(4); break;
+      case 8: NVC_LL(8); break;
+      default: NVC_REQUIRE(ctx, false, NVC_ESHAPE, "NVLS all-reduce supports tp_size 2, 4, 8");
     }
 #undef NVC_LL
   } else {
-    NVC_REQUIRE(ctx, mode == 2 || mode == 3, NVC_EINVAL, "mode must be 0..4");
+    NVC_REQUIRE(ctx, mode == 2 || mode == 3, NVC_EINVAL, "mode must be 0..3");
     NVC_REQUIRE(ctx, reinterpret_cast<const uint8_t*>(x_partial) == uc_slot, NVC_EINVAL,
                 "the two-shot kernel reduces in the switch: the partial sums must be in nvc_ctx_nvls_slot()");
     NVC_REQUIRE(ctx, msg <= n->slot_bytes, NVC_ENOMEM, "message larger than the NVLS slot");

@@ -123,19 +123,16 @@ class Context:
                                                    float(eps), _ptr(out), N, H, mode, _stream()), "nvc_nvls_allreduce_rmsnorm")
         return out
 
-    def gemm_ll_push(self, a: torch.Tensor, w: torch.Tensor):
-        """row-parallel a @ w.T whose epilogue pushes the partial rows into every rank's NVLS LL buffer; follow with
-        nvls_allreduce_rmsnorm_pushed over the same [M, N]."""
+    def gemm_allreduce(self, a: torch.Tensor, w: torch.Tensor, out=None):
+        """sum over ranks of a_rank @ w_rank.T in ONE kernel (row-parallel GEMM whose epilogue is the NVLS all-reduce);
+        collective, M <= 128."""
         _req(a, BF16, "a"); _req(w, BF16, "w")
         M, K = a.shape
+        N = w.shape[0]
         assert w.shape[1] == K and w.is_contiguous() and a.stride(1) == 1
-        self._ck(self.l.nvc_gemm_bf16_ll_push(self.h, _ptr(a), a.stride(0), _ptr(w), M, w.shape[0], K, _stream()),
-                 "nvc_gemm_bf16_ll_push")
-
-    def nvls_allreduce_rmsnorm_pushed(self, N, H, w=None, eps=1e-6, residual_in=None, residual_out=None, out=None, device=None):
-        out = torch.empty((N, H), dtype=BF16, device=device) if out is None else out
-        self._ck(self.l.nvc_nvls_allreduce_rmsnorm(self.h, None, _ptr(residual_in), _ptr(residual_out), _ptr(w),
-                                                   float(eps), _ptr(out), N, H, 4, _stream()), "nvc_nvls_allreduce_rmsnorm")
+        out = torch.empty((M, N), dtype=BF16, device=a.device) if out is None else out
+        self._ck(self.l.nvc_gemm_bf16_allreduce(self.h, _ptr(a), a.stride(0), _ptr(w), _ptr(out), out.stride(0), M, N, K,
+                                                _stream()), "nvc_gemm_bf16_allreduce")
         return out
 
     def allreduce(self, buf: torch.Tensor):

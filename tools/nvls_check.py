@@ -105,36 +105,39 @@ def main():
                     lines.append(rec)
                     if rank == 0 and not good:
                         print(json.dumps(rec), flush=True)
-    # ---- fused form: row-parallel GEMM whose epilogue pushes its rows into the LL buffers + all-reduce mode 4, against
-    # the unfused sequence (GEMM -> memory -> LL one-shot) on the same operands: bit-identical outputs required
+    # ---- GEMM + all-reduce in one kernel (nvc_gemm_bf16_allreduce) against the unfused sequence (GEMM -> memory -> LL
+    # one-shot all-reduce without norm) on the same operands: bit-identical when both GEMMs run unsplit (short K), within
+    # bf16 rounding otherwise; bit-identical across ranks always; twice in a row (epoch / refill bookkeeping)
     if ok_nvls:
         for (M, H, K) in [(64, 1024, 256), (64, 1024, 384), (1, 1024, 1024), (37, 1024, 2048), (128, 4096, 512), (64, 5120, 640),
-                          (64, 1024, 256), (16, 2048, 192)]:
+                          (64, 1024, 256), (16, 2048, 192), (100, 1024, 128)]:
             if M * H * 2 * world > ll_bytes or M * H * 2 * (world - 1) > (3 << 20):
                 continue
             call += 1
             gen.manual_seed(5000 * call + rank)
             a_in = (torch.randn((M, K), device=dev, generator=gen) * 0.5).bfloat16()
             wt = (torch.randn((H, K), device=dev, generator=gen) / K ** 0.5).bfloat16()
-            gen.manual_seed(91 * call)
-            res = torch.randn((M, H), device=dev, generator=gen)
-            wn = (1 + 0.1 * torch.randn((H,), device=dev, generator=gen)).bfloat16()
             x = ctx.gemm(a_in, wt)
-            r1, r2 = torch.empty_like(res), torch.empty_like(res)
             torch.cuda.synchronize(); dist.barrier()
-            o1 = ctx.nvls_allreduce_rmsnorm(x, wn, eps, res, r1, mode=1)
+            o1 = ctx.nvls_allreduce_rmsnorm(x, None, eps, None, None, mode=1)
             torch.cuda.synchronize(); dist.barrier()
-            ctx.gemm_ll_push(a_in, wt)
-            o2 = ctx.nvls_allreduce_rmsnorm_pushed(M, H, wn, eps, res, r2, device=dev)
+            o2 = ctx.gemm_allreduce(a_in, wt).clone()
+            o3 = ctx.gemm_allreduce(a_in, wt)
             torch.cuda.synchronize()
-            good = bool(torch.equal(o1.view(torch.int16), o2.view(torch.int16))) and bool(torch.equal(r1, r2))
+            err = float((o1.float() - o2.float()).abs().max())
+            exact = bool(torch.equal(o1.view(torch.int16), o2.view(torch.int16)))
+            outs = [torch.empty_like(o2) for _ in range(world)]
+            dist.all_gather(outs, o2)
+            same = all(torch.equal(o.view(torch.int16), outs[0].view(torch.int16)) for o in outs) and \
+                bool(torch.equal(o2.view(torch.int16), o3.view(torch.int16)))
+            good = same and (exact if K <= 1024 else err <= 2e-2 * max(1.0, float(o1.float().abs().max())))
             flag = torch.tensor([int(good)], device=dev)
             dist.all_reduce(flag, op=dist.ReduceOp.MIN)
             good = bool(flag[0])
             fails += int(not good)
-            rec = {"what": "parity", "N": M, "H": H, "K": K, "mode": 4, "picked": "gemm_ll_push", "norm": True,
-                   "max_err": float((o1.float() - o2.float()).abs().max()), "res_err": float((r1 - r2).abs().max()), "scale": 1.0,
-                   "ranks_bit_identical": good, "ok": good}
+            rec = {"what": "parity", "N": M, "H": H, "K": K, "mode": 5, "picked": "gemm_allreduce_one_kernel", "norm": False,
+                   "max_err": err, "res_err": 0.0, "scale": 1.0, "bit_identical_to_unfused": exact, "ranks_bit_identical": same,
+                   "ok": good}
             lines.append(rec)
             if rank == 0:
                 print(json.dumps(rec), flush=True)
@@ -172,11 +175,11 @@ def main():
                     ctx.gemm(ag, wg, out=xg)
                     ctx.nvls_allreduce_rmsnorm(xg, w, eps, res, res, out=out, mode=1)
 
-                def gemm_push_ll():
-                    ctx.gemm_ll_push(ag, wg)
-                    ctx.nvls_allreduce_rmsnorm_pushed(N, H, w, eps, res, res, out=out)
-                variants.append((f"gemm_k{Kg}_then_ll_oneshot", gemm_then_ll))
-                variants.append((f"gemm_k{Kg}_ll_push_fused", gemm_push_ll))
+                def gemm_ar_then_norm():
+                    ctx.gemm_allreduce(ag, wg, out=xg)
+                    ctx.fused_add_rmsnorm(xg, w, eps, res, res, out=out)
+                variants.append((f"gemm_k{Kg}_then_ll_oneshot_norm", gemm_then_ll))
+                variants.append((f"gemm_k{Kg}_allreduce_one_kernel_then_norm", gemm_ar_then_norm))
             xb = torch.zeros((N, H), device=dev, dtype=torch.bfloat16)
 
             def nccl():

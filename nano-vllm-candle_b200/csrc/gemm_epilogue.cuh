@@ -38,30 +38,67 @@ __device__ __forceinline__ uint4 ll_ld_volatile(const void* p) {     // written 
 // vector index of 8 columns [n0, n0 + 8) of row `row` inside one rank's [M, N] message
 __device__ __forceinline__ size_t ll_vec(int N, int row, int n0) { return (size_t)row * ((uint32_t)N >> 3) + (n0 >> 3); }
 // push 8 columns (16 bytes) of this rank's partial row to every rank
-__device__ __forceinline__ void ll_push8(const LLReduce& ll, uint32_t epoch, size_t T, size_t vec, const float* f) {
+__device__ __forceinline__ uint4 ll_push8(const LLReduce& ll, uint32_t epoch, size_t T, size_t vec, const float* f) {
   uint4 p = pack8(f);
   p.x = ll_scrub(p.x); p.y = ll_scrub(p.y); p.z = ll_scrub(p.z); p.w = ll_scrub(p.w);
   uint8_t* dst = ll.mc_ll + (size_t)(epoch % 3) * ll.ll_buf_bytes + ((size_t)ll.rank * T + vec) * 16;
   asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(p.x), "r"(p.y), "r"(p.z),
                "r"(p.w) : "memory");
+  return p;
 }
-// wait for the tp pieces of one vector and sum them in rank order (fp32); false: timed out
-__device__ __forceinline__ bool ll_wait_sum8(const LLReduce& ll, uint32_t epoch, size_t T, size_t vec, float* s) {
-  const uint8_t* cur = ll.uc_ll + (size_t)(epoch % 3) * ll.ll_buf_bytes + vec * 16;
+// Wait for the tp pieces of V vectors (16 bytes each, V * tp loads in flight at once: one NVLink / L2 latency, not V * tp)
+// and sum them in rank order (fp32).  mine[v] = what this thread pushed for vector v: taken from registers instead of
+// waiting for the multicast store to come back to this rank's own copy.  false: timed out.
+template <int V>
+__device__ __forceinline__ bool ll_wait_sum(const LLReduce& ll, uint32_t epoch, size_t T, const size_t* vec, const uint4* mine,
+                                            int nvalid, float (*s)[8]) {
+  constexpr int kMaxTp = 8;
+  const uint8_t* cur = ll.uc_ll + (size_t)(epoch % 3) * ll.ll_buf_bytes;
+  uint4 part[V][kMaxTp];
+  unsigned pending = 0;                                // bit v * 8 + p: piece not there yet
 #pragma unroll
-  for (int k = 0; k < 8; ++k) s[k] = 0.f;
-  for (int p = 0; p < ll.tp; ++p) {
-    const void* src = cur + (size_t)p * T * 16;
-    uint4 v = ll_ld_volatile(src);
-    unsigned spins = 0;
-    while (v.x == kLLSentinel || v.y == kLLSentinel || v.z == kLLSentinel || v.w == kLLSentinel) {
-      v = ll_ld_volatile(src);
-      if (++spins > kLLSpinLimit) return false;
+  for (int v = 0; v < V; ++v) {
+#pragma unroll
+    for (int p = 0; p < kMaxTp; ++p) {
+      if (v < nvalid && p < ll.tp) {
+        if (p == ll.rank) {
+          part[v][p] = mine[v];
+        } else {
+          part[v][p] = ll_ld_volatile(cur + ((size_t)p * T + vec[v]) * 16);
+          pending |= 1u << (v * kMaxTp + p);
+        }
+      }
     }
-    float f[8];
-    unpack8(v, f);
+  }
+  unsigned spins = 0;
+  while (pending) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) s[k] += f[k];
+    for (int v = 0; v < V; ++v) {
+#pragma unroll
+      for (int p = 0; p < kMaxTp; ++p) {
+        const unsigned bit = 1u << (v * kMaxTp + p);
+        if (pending & bit) {
+          const uint4 x = part[v][p];
+          if (x.x != kLLSentinel && x.y != kLLSentinel && x.z != kLLSentinel && x.w != kLLSentinel) pending &= ~bit;
+          else part[v][p] = ll_ld_volatile(cur + ((size_t)p * T + vec[v]) * 16);
+        }
+      }
+    }
+    if (++spins > kLLSpinLimit) return false;
+  }
+#pragma unroll
+  for (int v = 0; v < V; ++v) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[v][k] = 0.f;
+#pragma unroll
+    for (int p = 0; p < kMaxTp; ++p) {
+      if (v < nvalid && p < ll.tp) {
+        float f[8];
+        unpack8(part[v][p], f);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s[v][k] += f[k];
+      }
+    }
   }
   return true;
 }

@@ -276,19 +276,34 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           const uint4 sent = make_uint4(kLLSentinel, kLLSentinel, kLLSentinel, kLLSentinel);
           for (uint32_t j = (uint32_t)tile_id * kEpilogueThreads + et; j < ll_used; j += n_ctas * kEpilogueThreads) old[j] = sent;
         }
-        // this thread's pieces of every rank (its own included: the multicast store lands in this rank's copy too)
-        if (row_ok) {
+        // this thread's pieces of every rank, 16 columns (two vectors x tp loads in flight) at a time; its own pieces come
+        // back out of tensor memory instead of waiting for the multicast store to return to this rank's copy
 #pragma unroll 1
-          for (int c8 = 0; c8 < BN / 8; ++c8) {
-            const int n0 = n_tile * BN + c8 * 8;
-            if (n0 >= N) break;
-            float sum[8];
-            if (!ll_wait_sum8(ll, ll_epoch, ll_T, ll_vec(N, grow, n0), sum)) {
-              printf("nvc: GEMM + NVLS all-reduce timed out (rank %d, epoch %u, row %d, column %d)\n", ll.rank, ll_epoch, grow, n0);
-              __trap();
-            }
-            *reinterpret_cast<uint4*>(reinterpret_cast<nvc_bf16*>(C) + (int64_t)grow * ldc + n0) = pack8(sum);
+        for (int c = 0; c < BN / 16; ++c) {
+          const int n0 = n_tile * BN + c * 16;
+          uint32_t v[16];
+          ptx::tmem_ld_32x32b_x16(taddr + c * 16, v);      // warp-collective: outside the row / column guards
+          ptx::tmem_ld_wait();
+          if (!row_ok || n0 >= N) continue;
+          float f[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
+          uint4 mine[2] = {pack8(f), pack8(f + 8)};
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            mine[h].x = ll_scrub(mine[h].x); mine[h].y = ll_scrub(mine[h].y);
+            mine[h].z = ll_scrub(mine[h].z); mine[h].w = ll_scrub(mine[h].w);
           }
+          const size_t vec[2] = {ll_vec(N, grow, n0), ll_vec(N, grow, n0 + 8)};
+          const int nvalid = n0 + 8 < N ? 2 : 1;
+          float sum[2][8];
+          if (!ll_wait_sum<2>(ll, ll_epoch, ll_T, vec, mine, nvalid, sum)) {
+            printf("nvc: GEMM + NVLS all-reduce timed out (rank %d, epoch %u, row %d, column %d)\n", ll.rank, ll_epoch, grow, n0);
+            __trap();
+          }
+          nvc_bf16* dst = reinterpret_cast<nvc_bf16*>(C) + (int64_t)grow * ldc + n0;
+          *reinterpret_cast<uint4*>(dst) = pack8(sum[0]);
+          if (nvalid == 2) *reinterpret_cast<uint4*>(dst + 8) = pack8(sum[1]);
         }
         // the LAST CTA TO FINISH publishes the epoch and this call's footprint (as the LL all-reduce kernel does)
         ptx::named_bar_sync(1, kEpilogueThreads);

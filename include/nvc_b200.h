@@ -127,14 +127,7 @@ int nvc_p2p_allreduce_rmsnorm(nvc_ctx* ctx, int slot, const float* residual_in, 
  *     tp * N * H * 2 <= ll_buf_bytes); 2 = two-shot in the switch (multimem.ld_reduce of 1/tp of the slot,
  *     multimem.st of the sums in place, two flag barriers; x_partial must be nvc_ctx_nvls_slot); 3 = two-shot with
  *     the sums broadcast into an LL buffer (one barrier; N * H * 2 <= ll_buf_bytes).  Results are bit-identical on
- *     all ranks in every mode.  tp_size in {2, 4, 8}; H % 64 == 0, H <= 8192.
- *   nvc_gemm_bf16_allreduce: the fused form for decode (M <= 128): RowParallelLinear::forward
- *     (src/layers/linear.rs:184-198) and the all-reduce north_star (4) adds after it as ONE kernel.  The GEMM's epilogue
- *     multimem.st's this rank's partial rows into every rank's LL buffer, waits for the other ranks' rows to land in
- *     its own copy, sums the tp partials in rank order and stores C = sum over ranks (bf16, identical on every rank):
- *     the NVLink transfer overlaps the GEMM's tail and no all-reduce kernel runs; nvc_fused_add_rmsnorm follows as at
- *     tp_size 1.  COLLECTIVE (same M / Nout on every rank, same position in the LL call sequence); fails with
- *     NVC_ESHAPE when the message is too large for the LL one-shot protocol (the caller then uses the unfused pair). */
+ *     all ranks in every mode.  tp_size in {2, 4, 8}; H % 64 == 0, H <= 8192. */
 int nvc_ctx_nvls_init(nvc_ctx* ctx, size_t slot_bytes, size_t ll_buf_bytes, const char* group_name);
 int nvc_ctx_nvls_ready(const nvc_ctx* ctx);
 const char* nvc_ctx_nvls_status(const nvc_ctx* ctx);
@@ -143,8 +136,6 @@ size_t nvc_ctx_nvls_ll_bytes(const nvc_ctx* ctx);
 void* nvc_ctx_nvls_slot(nvc_ctx* ctx);
 int nvc_nvls_allreduce_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x_partial, const float* residual_in, float* residual_out,
                                const nvc_bf16* w, float eps, nvc_bf16* out, int N, int H, int mode, void* stream);
-int nvc_gemm_bf16_allreduce(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, nvc_bf16* C, int ldc, int M,
-                            int Nout, int K, void* stream);
 /* End of a TP step (vocab-parallel lm_head + per-shard argmax / sample): all-gather of the ranks' (best value,
  * token) candidates through the multicast LL buffers and merge - largest value, ties -> the larger token id
  * (llm_engine.rs:135-142 "last maximum") - in one kernel; out_tok [B] is identical on every rank.  out_val may be

@@ -3,105 +3,7 @@
 #pragma once
 #include "common.cuh"
 
-// NVC_EPI_LL_ALLREDUCE (tensor parallel, decode): the GEMM is a row-parallel projection and its epilogue IS the all-reduce.
-// Every epilogue thread multimem.st's its 16-byte pieces of this rank's partial rows into range `rank` of the current
-// low-latency buffer of the NVLS multicast object (one store reaches every rank), then waits for the same pieces of the
-// other ranks to land in its OWN copy of the buffer (spinning on the data: the buffers are kept filled with a sentinel no
-// partial can contain), sums the tp pieces in rank order (bit-identical on every rank) and stores the bf16 sums to C.
-// The NVLink transfer therefore overlaps the GEMM's own tail and no separate all-reduce kernel runs (a kernel boundary
-// would wait for the remote stores to drain: pushing from the epilogue but reducing in a second kernel measured no gain,
-// profiles/r02_nvls_gemm_push_tp2.jsonl).  Protocol state as in nvls_allreduce.cu (same buffers, same epochs).
-enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1, NVC_EPI_LL_ALLREDUCE = 2 };
-
-struct LLReduce {
-  uint8_t* mc_ll = nullptr;          // multicast address of LL buffer 0
-  uint8_t* uc_ll = nullptr;          // this rank's copy of LL buffer 0
-  size_t ll_buf_bytes = 0;           // bytes per LL buffer (three rotate by epoch)
-  uint32_t* state = nullptr;         // [0] epoch of the last completed LL call, [1] CTAs finished, [2..4] vectors in use per buffer
-  uint32_t epoch_mod = 0;
-  int rank = 0, tp = 1;
-};
-
-constexpr uint32_t kLLSentinel = 0xFFFFFFFFu;
-constexpr unsigned kLLSpinLimit = 1u << 24;
-// words of 0xFFFF / 0xFFFFFFFF are the LL protocol's "not arrived yet": a bf16 NaN with that payload is sent as 0x7FFF
-__device__ __forceinline__ uint32_t ll_scrub(uint32_t w) {
-  if ((w & 0xFFFFu) == 0xFFFFu) w &= ~0x8000u;
-  if ((w >> 16) == 0xFFFFu) w &= ~0x80000000u;
-  return w;
-}
-__device__ __forceinline__ uint4 ll_ld_volatile(const void* p) {     // written by peers through NVLink: never from L1
-  uint4 r;
-  asm volatile("ld.volatile.global.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
-  return r;
-}
-// vector index of 8 columns [n0, n0 + 8) of row `row` inside one rank's [M, N] message
-__device__ __forceinline__ size_t ll_vec(int N, int row, int n0) { return (size_t)row * ((uint32_t)N >> 3) + (n0 >> 3); }
-// push 8 columns (16 bytes) of this rank's partial row to every rank
-__device__ __forceinline__ uint4 ll_push8(const LLReduce& ll, uint32_t epoch, size_t T, size_t vec, const float* f) {
-  uint4 p = pack8(f);
-  p.x = ll_scrub(p.x); p.y = ll_scrub(p.y); p.z = ll_scrub(p.z); p.w = ll_scrub(p.w);
-  uint8_t* dst = ll.mc_ll + (size_t)(epoch % 3) * ll.ll_buf_bytes + ((size_t)ll.rank * T + vec) * 16;
-  asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};" ::"l"(dst), "r"(p.x), "r"(p.y), "r"(p.z),
-               "r"(p.w) : "memory");
-  return p;
-}
-// Wait for the tp pieces of V vectors (16 bytes each, V * tp loads in flight at once: one NVLink / L2 latency, not V * tp)
-// and sum them in rank order (fp32).  mine[v] = what this thread pushed for vector v: taken from registers instead of
-// waiting for the multicast store to come back to this rank's own copy.  false: timed out.
-template <int V>
-__device__ __forceinline__ bool ll_wait_sum(const LLReduce& ll, uint32_t epoch, size_t T, const size_t* vec, const uint4* mine,
-                                            int nvalid, float (*s)[8]) {
-  constexpr int kMaxTp = 8;
-  const uint8_t* cur = ll.uc_ll + (size_t)(epoch % 3) * ll.ll_buf_bytes;
-  uint4 part[V][kMaxTp];
-  unsigned pending = 0;                                // bit v * 8 + p: piece not there yet
-#pragma unroll
-  for (int v = 0; v < V; ++v) {
-#pragma unroll
-    for (int p = 0; p < kMaxTp; ++p) {
-      if (v < nvalid && p < ll.tp) {
-        if (p == ll.rank) {
-          part[v][p] = mine[v];
-        } else {
-          part[v][p] = ll_ld_volatile(cur + ((size_t)p * T + vec[v]) * 16);
-          pending |= 1u << (v * kMaxTp + p);
-        }
-      }
-    }
-  }
-  unsigned spins = 0;
-  while (pending) {
-#pragma unroll
-    for (int v = 0; v < V; ++v) {
-#pragma unroll
-      for (int p = 0; p < kMaxTp; ++p) {
-        const unsigned bit = 1u << (v * kMaxTp + p);
-        if (pending & bit) {
-          const uint4 x = part[v][p];
-          if (x.x != kLLSentinel && x.y != kLLSentinel && x.z != kLLSentinel && x.w != kLLSentinel) pending &= ~bit;
-          else part[v][p] = ll_ld_volatile(cur + ((size_t)p * T + vec[v]) * 16);
-        }
-      }
-    }
-    if (++spins > kLLSpinLimit) return false;
-  }
-#pragma unroll
-  for (int v = 0; v < V; ++v) {
-#pragma unroll
-    for (int k = 0; k < 8; ++k) s[v][k] = 0.f;
-#pragma unroll
-    for (int p = 0; p < kMaxTp; ++p) {
-      if (v < nvalid && p < ll.tp) {
-        float f[8];
-        unpack8(part[v][p], f);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s[v][k] += f[k];
-      }
-    }
-  }
-  return true;
-}
+enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1 };
 
 // 16 accumulator columns of one row -> C (bf16 or f32), 16-byte stores
 __device__ __forceinline__ void store16(void* C, int out_f32, int64_t off, const float* f) {

@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total,
                          int k_blocks_per_split, int a_box_rows, int prefetch_w, int ks_cluster, int epi, float* __restrict__ ws,
-                         int* __restrict__ counters, long long* __restrict__ trace, const LLReduce ll) {
+                         int* __restrict__ counters, long long* __restrict__ trace) {
   using cfg = Cfg<BN, KPS>;
   // optional phase timestamps of CTA (0,0,0) (tools/gemm_microbench.py); NULL in production
   const bool tr = trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
@@ -217,14 +217,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const int r = q * 32 + lane;            // row inside the tile
     const int grow = m_tile * BM + r;
     const bool row_ok = grow < M;
-    // LL all-reduce epilogue: the call's epoch = last completed epoch + 1 (every earlier LL call on this stream has
-    // completed: this is past the dependency wait) and the extent of the buffer to refill; fetched while the main loop runs
-    uint32_t ll_epoch = 0, ll_used = 0;
-    if (epi == NVC_EPI_LL_ALLREDUCE) {
-      const volatile uint32_t* vs = ll.state;
-      ll_epoch = (vs[0] + 1) % ll.epoch_mod;
-      ll_used = vs[2 + (ll_epoch + 2) % 3];
-    }
     ptx::mbar_wait(tmem_full_bar, 0);
     ptx::tcgen05_fence_after();
     if (tr && threadIdx.x == 64) trace[81] = clock64();
@@ -232,7 +224,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
     const int tile_id = m_tile * gridDim.x + n_tile;
 
     if (num_splits == 1) {
-      const size_t ll_T = (size_t)M * ((uint32_t)N >> 3);          // vectors of one rank's message
       if constexpr (BN >= 32) {
 #pragma unroll 1
         for (int c = 0; c < BN / 16; c += 2) {          // two 16-column chunks per tensor-memory round trip
@@ -243,14 +234,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
           float f[32];
 #pragma unroll
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-          if (epi == NVC_EPI_LL_ALLREDUCE) {
-            const int n0 = n_tile * BN + c * 16;
-#pragma unroll
-            for (int h = 0; h < 4; ++h)
-              if (row_ok && n0 + 8 * h < N) ll_push8(ll, ll_epoch, ll_T, ll_vec(N, grow, n0 + 8 * h), f + 8 * h);
-          } else if (row_ok) {
-            emit32(C, out_f32, epi, (int64_t)grow * ldc, n_tile * BN + c * 16, N, f);
-          }
+          if (row_ok) emit32(C, out_f32, epi, (int64_t)grow * ldc, n_tile * BN + c * 16, N, f);
         }
       } else {
         uint32_t v[16];
@@ -259,62 +243,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
         float f[16];
 #pragma unroll
         for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
-        if (row_ok && n_tile * BN < N) {
-          if (epi == NVC_EPI_LL_ALLREDUCE) {
-            ll_push8(ll, ll_epoch, ll_T, ll_vec(N, grow, n_tile * BN), f);
-            ll_push8(ll, ll_epoch, ll_T, ll_vec(N, grow, n_tile * BN + 8), f + 8);
-          } else {
-            store16(C, out_f32, (int64_t)grow * ldc + n_tile * BN, f);
-          }
-        }
-      }
-      if (epi == NVC_EPI_LL_ALLREDUCE) {
-        const int et = threadIdx.x - 64;
-        const uint32_t n_ctas = gridDim.x * gridDim.y;
-        {                                          // refill the buffer the previous LL call read (this rank's copy)
-          uint4* old = reinterpret_cast<uint4*>(ll.uc_ll + (size_t)((ll_epoch + 2) % 3) * ll.ll_buf_bytes);
-          const uint4 sent = make_uint4(kLLSentinel, kLLSentinel, kLLSentinel, kLLSentinel);
-          for (uint32_t j = (uint32_t)tile_id * kEpilogueThreads + et; j < ll_used; j += n_ctas * kEpilogueThreads) old[j] = sent;
-        }
-        // this thread's pieces of every rank, 16 columns (two vectors x tp loads in flight) at a time; its own pieces come
-        // back out of tensor memory instead of waiting for the multicast store to return to this rank's copy
-#pragma unroll 1
-        for (int c = 0; c < BN / 16; ++c) {
-          const int n0 = n_tile * BN + c * 16;
-          uint32_t v[16];
-          ptx::tmem_ld_32x32b_x16(taddr + c * 16, v);      // warp-collective: outside the row / column guards
-          ptx::tmem_ld_wait();
-          if (!row_ok || n0 >= N) continue;
-          float f[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[j]);
-          uint4 mine[2] = {pack8(f), pack8(f + 8)};
-#pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            mine[h].x = ll_scrub(mine[h].x); mine[h].y = ll_scrub(mine[h].y);
-            mine[h].z = ll_scrub(mine[h].z); mine[h].w = ll_scrub(mine[h].w);
-          }
-          const size_t vec[2] = {ll_vec(N, grow, n0), ll_vec(N, grow, n0 + 8)};
-          const int nvalid = n0 + 8 < N ? 2 : 1;
-          float sum[2][8];
-          if (!ll_wait_sum<2>(ll, ll_epoch, ll_T, vec, mine, nvalid, sum)) {
-            printf("nvc: GEMM + NVLS all-reduce timed out (rank %d, epoch %u, row %d, column %d)\n", ll.rank, ll_epoch, grow, n0);
-            __trap();
-          }
-          nvc_bf16* dst = reinterpret_cast<nvc_bf16*>(C) + (int64_t)grow * ldc + n0;
-          *reinterpret_cast<uint4*>(dst) = pack8(sum[0]);
-          if (nvalid == 2) *reinterpret_cast<uint4*>(dst + 8) = pack8(sum[1]);
-        }
-        // the LAST CTA TO FINISH publishes the epoch and this call's footprint (as the LL all-reduce kernel does)
-        ptx::named_bar_sync(1, kEpilogueThreads);
-        if (threadIdx.x == 64) {
-          __threadfence();
-          if (atomicAdd(&ll.state[1], 1u) == n_ctas - 1) {
-            ll.state[1] = 0;
-            ll.state[2 + ll_epoch % 3] = (uint32_t)ll.tp * (uint32_t)ll_T;
-            ll.state[0] = ll_epoch;
-          }
-        }
+        if (row_ok && n_tile * BN < N) store16(C, out_f32, (int64_t)grow * ldc + n_tile * BN, f);
       }
     } else if (ks_cluster) {
       // ---- split-K inside a cluster (1,1,S): park this CTA's fp32 partial tile in its own, now idle,
@@ -472,7 +401,7 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
 
 template <int BN, int KPS, int CL>
 int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M,
-           int N, int K, int splits, int ks_cluster, int epi, cudaStream_t stream, long long* trace, const LLReduce& ll) {
+           int N, int K, int splits, int ks_cluster, int epi, cudaStream_t stream, long long* trace) {
   using cfg = Cfg<BN, KPS>;
   CUtensorMap ta, tb;
   // a single partial m-tile only needs the rows that exist (rounded to the 8-row swizzle atom per
@@ -495,7 +424,7 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
                                           stream, dim3(CL, 1, ks ? eff_splits : 1), ta, tb, C, ldc, out_f32, M, N, kb_total,
                                           kb_per, a_rows / CL,
                                           (g_nvc_gemm_prefetch && M <= BM) ? 1 : 0,   // helps latency-bound decode, hurts M >= 256
-                                          ks, epi, ctx->gemm_ws, ctx->gemm_counters, trace, ll));
+                                          ks, epi, ctx->gemm_ws, ctx->gemm_counters, trace));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -589,7 +518,7 @@ extern "C" int nvc_gemm_init(nvc_ctx* ctx) {
 
 static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc,
                      int out_dtype, int M, int Nout, int K, int force_bn, int force_splits, int epi,
-                     void* stream, long long* trace, const LLReduce& ll = LLReduce{}) {
+                     void* stream, long long* trace) {
   NVC_REQUIRE(ctx, ctx && A && W && C, NVC_EINVAL, "null pointer");
   NVC_REQUIRE(ctx, M >= 0 && Nout > 0 && K > 0, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, K % 64 == 0, NVC_ESHAPE, "K must be a multiple of 64");
@@ -597,11 +526,8 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   NVC_REQUIRE(ctx, lda % 8 == 0 && lda >= K, NVC_ESHAPE, "lda must be >= K and a multiple of 8");
   NVC_REQUIRE(ctx, ldc >= (epi == NVC_EPI_SILU_MUL ? Nout / 2 : Nout) && ldc % 8 == 0, NVC_ESHAPE,
               "ldc must be >= the output width and a multiple of 8");
-  NVC_REQUIRE(ctx, epi == NVC_EPI_NONE || epi == NVC_EPI_LL_ALLREDUCE || (epi == NVC_EPI_SILU_MUL && Nout % 32 == 0 && out_dtype == NVC_DT_BF16),
+  NVC_REQUIRE(ctx, epi == NVC_EPI_NONE || (epi == NVC_EPI_SILU_MUL && Nout % 32 == 0 && out_dtype == NVC_DT_BF16),
               NVC_ESHAPE, "fused SiLU-mul epilogue needs Nout % 32 == 0 and bf16 output");
-  NVC_REQUIRE(ctx, epi != NVC_EPI_LL_ALLREDUCE || (M <= BM && out_dtype == NVC_DT_BF16 && ll.mc_ll != nullptr && force_bn != 512 &&
-                                                   Nout % 64 == 0),
-              NVC_ESHAPE, "the all-reduce epilogue needs M <= 128, bf16 output, Nout % 64 == 0 and the NVLS buffers");
   NVC_REQUIRE(ctx, out_dtype == NVC_DT_BF16 || out_dtype == NVC_DT_F32, NVC_EINVAL, "bad out_dtype");
   NVC_REQUIRE(ctx, ((uintptr_t)A % 16) == 0 && ((uintptr_t)W % 16) == 0 && ((uintptr_t)C % 16) == 0, NVC_EINVAL,
               "pointers must be 16-byte aligned");
@@ -646,7 +572,7 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   cudaStream_t st = nvc_stream(stream);
   const int f32 = out_dtype == NVC_DT_F32;
 #define X(BN, KPS, CL) \
-  if (bn == BN && kps == KPS && cl == CL) return launch<BN, KPS, CL>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, ks, epi, st, trace, ll);
+  if (bn == BN && kps == KPS && cl == CL) return launch<BN, KPS, CL>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, ks, epi, st, trace);
   NVC_GEMM_CONFIGS(X)
 #undef X
   NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported tile configuration");
@@ -683,16 +609,4 @@ extern "C" int nvc_gemm_bf16_silu_mul_ex(nvc_ctx* ctx, const nvc_bf16* A, int ld
 extern "C" int nvc_gemm_bf16_silu_mul(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W_gu16, nvc_bf16* act,
                                       int ldc, int M, int I, int K, void* stream) {
   return nvc_gemm_bf16_silu_mul_ex(ctx, A, lda, W_gu16, act, ldc, M, I, K, 0, 0, stream);
-}
-
-// Row-parallel projection + all-reduce in ONE kernel (decode, M <= 128, tensor parallel over the NVLS multicast object):
-// C[M, Nout] = sum over ranks of A_rank W_rank^T, bf16, identical on every rank (see NVC_EPI_LL_ALLREDUCE).  COLLECTIVE: every
-// rank of the group launches it with the same M / Nout at the same point of its LL call sequence.  No split-K (a tile's
-// rows leave from, and come back to, one CTA).
-extern "C" int nvc_gemm_bf16_allreduce(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, nvc_bf16* C, int ldc, int M,
-                                       int Nout, int K, void* stream) {
-  LLReduce ll;
-  int rc = nvc_nvls_ll_info(ctx, M, Nout, &ll.mc_ll, &ll.uc_ll, &ll.ll_buf_bytes, &ll.state, &ll.epoch_mod, &ll.rank, &ll.tp);
-  if (rc) return rc;
-  return gemm_impl(ctx, A, lda, W, C, ldc, NVC_DT_BF16, M, Nout, K, 0, 0, NVC_EPI_LL_ALLREDUCE, stream, nullptr, ll);
 }

@@ -24,8 +24,6 @@ int nvc_gemm_pair_init(nvc_ctx* ctx);
 // CTA-pair (cta_group::2) GEMM for M > 128; force_splits 0 = choose the in-cluster split-K factor
 int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M,
                   int N, int K, int force_splits, int epi, void* stream, long long* trace);
-int nvc_nvls_ll_info(nvc_ctx* ctx, int N, int H, uint8_t** mc_ll, uint8_t** uc_ll, size_t* ll_buf_bytes, uint32_t** state,
-                     uint32_t* epoch_mod, int* rank, int* tp_out);
 int nvc_prefill_attn_init(nvc_ctx* ctx);
 int nvc_paged_decode_init(nvc_ctx* ctx);
 }

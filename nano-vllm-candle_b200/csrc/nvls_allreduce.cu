@@ -787,28 +787,6 @@ extern "C" int nvc_ctx_nvls_init(nvc_ctx* ctx, size_t slot_bytes, size_t ll_buf_
 }
 
 // mode 0 = choose by size, 1 = LL one-shot, 2 = two-shot (flag barriers), 3 = two-shot with LL broadcast
-// what a GEMM with the all-reduce epilogue needs (nvc_gemm_bf16_allreduce, gemm_epilogue.cuh); fails unless the automatic
-// choice for an [N, H] bf16 message is the LL one-shot protocol
-extern "C" int nvc_nvls_ll_info(nvc_ctx* ctx, int N, int H, uint8_t** mc_ll, uint8_t** uc_ll, size_t* ll_buf_bytes, uint32_t** state,
-                                uint32_t* epoch_mod, int* rank, int* tp_out) {
-  NVC_REQUIRE(ctx, ctx && ctx->nvls_ready && ctx->nvls, NVC_ESTATE, "NVLS buffers not set up (nvc_ctx_nvls_init)");
-  nvc_nvls* n = ctx->nvls;
-  const int tp = ctx->tp_size;
-  const size_t msg = (size_t)N * H * 2;
-  NVC_REQUIRE(ctx, tp == 2 || tp == 4 || tp == 8, NVC_ESHAPE, "NVLS all-reduce supports tp_size 2, 4, 8");
-  NVC_REQUIRE(ctx, N > 0 && H > 0 && H % 64 == 0 && H / 8 <= 1024, NVC_ESHAPE, "H must be a multiple of 64 and <= 8192");
-  NVC_REQUIRE(ctx, msg * tp <= n->ll_buf_bytes && msg * (tp - 1) <= ((size_t)3 << 20), NVC_ESHAPE,
-              "message too large for the LL one-shot all-reduce");
-  *mc_ll = reinterpret_cast<uint8_t*>(n->mc_va) + kNvlsFlagBytes + n->slot_bytes;
-  *uc_ll = reinterpret_cast<uint8_t*>(n->uc_va) + kNvlsFlagBytes + n->slot_bytes;
-  *ll_buf_bytes = n->ll_buf_bytes;
-  *state = n->state;
-  *epoch_mod = kEpochMod;
-  *rank = ctx->tp_rank;
-  *tp_out = tp;
-  return NVC_OK;
-}
-
 extern "C" int nvc_nvls_allreduce_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x_partial, const float* residual_in,
                                           float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out, int N, int H,
                                           int mode, void* stream) {

@@ -113,20 +113,11 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
   const int H = c.hidden_size, hd = c.head_dim, L = c.num_hidden_layers;
   const float scale = 1.0f / sqrtf((float)hd);   // (head_dim as f32).powf(-0.5), qwen3.rs:132
   static const bool p2p_env = !(getenv("NVC_P2P_AR") && atoi(getenv("NVC_P2P_AR")) == 0);
-  // decode through the switch: o_proj / down_proj and their all-reduce are ONE kernel (nvc_gemm_bf16_allreduce: the GEMM's
-  // epilogue pushes, waits and sums over the multicast buffers), followed by the plain add + norm as at TP 1;
-  // NVC_GEMM_AR=0 keeps GEMM -> slot -> all-reduce + norm kernel
-  static const bool gemm_ar_env = !(getenv("NVC_GEMM_AR") && atoi(getenv("NVC_GEMM_AR")) == 0);
   // NVLS (in-switch) all-reduce + residual + norm for every step kind; else the peer-load kernel for decode-sized
   // messages; else NCCL + the norm kernel
   const bool nvls = r->tp > 1 && r->x_nvls && nvc_ctx_nvls_ready(ctx);
   const bool p2p = !nvls && r->tp > 1 && decode && p2p_env && nvc_ctx_p2p_ready(ctx) &&
                    (size_t)N * H * 2 <= nvc_ctx_p2p_slot_bytes(ctx);
-  bool gemm_ar = false;
-  if (r->tp > 1 && r->x_nvls && nvc_ctx_nvls_ready(ctx) && decode && gemm_ar_env && N <= 128) {
-    uint8_t *a0, *a1; size_t a2; uint32_t* a3; uint32_t a4; int a5, a6;
-    gemm_ar = nvc_nvls_ll_info(ctx, N, H, &a0, &a1, &a2, &a3, &a4, &a5, &a6) == NVC_OK;
-  }
   nvc_bf16* slot0 = p2p ? reinterpret_cast<nvc_bf16*>(nvc_ctx_p2p_slot(ctx, 0)) : nullptr;
   nvc_bf16* slot1 = p2p ? reinterpret_cast<nvc_bf16*>(nvc_ctx_p2p_slot(ctx, 1)) : nullptr;
   *final_norm_done = false;
@@ -169,12 +160,9 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     }
     if (rc) return rc;
     // o_proj (row-parallel) -> [all-reduce, N4] -> post_attention_layernorm with residual add
-    if (gemm_ar) rc = nvc_gemm_bf16_allreduce(ctx, r->attn, r->nh_l * hd, Ly.w_o, r->x, H, N, H, r->nh_l * hd, st);
-    else rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, Ly.w_o, p2p ? slot0 : r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
+    rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, Ly.w_o, p2p ? slot0 : r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
     if (rc) return rc;
-    if (gemm_ar) {
-      rc = nvc_fused_add_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
-    } else if (nvls) {
+    if (nvls) {
       rc = nvc_nvls_allreduce_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, 0, st);
     } else if (p2p) {
       rc = nvc_p2p_allreduce_rmsnorm(ctx, 0, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
@@ -187,11 +175,6 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     rc = nvc_gemm_bf16_silu_mul(ctx, r->xn, H, Ly.w_gu, r->act, r->I_l, N, r->I_l, H, st);
     if (rc) return rc;
     // down_proj (row-parallel) -> [all-reduce, N4]
-    if (gemm_ar) {        // the sum over ranks is in x: the next layer's (or the final) norm adds the residual, as at TP 1
-      rc = nvc_gemm_bf16_allreduce(ctx, r->act, r->I_l, Ly.w_down, r->x, H, N, H, r->I_l, st);
-      if (rc) return rc;
-      continue;
-    }
     rc = nvc_gemm_bf16(ctx, r->act, r->I_l, Ly.w_down, p2p ? slot1 : r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
     if (rc) return rc;
     if (nvls) {

@@ -123,18 +123,6 @@ class Context:
                                                    float(eps), _ptr(out), N, H, mode, _stream()), "nvc_nvls_allreduce_rmsnorm")
         return out
 
-    def gemm_allreduce(self, a: torch.Tensor, w: torch.Tensor, out=None):
-        """sum over ranks of a_rank @ w_rank.T in ONE kernel (row-parallel GEMM whose epilogue is the NVLS all-reduce);
-        collective, M <= 128."""
-        _req(a, BF16, "a"); _req(w, BF16, "w")
-        M, K = a.shape
-        N = w.shape[0]
-        assert w.shape[1] == K and w.is_contiguous() and a.stride(1) == 1
-        out = torch.empty((M, N), dtype=BF16, device=a.device) if out is None else out
-        self._ck(self.l.nvc_gemm_bf16_allreduce(self.h, _ptr(a), a.stride(0), _ptr(w), _ptr(out), out.stride(0), M, N, K,
-                                                _stream()), "nvc_gemm_bf16_allreduce")
-        return out
-
     def allreduce(self, buf: torch.Tensor):
         if buf.dtype == BF16:
             self._ck(self.l.nvc_allreduce_bf16(self.h, _ptr(buf), buf.numel(), _stream()), "nvc_allreduce_bf16")

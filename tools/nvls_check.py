@@ -105,42 +105,6 @@ def main():
                     lines.append(rec)
                     if rank == 0 and not good:
                         print(json.dumps(rec), flush=True)
-    # ---- GEMM + all-reduce in one kernel (nvc_gemm_bf16_allreduce) against the unfused sequence (GEMM -> memory -> LL
-    # one-shot all-reduce without norm) on the same operands: bit-identical when both GEMMs run unsplit (short K), within
-    # bf16 rounding otherwise; bit-identical across ranks always; twice in a row (epoch / refill bookkeeping)
-    if ok_nvls:
-        for (M, H, K) in [(64, 1024, 256), (64, 1024, 384), (1, 1024, 1024), (37, 1024, 2048), (128, 4096, 512), (64, 5120, 640),
-                          (64, 1024, 256), (16, 2048, 192), (100, 1024, 128)]:
-            if M * H * 2 * world > ll_bytes or M * H * 2 * (world - 1) > (3 << 20):
-                continue
-            call += 1
-            gen.manual_seed(5000 * call + rank)
-            a_in = (torch.randn((M, K), device=dev, generator=gen) * 0.5).bfloat16()
-            wt = (torch.randn((H, K), device=dev, generator=gen) / K ** 0.5).bfloat16()
-            x = ctx.gemm(a_in, wt)
-            torch.cuda.synchronize(); dist.barrier()
-            o1 = ctx.nvls_allreduce_rmsnorm(x, None, eps, None, None, mode=1)
-            torch.cuda.synchronize(); dist.barrier()
-            o2 = ctx.gemm_allreduce(a_in, wt).clone()
-            o3 = ctx.gemm_allreduce(a_in, wt)
-            torch.cuda.synchronize()
-            err = float((o1.float() - o2.float()).abs().max())
-            exact = bool(torch.equal(o1.view(torch.int16), o2.view(torch.int16)))
-            outs = [torch.empty_like(o2) for _ in range(world)]
-            dist.all_gather(outs, o2)
-            same = all(torch.equal(o.view(torch.int16), outs[0].view(torch.int16)) for o in outs) and \
-                bool(torch.equal(o2.view(torch.int16), o3.view(torch.int16)))
-            good = same and (exact if K <= 1024 else err <= 2e-2 * max(1.0, float(o1.float().abs().max())))
-            flag = torch.tensor([int(good)], device=dev)
-            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-            good = bool(flag[0])
-            fails += int(not good)
-            rec = {"what": "parity", "N": M, "H": H, "K": K, "mode": 5, "picked": "gemm_allreduce_one_kernel", "norm": False,
-                   "max_err": err, "res_err": 0.0, "scale": 1.0, "bit_identical_to_unfused": exact, "ranks_bit_identical": same,
-                   "ok": good}
-            lines.append(rec)
-            if rank == 0:
-                print(json.dumps(rec), flush=True)
     # ---- timing
     if not a.no_timing:
         tshapes = [(1, 1024), (64, 1024), (256, 1024), (64, 4096), (256, 4096), (256, 5120), (256, 8192), (1024, 4096), (4096, 4096),
@@ -165,21 +129,6 @@ def main():
                     ctx._ck(L.nvc_p2p_allreduce_rmsnorm(ctx.h, k[0], ops._ptr(res), ops._ptr(res), ops._ptr(w), eps, ops._ptr(out), N, H,
                                                         ops._stream()), "p2p")
                 variants.append(("p2p_oneshot_r01", p2p))
-            if ok_nvls and N <= 128 and msg * world <= ll_bytes and msg * (world - 1) <= (3 << 20):
-                Kg = 2048 // world if H == 1024 else 4096 // world
-                ag = torch.zeros((N, Kg), device=dev, dtype=torch.bfloat16)
-                wg = torch.zeros((H, Kg), device=dev, dtype=torch.bfloat16)
-                xg = torch.empty((N, H), device=dev, dtype=torch.bfloat16)
-
-                def gemm_then_ll():
-                    ctx.gemm(ag, wg, out=xg)
-                    ctx.nvls_allreduce_rmsnorm(xg, w, eps, res, res, out=out, mode=1)
-
-                def gemm_ar_then_norm():
-                    ctx.gemm_allreduce(ag, wg, out=xg)
-                    ctx.fused_add_rmsnorm(xg, w, eps, res, res, out=out)
-                variants.append((f"gemm_k{Kg}_then_ll_oneshot_norm", gemm_then_ll))
-                variants.append((f"gemm_k{Kg}_allreduce_one_kernel_then_norm", gemm_ar_then_norm))
             xb = torch.zeros((N, H), device=dev, dtype=torch.bfloat16)
 
             def nccl():

@@ -106,7 +106,7 @@ int dev_alloc(nvc_runner* r, T** p, size_t count) {
 // sequences are single tokens (rows 0 .. num_decode-1) and go through the paged decode kernel,
 // the other sequences through the paged prefill kernel with their own cu_seqlens (r->d_cu2).
 int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blocks_hint, bool* final_norm_done,
-               bool paged_prefill = false, int num_decode = 0, int row0 = 0, const int32_t* cu_rel = nullptr) {
+               bool paged_prefill = false, int num_decode = 0) {
   const nvc_qwen3_config& c = r->cfg;
   nvc_ctx* ctx = r->ctx;
   void* st = r->stream;
@@ -120,17 +120,6 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
                    (size_t)N * H * 2 <= nvc_ctx_p2p_slot_bytes(ctx);
   nvc_bf16* slot0 = p2p ? reinterpret_cast<nvc_bf16*>(nvc_ctx_p2p_slot(ctx, 0)) : nullptr;
   nvc_bf16* slot1 = p2p ? reinterpret_cast<nvc_bf16*>(nvc_ctx_p2p_slot(ctx, 1)) : nullptr;
-  // row window [row0, row0 + N) of the step's token buffers (a prefill step may run its sequences in sub-batches, see
-  // prefill_impl); cu_rel: that window's cu_seqlens, relative to row0
-  nvc_bf16* x_ = r->x + (size_t)row0 * H;
-  nvc_bf16* xn_ = r->xn + (size_t)row0 * H;
-  float* res_ = r->residual + (size_t)row0 * H;
-  nvc_bf16* qkv_ = r->qkv + (size_t)row0 * r->qkv_l;
-  nvc_bf16* attn_ = r->attn + (size_t)row0 * r->nh_l * hd;
-  nvc_bf16* act_ = r->act + (size_t)row0 * r->I_l;
-  const int32_t* pos_ = r->d_pos + row0;
-  const int32_t* slots_ = r->d_slots + row0;
-  const int32_t* cu_ = cu_rel ? cu_rel : r->d_cu;
   *final_norm_done = false;
   bool xn_ready = false;
   int rc;
@@ -138,74 +127,74 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     Layer& Ly = r->layers[li];
     if (!xn_ready) {
       // input_layernorm with fused residual add; layer 0 seeds the residual stream (qwen3.rs:376-387)
-      rc = nvc_fused_add_rmsnorm(ctx, x_, li == 0 ? nullptr : res_, res_, Ly.ln1, c.rms_norm_eps, xn_, N, H, st);
+      rc = nvc_fused_add_rmsnorm(ctx, r->x, li == 0 ? nullptr : r->residual, r->residual, Ly.ln1, c.rms_norm_eps, r->xn, N, H, st);
       if (rc) return rc;
     }
     xn_ready = false;
-    rc = nvc_gemm_bf16(ctx, xn_, H, Ly.w_qkv, qkv_, r->qkv_l, NVC_DT_BF16, N, r->qkv_l, H, st);
+    rc = nvc_gemm_bf16(ctx, r->xn, H, Ly.w_qkv, r->qkv, r->qkv_l, NVC_DT_BF16, N, r->qkv_l, H, st);
     if (rc) return rc;
-    rc = nvc_qk_norm_rope_store(ctx, qkv_, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, pos_, slots_,
+    rc = nvc_qk_norm_rope_store(ctx, r->qkv, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos, r->d_slots,
                                 Ly.k_cache, Ly.v_cache, N, r->nh_l, r->kv_l, hd, st);
     if (rc) return rc;
     if (decode) {
-      rc = nvc_paged_decode_attn_ex(ctx, qkv_, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
-                                    r->d_ctx, B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, attn_,
+      rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
+                                    r->d_ctx, B, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
                                     r->decode_ws, r->decode_ws_bytes, st);
     } else if (paged_prefill) {
       // cached prefix: K / V of the whole context come from the paged cache (this step's were just stored)
       rc = NVC_OK;
       if (num_decode > 0)
-        rc = nvc_paged_decode_attn_ex(ctx, qkv_, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
-                                      r->d_ctx, num_decode, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, attn_,
+        rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,
+                                      r->d_ctx, num_decode, r->nh_l, r->kv_l, hd, r->opt.kvcache_block_size, scale, r->attn,
                                       r->decode_ws, r->decode_ws_bytes, st);
       if (rc == NVC_OK && B > num_decode)
-        rc = nvc_prefill_attn_paged(ctx, qkv_ + (size_t)num_decode * r->qkv_l, r->qkv_l, Ly.k_cache, Ly.v_cache,
+        rc = nvc_prefill_attn_paged(ctx, r->qkv + (size_t)num_decode * r->qkv_l, r->qkv_l, Ly.k_cache, Ly.v_cache,
                                     r->d_bt + (size_t)num_decode * r->max_blocks_cap, r->max_blocks_cap, r->d_ctx + num_decode,
-                                    num_decode ? r->d_cu2 : cu_, B - num_decode, N - num_decode, max_seqlen, r->nh_l,
+                                    num_decode ? r->d_cu2 : r->d_cu, B - num_decode, N - num_decode, max_seqlen, r->nh_l,
                                     r->kv_l, hd, r->opt.kvcache_block_size, r->opt.num_kvcache_blocks, scale,
-                                    attn_ + (size_t)num_decode * r->nh_l * hd, st);
+                                    r->attn + (size_t)num_decode * r->nh_l * hd, st);
     } else {
-      rc = nvc_prefill_attn_varlen(ctx, qkv_, r->qkv_l, qkv_ + (size_t)r->nh_l * hd, r->qkv_l,
-                                   qkv_ + (size_t)(r->nh_l + r->kv_l) * hd, r->qkv_l, cu_, B, N, max_seqlen,
-                                   r->nh_l, r->kv_l, hd, scale, attn_, st);
+      rc = nvc_prefill_attn_varlen(ctx, r->qkv, r->qkv_l, r->qkv + (size_t)r->nh_l * hd, r->qkv_l,
+                                   r->qkv + (size_t)(r->nh_l + r->kv_l) * hd, r->qkv_l, r->d_cu, B, N, max_seqlen,
+                                   r->nh_l, r->kv_l, hd, scale, r->attn, st);
     }
     if (rc) return rc;
     // o_proj (row-parallel) -> [all-reduce, N4] -> post_attention_layernorm with residual add
-    rc = nvc_gemm_bf16(ctx, attn_, r->nh_l * hd, Ly.w_o, p2p ? slot0 : x_, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
+    rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, Ly.w_o, p2p ? slot0 : r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
     if (rc) return rc;
     if (nvls) {
-      rc = nvc_nvls_allreduce_rmsnorm(ctx, x_, res_, res_, Ly.ln2, c.rms_norm_eps, xn_, N, H, 0, st);
+      rc = nvc_nvls_allreduce_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, 0, st);
     } else if (p2p) {
-      rc = nvc_p2p_allreduce_rmsnorm(ctx, 0, res_, res_, Ly.ln2, c.rms_norm_eps, xn_, N, H, st);
+      rc = nvc_p2p_allreduce_rmsnorm(ctx, 0, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
     } else {
-      if (r->tp > 1) { rc = nvc_allreduce_bf16(ctx, x_, (size_t)N * H, st); if (rc) return rc; }
-      rc = nvc_fused_add_rmsnorm(ctx, x_, res_, res_, Ly.ln2, c.rms_norm_eps, xn_, N, H, st);
+      if (r->tp > 1) { rc = nvc_allreduce_bf16(ctx, r->x, (size_t)N * H, st); if (rc) return rc; }
+      rc = nvc_fused_add_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
     }
     if (rc) return rc;
     // gate_up projection with SiluAndMul fused into the epilogue (w_gu rows interleaved in groups of 16 at load)
-    rc = nvc_gemm_bf16_silu_mul(ctx, xn_, H, Ly.w_gu, act_, r->I_l, N, r->I_l, H, st);
+    rc = nvc_gemm_bf16_silu_mul(ctx, r->xn, H, Ly.w_gu, r->act, r->I_l, N, r->I_l, H, st);
     if (rc) return rc;
     // down_proj (row-parallel) -> [all-reduce, N4]
-    rc = nvc_gemm_bf16(ctx, act_, r->I_l, Ly.w_down, p2p ? slot1 : x_, H, NVC_DT_BF16, N, H, r->I_l, st);
+    rc = nvc_gemm_bf16(ctx, r->act, r->I_l, Ly.w_down, p2p ? slot1 : r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
     if (rc) return rc;
     if (nvls) {
       // the norm that opens layer l+1 (or the final norm) comes out of the same kernel; a prefill step keeps all
       // N normed rows in xn and run_head gathers the last-token rows from there
       const bool last = li + 1 == L;
-      rc = nvc_nvls_allreduce_rmsnorm(ctx, x_, res_, res_, last ? r->final_norm : r->layers[li + 1].ln1,
-                                      c.rms_norm_eps, last && decode ? r->xn_last : xn_, N, H, 0, st);
+      rc = nvc_nvls_allreduce_rmsnorm(ctx, r->x, r->residual, r->residual, last ? r->final_norm : r->layers[li + 1].ln1,
+                                      c.rms_norm_eps, last && decode ? r->xn_last : r->xn, N, H, 0, st);
       if (rc) return rc;
       xn_ready = !last;
       *final_norm_done = last;
     } else if (p2p) {
       const bool last = li + 1 == L;
-      rc = nvc_p2p_allreduce_rmsnorm(ctx, 1, res_, res_, last ? r->final_norm : r->layers[li + 1].ln1,
-                                     c.rms_norm_eps, last ? r->xn_last : xn_, N, H, st);
+      rc = nvc_p2p_allreduce_rmsnorm(ctx, 1, r->residual, r->residual, last ? r->final_norm : r->layers[li + 1].ln1,
+                                     c.rms_norm_eps, last ? r->xn_last : r->xn, N, H, st);
       if (rc) return rc;
       xn_ready = !last;
       *final_norm_done = last;
     } else if (r->tp > 1) {
-      rc = nvc_allreduce_bf16(ctx, x_, (size_t)N * H, st);
+      rc = nvc_allreduce_bf16(ctx, r->x, (size_t)N * H, st);
       if (rc) return rc;
     }
   }
@@ -410,7 +399,7 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
     r->d_ctx = blk + 3 * r->in_pitch;
   }
   if ((rc = dev_alloc(r, &r->d_cu, Bm + 1))) return rc;
-  if ((rc = dev_alloc(r, &r->d_cu2, 2 * Bm + 2))) return rc;
+  if ((rc = dev_alloc(r, &r->d_cu2, Bm + 1))) return rc;
   if ((rc = dev_alloc(r, &r->d_bt, Bm * r->max_blocks_cap))) return rc;
   if ((rc = dev_alloc(r, &r->d_last_rows, Bm))) return rc;
   if ((rc = dev_alloc(r, &r->d_tok, Bm))) return rc;
@@ -420,7 +409,7 @@ int nvc_runner_create(nvc_ctx* ctx, const nvc_qwen3_config* cfg, const nvc_runne
   if ((rc = dev_alloc(r, &r->d_streams, Bm))) return rc;
   R_CUDA(cudaMallocHost(&r->h_temps, Bm * sizeof(float)));
   R_CUDA(cudaMallocHost(&r->h_streams, Bm * sizeof(uint64_t)));
-  r->h_stage_ints = 3 * T + 2 * (Bm + 1) + Bm * r->max_blocks_cap + 2 * Bm + 2 * Bm + 2;
+  r->h_stage_ints = 3 * T + 2 * (Bm + 1) + Bm * r->max_blocks_cap + 2 * Bm;
   R_CUDA(cudaMallocHost(&r->h_stage, r->h_stage_ints * sizeof(int32_t)));
   r->bt_mirror.assign(Bm * r->max_blocks_cap, -1);
   R_CUDA(cudaMallocHost(&r->h_pairs, Bm * tp * sizeof(ArgPair)));
@@ -667,40 +656,8 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
   rc = nvc_embed_gather(ctx, r->d_ids, r->embed, r->x, N, r->cfg.hidden_size, r->cfg.vocab_size, st);
   if (rc) return rc;
   bool fnd = false;
-  // A large whole-prompt prefill step runs its sequences in sub-batches of ~8k tokens through all layers: every kernel's
-  // input was then written a moment ago by its predecessor and is still in the 126 MB L2 (the q/k-norm + RoPE pass, the
-  // norms and the attention read their operands from L2 instead of HBM; the weights are re-read once per sub-batch).
-  // NVC_PREFILL_SUB = tokens per sub-batch (0: off).  TP and the paged / mixed step kinds keep one pass.
-  const int sub_tokens = getenv("NVC_PREFILL_SUB") ? atoi(getenv("NVC_PREFILL_SUB")) : 8192;
-  if (!paged && r->tp == 1 && sub_tokens > 0 && B > 1 && N >= 2 * sub_tokens) {
-    int32_t* hcu2 = last + B;                  // relative cu_seqlens of every sub-batch, back to back (<= 2 B + 1 ints)
-    struct Sub { int b0, nb, row0, n, max_len, cu_off; };
-    std::vector<Sub> subs;
-    int off = 0;
-    for (int b = 0; b < B;) {
-      Sub sb{b, 0, cu_seqlens[b], 0, 0, off};
-      while (b < B && (sb.nb == 0 || sb.n + (cu_seqlens[b + 1] - cu_seqlens[b]) <= sub_tokens)) {
-        const int len = cu_seqlens[b + 1] - cu_seqlens[b];
-        hcu2[off + sb.nb] = sb.n;
-        sb.n += len;
-        sb.max_len = std::max(sb.max_len, len);
-        ++sb.nb;
-        ++b;
-      }
-      hcu2[off + sb.nb] = sb.n;
-      off += sb.nb + 1;
-      subs.push_back(sb);
-    }
-    R_CUDA(cudaMemcpyAsync(r->d_cu2, hcu2, (size_t)off * 4, cudaMemcpyHostToDevice, st));
-    r->last_h2d_bytes += (int64_t)off * 4;
-    for (const Sub& sb : subs) {
-      rc = run_layers(r, sb.n, false, sb.nb, sb.max_len, 0, &fnd, false, 0, sb.row0, r->d_cu2 + sb.cu_off);
-      if (rc) return rc;
-    }
-  } else {
-    rc = run_layers(r, N, false, B, max_seqlen_chunks, hint, &fnd, paged, num_decode);
-    if (rc) return rc;
-  }
+  rc = run_layers(r, N, false, B, max_seqlen_chunks, hint, &fnd, paged, num_decode);
+  if (rc) return rc;
   rc = run_head(r, B, false, fnd);
   r->sampling_armed = false;
   if (rc) return rc;

@@ -200,6 +200,17 @@ int nvc_qk_norm_rope_store(nvc_ctx* ctx, nvc_bf16* qkv, const nvc_bf16* qw, cons
                            const int32_t* slot_mapping, nvc_bf16* k_cache, nvc_bf16* v_cache,
                            int N, int nh, int kv, int hd, void* stream);
 
+/* K3 + K2: the fused QKV projection with K2 as its epilogue (Qwen3Attention::forward up to the attention call,
+ * src/models/qwen3.rs:205-234).  qkv [M, (nh + 2 kv) * hd] contiguous = A W_qkv^T with q / k heads normalised and rotated
+ * and the k / v rows scattered to the caches at slot_mapping[row] (may be NULL: no scatter) - exactly what nvc_gemm_bf16
+ * followed by nvc_qk_norm_rope_store produce, bit for bit.  Prefill-sized M runs as ONE kernel (the pair GEMM's persistent
+ * epilogue parks each head in shared memory and applies K2 there: the separate pass over the QKV buffer disappears);
+ * other shapes run the two kernels. */
+int nvc_qkv_proj_norm_rope(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W_qkv, nvc_bf16* qkv, int M, int K,
+                           const nvc_bf16* q_norm_w, const nvc_bf16* k_norm_w, float eps, const float* cos_sin,
+                           const int32_t* positions, const int32_t* slot_mapping, nvc_bf16* k_cache, nvc_bf16* v_cache,
+                           int nh, int kv, int hd, void* stream);
+
 /* K2'. Stand-alone slot-mapping scatter (N3): cache[slot_mapping[n]] = {k,v}[n]; slot < 0 skips.
  * k, v: bf16 rows of kv*hd elements with row stride ld (elements).  Bit-exact. */
 int nvc_store_kvcache(nvc_ctx* ctx, const nvc_bf16* k, const nvc_bf16* v, int ld,

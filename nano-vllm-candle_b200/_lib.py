@@ -80,6 +80,7 @@ def _declare(l: C.CDLL) -> None:
         "nvc_gemm_bf16_silu_mul_ex": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp],
         "nvc_gemm_bf16_trace": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp],
         "nvc_rope_table_init_sync": [_vp, _f, _i, _i, _vp],
+        "nvc_qkv_proj_norm_rope": [_vp, _vp, _i, _vp, _vp, _i, _i, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
         "nvc_qk_norm_rope_store": [_vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
         "nvc_store_kvcache": [_vp, _vp, _vp, _i, _vp, _vp, _vp, _i, _i, _i, _vp],
         "nvc_prefill_attn_varlen": [_vp, _vp, _i, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _vp],

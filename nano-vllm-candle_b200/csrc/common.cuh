@@ -150,6 +150,47 @@ __device__ __forceinline__ uint4 pack8(const float* f) {
   return u;
 }
 
+// q / k RMSNorm + neox RoPE of one 128-element head row held by 8 lanes: lane l owns ra = elements [8l, 8l + 8) and
+// rb = [64 + 8l, 64 + 8l + 8) (the rotation pairs (d, d + 64) are lane-local); c0 c1 / s0 s1 = cos / sin of frequencies
+// [8l, 8l + 8); mask = the 8 lanes of this unit.  has_w = false: rope only.  Every lane of the unit must call it (shuffles);
+// inactive units pass zeros.  Shared by qk_norm_rope_store_kernel and the QKV GEMM epilogue, which are bit-identical.
+// (src/models/qwen3.rs:206-234, src/layers/layernorm.rs:44-60, src/layers/rotary_embedding.rs:82-107)
+__device__ __forceinline__ void qk_norm_rope8(const uint4& ra, const uint4& rb, unsigned mask, bool has_w, const uint4& w_lo,
+                                              const uint4& w_hi, float eps, const float4& c0, const float4& c1,
+                                              const float4& s0, const float4& s1, uint4& o1, uint4& o2) {
+  float a[8], b[8];
+  unpack8(ra, a);
+  unpack8(rb, b);
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) ss += a[i] * a[i] + b[i] * b[i];
+  ss += __shfl_xor_sync(mask, ss, 1);
+  ss += __shfl_xor_sync(mask, ss, 2);
+  ss += __shfl_xor_sync(mask, ss, 4);
+  float rstd = 1.0f;
+  float wa[8], wb[8];
+  if (has_w) {
+    rstd = 1.0f / sqrtf(ss * (1.0f / 128.0f) + eps);
+    unpack8(w_lo, wa);
+    unpack8(w_hi, wb);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) wa[i] = wb[i] = 1.0f;
+  }
+  const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+  const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+  float y1[8], y2[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float x1 = a[i] * rstd * wa[i];
+    const float x2 = b[i] * rstd * wb[i];
+    y1[i] = x1 * c[i] - x2 * s[i];
+    y2[i] = x2 * c[i] + x1 * s[i];
+  }
+  o1 = pack8(y1);
+  o2 = pack8(y2);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -247,45 +247,16 @@ qk_norm_rope_store_kernel(uint4* __restrict__ qkv, const uint4* __restrict__ qw,
   // kinds align to warp boundaries, which they do not in general; the shuffles below use
   // an 8-lane mask so they only involve the lanes of this unit.
   const unsigned mask = 0xffu << ((threadIdx.x & 31) & ~7);
-  float a[8], b[8];
+  uint4 ra = make_uint4(0, 0, 0, 0), rb = ra;
   if (active) {
-    const uint4 ra = row[l], rb = row[l + 8];
+    ra = row[l];
+    rb = row[l + 8];
     if (!early) load_static();
-    unpack8(ra, a);
-    unpack8(rb, b);
-  } else {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) a[i] = b[i] = 0.f;
   }
-  float ss = 0.f;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) ss += a[i] * a[i] + b[i] * b[i];
-  ss += __shfl_xor_sync(mask, ss, 1);
-  ss += __shfl_xor_sync(mask, ss, 2);
-  ss += __shfl_xor_sync(mask, ss, 4);
+  uint4 o1, o2;
+  qk_norm_rope8(ra, rb, mask, wp != nullptr, w_lo, w_hi, eps, c0, c1, s0, s1, o1, o2);
   if (!active) return;
   const bool is_q = u < nh;
-  float rstd = 1.0f;
-  float wa[8], wb[8];
-  if (wp != nullptr) {   // NULL weight: rope only (RotaryEmbedding::apply on its own)
-    rstd = 1.0f / sqrtf(ss * (1.0f / 128.0f) + eps);
-    unpack8(w_lo, wa);
-    unpack8(w_hi, wb);
-  } else {
-#pragma unroll
-    for (int i = 0; i < 8; ++i) wa[i] = wb[i] = 1.0f;
-  }
-  const float c[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
-  const float s[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
-  float y1[8], y2[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const float x1 = a[i] * rstd * wa[i];
-    const float x2 = b[i] * rstd * wb[i];
-    y1[i] = x1 * c[i] - x2 * s[i];
-    y2[i] = x2 * c[i] + x1 * s[i];
-  }
-  const uint4 o1 = pack8(y1), o2 = pack8(y2);
   row[l] = o1;
   row[l + 8] = o2;
   if (!is_q && slot >= 0) {

@@ -58,8 +58,11 @@ struct PairCfg {
   static constexpr int kStages = kRingBudget / kStageBytes < 6 ? kRingBudget / kStageBytes : 6;
   static constexpr int kAccStages = kTwo ? 1 : 2;
   static constexpr int kNumBars = 2 * kStages + 4;       // full[], empty[], tmem_full[2], tmem_empty[2]
-  static constexpr int kOffStage = (kStages * kStageBytes + kNumBars * 8 + 16 + 127) & ~127;   // 4 epilogue warps x 4 KB row staging
-  static constexpr int kSmemBytes = kOffStage + 4 * 4096 + 1024;
+  static constexpr int kOffStage = (kStages * kStageBytes + kNumBars * 8 + 16 + 127) & ~127;   // 4 epilogue warps x row staging
+  // 4 KB per warp (32 rows x 128 B, RowStage); 8 KB for 256-wide tiles, whose QK-norm epilogue parks whole heads (32 rows x 256 B)
+  static constexpr int kStageBuf = NT == 256 ? 8192 : 4096;
+  static constexpr int kSmemBytes = kOffStage + 4 * kStageBuf + 1024;
+  static_assert(kSmemBytes <= 232448, "shared memory per CTA");
   static constexpr int kChunks = NT / 16;                // 16-column accumulator chunks of a tile
   static constexpr int kPartF4 = kChunks * 4 * kHalf;    // float4s of one CTA's partial tile in the split-K workspace
   static_assert(kStageBytes % 1024 == 0 && (kBoxRowsB % 8) == 0, "swizzle atoms");
@@ -199,7 +202,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total, int kb_per_split,
                  int num_tiles, int n_tiles, int prefetch_w, int epi, float4* __restrict__ ws,
-                 long long* __restrict__ trace, int w_packed) {
+                 long long* __restrict__ trace, int w_packed, const QkEpi qk) {
   using cfg = PairCfg<NT>;
   constexpr int kStages = cfg::kStages;
   constexpr int kStageBytes = cfg::kStageBytes;
@@ -366,7 +369,84 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       ptx::tcgen05_fence_after();
       if (tr && threadIdx.x == 64 && ti == 0) trace[81] = clock64();
       if (tr && threadIdx.x == 64 && tile + num_clusters >= num_tiles) trace[86] = clock64();   // last tile: exposed epilogue
-      RowStage st = make_row_stage(smem_gen + cfg::kOffStage + q * 4096, C, out_f32, epi, ldc,
+      if constexpr (NT == 256) {
+        if (epi == NVC_EPI_QK_NORM_ROPE) {
+          // ---- K2 as the epilogue of the QKV projection: two heads of 128 columns per tile
+          const int row_base = m_tile * kTileM + h * kHalf + q * 32;            // first row of this warp
+          const uint32_t stage = smem_u32(smem_gen + cfg::kOffStage + q * cfg::kStageBuf);   // [32 rows][16 chunks of 16 B], chunk ^= row & 7
+          const int l = lane & 7, sub = lane >> 3;
+          const unsigned mask8 = 0xffu << (lane & 24);
+          const int my_row = row_base + lane;
+          const int pos_lane = my_row < M ? __ldg(qk.positions + my_row) : 0;
+          const int slot_lane = (my_row < M && qk.slot_mapping != nullptr) ? __ldg(qk.slot_mapping + my_row) : -1;
+          nvc_bf16* Cb = reinterpret_cast<nvc_bf16*>(C);
+#pragma unroll 1
+          for (int hh = 0; hh < 2; ++hh) {
+            const int head = n_tile * 2 + hh;                                   // head index in the fused [q | k | v] row
+            if (head * 128 >= N) break;
+            // park the head's 128 accumulator columns as bf16 (what the plain epilogue would have stored)
+#pragma unroll 1
+            for (int c4 = 0; c4 < 4; ++c4) {
+              uint32_t v[32];
+              ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(acc * 256 + hh * 128 + c4 * 32), v);
+              ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(acc * 256 + hh * 128 + c4 * 32 + 16), v + 16);
+              ptx::tmem_ld_wait();
+              float f[32];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                const uint4 pk = pack8(f + 8 * k);
+                const int chunk = c4 * 4 + k;
+                asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(stage + lane * 256 + ((chunk ^ (lane & 7)) << 4)),
+                             "r"(pk.x), "r"(pk.y), "r"(pk.z), "r"(pk.w) : "memory");
+              }
+            }
+            __syncwarp();
+            const bool is_q = head < qk.nh, is_k = !is_q && head < qk.nh + qk.kv;
+            const uint4 w_lo = is_q ? __ldg(qk.qw + l) : (is_k ? __ldg(qk.kw + l) : make_uint4(0, 0, 0, 0));
+            const uint4 w_hi = is_q ? __ldg(qk.qw + l + 8) : (is_k ? __ldg(qk.kw + l + 8) : make_uint4(0, 0, 0, 0));
+#pragma unroll 2
+            for (int pass = 0; pass < 8; ++pass) {
+              const int rr = pass * 4 + sub;                                    // row inside the warp's 32: 8 lanes per row
+              const int grow = row_base + rr;
+              const bool ok = grow < M;
+              const int pos = __shfl_sync(0xffffffffu, pos_lane, rr);
+              const int slot = __shfl_sync(0xffffffffu, slot_lane, rr);
+              uint4 ra, rb;
+              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(ra.x), "=r"(ra.y), "=r"(ra.z), "=r"(ra.w)
+                           : "r"(stage + rr * 256 + ((l ^ (rr & 7)) << 4)) : "memory");
+              asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(rb.x), "=r"(rb.y), "=r"(rb.z), "=r"(rb.w)
+                           : "r"(stage + rr * 256 + (((l + 8) ^ (rr & 7)) << 4)) : "memory");
+              uint4 o1 = ra, o2 = rb;
+              if (is_q || is_k) {
+                const float4* cs = qk.cos_sin + (int64_t)pos * 32;
+                const float4 c0 = __ldg(cs + 2 * l), c1 = __ldg(cs + 2 * l + 1);
+                const float4 s0 = __ldg(cs + 16 + 2 * l), s1 = __ldg(cs + 16 + 2 * l + 1);
+                if (!ok) ra = rb = make_uint4(0, 0, 0, 0);
+                qk_norm_rope8(ra, rb, mask8, true, w_lo, w_hi, qk.eps, c0, c1, s0, s1, o1, o2);
+              }
+              if (ok) {
+                uint4* dst = reinterpret_cast<uint4*>(Cb + (int64_t)grow * ldc + head * 128);
+                dst[l] = o1;
+                dst[l + 8] = o2;
+                if (!is_q && slot >= 0) {
+                  const int kvh = is_k ? head - qk.nh : head - qk.nh - qk.kv;
+                  uint4* cdst = (is_k ? qk.k_cache : qk.v_cache) + ((int64_t)slot * qk.kv + kvh) * 16;
+                  cdst[l] = o1;
+                  cdst[l + 8] = o2;
+                }
+              }
+            }
+            __syncwarp();                       // the staging buffer is reused by the next head
+          }
+          ptx::tcgen05_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive_cluster(leader_tmem_empty0 + 8u * acc);
+          continue;
+        }
+      }
+      RowStage st = make_row_stage(smem_gen + cfg::kOffStage + q * cfg::kStageBuf, C, out_f32, epi, ldc,
                                    m_tile * kTileM + h * kHalf + q * 32, M, n_tile * NT, NT, N);
 #pragma unroll 1
       for (int c = 0; c < cfg::kChunks; c += 2) {       // two 16-column chunks per tensor-memory round trip
@@ -410,7 +490,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     if (tr && threadIdx.x == 64) trace[85] = clock64();
     if (warp >= 2) {
       const int row0 = m_tile * kTileM + h * kHalf + q * 32;          // first row of this warp
-      uint8_t* stage_buf = smem_gen + cfg::kOffStage + q * 4096;
+      uint8_t* stage_buf = smem_gen + cfg::kOffStage + q * cfg::kStageBuf;
       if (S == 2) pair_reduce<NT, 2>(ws_cluster, taddr, p, h, r, C, out_f32, epi, ldc, row0, M, n_tile * NT, N, stage_buf);
       else if (S == 3) pair_reduce<NT, 3>(ws_cluster, taddr, p, h, r, C, out_f32, epi, ldc, row0, M, n_tile * NT, N, stage_buf);
       else pair_reduce<NT, 4>(ws_cluster, taddr, p, h, r, C, out_f32, epi, ldc, row0, M, n_tile * NT, N, stage_buf);
@@ -465,7 +545,7 @@ int make_tma_packed(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t K
 
 template <int NT>
 int launch_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M, int N,
-                int K, int S, int epi, cudaStream_t stream, long long* trace, bool packed) {
+                int K, int S, int epi, cudaStream_t stream, long long* trace, bool packed, const QkEpi& qk = QkEpi{}) {
   using cfg = PairCfg<NT>;
   CUtensorMap ta, tb;
   int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, kHalf);
@@ -490,7 +570,7 @@ int launch_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, voi
   NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, gemm_pair_kernel<NT>, grid, dim3(kThreads), cfg::kSmemBytes, stream, 2 * S,
                                          ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, tiles, n_tiles,
                                          (M <= kTileM) ? 1 : 0, epi, reinterpret_cast<float4*>(ctx->gemm_ws), trace,
-                                         packed ? 1 : 0));
+                                         packed ? 1 : 0, qk));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -597,4 +677,52 @@ extern "C" int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc
 #undef X
   NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported pair tile width");
   return NVC_OK;
+}
+
+// K3 + K2 in one launch for the fused QKV projection of a prefill-sized step (src/models/qwen3.rs:205-234): returns
+// NVC_ENOTIMPL (nothing launched) when the shape does not take the persistent 256-wide schedule - the caller then runs
+// nvc_gemm_bf16 + nvc_qk_norm_rope_store.  N = (nh + 2 kv) * 128.
+extern "C" int nvc_gemm_pair_qk(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, nvc_bf16* C, int ldc, int M, int N,
+                                int K, const nvc_bf16* qw, const nvc_bf16* kw, float eps, const float* cos_sin,
+                                const int32_t* positions, const int32_t* slot_mapping, nvc_bf16* k_cache, nvc_bf16* v_cache,
+                                int nh, int kv, void* stream) {
+  if (M <= kTileM || N != (nh + 2 * kv) * 128 || K % BK != 0) return NVC_ENOTIMPL;
+  int nt = 256, S = 1;
+  choose_schedule(ctx, M, N, K / BK, &nt, &S);
+  if (nt != 256 || S != 1) return NVC_ENOTIMPL;
+  QkEpi qk;
+  qk.qw = reinterpret_cast<const uint4*>(qw);
+  qk.kw = reinterpret_cast<const uint4*>(kw);
+  qk.cos_sin = reinterpret_cast<const float4*>(cos_sin);
+  qk.positions = positions;
+  qk.slot_mapping = slot_mapping;
+  qk.k_cache = reinterpret_cast<uint4*>(k_cache);
+  qk.v_cache = reinterpret_cast<uint4*>(v_cache);
+  qk.eps = eps;
+  qk.nh = nh;
+  qk.kv = kv;
+  return launch_pair<256>(ctx, A, lda, W, C, ldc, 0, M, N, K, 1, NVC_EPI_QK_NORM_ROPE, nvc_stream(stream), nullptr, false, qk);
+}
+
+// Public form: the fused QKV projection followed by K2, one launch when the shape takes the persistent pair schedule
+// (prefill-sized M), the two-kernel sequence otherwise - the results are bit-identical either way.
+extern "C" int nvc_qkv_proj_norm_rope(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W_qkv, nvc_bf16* qkv, int M, int K,
+                                      const nvc_bf16* q_norm_w, const nvc_bf16* k_norm_w, float eps, const float* cos_sin,
+                                      const int32_t* positions, const int32_t* slot_mapping, nvc_bf16* k_cache,
+                                      nvc_bf16* v_cache, int nh, int kv, int hd, void* stream) {
+  NVC_REQUIRE(ctx, ctx && A && W_qkv && qkv && q_norm_w && k_norm_w && cos_sin && positions, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, slot_mapping == nullptr || (k_cache && v_cache), NVC_EINVAL, "slot_mapping without caches");
+  NVC_REQUIRE(ctx, hd == 128 && nh > 0 && kv > 0 && M >= 0, NVC_ESHAPE, "head_dim must be 128");
+  if (M == 0) return NVC_OK;
+  const int N = (nh + 2 * kv) * hd;
+  static const bool fused = !(getenv("NVC_QKV_FUSED") && atoi(getenv("NVC_QKV_FUSED")) == 0);
+  int rc = (fused && g_nvc_debug[7] != 1)
+               ? nvc_gemm_pair_qk(ctx, A, lda, W_qkv, qkv, N, M, N, K, q_norm_w, k_norm_w, eps, cos_sin, positions, slot_mapping,
+                                  k_cache, v_cache, nh, kv, stream)
+               : NVC_ENOTIMPL;
+  if (rc != NVC_ENOTIMPL) return rc;
+  rc = nvc_gemm_bf16(ctx, A, lda, W_qkv, qkv, N, NVC_DT_BF16, M, N, K, stream);
+  if (rc) return rc;
+  return nvc_qk_norm_rope_store(ctx, qkv, q_norm_w, k_norm_w, eps, cos_sin, positions, slot_mapping, k_cache, v_cache, M, nh, kv,
+                                hd, stream);
 }

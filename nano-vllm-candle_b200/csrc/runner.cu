@@ -131,10 +131,9 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
       if (rc) return rc;
     }
     xn_ready = false;
-    rc = nvc_gemm_bf16(ctx, r->xn, H, Ly.w_qkv, r->qkv, r->qkv_l, NVC_DT_BF16, N, r->qkv_l, H, st);
-    if (rc) return rc;
-    rc = nvc_qk_norm_rope_store(ctx, r->qkv, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos, r->d_slots,
-                                Ly.k_cache, Ly.v_cache, N, r->nh_l, r->kv_l, hd, st);
+    // QKV projection + q/k-norm + RoPE + KV scatter: one kernel at prefill sizes, GEMM + K2 otherwise (same bits)
+    rc = nvc_qkv_proj_norm_rope(ctx, r->xn, H, Ly.w_qkv, r->qkv, N, H, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos,
+                                r->d_slots, Ly.k_cache, Ly.v_cache, r->nh_l, r->kv_l, hd, st);
     if (rc) return rc;
     if (decode) {
       rc = nvc_paged_decode_attn_ex(ctx, r->qkv, r->qkv_l, Ly.k_cache, Ly.v_cache, r->d_bt, r->max_blocks_cap, blocks_hint,

@@ -198,6 +198,20 @@ class Context:
                                                N, nh, kv, hd, _stream()), "nvc_qk_norm_rope_store")
         return qkv
 
+    def qkv_proj_norm_rope(self, a, w_qkv, qw, kw, eps, cos_sin, positions, nh, kv, hd, slot_mapping=None, k_cache=None,
+                           v_cache=None, out=None):
+        """K3 + K2: qkv = a @ w_qkv.T with q / k heads normalised + rotated and k / v scattered to the caches (one kernel at
+        prefill sizes)."""
+        _req(a, BF16, "a"); _req(w_qkv, BF16, "w_qkv"); _req(positions, torch.int32, "positions")
+        M, K = a.shape
+        N = (nh + 2 * kv) * hd
+        assert w_qkv.shape == (N, K) and w_qkv.is_contiguous() and a.stride(1) == 1
+        out = torch.empty((M, N), dtype=BF16, device=a.device) if out is None else out
+        self._ck(self.l.nvc_qkv_proj_norm_rope(self.h, _ptr(a), a.stride(0), _ptr(w_qkv), _ptr(out), M, K, _ptr(qw), _ptr(kw),
+                                               float(eps), _ptr(cos_sin), _ptr(positions), _ptr(slot_mapping), _ptr(k_cache),
+                                               _ptr(v_cache), nh, kv, hd, _stream()), "nvc_qkv_proj_norm_rope")
+        return out
+
     def store_kvcache(self, k, v, k_cache, v_cache, slot_mapping, kv, hd):
         _req(k, BF16, "k"); _req(slot_mapping, torch.int32, "slot_mapping")
         N = k.shape[0]

@@ -108,6 +108,55 @@ def test_gemm_bf16(ctx, M, N, K, bn, splits, out_dtype):
     _close(out, ref, 2e-3, rtol, f"gemm M={M} N={N} K={K} bn={bn} s={splits} {out_dtype}")
 
 
+@pytest.mark.parametrize("M,nh,kv,K", [
+    (1500, 16, 8, 1024),      # 0.6B qkv at a prefill size: 6 m-tiles (last one ragged) x 16 tiles of two heads
+    (32768, 16, 8, 1024),     # the bench's prefill step
+    (2048, 5, 1, 512),        # 7 heads = 896 columns: the last 256-column tile holds one head
+    (700, 32, 8, 4096),       # 8B shape, M not a multiple of 128
+    (300, 4, 2, 256),         # few tiles: whatever schedule the library picks, the results must not change
+    (64, 16, 8, 1024),        # decode-sized: the two-kernel path
+])
+def test_qkv_proj_norm_rope_fused(ctx, nvc, M, nh, kv, K):
+    """K3 + K2 as one kernel (the QKV GEMM's persistent epilogue applies the q/k-norm, RoPE and the KV scatter) against
+    the two-kernel sequence on the same operands: qkv rows and both caches bit-identical; and against the oracle
+    (qwen3.rs:205-234, rotary_embedding.rs:82-107) through the existing K2 reference."""
+    hd, bs, theta, eps = 128, 16, 1e6, 1e-6
+    g = torch.Generator().manual_seed(M + nh + K)
+    N = (nh + 2 * kv) * hd
+    a = torch.randn(M, K, generator=g).to(BF16).cuda()
+    w = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(BF16).cuda()
+    qw = (1 + 0.2 * torch.randn(hd, generator=g)).to(BF16).cuda()
+    kw = (1 + 0.2 * torch.randn(hd, generator=g)).to(BF16).cuda()
+    pos = torch.randint(0, 4000, (M,), generator=g, dtype=torch.int32).cuda()
+    nslots = ((M + bs - 1) // bs + 2) * bs
+    slots = torch.randperm(nslots, generator=g)[:M].to(torch.int32)
+    if M > 2:
+        slots[1] = -1                                         # skipped token
+    slots = slots.cuda()
+    tab = ctx.rope_table(theta, hd, 4096)
+    res = {}
+    for fused in (0, 1):
+        nvc.lib().nvc_debug_set(7, 0 if fused else 1)
+        try:
+            kc = torch.zeros(nslots, kv, hd, dtype=BF16, device="cuda")
+            vc = torch.zeros_like(kc)
+            qkv = ctx.qkv_proj_norm_rope(a, w, qw, kw, eps, tab, pos, nh, kv, hd, slot_mapping=slots, k_cache=kc, v_cache=vc)
+            torch.cuda.synchronize()
+            res[fused] = (qkv, kc, vc)
+        finally:
+            nvc.lib().nvc_debug_set(7, 0)
+    for name, x, y in zip(("qkv", "k_cache", "v_cache"), res[0], res[1]):
+        assert torch.equal(x.view(torch.int16), y.view(torch.int16)), f"fused QKV epilogue: {name} differs from GEMM + K2"
+    # oracle: linear, then per-head rmsnorm + rope on the bf16 projection
+    from test_kernels_gpu import _rope_ref
+    proj = ctx.gemm(a, w).cpu()
+    q_ref, k_ref = _rope_ref(proj, qw.cpu(), kw.cpu(), eps, pos.cpu(), nh, kv, hd, theta)
+    got = res[1][0].cpu()
+    _close(got[:, :nh * hd].reshape(M, nh, hd), q_ref, 1e-5, 2 ** -7, f"fused qkv epilogue q M={M}")
+    _close(got[:, nh * hd:(nh + kv) * hd].reshape(M, kv, hd), k_ref, 1e-5, 2 ** -7, f"fused qkv epilogue k M={M}")
+    assert torch.equal(got[:, (nh + kv) * hd:], proj[:, (nh + kv) * hd:]), "v columns must be the projection itself"
+
+
 def test_gemm_reference_goldens(ctx):
     """src/layers/linear.rs:231-267 (replicated, exact small integers; bias added on the host
     here since the Qwen3 path has no biases) and :274-319 (two hand-sharded column ranks),

@@ -96,10 +96,14 @@ class ClockSampler:
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, device: int):
-        self.device, self.proc, self.lines = device, None, []
+    def __init__(self, devices):
+        # `devices`: one index or a comma-separated list ("0,1,...": ONE nvidia-smi client for all the GPUs of the run - eight
+        # per-rank pollers contended for the driver and stretched the host side of the TP steps); None: this rank does not sample
+        self.device, self.proc, self.lines = devices, None, []
 
     def start(self):
+        if self.device is None:
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "200"],
@@ -330,14 +334,16 @@ def measure(env: _Env, model: str, batch: int, prompt_len: int, K: int, W: int, 
             break
     env.barrier()
     t_prefill = time.perf_counter() - t0
+    # clocks: rank 0 polls every GPU of the run from one nvidia-smi client, started before the warm-up so that its start-up
+    # is not inside the timed region
+    sampler = ClockSampler(",".join(str(i) for i in range(env.world)) if env.rank == 0 else None)
+    sampler.start()
     # ---- warm-up decode steps (also captures the CUDA graph)
     for _ in range(W):
         s = engine.step()
         assert not s.is_prefill
     # ---- e2e: K decode steps through the public API, host buffers, H2D + D2H inside
-    sampler = ClockSampler(env.local)
     env.barrier()
-    sampler.start()
     t0 = time.perf_counter()
     for _ in range(K):
         engine.step()

@@ -40,23 +40,19 @@ constexpr int kTmemCols = 512;
 constexpr int kRingBudget = 200 * 1024;
 
 // Tile width NT.  NT = 256: one MMA (N = 256) per k-step, two accumulator stages (persistent
-// schedule overlaps the epilogue).  NT in (256, 512]: two MMAs of N = NT/2 per k-step into
-// tensor-memory columns [0, NT/2) and [256, 256 + NT/2), one accumulator stage - used when a
-// decode GEMM has between #pairs and 2 x #pairs 256-wide tiles, so that wider tiles finish in ONE
-// wave (Qwen3-8B gate_up at batch 256: 96 tiles of 256 -> 70 tiles of 352 on 74 pairs).
-// NT in [128, 256): one narrower MMA per k-step, two accumulator stages - more, smaller tiles when
-// 256-wide ones quantise badly onto the 74 pairs (96 tiles = two waves of which the second is 30 %
-// full; 128 tiles of 192 = two full waves of 3/4 the work each).
+// schedule overlaps the epilogue).  NT in [128, 256): one narrower MMA per k-step, two accumulator stages - more,
+// smaller tiles when 256-wide ones quantise badly onto the 74 pairs (96 tiles = two waves of which the second is 30 %
+// full; 128 tiles of 192 = two full waves of 3/4 the work each).  (Wide tiles, NT in (256, 512] as two MMAs per k-step
+// into one accumulator stage, measured no gain - 8B gate_up at batch 256: 53.1 vs 53.6 us - and were deleted in round 2.)
 template <int NT>
 struct PairCfg {
-  static_assert(NT >= 128 && NT <= 512 && NT % 32 == 0, "tile width");
-  static constexpr bool kTwo = NT > 256;
-  static constexpr int NH = kTwo ? NT / 2 : NT;          // N of one tcgen05.mma
+  static_assert(NT >= 128 && NT <= 256 && NT % 32 == 0, "tile width");
+  static constexpr int NH = NT;                          // N of one tcgen05.mma
   static constexpr int kBoxRowsB = NH / 2;               // rows of W one CTA supplies per MMA (multiple of 8)
   static constexpr int kBytesB = (NT / 2) * BK * 2;      // this CTA's rows of the weight tile per k-block
   static constexpr int kStageBytes = kBytesA + kBytesB;
   static constexpr int kStages = kRingBudget / kStageBytes < 6 ? kRingBudget / kStageBytes : 6;
-  static constexpr int kAccStages = kTwo ? 1 : 2;
+  static constexpr int kAccStages = 2;
   static constexpr int kNumBars = 2 * kStages + 4;       // full[], empty[], tmem_full[2], tmem_empty[2]
   static constexpr int kOffStage = (kStages * kStageBytes + kNumBars * 8 + 16 + 127) & ~127;   // 4 epilogue warps x row staging
   // 4 KB per warp (32 rows x 128 B, RowStage); 8 KB for 256-wide tiles, whose QK-norm epilogue parks whole heads (32 rows x 256 B)
@@ -68,7 +64,7 @@ struct PairCfg {
   static_assert(kStageBytes % 1024 == 0 && (kBoxRowsB % 8) == 0, "swizzle atoms");
   // tensor-memory column of accumulator chunk c (accumulator stage 0)
   __device__ static constexpr uint32_t chunk_col(int c) {
-    return kTwo && c * 16 >= NH ? (uint32_t)(256 + c * 16 - NH) : (uint32_t)(c * 16);
+    return (uint32_t)(c * 16);
   }
 };
 
@@ -82,17 +78,6 @@ __device__ __forceinline__ void tma_load_2d_pair(uint32_t smem_dst, const CUtens
   asm volatile(
       "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(leader_bar), "r"(c0), "r"(c1) : "memory");
-}
-// 4-D forms for atom-packed weights (see launch_pair): coordinates {k in block, row in atom, k-block, atom row}
-__device__ __forceinline__ void tma_load_4d_pair(uint32_t smem_dst, const CUtensorMap* m, uint32_t leader_bar,
-                                                 int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
-  asm volatile(
-      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];"
-      ::"r"(smem_dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(leader_bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
-}
-__device__ __forceinline__ void tma_prefetch_l2_4d(const CUtensorMap* m, int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
-  asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];"
-               ::"l"(reinterpret_cast<uint64_t>(m)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
 __device__ __forceinline__ void tmem_alloc_pair(uint32_t smem_dst, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_dst), "r"(ncols) : "memory");
@@ -202,7 +187,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                  void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total, int kb_per_split,
                  int num_tiles, int n_tiles, int prefetch_w, int epi, float4* __restrict__ ws,
-                 long long* __restrict__ trace, int w_packed, const QkEpi qk) {
+                 long long* __restrict__ trace, const QkEpi qk) {
   using cfg = PairCfg<NT>;
   constexpr int kStages = cfg::kStages;
   constexpr int kStageBytes = cfg::kStageBytes;
@@ -272,10 +257,9 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
       const int n = min(num_kb, kPrefetchKb);
       for (int kb = 0; kb < n; ++kb) {
 #pragma unroll
-        for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i) {
+        for (int i = 0; i < 1; ++i) {
           const int row = n_tile * NT + i * cfg::NH + h * cfg::kBoxRowsB;
-          if (w_packed) tma_prefetch_l2_4d(&tma_b, 0, 0, kb_begin + kb, row >> 3);
-          else ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, row);
+          ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb) * BK, row);
         }
       }
     }
@@ -301,16 +285,14 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           const int k0 = (kb_begin + kb) * BK;
           tma_load_2d_pair(dst, &tma_a, leader_full0 + 8u * s, k0, a_row);
 #pragma unroll
-          for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i) {   // this CTA's rows of each MMA's weight tile
+          for (int i = 0; i < 1; ++i) {   // this CTA's rows of each MMA's weight tile
             const uint32_t bdst = dst + kBytesA + i * (cfg::kBoxRowsB * BK * 2);
-            if (w_packed) tma_load_4d_pair(bdst, &tma_b, leader_full0 + 8u * s, 0, 0, kb_begin + kb, (b_row + i * cfg::NH) >> 3);
-            else tma_load_2d_pair(bdst, &tma_b, leader_full0 + 8u * s, k0, b_row + i * cfg::NH);
+            tma_load_2d_pair(bdst, &tma_b, leader_full0 + 8u * s, k0, b_row + i * cfg::NH);
           }
           if (prefetch_w && kb + kPrefetchKb < num_kb) {
 #pragma unroll
-            for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i) {
-              if (w_packed) tma_prefetch_l2_4d(&tma_b, 0, 0, kb_begin + kb + kPrefetchKb, (b_row + i * cfg::NH) >> 3);
-              else ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb + kPrefetchKb) * BK, b_row + i * cfg::NH);
+            for (int i = 0; i < 1; ++i) {
+              ptx::tma_prefetch_l2_2d(&tma_b, (kb_begin + kb + kPrefetchKb) * BK, b_row + i * cfg::NH);
             }
           }
           if (tr && it < 32) trace[3 + it] = clock64();
@@ -326,7 +308,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     uint32_t it = 0;
     int ti = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
-      const int acc = cfg::kTwo ? 0 : (ti & 1), use = cfg::kTwo ? ti : (ti >> 1);
+      const int acc = ti & 1, use = ti >> 1;
       ptx::mbar_wait(tmem_empty_bar(acc), (use & 1) ^ 1u);    // both CTAs' epilogues drained this accumulator
       ptx::tcgen05_fence_after();
       const uint32_t d = tmem_base + (uint32_t)(acc * 256);
@@ -341,7 +323,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
 #pragma unroll
-            for (int i = 0; i < (cfg::kTwo ? 2 : 1); ++i)
+            for (int i = 0; i < 1; ++i)
               umma_bf16_ss_pair(d + (uint32_t)(i * 256), ptx::umma_desc(a_lo + 2 * k, desc_hi),
                                 ptx::umma_desc(b_lo + i * ((cfg::kBoxRowsB * BK * 2) >> 4) + 2 * k, desc_hi), idesc,
                                 (kb | k) != 0 ? 1u : 0u);
@@ -362,7 +344,7 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
     int ti = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters, ++ti) {
       const int m_tile = tile / n_tiles, n_tile = tile - m_tile * n_tiles;
-      const int acc = cfg::kTwo ? 0 : (ti & 1), use = cfg::kTwo ? ti : (ti >> 1);
+      const int acc = ti & 1, use = ti >> 1;
       const int grow = m_tile * kTileM + h * kHalf + r;
       const bool row_ok = grow < M;
       ptx::mbar_wait(tmem_full_bar(acc), use & 1);
@@ -522,36 +504,16 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
   return NVC_OK;
 }
 
-#define NVC_PAIR_WIDTHS(X) X(128) X(160) X(192) X(224) X(256) X(320) X(352) X(384) X(448) X(512)
-
-// Atom-packed weights: W[N, K] stored as [N/8][K/64][8][64], i.e. every 8-row x 128-byte swizzle atom
-// (1 KB) is contiguous in HBM instead of eight 128-byte pieces K*2 bytes apart.  A TMA box of R rows of
-// one k-block is R/8 contiguous kilobytes spaced (K/64) KB apart; it lands in shared memory exactly
-// like the 2-D box [R][64] of the row-major layout.
-int make_tma_packed(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t K, uint64_t N, uint32_t box_rows) {
-  cuuint64_t gdim[4] = {64, 8, K / 64, N / 8};
-  cuuint64_t gstr[3] = {128, 1024, (K / 64) * 1024};
-  cuuint32_t box[4] = {64, 8, 1, box_rows / 8};
-  cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = ctx->encode_tiled(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstr, box,
-                                 estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) {
-    nvc_set_error(ctx, "cuTensorMapEncodeTiled (packed weights) failed with CUresult " + std::to_string((int)r));
-    return NVC_EINVAL;
-  }
-  return NVC_OK;
-}
+#define NVC_PAIR_WIDTHS(X) X(128) X(160) X(192) X(224) X(256)
 
 template <int NT>
 int launch_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M, int N,
-                int K, int S, int epi, cudaStream_t stream, long long* trace, bool packed, const QkEpi& qk = QkEpi{}) {
+                int K, int S, int epi, cudaStream_t stream, long long* trace, const QkEpi& qk = QkEpi{}) {
   using cfg = PairCfg<NT>;
   CUtensorMap ta, tb;
   int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, kHalf);
   if (rc) return rc;
-  rc = packed ? make_tma_packed(ctx, &tb, W, (uint64_t)K, (uint64_t)N, cfg::kBoxRowsB)
-              : make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, cfg::kBoxRowsB);
+  rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, cfg::kBoxRowsB);
   if (rc) return rc;
   const int kb_total = K / BK;
   const int m_tiles = (M + kTileM - 1) / kTileM, n_tiles = (N + NT - 1) / NT;
@@ -570,7 +532,7 @@ int launch_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, voi
   NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, gemm_pair_kernel<NT>, grid, dim3(kThreads), cfg::kSmemBytes, stream, 2 * S,
                                          ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, tiles, n_tiles,
                                          (M <= kTileM) ? 1 : 0, epi, reinterpret_cast<float4*>(ctx->gemm_ws), trace,
-                                         packed ? 1 : 0, qk));
+                                         qk));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;
@@ -655,24 +617,20 @@ static void choose_schedule(const nvc_ctx* ctx, int M, int N, int kb, int* nt_ou
     const double t = S == 1 ? waves * kbs * 560.0 + 10000.0 : waves * (kbs * 600.0 + 12000.0);
     if (t < best * 0.98) { best = t; best_s = S; best_nt = 256; }
   }
-  // Wide tiles (NT > 256, one wave instead of two for 75..148 tiles) are NOT chosen automatically: measured on
-  // Qwen3-8B gate_up at batch 256 (N 24576: 70 tiles of 352) 53.1 us vs 53.6 us for two waves of 256-wide tiles;
-  // the single accumulator stage exposes the 11k-cycle epilogue.  They stay selectable and tested.
   *nt_out = best_nt;
   *s_out = best_s;
 }
 
-// force_splits: 0 = choose; 1..4 = in-cluster split-K factor with 256-wide tiles; 1000 + NT = one-wave wide tiles
+// force_splits: 0 = choose; 1..4 = in-cluster split-K factor with 256-wide tiles; 10000 * S + 1000 + NT = tile width NT
 extern "C" int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32,
                              int M, int N, int K, int force_splits, int epi, void* stream, long long* trace) {
-  const bool packed = g_nvc_debug[2] == 1;   // experiment: W is atom-packed (make_tma_packed)
   // force_splits >= 1000: 10000 * S + 1000 + NT (S omitted = 1)
   int nt = 256, S = 1;
   if (force_splits >= 1000) { nt = force_splits % 10000 - 1000; S = force_splits / 10000; S = S < 1 ? 1 : (S > 4 ? 4 : S); }
   else if (force_splits > 0) { S = force_splits > 4 ? 4 : force_splits; }
   else choose_schedule(ctx, M, N, K / BK, &nt, &S);
 #define X(NT) \
-  if (nt == NT) return launch_pair<NT>(ctx, A, lda, W, C, ldc, out_f32, M, N, K, S, epi, nvc_stream(stream), trace, packed);
+  if (nt == NT) return launch_pair<NT>(ctx, A, lda, W, C, ldc, out_f32, M, N, K, S, epi, nvc_stream(stream), trace);
   NVC_PAIR_WIDTHS(X)
 #undef X
   NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported pair tile width");
@@ -701,7 +659,7 @@ extern "C" int nvc_gemm_pair_qk(nvc_ctx* ctx, const nvc_bf16* A, int lda, const 
   qk.eps = eps;
   qk.nh = nh;
   qk.kv = kv;
-  return launch_pair<256>(ctx, A, lda, W, C, ldc, 0, M, N, K, 1, NVC_EPI_QK_NORM_ROPE, nvc_stream(stream), nullptr, false, qk);
+  return launch_pair<256>(ctx, A, lda, W, C, ldc, 0, M, N, K, 1, NVC_EPI_QK_NORM_ROPE, nvc_stream(stream), nullptr, qk);
 }
 
 // Public form: the fused QKV projection followed by K2, one launch when the shape takes the persistent pair schedule

@@ -138,146 +138,6 @@ p2p_allreduce_rmsnorm_kernel(uint8_t* const* __restrict__ peers, uint32_t* __res
   }
 }
 
-
-// Two-shot variant for wide TP / large messages.  One-shot makes every rank read all tp partial
-// copies of every row (tp x message bytes over NVLink per rank: 39 us for 2 MB at TP = 8, 360 GB/s);
-// here rank r sums only ITS block of rows (reduce-scatter by peer loads: 1 x message bytes in),
-// pushes the bf16 sums into every rank's gather buffer (all-gather by peer stores: 1 x message
-// bytes out), and after a second flag barrier every rank applies residual add + RMSNorm to all
-// rows from its local gather buffer.  Same launch, same epoch protocol; grid = N rows, the CTAs
-// with the lowest indices do the reduce-scatter step (they are dispatched first, so a grid larger
-// than one wave cannot dead-lock on the second barrier).
-__device__ __forceinline__ void st_peer_u4(void* p, const uint4& v) {
-  asm volatile("st.global.relaxed.sys.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
-}
-
-template <int TP>
-__global__ void __launch_bounds__(1024)
-p2p_allreduce2_rmsnorm_kernel(uint8_t* const* __restrict__ peers, uint32_t* __restrict__ state, int my_rank,
-                              size_t slot_off, size_t gather_off, const float4* __restrict__ res_in,
-                              float4* __restrict__ res_out, const uint4* __restrict__ w, float eps,
-                              uint4* __restrict__ out, int H, int N) {
-  __shared__ float red[32];
-  __shared__ uint32_t s_epoch;
-  pdl_trigger();
-  pdl_wait();                                  // this rank's GEMM has completed and flushed
-  if (threadIdx.x == 0) s_epoch = state[0] + 1;
-  __syncthreads();
-  const uint32_t e = s_epoch;
-  const int per = (N + TP - 1) / TP;           // rows per rank in the reduce-scatter step
-  const int row0 = my_rank * per;
-  const int my_rows = max(0, min(N, row0 + per) - row0);
-  const int nvec = H >> 3;
-  const int v = threadIdx.x;
-  if (blockIdx.x == 0 && threadIdx.x < TP) {
-    st_release_sys(reinterpret_cast<uint32_t*>(peers[threadIdx.x]) + my_rank, e);            // barrier 1: my partial is complete
-    if (my_rows == 0) st_release_sys(reinterpret_cast<uint32_t*>(peers[threadIdx.x]) + 16 + my_rank, e);   // nothing to push
-  }
-  if ((int)blockIdx.x < my_rows) {
-    if (threadIdx.x < TP) {
-      const uint32_t* flag = reinterpret_cast<const uint32_t*>(peers[my_rank]) + threadIdx.x;
-      unsigned spins = 0;
-      while ((int32_t)(ld_acquire_sys(flag) - e) < 0) {
-        if (++spins > kSpinLimit) {
-          printf("nvc: p2p all-reduce (two-shot) timed out waiting for the partial of rank %d (epoch %u)\n", (int)threadIdx.x, e);
-          __trap();
-        }
-      }
-    }
-    __syncthreads();
-    const int row = row0 + (int)blockIdx.x;
-    if (v < nvec) {
-      uint4 part[TP];
-#pragma unroll
-      for (int p = 0; p < TP; ++p) part[p] = ld_peer_u4(peers[p] + slot_off + ((size_t)row * nvec + v) * 16);
-      float s[8];
-#pragma unroll
-      for (int i = 0; i < 8; ++i) s[i] = 0.f;
-#pragma unroll
-      for (int p = 0; p < TP; ++p) {           // fixed rank order
-        float f[8];
-        unpack8(part[p], f);
-#pragma unroll
-        for (int i = 0; i < 8; ++i) s[i] += f[i];
-      }
-      const uint4 pk = pack8(s);
-#pragma unroll
-      for (int p = 0; p < TP; ++p) st_peer_u4(peers[p] + gather_off + ((size_t)row * nvec + v) * 16, pk);
-    }
-    __syncthreads();                           // every thread's pushes precede thread 0's fence + count (cumulativity)
-    if (threadIdx.x == 0) {
-      __threadfence_system();
-      const uint32_t done = atomicAdd(&state[2], 1u);
-      if (done == (uint32_t)my_rows - 1) {
-        state[2] = 0;
-        __threadfence_system();
-        for (int p = 0; p < TP; ++p) st_release_sys(reinterpret_cast<uint32_t*>(peers[p]) + 16 + my_rank, e);   // barrier 2: my rows are everywhere
-      }
-    }
-  }
-  if (threadIdx.x < TP) {
-    const uint32_t* flag = reinterpret_cast<const uint32_t*>(peers[my_rank]) + 16 + threadIdx.x;
-    unsigned spins = 0;
-    while ((int32_t)(ld_acquire_sys(flag) - e) < 0) {
-      if (++spins > kSpinLimit) {
-        printf("nvc: p2p all-reduce (two-shot) timed out waiting for the rows of rank %d (epoch %u)\n", (int)threadIdx.x, e);
-        __trap();
-      }
-    }
-  }
-  __syncthreads();
-
-  const int row = blockIdx.x;
-  float s[8];
-  float ss = 0.f;
-  if (v < nvec) {
-    unpack8(ld_peer_u4(peers[my_rank] + gather_off + ((size_t)row * nvec + v) * 16), s);   // written by peers: bypass L1
-    if (w != nullptr) {
-      const int64_t o = ((int64_t)row * nvec + v) * 2;
-      if (res_in) {
-        const float4 a = res_in[o], b = res_in[o + 1];
-        s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
-        s[4] += b.x; s[5] += b.y; s[6] += b.z; s[7] += b.w;
-      }
-      if (res_out) {
-        res_out[o] = make_float4(s[0], s[1], s[2], s[3]);
-        res_out[o + 1] = make_float4(s[4], s[5], s[6], s[7]);
-      }
-#pragma unroll
-      for (int i = 0; i < 8; ++i) ss += s[i] * s[i];
-    }
-  }
-  if (w != nullptr) {
-    ss = warp_sum(ss);
-    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-    if (lane == 0) red[wid] = ss;
-    __syncthreads();
-    const int nw = (blockDim.x + 31) >> 5;
-    float tot = (lane < nw) ? red[lane] : 0.f;
-    tot = warp_sum(tot);
-    const float rstd = 1.0f / sqrtf(tot / (float)H + eps);
-    if (v < nvec) {
-      float wf[8];
-      unpack8(__ldg(w + v), wf);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) s[i] = s[i] * rstd * wf[i];
-    }
-  }
-  if (v < nvec) out[(int64_t)row * nvec + v] = pack8(s);
-
-  // the last CTA to finish publishes the epoch for the next call
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    __threadfence();
-    const uint32_t done = atomicAdd(&state[1], 1u);
-    if (done == gridDim.x - 1) {
-      state[1] = 0;
-      __threadfence();
-      state[0] = e;
-    }
-  }
-}
-
 }  // namespace
 
 void nvc_p2p_destroy(nvc_ctx* ctx) {
@@ -298,7 +158,7 @@ extern "C" int nvc_ctx_p2p_export(nvc_ctx* ctx, size_t slot_bytes, void* handle_
   NVC_REQUIRE(ctx, slot_bytes > 0 && slot_bytes % 256 == 0, NVC_EINVAL, "slot_bytes must be a multiple of 256");
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t size");
   NVC_CUDA_CHECK(ctx, cudaSetDevice(ctx->device));
-  const size_t total = kFlagBytes + 3 * slot_bytes;      // flags | slot 0 | slot 1 | gather buffer of the two-shot kernel
+  const size_t total = kFlagBytes + 2 * slot_bytes;      // flags | slot 0 | slot 1
   NVC_CUDA_CHECK(ctx, cudaMalloc(&ctx->p2p_local, total));
   NVC_CUDA_CHECK(ctx, cudaMemset(ctx->p2p_local, 0, total));
   NVC_CUDA_CHECK(ctx, cudaMalloc(&ctx->p2p_state, 4 * sizeof(uint32_t)));      // epoch, CTAs done, rows pushed
@@ -348,29 +208,8 @@ extern "C" int nvc_p2p_allreduce_rmsnorm(nvc_ctx* ctx, int slot, const float* re
   const size_t off = kFlagBytes + (size_t)slot * ctx->p2p_slot_bytes;
   const int threads = ((H / 8 + 31) / 32) * 32;
   cudaStream_t st = nvc_stream(stream);
-  // NVC_P2P_MODE=2 selects the two-shot kernel.  Measured on 8 x B200 its second flag
-  // barrier costs more than the NVLink bytes it saves (TP 8, 2 MB: 44 us vs 39 us one-shot; 128 KB: far worse),
-  // so one-shot stays the default at every size.
-  static const int mode_env = getenv("NVC_P2P_MODE") ? atoi(getenv("NVC_P2P_MODE")) : 0;
-  const bool two_shot = mode_env == 2;
-  if (two_shot) {
-    const size_t goff = kFlagBytes + 2 * ctx->p2p_slot_bytes;
-#define NVC_AR2(TPV)                                                                                             \
-  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, p2p_allreduce2_rmsnorm_kernel<TPV>, dim3(N), dim3(threads), 0, st,         \
-                                 (uint8_t* const*)ctx->p2p_peer_d, ctx->p2p_state, ctx->tp_rank, off, goff,      \
-                                 reinterpret_cast<const float4*>(residual_in), reinterpret_cast<float4*>(residual_out), \
-                                 reinterpret_cast<const uint4*>(w), eps, reinterpret_cast<uint4*>(out), H, N))
-    switch (ctx->tp_size) {
-      case 2: NVC_AR2(2); break;
-      case 4: NVC_AR2(4); break;
-      case 8: NVC_AR2(8); break;
-      default: NVC_REQUIRE(ctx, false, NVC_ESHAPE, "peer all-reduce supports tp_size 2, 4, 8");
-    }
-#undef NVC_AR2
-    NVC_CUDA_CHECK(ctx, cudaGetLastError());
-    ctx->launches++;
-    return NVC_OK;
-  }
+  // (a two-shot variant - reduce-scatter by peer loads, all-gather by peer stores, second flag barrier - measured slower at
+  // every size on 8 x B200, 44 vs 39 us for 2 MB, and was deleted in round 2; large messages go through the switch, nvls_allreduce.cu)
 #define NVC_AR(TPV)                                                                                              \
   NVC_CUDA_CHECK(ctx, nvc_launch(ctx, p2p_allreduce_rmsnorm_kernel<TPV>, dim3(N), dim3(threads), 0, st,          \
                                  (uint8_t* const*)ctx->p2p_peer_d, ctx->p2p_state, ctx->tp_rank, off,            \

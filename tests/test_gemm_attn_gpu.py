@@ -71,14 +71,6 @@ GEMM_SHAPES = [
     (256, 512, 64, 512, 4),        # more splits than k-blocks: clamps to 1
     (256, 4096, 4096, 512, 0),     # auto split choice
     (512, 151936 // 8, 1024, 512, 0),   # lm_head shard, ragged last n-tile
-    # wide pair tiles (two MMAs of N = NT/2 per k-step, one accumulator stage): force_splits = 1000 + NT
-    (256, 1056, 256, 512, 1352),   # 3 tiles of 352
-    (256, 704, 512, 512, 1320),    # NT = 320, ragged last tile
-    (300, 2000, 192, 512, 1512),   # NT = 512, ragged M and N
-    (512, 768, 320, 512, 1384),    # NT = 384, two m-tiles
-    (256, 896, 1024, 512, 1448),   # NT = 448, ring wraps
-    (4096, 4096, 128, 512, 1512),  # 128 wide tiles: two per cluster through the single accumulator stage
-    (256, 24576, 4096, 512, 1352), # 8B gate_up at batch 256: 70 tiles, one wave
     (256, 24576, 4096, 0, 0),      # the same through the schedule choice
     # narrow pair tiles (one MMA of N = NT < 256, two accumulator stages): force_splits = 10000 * S + 1000 + NT
     (256, 1536, 512, 512, 1192),   # 8 tiles of 192
@@ -187,7 +179,6 @@ SILU_SHAPES = [
     (256, 12288, 4096, 0, 0),      # 8B gate_up at batch 256 (pair kernel, schedule chosen)
     (256, 1600, 1024, 512, 2),     # pair kernel, split-K 2 (32B/TP8-like shard), ragged last tile
     (300, 512, 448, 512, 3),       # pair kernel, split-K 3, ragged M
-    (256, 704, 256, 512, 1352),    # wide pair tile: unit straddles the two accumulators
     (2048, 3072, 1024, 0, 0),      # prefill-sized, persistent pair schedule
     (256, 12288, 4096, 512, 1192), # 8B gate_up at batch 256 on 192-wide pair tiles (6 gate/up groups per tile)
     (256, 880, 256, 512, 21160),   # NT = 160 (5 units), split 2, ragged last tile

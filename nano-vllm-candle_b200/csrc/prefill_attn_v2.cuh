@@ -293,35 +293,6 @@ prefill_attn_v2_kernel(const __grid_constant__ CUtensorMap tma_q, const __grid_c
         const uint32_t s_addr = tmem_s + (gi & 1) * kKT + lane_addr;
         ptx::mbar_wait(s_full(gi & 1), (gi >> 1) & 1);
         ptx::tcgen05_fence_after();
-        // a diagonal tile whose first key lies past the position of this warp's LAST row (rows 0..63 of the second diagonal
-        // tile of a q tile): every probability of the warp's 32 rows is 0 - store zeros, skip the pass (half of that tile's
-        // softmax work, 10 % of all of it at T = 512)
-        if (j * kKT > ge.q0 + quad * 32 + 31) {
-          uint32_t z[kKT / 2];
-#pragma unroll
-          for (int i = 0; i < kKT / 2; ++i) z[i] = 0u;
-          if (j > 0) ptx::mbar_wait(o_full, (gi - 1) & 1);     // every o_full phase is observed (see below)
-          ptx::tmem_st_32x32b_x32(s_addr, z);
-          ptx::tmem_st_wait();
-          if constexpr (kPaged) {
-            if (j * kKT + kKT > ge.kv_len) {                   // same duty as below: V rows past the context hold anything
-              const int vs = (int)(gi % kVStages);
-              ptx::mbar_wait(v_full(vs), (gi / kVStages) & 1);
-              if (r < kKT && j * kKT + r >= ge.kv_len) {
-                uint8_t* v_row = gen + kOffV + vs * kKBytes + r * 128;
-#pragma unroll
-                for (int k16 = 0; k16 < 8; ++k16) {
-                  *reinterpret_cast<uint4*>(v_row + (k16 << 4)) = make_uint4(0, 0, 0, 0);
-                  *reinterpret_cast<uint4*>(v_row + kHalfKV + (k16 << 4)) = make_uint4(0, 0, 0, 0);
-                }
-              }
-              ptx::fence_proxy_async_smem();
-            }
-          }
-          ptx::tcgen05_fence_before();
-          ptx::mbar_arrive(p_full);
-          continue;
-        }
         uint32_t sv[kKT];
         ptx::tmem_ld_32x32b_x32(s_addr, sv);
         ptx::tmem_ld_32x32b_x32(s_addr + 32, sv + 32);

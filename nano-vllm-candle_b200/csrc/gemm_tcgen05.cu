@@ -34,26 +34,17 @@ constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int kThreads = 192;
 constexpr int kEpilogueThreads = 128;
+constexpr int kSmemBudget = 200 * 1024;
 
-// AR: rows of shared memory reserved per A sub-tile.  128 = a full m-tile.  64 (decode, M <= 64): the MMA still reads 128
-// rows - rows 64..127 are whatever follows in the ring, and their accumulator rows are never stored - but a stage is
-// 1/3 - 2/5 smaller, and with the ring capped at 100 KB two consecutive decode GEMMs (gate_up -> down) fit on one SM
-// together: the second one's prologue and its first lap of weights then really overlap the first one's run (PDL).
-// AR = 63: 64 rows with the full 200 KB ring (deeper ring instead of co-residency; measured against AR = 64).
-template <int BN, int KPS, int AR = 128>
+template <int BN, int KPS>
 struct Cfg {
-  static constexpr int kRowsA = AR == 128 ? 128 : 64;
-  static constexpr int kSmemBudget = AR == 64 ? (BN >= 64 ? 128 * 1024 : 100 * 1024) : 200 * 1024;
-  static constexpr int kBytesA = kRowsA * BK * 2;             // one A sub-tile
+  static constexpr int kBytesA = BM * BK * 2;                 // one A sub-tile
   static constexpr int kBytesB = BN * BK * 2;                 // one W sub-tile
   static constexpr int kStageBytes = KPS * (kBytesA + kBytesB);
   static constexpr int kStages = kSmemBudget / kStageBytes < 8 ? kSmemBudget / kStageBytes : 8;
   static constexpr int kTmemCols = BN <= 32 ? 32 : (BN <= 64 ? 64 : (BN <= 128 ? 128 : 256));   // power of two >= 32
   // tiles + (2*stages + 1) mbarriers + tmem slot + ticket, plus 1024 for manual alignment
-  // + the manual 1024-byte alignment pad (768 for the co-residency variants: a 128 KB gate_up CTA and a 96 KB down CTA must
-  // fit one SM together; the dynamic shared memory of a kernel without static shared memory starts 1024-aligned, the
-  // kernel traps if a larger pad were ever needed)
-  static constexpr int kSmemBytes = kStages * kStageBytes + (2 * kStages + 1) * 8 + 16 + (AR == 64 ? 768 : 1024);
+  static constexpr int kSmemBytes = kStages * kStageBytes + (2 * kStages + 1) * 8 + 16 + 1024;
   static_assert(kStages >= 2, "need at least a double buffer");
 };
 
@@ -63,13 +54,13 @@ __device__ __forceinline__ int atomic_add_acq_rel_gpu(int* p, int v) {
   return old;
 }
 
-template <int BN, int KPS, int CL, int AR>
+template <int BN, int KPS, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
                          void* __restrict__ C, int ldc, int out_f32, int M, int N, int k_blocks_total,
                          int k_blocks_per_split, int a_box_rows, int prefetch_w, int ks_cluster, int epi, float* __restrict__ ws,
                          int* __restrict__ counters, long long* __restrict__ trace) {
-  using cfg = Cfg<BN, KPS, AR>;
+  using cfg = Cfg<BN, KPS>;
   // optional phase timestamps of CTA (0,0,0) (tools/gemm_microbench.py); NULL in production
   const bool tr = trace != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0;
   pdl_trigger();   // the next kernel may start its own prologue
@@ -77,8 +68,6 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
-  if ((smem_base - smem_u32(smem_raw)) + cfg::kStages * cfg::kStageBytes + (2 * cfg::kStages + 1) * 8 + 16 > (uint32_t)cfg::kSmemBytes)
-    __trap();                                      // alignment pad larger than budgeted
   const uint32_t bar_base = smem_base + cfg::kStages * cfg::kStageBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (cfg::kStages + s); };
@@ -410,10 +399,10 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
   return NVC_OK;
 }
 
-template <int BN, int KPS, int CL, int AR = 128>
+template <int BN, int KPS, int CL>
 int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M,
            int N, int K, int splits, int ks_cluster, int epi, cudaStream_t stream, long long* trace) {
-  using cfg = Cfg<BN, KPS, AR>;
+  using cfg = Cfg<BN, KPS>;
   CUtensorMap ta, tb;
   // a single partial m-tile only needs the rows that exist (rounded to the 8-row swizzle atom per
   // cluster CTA); each CTA of a cluster loads a_rows / CL of them
@@ -431,7 +420,7 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
   // ks_cluster: the eff_splits CTAs of one output tile form a cluster (1,1,S) and reduce over DSMEM
   const int ks = (ks_cluster && CL == 1 && eff_splits > 1 && eff_splits <= 8) ? 1 : 0;
   NVC_REQUIRE(ctx, !ks || (size_t)BN * BM * 4 <= (size_t)cfg::kStages * cfg::kStageBytes, NVC_EINVAL, "ring too small for the partial tile");
-  NVC_CUDA_CHECK(ctx, nvc_launch_cluster3(ctx, gemm_bf16_tcgen05_kernel<BN, KPS, CL, AR>, grid, dim3(kThreads), cfg::kSmemBytes,
+  NVC_CUDA_CHECK(ctx, nvc_launch_cluster3(ctx, gemm_bf16_tcgen05_kernel<BN, KPS, CL>, grid, dim3(kThreads), cfg::kSmemBytes,
                                           stream, dim3(CL, 1, ks ? eff_splits : 1), ta, tb, C, ldc, out_f32, M, N, kb_total,
                                           kb_per, a_rows / CL,
                                           (g_nvc_gemm_prefetch && M <= BM) ? 1 : 0,   // helps latency-bound decode, hurts M >= 256
@@ -447,9 +436,6 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
 #define NVC_GEMM_CONFIGS(X)                                                                          \
   X(256, 1, 1) X(128, 1, 1) X(128, 2, 1) X(64, 2, 1) X(64, 4, 1) X(32, 4, 1)                       \
   X(16, 4, 8) X(16, 4, 4) X(32, 4, 4) X(32, 4, 8) X(64, 4, 4) X(64, 2, 4) X(96, 2, 4) X(128, 2, 4) X(128, 1, 4) X(256, 1, 2)
-
-// one-CTA configurations that also exist with a 64-row A sub-tile (decode, M <= 64)
-#define NVC_GEMM_TRIM_CONFIGS(X) X(128, 2) X(64, 2) X(64, 4) X(32, 4)
 
 // Tile choice, fitted to tools/gemm_microbench.py (CUDA-graph timing + CTA phase traces) on B200:
 //  * a CTA ingests ~60 B/clk through TMA when the operands stream from HBM, so a k-block costs
@@ -522,17 +508,10 @@ void choose_config(const nvc_ctx* ctx, int M, int N, int K, bool allow_split, in
 }  // namespace
 
 extern "C" int nvc_gemm_init(nvc_ctx* ctx) {
-#define X(BN, KPS, CL)                                                                    \
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, KPS, CL, 128>,    \
+#define X(BN, KPS, CL)                                                               \
+  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, KPS, CL>,    \
                                            cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, KPS>::kSmemBytes));
   NVC_GEMM_CONFIGS(X)
-#undef X
-#define X(BN, KPS)                                                                         \
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, KPS, 1, 64>,       \
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, KPS, 64>::kSmemBytes)); \
-  NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(gemm_bf16_tcgen05_kernel<BN, KPS, 1, 63>,       \
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN, KPS, 63>::kSmemBytes));
-  NVC_GEMM_TRIM_CONFIGS(X)
 #undef X
   return NVC_OK;
 }
@@ -592,17 +571,6 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   }
   cudaStream_t st = nvc_stream(stream);
   const int f32 = out_dtype == NVC_DT_F32;
-  // M <= 64: the 64-row A sub-tile (NVC_GEMM_TRIM=0 keeps the full m-tile, =2 the trimmed tile with the deep ring)
-  static const int trim_env = getenv("NVC_GEMM_TRIM") ? atoi(getenv("NVC_GEMM_TRIM")) : 1;
-  if (trim_env != 0 && M <= 64 && cl == 1 && (!ks || (size_t)bn * BM * 4 <= (size_t)96 * 1024)) {
-#define X(BN, KPS)                                                                                                          \
-  if (bn == BN && kps == KPS) {                                                                                             \
-    if (trim_env == 2) return launch<BN, KPS, 1, 63>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, ks, epi, st, trace);   \
-    return launch<BN, KPS, 1, 64>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, ks, epi, st, trace);                      \
-  }
-    NVC_GEMM_TRIM_CONFIGS(X)
-#undef X
-  }
 #define X(BN, KPS, CL) \
   if (bn == BN && kps == KPS && cl == CL) return launch<BN, KPS, CL>(ctx, A, lda, W, C, ldc, f32, M, Nout, K, splits, ks, epi, st, trace);
   NVC_GEMM_CONFIGS(X)

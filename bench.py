@@ -289,8 +289,38 @@ class _Env:
         return [float(x) for x in t]
 
 
+def decode_vs_prefill(env, runner, engine, prompts, sids, rows) -> dict:
+    """Self-consistency of the CUDA path at a configuration the fp32 oracle cannot reach in a bench run (Qwen3-8B at a
+    1 000-token context): the last token each checked sequence produced by incremental paged-KV decode (M = batch GEMMs,
+    paged decode attention) must be within the parity tolerance of the best logit of a whole-sequence PREFILL of the same
+    tokens (prompt + its own earlier outputs; persistent-tile GEMMs, varlen flash attention, no cache) - two disjoint sets
+    of kernels computing the same function.  Not an oracle check: the headline record carries that one."""
+    import numpy as np
+    ids, pos, cu, got = [], [], [0], []
+    for b in rows:
+        out = engine.output_of(sids[b])[0]
+        seq = list(prompts[b]) + list(out[:-1])
+        ids += seq
+        pos += list(range(len(seq)))
+        cu.append(len(ids))
+        got.append(int(out[-1]))
+    slots = [-1] * len(ids)                                  # no cache scatter: the engine's blocks stay untouched
+    runner.prefill(np.asarray(ids, dtype=np.int32), np.asarray(pos, dtype=np.int32), np.asarray(cu, dtype=np.int32),
+                   np.asarray(slots, dtype=np.int32))
+    logits = runner.last_logits(len(rows))
+    worst, exact = 0.0, 0
+    for i, t in enumerate(got):
+        row = logits[i]
+        worst = max(worst, float(row.max() - row[t]))
+        exact += int(int(np.flatnonzero(row == row.max())[-1]) == t)
+    return {"kind": "last decode token of each checked sequence vs a whole-sequence prefill of the same tokens (CUDA decode "
+                    "path against CUDA prefill path; not the oracle)",
+            "batch_rows": list(rows), "context": cu[1], "tokens_checked": len(got), "tokens_exact_argmax": exact,
+            "worst_logit_deficit": worst, "tolerance": PARITY_TOL, "ok": bool(worst <= PARITY_TOL)}
+
+
 def measure(env: _Env, model: str, batch: int, prompt_len: int, K: int, W: int, device_weights: bool,
-            max_batched_tokens: int, keep_outputs: int = 0) -> dict:
+            max_batched_tokens: int, keep_outputs: int = 0, consistency: bool = False) -> dict:
     """Prefill the batch, warm up, time K decode steps through the engine (e2e) and K replays of the
     captured step (device), then each kernel family alone.  Returns the pieces of a bench record."""
     eng, synth, ctx, torch = env.eng, env.synth, env.ctx, env.torch
@@ -401,6 +431,8 @@ def measure(env: _Env, model: str, batch: int, prompt_len: int, K: int, W: int, 
                     "ms": t_prefill * 1e3},
         "context_len_at_timing": ctx_len, "kernels_per_step": launches_per_step, "weights_load_s": round(t_load, 1),
     }
+    if consistency and world == 1:
+        rec["consistency"] = decode_vs_prefill(env, runner, engine, prompts, sids, [0, batch - 1])
     engine.close()
     runner.close()
     torch.cuda.empty_cache()
@@ -441,7 +473,7 @@ def run_ours(args):
     if not args.no_north_star:
         try:
             ns, _, _ = measure(env, NS_MODEL, NS_BATCH, NS_PROMPT_LEN, min(K, 16), W, device_weights=True,
-                               max_batched_tokens=32 * 1024)
+                               max_batched_tokens=32 * 1024, consistency=True)
             ns = {"workload": f"{NS_MODEL} bf16 decode, batch {NS_BATCH}, {NS_PROMPT_LEN}-token prompts, paged KV block "
                               f"{BLOCK_SIZE}, device-generated weights (BASELINE.json configs[2], decode phase; targets: paged "
                               f"decode >= 0.70 of HBM, GEMMs >= 0.60 of bf16 peak)",
@@ -464,7 +496,8 @@ def run_ours(args):
     ok = True
     if env.rank == 0:
         _emit(line)
-        ok = parity["ok"]
+        ns_c = line.get("north_star", {}).get("consistency") if isinstance(line.get("north_star"), dict) else None
+        ok = parity["ok"] and (ns_c is None or ns_c["ok"])
     if env.dist is not None:
         flag = [ok]
         env.dist.broadcast_object_list(flag, src=0)

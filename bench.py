@@ -393,7 +393,15 @@ def measure(env: _Env, model: str, batch: int, prompt_len: int, K: int, W: int, 
     ops_list = [op for op in ("paged_decode", "gemm_qkv", "gemm_o", "gemm_gate_up", "gemm_down", "rmsnorm", "qk_norm_rope",
                               "lm_head", "argmax", "noop") if op in runner.OPS] + (["allreduce"] if world > 1 else [])
     for op in ops_list:
+        # NVC_NCU_RANGE=<op>: cudaProfilerStart / Stop around that family's timing run, so that
+        # `ncu --profile-from-start off` captures exactly the launches the roofline is computed from
+        marked = os.environ.get("NVC_NCU_RANGE") == op
+        if marked:
+            torch.cuda.profiler.start()
         ms, _ = runner.time_op(op, 5)
+        if marked:
+            torch.cuda.synchronize()
+            torch.cuda.profiler.stop()
         breakdown[op + "_us"] = round(ms * 1e3, 2)
     attn_bytes = batch * ctx_len * 2 * kv_l * 128 * 2 + 2 * batch * nh_l * 128 * 2     # K+V once per kv head, q in, out
     pk = env.peaks

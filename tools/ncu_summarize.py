@@ -2,7 +2,7 @@
 
     python tools/ncu_summarize.py launches <launches.csv>       # --metrics gpu__time_duration.sum --csv log
     python tools/ncu_summarize.py full <raw.csv>                 # ncu -i x.ncu-rep --page raw --csv
-    python tools/ncu_summarize.py traffic <raw.csv> <kernel regex> <out.json> [note]
+    python tools/ncu_summarize.py traffic <raw.csv> <kernel regex> <out.json> [note [batch kv_heads_local context_len]]
         # dram__bytes_read.sum + dram__bytes_write.sum per launch of the matching kernels -> the
         # file bench.py's roofline.traffic reads (profiles/paged_decode_ncu_traffic.json)
 """
@@ -59,7 +59,7 @@ def _bytes(v, unit):
     return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
 
 
-def traffic(path, pattern, out, note=""):
+def traffic(path, pattern, out, note="", batch=None, kv_heads_local=None, context_len=None):
     import json
     rows = list(csv.reader(open(path)))
     hdr, units, data = rows[0], rows[1], rows[2:]
@@ -70,7 +70,11 @@ def traffic(path, pattern, out, note=""):
     json.dump({"kernel": pattern, "launches": len(sel), "grid": sel[0][hdr.index("Grid Size")],
                "dram_bytes_read_per_launch": sum(rd) / len(rd), "dram_bytes_write_per_launch": sum(wr) / len(wr),
                "dram_bytes_per_launch": (sum(rd) + sum(wr)) / len(sel),
-               "gpu_time_us_under_ncu": [float(d[it].replace(",", "")) for d in sel], "note": note},
+               "gpu_time_us_under_ncu": [float(d[it].replace(",", "")) for d in sel], "note": note,
+               # the shape the capture was taken on: bench.py's roofline.traffic only uses a capture of its own shape
+               "batch": None if batch is None else int(batch),
+               "kv_heads_local": None if kv_heads_local is None else int(kv_heads_local),
+               "context_len": None if context_len is None else int(context_len)},
               open(out, "w"), indent=1)
     print(open(out).read())
 

@@ -160,15 +160,6 @@ int nvc_fused_add_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x, const float* residual
                           float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out,
                           int N, int H, void* stream);
 
-/* K3 with the residual add as its epilogue (RowParallelLinear::forward at tp_size 1 followed by the add half of
- * RMSNorm::add_rms_forward, src/layers/linear.rs:184-198 + layernorm.rs:44-60): residual[M, Nout] += bf16(A W^T), fp32, in
- * place; the projection's output is never written.  Follow it with nvc_fused_add_rmsnorm(x = NULL, residual_in = residual,
- * residual_out = NULL, ...), which then only reads the residual.  Bit-identical to nvc_gemm_bf16 + nvc_fused_add_rmsnorm.
- * Prefill-sized M only: returns NVC_ENOTIMPL with nothing launched for shapes that do not take the persistent pair schedule
- * (decode), where the caller keeps the two-kernel form. */
-int nvc_gemm_bf16_residual_add(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, float* residual, int M, int Nout,
-                               int K, void* stream);
-
 /* K3. Replaces candle_nn::Linear::forward inside every *ParallelLinear::forward
  * (src/layers/linear.rs:33-38,72-77,99-104,171-175,184-198) and compute_logits
  * (src/models/qwen3.rs:542-550):  C[M, Nout] = A[M, K] * W[Nout, K]^T  (W is the

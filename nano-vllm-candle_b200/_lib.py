@@ -74,7 +74,6 @@ def _declare(l: C.CDLL) -> None:
         "nvc_nvls_argmax_merge": [_vp, _vp, _vp, _vp, _vp, _i, _vp],
         "nvc_embed_gather": [_vp, _vp, _vp, _vp, _i, _i, _i, _vp],
         "nvc_fused_add_rmsnorm": [_vp, _vp, _vp, _vp, _vp, _f, _vp, _i, _i, _vp],
-        "nvc_gemm_bf16_residual_add": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp],
         "nvc_gemm_bf16": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _vp],
         "nvc_gemm_bf16_ex": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp],
         "nvc_gemm_bf16_silu_mul": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _vp],

@@ -68,7 +68,7 @@ fused_add_rmsnorm_kernel(const uint4* __restrict__ x, const float4* __restrict__
   if (!kLoop) {
     const int v = threadIdx.x;
     if (v < nvec) {
-      if (x != nullptr) unpack8(ldg_nc_u4(x + vbase + v), s); else { s[0] = s[1] = s[2] = s[3] = s[4] = s[5] = s[6] = s[7] = 0.f; }
+      unpack8(ldg_nc_u4(x + vbase + v), s);
       if (res_in) {
         float4 a = res_in[(vbase + v) * 2], b = res_in[(vbase + v) * 2 + 1];
         s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
@@ -83,7 +83,7 @@ fused_add_rmsnorm_kernel(const uint4* __restrict__ x, const float4* __restrict__
     }
   } else {
     for (int v = threadIdx.x; v < nvec; v += blockDim.x) {
-      if (x != nullptr) unpack8(ldg_nc_u4(x + vbase + v), s); else { s[0] = s[1] = s[2] = s[3] = s[4] = s[5] = s[6] = s[7] = 0.f; }
+      unpack8(ldg_nc_u4(x + vbase + v), s);
       if (res_in) {
         float4 a = res_in[(vbase + v) * 2], b = res_in[(vbase + v) * 2 + 1];
         s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
@@ -121,7 +121,7 @@ fused_add_rmsnorm_kernel(const uint4* __restrict__ x, const float4* __restrict__
         float4 a = res_out[(vbase + v) * 2], b = res_out[(vbase + v) * 2 + 1];
         s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
       } else {
-        if (x != nullptr) unpack8(ldg_nc_u4(x + vbase + v), s); else { s[0] = s[1] = s[2] = s[3] = s[4] = s[5] = s[6] = s[7] = 0.f; }
+        unpack8(ldg_nc_u4(x + vbase + v), s);
         if (res_in) {
           float4 a = res_in[(vbase + v) * 2], b = res_in[(vbase + v) * 2 + 1];
           s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
@@ -140,9 +140,7 @@ fused_add_rmsnorm_kernel(const uint4* __restrict__ x, const float4* __restrict__
 extern "C" int nvc_fused_add_rmsnorm(nvc_ctx* ctx, const nvc_bf16* x, const float* residual_in,
                                      float* residual_out, const nvc_bf16* w, float eps, nvc_bf16* out,
                                      int N, int H, void* stream) {
-  // x == NULL: the norm of the residual stream alone (the row-parallel GEMM before it has already added its output,
-  // nvc_gemm_bf16_residual_add)
-  NVC_REQUIRE(ctx, ctx && (x || residual_in) && w && out, NVC_EINVAL, "null pointer");
+  NVC_REQUIRE(ctx, ctx && x && w && out, NVC_EINVAL, "null pointer");
   NVC_REQUIRE(ctx, N >= 0 && H > 0, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, H % 8 == 0 && H <= 65536, NVC_ESHAPE, "H must be a multiple of 8 and <= 65536");
   if (N == 0) return NVC_OK;

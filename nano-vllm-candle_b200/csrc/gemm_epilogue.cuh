@@ -8,11 +8,7 @@
 // scattered to the paged cache at slot_mapping[row] - so the separate pass over the QKV buffer (120-160 us for 600 MB at
 // 32 768 tokens, 10-13 % of a 0.6B prefill step) disappears.  A 256-column tile is two heads of one row; the warp parks a head
 // (32 rows x 256 B) in its staging buffer and works on it with the lane mapping and arithmetic of qk_norm_rope_store_kernel.
-// NVC_EPI_RESIDUAL_ADD (pair kernel, persistent schedule): the GEMM is a row-parallel projection at TP 1 (o_proj / down_proj)
-// and its epilogue adds the bf16-rounded result to the fp32 residual stream in place (residual[M, N] += bf16(A W^T)): the
-// projection's output is never written, and the RMSNorm that follows reads the residual only - half the bytes of the
-// x + residual pass it replaces (src/layers/layernorm.rs:44-60 add_rms_forward, same arithmetic, same bits).
-enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1, NVC_EPI_QK_NORM_ROPE = 3, NVC_EPI_RESIDUAL_ADD = 4 };
+enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1, NVC_EPI_QK_NORM_ROPE = 3 };
 
 struct QkEpi {
   const uint4* qw = nullptr;         // q_norm weight [128] bf16
@@ -24,7 +20,6 @@ struct QkEpi {
   uint4* v_cache = nullptr;
   float eps = 0.f;
   int nh = 0, kv = 0;                // local q / kv heads: C columns [0, nh) q heads, [nh, nh + kv) k heads, then v heads
-  float* residual = nullptr;         // NVC_EPI_RESIDUAL_ADD: fp32 [M, N] (row stride N), updated in place
 };
 
 // 16 accumulator columns of one row -> C (bf16 or f32), 16-byte stores

@@ -428,69 +428,6 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           continue;
         }
       }
-      if (epi == NVC_EPI_RESIDUAL_ADD) {
-        // ---- residual[rows, cols of this tile] += bf16(acc), 32 columns (128 B of fp32 per row) at a time.  One thread owns
-        // one accumulator row, but the residual is read and written with 8 lanes per row (4 rows x 128 contiguous bytes per
-        // instruction) through the warp's staging buffer; the next chunk's residual is in flight while this one is added.
-        const int row_base = m_tile * kTileM + h * kHalf + q * 32;
-        const uint32_t stage = smem_u32(smem_gen + cfg::kOffStage + q * cfg::kStageBuf);   // [32 rows][8 chunks of 16 B], chunk ^= row & 7
-        const int ch = lane & 7, sub = lane >> 3;
-        const int cols_valid = min(NT, N - n_tile * NT);
-        auto gptr = [&](int i, int c32) {      // this lane's 16 bytes of row (4 i + sub), columns [32 c32 + 4 ch, + 4)
-          return reinterpret_cast<float4*>(qk.residual + (int64_t)(row_base + 4 * i + sub) * N + n_tile * NT + c32 * 32 + 4 * ch);
-        };
-        auto lane_ok = [&](int i, int c32) { return row_base + 4 * i + sub < M && c32 * 32 + 4 * ch < cols_valid; };
-        float4 nxt[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) nxt[i] = lane_ok(i, 0) ? *gptr(i, 0) : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 1
-        for (int c32 = 0; c32 < cfg::kChunks / 2; ++c32) {
-          float4 cur[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) cur[i] = nxt[i];
-          if (c32 + 1 < cfg::kChunks / 2) {
-#pragma unroll
-            for (int i = 0; i < 8; ++i) nxt[i] = lane_ok(i, c32 + 1) ? *gptr(i, c32 + 1) : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
-          uint32_t v[32];
-          ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(acc * 256) + cfg::chunk_col(2 * c32), v);
-          ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(acc * 256) + cfg::chunk_col(2 * c32 + 1), v + 16);
-          ptx::tmem_ld_wait();
-          // residual chunk -> staging (coalesced layout) -> own row
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int rr = 4 * i + sub;
-            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(stage + rr * 128 + ((ch ^ (rr & 7)) << 4)), "f"(cur[i].x),
-                         "f"(cur[i].y), "f"(cur[i].z), "f"(cur[i].w) : "memory");
-          }
-          __syncwarp();
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            float4 rv;
-            const uint32_t a = stage + lane * 128 + ((k ^ (lane & 7)) << 4);
-            asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(rv.x), "=f"(rv.y), "=f"(rv.z), "=f"(rv.w) : "r"(a) : "memory");
-            // the projection's output is bf16 (linear.rs:171-175): round, then add in fp32 as the norm kernel did
-            const uint32_t p01 = pack_bf16(__uint_as_float(v[4 * k]), __uint_as_float(v[4 * k + 1]));
-            const uint32_t p23 = pack_bf16(__uint_as_float(v[4 * k + 2]), __uint_as_float(v[4 * k + 3]));
-            rv.x += bf16_lo(p01); rv.y += bf16_hi(p01); rv.z += bf16_lo(p23); rv.w += bf16_hi(p23);
-            asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a), "f"(rv.x), "f"(rv.y), "f"(rv.z), "f"(rv.w) : "memory");
-          }
-          __syncwarp();
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int rr = 4 * i + sub;
-            float4 o;
-            asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(o.x), "=f"(o.y), "=f"(o.z), "=f"(o.w)
-                         : "r"(stage + rr * 128 + ((ch ^ (rr & 7)) << 4)) : "memory");
-            if (lane_ok(i, c32)) *gptr(i, c32) = o;
-          }
-          __syncwarp();
-        }
-        ptx::tcgen05_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_cluster(leader_tmem_empty0 + 8u * acc);
-        continue;
-      }
       RowStage st = make_row_stage(smem_gen + cfg::kOffStage + q * cfg::kStageBuf, C, out_f32, epi, ldc,
                                    m_tile * kTileM + h * kHalf + q * 32, M, n_tile * NT, NT, N);
 #pragma unroll 1
@@ -746,33 +683,4 @@ extern "C" int nvc_qkv_proj_norm_rope(nvc_ctx* ctx, const nvc_bf16* A, int lda, 
   if (rc) return rc;
   return nvc_qk_norm_rope_store(ctx, qkv, q_norm_w, k_norm_w, eps, cos_sin, positions, slot_mapping, k_cache, v_cache, M, nh, kv,
                                 hd, stream);
-}
-
-// Row-parallel projection at TP 1 with the residual add as its epilogue (prefill-sized M): residual[M, N] += bf16(A W^T), in
-// place, fp32; nothing else is written.  NVC_ENOTIMPL (nothing launched) when the shape does not take the persistent
-// schedule - the caller then runs nvc_gemm_bf16 + nvc_fused_add_rmsnorm.
-extern "C" int nvc_gemm_pair_residual(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, float* residual, int M, int N,
-                                      int K, void* stream) {
-  if (M <= kTileM || N % 8 != 0 || K % BK != 0 || residual == nullptr) return NVC_ENOTIMPL;
-  int nt = 256, S = 1;
-  choose_schedule(ctx, M, N, K / BK, &nt, &S);
-  if (nt != 256 || S != 1) return NVC_ENOTIMPL;
-  QkEpi e;
-  e.residual = residual;
-  return launch_pair<256>(ctx, A, lda, W, residual, N, 0, M, N, K, 1, NVC_EPI_RESIDUAL_ADD, nvc_stream(stream), nullptr, e);
-}
-
-// Public form: residual[M, N] += bf16(A W^T) (fp32 residual stream, in place).  One kernel at prefill sizes (the pair GEMM's
-// persistent epilogue); otherwise nvc_gemm_bf16 into `scratch` [M, N] bf16 followed by an add pass is NOT what a caller
-// wants at decode sizes (the fused norm kernel does the add there), so small shapes return NVC_ENOTIMPL and the caller keeps
-// nvc_gemm_bf16 + nvc_fused_add_rmsnorm.
-extern "C" int nvc_gemm_bf16_residual_add(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, float* residual, int M,
-                                          int Nout, int K, void* stream) {
-  NVC_REQUIRE(ctx, ctx && A && W && residual, NVC_EINVAL, "null pointer");
-  NVC_REQUIRE(ctx, M >= 0 && Nout > 0 && K > 0 && K % 64 == 0 && Nout % 16 == 0, NVC_ESHAPE, "K % 64 == 0 and Nout % 16 == 0");
-  NVC_REQUIRE(ctx, lda % 8 == 0 && lda >= K, NVC_ESHAPE, "lda must be >= K and a multiple of 8");
-  if (M == 0) return NVC_OK;
-  static const bool fused = !(getenv("NVC_RESIDUAL_FUSED") && atoi(getenv("NVC_RESIDUAL_FUSED")) == 0);
-  if (!fused || g_nvc_debug[7] == 2) return NVC_ENOTIMPL;
-  return nvc_gemm_pair_residual(ctx, A, lda, W, residual, M, Nout, K, stream);
 }

@@ -28,8 +28,6 @@ int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, v
 int nvc_gemm_pair_qk(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, nvc_bf16* C, int ldc, int M, int N, int K,
                      const nvc_bf16* qw, const nvc_bf16* kw, float eps, const float* cos_sin, const int32_t* positions,
                      const int32_t* slot_mapping, nvc_bf16* k_cache, nvc_bf16* v_cache, int nh, int kv, void* stream);
-int nvc_gemm_pair_residual(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, float* residual, int M, int N, int K,
-                           void* stream);
 int nvc_prefill_attn_init(nvc_ctx* ctx);
 int nvc_paged_decode_init(nvc_ctx* ctx);
 }

@@ -106,7 +106,7 @@ int dev_alloc(nvc_runner* r, T** p, size_t count) {
 // sequences are single tokens (rows 0 .. num_decode-1) and go through the paged decode kernel,
 // the other sequences through the paged prefill kernel with their own cu_seqlens (r->d_cu2).
 int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blocks_hint, bool* final_norm_done,
-               bool paged_prefill = false, int num_decode = 0, bool* x_in_residual = nullptr) {
+               bool paged_prefill = false, int num_decode = 0) {
   const nvc_qwen3_config& c = r->cfg;
   nvc_ctx* ctx = r->ctx;
   void* st = r->stream;
@@ -122,20 +122,14 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
   nvc_bf16* slot1 = p2p ? reinterpret_cast<nvc_bf16*>(nvc_ctx_p2p_slot(ctx, 1)) : nullptr;
   *final_norm_done = false;
   bool xn_ready = false;
-  // TP 1, prefill-sized steps: o_proj / down_proj add their output to the residual stream in their own epilogue
-  // (nvc_gemm_bf16_residual_add) and the norm that follows reads the residual only; x_res: the last projection did so
-  const bool res_fused = !decode && r->tp == 1 && x_in_residual != nullptr;
-  bool x_res = false;
   int rc;
   for (int li = 0; li < L; ++li) {
     Layer& Ly = r->layers[li];
     if (!xn_ready) {
       // input_layernorm with fused residual add; layer 0 seeds the residual stream (qwen3.rs:376-387)
-      if (x_res) rc = nvc_fused_add_rmsnorm(ctx, nullptr, r->residual, nullptr, Ly.ln1, c.rms_norm_eps, r->xn, N, H, st);
-      else rc = nvc_fused_add_rmsnorm(ctx, r->x, li == 0 ? nullptr : r->residual, r->residual, Ly.ln1, c.rms_norm_eps, r->xn, N, H, st);
+      rc = nvc_fused_add_rmsnorm(ctx, r->x, li == 0 ? nullptr : r->residual, r->residual, Ly.ln1, c.rms_norm_eps, r->xn, N, H, st);
       if (rc) return rc;
     }
-    x_res = false;
     xn_ready = false;
     // QKV projection + q/k-norm + RoPE + KV scatter: one kernel at prefill sizes, GEMM + K2 otherwise (same bits)
     rc = nvc_qkv_proj_norm_rope(ctx, r->xn, H, Ly.w_qkv, r->qkv, N, H, Ly.q_norm, Ly.k_norm, c.rms_norm_eps, r->rope, r->d_pos,
@@ -165,19 +159,9 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     }
     if (rc) return rc;
     // o_proj (row-parallel) -> [all-reduce, N4] -> post_attention_layernorm with residual add
-    bool o_res = false;
-    if (res_fused) {
-      rc = nvc_gemm_bf16_residual_add(ctx, r->attn, r->nh_l * hd, Ly.w_o, r->residual, N, H, r->nh_l * hd, st);
-      if (rc != NVC_OK && rc != NVC_ENOTIMPL) return rc;
-      o_res = rc == NVC_OK;
-    }
-    if (!o_res) {
-      rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, Ly.w_o, p2p ? slot0 : r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
-      if (rc) return rc;
-    }
-    if (o_res) {
-      rc = nvc_fused_add_rmsnorm(ctx, nullptr, r->residual, nullptr, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
-    } else if (nvls) {
+    rc = nvc_gemm_bf16(ctx, r->attn, r->nh_l * hd, Ly.w_o, p2p ? slot0 : r->x, H, NVC_DT_BF16, N, H, r->nh_l * hd, st);
+    if (rc) return rc;
+    if (nvls) {
       rc = nvc_nvls_allreduce_rmsnorm(ctx, r->x, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, 0, st);
     } else if (p2p) {
       rc = nvc_p2p_allreduce_rmsnorm(ctx, 0, r->residual, r->residual, Ly.ln2, c.rms_norm_eps, r->xn, N, H, st);
@@ -190,14 +174,6 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
     rc = nvc_gemm_bf16_silu_mul(ctx, r->xn, H, Ly.w_gu, r->act, r->I_l, N, r->I_l, H, st);
     if (rc) return rc;
     // down_proj (row-parallel) -> [all-reduce, N4]
-    if (res_fused) {
-      rc = nvc_gemm_bf16_residual_add(ctx, r->act, r->I_l, Ly.w_down, r->residual, N, H, r->I_l, st);
-      if (rc != NVC_OK && rc != NVC_ENOTIMPL) return rc;
-      if (rc == NVC_OK) {
-        x_res = true;
-        continue;
-      }
-    }
     rc = nvc_gemm_bf16(ctx, r->act, r->I_l, Ly.w_down, p2p ? slot1 : r->x, H, NVC_DT_BF16, N, H, r->I_l, st);
     if (rc) return rc;
     if (nvls) {
@@ -221,13 +197,11 @@ int run_layers(nvc_runner* r, int N, bool decode, int B, int max_seqlen, int blo
       if (rc) return rc;
     }
   }
-  if (x_in_residual) *x_in_residual = x_res;
   return NVC_OK;
 }
 
 // last-token rows -> final norm -> lm_head (fp32 logits) -> argmax (vocab shard offset)
-// x_in_residual: the last down_proj already added its output to the residual stream (the final norm reads that alone)
-int run_head(nvc_runner* r, int B, bool decode, bool final_norm_done, bool x_in_residual = false) {
+int run_head(nvc_runner* r, int B, bool decode, bool final_norm_done) {
   const nvc_qwen3_config& c = r->cfg;
   nvc_ctx* ctx = r->ctx;
   void* st = r->stream;
@@ -245,7 +219,7 @@ int run_head(nvc_runner* r, int B, bool decode, bool final_norm_done, bool x_in_
     rs = r->res_last;
   }
   if (!final_norm_done) {
-    rc = nvc_fused_add_rmsnorm(ctx, x_in_residual ? nullptr : xs, rs, nullptr, r->final_norm, c.rms_norm_eps, r->xn_last, B, H, st);   // qwen3.rs:497
+    rc = nvc_fused_add_rmsnorm(ctx, xs, rs, nullptr, r->final_norm, c.rms_norm_eps, r->xn_last, B, H, st);   // qwen3.rs:497
     if (rc) return rc;
   }
   rc = nvc_gemm_bf16(ctx, r->xn_last, H, r->lm_head, r->logits, r->V_l, NVC_DT_F32, B, r->V_l, H, st);     // qwen3.rs:548
@@ -681,10 +655,9 @@ int prefill_impl(nvc_runner* r, const int32_t* ids, const int32_t* positions, co
   rc = nvc_embed_gather(ctx, r->d_ids, r->embed, r->x, N, r->cfg.hidden_size, r->cfg.vocab_size, st);
   if (rc) return rc;
   bool fnd = false;
-  bool x_res = false;
-  rc = run_layers(r, N, false, B, max_seqlen_chunks, hint, &fnd, paged, num_decode, &x_res);
+  rc = run_layers(r, N, false, B, max_seqlen_chunks, hint, &fnd, paged, num_decode);
   if (rc) return rc;
-  rc = run_head(r, B, false, fnd, x_res);
+  rc = run_head(r, B, false, fnd);
   r->sampling_armed = false;
   if (rc) return rc;
   r->last_B = B;

@@ -141,13 +141,9 @@ class Context:
         return out
 
     def fused_add_rmsnorm(self, x, w, eps, residual_in=None, residual_out=None, out=None):
-        """x may be None: the norm of residual_in alone."""
-        _req(w, BF16, "w")
-        if x is not None:
-            _req(x, BF16, "x")
-        N, H = (x if x is not None else residual_in).shape
-        if out is None:
-            out = torch.empty((N, H), dtype=BF16, device=w.device)
+        _req(x, BF16, "x"); _req(w, BF16, "w")
+        N, H = x.shape
+        out = torch.empty_like(x) if out is None else out
         self._ck(self.l.nvc_fused_add_rmsnorm(self.h, _ptr(x), _ptr(residual_in), _ptr(residual_out), _ptr(w),
                                               float(eps), _ptr(out), N, H, _stream()), "nvc_fused_add_rmsnorm")
         return out
@@ -164,18 +160,6 @@ class Context:
         self._ck(self.l.nvc_gemm_bf16_ex(self.h, _ptr(a), a.stride(0), _ptr(w), _ptr(out), out.stride(0), dt,
                                          M, N, K, force_bn, force_splits, _stream()), "nvc_gemm_bf16")
         return out
-
-    def gemm_residual_add(self, a: torch.Tensor, w: torch.Tensor, residual: torch.Tensor) -> bool:
-        """residual += bf16(a @ w.T) in one kernel (prefill sizes); False (nothing done) when the shape keeps the two-kernel form."""
-        _req(a, BF16, "a"); _req(w, BF16, "w"); _req(residual, torch.float32, "residual")
-        M, K = a.shape
-        N = w.shape[0]
-        assert w.shape[1] == K and w.is_contiguous() and a.stride(1) == 1 and residual.shape == (M, N) and residual.is_contiguous()
-        st = self.l.nvc_gemm_bf16_residual_add(self.h, _ptr(a), a.stride(0), _ptr(w), _ptr(residual), M, N, K, _stream())
-        if st == -3:          # NVC_ENOTIMPL
-            return False
-        self._ck(st, "nvc_gemm_bf16_residual_add")
-        return True
 
     @staticmethod
     def interleave_gate_up(w_gu: torch.Tensor) -> torch.Tensor:

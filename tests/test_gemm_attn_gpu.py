@@ -149,39 +149,6 @@ def test_qkv_proj_norm_rope_fused(ctx, nvc, M, nh, kv, K):
     assert torch.equal(got[:, (nh + kv) * hd:], proj[:, (nh + kv) * hd:]), "v columns must be the projection itself"
 
 
-@pytest.mark.parametrize("M,N,K", [
-    (32768, 1024, 2048),     # 0.6B o_proj at the bench's prefill step
-    (5000, 1024, 3072),      # down_proj, ragged last m-tile
-    (4096, 4096, 4096),      # 8B o_proj
-    (3000, 1040, 512),       # ragged N: the last 256-column tile holds 16 columns
-    (64, 1024, 2048),        # decode-sized: NVC_ENOTIMPL, nothing launched
-])
-def test_gemm_residual_add_fused(ctx, M, N, K):
-    """row-parallel projection with the residual add as its epilogue: residual += bf16(a w^T) must equal the two-step form
-    (nvc_gemm_bf16 to bf16, then the fp32 add the norm kernel does) bit for bit, and the norm of the residual alone
-    (x = NULL) must equal the fused add + norm over the unfused operands (linear.rs:184-198, layernorm.rs:44-60)."""
-    g = torch.Generator().manual_seed(M + N + K)
-    a = torch.randn(M, K, generator=g).to(BF16).cuda()
-    w = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(BF16).cuda()
-    res = torch.randn(M, N, generator=g).cuda()
-    wn = (1 + 0.2 * torch.randn(N, generator=g)).to(BF16).cuda()
-    x = ctx.gemm(a, w)
-    r_ref = torch.empty_like(res)
-    o_ref = ctx.fused_add_rmsnorm(x, wn, 1e-6, residual_in=res, residual_out=r_ref)
-    r = res.clone()
-    done = ctx.gemm_residual_add(a, w, r)
-    torch.cuda.synchronize()
-    if M <= 256:
-        assert not done and torch.equal(r, res), "decode-sized shapes keep the two-kernel form (nothing may be written)"
-        return
-    assert done, "prefill-sized shape did not take the fused path"
-    assert torch.equal(r, r_ref), "residual += bf16(a w^T) differs from gemm + add"
-    o = ctx.fused_add_rmsnorm(None, wn, 1e-6, residual_in=r)
-    torch.cuda.synchronize()
-    assert torch.equal(o.view(torch.int16), o_ref.view(torch.int16)), "norm of the residual alone differs from add + norm"
-    _close(r, res.cpu() + O.linear(a.float().cpu(), w.float().cpu()), 2e-2, 2 ** -7, f"residual add M={M} N={N} K={K}")
-
-
 def test_gemm_reference_goldens(ctx):
     """src/layers/linear.rs:231-267 (replicated, exact small integers; bias added on the host
     here since the Qwen3 path has no biases) and :274-319 (two hand-sharded column ranks),

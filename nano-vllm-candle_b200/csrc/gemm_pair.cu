@@ -529,9 +529,14 @@ int launch_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, voi
     clusters = (tiles + waves - 1) / waves;
   }
   dim3 grid(clusters * 2 * S);
+  // L2 prefetch of the first weight k-blocks before the dependency wait + 16 k-blocks ahead of the ring: pays for short,
+  // latency-bound k-loops (decode at K <= 3072: 1 - 3 %), costs 4 - 9 % on the long ones (Qwen3-8B at batch 256, K >= 4096:
+  // qkv 18.4 -> 16.8 us, o_proj 14.6 -> 13.9, gate_up 49.6 -> 47.4, down 30.3 -> 28.4 without it) - the prefetches compete
+  // with the ring's own TMA loads for the same L2 / HBM queues (profiles/r02_pair_prefetch_ab.txt)
+  const int prefetch_w = (M <= kTileM && kb_total <= 48) ? 1 : 0;
   NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, gemm_pair_kernel<NT>, grid, dim3(kThreads), cfg::kSmemBytes, stream, 2 * S,
                                          ta, tb, C, ldc, out_f32, M, N, kb_total, kb_per, tiles, n_tiles,
-                                         (M <= kTileM) ? 1 : 0, epi, reinterpret_cast<float4*>(ctx->gemm_ws), trace,
+                                         prefetch_w, epi, reinterpret_cast<float4*>(ctx->gemm_ws), trace,
                                          qk));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;

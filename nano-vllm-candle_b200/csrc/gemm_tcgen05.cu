@@ -423,7 +423,10 @@ int launch(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C,
   NVC_CUDA_CHECK(ctx, nvc_launch_cluster3(ctx, gemm_bf16_tcgen05_kernel<BN, KPS, CL>, grid, dim3(kThreads), cfg::kSmemBytes,
                                           stream, dim3(CL, 1, ks ? eff_splits : 1), ta, tb, C, ldc, out_f32, M, N, kb_total,
                                           kb_per, a_rows / CL,
-                                          (g_nvc_gemm_prefetch && M <= BM) ? 1 : 0,   // helps latency-bound decode, hurts M >= 256
+                                          // first ring lap of W before the dependency wait + L2 prefetch ahead of the ring:
+                                          // helps the short, latency-bound k-loops of decode (K <= 3072: 5.1 vs 5.7 us), costs
+                                          // 2 - 8 % on the long ones (K 12288 at M 64: 23.2 -> 21.6 us without it) and at M >= 256
+                                          (g_nvc_gemm_prefetch && M <= BM && kb_total <= 48) ? 1 : 0,
                                           ks, epi, ctx->gemm_ws, ctx->gemm_counters, trace));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;

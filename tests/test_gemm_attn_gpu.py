@@ -101,10 +101,11 @@ def test_gemm_bf16(ctx, M, N, K, bn, splits, out_dtype):
 
 
 @pytest.mark.parametrize("M,nh,kv,K", [
-    (1500, 16, 8, 1024),      # 0.6B qkv at a prefill size: 6 m-tiles (last one ragged) x 16 tiles of two heads
+    (8200, 16, 8, 1024),      # 0.6B qkv at a prefill size: 33 m-tiles (last one ragged) x 16 tiles of two heads
     (32768, 16, 8, 1024),     # the bench's prefill step
-    (2048, 5, 1, 512),        # 7 heads = 896 columns: the last 256-column tile holds one head
-    (700, 32, 8, 4096),       # 8B shape, M not a multiple of 128
+    (8192, 5, 1, 512),        # 7 heads = 896 columns: the last 256-column tile holds one head
+    (9000, 32, 8, 4096),      # 8B shape, M not a multiple of 128
+    (1500, 16, 8, 1024),      # below the fusion threshold: the two-kernel path
     (300, 4, 2, 256),         # few tiles: whatever schedule the library picks, the results must not change
     (64, 16, 8, 1024),        # decode-sized: the two-kernel path
 ])

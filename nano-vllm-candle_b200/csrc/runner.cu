@@ -4,7 +4,8 @@
 // forward it drives (src/models/qwen3.rs:202-281,323-327,374-399,458-499,542-550).
 //
 // Per layer (prefill and decode differ only in the attention kernel):
-//   fused_add_rmsnorm -> qkv GEMM -> qk_norm_rope_store -> attention -> o_proj GEMM [-> all-reduce]
+//   fused_add_rmsnorm -> qkv GEMM -> qk_norm_rope_store (one kernel from 8 192 rows up: nvc_qkv_proj_norm_rope)
+//   -> attention -> o_proj GEMM [-> all-reduce]
 //   -> fused_add_rmsnorm -> gate_up GEMM (+ SiLU-mul epilogue) -> down GEMM [-> all-reduce]
 // then: gather last rows -> final fused_add_rmsnorm -> lm_head GEMM (fp32) -> argmax.
 #include "common.cuh"

@@ -136,6 +136,33 @@ def test_guard_qk_norm_rope_store_and_attention(ctx):
     assert (out3.view.float() - out.view[last].float()).abs().max().item() < 2e-2
 
 
+def test_guard_qkv_proj_norm_rope_fused(ctx):
+    """K3 + K2 as one kernel (M >= 8192 takes the fused epilogue): qkv rows and both caches inside sentinel bands, M ragged"""
+    g = torch.Generator().manual_seed(9)
+    nh, kv, hd, bs, K = 4, 2, 128, 16, 256
+    M = 8192 + 77
+    width = (nh + 2 * kv) * hd
+    a = edged(torch.randn(M, K, generator=g).to(BF16))
+    w = edged((torch.randn(width, K, generator=g) / math.sqrt(K)).to(BF16))
+    qw, kw = edged(torch.randn(hd, generator=g).to(BF16)), edged(torch.randn(hd, generator=g).to(BF16))
+    tab = ctx.rope_table(1e6, hd, M)
+    pos = edged(torch.arange(M, dtype=torch.int32))
+    nblk = (M + bs - 1) // bs
+    slots = edged(torch.randperm(nblk * bs, generator=g)[:M].to(torch.int32))
+    kc, vc = Guarded(nblk * bs * kv, hd, BF16), Guarded(nblk * bs * kv, hd, BF16)
+    kc.view.zero_(); vc.view.zero_()
+    kc4, vc4 = kc.view.view(nblk, bs, kv, hd), vc.view.view(nblk, bs, kv, hd)
+    qkv = Guarded(M, width, BF16)
+    ctx.qkv_proj_norm_rope(a, w, qw, kw, 1e-6, tab, pos, nh, kv, hd, slot_mapping=slots, k_cache=kc4, v_cache=vc4, out=qkv.view)
+    qkv.check("qkv_proj_norm_rope qkv"); kc.check("qkv_proj_norm_rope k_cache"); vc.check("qkv_proj_norm_rope v_cache")
+    assert not torch.isnan(qkv.view.float()).any()
+    # the two-kernel path on the same inputs is bit-identical
+    ref = ctx.gemm(a, w)
+    kr, vr = torch.zeros_like(kc4), torch.zeros_like(vc4)
+    ctx.qk_norm_rope_store(ref, qw, kw, 1e-6, tab, pos, nh, kv, hd, slot_mapping=slots, k_cache=kr, v_cache=vr)
+    assert torch.equal(ref, qkv.view) and torch.equal(kr, kc4) and torch.equal(vr, vc4)
+
+
 def test_guard_head(ctx):
     g = torch.Generator().manual_seed(5)
     B, V = 7, 1040

@@ -5,6 +5,7 @@
 // replaces in include/nvc_b200.h.
 #include "common.cuh"
 #include "internal.h"
+#include "ptx.cuh"
 
 #include <cmath>
 #include <vector>
@@ -411,19 +412,28 @@ __device__ __forceinline__ void argmax_combine(float& v, int& i, float ov, int o
   if (ov > v || (ov == v && oi > i)) { v = ov; i = oi; }
 }
 
+// A row is shared by the `csz` CTAs of a cluster (csz = 1, 2 or 4: at batch 64 one CTA per row would leave 84 SMs idle):
+// CTA r scans the r-th slice of the row, stores its (value, index) into CTA 0's shared memory over DSMEM, and CTA 0
+// merges after one cluster barrier.  The "last maximal index" rule is order-independent, so the split does not show.
 __global__ void __launch_bounds__(1024)
 argmax_last_kernel(const float* __restrict__ logits, int ld, int32_t* __restrict__ idx, float* __restrict__ val,
-                   int V, int index_offset) {
+                   int V, int index_offset, int csz) {
   pdl_trigger();
   pdl_wait();
   __shared__ float sv[32];
   __shared__ int si[32];
-  const float* row = logits + (int64_t)blockIdx.x * ld;
+  __shared__ float cv[4];
+  __shared__ int ci[4];
+  const int r = blockIdx.x / csz, rank = blockIdx.x - r * csz;
+  const float* row = logits + (int64_t)r * ld;
   float bv = -INFINITY;
   int bi = -1;
   const int v4 = V >> 2;
+  const int per = (v4 + csz - 1) / csz;
+  const int j1 = min(v4, (rank + 1) * per);
   const float4* row4 = reinterpret_cast<const float4*>(row);
-  for (int j = threadIdx.x; j < v4; j += blockDim.x) {
+#pragma unroll 4
+  for (int j = rank * per + threadIdx.x; j < j1; j += blockDim.x) {
     const float4 f = __ldg(row4 + j);
     const int base = j << 2;
     argmax_combine(bv, bi, f.x, base);
@@ -431,7 +441,8 @@ argmax_last_kernel(const float* __restrict__ logits, int ld, int32_t* __restrict
     argmax_combine(bv, bi, f.z, base + 2);
     argmax_combine(bv, bi, f.w, base + 3);
   }
-  for (int j = (v4 << 2) + threadIdx.x; j < V; j += blockDim.x) argmax_combine(bv, bi, __ldg(row + j), j);
+  if (rank == csz - 1)
+    for (int j = (v4 << 2) + threadIdx.x; j < V; j += blockDim.x) argmax_combine(bv, bi, __ldg(row + j), j);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
@@ -451,10 +462,23 @@ argmax_last_kernel(const float* __restrict__ logits, int ld, int32_t* __restrict
       const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
       argmax_combine(bv, bi, ov, oi);
     }
-    if (lane == 0) {
-      idx[blockIdx.x] = bi + index_offset;
-      if (val) val[blockIdx.x] = bv;
+    if (lane == 0 && csz > 1) {
+      asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(ptx::mapa_u32(smem_u32(&cv[rank]), 0)), "f"(bv) : "memory");
+      asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(ptx::mapa_u32(smem_u32(&ci[rank]), 0)), "r"(bi) : "memory");
     }
+  }
+  if (csz > 1) {
+    ptx::cluster_sync_all();
+    if (rank != 0) return;
+    if (threadIdx.x == 0) {
+      bv = cv[0];
+      bi = ci[0];
+      for (int c = 1; c < csz; ++c) argmax_combine(bv, bi, cv[c], ci[c]);
+    }
+  }
+  if (threadIdx.x == 0) {
+    idx[r] = bi + index_offset;
+    if (val) val[r] = bv;
   }
 }
 
@@ -464,8 +488,10 @@ extern "C" int nvc_argmax_last(nvc_ctx* ctx, const float* logits, int ld, int32_
   NVC_REQUIRE(ctx, B >= 0 && V > 0 && ld >= V, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, ld % 4 == 0, NVC_ESHAPE, "ld must be a multiple of 4");
   if (B == 0) return NVC_OK;
-  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, argmax_last_kernel, dim3(B), dim3(1024), 0, nvc_stream(stream), logits, ld, idx,
-                                 val, V, index_offset));
+  // two 1024-thread CTAs fit one SM: the widest cluster that keeps the grid within one resident wave
+  const int csz = (V >= 16384 && 4 * B <= 2 * ctx->num_sms) ? 4 : (V >= 16384 && 2 * B <= 2 * ctx->num_sms) ? 2 : 1;
+  NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, argmax_last_kernel, dim3(B * csz), dim3(1024), 0, nvc_stream(stream), csz,
+                                         logits, ld, idx, val, V, index_offset, csz));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;

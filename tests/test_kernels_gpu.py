@@ -197,16 +197,20 @@ def test_gather_rows_bit_exact(ctx):
     assert torch.equal(xo.cpu(), x[rows.long()]) and torch.equal(ro.cpu(), r[rows.long()])
 
 
-@pytest.mark.parametrize("B,V", [(1, 151936), (64, 151936), (3, 1000), (2, 18992)])
+@pytest.mark.parametrize("B,V", [(1, 151936), (64, 151936), (3, 1000), (2, 18992), (100, 151936), (200, 32000), (7, 18998),
+                                 (74, 16385)])
 def test_argmax_last_index(ctx, B, V):
+    """rows are split over clusters of 4 / 2 / 1 CTAs by batch (elementwise.cu nvc_argmax_last): every width, ragged V"""
     g = torch.Generator().manual_seed(V)
-    logits = torch.randn(B, V, generator=g)
+    logits = torch.randn(B, (V + 3) // 4 * 4, generator=g)[:, :V]
     # force ties: the reference's Iterator::max_by keeps the LAST maximum (llm_engine.rs:135-142)
     mx = logits.max(dim=1).values
     for b in range(B):
         logits[b, (b * 37) % V] = mx[b]
         logits[b, V - 1 - (b * 11) % 50] = mx[b]
-    idx, val = ctx.argmax_last(logits.cuda(), index_offset=5)
+    dev = torch.full((B, (V + 3) // 4 * 4), float("inf"), device="cuda")[:, :V]      # +inf in the row padding: never read
+    dev.copy_(logits)
+    idx, val = ctx.argmax_last(dev, index_offset=5)
     want = [O.argmax_last(logits[b].numpy()) + 5 for b in range(B)]
     assert idx.cpu().tolist() == want
     assert torch.equal(val.cpu(), logits.max(dim=1).values)

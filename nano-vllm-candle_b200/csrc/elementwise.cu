@@ -406,43 +406,20 @@ extern "C" int nvc_gather_rows(nvc_ctx* ctx, const nvc_bf16* x, const float* res
 
 // ------------------------------------------------------------------------------------
 // K8 argmax with the reference's tie rule (LAST maximal index)  (llm_engine.rs:135-142)
-// one CTA per row; float4 loads; (value, index) reduced with "greater, or equal and later".
+// float4 loads; (value, index) reduced with "greater, or equal and later".
 // ------------------------------------------------------------------------------------
 __device__ __forceinline__ void argmax_combine(float& v, int& i, float ov, int oi) {
   if (ov > v || (ov == v && oi > i)) { v = ov; i = oi; }
 }
 
-// A row is shared by the `csz` CTAs of a cluster (csz = 1, 2 or 4: at batch 64 one CTA per row would leave 84 SMs idle):
-// CTA r scans the r-th slice of the row, stores its (value, index) into CTA 0's shared memory over DSMEM, and CTA 0
-// merges after one cluster barrier.  The "last maximal index" rule is order-independent, so the split does not show.
-__global__ void __launch_bounds__(1024)
-argmax_last_kernel(const float* __restrict__ logits, int ld, int32_t* __restrict__ idx, float* __restrict__ val,
-                   int V, int index_offset, int csz) {
-  pdl_trigger();
-  pdl_wait();
+// Block reduce of the threads' (value, index) candidates, then - when the row is shared by the `csz` CTAs of a cluster -
+// every CTA stores its pair into CTA 0's shared memory over DSMEM and CTA 0 merges after one cluster barrier.
+__device__ __forceinline__ void argmax_finish_row(float bv, int bi, int r, int rank, int csz, int32_t* __restrict__ idx,
+                                                  float* __restrict__ val, int index_offset) {
   __shared__ float sv[32];
   __shared__ int si[32];
   __shared__ float cv[4];
   __shared__ int ci[4];
-  const int r = blockIdx.x / csz, rank = blockIdx.x - r * csz;
-  const float* row = logits + (int64_t)r * ld;
-  float bv = -INFINITY;
-  int bi = -1;
-  const int v4 = V >> 2;
-  const int per = (v4 + csz - 1) / csz;
-  const int j1 = min(v4, (rank + 1) * per);
-  const float4* row4 = reinterpret_cast<const float4*>(row);
-#pragma unroll 4
-  for (int j = rank * per + threadIdx.x; j < j1; j += blockDim.x) {
-    const float4 f = __ldg(row4 + j);
-    const int base = j << 2;
-    argmax_combine(bv, bi, f.x, base);
-    argmax_combine(bv, bi, f.y, base + 1);
-    argmax_combine(bv, bi, f.z, base + 2);
-    argmax_combine(bv, bi, f.w, base + 3);
-  }
-  if (rank == csz - 1)
-    for (int j = (v4 << 2) + threadIdx.x; j < V; j += blockDim.x) argmax_combine(bv, bi, __ldg(row + j), j);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
@@ -482,14 +459,48 @@ argmax_last_kernel(const float* __restrict__ logits, int ld, int32_t* __restrict
   }
 }
 
+// widest cluster (4 / 2 / 1 CTAs per row) that keeps the grid within one resident wave of two 1024-thread CTAs per SM
+static int argmax_cluster_width(const nvc_ctx* ctx, int B, int V) {
+  return (V >= 16384 && 4 * B <= 2 * ctx->num_sms) ? 4 : (V >= 16384 && 2 * B <= 2 * ctx->num_sms) ? 2 : 1;
+}
+
+// A row is shared by the `csz` CTAs of a cluster (csz = 1, 2 or 4: at batch 64 one CTA per row would leave 84 SMs idle):
+// CTA r scans the r-th slice of the row, stores its (value, index) into CTA 0's shared memory over DSMEM, and CTA 0
+// merges after one cluster barrier.  The "last maximal index" rule is order-independent, so the split does not show.
+__global__ void __launch_bounds__(1024)
+argmax_last_kernel(const float* __restrict__ logits, int ld, int32_t* __restrict__ idx, float* __restrict__ val,
+                   int V, int index_offset, int csz) {
+  pdl_trigger();
+  pdl_wait();
+  const int r = blockIdx.x / csz, rank = blockIdx.x - r * csz;
+  const float* row = logits + (int64_t)r * ld;
+  float bv = -INFINITY;
+  int bi = -1;
+  const int v4 = V >> 2;
+  const int per = (v4 + csz - 1) / csz;
+  const int j1 = min(v4, (rank + 1) * per);
+  const float4* row4 = reinterpret_cast<const float4*>(row);
+#pragma unroll 4
+  for (int j = rank * per + threadIdx.x; j < j1; j += blockDim.x) {
+    const float4 f = __ldg(row4 + j);
+    const int base = j << 2;
+    argmax_combine(bv, bi, f.x, base);
+    argmax_combine(bv, bi, f.y, base + 1);
+    argmax_combine(bv, bi, f.z, base + 2);
+    argmax_combine(bv, bi, f.w, base + 3);
+  }
+  if (rank == csz - 1)
+    for (int j = (v4 << 2) + threadIdx.x; j < V; j += blockDim.x) argmax_combine(bv, bi, __ldg(row + j), j);
+  argmax_finish_row(bv, bi, r, rank, csz, idx, val, index_offset);
+}
+
 extern "C" int nvc_argmax_last(nvc_ctx* ctx, const float* logits, int ld, int32_t* idx, float* val,
                                int B, int V, int index_offset, void* stream) {
   NVC_REQUIRE(ctx, ctx && logits && idx, NVC_EINVAL, "null pointer");
   NVC_REQUIRE(ctx, B >= 0 && V > 0 && ld >= V, NVC_EINVAL, "bad sizes");
   NVC_REQUIRE(ctx, ld % 4 == 0, NVC_ESHAPE, "ld must be a multiple of 4");
   if (B == 0) return NVC_OK;
-  // two 1024-thread CTAs fit one SM: the widest cluster that keeps the grid within one resident wave
-  const int csz = (V >= 16384 && 4 * B <= 2 * ctx->num_sms) ? 4 : (V >= 16384 && 2 * B <= 2 * ctx->num_sms) ? 2 : 1;
+  const int csz = argmax_cluster_width(ctx, B, V);
   NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, argmax_last_kernel, dim3(B * csz), dim3(1024), 0, nvc_stream(stream), csz,
                                          logits, ld, idx, val, V, index_offset, csz));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
@@ -529,12 +540,10 @@ __device__ __forceinline__ float gumbel_from_bits(uint32_t x) {
 __global__ void __launch_bounds__(1024)
 sample_gumbel_kernel(const float* __restrict__ logits, int ld, const float* __restrict__ temperatures,
                      const uint64_t* __restrict__ streams, uint64_t seed, int32_t* __restrict__ idx,
-                     float* __restrict__ val, int V, int index_offset) {
+                     float* __restrict__ val, int V, int index_offset, int csz) {
   pdl_trigger();
   pdl_wait();
-  __shared__ float sv[32];
-  __shared__ int si[32];
-  const int b = blockIdx.x;
+  const int b = blockIdx.x / csz, rank = blockIdx.x - b * csz;     // a row is shared by a cluster, as in the argmax
   const float* row = logits + (int64_t)b * ld;
   const float T = fmaxf(__ldg(temperatures + b), 1e-6f);          // llm_engine.rs:104
   const uint64_t stream = __ldg(streams + b);
@@ -544,8 +553,10 @@ sample_gumbel_kernel(const float* __restrict__ logits, int ld, const float* __re
   int bi = -1;
   // index_offset % 4 == 0 and V % 4 == 0: one Philox block covers the float4 at local index 4j
   const int v4 = V >> 2;
+  const int per = (v4 + csz - 1) / csz;
+  const int j1 = min(v4, (rank + 1) * per);
   const float4* row4 = reinterpret_cast<const float4*>(row);
-  for (int j = threadIdx.x; j < v4; j += blockDim.x) {
+  for (int j = rank * per + threadIdx.x; j < j1; j += blockDim.x) {
     const float4 f = __ldg(row4 + j);
     const uint4 n = philox4x32_10(make_uint4((uint32_t)((index_offset >> 2) + j), s_lo, s_hi, 0u), key);
     const int base = j << 2;
@@ -554,30 +565,7 @@ sample_gumbel_kernel(const float* __restrict__ logits, int ld, const float* __re
     argmax_combine(bv, bi, __fdiv_rn(f.z, T) + gumbel_from_bits(n.z), base + 2);
     argmax_combine(bv, bi, __fdiv_rn(f.w, T) + gumbel_from_bits(n.w), base + 3);
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-    argmax_combine(bv, bi, ov, oi);
-  }
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-  if (lane == 0) { sv[wid] = bv; si[wid] = bi; }
-  __syncthreads();
-  if (wid == 0) {
-    const int nw = (blockDim.x + 31) >> 5;
-    bv = lane < nw ? sv[lane] : -INFINITY;
-    bi = lane < nw ? si[lane] : -1;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      argmax_combine(bv, bi, ov, oi);
-    }
-    if (lane == 0) {
-      idx[b] = bi + index_offset;
-      if (val) val[b] = bv;
-    }
-  }
+  argmax_finish_row(bv, bi, b, rank, csz, idx, val, index_offset);
 }
 
 extern "C" int nvc_sample_gumbel(nvc_ctx* ctx, const float* logits, int ld, const float* temperatures,
@@ -588,8 +576,9 @@ extern "C" int nvc_sample_gumbel(nvc_ctx* ctx, const float* logits, int ld, cons
   NVC_REQUIRE(ctx, ld % 4 == 0 && V % 4 == 0 && index_offset % 4 == 0 && index_offset >= 0, NVC_ESHAPE,
               "ld, V and index_offset must be multiples of 4");
   if (B == 0) return NVC_OK;
-  NVC_CUDA_CHECK(ctx, nvc_launch(ctx, sample_gumbel_kernel, dim3(B), dim3(1024), 0, nvc_stream(stream), logits, ld,
-                                 temperatures, streams, seed, idx, val, V, index_offset));
+  const int csz = argmax_cluster_width(ctx, B, V);
+  NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, sample_gumbel_kernel, dim3(B * csz), dim3(1024), 0, nvc_stream(stream), csz,
+                                         logits, ld, temperatures, streams, seed, idx, val, V, index_offset, csz));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;

@@ -217,7 +217,7 @@ def test_argmax_last_index(ctx, B, V):
 
 
 # ----------------------------------------------------------------------------- K8s sampling
-@pytest.mark.parametrize("B,V,offset", [(5, 2048, 0), (3, 151936, 0), (4, 18992, 37984)])
+@pytest.mark.parametrize("B,V,offset", [(5, 2048, 0), (3, 151936, 0), (4, 18992, 37984), (100, 32768, 0), (64, 151936, 0)])
 def test_sample_gumbel_matches_oracle(ctx, B, V, offset):
     """Device Gumbel-max draw against oracle/sampling_oracle.py (same Philox counters).  The noise
     bits are exact; logf differs from numpy's float64 log by ulps, so the device's token must be
@@ -226,7 +226,7 @@ def test_sample_gumbel_matches_oracle(ctx, B, V, offset):
     from oracle import sampling_oracle as S
     g = torch.Generator().manual_seed(B * 7 + V)
     logits = torch.randn(B, V, generator=g) * 3.0
-    temps = torch.tensor([0.5, 1.0, 2.0, 1e-9, 0.8][:B], dtype=torch.float32)
+    temps = torch.tensor([[0.5, 1.0, 2.0, 1e-9, 0.8][b % 5] for b in range(B)], dtype=torch.float32)
     streams = torch.tensor([S.stream_id(10 + b, 3 * b) for b in range(B)], dtype=torch.int64)
     seed = 0x1234_5678_9ABC_DEF0
     idx, val = ctx.sample_gumbel(logits.cuda(), temps.cuda(), streams.cuda(), seed, index_offset=offset)
@@ -241,7 +241,7 @@ def test_sample_gumbel_matches_oracle(ctx, B, V, offset):
         assert abs(float(val[b]) - sc[t]) <= tol
         exact += int(S.sample(logits[b].numpy(), float(temps[b]), seed, int(streams[b]), offset) == int(idx[b]))
     diag(f"[sample_gumbel B={B} V={V}] {exact}/{B} draws identical to the oracle")
-    assert exact >= B - 1
+    assert exact >= B - 1 - B // 32
 
 
 def test_sample_gumbel_distribution_and_reproducibility(ctx):

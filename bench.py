@@ -419,7 +419,9 @@ def measure(env: _Env, model: str, batch: int, prompt_len: int, K: int, W: int, 
     rec = {
         "value": batch / (ms_step * 1e-3), "ms_per_step": ms_step, "clocks": clocks,
         "e2e": {"value": batch * K / t_e2e, "unit": "tok/s", "ms_per_step": t_e2e / K * 1e3,
-                "h2d_bytes_per_step": runner.h2d_bytes_last_step(), "d2h_bytes_per_step": batch * 4},
+                "h2d_bytes_per_step": runner.h2d_bytes_last_step(), "d2h_bytes_per_step": batch * 4,
+                "contexts": f"{prompt_len + W + 1}..{ctx_len} over the K engine steps (host wall clock, max over ranks); the "
+                            f"device-timed replay behind `value` runs K times at the last one ({ctx_len})"},
         "gpu_launches": launches_per_step * K,
         "roofline": {"kernel": "pdmma::paged_decode_mma_kernel (K5)", "bound": "hbm", "achieved": achieved,
                      "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": achieved / pk["hbm_gbs"],

@@ -7,6 +7,8 @@
 #include "internal.h"
 #include "ptx.cuh"
 
+extern int g_nvc_debug[8];   // prefill_attn.cu: [6] == 1 switches the sampling kernel's screening off (tests)
+
 #include <cmath>
 #include <vector>
 
@@ -537,33 +539,78 @@ __device__ __forceinline__ float gumbel_from_bits(uint32_t x) {
   return -logf(-logf(u));
 }
 
+// Screening: almost every element loses by a wide margin, and the exact score costs two logf + one IEEE division.  After
+// its first (exact) float4 every thread knows the CTA's best score so far (`s_thr`, kept current with shared-memory
+// atomics) and evaluates an UPPER BOUND of each later score with the fast intrinsics: x * (1/T) is within 2 ulp of x / T
+// (margin |x| * 1e-6), and for u <= 1 - 2^-10 the two MUFU.LG2 give the Gumbel term to 2e-4 (margin 2e-3); draws nearer to
+// one than that (1 in 1024) always take the exact path.  Only a float4 with an element whose bound reaches the threshold
+// is evaluated exactly, so the result is the one the unscreened kernel gives, bit for bit (GPU test).
+__device__ __forceinline__ int float_order_key(float x) {
+  const int b = __float_as_int(x);
+  return b >= 0 ? b : b ^ 0x7fffffff;
+}
+__device__ __forceinline__ float float_from_order_key(int k) { return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff); }
+
+__device__ __forceinline__ bool gumbel_may_reach(float l, float rT, uint32_t bits, float thr) {
+  const float u = (float)(((bits >> 9) << 1) | 1u) * 5.9604644775390625e-08f;
+  const float inner = -0.69314718f * __log2f(u);
+  const float g = -0.69314718f * __log2f(inner);
+  const float x = l * rT;
+  const float ub = x + g + 2e-3f + fabsf(x) * 1e-6f;
+  return (bits >> 22) == 0x3ffu || !(ub < thr);           // NaN / inf in the bound: not "below", so exact
+}
+
 __global__ void __launch_bounds__(1024)
 sample_gumbel_kernel(const float* __restrict__ logits, int ld, const float* __restrict__ temperatures,
                      const uint64_t* __restrict__ streams, uint64_t seed, int32_t* __restrict__ idx,
-                     float* __restrict__ val, int V, int index_offset, int csz) {
+                     float* __restrict__ val, int V, int index_offset, int csz, int screen) {
   pdl_trigger();
   pdl_wait();
+  __shared__ int s_thr;
   const int b = blockIdx.x / csz, rank = blockIdx.x - b * csz;     // a row is shared by a cluster, as in the argmax
   const float* row = logits + (int64_t)b * ld;
   const float T = fmaxf(__ldg(temperatures + b), 1e-6f);          // llm_engine.rs:104
+  const float rT = 1.0f / T;
   const uint64_t stream = __ldg(streams + b);
   const uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
   const uint32_t s_lo = (uint32_t)stream, s_hi = (uint32_t)(stream >> 32);
   float bv = -INFINITY;
   int bi = -1;
+  if (threadIdx.x == 0) s_thr = float_order_key(-INFINITY);
+  __syncthreads();
   // index_offset % 4 == 0 and V % 4 == 0: one Philox block covers the float4 at local index 4j
   const int v4 = V >> 2;
   const int per = (v4 + csz - 1) / csz;
   const int j1 = min(v4, (rank + 1) * per);
+  const int jbeg = rank * per;
   const float4* row4 = reinterpret_cast<const float4*>(row);
-  for (int j = rank * per + threadIdx.x; j < j1; j += blockDim.x) {
-    const float4 f = __ldg(row4 + j);
-    const uint4 n = philox4x32_10(make_uint4((uint32_t)((index_offset >> 2) + j), s_lo, s_hi, 0u), key);
-    const int base = j << 2;
-    argmax_combine(bv, bi, __fdiv_rn(f.x, T) + gumbel_from_bits(n.x), base);
-    argmax_combine(bv, bi, __fdiv_rn(f.y, T) + gumbel_from_bits(n.y), base + 1);
-    argmax_combine(bv, bi, __fdiv_rn(f.z, T) + gumbel_from_bits(n.z), base + 2);
-    argmax_combine(bv, bi, __fdiv_rn(f.w, T) + gumbel_from_bits(n.w), base + 3);
+  for (int j0 = jbeg; j0 < j1; j0 += blockDim.x) {                 // block-uniform trip count (the barrier below)
+    const int j = j0 + threadIdx.x;
+    const bool first = j0 == jbeg;
+    if (j < j1) {
+      const float4 f = __ldg(row4 + j);
+      const uint4 n = philox4x32_10(make_uint4((uint32_t)((index_offset >> 2) + j), s_lo, s_hi, 0u), key);
+      bool exact = first || !screen;
+      if (!exact) {
+        const float thr = float_from_order_key(*reinterpret_cast<volatile int*>(&s_thr));
+        exact = gumbel_may_reach(f.x, rT, n.x, thr) | gumbel_may_reach(f.y, rT, n.y, thr) |
+                gumbel_may_reach(f.z, rT, n.z, thr) | gumbel_may_reach(f.w, rT, n.w, thr);
+      }
+      if (exact) {
+        const int base = j << 2;
+        const float before = bv;
+        argmax_combine(bv, bi, __fdiv_rn(f.x, T) + gumbel_from_bits(n.x), base);
+        argmax_combine(bv, bi, __fdiv_rn(f.y, T) + gumbel_from_bits(n.y), base + 1);
+        argmax_combine(bv, bi, __fdiv_rn(f.z, T) + gumbel_from_bits(n.z), base + 2);
+        argmax_combine(bv, bi, __fdiv_rn(f.w, T) + gumbel_from_bits(n.w), base + 3);
+        if (!first && bv > before) atomicMax(&s_thr, float_order_key(bv));
+      }
+    }
+    if (first && screen) {           // the CTA's best over everybody's first float4 becomes the first threshold
+      const float wm = warp_max(bv);
+      if ((threadIdx.x & 31) == 0) atomicMax(&s_thr, float_order_key(wm));
+      __syncthreads();
+    }
   }
   argmax_finish_row(bv, bi, b, rank, csz, idx, val, index_offset);
 }
@@ -578,7 +625,8 @@ extern "C" int nvc_sample_gumbel(nvc_ctx* ctx, const float* logits, int ld, cons
   if (B == 0) return NVC_OK;
   const int csz = argmax_cluster_width(ctx, B, V);
   NVC_CUDA_CHECK(ctx, nvc_launch_cluster(ctx, sample_gumbel_kernel, dim3(B * csz), dim3(1024), 0, nvc_stream(stream), csz,
-                                         logits, ld, temperatures, streams, seed, idx, val, V, index_offset, csz));
+                                         logits, ld, temperatures, streams, seed, idx, val, V, index_offset, csz,
+                                         g_nvc_debug[6] == 1 ? 0 : 1));
   NVC_CUDA_CHECK(ctx, cudaGetLastError());
   ctx->launches++;
   return NVC_OK;

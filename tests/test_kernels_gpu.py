@@ -244,6 +244,32 @@ def test_sample_gumbel_matches_oracle(ctx, B, V, offset):
     assert exact >= B - 1 - B // 32
 
 
+@pytest.mark.parametrize("B,V", [(64, 151936), (3, 18992), (150, 32768), (8, 65536)])
+def test_sample_gumbel_screening_is_exact(ctx, B, V):
+    """The fast upper-bound screen (elementwise.cu sample_gumbel_kernel) only skips elements that cannot win: tokens and
+    winning scores are bit-identical with the screen switched off, incl. rows of huge / tiny temperature, -inf masks, ties."""
+    import importlib
+    nvc = importlib.import_module("nano-vllm-candle_b200")
+    g = torch.Generator().manual_seed(B + V)
+    logits = torch.randn(B, V, generator=g) * 4.0
+    logits[0, : V // 2] = float("-inf")                       # a masked half row
+    logits[1 % B] = 1.25                                      # a constant row: the noise alone decides
+    logits[2 % B, ::7] = 30.0                                 # many equal front-runners
+    temps = torch.tensor([[0.5, 1.0, 2.0, 1e-9, 0.8, 50.0][b % 6] for b in range(B)], dtype=torch.float32).cuda()
+    streams = (torch.arange(B, dtype=torch.int64) * 977 + 5).cuda()
+    dev = logits.cuda()
+    outs = []
+    for off in (1, 0):
+        nvc.lib().nvc_debug_set(6, off)
+        try:
+            outs.append([ctx.sample_gumbel(dev, temps, streams, seed, index_offset=8) for seed in (1, 2, 0xDEADBEEF)])
+            torch.cuda.synchronize()
+        finally:
+            nvc.lib().nvc_debug_set(6, 0)
+    for (i0, v0), (i1, v1) in zip(*outs):
+        assert torch.equal(i0, i1) and torch.equal(v0, v1)
+
+
 def test_sample_gumbel_distribution_and_reproducibility(ctx):
     """4096 independent streams over a 16-way row: frequencies follow the distribution the
     reference samples from (llm_engine.rs:100-125); same (seed, stream) -> same token; the draw

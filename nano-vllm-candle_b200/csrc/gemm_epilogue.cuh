@@ -8,7 +8,10 @@
 // scattered to the paged cache at slot_mapping[row] - so the separate pass over the QKV buffer (120-160 us for 600 MB at
 // 32 768 tokens, 10-13 % of a 0.6B prefill step) disappears.  A 256-column tile is two heads of one row; the warp parks a head
 // (32 rows x 256 B) in its staging buffer and works on it with the lane mapping and arithmetic of qk_norm_rope_store_kernel.
-enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1, NVC_EPI_QK_NORM_ROPE = 3 };
+// NVC_EPI_TRANSPOSE (pair kernel, persistent schedule): the operands are swapped by the host - the kernel's "A" rows are
+// weight rows, its "W" rows are tokens - and the epilogue stores its accumulator row r as COLUMN r of C: lm_head at decode
+// batch sizes, where 64 tokens would fill a quarter of a 256-row MMA and only one CTA of the pair would hold valid rows.
+enum { NVC_EPI_NONE = 0, NVC_EPI_SILU_MUL = 1, NVC_EPI_TRANSPOSE = 2, NVC_EPI_QK_NORM_ROPE = 3 };
 
 struct QkEpi {
   const uint4* qw = nullptr;         // q_norm weight [128] bf16

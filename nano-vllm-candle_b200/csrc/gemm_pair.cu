@@ -46,12 +46,14 @@ constexpr int kRingBudget = 200 * 1024;
 // into one accumulator stage, measured no gain - 8B gate_up at batch 256: 53.1 vs 53.6 us - and were deleted in round 2.)
 template <int NT>
 struct PairCfg {
-  static_assert(NT >= 128 && NT <= 256 && NT % 32 == 0, "tile width");
+  static_assert(NT == 64 || (NT >= 128 && NT <= 256 && NT % 32 == 0), "tile width");
   static constexpr int NH = NT;                          // N of one tcgen05.mma
   static constexpr int kBoxRowsB = NH / 2;               // rows of W one CTA supplies per MMA (multiple of 8)
   static constexpr int kBytesB = (NT / 2) * BK * 2;      // this CTA's rows of the weight tile per k-block
   static constexpr int kStageBytes = kBytesA + kBytesB;
-  static constexpr int kStages = kRingBudget / kStageBytes < 6 ? kRingBudget / kStageBytes : 6;
+  // NT = 64 is the swapped-operand lm_head (NVC_EPI_TRANSPOSE): 20 KB stages, a deeper ring keeps as many bytes in flight
+  static constexpr int kMaxStages = NT == 64 ? 10 : 6;
+  static constexpr int kStages = kRingBudget / kStageBytes < kMaxStages ? kRingBudget / kStageBytes : kMaxStages;
   static constexpr int kAccStages = 2;
   static constexpr int kNumBars = 2 * kStages + 4;       // full[], empty[], tmem_full[2], tmem_empty[2]
   static constexpr int kOffStage = (kStages * kStageBytes + kNumBars * 8 + 16 + 127) & ~127;   // 4 epilogue warps x row staging
@@ -428,6 +430,28 @@ gemm_pair_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constan
           continue;
         }
       }
+      if (epi == NVC_EPI_TRANSPOSE) {
+        // accumulator row `grow` (a weight row) is column `grow` of the fp32 C; the warp's 32 rows are 128 contiguous bytes of
+        // every C row (token) they touch
+        float* Ct = reinterpret_cast<float*>(C) + grow;
+#pragma unroll 1
+        for (int c = 0; c < cfg::kChunks; c += 2) {
+          uint32_t v[32];
+          ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(acc * 256) + cfg::chunk_col(c), v);
+          ptx::tmem_ld_32x32b_x16(taddr + (uint32_t)(acc * 256) + cfg::chunk_col(c + 1), v + 16);
+          ptx::tmem_ld_wait();
+          const int col0 = n_tile * NT + c * 16;
+          if (row_ok) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (col0 + j < N) Ct[(int64_t)(col0 + j) * ldc] = __uint_as_float(v[j]);
+          }
+        }
+        ptx::tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cluster(leader_tmem_empty0 + 8u * acc);
+        continue;
+      }
       RowStage st = make_row_stage(smem_gen + cfg::kOffStage + q * cfg::kStageBuf, C, out_f32, epi, ldc,
                                    m_tile * kTileM + h * kHalf + q * 32, M, n_tile * NT, NT, N);
 #pragma unroll 1
@@ -504,16 +528,17 @@ int make_tma_2d(nvc_ctx* ctx, CUtensorMap* map, const void* base, uint64_t inner
   return NVC_OK;
 }
 
-#define NVC_PAIR_WIDTHS(X) X(128) X(160) X(192) X(224) X(256)
+#define NVC_PAIR_WIDTHS(X) X(64) X(128) X(160) X(192) X(224) X(256)
 
 template <int NT>
 int launch_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M, int N,
-                int K, int S, int epi, cudaStream_t stream, long long* trace, const QkEpi& qk = QkEpi{}) {
+                int K, int S, int epi, cudaStream_t stream, long long* trace, const QkEpi& qk = QkEpi{}, int ldw = 0) {
   using cfg = PairCfg<NT>;
+  if (ldw == 0) ldw = K;
   CUtensorMap ta, tb;
   int rc = make_tma_2d(ctx, &ta, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda * 2, BK, kHalf);
   if (rc) return rc;
-  rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)K * 2, BK, cfg::kBoxRowsB);
+  rc = make_tma_2d(ctx, &tb, W, (uint64_t)K, (uint64_t)N, (uint64_t)ldw * 2, BK, cfg::kBoxRowsB);
   if (rc) return rc;
   const int kb_total = K / BK;
   const int m_tiles = (M + kTileM - 1) / kTileM, n_tiles = (N + NT - 1) / NT;
@@ -640,6 +665,17 @@ extern "C" int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc
 #undef X
   NVC_REQUIRE(ctx, false, NVC_EINVAL, "unsupported pair tile width");
   return NVC_OK;
+}
+
+// lm_head at decode batch sizes with the operands swapped: logits[M tokens, N vocab] (fp32) = X [M, K] . W [N, K]^T computed
+// as W . X^T - 256 weight rows per MMA (128 per CTA of the pair, both CTAs' epilogues busy), the tokens as its 64 / 128
+// columns - and stored transposed (NVC_EPI_TRANSPOSE).  The 64 tokens of a decode step cost a quarter of the tensor time
+// of a 256-row token tile, and the weight stream is what the kernel waits for.
+extern "C" int nvc_gemm_pair_swapped(nvc_ctx* ctx, const nvc_bf16* X, int ldx, const nvc_bf16* W, float* C, int ldc, int M,
+                                     int N, int K, void* stream, long long* trace) {
+  if (M < 1 || M > 128 || K % BK != 0) return NVC_ENOTIMPL;
+  if (M <= 64) return launch_pair<64>(ctx, W, K, X, C, ldc, 1, N, M, K, 1, NVC_EPI_TRANSPOSE, nvc_stream(stream), trace, QkEpi{}, ldx);
+  return launch_pair<128>(ctx, W, K, X, C, ldc, 1, N, M, K, 1, NVC_EPI_TRANSPOSE, nvc_stream(stream), trace, QkEpi{}, ldx);
 }
 
 // K3 + K2 in one launch for the fused QKV projection of a prefill-sized step (src/models/qwen3.rs:205-234): returns

@@ -27,6 +27,8 @@ static int g_nvc_gemm_prefetch = getenv("NVC_GEMM_PREFETCH") ? atoi(getenv("NVC_
 
 static int g_nvc_gemm_ks = getenv("NVC_GEMM_KS") ? atoi(getenv("NVC_GEMM_KS")) : 1;
 static int g_nvc_gemm_pair = getenv("NVC_GEMM_PAIR") ? atoi(getenv("NVC_GEMM_PAIR")) : 1;
+// smallest N whose fp32 output at M <= 128 goes through the swapped-operand pair schedule (lm_head at decode batch sizes)
+static int g_nvc_swap_min_n = getenv("NVC_SWAP_MIN_N") ? atoi(getenv("NVC_SWAP_MIN_N")) : 32768;
 
 namespace {
 
@@ -543,6 +545,16 @@ static int gemm_impl(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W
   // profiles/r02_lm_head_sweep_pair.txt)
   const bool vocab_pair = force_bn == 0 && force_splits == 0 && epi == NVC_EPI_NONE && M >= 32 && M <= BM && Nout >= 65536 &&
                           K <= 1024 && g_nvc_gemm_pair;
+  // ... and with fp32 logits the operands go in swapped (weights as the 256-row MMA operand, transposed store): force_bn 513
+  // (fp32 logits for up to 128 tokens, any K: 64 x 151 936 x 1 024 68.0 -> 64.1 us, M = 1 62.3 -> 53.8, K = 4 096 224.7 ->
+  // 202.5 = 0.97 of the HBM peak; profiles/r02_lm_head_sweep_swapped.txt)
+  // Down to vocabulary shards of TP 4 for M <= 64 (37 984 columns: 25.5 -> 20.5 us); at 65..128 tokens only where it measured
+  // ahead (full vocabulary, or K >= 2 048 from 65 536 columns); the TP 8 shard (18 992) stays on the 1-CTA kernel (11.2 vs 13.2).
+  const bool swap_n = M <= 64 ? Nout >= g_nvc_swap_min_n : (Nout >= 131072 || (Nout >= 65536 && K >= 2048));
+  const bool vocab_swapped = force_bn == 0 && force_splits == 0 && epi == NVC_EPI_NONE && out_dtype == NVC_DT_F32 && M <= BM &&
+                             swap_n && g_nvc_gemm_pair;
+  if (vocab_swapped || (force_bn == 513 && out_dtype == NVC_DT_F32 && epi == NVC_EPI_NONE && M <= BM))
+    return nvc_gemm_pair_swapped(ctx, A, lda, W, reinterpret_cast<float*>(C), ldc, M, Nout, K, stream, trace);
   if (force_bn == 512 || vocab_pair || (force_bn == 0 && M > BM && g_nvc_gemm_pair))
     return nvc_gemm_pair(ctx, A, lda, W, C, ldc, out_dtype == NVC_DT_F32, M, Nout, K, force_splits, epi, stream, trace);
   int bn, kps, splits, cl = 1, ks = 0;

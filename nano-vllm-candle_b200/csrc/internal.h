@@ -24,6 +24,9 @@ int nvc_gemm_pair_init(nvc_ctx* ctx);
 // CTA-pair (cta_group::2) GEMM for M > 128; force_splits 0 = choose the in-cluster split-K factor
 int nvc_gemm_pair(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, void* C, int ldc, int out_f32, int M,
                   int N, int K, int force_splits, int epi, void* stream, long long* trace);
+// fp32 C [M <= 128 tokens, N] = X . W^T with the operands swapped in the pair kernel (lm_head at decode batch sizes)
+int nvc_gemm_pair_swapped(nvc_ctx* ctx, const nvc_bf16* X, int ldx, const nvc_bf16* W, float* C, int ldc, int M, int N, int K,
+                          void* stream, long long* trace);
 // K3 + K2 through the pair kernel's persistent epilogue; NVC_ENOTIMPL (nothing launched) when the shape takes another schedule
 int nvc_gemm_pair_qk(nvc_ctx* ctx, const nvc_bf16* A, int lda, const nvc_bf16* W, nvc_bf16* C, int ldc, int M, int N, int K,
                      const nvc_bf16* qw, const nvc_bf16* kw, float eps, const float* cos_sin, const int32_t* positions,

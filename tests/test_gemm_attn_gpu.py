@@ -100,6 +100,39 @@ def test_gemm_bf16(ctx, M, N, K, bn, splits, out_dtype):
     _close(out, ref, 2e-3, rtol, f"gemm M={M} N={N} K={K} bn={bn} s={splits} {out_dtype}")
 
 
+@pytest.mark.parametrize("M,N,K", [
+    (64, 151936, 1024),      # 0.6B lm_head at the bench's decode batch: 594 tiles of 256 weight rows, the last one half full
+    (40, 65616, 512),        # tokens not a multiple of the 32-row box (second CTA's token rows 40..63 zero-filled), ragged vocab
+    (100, 70000, 1024),      # 65..128 tokens: 128-column tiles
+    (128, 65536, 256),       # full 128 tokens, 4 k-blocks (shorter than the ring)
+    (1, 66000, 1024),        # a single token
+    (64, 1040, 192),         # small N: 5 tiles, fewer than the pairs (forced only)
+    (48, 37984, 1024),       # the TP 4 vocabulary shard
+    (128, 65536, 2048),      # 65..128 tokens take it from K = 2 048
+])
+def test_gemm_lm_head_swapped_operands(ctx, M, N, K):
+    """lm_head at decode batch sizes with the operands swapped in the pair kernel (weights as the 256-row MMA operand, fp32
+    logits stored transposed; gemm_pair.cu nvc_gemm_pair_swapped): against the fp32 oracle, against the unswapped pair
+    schedule, with a row stride on both sides, and as the automatic route of vocabulary-sized fp32 outputs."""
+    g = torch.Generator().manual_seed(M + N + K)
+    a_full = torch.randn(M, K + 64, generator=g).to(BF16).cuda()
+    a = a_full[:, :K]                                          # lda > K
+    w = (torch.randn(N, K, generator=g) / math.sqrt(K)).to(BF16).cuda()
+    ref = O.linear(a.float().cpu(), w.float().cpu())
+    buf = torch.full((M, N + 16), float("nan"), dtype=torch.float32, device="cuda")
+    out = ctx.gemm(a, w, out=buf[:, :N], force_bn=513)         # ldc > N: the padding columns must stay NaN
+    torch.cuda.synchronize()
+    _close(out, ref, 2e-3, 1e-5, f"swapped lm_head M={M} N={N} K={K}")
+    assert bool(torch.isnan(buf[:, N:]).all())
+    plain = ctx.gemm(a, w, out_dtype=torch.float32, force_bn=512)
+    diag(f"[lm_head swapped M={M} N={N} K={K}] bit-identical with the unswapped pair schedule: {torch.equal(plain, out)}, "
+         f"max diff {(plain - out).abs().max().item():.2e}")
+    assert (plain - out).abs().max().item() < 1e-3
+    auto = ctx.gemm(a, w, out_dtype=torch.float32)
+    if (M <= 64 and N >= 32768) or N >= 131072 or (N >= 65536 and K >= 2048):
+        assert torch.equal(auto, out)                          # the automatic route IS the swapped kernel
+
+
 @pytest.mark.parametrize("M,nh,kv,K", [
     (8200, 16, 8, 1024),      # 0.6B qkv at a prefill size: 33 m-tiles (last one ragged) x 16 tiles of two heads
     (32768, 16, 8, 1024),     # the bench's prefill step

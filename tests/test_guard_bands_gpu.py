@@ -65,7 +65,8 @@ def test_guard_elementwise(ctx):
 
 @pytest.mark.parametrize("M,N,K,out_dtype", [(1, 1024, 1024, BF16), (64, 2000, 512, BF16), (100, 1040, 192, torch.float32),
                                              (129, 272, 64, BF16), (333, 1040, 192, BF16), (300, 4112, 1024, torch.float32),
-                                             (64, 1024, 2048, BF16)])
+                                             (64, 1024, 2048, BF16), (64, 65616, 256, torch.float32),
+                                             (100, 65552, 128, torch.float32)])   # the last two: swapped-operand lm_head route
 def test_guard_gemm(ctx, M, N, K, out_dtype):
     g = torch.Generator().manual_seed(M + N)
     a = edged(torch.randn(M, K, generator=g).to(BF16))

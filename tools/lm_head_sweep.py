@@ -10,7 +10,7 @@ import torch
 ops = importlib.import_module("nano-vllm-candle_b200.ops")
 ctx = ops.Context(0)
 BF16 = torch.bfloat16
-V = 151936
+V = int(sys.argv[1]) if len(sys.argv) > 1 else 151936
 
 
 def timed(M, K, force_bn, iters=8, force_splits=0):
@@ -35,14 +35,17 @@ def timed(M, K, force_bn, iters=8, force_splits=0):
     return e0.elapsed_time(e1) * 1e3 / iters
 
 
-for M, K in ((64, 1024), (1, 1024), (64, 4096), (128, 5120)):
+for M, K in ((64, 1024), (1, 1024), (16, 1024), (128, 1024), (64, 4096), (128, 5120)):
     gb = (V * K * 2 + M * V * 4) / 1e3
     row = []
-    for fb in (0, 1256, 1128, 2128, 2064, 4064, 21256, 41128, 42128):
+    for fb in (0, 1256, 21256):
         us = timed(M, K, fb)
         row.append(f"{fb}:{'-' if us is None else f'{us:.1f}us/{gb / us:.0f}GB/s'}")
     # the CTA-pair kernel (persistent, two accumulator stages) on the same decode shape: force_bn 512, tile width NT
-    for nt in (256, 224, 208, 192, 160, 128):
+    for nt in (256, 192):
         us = timed(M, K, 512, force_splits=1000 + nt)
         row.append(f"pair{nt}:{'-' if us is None else f'{us:.1f}us/{gb / us:.0f}GB/s'}")
-    print(f"M={M} K={K}  " + "  ".join(row), flush=True)
+    # operands swapped in the pair kernel (weights as the 256-row MMA operand, transposed fp32 store): force_bn 513
+    us = timed(M, K, 513)
+    row.append(f"swapped:{'-' if us is None else f'{us:.1f}us/{gb / us:.0f}GB/s'}")
+    print(f"V={V} M={M} K={K}  " + "  ".join(row), flush=True)

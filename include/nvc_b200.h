@@ -254,6 +254,20 @@ int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf
                           float scale, nvc_bf16* out, void* workspace, size_t workspace_bytes,
                           void* stream);
 
+/* K5, allocation-free variant.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same
+ * kernels and results as nvc_paged_decode_attn; the KV-split partials go to a static device array inside the
+ * library (nvc_paged_decode_static_scratch_bytes() = 4 MiB per GPU, held until exit) instead of a caller workspace.
+ * Returns NVC_ENOMEM (nothing launched, message in nvc_last_error) when the shape's partials exceed that array -
+ * the library's own split choice needs at most ~2.5 MB.  Calls no cudaMalloc / cudaFree.  All calls on a device
+ * share the array: calls that overlap on the GPU (different streams) race; nothing in it has to be cleared between
+ * calls (every partial read is written by the same call). */
+size_t nvc_paged_decode_static_scratch_bytes(void);
+int nvc_paged_decode_attn_static(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
+                                 const nvc_bf16* v_cache, const int32_t* block_tables, int max_blocks,
+                                 const int32_t* context_lens, int B, int nh, int kv, int hd, int block_size,
+                                 float scale, nvc_bf16* out, void* stream);
+
 /* K6. Replaces SiluAndMul::forward (src/layers/activation.rs:13-18):
  * out[n, i] = silu(x[n, i]) * x[n, I + i]. */
 int nvc_silu_and_mul(nvc_ctx* ctx, const nvc_bf16* x, nvc_bf16* out, int N, int I, void* stream);

@@ -86,6 +86,7 @@ def _declare(l: C.CDLL) -> None:
         "nvc_prefill_attn_varlen": [_vp, _vp, _i, _vp, _i, _vp, _i, _vp, _i, _i, _i, _i, _i, _i, _f, _vp, _vp],
         "nvc_prefill_attn_paged": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _i, _f, _vp, _vp],
         "nvc_paged_decode_attn": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp, _sz, _vp],
+        "nvc_paged_decode_attn_static": [_vp, _vp, _i, _vp, _vp, _vp, _i, _vp, _i, _i, _i, _i, _i, _f, _vp, _vp],
         "nvc_silu_and_mul": [_vp, _vp, _vp, _i, _i, _vp],
         "nvc_gather_rows": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _vp],
         "nvc_argmax_last": [_vp, _vp, _i, _vp, _vp, _i, _i, _i, _vp],
@@ -110,6 +111,8 @@ def _declare(l: C.CDLL) -> None:
     l.nvc_ctx_nvls_status.argtypes = [_vp]
     l.nvc_paged_decode_workspace_bytes.restype = _sz
     l.nvc_paged_decode_workspace_bytes.argtypes = [_i, _i, _i, _i]
+    l.nvc_paged_decode_static_scratch_bytes.restype = _sz
+    l.nvc_paged_decode_static_scratch_bytes.argtypes = []
     from . import _engine_sigs
     _engine_sigs.declare(l)
 

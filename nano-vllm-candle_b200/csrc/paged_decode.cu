@@ -18,6 +18,14 @@
 
 extern int g_nvc_debug[8];
 
+// Scratch of nvc_paged_decode_attn_static (the entry point that allocates nothing): the KV-split partials (fp32 O rows +
+// (max, sum) pairs) live in this file-scope array instead of a caller workspace.  4 MiB per GPU that loads the library,
+// held until exit.  In HOST code `g_pd_static_scratch` is only a stand-in for the symbol: the device address comes from
+// cudaGetSymbolAddress (nvc_paged_decode_init, once per device, that device current) and is what the kernels receive.
+#define NVC_PD_STATIC_SCRATCH_BYTES (4u << 20)
+static __device__ __align__(256) unsigned char g_pd_static_scratch[NVC_PD_STATIC_SCRATCH_BYTES];
+static void* g_pd_static_scratch_addr[64] = {nullptr};   // device address of the array, per device ordinal
+
 namespace {
 
 __device__ __forceinline__ float fast_exp2(float x) {
@@ -137,6 +145,12 @@ extern "C" int nvc_paged_decode_init(nvc_ctx* ctx) {
                                            pdmma::smem_bytes<4>()));
   NVC_CUDA_CHECK(ctx, cudaFuncSetAttribute(pdmma::paged_decode_mma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            pdmma::smem_bytes<2>()));
+  // device address of the static scratch (ctx creation runs with ctx->device current)
+  if (ctx->device >= 0 && ctx->device < 64 && g_pd_static_scratch_addr[ctx->device] == nullptr) {
+    void* p = nullptr;
+    NVC_CUDA_CHECK(ctx, cudaGetSymbolAddress(&p, g_pd_static_scratch));
+    g_pd_static_scratch_addr[ctx->device] = p;
+  }
   return NVC_OK;
 }
 
@@ -163,4 +177,27 @@ extern "C" int nvc_paged_decode_attn(nvc_ctx* ctx, const nvc_bf16* q, int ldq, c
                                      void* stream) {
   return nvc_paged_decode_attn_ex(ctx, q, ldq, k_cache, v_cache, block_tables, max_blocks, max_blocks, context_lens, B,
                                   nh, kv, hd, block_size, scale, out, workspace, workspace_bytes, stream);
+}
+
+// K5 without any allocation (no counterpart in the reference): the same
+// kernels as nvc_paged_decode_attn, the KV-split partials in the library's static device array (4 MiB) instead of a caller
+// workspace.  Calls no cudaMalloc / cudaFree; every call on a device shares the one array, so calls that overlap on the GPU
+// (two streams) race - serialise them.  Nothing has to start at zero: every (sequence, head, split) partial the combine
+// kernel reads is written by the attention kernel of the same call.
+extern "C" size_t nvc_paged_decode_static_scratch_bytes(void) { return NVC_PD_STATIC_SCRATCH_BYTES; }
+
+extern "C" int nvc_paged_decode_attn_static(nvc_ctx* ctx, const nvc_bf16* q, int ldq, const nvc_bf16* k_cache,
+                                            const nvc_bf16* v_cache, const int32_t* block_tables, int max_blocks,
+                                            const int32_t* context_lens, int B, int nh, int kv, int hd, int block_size,
+                                            float scale, nvc_bf16* out, void* stream) {
+  NVC_REQUIRE(ctx, ctx != nullptr, NVC_EINVAL, "null context");
+  void* scratch = (ctx->device >= 0 && ctx->device < 64) ? g_pd_static_scratch_addr[ctx->device] : nullptr;
+  NVC_REQUIRE(ctx, scratch != nullptr, NVC_EDEVICE, "static scratch address was not resolved for this device");
+  const int rc = paged_decode_impl(ctx, q, ldq, k_cache, v_cache, block_tables, max_blocks, max_blocks, context_lens, B, nh,
+                                   kv, hd, block_size, scale, out, scratch, NVC_PD_STATIC_SCRATCH_BYTES, stream);
+  if (rc == NVC_ENOMEM)      // refused before any launch: the KV-split partials of this shape exceed the static array
+    nvc_set_error(ctx, "nvc_paged_decode_attn_static: the KV-split partials of B=" + std::to_string(B) + ", nh=" +
+                           std::to_string(nh) + " exceed the " + std::to_string(NVC_PD_STATIC_SCRATCH_BYTES) +
+                           "-byte static scratch; use nvc_paged_decode_attn with a caller workspace");
+  return rc;
 }
